@@ -1,0 +1,228 @@
+/*
+ * vmasb200.h - C ABI of libvmasb200.so: the B200-native (sm_100a) batched 2-D physics step of VMAS.
+ *
+ * This is the drop-in boundary for ONE hot path of the reference
+ * (robj0nes/VectorizedMultiAgentSimulator, all citations relative to its tree):
+ *
+ *   vmas/simulator/core.py:1971  World.step()        -> vmasb200_step / vmasb200_step_host
+ *   vmas/simulator/core.py:1661  World.cast_rays()   -> vmasb200_cast_rays (and the LIDAR epilogue of
+ *                                                        vmasb200_step, called from sensors.py:100 Lidar.measure)
+ *
+ * The reference has no FFI layer (it is pure Python/PyTorch); the binding a maintainer would add is the
+ * ctypes stub shown in INTEGRATION.md, and the host-side mirror that monkey-patches those two bound methods
+ * lives in vectorizedmultiagentsimulator_b200/dropin.py.
+ *
+ * Conventions
+ *   - plain C types only; every pointer is either HOST ("h:") or DEVICE ("d:") memory as annotated;
+ *   - every entry point returns 0 on success or a negative vmasb200_status; a thread-local, human readable
+ *     message for the last failure is returned by vmasb200_last_error();
+ *   - all device work is enqueued on the cudaStream_t passed as `stream` (NULL = legacy default stream);
+ *     no entry point synchronises the host unless its comment says so;
+ *   - a plan owns small device scratch (flag words) and must be used by one stream at a time;
+ *   - there is NO CPU fallback anywhere in this library: without a CUDA device every compute entry point
+ *     fails with VMASB200_ERR_CUDA.
+ *
+ * Data layout in HBM ("env records", env-major, fp32):
+ *   dyn   [n_envs][dyn_stride]   per dynamic entity (movable or rotatable), in entity order:
+ *                                 px py vx vy rot ang_vel                      (core.py:205-315 EntityState)
+ *   stat  [n_envs][stat_stride]  per static entity that can collide / is jointed / is a LIDAR target:
+ *                                 px py rot; then one float per joint whose fixed_rotation is per-env
+ *                                 (joints.py:139-143)
+ *   actout[n_envs][act_stride]   clamped fx fy torque of every agent that has max_f/f_range/max_t/t_range
+ *                                 (the write-back of core.py:2017-2040)
+ *   lidar [n_envs][lidar_stride] one float per ray, sensors concatenated in desc order (sensors.py:100-122)
+ * strides are padded to multiples of 4 floats so that every env record (and any run of records) is a legal
+ * cp.async.bulk (TMA 1-D) source/destination.  vmasb200_plan_layout() reports all offsets.
+ */
+#ifndef VMASB200_H_
+#define VMASB200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VMASB200_ABI_VERSION 1
+
+typedef enum vmasb200_status {
+  VMASB200_OK = 0,
+  VMASB200_ERR_INVALID = -1,      /* bad argument / inconsistent description            */
+  VMASB200_ERR_UNSUPPORTED = -2,  /* description uses something the kernel does not do  */
+  VMASB200_ERR_CUDA = -3,         /* a CUDA runtime call failed (no device, launch...)  */
+  VMASB200_ERR_NOMEM = -4
+} vmasb200_status;
+
+/* shape classes: core.py:102 Box, :140 Sphere, :171 Line */
+enum { VMASB200_SPHERE = 0, VMASB200_BOX = 1, VMASB200_LINE = 2 };
+
+/* entity flag bits (which optional attributes of core.py:537 Entity / :829 Agent are set) */
+enum {
+  VMASB200_E_MOVABLE = 1u << 0,
+  VMASB200_E_ROTATABLE = 1u << 1,
+  VMASB200_E_AGENT = 1u << 2,
+  VMASB200_E_HOLLOW = 1u << 3,        /* Box(hollow=True), core.py:103                      */
+  VMASB200_E_MAX_SPEED = 1u << 4,
+  VMASB200_E_V_RANGE = 1u << 5,
+  VMASB200_E_DRAG = 1u << 6,          /* entity.drag overrides world drag, core.py:2865     */
+  VMASB200_E_LIN_FRICTION = 1u << 7,  /* entity.linear_friction is not None, core.py:2075   */
+  VMASB200_E_ANG_FRICTION = 1u << 8,
+  VMASB200_E_GRAVITY = 1u << 9,       /* entity.gravity is not None, core.py:2048           */
+  VMASB200_E_MAX_F = 1u << 10,
+  VMASB200_E_F_RANGE = 1u << 11,
+  VMASB200_E_MAX_T = 1u << 12,
+  VMASB200_E_T_RANGE = 1u << 13,
+  VMASB200_E_COLLIDE = 1u << 14       /* entity.collide, core.py:620                        */
+};
+
+/* One row per entry of World.entities (landmarks first, then agents: core.py:1220). */
+typedef struct vmasb200_entity {
+  int32_t shape;              /* VMASB200_SPHERE / BOX / LINE                                         */
+  uint32_t flags;             /* VMASB200_E_*                                                         */
+  float radius;               /* Sphere.radius                                                        */
+  float length;               /* Box.length / Line.length                                             */
+  float width;                /* Box.width                                                            */
+  float mass;
+  float moment_of_inertia;    /* Shape.moment_of_inertia(mass), core.py:122,159,186 (double -> fp32)  */
+  float max_speed;
+  float v_range;
+  float drag;
+  float linear_friction;
+  float angular_friction;
+  float gravity[2];
+  float max_f, f_range, max_t, t_range;
+  double circumscribed_radius;/* core.py:125,162,189; kept in double: the broad phase adds two of them
+                                 in double before the fp32 compare (core.py:2796-2800)                */
+} vmasb200_entity;
+
+/* One row per JointConstraint (joints.py:147), in the order World._apply_vectorized_enviornment_force
+ * meets them (pair enumeration a<b, core.py:2111-2121). */
+typedef struct vmasb200_joint {
+  int32_t entity_a, entity_b;    /* indices into entities[] of constraint.entity_a / entity_b          */
+  float delta_a[2], delta_b[2];  /* shape.get_delta_from_anchor(anchor), joints.py:185-201             */
+  float dist;                    /* constraint.dist                                                     */
+  int32_t rotate;                /* constraint.rotate                                                   */
+  float fixed_rotation;          /* scalar fixed rotation (ignored when fixed_rotation_per_env != 0)   */
+  int32_t fixed_rotation_per_env;/* 1: value is read from the stat record (joints.py:139-143)          */
+} vmasb200_joint;
+
+/* One row per Lidar (sensors.py:46) whose measurement is produced by the step epilogue. */
+typedef struct vmasb200_lidar {
+  int32_t entity;          /* the sensing agent                                                       */
+  int32_t n_rays;
+  const float* angles;     /* h: [n_rays] sensor-frame ray angles (row 0 of Lidar._angles)            */
+  float max_range;
+  int32_t n_targets;
+  const int32_t* targets;  /* h: [n_targets] entity indices passing entity_filter, in entity order    */
+} vmasb200_lidar;
+
+typedef struct vmasb200_world_desc {
+  int32_t abi_version;     /* VMASB200_ABI_VERSION */
+  int32_t n_entities;
+  const vmasb200_entity* entities;  /* h: [n_entities]                                               */
+  /* h: [n_entities*n_entities] row-major; collide_mask[a*E+b] (a<b) != 0 iff the pair passes the STATIC
+   * part of World.collides (collide flags, both collision_filters, not both static, core.py:2787-2795)
+   * and is not excluded by a dist-0 joint (core.py:2118-2121).  The batch-wide distance test of
+   * core.py:2796-2800 is evaluated on the device every substep. */
+  const uint8_t* collide_mask;
+  int32_t n_joints;
+  const vmasb200_joint* joints;     /* h: [n_joints]                                                 */
+  int32_t n_lidars;
+  const vmasb200_lidar* lidars;     /* h: [n_lidars]                                                 */
+  /* World constants, core.py:1090-1143 */
+  float dt;
+  int32_t substeps;
+  float drag;
+  float linear_friction, angular_friction;
+  int32_t has_x_semidim, has_y_semidim;
+  float x_semidim, y_semidim;
+  float collision_force, joint_force, torque_constraint_force, contact_margin;
+  float gravity[2];
+  /* Kernel shape override: lanes cooperating on one environment (4, 8, 16 or 32); 0 = let the plan choose. */
+  int32_t lanes_per_env;
+} vmasb200_world_desc;
+
+enum { VMASB200_PAIR_SS = 0, VMASB200_PAIR_LS, VMASB200_PAIR_LL, VMASB200_PAIR_BS, VMASB200_PAIR_BL, VMASB200_PAIR_BB };
+
+typedef struct vmasb200_pair {
+  int32_t type;   /* VMASB200_PAIR_*                                                                   */
+  int32_t a, b;   /* entity indices in the reference's per-type order: (line,sphere) (box,sphere) (box,line) */
+} vmasb200_pair;
+
+typedef struct vmasb200_layout {
+  int32_t dyn_stride, stat_stride, act_stride, lidar_stride; /* floats per env record (multiples of 4)  */
+  int32_t n_pairs;        /* candidate pairs, in flag-bit order (ss, ls, ll, bs, bl, bb; a<b inside)     */
+  int32_t pair_words;     /* ceil(n_pairs/32): words per substep in pair_active_out                      */
+  int32_t lanes_per_env;  /* kernel shape actually chosen                                                 */
+  int32_t n_dyn, n_stat, n_agents, n_act_out;
+  int64_t alg_bytes_per_env; /* algorithmic HBM bytes per env-step (SURVEY 8d formula)                    */
+} vmasb200_layout;
+
+typedef struct vmasb200_plan vmasb200_plan;
+
+int vmasb200_version(void);
+const char* vmasb200_last_error(void);
+
+/* Builds the static plan (entity / pair / joint / sensor tables, record layout) and uploads it.
+ * Host only reads `desc` during the call.  Replaces the per-substep Python pair enumeration of core.py:2103-2173. */
+int vmasb200_plan_create(const vmasb200_world_desc* desc, vmasb200_plan** out);
+int vmasb200_plan_destroy(vmasb200_plan* plan);
+int vmasb200_plan_layout(const vmasb200_plan* plan, vmasb200_layout* out);
+/* Per-entity record slots: dyn_slot[e] / stat_slot[e] = float offset of the entity inside the dyn / stat
+ * record, or -1; act_slot[e] = float offset of the clamped (fx fy torque) triple in the actout record, or -1.
+ * h: each array [n_entities] (any may be NULL). */
+int vmasb200_plan_slots(const vmasb200_plan* plan, int32_t* dyn_slot, int32_t* stat_slot, int32_t* act_slot);
+/* h: pairs[n_pairs] */
+int vmasb200_plan_pairs(const vmasb200_plan* plan, vmasb200_pair* pairs);
+/* float offset inside the stat record of the per-env fixed rotation of joint j, or -1. h: [n_joints] */
+int vmasb200_plan_joint_slots(const vmasb200_plan* plan, int32_t* joint_slot);
+/* float offset inside the lidar record of sensor i. h: [n_lidars] */
+int vmasb200_plan_lidar_slots(const vmasb200_plan* plan, int32_t* lidar_slot);
+
+typedef struct vmasb200_step_io {
+  const float* dyn_in;             /* d: [n_envs][dyn_stride]                                           */
+  float* dyn_out;                  /* d: [n_envs][dyn_stride]; may alias dyn_in                         */
+  const float* stat;               /* d: [n_envs][stat_stride] (NULL iff stat_stride == 0)              */
+  /* agent.state.force / agent.state.torque of every agent, in entity order of the agents (core.py:2017-2040).
+   * h: arrays of n_agents device pointers + row strides in floats; a NULL pointer reads as zeros.        */
+  const float* const* force_ptrs;
+  const int64_t* force_strides;
+  const float* const* torque_ptrs;
+  const int64_t* torque_strides;
+  float* act_out;                  /* d: [n_envs][act_stride] or NULL (NULL iff act_stride == 0)        */
+  float* lidar_out;                /* d: [n_envs][lidar_stride]; NULL skips the LIDAR epilogue          */
+  uint32_t* pair_active_out;       /* d: [substeps][pair_words] batch-wide broad-phase results of
+                                      core.py:2796-2800 per (substep, pair), or NULL                     */
+  int64_t n_envs;
+  /* 0: one fused speculative launch + a device-side verified exact fix-up (no host sync);
+   * 1: always take the exact per-substep path (flag reduction before every substep).                    */
+  int32_t exact;
+  void* stream;                    /* cudaStream_t                                                       */
+} vmasb200_step_io;
+
+/* One World.step(): all substeps of {action/friction/gravity forces, joints, six collision pair types,
+ * semi-implicit Euler integration} plus the LIDAR epilogue, for every env.  Asynchronous. */
+int vmasb200_step(vmasb200_plan* plan, const vmasb200_step_io* io);
+
+/* Same step with HOST buffers: H2D of inputs, kernel(s), D2H of results, then a stream sync.
+ * h_force [n_envs][n_agents][2], h_torque [n_envs][n_agents] (either may be NULL = zeros).
+ * Output pointers may be NULL to skip that copy.  Device staging is owned by the plan and grows on demand. */
+int vmasb200_step_host(vmasb200_plan* plan, const float* h_dyn_in, const float* h_stat, const float* h_force,
+                       const float* h_torque, float* h_dyn_out, float* h_act_out, float* h_lidar_out,
+                       uint32_t* h_pair_active, int64_t n_envs, int32_t exact);
+
+/* World.cast_rays(entity, angles, max_range, entity_filter) (core.py:1661-1785) on the current records.
+ * angles d: [n_envs][n_rays] WORLD-frame ray angles with row stride `angles_stride` floats;
+ * targets h: [n_targets] entity indices (already filtered); out d: [n_envs][n_rays] contiguous. */
+int vmasb200_cast_rays(vmasb200_plan* plan, const float* dyn, const float* stat, int32_t entity,
+                       const float* angles, int64_t angles_stride, int32_t n_rays, float max_range,
+                       const int32_t* targets, int32_t n_targets, float* out, int64_t n_envs, void* stream);
+
+/* Synchronises `stream` and reports any deferred CUDA error; also returns, in *n_fixups (may be NULL), how many
+ * steps of this plan needed the exact fix-up path since creation. */
+int vmasb200_sync_check(vmasb200_plan* plan, void* stream, int64_t* n_fixups);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VMASB200_H_ */
