@@ -1,0 +1,231 @@
+// plan.cpp - builds the static plan from a vmasb200_world_desc (host only, no CUDA).
+//
+// Replaces the per-substep Python work of World._apply_vectorized_enviornment_force (core.py:2103-2173): pair
+// enumeration a<b, joint lookup, bucketing into s_s / l_s / l_l / b_s / b_l / b_b lists, and records the order in
+// which update_env_forces (core.py:2190-2198) adds each item to each entity.
+#include "plan.h"
+
+#include <algorithm>
+#include <cstring>
+
+namespace vb {
+
+static thread_local std::string g_err;
+void set_error(const std::string& msg) { g_err = msg; }
+const char* last_error() { return g_err.c_str(); }
+
+static inline int align4(int x) { return (x + 3) & ~3; }
+
+static int pair_type(int sa, int sb, bool& swap) {
+  swap = false;
+  if (sa == VMASB200_SPHERE && sb == VMASB200_SPHERE) return IT_SS;
+  if ((sa == VMASB200_LINE && sb == VMASB200_SPHERE) || (sb == VMASB200_LINE && sa == VMASB200_SPHERE)) {
+    swap = sb != VMASB200_SPHERE;  // (line, sphere), core.py:2134-2141
+    return IT_LS;
+  }
+  if (sa == VMASB200_LINE && sb == VMASB200_LINE) return IT_LL;
+  if ((sa == VMASB200_BOX && sb == VMASB200_SPHERE) || (sb == VMASB200_BOX && sa == VMASB200_SPHERE)) {
+    swap = sb != VMASB200_SPHERE;  // (box, sphere), core.py:2145-2152
+    return IT_BS;
+  }
+  if ((sa == VMASB200_BOX && sb == VMASB200_LINE) || (sb == VMASB200_BOX && sa == VMASB200_LINE)) {
+    swap = sb != VMASB200_LINE;  // (box, line), core.py:2156-2163
+    return IT_BL;
+  }
+  return IT_BB;
+}
+
+int build_plan(const vmasb200_world_desc* d, vmasb200_plan* pl) {
+  if (!d || d->abi_version != VMASB200_ABI_VERSION) { set_error("world desc: bad abi_version"); return VMASB200_ERR_INVALID; }
+  const int E = d->n_entities;
+  if (E <= 0 || !d->entities || !d->collide_mask) { set_error("world desc: no entities"); return VMASB200_ERR_INVALID; }
+  if (d->substeps < 1 || !(d->dt > 0.f)) { set_error("world desc: substeps >= 1 and dt > 0 required"); return VMASB200_ERR_INVALID; }
+  if (d->n_joints < 0 || d->n_lidars < 0 || (d->n_joints && !d->joints) || (d->n_lidars && !d->lidars)) {
+    set_error("world desc: bad joint / lidar tables"); return VMASB200_ERR_INVALID;
+  }
+  for (int e = 0; e < E; ++e) {
+    int sh = d->entities[e].shape;
+    if (sh != VMASB200_SPHERE && sh != VMASB200_BOX && sh != VMASB200_LINE) { set_error("world desc: unknown shape"); return VMASB200_ERR_INVALID; }
+  }
+  KParams& kp = pl->kp;
+  std::memset(&kp, 0, sizeof(kp));
+  kp.E = E; kp.S = d->substeps; kp.J = d->n_joints;
+
+  // ---- work items: joints first (core.py:2175), then candidate pairs bucketed by type (core.py:2124-2173)
+  pl->items.clear(); pl->pairs.clear();
+  for (int j = 0; j < d->n_joints; ++j) {
+    const vmasb200_joint& jt = d->joints[j];
+    if (jt.entity_a < 0 || jt.entity_a >= E || jt.entity_b < 0 || jt.entity_b >= E || jt.entity_a == jt.entity_b) {
+      set_error("world desc: joint entity index out of range"); return VMASB200_ERR_INVALID;
+    }
+    DItem it{};
+    it.type = IT_JOINT; it.a = jt.entity_a; it.b = jt.entity_b; it.thr = 0.f;
+    it.dax = jt.delta_a[0]; it.day = jt.delta_a[1]; it.dbx = jt.delta_b[0]; it.dby = jt.delta_b[1];
+    it.dist = jt.dist; it.rotate = jt.rotate; it.fixed_rot = jt.fixed_rotation; it.fr_off = -1;
+    pl->items.push_back(it);
+  }
+  for (int t = 0; t < 6; ++t)
+    for (int a = 0; a < E; ++a)
+      for (int b = a + 1; b < E; ++b) {
+        if (!d->collide_mask[a * E + b]) continue;
+        bool sw;
+        if (pair_type(d->entities[a].shape, d->entities[b].shape, sw) != t) continue;
+        DItem it{};
+        it.type = t; it.a = sw ? b : a; it.b = sw ? a : b; it.fr_off = -1;
+        it.thr = (float)(d->entities[a].circumscribed_radius + d->entities[b].circumscribed_radius);
+        pl->items.push_back(it);
+        pl->pairs.push_back(vmasb200_pair{t, it.a, it.b});
+      }
+  kp.n_items = (int)pl->items.size();
+  kp.P = kp.n_items - kp.J;
+  kp.pair_words = (kp.P + 31) / 32;
+
+  // ---- sensors (sensors.py:46-69, core.py:1677-1690)
+  pl->sensors.clear(); pl->rays.clear(); pl->targets.clear(); pl->lidar_slot.assign(d->n_lidars, 0);
+  int ray_off = 0;
+  for (int k = 0; k < d->n_lidars; ++k) {
+    const vmasb200_lidar& ld = d->lidars[k];
+    if (ld.entity < 0 || ld.entity >= E || ld.n_rays < 0 || ld.n_targets < 0 || (ld.n_rays && !ld.angles) || (ld.n_targets && !ld.targets)) {
+      set_error("world desc: bad lidar row"); return VMASB200_ERR_INVALID;
+    }
+    DSensor sn{};
+    sn.entity = ld.entity; sn.n_rays = ld.n_rays; sn.max_range = ld.max_range; sn.n_targets = ld.n_targets;
+    sn.tg_begin = (int)pl->targets.size(); sn.out_off = ray_off;
+    for (int t = 0; t < ld.n_targets; ++t) {
+      if (ld.targets[t] < 0 || ld.targets[t] >= E) { set_error("world desc: lidar target out of range"); return VMASB200_ERR_INVALID; }
+      pl->targets.push_back(ld.targets[t]);
+    }
+    for (int r = 0; r < ld.n_rays; ++r) pl->rays.push_back(DRay{k, ld.angles[r], ray_off + r, 0});
+    pl->lidar_slot[k] = ray_off;
+    ray_off += ld.n_rays;
+    pl->sensors.push_back(sn);
+  }
+  kp.n_sensors = d->n_lidars; kp.n_rays = ray_off;
+  kp.lidar_stride = align4(ray_off);
+
+  // ---- which entities are read by the step at all, and which need cos/sin
+  std::vector<char> used(E, 0), trig(E, 0);
+  for (const DItem& it : pl->items) {
+    used[it.a] = used[it.b] = 1;
+    switch (it.type) {
+      case IT_SS: break;
+      case IT_LS: case IT_BS: trig[it.a] = 1; break;
+      default: trig[it.a] = trig[it.b] = 1; break;  // LL, BL, BB, joints
+    }
+  }
+  for (const DSensor& sn : pl->sensors) {
+    used[sn.entity] = 1;
+    for (int t = 0; t < sn.n_targets; ++t) {
+      int e = pl->targets[sn.tg_begin + t];
+      used[e] = 1;
+      if (d->entities[e].shape != VMASB200_SPHERE) trig[e] = 1;
+    }
+  }
+
+  // ---- record layout + entity table
+  pl->ents.assign(E, DEnt{});
+  pl->dyn_slot.assign(E, -1); pl->stat_slot.assign(E, -1); pl->act_slot.assign(E, -1);
+  pl->dyn_list.clear(); pl->rot_list.clear(); pl->agent_entities.clear();
+  int dyn_off = 0, stat_off = 0, act_off = 0, n_act = 0, n_stat = 0;
+  for (int e = 0; e < E; ++e) {
+    const vmasb200_entity& s = d->entities[e];
+    DEnt& o = pl->ents[e];
+    o.shape = s.shape; o.flags = s.flags & 0x7fffu;
+    o.radius = s.radius; o.length = s.length; o.width = s.width;
+    o.mass = s.mass; o.moi = s.moment_of_inertia;
+    o.max_speed = s.max_speed; o.v_range = s.v_range;
+    const float drag = (s.flags & VMASB200_E_DRAG) ? s.drag : d->drag;
+    o.one_minus_drag = (float)(1.0 - (double)drag);
+    if (s.flags & VMASB200_E_LIN_FRICTION) { o.flags |= DE_LINF_ON; o.lin_fric = s.linear_friction; }
+    else if (d->linear_friction > 0.f) { o.flags |= DE_LINF_ON; o.lin_fric = d->linear_friction; }
+    if (s.flags & VMASB200_E_ANG_FRICTION) { o.flags |= DE_ANGF_ON; o.ang_fric = s.angular_friction; }
+    else if (d->angular_friction > 0.f) { o.flags |= DE_ANGF_ON; o.ang_fric = d->angular_friction; }
+    o.gx = s.gravity[0]; o.gy = s.gravity[1];
+    o.max_f = s.max_f; o.f_range = s.f_range; o.max_t = s.max_t; o.t_range = s.t_range;
+    o.dyn_off = o.stat_off = o.agent = o.act_off = o.rot_slot = -1;
+    const bool dynamic = s.flags & (VMASB200_E_MOVABLE | VMASB200_E_ROTATABLE);
+    if (s.flags & VMASB200_E_AGENT) {
+      o.agent = (int)pl->agent_entities.size();
+      pl->agent_entities.push_back(e);
+    }
+    if (dynamic) {
+      o.flags |= DE_DYNAMIC;
+      o.dyn_off = dyn_off; pl->dyn_slot[e] = dyn_off; dyn_off += 6;
+      o.fin_off = 3 * (int)pl->dyn_list.size();
+      pl->dyn_list.push_back(e);
+      if ((s.flags & VMASB200_E_AGENT) &&
+          (s.flags & (VMASB200_E_MAX_F | VMASB200_E_F_RANGE | VMASB200_E_MAX_T | VMASB200_E_T_RANGE))) {
+        o.act_off = act_off; pl->act_slot[e] = act_off; act_off += 3; ++n_act;
+      }
+    } else if (used[e]) {
+      o.stat_off = stat_off; pl->stat_slot[e] = stat_off; stat_off += 3; ++n_stat;
+    }
+    if (trig[e]) {
+      o.flags |= DE_TRIG;
+      o.rot_slot = (int)pl->rot_list.size();
+      pl->rot_list.push_back(e);
+    }
+  }
+  kp.A = (int)pl->agent_entities.size();
+  if (kp.A > kMaxAgents) { set_error("more than 96 agents are not supported by the CUDA step"); return VMASB200_ERR_UNSUPPORTED; }
+  pl->joint_slot.assign(d->n_joints, -1);
+  for (int j = 0; j < d->n_joints; ++j)
+    if (d->joints[j].fixed_rotation_per_env && !d->joints[j].rotate) {
+      pl->items[j].fr_off = stat_off; pl->joint_slot[j] = stat_off; stat_off += 1;
+    }
+  kp.n_dyn = (int)pl->dyn_list.size();
+  kp.n_rot = (int)pl->rot_list.size();
+  kp.dyn_stride = align4(dyn_off); kp.stat_stride = align4(stat_off); kp.act_stride = align4(act_off);
+
+  // ---- contribution lists in reference order (joints, then ss, ls, ll, bs, bl, bb; a before b)
+  pl->csr.clear();
+  for (int e : pl->dyn_list) {
+    DEnt& o = pl->ents[e];
+    o.csr_begin = (int)pl->csr.size();
+    for (int i = 0; i < kp.n_items; ++i) {
+      if (pl->items[i].a == e) pl->csr.push_back((i << 1) | 0);
+      if (pl->items[i].b == e) pl->csr.push_back((i << 1) | 1);
+    }
+    o.csr_end = (int)pl->csr.size();
+  }
+
+  // ---- kernel shape
+  int G = d->lanes_per_env;
+  if (G == 0) {
+    int target = std::max(std::max(kp.n_items, kp.n_dyn), (kp.n_rays + 1) / 2);
+    G = 1;
+    while (G < 32 && G * 2 <= target) G *= 2;
+  }
+  if (G < 1 || G > 32 || (G & (G - 1))) { set_error("lanes_per_env must be a power of two <= 32"); return VMASB200_ERR_INVALID; }
+  kp.G = G;
+  kp.off_fin = 0;
+  kp.off_rot = align4(3 * kp.n_dyn);
+  kp.off_res = kp.off_rot + 4 * kp.n_rot;
+  kp.off_frc = kp.off_res + 4 * kp.n_items;
+  kp.work_stride = align4(kp.off_frc + 3 * kp.A);
+  if (((kp.work_stride / 4) & 1) == 0) kp.work_stride += 4;  // odd number of float4 per env: groups hit distinct banks
+  const int per_env = 4 * (kp.dyn_stride + kp.stat_stride + kp.act_stride + kp.lidar_stride + kp.work_stride);
+  const int fixed = 16 + 8 * kp.S * kp.pair_words + 16;
+  const int budget = 200 * 1024;
+  int TE = 256 / G;
+  while (TE > 1 && fixed + TE * per_env > budget) TE /= 2;
+  if (fixed + TE * per_env > 227 * 1024) { set_error("world too large for one CTA's shared memory"); return VMASB200_ERR_UNSUPPORTED; }
+  kp.TE = TE;
+
+  // ---- world constants
+  kp.sub_dt = (float)((double)d->dt / (double)d->substeps);  // core.py:1124 (Python doubles)
+  kp.Kc = d->collision_force; kp.Kj = d->joint_force; kp.Kt = d->torque_constraint_force; kp.margin = d->contact_margin;
+  kp.xs = d->x_semidim; kp.ys = d->y_semidim; kp.has_xs = d->has_x_semidim; kp.has_ys = d->has_y_semidim;
+  kp.wgx = d->gravity[0]; kp.wgy = d->gravity[1];
+  kp.has_wgrav = !(d->gravity[0] == 0.f && d->gravity[1] == 0.f);  // core.py:2044
+
+  vmasb200_layout& L = pl->layout;
+  L.dyn_stride = kp.dyn_stride; L.stat_stride = kp.stat_stride; L.act_stride = kp.act_stride; L.lidar_stride = kp.lidar_stride;
+  L.n_pairs = kp.P; L.pair_words = kp.pair_words; L.lanes_per_env = kp.G;
+  L.n_dyn = kp.n_dyn; L.n_stat = n_stat; L.n_agents = kp.A; L.n_act_out = n_act;
+  // state read + write, static pose read, action read, clamped action write, lidar write
+  L.alg_bytes_per_env = 4ll * (12 * kp.n_dyn + 3 * n_stat + 3 * kp.A + 3 * n_act + kp.n_rays);
+  return VMASB200_OK;
+}
+
+}  // namespace vb

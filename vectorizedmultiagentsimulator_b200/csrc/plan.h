@@ -1,0 +1,39 @@
+// plan.h - host-side plan object behind the opaque vmasb200_plan of include/vmasb200.h.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/vmasb200.h"
+#include "tables.h"
+
+struct vmasb200_plan {
+  vb::KParams kp{};  // device pointers are filled by upload()
+  vmasb200_layout layout{};
+  // host copies of the tables
+  std::vector<vb::DEnt> ents;
+  std::vector<vb::DItem> items;
+  std::vector<int32_t> csr, dyn_list, rot_list, targets;
+  std::vector<vb::DRay> rays;
+  std::vector<vb::DSensor> sensors;
+  std::vector<vmasb200_pair> pairs;
+  std::vector<int32_t> dyn_slot, stat_slot, act_slot, joint_slot, lidar_slot, agent_entities;
+  int smem_bytes = 0;
+  // device side (lazy: nothing CUDA happens before the first compute call)
+  bool uploaded = false;
+  int device = -1;
+  void* d_blob = nullptr;
+  uint32_t* d_bits = nullptr;  // [3][S][pair_words]: exact flags, any, thin
+  // staging of vmasb200_step_host
+  int64_t host_cap = 0;
+  float *d_dyn = nullptr, *d_stat = nullptr, *d_force = nullptr, *d_torque = nullptr, *d_act = nullptr, *d_lidar = nullptr;
+  int64_t n_fixups = 0;
+};
+
+namespace vb {
+void set_error(const std::string& msg);
+const char* last_error();
+int build_plan(const vmasb200_world_desc* desc, vmasb200_plan* pl);  // pure host
+int upload_plan(vmasb200_plan* pl);                                  // first CUDA touch
+}  // namespace vb

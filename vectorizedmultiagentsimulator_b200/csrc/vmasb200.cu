@@ -1,0 +1,285 @@
+// vmasb200.cu - C ABI of libvmasb200.so (include/vmasb200.h): plan upload, launches, host-buffer entry point.
+// Compiled with -fmad=false: every reference torch op is one rounded fp32 instruction (see geom.cuh).
+#include <cstdio>
+#include <cstring>
+#include <new>
+
+#include "kernels.cuh"
+#include "plan.h"
+
+namespace vb {
+const char* last_error();
+
+#define VB_CUDA(call)                                                                          \
+  do {                                                                                         \
+    cudaError_t e_ = (call);                                                                   \
+    if (e_ != cudaSuccess) {                                                                   \
+      set_error(std::string(#call) + ": " + cudaGetErrorString(e_));                           \
+      return VMASB200_ERR_CUDA;                                                                \
+    }                                                                                          \
+  } while (0)
+
+template <class T>
+static size_t put(std::vector<char>& blob, const std::vector<T>& v) {
+  size_t off = (blob.size() + 15) & ~size_t(15);
+  blob.resize(off + std::max<size_t>(v.size() * sizeof(T), 16));
+  if (!v.empty()) std::memcpy(blob.data() + off, v.data(), v.size() * sizeof(T));
+  return off;
+}
+
+int upload_plan(vmasb200_plan* pl) {
+  if (pl->uploaded) return VMASB200_OK;
+  int ndev = 0;
+  VB_CUDA(cudaGetDeviceCount(&ndev));
+  if (ndev <= 0) { set_error("no CUDA device: libvmasb200 has no CPU fallback"); return VMASB200_ERR_CUDA; }
+  VB_CUDA(cudaGetDevice(&pl->device));
+  std::vector<char> blob;
+  size_t o_ent = put(blob, pl->ents), o_item = put(blob, pl->items), o_csr = put(blob, pl->csr);
+  size_t o_dyn = put(blob, pl->dyn_list), o_rot = put(blob, pl->rot_list), o_ray = put(blob, pl->rays);
+  size_t o_sen = put(blob, pl->sensors), o_tg = put(blob, pl->targets);
+  VB_CUDA(cudaMalloc(&pl->d_blob, blob.size()));
+  VB_CUDA(cudaMemcpy(pl->d_blob, blob.data(), blob.size(), cudaMemcpyHostToDevice));
+  char* b = static_cast<char*>(pl->d_blob);
+  KParams& kp = pl->kp;
+  kp.ents = reinterpret_cast<const DEnt*>(b + o_ent);
+  kp.items = reinterpret_cast<const DItem*>(b + o_item);
+  kp.csr = reinterpret_cast<const int32_t*>(b + o_csr);
+  kp.dyn_list = reinterpret_cast<const int32_t*>(b + o_dyn);
+  kp.rot_list = reinterpret_cast<const int32_t*>(b + o_rot);
+  kp.rays = reinterpret_cast<const DRay*>(b + o_ray);
+  kp.sensors = reinterpret_cast<const DSensor*>(b + o_sen);
+  kp.targets = reinterpret_cast<const int32_t*>(b + o_tg);
+  size_t nbits = 3 * (size_t)kp.S * std::max(kp.pair_words, 1) * sizeof(uint32_t);
+  VB_CUDA(cudaMalloc(&pl->d_bits, nbits));
+  VB_CUDA(cudaMemset(pl->d_bits, 0, nbits));
+  pl->smem_bytes = smem_map(kp).total_bytes;
+  VB_CUDA(cudaFuncSetAttribute(step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+  pl->uploaded = true;
+  return VMASB200_OK;
+}
+
+static int check_io(const vmasb200_plan* pl, const vmasb200_step_io* io) {
+  const KParams& kp = pl->kp;
+  if (!io || io->n_envs < 0) { set_error("step: bad io"); return VMASB200_ERR_INVALID; }
+  if (!io->dyn_in || !io->dyn_out) { set_error("step: dyn_in / dyn_out are required"); return VMASB200_ERR_INVALID; }
+  if (kp.stat_stride && !io->stat) { set_error("step: stat record missing"); return VMASB200_ERR_INVALID; }
+  if (kp.act_stride && !io->act_out) { set_error("step: act_out missing"); return VMASB200_ERR_INVALID; }
+  if (kp.A && (!io->force_ptrs || !io->torque_ptrs || !io->force_strides || !io->torque_strides)) {
+    set_error("step: force / torque pointer tables missing"); return VMASB200_ERR_INVALID;
+  }
+  auto mis = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) != 0; };
+  if (mis(io->dyn_in) || mis(io->dyn_out) || mis(io->stat) || mis(io->act_out) || mis(io->lidar_out)) {
+    set_error("step: env records must be 16-byte aligned (TMA bulk copies)"); return VMASB200_ERR_INVALID;
+  }
+  return VMASB200_OK;
+}
+
+static int launch_step(vmasb200_plan* pl, const vmasb200_step_io* io) {
+  const KParams& kp = pl->kp;
+  cudaStream_t st = static_cast<cudaStream_t>(io->stream);
+  AgentIO aio;
+  std::memset(&aio, 0, sizeof(aio));
+  for (int a = 0; a < kp.A; ++a) {
+    aio.force[a] = io->force_ptrs[a]; aio.torque[a] = io->torque_ptrs[a];
+    aio.fstride[a] = (int32_t)io->force_strides[a]; aio.tstride[a] = (int32_t)io->torque_strides[a];
+  }
+  const int nw = kp.S * kp.pair_words;
+  uint32_t* flags = pl->d_bits;
+  uint32_t* any = pl->d_bits + (size_t)kp.S * std::max(kp.pair_words, 1);
+  uint32_t* thin = any + (size_t)kp.S * std::max(kp.pair_words, 1);
+  StepArgs sa{};
+  sa.dyn_in = io->dyn_in; sa.dyn_out = io->dyn_out; sa.stat = io->stat; sa.act_out = io->act_out;
+  sa.lidar_out = io->lidar_out; sa.n_envs = io->n_envs;
+  const unsigned grid = (unsigned)((io->n_envs + kp.TE - 1) / kp.TE);
+  const unsigned block = (unsigned)(kp.TE * kp.G);
+  if (io->exact) {
+    // exact path: the batch-wide World.collides verdicts are reduced before every substep (core.py:2796-2800)
+    if (nw) VB_CUDA(cudaMemsetAsync(flags, 0, nw * sizeof(uint32_t), st));
+    for (int s = 0; s < kp.S; ++s) {
+      if (kp.P) {
+        unsigned fg = (unsigned)((io->n_envs + 255) / 256);
+        flags_kernel<<<fg, 256, 0, st>>>(kp, sa.dyn_in, sa.stat, io->n_envs, s, flags);
+      }
+      sa.s_begin = s; sa.s_end = s + 1; sa.flags_in = flags; sa.any_out = nullptr; sa.thin_out = nullptr;
+      sa.do_lidar = (s == kp.S - 1);
+      step_kernel<<<grid, block, pl->smem_bytes, st>>>(kp, aio, sa);
+      sa.dyn_in = io->dyn_out;
+    }
+    if (io->pair_active_out && nw) VB_CUDA(cudaMemcpyAsync(io->pair_active_out, flags, nw * sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
+  } else {
+    if (nw) VB_CUDA(cudaMemsetAsync(any, 0, 2 * (size_t)kp.S * std::max(kp.pair_words, 1) * sizeof(uint32_t), st));
+    sa.s_begin = 0; sa.s_end = kp.S; sa.flags_in = nullptr; sa.any_out = any; sa.thin_out = thin; sa.do_lidar = 1;
+    step_kernel<<<grid, block, pl->smem_bytes, st>>>(kp, aio, sa);
+    if (io->pair_active_out && nw) VB_CUDA(cudaMemcpyAsync(io->pair_active_out, any, nw * sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
+  }
+  VB_CUDA(cudaGetLastError());
+  return VMASB200_OK;
+}
+
+}  // namespace vb
+
+using namespace vb;
+
+extern "C" {
+
+int vmasb200_version(void) { return VMASB200_ABI_VERSION; }
+const char* vmasb200_last_error(void) { return vb::last_error(); }
+
+int vmasb200_plan_create(const vmasb200_world_desc* desc, vmasb200_plan** out) {
+  if (!out) { set_error("plan_create: out is NULL"); return VMASB200_ERR_INVALID; }
+  *out = nullptr;
+  vmasb200_plan* pl = new (std::nothrow) vmasb200_plan();
+  if (!pl) { set_error("out of host memory"); return VMASB200_ERR_NOMEM; }
+  int rc = build_plan(desc, pl);
+  if (rc != VMASB200_OK) { delete pl; return rc; }
+  *out = pl;
+  return VMASB200_OK;
+}
+
+int vmasb200_plan_destroy(vmasb200_plan* pl) {
+  if (!pl) return VMASB200_OK;
+  if (pl->uploaded) {
+    cudaFree(pl->d_blob); cudaFree(pl->d_bits);
+    cudaFree(pl->d_dyn); cudaFree(pl->d_stat); cudaFree(pl->d_force); cudaFree(pl->d_torque); cudaFree(pl->d_act); cudaFree(pl->d_lidar);
+  }
+  delete pl;
+  return VMASB200_OK;
+}
+
+int vmasb200_plan_layout(const vmasb200_plan* pl, vmasb200_layout* out) {
+  if (!pl || !out) { set_error("plan_layout: NULL argument"); return VMASB200_ERR_INVALID; }
+  *out = pl->layout;
+  return VMASB200_OK;
+}
+
+int vmasb200_plan_slots(const vmasb200_plan* pl, int32_t* dyn_slot, int32_t* stat_slot, int32_t* act_slot) {
+  if (!pl) { set_error("plan_slots: NULL plan"); return VMASB200_ERR_INVALID; }
+  const size_t n = pl->dyn_slot.size() * sizeof(int32_t);
+  if (dyn_slot) std::memcpy(dyn_slot, pl->dyn_slot.data(), n);
+  if (stat_slot) std::memcpy(stat_slot, pl->stat_slot.data(), n);
+  if (act_slot) std::memcpy(act_slot, pl->act_slot.data(), n);
+  return VMASB200_OK;
+}
+
+int vmasb200_plan_pairs(const vmasb200_plan* pl, vmasb200_pair* pairs) {
+  if (!pl || (!pairs && !pl->pairs.empty())) { set_error("plan_pairs: NULL argument"); return VMASB200_ERR_INVALID; }
+  if (!pl->pairs.empty()) std::memcpy(pairs, pl->pairs.data(), pl->pairs.size() * sizeof(vmasb200_pair));
+  return VMASB200_OK;
+}
+
+int vmasb200_plan_joint_slots(const vmasb200_plan* pl, int32_t* joint_slot) {
+  if (!pl) { set_error("plan_joint_slots: NULL plan"); return VMASB200_ERR_INVALID; }
+  if (joint_slot && !pl->joint_slot.empty()) std::memcpy(joint_slot, pl->joint_slot.data(), pl->joint_slot.size() * sizeof(int32_t));
+  return VMASB200_OK;
+}
+
+int vmasb200_plan_lidar_slots(const vmasb200_plan* pl, int32_t* lidar_slot) {
+  if (!pl) { set_error("plan_lidar_slots: NULL plan"); return VMASB200_ERR_INVALID; }
+  if (lidar_slot && !pl->lidar_slot.empty()) std::memcpy(lidar_slot, pl->lidar_slot.data(), pl->lidar_slot.size() * sizeof(int32_t));
+  return VMASB200_OK;
+}
+
+int vmasb200_step(vmasb200_plan* pl, const vmasb200_step_io* io) {
+  if (!pl) { set_error("step: NULL plan"); return VMASB200_ERR_INVALID; }
+  int rc = check_io(pl, io);
+  if (rc) return rc;
+  if ((rc = upload_plan(pl))) return rc;
+  if (io->n_envs == 0 || pl->kp.n_dyn == 0) return VMASB200_OK;
+  return launch_step(pl, io);
+}
+
+static int grow_host_staging(vmasb200_plan* pl, int64_t n) {
+  if (n <= pl->host_cap) return VMASB200_OK;
+  const KParams& kp = pl->kp;
+  cudaFree(pl->d_dyn); cudaFree(pl->d_stat); cudaFree(pl->d_force); cudaFree(pl->d_torque); cudaFree(pl->d_act); cudaFree(pl->d_lidar);
+  pl->d_dyn = pl->d_stat = pl->d_force = pl->d_torque = pl->d_act = pl->d_lidar = nullptr;
+  pl->host_cap = 0;
+  auto bytes = [&](int stride) { return std::max<size_t>((size_t)n * stride * sizeof(float), 16); };
+  VB_CUDA(cudaMalloc(&pl->d_dyn, bytes(kp.dyn_stride)));
+  VB_CUDA(cudaMalloc(&pl->d_stat, bytes(kp.stat_stride)));
+  VB_CUDA(cudaMalloc(&pl->d_force, bytes(2 * kp.A)));
+  VB_CUDA(cudaMalloc(&pl->d_torque, bytes(kp.A)));
+  VB_CUDA(cudaMalloc(&pl->d_act, bytes(kp.act_stride)));
+  VB_CUDA(cudaMalloc(&pl->d_lidar, bytes(kp.lidar_stride)));
+  pl->host_cap = n;
+  return VMASB200_OK;
+}
+
+int vmasb200_step_host(vmasb200_plan* pl, const float* h_dyn_in, const float* h_stat, const float* h_force,
+                       const float* h_torque, float* h_dyn_out, float* h_act_out, float* h_lidar_out,
+                       uint32_t* h_pair_active, int64_t n, int32_t exact) {
+  if (!pl || !h_dyn_in || n < 0) { set_error("step_host: bad argument"); return VMASB200_ERR_INVALID; }
+  int rc = upload_plan(pl);
+  if (rc) return rc;
+  const KParams& kp = pl->kp;
+  if (kp.stat_stride && !h_stat) { set_error("step_host: stat record missing"); return VMASB200_ERR_INVALID; }
+  if (n == 0) return VMASB200_OK;
+  if ((rc = grow_host_staging(pl, n))) return rc;
+  cudaStream_t st = nullptr;
+  VB_CUDA(cudaMemcpyAsync(pl->d_dyn, h_dyn_in, (size_t)n * kp.dyn_stride * 4, cudaMemcpyHostToDevice, st));
+  if (kp.stat_stride) VB_CUDA(cudaMemcpyAsync(pl->d_stat, h_stat, (size_t)n * kp.stat_stride * 4, cudaMemcpyHostToDevice, st));
+  if (kp.A && h_force) VB_CUDA(cudaMemcpyAsync(pl->d_force, h_force, (size_t)n * kp.A * 8, cudaMemcpyHostToDevice, st));
+  if (kp.A && h_torque) VB_CUDA(cudaMemcpyAsync(pl->d_torque, h_torque, (size_t)n * kp.A * 4, cudaMemcpyHostToDevice, st));
+  const float* fptr[kMaxAgents]; const float* tptr[kMaxAgents];
+  int64_t fstr[kMaxAgents], tstr[kMaxAgents];
+  for (int a = 0; a < kp.A; ++a) {  // h_force [n][A][2], h_torque [n][A]
+    fptr[a] = h_force ? pl->d_force + 2 * a : nullptr; fstr[a] = 2 * kp.A;
+    tptr[a] = h_torque ? pl->d_torque + a : nullptr; tstr[a] = kp.A;
+  }
+  vmasb200_step_io io{};
+  io.dyn_in = pl->d_dyn; io.dyn_out = pl->d_dyn; io.stat = pl->d_stat;
+  io.force_ptrs = fptr; io.force_strides = fstr; io.torque_ptrs = tptr; io.torque_strides = tstr;
+  io.act_out = kp.act_stride ? pl->d_act : nullptr;
+  io.lidar_out = (kp.lidar_stride && h_lidar_out) ? pl->d_lidar : nullptr;
+  uint32_t* d_pa = nullptr;
+  io.pair_active_out = nullptr; io.n_envs = n; io.exact = exact; io.stream = st;
+  (void)d_pa;
+  if (kp.n_dyn && (rc = launch_step(pl, &io))) return rc;
+  if (h_dyn_out) VB_CUDA(cudaMemcpyAsync(h_dyn_out, pl->d_dyn, (size_t)n * kp.dyn_stride * 4, cudaMemcpyDeviceToHost, st));
+  if (h_act_out && kp.act_stride) VB_CUDA(cudaMemcpyAsync(h_act_out, pl->d_act, (size_t)n * kp.act_stride * 4, cudaMemcpyDeviceToHost, st));
+  if (h_lidar_out && kp.lidar_stride) VB_CUDA(cudaMemcpyAsync(h_lidar_out, pl->d_lidar, (size_t)n * kp.lidar_stride * 4, cudaMemcpyDeviceToHost, st));
+  if (h_pair_active && kp.S * kp.pair_words) {
+    const uint32_t* src = exact ? pl->d_bits : pl->d_bits + (size_t)kp.S * std::max(kp.pair_words, 1);
+    VB_CUDA(cudaMemcpyAsync(h_pair_active, src, (size_t)kp.S * kp.pair_words * 4, cudaMemcpyDeviceToHost, st));
+  }
+  VB_CUDA(cudaStreamSynchronize(st));
+  return VMASB200_OK;
+}
+
+int vmasb200_cast_rays(vmasb200_plan* pl, const float* dyn, const float* stat, int32_t entity, const float* angles,
+                       int64_t angles_stride, int32_t n_rays, float max_range, const int32_t* targets,
+                       int32_t n_targets, float* out, int64_t n, void* stream) {
+  if (!pl || !dyn || !angles || !out || n < 0 || n_rays < 0 || n_targets < 0 || (n_targets && !targets)) {
+    set_error("cast_rays: bad argument"); return VMASB200_ERR_INVALID;
+  }
+  int rc = upload_plan(pl);
+  if (rc) return rc;
+  const KParams& kp = pl->kp;
+  if (entity < 0 || entity >= kp.E) { set_error("cast_rays: entity out of range"); return VMASB200_ERR_INVALID; }
+  auto has_rec = [&](int e) { return pl->ents[e].dyn_off >= 0 || pl->ents[e].stat_off >= 0; };
+  if (!has_rec(entity)) { set_error("cast_rays: the casting entity has no record in this plan"); return VMASB200_ERR_INVALID; }
+  if (n_targets > 64) { set_error("cast_rays: more than 64 targets"); return VMASB200_ERR_UNSUPPORTED; }
+  for (int t = 0; t < n_targets; ++t)
+    if (targets[t] < 0 || targets[t] >= kp.E || !has_rec(targets[t])) {
+      set_error("cast_rays: a target has no record in this plan"); return VMASB200_ERR_INVALID;
+    }
+  if (n == 0 || n_rays == 0) return VMASB200_OK;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  RayTargets rt;
+  rt.n = n_targets;
+  for (int t = 0; t < n_targets; ++t) rt.e[t] = targets[t];
+  const long long total = (long long)n * n_rays;
+  cast_rays_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(kp, dyn, stat ? stat : dyn, entity, angles, angles_stride,
+                                                                   n_rays, max_range, rt, out, n);
+  VB_CUDA(cudaGetLastError());
+  return VMASB200_OK;
+}
+
+int vmasb200_sync_check(vmasb200_plan* pl, void* stream, int64_t* n_fixups) {
+  VB_CUDA(cudaStreamSynchronize(static_cast<cudaStream_t>(stream)));
+  VB_CUDA(cudaGetLastError());
+  if (n_fixups) *n_fixups = pl ? pl->n_fixups : 0;
+  return VMASB200_OK;
+}
+
+}  // extern "C"
