@@ -1,0 +1,333 @@
+#!/usr/bin/env python
+"""bench.py - env-steps/s of the batched physics step (World.step + LIDAR epilogue) on N B200s.
+
+Contract: `python bench.py --gpus N --steps K --warmup W` prints ONE JSON line on rank 0 (see DESIGN.md "Measurement").
+A "step" is one World.step (all substeps + the LIDAR epilogue) over the whole env batch.
+`--impl reference` times the reference's own torch CPU path (oracle/_ref, the patched copy of the reference made by
+oracle/make_ref.sh) when it is present, else the C oracle port, on the host cores.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "env_steps_per_sec"
+L2_BYTES = 126 * 1024 * 1024
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--scenario", default="navigation")
+    ap.add_argument("--num-envs", type=int, default=32768, help="environments PER GPU (weak scaling)")
+    ap.add_argument("--lanes", type=int, default=0, help="lanes per env override (0 = plan default)")
+    ap.add_argument("--exact", type=int, default=0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.p = [], None
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                       "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.p = None
+
+    def _read(self):
+        for line in self.p.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.p is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.p.terminate()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1]))
+            except Exception:
+                continue
+            for n, v in zip(names, r[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def dist_env():
+    return int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def cpu_port_rate(wl, seconds=8.0, n_sample=None, threads=0):
+    """The C oracle (oracle/vmas_oracle.c: scalar port of the reference step, OpenMP over envs) timed on the host."""
+    from oracle.oracle import Oracle
+
+    n = min(wl.n_envs, n_sample or wl.n_envs)
+    orc = Oracle(wl.desc, n_threads=threads)
+    st = np.ascontiguousarray(wl.state0[:, :n].copy())
+    jr = np.ascontiguousarray(wl.jrot0[:, :n]) if wl.jrot0.size else None
+    f, t = wl.random_actions(4)
+    f = [np.ascontiguousarray(x[:n].transpose(1, 0, 2)) for x in f]
+    t = [np.ascontiguousarray(x[:n].transpose(1, 0)) for x in t]
+    steps, t0 = 0, time.perf_counter()
+    while True:
+        orc.step(st, f[steps % 4].copy(), t[steps % 4].copy(), jr, want_masks=False)
+        for k in range(len(wl.desc.lidars)):
+            orc.lidar(st, k)
+        steps += 1
+        el = time.perf_counter() - t0
+        if el >= seconds and steps >= 3:
+            break
+    cores = threads or (os.cpu_count() or 1)
+    return n * steps / el, cores, f"{steps} steps x {n} envs of {wl.scenario} ({el:.1f} s)"
+
+
+def run_reference(args, rank, world):
+    """Reference arm: the reference's own CPU implementation of the path, on the host cores (rank 0 only)."""
+    if rank != 0:
+        return
+    from vectorizedmultiagentsimulator_b200.workload import Workload
+
+    ref_dir = os.path.join(ROOT, "oracle", "_ref")
+    line = {"impl": "reference", "metric": METRIC, "unit": "env-steps/s", "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic"}
+    n = args.num_envs
+    value = kind = sample = None
+    cores = os.cpu_count() or 1
+    if os.path.isdir(os.path.join(ref_dir, "vmas")):
+        try:
+            value, sample = _time_ref_torch(args, ref_dir, n)
+            kind = "reference"
+        except Exception as e:  # the copy did not import on this box: fall back to the port, say so
+            sample = f"oracle/_ref failed ({type(e).__name__}: {e}); "
+    if value is None:
+        wl = Workload(args.scenario, n, seed=0)
+        value, cores, s2 = cpu_port_rate(wl, seconds=max(2.0, 0.05 * args.steps))
+        kind, sample = "port", (sample or "") + s2
+    line.update({"value": value, "ms_per_step": 1e3 * n / value,
+                 "config": {"workload": f"{args.scenario} num_envs={n} (host CPU, {kind})"},
+                 "cpu_baseline": {"value": value, "unit": "env-steps/s", "cores": cores, "kind": kind, "sample": sample},
+                 "e2e": {"value": value, "unit": "env-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                 "gpu_launches": 0})
+    print(json.dumps(line), flush=True)
+
+
+def _time_ref_torch(args, ref_dir, n):
+    """World.step + Lidar.measure of the UNMODIFIED reference physics (oracle/_ref = reference copy with the one-line
+    import fix of oracle/make_ref.sh) under torch CPU with all host threads."""
+    import torch
+
+    sys.path.insert(0, ref_dir)
+    sys.path.insert(0, os.path.join(ROOT, "oracle", "gym_stub"))
+    import vmas  # noqa
+
+    from vectorizedmultiagentsimulator_b200.workload import Workload
+
+    torch.set_num_threads(os.cpu_count() or 1)
+    wl = Workload(args.scenario, 1, seed=0)  # fixture meta: reference scenario name, kwargs, substeps, action scale
+    env = vmas.make_env(wl.meta["scenario"], num_envs=n, device="cpu", seed=0, continuous_actions=True, **wl.meta["kwargs"])
+    world = env.world
+    if world._substeps != wl.desc.substeps:  # "transport, substeps>1": imposed on the built world (note i)
+        world._substeps, world._sub_dt = wl.desc.substeps, world._dt / wl.desc.substeps
+    agents = list(world.agents)
+    g = torch.Generator().manual_seed(1234)
+    scale = [float(v) for v in wl.f_scale]
+
+    def one():
+        for a, sc in zip(agents, scale):
+            a.state.force = (torch.rand(n, 2, generator=g) * 2 - 1) * sc
+        world.step()
+        for a in agents:
+            for s in a.sensors or []:
+                s.measure()
+
+    for _ in range(args.warmup):
+        one()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        one()
+    el = time.perf_counter() - t0
+    return n * args.steps / el, f"{args.steps} steps x {n} envs, reference torch {torch.__version__} CPU World.step + Lidar.measure, {torch.get_num_threads()} threads ({el:.1f} s)"
+
+
+def run_b200(args, rank, local_rank, world):
+    import torch
+    import torch.distributed as dist
+
+    from vectorizedmultiagentsimulator_b200.plan import StepPlan
+    from vectorizedmultiagentsimulator_b200.workload import Workload
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (the CUDA step has no CPU fallback)")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    n = args.num_envs
+    wl = Workload(args.scenario, n, seed=rank)
+    wl.desc.lanes_per_env = args.lanes
+    plan = StepPlan(wl.desc)
+    A, K, W = plan.A, args.steps, args.warmup
+
+    # R independent env batches visited round-robin so that a step's inputs come from HBM, not from L2
+    per_batch = 4 * n * (2 * plan.dyn_stride + plan.stat_stride + plan.act_stride + plan.lidar_stride + 3 * A)
+    R = max(2, min(64, -(-2 * L2_BYTES // max(per_batch, 1))))
+    dyn0, stat0 = plan.pack(wl.state0, wl.jrot0 if wl.jrot0.size else None)
+    f_all, t_all = wl.random_actions(R)
+    stream = torch.cuda.current_stream().cuda_stream
+    ios, keep = [], []
+    for r in range(R):
+        dyn = torch.from_numpy(dyn0).to(dev)
+        stat = torch.from_numpy(stat0).to(dev) if plan.stat_stride else None
+        fr = torch.from_numpy(f_all[r]).to(dev)  # [N, A, 2]
+        tr = torch.from_numpy(t_all[r]).to(dev)  # [N, A]
+        forces = [fr[:, a, :] for a in range(A)]
+        torques = [tr[:, a:a + 1] for a in range(A)]
+        act = torch.zeros(n, plan.act_stride, device=dev) if plan.act_stride else None
+        lid = torch.zeros(n, plan.lidar_stride, device=dev) if plan.lidar_stride else None
+        ios.append(plan.make_io(dyn, dyn, stat, forces, torques, act, lid, None, n, bool(args.exact), stream))
+        keep.append((dyn, stat, fr, tr, act, lid))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for i in range(max(W, 3) * R):  # every batch gets >= 3 warm-up steps
+        plan.step_io(ios[i % R])
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sampler = ClockSampler(local_rank)
+    barrier()
+    e0.record()
+    for i in range(K):
+        plan.step_io(ios[i % R])
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1)
+    clocks = sampler.stop()
+    plan.sync_check(stream)
+    if world > 1:
+        t = torch.tensor([ms], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    value = world * n * K / (ms * 1e-3)
+
+    # L2-resident variant (one batch stepped in place, what a rollout does): reported beside, not as `value`
+    for _ in range(3):
+        plan.step_io(ios[0])
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(K):
+        plan.step_io(ios[0])
+    e1.record()
+    torch.cuda.synchronize()
+    ms_hot = e0.elapsed_time(e1)
+
+    e2e = None
+    if not args.no_e2e:
+        e2e = run_e2e(plan, wl, n, K, world, dev)
+    if rank == 0:
+        peak, peak_src = peaks()
+        alg = plan.alg_bytes_per_env * n
+        achieved = alg / (ms / K * 1e-3) / 1e9
+        line = {
+            "metric": METRIC, "value": value, "unit": "env-steps/s", "n_gpus": world, "steps": K, "warmup": max(W, 3),
+            "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic",
+            "config": {"workload": f"{args.scenario} num_envs={n} per GPU, substeps={plan.S}, {len(wl.desc.lidars)} lidars",
+                       "l2": f"{R} env batches visited round-robin, working set {R * per_batch / 2**20:.0f} MiB > L2 126 MiB",
+                       "lanes_per_env": plan.lanes_per_env, "exact": int(args.exact),
+                       "l2_resident_ms_per_step": ms_hot / K},
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": None, "peak_source": peak_src, "alg_bytes_per_env": plan.alg_bytes_per_env,
+                         "kernel": "vb::step_kernel"},
+            "gpu_launches": K * (2 * plan.S if args.exact else 1),
+            "clocks": clocks,
+        }
+        if e2e is not None:
+            line["e2e"] = e2e
+        if world == 1 and not args.no_cpu_baseline:
+            v, cores, sample = cpu_port_rate(wl, seconds=10.0)
+            line["cpu_baseline"] = {"value": v, "unit": "env-steps/s", "cores": cores, "kind": "port", "sample": sample}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def run_e2e(plan, wl, n, K, world, dev):
+    """Same metric through the C-ABI HOST-buffer call (vmasb200_step_host): pinned host records in, H2D, kernel,
+    D2H of state / clamped actions / LIDAR, stream sync - every step."""
+    import torch
+    import torch.distributed as dist
+
+    def pinned(a):
+        t = torch.from_numpy(np.ascontiguousarray(a)).pin_memory()
+        return t, t.numpy()
+
+    dyn0, stat0 = plan.pack(wl.state0, wl.jrot0 if wl.jrot0.size else None)
+    f, t = wl.random_actions(1)
+    keep = [pinned(dyn0), pinned(stat0), pinned(f[0]), pinned(t[0])]
+    dyn, stat, fr, tq = (k[1] for k in keep)
+    for _ in range(3):
+        out = plan.step_host(dyn, stat if plan.stat_stride else None, fr, tq, exact=False, want_masks=False)
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(K):
+        out = plan.step_host(dyn, stat if plan.stat_stride else None, fr, tq, exact=False, want_masks=False)
+        np.copyto(dyn, out[0])
+    torch.cuda.synchronize()
+    el = time.perf_counter() - t0
+    if world > 1:
+        tt = torch.tensor([el], device=dev)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        el = float(tt.item())
+    h2d = 4 * n * (plan.dyn_stride + plan.stat_stride + 3 * plan.A)
+    d2h = 4 * n * (plan.dyn_stride + plan.act_stride + plan.lidar_stride)
+    return {"value": world * n * K / el, "unit": "env-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+            "api": "vmasb200_step_host (C ABI, host buffers)"}
+
+
+def main():
+    args = parse()
+    rank, local_rank, world = dist_env()
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+    else:
+        run_b200(args, rank, local_rank, world)
+
+
+if __name__ == "__main__":
+    main()
