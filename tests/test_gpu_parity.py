@@ -81,3 +81,46 @@ def test_rollout_drift(name):
             assert max_err(st[..., 2:4], exp[..., 2:4]) <= vel_tol, f"{name} vel drift at step {t+1}"
     assert np.isfinite(st).all()
     assert not diverged or fx.desc.joints, f"{name}: collision masks diverged from the reference's"
+
+
+@pytest.mark.parametrize("name", ALL)
+def test_speculative_equals_exact_bitwise(name):
+    """The fused speculative launch (+ in-kernel verification / repair of tainted envs) must reproduce the exact
+    per-substep path bit for bit: same device code, same flags.  Envs are tiled so that every thin-shell event is
+    shared by many envs (tainted list longer than one CTA tile) and, on a second pass, de-synchronised by jitter."""
+    fx = Fixture(name)
+    pl = StepPlan(fx.desc)
+    reps = 40
+    fixups = 0
+    for state_in, t, k in fx.one_step_cases()[:4]:
+        for jitter in (0.0, 1e-3):
+            st = np.ascontiguousarray(np.tile(state_in, (1, reps, 1)))
+            if jitter:
+                rng = np.random.default_rng(t)
+                for e, en in enumerate(fx.desc.entities):
+                    if en.movable:
+                        st[e, :, 0:2] += rng.uniform(-jitter, jitter, st[e, :, 0:2].shape).astype(np.float32)
+            jr = fx.jrot_at(t)
+            jr = np.tile(jr, (1, reps)) if jr.size else jr
+            dyn, stat = pl.pack(st, jr)
+            f, tq = _forces(fx, t)
+            f, tq = np.ascontiguousarray(np.tile(f, (reps, 1, 1))), np.ascontiguousarray(np.tile(tq, (reps, 1)))
+            a = pl.step_host(dyn, stat, f, tq, exact=True)
+            b = pl.step_host(dyn, stat, f, tq, exact=False)
+            for x, y, what in zip(a, b, ("dyn", "act", "lidar", "masks")):
+                if x is not None:
+                    assert np.array_equal(x.view(np.uint32), y.view(np.uint32)), f"{name} t={t} jitter={jitter}: {what} differs"
+    fixups = pl.sync_check()
+    if name in ("pollock", "transport", "joint_passage"):
+        print(name, "repairs:", fixups)
+
+
+def test_repair_path_is_exercised():
+    """pollock (45 mixed shapes, 12 envs) has thin-shell contacts whose batch-wide flag is false: the repair must run."""
+    fx = Fixture("pollock")
+    pl = StepPlan(fx.desc)
+    for state_in, t, k in fx.one_step_cases():
+        dyn, stat = pl.pack(state_in, fx.jrot_at(t))
+        f, tq = _forces(fx, t)
+        pl.step_host(dyn, stat, f, tq, exact=False)
+    assert pl.sync_check() > 0

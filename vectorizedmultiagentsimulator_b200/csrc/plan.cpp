@@ -205,11 +205,15 @@ int build_plan(const vmasb200_world_desc* d, vmasb200_plan* pl) {
   kp.work_stride = align4(kp.off_frc + 3 * kp.A);
   if (((kp.work_stride / 4) & 1) == 0) kp.work_stride += 4;  // odd number of float4 per env: groups hit distinct banks
   const int per_env = 4 * (kp.dyn_stride + kp.stat_stride + kp.act_stride + kp.lidar_stride + kp.work_stride);
-  const int fixed = 16 + 8 * kp.S * kp.pair_words + 16;
+  const int fixed = 16 + 12 * kp.S * kp.pair_words + 16;
   const int budget = 200 * 1024;
   int TE = 256 / G;
   while (TE > 1 && fixed + TE * per_env > budget) TE /= 2;
-  if (fixed + TE * per_env > 227 * 1024) { set_error("world too large for one CTA's shared memory"); return VMASB200_ERR_UNSUPPORTED; }
+  if (fixed + TE * per_env > 226 * 1024) { set_error("world too large for one CTA's shared memory"); return VMASB200_ERR_UNSUPPORTED; }
+  if ((TE * G) % 32) {  // warp votes need full warps: fall back to a warp per env
+    G = 32; kp.G = 32; TE = 8;
+    while (TE > 1 && fixed + TE * per_env > budget) TE /= 2;
+  }
   kp.TE = TE;
 
   // ---- world constants

@@ -28,7 +28,9 @@ struct vmasb200_plan {
   // staging of vmasb200_step_host
   int64_t host_cap = 0;
   float *d_dyn = nullptr, *d_stat = nullptr, *d_force = nullptr, *d_torque = nullptr, *d_act = nullptr, *d_lidar = nullptr;
-  int64_t n_fixups = 0;
+  int64_t u_cap = 0;           // speculative path scratch: tainted env list + their records
+  int* d_ulist = nullptr;
+  float* d_ubuf = nullptr;
 };
 
 namespace vb {

@@ -49,11 +49,11 @@ int upload_plan(vmasb200_plan* pl) {
   kp.rays = reinterpret_cast<const DRay*>(b + o_ray);
   kp.sensors = reinterpret_cast<const DSensor*>(b + o_sen);
   kp.targets = reinterpret_cast<const int32_t*>(b + o_tg);
-  size_t nbits = 3 * (size_t)kp.S * std::max(kp.pair_words, 1) * sizeof(uint32_t);
+  size_t nbits = (4 * (size_t)kp.S * std::max(kp.pair_words, 1) + 4) * sizeof(uint32_t);  // 4 bit arrays + counters
   VB_CUDA(cudaMalloc(&pl->d_bits, nbits));
   VB_CUDA(cudaMemset(pl->d_bits, 0, nbits));
   pl->smem_bytes = smem_map(kp).total_bytes;
-  VB_CUDA(cudaFuncSetAttribute(step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+  VB_CUDA(cudaFuncSetAttribute(step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
   pl->uploaded = true;
   return VMASB200_OK;
 }
@@ -84,12 +84,13 @@ static int launch_step(vmasb200_plan* pl, const vmasb200_step_io* io) {
     aio.fstride[a] = (int32_t)io->force_strides[a]; aio.tstride[a] = (int32_t)io->torque_strides[a];
   }
   const int nw = kp.S * kp.pair_words;
+  const size_t bw = (size_t)kp.S * std::max(kp.pair_words, 1);
   uint32_t* flags = pl->d_bits;
-  uint32_t* any = pl->d_bits + (size_t)kp.S * std::max(kp.pair_words, 1);
-  uint32_t* thin = any + (size_t)kp.S * std::max(kp.pair_words, 1);
   StepArgs sa{};
   sa.dyn_in = io->dyn_in; sa.dyn_out = io->dyn_out; sa.stat = io->stat; sa.act_out = io->act_out;
   sa.lidar_out = io->lidar_out; sa.n_envs = io->n_envs;
+  sa.flags_out = flags; sa.any_exact = flags + bw; sa.any_spec = flags + 2 * bw; sa.thin = flags + 3 * bw;
+  sa.counters = reinterpret_cast<int*>(flags + 4 * bw);
   const unsigned grid = (unsigned)((io->n_envs + kp.TE - 1) / kp.TE);
   const unsigned block = (unsigned)(kp.TE * kp.G);
   if (io->exact) {
@@ -100,18 +101,25 @@ static int launch_step(vmasb200_plan* pl, const vmasb200_step_io* io) {
         unsigned fg = (unsigned)((io->n_envs + 255) / 256);
         flags_kernel<<<fg, 256, 0, st>>>(kp, sa.dyn_in, sa.stat, io->n_envs, s, flags);
       }
-      sa.s_begin = s; sa.s_end = s + 1; sa.flags_in = flags; sa.any_out = nullptr; sa.thin_out = nullptr;
+      sa.s_begin = s; sa.s_end = s + 1; sa.flags_in = flags;
       sa.do_lidar = (s == kp.S - 1);
       step_kernel<<<grid, block, pl->smem_bytes, st>>>(kp, aio, sa);
       sa.dyn_in = io->dyn_out;
     }
-    if (io->pair_active_out && nw) VB_CUDA(cudaMemcpyAsync(io->pair_active_out, flags, nw * sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
   } else {
-    if (nw) VB_CUDA(cudaMemsetAsync(any, 0, 2 * (size_t)kp.S * std::max(kp.pair_words, 1) * sizeof(uint32_t), st));
-    sa.s_begin = 0; sa.s_end = kp.S; sa.flags_in = nullptr; sa.any_out = any; sa.thin_out = thin; sa.do_lidar = 1;
+    // fused speculative launch; the last CTA verifies it and repairs the (rare) tainted envs in place
+    if (io->n_envs > pl->u_cap) {
+      cudaFree(pl->d_ulist); cudaFree(pl->d_ubuf);
+      pl->d_ulist = nullptr; pl->d_ubuf = nullptr; pl->u_cap = 0;
+      VB_CUDA(cudaMalloc(&pl->d_ulist, (size_t)io->n_envs * sizeof(int)));
+      VB_CUDA(cudaMalloc(&pl->d_ubuf, (size_t)io->n_envs * kp.dyn_stride * sizeof(float)));
+      pl->u_cap = io->n_envs;
+    }
+    sa.u_list = pl->d_ulist; sa.u_buf = pl->d_ubuf;
+    sa.s_begin = 0; sa.s_end = kp.S; sa.flags_in = nullptr; sa.do_lidar = 1;
     step_kernel<<<grid, block, pl->smem_bytes, st>>>(kp, aio, sa);
-    if (io->pair_active_out && nw) VB_CUDA(cudaMemcpyAsync(io->pair_active_out, any, nw * sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
   }
+  if (io->pair_active_out && nw) VB_CUDA(cudaMemcpyAsync(io->pair_active_out, flags, nw * sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
   VB_CUDA(cudaGetLastError());
   return VMASB200_OK;
 }
@@ -139,7 +147,7 @@ int vmasb200_plan_create(const vmasb200_world_desc* desc, vmasb200_plan** out) {
 int vmasb200_plan_destroy(vmasb200_plan* pl) {
   if (!pl) return VMASB200_OK;
   if (pl->uploaded) {
-    cudaFree(pl->d_blob); cudaFree(pl->d_bits);
+    cudaFree(pl->d_blob); cudaFree(pl->d_bits); cudaFree(pl->d_ulist); cudaFree(pl->d_ubuf);
     cudaFree(pl->d_dyn); cudaFree(pl->d_stat); cudaFree(pl->d_force); cudaFree(pl->d_torque); cudaFree(pl->d_act); cudaFree(pl->d_lidar);
   }
   delete pl;
@@ -231,16 +239,13 @@ int vmasb200_step_host(vmasb200_plan* pl, const float* h_dyn_in, const float* h_
   io.force_ptrs = fptr; io.force_strides = fstr; io.torque_ptrs = tptr; io.torque_strides = tstr;
   io.act_out = kp.act_stride ? pl->d_act : nullptr;
   io.lidar_out = (kp.lidar_stride && h_lidar_out) ? pl->d_lidar : nullptr;
-  uint32_t* d_pa = nullptr;
   io.pair_active_out = nullptr; io.n_envs = n; io.exact = exact; io.stream = st;
-  (void)d_pa;
   if (kp.n_dyn && (rc = launch_step(pl, &io))) return rc;
   if (h_dyn_out) VB_CUDA(cudaMemcpyAsync(h_dyn_out, pl->d_dyn, (size_t)n * kp.dyn_stride * 4, cudaMemcpyDeviceToHost, st));
   if (h_act_out && kp.act_stride) VB_CUDA(cudaMemcpyAsync(h_act_out, pl->d_act, (size_t)n * kp.act_stride * 4, cudaMemcpyDeviceToHost, st));
   if (h_lidar_out && kp.lidar_stride) VB_CUDA(cudaMemcpyAsync(h_lidar_out, pl->d_lidar, (size_t)n * kp.lidar_stride * 4, cudaMemcpyDeviceToHost, st));
   if (h_pair_active && kp.S * kp.pair_words) {
-    const uint32_t* src = exact ? pl->d_bits : pl->d_bits + (size_t)kp.S * std::max(kp.pair_words, 1);
-    VB_CUDA(cudaMemcpyAsync(h_pair_active, src, (size_t)kp.S * kp.pair_words * 4, cudaMemcpyDeviceToHost, st));
+    VB_CUDA(cudaMemcpyAsync(h_pair_active, pl->d_bits, (size_t)kp.S * kp.pair_words * 4, cudaMemcpyDeviceToHost, st));
   }
   VB_CUDA(cudaStreamSynchronize(st));
   return VMASB200_OK;
@@ -278,7 +283,15 @@ int vmasb200_cast_rays(vmasb200_plan* pl, const float* dyn, const float* stat, i
 int vmasb200_sync_check(vmasb200_plan* pl, void* stream, int64_t* n_fixups) {
   VB_CUDA(cudaStreamSynchronize(static_cast<cudaStream_t>(stream)));
   VB_CUDA(cudaGetLastError());
-  if (n_fixups) *n_fixups = pl ? pl->n_fixups : 0;
+  if (n_fixups) {
+    *n_fixups = 0;
+    if (pl && pl->uploaded) {
+      int c = 0;
+      const size_t bw = (size_t)pl->kp.S * std::max(pl->kp.pair_words, 1);
+      VB_CUDA(cudaMemcpy(&c, reinterpret_cast<int*>(pl->d_bits + 4 * bw) + 2, sizeof(int), cudaMemcpyDeviceToHost));
+      *n_fixups = c;
+    }
+  }
   return VMASB200_OK;
 }
 
