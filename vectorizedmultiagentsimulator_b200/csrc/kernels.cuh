@@ -73,7 +73,7 @@ VB_DI void load_forces(const KParams& kp, const AgentIO& aio, float* workE, long
 }
 
 // Substeps [s_begin, s_end) of one env on the staged tile.  flags: batch-wide verdicts to obey (smem or global), or
-// NULL = speculative (every pair evaluated, verdict / thin bits collected into the tile's bit arrays).
+// NULL = speculative (every pair considered, verdict / thin bits collected into the tile's bit arrays).
 // Returns the env's taint (speculative mode).
 VB_DI bool run_env(const KParams& kp, const Tile& t, int el, int lg, bool env_ok, int s_begin, int s_end,
                    const uint32_t* flags, bool do_lidar) {
@@ -82,9 +82,12 @@ VB_DI bool run_env(const KParams& kp, const Tile& t, int el, int lg, bool env_ok
   ep.dyn = t.dynS + el * kp.dyn_stride;
   ep.stat = t.statS + el * kp.stat_stride;
   ep.work = t.workS + el * kp.work_stride;
-  const unsigned gmask = (G == 32 ? 0xffffffffu : ((1u << G) - 1u)) << ((threadIdx.x & 31) & ~(G - 1));
+  const int gshift = (threadIdx.x & 31) & ~(G - 1);
+  const unsigned gbits = G == 32 ? 0xffffffffu : ((1u << G) - 1u);
+  const unsigned gmask = gbits << gshift;
+  const unsigned below = (1u << lg) - 1u;
 
-  // prologue: cos/sin cache of every entity that needs it, first force accumulators
+  // prologue: cos/sin cache of every entity that needs it, first force accumulators, joints at the list head
   for (int r = lg; r < kp.n_rot; r += G) {
     const DEnt* en = kp.ents + __ldg(kp.rot_list + r);
     V2 p; float rot;
@@ -95,51 +98,98 @@ VB_DI bool run_env(const KParams& kp, const Tile& t, int el, int lg, bool env_ok
   // that earlier launches of a split step already did
   for (int rep = 0; rep <= s_begin; ++rep)
     for (int d = lg; d < kp.n_dyn; d += G) begin_forces(kp, kp.ents + __ldg(kp.dyn_list + d), ep);
+  int* list = reinterpret_cast<int*>(ep.work + kp.off_list);
+  for (int j = lg; j < kp.J; j += G) {
+    const DItem* it = kp.items + j;
+    list[j] = j | (it->a << kEntryItemBits) | (it->b << (kEntryItemBits + kEntryEntBits));
+  }
   __syncwarp();
 
   bool tainted = false;
   float4* res = reinterpret_cast<float4*>(ep.work + kp.off_res);
   for (int s = s_begin; s < s_end; ++s) {
+    // ---- phase A: broad phase + compaction of the surviving pairs (all lanes of the warp run the same trip count)
+    int count = kp.J;
+    for (int base = 0; base < kp.P; base += G) {
+      const int p = base + lg;
+      bool surv = false;
+      int entry = 0;
+      if (p < kp.P) {
+        const int4 bi = __ldg(reinterpret_cast<const int4*>(kp.broad + p));
+        const float4 bf = __ldg(reinterpret_cast<const float4*>(kp.broad + p) + 1);
+        const V2 pa = pos_enc(ep, bi.x), pb = pos_enc(ep, bi.y);
+        const float dx = pa.x - pb.x, dy = pa.y - pb.y;
+        const float d2 = fmaf(dy, dy, dx * dx);
+        const bool bp = d2 <= bf.x;  // == (norm(pa - pb) <= Rc_a + Rc_b), core.py:2796-2800
+        const int w = s * kp.pair_words + (p >> 5);
+        const uint32_t bit = 1u << (p & 31);
+        bool active = true;
+        if (flags) active = (flags[w] & bit) != 0u;
+        else if (bp && env_ok) set_bit(tainted ? t.bitsS : t.bitsE, w, bit);
+        if (bi.z < 0) {
+          surv = !(d2 > bf.y);
+        } else {  // sphere centre in the line / box frame
+          const float c = ep.work[bi.z], sn = ep.work[bi.z + 1];
+          const float lx = -(dx * c + dy * sn), ly = dx * sn - dy * c;
+          surv = !(fabsf(lx) > bf.z) && !(fabsf(ly) > bf.w);
+        }
+        surv = surv && active;
+        entry = bi.w | (bp ? (1 << 30) : 0);
+      }
+      const unsigned votes = (__ballot_sync(0xffffffffu, surv) >> gshift) & gbits;
+      if (surv) list[count + __popc(votes & below)] = entry;
+      count += __popc(votes);
+    }
+    __syncwarp();
+    // ---- phase B: joints and surviving pairs
     bool thin_now = false;
-    // ---- phase B: joints and pairs
-    for (int i = lg; i < kp.n_items; i += G) {
-      const DItem* it = kp.items + i;
-      const int p = i - kp.J;  // pair index (flag bit)
-      bool active = true;
-      if (p >= 0 && flags) active = (flags[s * kp.pair_words + (p >> 5)] >> (p & 31)) & 1u;
+    for (int k = lg; k < count; k += G) {
+      const int entry = list[k];
+      const int i = entry & ((1 << kEntryItemBits) - 1);
       V2 fa = mk(0.f, 0.f);
       float ta = 0.f, tb = 0.f;
-      if (active) {
-        bool bp = eval_item(kp, it, ep, fa, ta, tb);
-        if (!flags && p >= 0 && env_ok) {
-          const uint32_t bit = 1u << (p & 31);
-          const int w = s * kp.pair_words + (p >> 5);
-          if (bp) set_bit(tainted ? t.bitsS : t.bitsE, w, bit);
-          else if (fa.x != 0.f || fa.y != 0.f) { set_bit(t.bitsT, w, bit); thin_now = true; }
-        }
+      eval_item(kp, kp.items + i, ep, fa, ta, tb);
+      if (!flags && i >= kp.J && env_ok && !(entry & (1 << 30)) && (fa.x != 0.f || fa.y != 0.f)) {
+        const int p = i - kp.J;
+        set_bit(t.bitsT, s * kp.pair_words + (p >> 5), 1u << (p & 31));
+        thin_now = true;
       }
-      res[i] = make_float4(fa.x, fa.y, ta, tb);
+      res[k] = make_float4(fa.x, fa.y, ta, tb);
     }
     // warp-wide vote doubles as the phase barrier; the taint applies from the NEXT substep on
     const unsigned vote = __ballot_sync(0xffffffffu, thin_now);
     tainted = tainted || (vote & gmask);
     // ---- phase C: accumulate + integrate, then open the next substep's accumulators
     for (int d = lg; d < kp.n_dyn; d += G) {
-      const DEnt* en = kp.ents + __ldg(kp.dyn_list + d);
-      finish_entity(kp, en, ep, s);
+      const int e = __ldg(kp.dyn_list + d);
+      const DEnt* en = kp.ents + e;
+      finish_entity(kp, en, e, ep, s, list, count);
       if (s + 1 < s_end) begin_forces(kp, en, ep);
     }
     __syncwarp();
   }
 
   if (do_lidar) {  // LIDAR epilogue
+    uint32_t* lm = reinterpret_cast<uint32_t*>(ep.work + kp.off_lmask);
+    for (int sw = lg; sw < kp.n_lmask_words; sw += G) {  // which targets can a ray of this sensor reach at all
+      const DSWord* q = kp.swords + sw;
+      const V2 o = posof(kp.ents + kp.sensors[q->sensor].entity, ep);
+      uint32_t m = 0u;
+      for (int k = 0; k < q->n; ++k) {
+        const V2 p = posof(kp.ents + __ldg(kp.targets + q->tg_begin + k), ep);
+        const float dx = o.x - p.x, dy = o.y - p.y;
+        if (!(fmaf(dy, dy, dx * dx) > __ldg(kp.tcull2 + q->tg_begin + k))) m |= 1u << k;
+      }
+      lm[sw] = m;
+    }
+    __syncwarp();
     float* lid = t.lidS + el * kp.lidar_stride;
     for (int r = lg; r < kp.n_rays; r += G) {
       const DRay* ry = kp.rays + r;
       const DSensor* sn = kp.sensors + ry->sensor;
       V2 o; float rot;
       pose(kp.ents + sn->entity, ep, o, rot);
-      lid[ry->out_off] = cast_one_ray(kp, sn, ep, o, ry->angle + rot);  // sensors.py:117
+      lid[ry->out_off] = cast_one_ray(kp, sn, ep, o, ry->angle + rot, lm + sn->tw_off);  // sensors.py:117
     }
   }
   return tainted;
@@ -165,9 +215,10 @@ __device__ __noinline__ void repair_tainted(const KParams& kp, const AgentIO& ai
           ep.stat = sa.stat + (size_t)sa.u_list[idx] * kp.stat_stride;
           ep.work = nullptr;
           for (int p = lg; p < kp.P; p += G) {
-            const DItem* it = kp.items + kp.J + p;
-            V2 pa = posof(kp.ents + it->a, ep), pb = posof(kp.ents + it->b, ep);
-            if (norm(pa - pb) <= it->thr) set_bit(flagS, s * kp.pair_words + (p >> 5), 1u << (p & 31));
+            const DBroad* bq = kp.broad + p;
+            V2 pa = pos_enc(ep, bq->pa_off), pb = pos_enc(ep, bq->pb_off);
+            const float dx = pa.x - pb.x, dy = pa.y - pb.y;
+            if (fmaf(dy, dy, dx * dx) <= bq->t2_bp) set_bit(flagS, s * kp.pair_words + (p >> 5), 1u << (p & 31));
           }
         }
       }
@@ -330,9 +381,10 @@ __global__ void __launch_bounds__(256) flags_kernel(const __grid_constant__ KPar
   ep.stat = stat + (ok ? env : 0) * kp.stat_stride;
   ep.work = nullptr;
   for (int p = 0; p < kp.P; ++p) {
-    const DItem* it = kp.items + kp.J + p;
-    V2 pa = posof(kp.ents + it->a, ep), pb = posof(kp.ents + it->b, ep);
-    bool bp = ok && (norm(pa - pb) <= it->thr);
+    const DBroad* bq = kp.broad + p;
+    V2 pa = pos_enc(ep, bq->pa_off), pb = pos_enc(ep, bq->pb_off);
+    const float dx = pa.x - pb.x, dy = pa.y - pb.y;
+    bool bp = ok && (fmaf(dy, dy, dx * dx) <= bq->t2_bp);
     unsigned any = __ballot_sync(0xffffffffu, bp);
     if (any && (threadIdx.x & 31) == 0) {
       uint32_t* w = flags + s * kp.pair_words + (p >> 5);

@@ -6,6 +6,7 @@
 #include "plan.h"
 
 #include <algorithm>
+#include <cmath>
 #include <cstring>
 
 namespace vb {
@@ -15,6 +16,21 @@ void set_error(const std::string& msg) { g_err = msg; }
 const char* last_error() { return g_err.c_str(); }
 
 static inline int align4(int x) { return (x + 3) & ~3; }
+
+// Largest float x with sqrtf(x) <= t (sqrtf is correctly rounded and monotonic), so that for every float d2
+//   sqrtf(d2) <= t  <=>  d2 <= sq_le(t)   and   sqrtf(d2) > t  <=>  d2 > sq_le(t).
+static float sq_le(float t) {
+  if (!(t >= 0.f)) return -1.f;  // nothing satisfies sqrtf(x) <= negative (or NaN) threshold
+  if (std::isinf(t)) return t;
+  float x = (float)((double)t * (double)t);
+  while (std::sqrt(x) <= t) x = std::nextafter(x, INFINITY);
+  while (std::sqrt(x) > t) x = std::nextafter(x, -INFINITY);
+  return x;
+}
+// conservative reach used by the culls: anything farther than this is provably force-free / unseen
+static double with_margin(double reach) { return reach * (1.0 + 1e-3) + 1e-5; }
+static float sq_up(double reach) { return std::nextafter((float)(reach * reach), INFINITY); }
+static const double kLMDd = 4.0 / 6e2;  // utils.py:27 LINE_MIN_DIST
 
 static int pair_type(int sa, int sb, bool& swap) {
   swap = false;
@@ -79,9 +95,13 @@ int build_plan(const vmasb200_world_desc* d, vmasb200_plan* pl) {
   kp.n_items = (int)pl->items.size();
   kp.P = kp.n_items - kp.J;
   kp.pair_words = (kp.P + 31) / 32;
+  if (kp.n_items > (1 << kEntryItemBits) || E > (1 << kEntryEntBits)) {
+    set_error("more than 4096 work items or 512 entities are not supported by the CUDA step"); return VMASB200_ERR_UNSUPPORTED;
+  }
 
   // ---- sensors (sensors.py:46-69, core.py:1677-1690)
   pl->sensors.clear(); pl->rays.clear(); pl->targets.clear(); pl->lidar_slot.assign(d->n_lidars, 0);
+  pl->tcull2.clear(); pl->swords.clear();
   int ray_off = 0;
   for (int k = 0; k < d->n_lidars; ++k) {
     const vmasb200_lidar& ld = d->lidars[k];
@@ -94,7 +114,13 @@ int build_plan(const vmasb200_world_desc* d, vmasb200_plan* pl) {
     for (int t = 0; t < ld.n_targets; ++t) {
       if (ld.targets[t] < 0 || ld.targets[t] >= E) { set_error("world desc: lidar target out of range"); return VMASB200_ERR_INVALID; }
       pl->targets.push_back(ld.targets[t]);
+      // a ray of length max_range cannot reach a shape whose centre is farther than max_range + circumscribed radius
+      pl->tcull2.push_back(sq_up(with_margin((double)ld.max_range + d->entities[ld.targets[t]].circumscribed_radius)));
     }
+    sn.tw_off = (int)pl->swords.size();
+    sn.n_tw = (ld.n_targets + 31) / 32;
+    for (int w = 0; w < sn.n_tw; ++w)
+      pl->swords.push_back(DSWord{k, sn.tg_begin + 32 * w, std::min(32, ld.n_targets - 32 * w), 0});
     for (int r = 0; r < ld.n_rays; ++r) pl->rays.push_back(DRay{k, ld.angles[r], ray_off + r, 0});
     pl->lidar_slot[k] = ray_off;
     ray_off += ld.n_rays;
@@ -177,16 +203,30 @@ int build_plan(const vmasb200_world_desc* d, vmasb200_plan* pl) {
   kp.n_rot = (int)pl->rot_list.size();
   kp.dyn_stride = align4(dyn_off); kp.stat_stride = align4(stat_off); kp.act_stride = align4(act_off);
 
-  // ---- contribution lists in reference order (joints, then ss, ls, ll, bs, bl, bb; a before b)
-  pl->csr.clear();
-  for (int e : pl->dyn_list) {
-    DEnt& o = pl->ents[e];
-    o.csr_begin = (int)pl->csr.size();
-    for (int i = 0; i < kp.n_items; ++i) {
-      if (pl->items[i].a == e) pl->csr.push_back((i << 1) | 0);
-      if (pl->items[i].b == e) pl->csr.push_back((i << 1) | 1);
+  // ---- broad-phase table (one row per candidate pair, same order as the pair items)
+  pl->broad.clear();
+  auto enc_pos = [&](int e) { return pl->ents[e].dyn_off >= 0 ? pl->ents[e].dyn_off : ~pl->ents[e].stat_off; };
+  for (int p = 0; p < kp.P; ++p) {
+    const DItem& it = pl->items[kp.J + p];
+    const vmasb200_entity &sa = d->entities[it.a], &sb = d->entities[it.b];
+    DBroad b{};
+    b.pa_off = enc_pos(it.a); b.pb_off = enc_pos(it.b);
+    b.rot_off = -1;
+    b.entry = (kp.J + p) | (it.a << kEntryItemBits) | (it.b << (kEntryItemBits + kEntryEntBits));
+    b.t2_bp = sq_le(it.thr);
+    if (it.type == IT_SS) {
+      const float dmin = sa.radius + sb.radius;  // fp32 sum = the kernel's dist_min (core.py:2312)
+      b.t2_cull = sq_le(dmin);
+    } else {
+      b.t2_cull = sq_up(with_margin(sa.circumscribed_radius + sb.circumscribed_radius + kLMDd));
+      if (it.type == IT_LS || it.type == IT_BS) {  // a = line / box, b = sphere: cull in a's frame
+        const double reach = with_margin((double)sb.radius + kLMDd);
+        b.hx = (float)((double)sa.length / 2 + reach);
+        b.hy = (float)((it.type == IT_BS ? (double)sa.width / 2 : 0.0) + reach);
+        b.rot_off = -2;  // resolved below, once the work area layout is known
+      }
     }
-    o.csr_end = (int)pl->csr.size();
+    pl->broad.push_back(b);
   }
 
   // ---- kernel shape
@@ -202,7 +242,12 @@ int build_plan(const vmasb200_world_desc* d, vmasb200_plan* pl) {
   kp.off_rot = align4(3 * kp.n_dyn);
   kp.off_res = kp.off_rot + 4 * kp.n_rot;
   kp.off_frc = kp.off_res + 4 * kp.n_items;
-  kp.work_stride = align4(kp.off_frc + 3 * kp.A);
+  kp.off_list = kp.off_frc + 3 * kp.A;
+  kp.off_lmask = kp.off_list + kp.n_items;
+  kp.n_lmask_words = (int)pl->swords.size();
+  kp.work_stride = align4(kp.off_lmask + kp.n_lmask_words);
+  for (int p = 0; p < kp.P; ++p)
+    if (pl->broad[p].rot_off == -2) pl->broad[p].rot_off = kp.off_rot + 4 * pl->ents[pl->items[kp.J + p].a].rot_slot;
   if (((kp.work_stride / 4) & 1) == 0) kp.work_stride += 4;  // odd number of float4 per env: groups hit distinct banks
   const int per_env = 4 * (kp.dyn_stride + kp.stat_stride + kp.act_stride + kp.lidar_stride + kp.work_stride);
   const int fixed = 16 + 12 * kp.S * kp.pair_words + 16;

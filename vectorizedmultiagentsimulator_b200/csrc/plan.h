@@ -14,7 +14,10 @@ struct vmasb200_plan {
   // host copies of the tables
   std::vector<vb::DEnt> ents;
   std::vector<vb::DItem> items;
-  std::vector<int32_t> csr, dyn_list, rot_list, targets;
+  std::vector<vb::DBroad> broad;
+  std::vector<int32_t> dyn_list, rot_list, targets;
+  std::vector<float> tcull2;
+  std::vector<vb::DSWord> swords;
   std::vector<vb::DRay> rays;
   std::vector<vb::DSensor> sensors;
   std::vector<vmasb200_pair> pairs;

@@ -3,13 +3,16 @@
 // One CTA owns a tile of TE consecutive environments.  The tile's env records (dyn + stat) are staged into
 // shared memory by ONE cp.async.bulk (TMA 1-D) each, stay resident across all substeps, and are written back by
 // one bulk store per output record type.  G lanes (a sub-warp group, G in {1,2,4,8,16,32}) cooperate on one
-// environment; per substep they run three phases separated by __syncwarp():
-//   B  lanes stride over the work items (joint constraints, then candidate pairs in the reference's type order)
-//      and write each item's (force on a, torque a, torque b) into the env's result slots;
-//   C  lanes stride over the dynamic entities, add the slots up IN THE REFERENCE'S ORDER (core.py:2175-2198),
-//      integrate (core.py:2861-2907), refresh cos/sin of a rotated entity and start the next substep's force
-//      accumulator (action / friction / gravity, core.py:1994-2005);
-// and after the last substep the LIDAR epilogue (core.py:1661-1785) with lanes striding over the rays.
+// environment; per substep they run three phases separated by warp barriers:
+//   A  broad phase: lanes stride over the candidate pairs (tables.h DBroad), take the reference's own verdict
+//      (core.py:2796-2800) sqrt-free, drop every pair whose force is provably zero, and compact the survivors - by
+//      warp ballot, in item order - into the env's active list (behind the joint constraints, always active);
+//   B  narrow phase: lanes stride over the ACTIVE LIST only and write each item's (force on a, torque a, torque b);
+//   C  lanes stride over the dynamic entities, add the active items up IN THE REFERENCE'S ORDER (core.py:2175-2198;
+//      a dropped item would have added exact zeros), integrate (core.py:2861-2907), refresh cos/sin of a rotated
+//      entity and start the next substep's force accumulator (action / friction / gravity, core.py:1994-2005);
+// and after the last substep the LIDAR epilogue (core.py:1661-1785): per sensor a mask of the targets within
+// reach, then lanes stride over the rays and cast only against those.
 #pragma once
 #include "geom.cuh"
 #include "tables.h"
@@ -71,6 +74,11 @@ VB_DI void pose(const DEnt* __restrict__ en, const EnvPtrs& ep, V2& p, float& ro
     p = mk(ep.stat[s], ep.stat[s + 1]);
     rot = ep.stat[s + 2];
   }
+}
+// encoded position offset of the broad-phase table: >= 0 dyn record, < 0 ~offset into the stat record
+VB_DI V2 pos_enc(const EnvPtrs& ep, int off) {
+  const float* q = off >= 0 ? ep.dyn + off : ep.stat + ~off;
+  return mk(q[0], q[1]);
 }
 VB_DI V2 posof(const DEnt* __restrict__ en, const EnvPtrs& ep) {
   int d = en->dyn_off;
@@ -136,8 +144,8 @@ VB_DI void begin_forces(const KParams& kp, const DEnt* __restrict__ en, const En
 }
 
 // One work item (joint constraint or candidate pair): force on a (the force on b is its exact negation) and the
-// two torques.  Returns the env's own broad-phase verdict for pairs (core.py:2796-2800 without the .any()).
-VB_DI bool eval_item(const KParams& kp, const DItem* __restrict__ it, const EnvPtrs& ep, V2& fa, float& ta, float& tb) {
+// two torques.
+VB_DI void eval_item(const KParams& kp, const DItem* __restrict__ it, const EnvPtrs& ep, V2& fa, float& ta, float& tb) {
   const int type = it->type;
   const DEnt* __restrict__ ea = kp.ents + it->a;
   const DEnt* __restrict__ eb = kp.ents + it->b;
@@ -163,9 +171,8 @@ VB_DI bool eval_item(const KParams& kp, const DItem* __restrict__ it, const EnvP
       ta = ta + (-tq);
       tb = tb + tq;
     }
-    return true;
+    return;
   }
-  const bool bp = norm(pa - pb) <= it->thr;
   switch (type) {
     case IT_SS: {  // core.py:2293
       fa = constraint_force(pa, pb, ea->radius + eb->radius, Kc, k, false);
@@ -219,28 +226,30 @@ VB_DI bool eval_item(const KParams& kp, const DItem* __restrict__ it, const EnvP
       tb = cross(cb - pb, -fa);
     } break;
   }
-  return bp;
 }
 
-// Accumulate the item results of one dynamic entity in reference order (core.py:2190-2198) and integrate
-// (core.py:2861-2907).  Returns the new rotation.
-VB_DI void finish_entity(const KParams& kp, const DEnt* __restrict__ en, const EnvPtrs& ep, int substep) {
+// Accumulate the active items of one dynamic entity in reference order (core.py:2190-2198; the list is in item
+// order) and integrate (core.py:2861-2907).
+VB_DI void finish_entity(const KParams& kp, const DEnt* __restrict__ en, int e, const EnvPtrs& ep, int substep,
+                         const int* __restrict__ list, int count) {
   const uint32_t fl = en->flags;
   const float* fin = ep.work + kp.off_fin + en->fin_off;
   V2 F = mk(fin[0], fin[1]);
   float T = fin[2];
   const float4* res = reinterpret_cast<const float4*>(ep.work + kp.off_res);
-  const int cb = en->csr_begin, ce = en->csr_end;
   const bool mov = fl & VMASB200_E_MOVABLE, rotb = fl & VMASB200_E_ROTATABLE;
-  for (int c = cb; c < ce; ++c) {
-    int code = __ldg(kp.csr + c);
-    float4 r = res[code >> 1];
-    if (code & 1) {
-      if (mov) F = F + mk(-r.x, -r.y);
-      if (rotb) T = T + r.w;
-    } else {
+  constexpr int em = (1 << kEntryEntBits) - 1;
+  for (int k = 0; k < count; ++k) {
+    const int entry = list[k];
+    const int a = (entry >> kEntryItemBits) & em, b = (entry >> (kEntryItemBits + kEntryEntBits)) & em;
+    if (a == e) {
+      float4 r = res[k];
       if (mov) F = F + mk(r.x, r.y);
       if (rotb) T = T + r.z;
+    } else if (b == e) {
+      float4 r = res[k];
+      if (mov) F = F + mk(-r.x, -r.y);
+      if (rotb) T = T + r.w;
     }
   }
   float* st = ep.dyn + en->dyn_off;
@@ -271,25 +280,36 @@ VB_DI void finish_entity(const KParams& kp, const DEnt* __restrict__ en, const E
   }
 }
 
-// One LIDAR ray (sensors.py:115-118 -> core.py:1661-1785): min over the sensor's targets.
-VB_DI float cast_one_ray(const KParams& kp, const DSensor* __restrict__ sn, const EnvPtrs& ep, V2 o, float ang) {
-  float ds, dc;
-  sincosf(ang, &ds, &dc);
+// One LIDAR ray (sensors.py:115-118 -> core.py:1661-1785): min over the sensor's targets within reach (`lm`: the
+// sensor's survival mask words; an unreachable target would have contributed max_range).
+VB_DI float cast_one_ray(const KParams& kp, const DSensor* __restrict__ sn, const EnvPtrs& ep, V2 o, float ang,
+                         const uint32_t* __restrict__ lm) {
   const float max_range = sn->max_range;
   float best = max_range;
-  const int tb = sn->tg_begin, nt = sn->n_targets;
-  for (int t = 0; t < nt; ++t) {
-    const DEnt* __restrict__ en = kp.ents + __ldg(kp.targets + tb + t);
-    V2 p = posof(en, ep);
-    float d;
-    if (en->shape == VMASB200_SPHERE) {
-      d = ray_sphere(p, en->radius, o, dc, ds, max_range);
-    } else {
-      Rot q = rotof(kp, en, ep);
-      if (en->shape == VMASB200_BOX) d = ray_box(p, q.c, q.s, en->length, en->width, o, dc, ds, max_range);
-      else d = ray_line(p, q.c, q.s, en->length, o, dc, ds, max_range);
+  const int ntw = sn->n_tw;
+  uint32_t any = 0u;
+  for (int w = 0; w < ntw; ++w) any |= lm[w];
+  if (!any) return best;
+  float ds, dc;
+  sincosf(ang, &ds, &dc);
+  for (int w = 0; w < ntw; ++w) {
+    uint32_t m = lm[w];
+    const int tb = sn->tg_begin + 32 * w;
+    while (m) {
+      const int t = __ffs(m) - 1;
+      m &= m - 1;
+      const DEnt* __restrict__ en = kp.ents + __ldg(kp.targets + tb + t);
+      V2 p = posof(en, ep);
+      float d;
+      if (en->shape == VMASB200_SPHERE) {
+        d = ray_sphere(p, en->radius, o, dc, ds, max_range);
+      } else {
+        Rot q = rotof(kp, en, ep);
+        if (en->shape == VMASB200_BOX) d = ray_box(p, q.c, q.s, en->length, en->width, o, dc, ds, max_range);
+        else d = ray_line(p, q.c, q.s, en->length, o, dc, ds, max_range);
+      }
+      best = pmin(best, d);
     }
-    best = pmin(best, d);
   }
   return best;
 }

@@ -34,9 +34,8 @@ struct DEnt {               // 32 words
   int32_t agent;            // agent slot (index into the force / torque pointer tables) or -1
   int32_t act_off;          // float offset of (fx fy tq) inside the actout record or -1
   int32_t rot_slot;         // slot of the cos/sin cache or -1
-  int32_t csr_begin, csr_end;  // contribution list range (dynamic entities only)
   int32_t fin_off;          // float offset of (Fx Fy T) in the per-env work area (dynamic entities only)
-  int32_t pad[6];
+  int32_t pad[8];
 };
 static_assert(sizeof(DEnt) == 32 * 4, "DEnt must be 32 words");
 
@@ -54,6 +53,27 @@ struct DItem {              // 12 words; joints first (in reference order), then
 };
 static_assert(sizeof(DItem) == 12 * 4, "DItem must be 12 words");
 
+// Broad-phase row of candidate pair p (same order as the pair items): everything phase A of a substep reads, as two
+// 16-byte loads.  Position offsets are encoded: >= 0 float offset inside the dyn record, < 0: ~offset inside the stat
+// record.  The tests are sqrt-free but EXACT:
+//   verdict of World.collides (core.py:2796-2800):  sqrtf(d2) <= thr   <=>  d2 <= t2_bp
+//   (t2_bp = the largest float whose correctly rounded square root is <= thr; d2 = fma(dy,dy,dx*dx) is the very
+//   argument torch.linalg.vector_norm takes the root of)
+// and the cull only drops pairs whose force is provably zero (dist > dist_min, core.py:2835):
+//   rot_off < 0   circle cull: keep iff !(d2 > t2_cull)   (sphere-sphere: exact image of dist > r_a + r_b;
+//                 other types: (Rc_a + Rc_b + LINE_MIN_DIST) with a safety margin)
+//   rot_off >= 0  frame cull (a = line or box, b = sphere): b's centre in a's frame, keep iff |x| <= hx and |y| <= hy
+//                 (half extents + radius + LINE_MIN_DIST with a safety margin); rot_off = float offset of a's
+//                 cos/sin cache inside the env work area.
+struct DBroad {             // 8 words
+  int32_t pa_off, pb_off;
+  int32_t rot_off;
+  int32_t entry;            // list entry of the pair: item index | a << 12 | b << 21  (bit 30 = verdict, set at run time)
+  float t2_bp, t2_cull, hx, hy;
+};
+static_assert(sizeof(DBroad) == 8 * 4, "DBroad must be 8 words");
+constexpr int kEntryItemBits = 12, kEntryEntBits = 9;   // limits: 4096 items, 512 entities
+
 struct DRay {               // one per (sensor, ray): 4 words
   int32_t sensor;
   float angle;              // sensor-frame angle (row 0 of Lidar._angles)
@@ -68,7 +88,15 @@ struct DSensor {            // 8 words
   int32_t n_targets;
   int32_t tg_begin;         // index into the target list
   int32_t out_off;
-  int32_t pad[2];
+  int32_t tw_off;           // first word of this sensor's target survival mask inside the env's lmask area
+  int32_t n_tw;             // words of that mask = ceil(n_targets / 32)
+};
+
+struct DSWord {             // one per (sensor, 32-target word) of the LIDAR cull: 4 words
+  int32_t sensor;
+  int32_t tg_begin;         // index into targets[] / tcull2[] of bit 0
+  int32_t n;                // targets in this word (<= 32)
+  int32_t pad;
 };
 
 constexpr int kMaxAgents = 96;   // by-value kernel parameter tables
@@ -85,17 +113,19 @@ struct KParams {            // kernel parameter (by value)
   int32_t E, n_dyn, J, P, n_items, S, A, n_rot, n_sensors, n_rays, pair_words;
   int32_t dyn_stride, stat_stride, act_stride, lidar_stride;
   int32_t G, TE;            // lanes per env, envs per CTA (threads per CTA = G * TE)
-  // per-env work area (floats): [fin 3*n_dyn][rot 4*n_rot][res 4*n_items][frc 3*A]
-  int32_t work_stride, off_fin, off_rot, off_res, off_frc;
+  // per-env work area (4-byte words): [fin 3*n_dyn][rot 4*n_rot][res 4*n_items][frc 3*A][list n_items][lmask]
+  int32_t work_stride, off_fin, off_rot, off_res, off_frc, off_list, off_lmask, n_lmask_words;
   // device tables
   const DEnt* ents;
   const DItem* items;
-  const int32_t* csr;       // (item << 1) | side
+  const DBroad* broad;      // [P]
   const int32_t* dyn_list;  // entity index of every dynamic entity, in entity order
   const int32_t* rot_list;  // entity index per rot slot
   const DRay* rays;
   const DSensor* sensors;
   const int32_t* targets;
+  const float* tcull2;      // [n targets] squared LIDAR cull distance per (sensor, target): (max_range + Rc) with margin
+  const DSWord* swords;     // [n_lmask_words]
   // world constants (core.py:1090-1143)
   float sub_dt, Kc, Kj, Kt, margin;
   float xs, ys;

@@ -34,7 +34,8 @@ int upload_plan(vmasb200_plan* pl) {
   if (ndev <= 0) { set_error("no CUDA device: libvmasb200 has no CPU fallback"); return VMASB200_ERR_CUDA; }
   VB_CUDA(cudaGetDevice(&pl->device));
   std::vector<char> blob;
-  size_t o_ent = put(blob, pl->ents), o_item = put(blob, pl->items), o_csr = put(blob, pl->csr);
+  size_t o_ent = put(blob, pl->ents), o_item = put(blob, pl->items), o_broad = put(blob, pl->broad);
+  size_t o_tc = put(blob, pl->tcull2), o_sw = put(blob, pl->swords);
   size_t o_dyn = put(blob, pl->dyn_list), o_rot = put(blob, pl->rot_list), o_ray = put(blob, pl->rays);
   size_t o_sen = put(blob, pl->sensors), o_tg = put(blob, pl->targets);
   VB_CUDA(cudaMalloc(&pl->d_blob, blob.size()));
@@ -43,7 +44,9 @@ int upload_plan(vmasb200_plan* pl) {
   KParams& kp = pl->kp;
   kp.ents = reinterpret_cast<const DEnt*>(b + o_ent);
   kp.items = reinterpret_cast<const DItem*>(b + o_item);
-  kp.csr = reinterpret_cast<const int32_t*>(b + o_csr);
+  kp.broad = reinterpret_cast<const DBroad*>(b + o_broad);
+  kp.tcull2 = reinterpret_cast<const float*>(b + o_tc);
+  kp.swords = reinterpret_cast<const DSWord*>(b + o_sw);
   kp.dyn_list = reinterpret_cast<const int32_t*>(b + o_dyn);
   kp.rot_list = reinterpret_cast<const int32_t*>(b + o_rot);
   kp.rays = reinterpret_cast<const DRay*>(b + o_ray);
