@@ -31,7 +31,7 @@ def parse():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--scenario", default="navigation")
     ap.add_argument("--num-envs", type=int, default=32768, help="environments PER GPU (weak scaling)")
-    ap.add_argument("--lanes", type=int, default=0, help="lanes per env override (0 = plan default)")
+    ap.add_argument("--envs-per-cta", type=int, default=0, help="CTA tile override (0 = plan default)")
     ap.add_argument("--exact", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
@@ -195,12 +195,13 @@ def run_b200(args, rank, local_rank, world):
         dist.init_process_group("nccl", device_id=dev)
     n = args.num_envs
     wl = Workload(args.scenario, n, seed=rank)
-    wl.desc.lanes_per_env = args.lanes
+    wl.desc.envs_per_cta = args.envs_per_cta
     plan = StepPlan(wl.desc)
     A, K, W = plan.A, args.steps, args.warmup
 
     # R independent env batches visited round-robin so that a step's inputs come from HBM, not from L2
-    per_batch = 4 * n * (2 * plan.dyn_stride + plan.stat_stride + plan.act_stride + plan.lidar_stride + 3 * A)
+    ld = plan.ld_for(n)
+    per_batch = 4 * ld * (2 * plan.dyn_rows + plan.stat_rows + plan.act_rows + plan.lidar_rows + 3 * A)
     R = max(2, min(64, -(-2 * L2_BYTES // max(per_batch, 1))))
     dyn0, stat0 = plan.pack(wl.state0, wl.jrot0 if wl.jrot0.size else None)
     f_all, t_all = wl.random_actions(R)
@@ -208,14 +209,14 @@ def run_b200(args, rank, local_rank, world):
     ios, keep = [], []
     for r in range(R):
         dyn = torch.from_numpy(dyn0).to(dev)
-        stat = torch.from_numpy(stat0).to(dev) if plan.stat_stride else None
+        stat = torch.from_numpy(stat0).to(dev) if plan.stat_rows else None
         fr = torch.from_numpy(f_all[r]).to(dev)  # [N, A, 2]
         tr = torch.from_numpy(t_all[r]).to(dev)  # [N, A]
         forces = [fr[:, a, :] for a in range(A)]
         torques = [tr[:, a:a + 1] for a in range(A)]
-        act = torch.zeros(n, plan.act_stride, device=dev) if plan.act_stride else None
-        lid = torch.zeros(n, plan.lidar_stride, device=dev) if plan.lidar_stride else None
-        ios.append(plan.make_io(dyn, dyn, stat, forces, torques, act, lid, None, n, bool(args.exact), stream))
+        act = torch.zeros(plan.act_rows, ld, device=dev) if plan.act_rows else None
+        lid = torch.zeros(plan.lidar_rows, ld, device=dev) if plan.lidar_rows else None
+        ios.append(plan.make_io(dyn, dyn, stat, forces, torques, act, lid, None, n, ld, bool(args.exact), stream))
         keep.append((dyn, stat, fr, tr, act, lid))
 
     def barrier():
@@ -267,7 +268,8 @@ def run_b200(args, rank, local_rank, world):
             "data": "synthetic",
             "config": {"workload": f"{args.scenario} num_envs={n} per GPU, substeps={plan.S}, {len(wl.desc.lidars)} lidars",
                        "l2": f"{R} env batches visited round-robin, working set {R * per_batch / 2**20:.0f} MiB > L2 126 MiB",
-                       "lanes_per_env": plan.lanes_per_env, "exact": int(args.exact),
+                       "envs_per_cta": plan.envs_per_cta, "layout": "SoA rows [field][env], one thread per env",
+                       "exact": int(args.exact),
                        "l2_resident_ms_per_step": ms_hot / K},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": None, "peak_source": peak_src, "alg_bytes_per_env": plan.alg_bytes_per_env,
@@ -296,28 +298,34 @@ def run_e2e(plan, wl, n, K, world, dev):
         return t, t.numpy()
 
     dyn0, stat0 = plan.pack(wl.state0, wl.jrot0 if wl.jrot0.size else None)
+    ld = dyn0.shape[1]
     f, t = wl.random_actions(1)
     keep = [pinned(dyn0), pinned(stat0), pinned(f[0]), pinned(t[0])]
     dyn, stat, fr, tq = (k[1] for k in keep)
+    outs = [pinned(np.zeros((plan.dyn_rows, ld), np.float32)), pinned(np.zeros((max(plan.act_rows, 1), ld), np.float32)),
+            pinned(np.zeros((max(plan.lidar_rows, 1), ld), np.float32))]
+    out = (outs[0][1], outs[1][1][:plan.act_rows] if plan.act_rows else None,
+           outs[2][1][:plan.lidar_rows] if plan.lidar_rows else None)
     for _ in range(3):
-        out = plan.step_host(dyn, stat if plan.stat_stride else None, fr, tq, exact=False, want_masks=False)
+        plan.step_host(dyn, stat, fr, tq, exact=False, want_masks=False, out=out)
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
     t0 = time.perf_counter()
     for _ in range(K):
-        out = plan.step_host(dyn, stat if plan.stat_stride else None, fr, tq, exact=False, want_masks=False)
-        np.copyto(dyn, out[0])
+        # the step's results land in pinned host memory; the next step starts from them (a rollout through the host API)
+        plan.step_host(dyn, stat, fr, tq, exact=False, want_masks=False, out=out)
+        dyn, out = out[0], (dyn, out[1], out[2])
     torch.cuda.synchronize()
     el = time.perf_counter() - t0
     if world > 1:
         tt = torch.tensor([el], device=dev)
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         el = float(tt.item())
-    h2d = 4 * n * (plan.dyn_stride + plan.stat_stride + 3 * plan.A)
-    d2h = 4 * n * (plan.dyn_stride + plan.act_stride + plan.lidar_stride)
+    h2d = 4 * n * (plan.dyn_rows + plan.stat_rows + 3 * plan.A)
+    d2h = 4 * n * (plan.dyn_rows + plan.act_rows + plan.lidar_rows)
     return {"value": world * n * K / el, "unit": "env-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-            "api": "vmasb200_step_host (C ABI, host buffers)"}
+            "api": "vmasb200_step_host (C ABI, pinned host SoA buffers, chunked over 4 streams)"}
 
 
 def main():

@@ -22,17 +22,18 @@
  *   - there is NO CPU fallback anywhere in this library: without a CUDA device every compute entry point
  *     fails with VMASB200_ERR_CUDA.
  *
- * Data layout in HBM ("env records", env-major, fp32):
- *   dyn   [n_envs][dyn_stride]   per dynamic entity (movable or rotatable), in entity order:
- *                                 px py vx vy rot ang_vel                      (core.py:205-315 EntityState)
- *   stat  [n_envs][stat_stride]  per static entity that can collide / is jointed / is a LIDAR target:
- *                                 px py rot; then one float per joint whose fixed_rotation is per-env
- *                                 (joints.py:139-143)
- *   actout[n_envs][act_stride]   clamped fx fy torque of every agent that has max_f/f_range/max_t/t_range
- *                                 (the write-back of core.py:2017-2040)
- *   lidar [n_envs][lidar_stride] one float per ray, sensors concatenated in desc order (sensors.py:100-122)
- * strides are padded to multiples of 4 floats so that every env record (and any run of records) is a legal
- * cp.async.bulk (TMA 1-D) source/destination.  vmasb200_plan_layout() reports all offsets.
+ * Data layout in HBM: structure of arrays, fp32, one ROW per scalar field and `ld` floats between rows
+ * (ld >= n_envs, ld % 4 == 0, every buffer 16-byte aligned, so that any tile of a row is a legal cp.async.bulk /
+ * TMA 1-D source or destination and a warp's 32 lanes touch 32 consecutive environments):
+ *   dyn   [dyn_rows][ld]    6 rows per dynamic entity (movable or rotatable), in entity order:
+ *                            px py vx vy rot ang_vel                           (core.py:205-315 EntityState)
+ *   stat  [stat_rows][ld]   3 rows (px py rot) per static entity that can collide / is jointed / is a LIDAR
+ *                            target; then one row per joint whose fixed_rotation is per-env (joints.py:139-143)
+ *   actout[act_rows][ld]    3 rows (clamped fx fy torque) per agent that has max_f/f_range/max_t/t_range
+ *                            (the write-back of core.py:2017-2040)
+ *   lidar [lidar_rows][ld]  one row per ray, sensors concatenated in desc order (sensors.py:100-122)
+ * vmasb200_plan_layout() / _slots() report all row numbers.  A torch view of one field of all environments is
+ * `buf[row]` (contiguous [n_envs]); of an entity's position `buf[row:row+2].T` ([n_envs, 2], strides (1, ld)).
  */
 #ifndef VMASB200_H_
 #define VMASB200_H_
@@ -43,7 +44,7 @@
 extern "C" {
 #endif
 
-#define VMASB200_ABI_VERSION 1
+#define VMASB200_ABI_VERSION 2
 
 typedef enum vmasb200_status {
   VMASB200_OK = 0,
@@ -138,8 +139,8 @@ typedef struct vmasb200_world_desc {
   float x_semidim, y_semidim;
   float collision_force, joint_force, torque_constraint_force, contact_margin;
   float gravity[2];
-  /* Kernel shape override: lanes cooperating on one environment (4, 8, 16 or 32); 0 = let the plan choose. */
-  int32_t lanes_per_env;
+  /* Kernel shape override: environments (= threads) per CTA, a multiple of 32 up to 256; 0 = let the plan choose. */
+  int32_t envs_per_cta;
 } vmasb200_world_desc;
 
 enum { VMASB200_PAIR_SS = 0, VMASB200_PAIR_LS, VMASB200_PAIR_LL, VMASB200_PAIR_BS, VMASB200_PAIR_BL, VMASB200_PAIR_BB };
@@ -150,10 +151,10 @@ typedef struct vmasb200_pair {
 } vmasb200_pair;
 
 typedef struct vmasb200_layout {
-  int32_t dyn_stride, stat_stride, act_stride, lidar_stride; /* floats per env record (multiples of 4)  */
+  int32_t dyn_rows, stat_rows, act_rows, lidar_rows; /* rows of the four SoA buffers                     */
   int32_t n_pairs;        /* candidate pairs, in flag-bit order (ss, ls, ll, bs, bl, bb; a<b inside)     */
   int32_t pair_words;     /* ceil(n_pairs/32): words per substep in pair_active_out                      */
-  int32_t lanes_per_env;  /* kernel shape actually chosen                                                 */
+  int32_t envs_per_cta;   /* kernel shape actually chosen                                                 */
   int32_t n_dyn, n_stat, n_agents, n_act_out;
   int64_t alg_bytes_per_env; /* algorithmic HBM bytes per env-step (SURVEY 8d formula)                    */
 } vmasb200_layout;
@@ -168,32 +169,33 @@ const char* vmasb200_last_error(void);
 int vmasb200_plan_create(const vmasb200_world_desc* desc, vmasb200_plan** out);
 int vmasb200_plan_destroy(vmasb200_plan* plan);
 int vmasb200_plan_layout(const vmasb200_plan* plan, vmasb200_layout* out);
-/* Per-entity record slots: dyn_slot[e] / stat_slot[e] = float offset of the entity inside the dyn / stat
- * record, or -1; act_slot[e] = float offset of the clamped (fx fy torque) triple in the actout record, or -1.
+/* Per-entity rows: dyn_slot[e] / stat_slot[e] = first row of the entity inside the dyn / stat buffer, or -1;
+ * act_slot[e] = first row of the clamped (fx fy torque) triple in the actout buffer, or -1.
  * h: each array [n_entities] (any may be NULL). */
 int vmasb200_plan_slots(const vmasb200_plan* plan, int32_t* dyn_slot, int32_t* stat_slot, int32_t* act_slot);
 /* h: pairs[n_pairs] */
 int vmasb200_plan_pairs(const vmasb200_plan* plan, vmasb200_pair* pairs);
-/* float offset inside the stat record of the per-env fixed rotation of joint j, or -1. h: [n_joints] */
+/* row inside the stat buffer of the per-env fixed rotation of joint j, or -1. h: [n_joints] */
 int vmasb200_plan_joint_slots(const vmasb200_plan* plan, int32_t* joint_slot);
-/* float offset inside the lidar record of sensor i. h: [n_lidars] */
+/* first row inside the lidar buffer of sensor i. h: [n_lidars] */
 int vmasb200_plan_lidar_slots(const vmasb200_plan* plan, int32_t* lidar_slot);
 
 typedef struct vmasb200_step_io {
-  const float* dyn_in;             /* d: [n_envs][dyn_stride]                                           */
-  float* dyn_out;                  /* d: [n_envs][dyn_stride]; may alias dyn_in                         */
-  const float* stat;               /* d: [n_envs][stat_stride] (NULL iff stat_stride == 0)              */
+  const float* dyn_in;             /* d: [dyn_rows][ld]                                                 */
+  float* dyn_out;                  /* d: [dyn_rows][ld]; may alias dyn_in                               */
+  const float* stat;               /* d: [stat_rows][ld] (NULL iff stat_rows == 0)                      */
   /* agent.state.force / agent.state.torque of every agent, in entity order of the agents (core.py:2017-2040).
    * h: arrays of n_agents device pointers + row strides in floats; a NULL pointer reads as zeros.        */
   const float* const* force_ptrs;
   const int64_t* force_strides;
   const float* const* torque_ptrs;
   const int64_t* torque_strides;
-  float* act_out;                  /* d: [n_envs][act_stride] or NULL (NULL iff act_stride == 0)        */
-  float* lidar_out;                /* d: [n_envs][lidar_stride]; NULL skips the LIDAR epilogue          */
+  float* act_out;                  /* d: [act_rows][ld] (NULL iff act_rows == 0)                        */
+  float* lidar_out;                /* d: [lidar_rows][ld]; NULL skips the LIDAR epilogue                */
   uint32_t* pair_active_out;       /* d: [substeps][pair_words] batch-wide broad-phase results of
                                       core.py:2796-2800 per (substep, pair), or NULL                     */
   int64_t n_envs;
+  int64_t ld;                      /* floats between rows of every SoA buffer: >= n_envs, multiple of 4 */
   /* 0: one fused speculative launch + a device-side verified exact fix-up (no host sync);
    * 1: always take the exact per-substep path (flag reduction before every substep).                    */
   int32_t exact;
@@ -204,17 +206,21 @@ typedef struct vmasb200_step_io {
  * semi-implicit Euler integration} plus the LIDAR epilogue, for every env.  Asynchronous. */
 int vmasb200_step(vmasb200_plan* plan, const vmasb200_step_io* io);
 
-/* Same step with HOST buffers: H2D of inputs, kernel(s), D2H of results, then a stream sync.
- * h_force [n_envs][n_agents][2], h_torque [n_envs][n_agents] (either may be NULL = zeros).
- * Output pointers may be NULL to skip that copy.  Device staging is owned by the plan and grows on demand. */
+/* Same step with HOST buffers (same SoA layout, row stride ld): H2D of inputs, kernel(s), D2H of results, then a
+ * sync.  The batch is cut into chunks of environments that are pipelined over several streams so that the H2D of
+ * one chunk, the kernel of another and the D2H of a third overlap (pinned host buffers make the copies truly
+ * asynchronous; pageable ones still work).  h_force [n_envs][n_agents][2], h_torque [n_envs][n_agents] (either may
+ * be NULL = zeros).  Output pointers may be NULL to skip that copy.  h_pair_active / exact != 0 need the batch-wide
+ * verdicts and therefore run the batch as ONE chunk.  Device staging is owned by the plan and grows on demand. */
 int vmasb200_step_host(vmasb200_plan* plan, const float* h_dyn_in, const float* h_stat, const float* h_force,
                        const float* h_torque, float* h_dyn_out, float* h_act_out, float* h_lidar_out,
-                       uint32_t* h_pair_active, int64_t n_envs, int32_t exact);
+                       uint32_t* h_pair_active, int64_t n_envs, int64_t ld, int32_t exact);
 
-/* World.cast_rays(entity, angles, max_range, entity_filter) (core.py:1661-1785) on the current records.
- * angles d: [n_envs][n_rays] WORLD-frame ray angles with row stride `angles_stride` floats;
- * targets h: [n_targets] entity indices (already filtered); out d: [n_envs][n_rays] contiguous. */
-int vmasb200_cast_rays(vmasb200_plan* plan, const float* dyn, const float* stat, int32_t entity,
+/* World.cast_rays(entity, angles, max_range, entity_filter) (core.py:1661-1785) on the current SoA buffers.
+ * angles d: [n_envs][n_rays] WORLD-frame ray angles with row stride `angles_stride` floats (the torch tensor
+ * Lidar.measure builds, sensors.py:115); targets h: [n_targets] entity indices (already filtered);
+ * out d: [n_envs][n_rays] contiguous (the tensor World.cast_rays returns). */
+int vmasb200_cast_rays(vmasb200_plan* plan, const float* dyn, const float* stat, int64_t ld, int32_t entity,
                        const float* angles, int64_t angles_stride, int32_t n_rays, float max_range,
                        const int32_t* targets, int32_t n_targets, float* out, int64_t n_envs, void* stream);
 

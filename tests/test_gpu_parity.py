@@ -24,10 +24,10 @@ def _forces(fx, t):
 
 def _act_check(pl, fx, act, k):
     for slot, e in enumerate(pl.agents):
-        o = pl.act_slot[e]
-        if o >= 0:
-            assert close(act[:, o:o + 2], fx.force_after[k][slot])
-            assert close(act[:, o + 2], fx.torque_after[k][slot])
+        if pl.act_slot[e] >= 0:
+            f, tq = pl.act_of(act, e, fx.n_envs)
+            assert close(f, fx.force_after[k][slot])
+            assert close(tq, fx.torque_after[k][slot])
 
 
 @pytest.mark.parametrize("exact", [True, False])
@@ -55,9 +55,8 @@ def test_one_step(name, exact):
         if act is not None:
             _act_check(pl, fx, act, k)
         for li in range(len(fx.desc.lidars)):
-            o = pl.lidar_slot[li]
-            r = len(fx.desc.lidars[li].angles)
-            assert close(lid[:, o:o + r], fx.lidar[li][k]), f"{name} lidar {li}: {max_err(lid[:, o:o+r], fx.lidar[li][k]):.3e}"
+            got_l = pl.lidar_of(lid, li, fx.n_envs)
+            assert close(got_l, fx.lidar[li][k]), f"{name} lidar {li}: {max_err(got_l, fx.lidar[li][k]):.3e}"
 
 
 @pytest.mark.parametrize("name", ALL)

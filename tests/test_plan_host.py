@@ -23,7 +23,7 @@ def test_exports_match_header():
     assert declared == set(_lib.EXPORTS)
     for name in declared:
         assert hasattr(L, name), name
-    assert L.vmasb200_version() == 1
+    assert L.vmasb200_version() == 2
 
 
 def _expected_pairs(desc):
@@ -52,11 +52,12 @@ def test_plan_layout(name):
     assert pl.pairs == _expected_pairs(fx.desc)
     ents = fx.desc.entities
     n_dyn = sum(e.dynamic for e in ents)
-    assert pl.n_dyn == n_dyn and pl.dyn_stride % 4 == 0 and pl.dyn_stride >= 6 * n_dyn
+    assert pl.n_dyn == n_dyn and pl.dyn_rows == 6 * n_dyn and pl.envs_per_cta % 32 == 0
     assert all((pl.dyn_slot[i] >= 0) == e.dynamic for i, e in enumerate(ents))
     assert all(not (pl.dyn_slot[i] >= 0 and pl.stat_slot[i] >= 0) for i in range(len(ents)))
     # pack / unpack round trip
     dyn, stat = pl.pack(fx.state0, fx.jrot0)
+    assert dyn.shape[1] % 4 == 0 and dyn.shape[1] >= fx.n_envs
     back = pl.unpack(dyn, np.zeros_like(fx.state0))
     for i, e in enumerate(ents):
         if e.dynamic:

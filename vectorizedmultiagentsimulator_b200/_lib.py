@@ -55,9 +55,9 @@ def lib():
     L.vmasb200_plan_joint_slots.argtypes = [vp, i32p]
     L.vmasb200_plan_lidar_slots.argtypes = [vp, i32p]
     L.vmasb200_step.argtypes = [vp, C.POINTER(CStepIO)]
-    L.vmasb200_step_host.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp, C.c_int64, C.c_int32]
+    L.vmasb200_step_host.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp, C.c_int64, C.c_int64, C.c_int32]
     L.vmasb200_cast_rays.argtypes = [
-        vp, vp, vp, C.c_int32, vp, C.c_int64, C.c_int32, C.c_float, i32p, C.c_int32, vp, C.c_int64, vp,
+        vp, vp, vp, C.c_int64, C.c_int32, vp, C.c_int64, C.c_int32, C.c_float, i32p, C.c_int32, vp, C.c_int64, vp,
     ]
     L.vmasb200_sync_check.argtypes = [vp, vp, C.POINTER(C.c_int64)]
     for name in EXPORTS:

@@ -77,7 +77,7 @@ int build_plan(const vmasb200_world_desc* d, vmasb200_plan* pl) {
     DItem it{};
     it.type = IT_JOINT; it.a = jt.entity_a; it.b = jt.entity_b; it.thr = 0.f;
     it.dax = jt.delta_a[0]; it.day = jt.delta_a[1]; it.dbx = jt.delta_b[0]; it.dby = jt.delta_b[1];
-    it.dist = jt.dist; it.rotate = jt.rotate; it.fixed_rot = jt.fixed_rotation; it.fr_off = -1;
+    it.dist = jt.dist; it.rotate = jt.rotate; it.fixed_rot = jt.fixed_rotation; it.fr_row = -1;
     pl->items.push_back(it);
   }
   for (int t = 0; t < 6; ++t)
@@ -87,7 +87,7 @@ int build_plan(const vmasb200_world_desc* d, vmasb200_plan* pl) {
         bool sw;
         if (pair_type(d->entities[a].shape, d->entities[b].shape, sw) != t) continue;
         DItem it{};
-        it.type = t; it.a = sw ? b : a; it.b = sw ? a : b; it.fr_off = -1;
+        it.type = t; it.a = sw ? b : a; it.b = sw ? a : b; it.fr_row = -1;
         it.thr = (float)(d->entities[a].circumscribed_radius + d->entities[b].circumscribed_radius);
         pl->items.push_back(it);
         pl->pairs.push_back(vmasb200_pair{t, it.a, it.b});
@@ -95,14 +95,11 @@ int build_plan(const vmasb200_world_desc* d, vmasb200_plan* pl) {
   kp.n_items = (int)pl->items.size();
   kp.P = kp.n_items - kp.J;
   kp.pair_words = (kp.P + 31) / 32;
-  if (kp.n_items > (1 << kEntryItemBits) || E > (1 << kEntryEntBits)) {
-    set_error("more than 4096 work items or 512 entities are not supported by the CUDA step"); return VMASB200_ERR_UNSUPPORTED;
-  }
 
   // ---- sensors (sensors.py:46-69, core.py:1677-1690)
-  pl->sensors.clear(); pl->rays.clear(); pl->targets.clear(); pl->lidar_slot.assign(d->n_lidars, 0);
-  pl->tcull2.clear(); pl->swords.clear();
-  int ray_off = 0;
+  pl->sensors.clear(); pl->ray_angles.clear(); pl->targets.clear(); pl->lidar_slot.assign(d->n_lidars, 0);
+  pl->tcull2.clear();
+  int ray_off = 0, n_lmask = 0, max_rays = 0;
   for (int k = 0; k < d->n_lidars; ++k) {
     const vmasb200_lidar& ld = d->lidars[k];
     if (ld.entity < 0 || ld.entity >= E || ld.n_rays < 0 || ld.n_targets < 0 || (ld.n_rays && !ld.angles) || (ld.n_targets && !ld.targets)) {
@@ -117,17 +114,18 @@ int build_plan(const vmasb200_world_desc* d, vmasb200_plan* pl) {
       // a ray of length max_range cannot reach a shape whose centre is farther than max_range + circumscribed radius
       pl->tcull2.push_back(sq_up(with_margin((double)ld.max_range + d->entities[ld.targets[t]].circumscribed_radius)));
     }
-    sn.tw_off = (int)pl->swords.size();
+    sn.tw_off = n_lmask;  // relative to row_lmask
     sn.n_tw = (ld.n_targets + 31) / 32;
-    for (int w = 0; w < sn.n_tw; ++w)
-      pl->swords.push_back(DSWord{k, sn.tg_begin + 32 * w, std::min(32, ld.n_targets - 32 * w), 0});
-    for (int r = 0; r < ld.n_rays; ++r) pl->rays.push_back(DRay{k, ld.angles[r], ray_off + r, 0});
+    n_lmask += sn.n_tw;
+    for (int r = 0; r < ld.n_rays; ++r) pl->ray_angles.push_back(ld.angles[r]);
     pl->lidar_slot[k] = ray_off;
     ray_off += ld.n_rays;
+    max_rays = std::max(max_rays, ld.n_rays);
     pl->sensors.push_back(sn);
   }
-  kp.n_sensors = d->n_lidars; kp.n_rays = ray_off;
-  kp.lidar_stride = align4(ray_off);
+  kp.n_sensors = d->n_lidars; kp.n_rays = ray_off; kp.max_rays = max_rays;
+  kp.lidar_rows = ray_off;
+  kp.n_lmask_words = n_lmask;
 
   // ---- which entities are read by the step at all, and which need cos/sin
   std::vector<char> used(E, 0), trig(E, 0);
@@ -148,10 +146,10 @@ int build_plan(const vmasb200_world_desc* d, vmasb200_plan* pl) {
     }
   }
 
-  // ---- record layout + entity table
+  // ---- SoA row layout + entity table
   pl->ents.assign(E, DEnt{});
   pl->dyn_slot.assign(E, -1); pl->stat_slot.assign(E, -1); pl->act_slot.assign(E, -1);
-  pl->dyn_list.clear(); pl->rot_list.clear(); pl->agent_entities.clear();
+  pl->dyn_list.clear(); pl->trig_list.clear(); pl->agent_entities.clear();
   int dyn_off = 0, stat_off = 0, act_off = 0, n_act = 0, n_stat = 0;
   for (int e = 0; e < E; ++e) {
     const vmasb200_entity& s = d->entities[e];
@@ -168,7 +166,7 @@ int build_plan(const vmasb200_world_desc* d, vmasb200_plan* pl) {
     else if (d->angular_friction > 0.f) { o.flags |= DE_ANGF_ON; o.ang_fric = d->angular_friction; }
     o.gx = s.gravity[0]; o.gy = s.gravity[1];
     o.max_f = s.max_f; o.f_range = s.f_range; o.max_t = s.max_t; o.t_range = s.t_range;
-    o.dyn_off = o.stat_off = o.agent = o.act_off = o.rot_slot = -1;
+    o.dyn_off = o.stat_off = o.agent = o.act_off = o.trig_row = o.fin_row = o.pos_row = o.rot_row = -1;
     const bool dynamic = s.flags & (VMASB200_E_MOVABLE | VMASB200_E_ROTATABLE);
     if (s.flags & VMASB200_E_AGENT) {
       o.agent = (int)pl->agent_entities.size();
@@ -177,7 +175,6 @@ int build_plan(const vmasb200_world_desc* d, vmasb200_plan* pl) {
     if (dynamic) {
       o.flags |= DE_DYNAMIC;
       o.dyn_off = dyn_off; pl->dyn_slot[e] = dyn_off; dyn_off += 6;
-      o.fin_off = 3 * (int)pl->dyn_list.size();
       pl->dyn_list.push_back(e);
       if ((s.flags & VMASB200_E_AGENT) &&
           (s.flags & (VMASB200_E_MAX_F | VMASB200_E_F_RANGE | VMASB200_E_MAX_T | VMASB200_E_T_RANGE))) {
@@ -188,31 +185,49 @@ int build_plan(const vmasb200_world_desc* d, vmasb200_plan* pl) {
     }
     if (trig[e]) {
       o.flags |= DE_TRIG;
-      o.rot_slot = (int)pl->rot_list.size();
-      pl->rot_list.push_back(e);
+      pl->trig_list.push_back(e);
     }
   }
   kp.A = (int)pl->agent_entities.size();
   if (kp.A > kMaxAgents) { set_error("more than 96 agents are not supported by the CUDA step"); return VMASB200_ERR_UNSUPPORTED; }
   pl->joint_slot.assign(d->n_joints, -1);
   for (int j = 0; j < d->n_joints; ++j)
-    if (d->joints[j].fixed_rotation_per_env && !d->joints[j].rotate) {
-      pl->items[j].fr_off = stat_off; pl->joint_slot[j] = stat_off; stat_off += 1;
-    }
+    if (d->joints[j].fixed_rotation_per_env && !d->joints[j].rotate) { pl->joint_slot[j] = stat_off; stat_off += 1; }
   kp.n_dyn = (int)pl->dyn_list.size();
-  kp.n_rot = (int)pl->rot_list.size();
-  kp.dyn_stride = align4(dyn_off); kp.stat_stride = align4(stat_off); kp.act_stride = align4(act_off);
+  kp.n_trig = (int)pl->trig_list.size();
+  kp.dyn_rows = dyn_off; kp.stat_rows = stat_off; kp.act_rows = act_off;
+
+  // work rows
+  kp.row_fin = 0;
+  kp.row_trig = kp.row_fin + 3 * kp.n_dyn;
+  kp.row_frc = kp.row_trig + 4 * kp.n_trig;
+  kp.row_lmask = kp.row_frc + 3 * kp.A;
+  kp.work_rows = kp.row_lmask + kp.n_lmask_words;
+  for (int i = 0; i < kp.n_dyn; ++i) pl->ents[pl->dyn_list[i]].fin_row = kp.row_fin + 3 * i;
+  for (int i = 0; i < kp.n_trig; ++i) pl->ents[pl->trig_list[i]].trig_row = kp.row_trig + 4 * i;
+  for (int e = 0; e < E; ++e) {
+    DEnt& o = pl->ents[e];
+    if (o.dyn_off >= 0) { o.pos_row = o.dyn_off; o.rot_row = o.dyn_off + 4; }
+    else if (o.stat_off >= 0) { o.pos_row = kp.dyn_rows + o.stat_off; o.rot_row = o.pos_row + 2; }
+  }
+  for (DSensor& sn : pl->sensors) sn.tw_off += kp.row_lmask;
+  for (int i = 0; i < kp.n_items; ++i) {
+    DItem& it = pl->items[i];
+    const DEnt &a = pl->ents[it.a], &b = pl->ents[it.b];
+    it.fin_a = a.fin_row; it.fin_b = b.fin_row;
+    it.acc = ((a.flags & VMASB200_E_MOVABLE) ? ACC_A_MOV : 0) | ((a.flags & VMASB200_E_ROTATABLE) ? ACC_A_ROT : 0) |
+             ((b.flags & VMASB200_E_MOVABLE) ? ACC_B_MOV : 0) | ((b.flags & VMASB200_E_ROTATABLE) ? ACC_B_ROT : 0);
+    if (i < kp.J && pl->joint_slot[i] >= 0) it.fr_row = kp.dyn_rows + pl->joint_slot[i];
+  }
 
   // ---- broad-phase table (one row per candidate pair, same order as the pair items)
   pl->broad.clear();
-  auto enc_pos = [&](int e) { return pl->ents[e].dyn_off >= 0 ? pl->ents[e].dyn_off : ~pl->ents[e].stat_off; };
   for (int p = 0; p < kp.P; ++p) {
     const DItem& it = pl->items[kp.J + p];
     const vmasb200_entity &sa = d->entities[it.a], &sb = d->entities[it.b];
     DBroad b{};
-    b.pa_off = enc_pos(it.a); b.pb_off = enc_pos(it.b);
-    b.rot_off = -1;
-    b.entry = (kp.J + p) | (it.a << kEntryItemBits) | (it.b << (kEntryItemBits + kEntryEntBits));
+    b.pa_row = pl->ents[it.a].pos_row; b.pb_row = pl->ents[it.b].pos_row;
+    b.trig_row = -1;
     b.t2_bp = sq_le(it.thr);
     if (it.type == IT_SS) {
       const float dmin = sa.radius + sb.radius;  // fp32 sum = the kernel's dist_min (core.py:2312)
@@ -223,42 +238,22 @@ int build_plan(const vmasb200_world_desc* d, vmasb200_plan* pl) {
         const double reach = with_margin((double)sb.radius + kLMDd);
         b.hx = (float)((double)sa.length / 2 + reach);
         b.hy = (float)((it.type == IT_BS ? (double)sa.width / 2 : 0.0) + reach);
-        b.rot_off = -2;  // resolved below, once the work area layout is known
+        b.trig_row = pl->ents[it.a].trig_row;
       }
     }
     pl->broad.push_back(b);
   }
 
-  // ---- kernel shape
-  int G = d->lanes_per_env;
-  if (G == 0) {
-    int target = std::max(std::max(kp.n_items, kp.n_dyn), (kp.n_rays + 1) / 2);
-    G = 1;
-    while (G < 32 && G * 2 <= target) G *= 2;
+  // ---- kernel shape: one thread per env, TE envs per CTA; keep >= 2 CTAs per SM resident when the world allows it
+  const int per_env = 4 * (kp.dyn_rows + kp.stat_rows + kp.lidar_rows + kp.work_rows) + 4 * kp.n_sensors;
+  const int fixed = 64;
+  int TE = d->envs_per_cta;
+  if (TE == 0) {
+    TE = 64;
+    while (TE > 32 && fixed + TE * per_env > 100 * 1024) TE -= 32;
   }
-  if (G < 1 || G > 32 || (G & (G - 1))) { set_error("lanes_per_env must be a power of two <= 32"); return VMASB200_ERR_INVALID; }
-  kp.G = G;
-  kp.off_fin = 0;
-  kp.off_rot = align4(3 * kp.n_dyn);
-  kp.off_res = kp.off_rot + 4 * kp.n_rot;
-  kp.off_frc = kp.off_res + 4 * kp.n_items;
-  kp.off_list = kp.off_frc + 3 * kp.A;
-  kp.off_lmask = kp.off_list + kp.n_items;
-  kp.n_lmask_words = (int)pl->swords.size();
-  kp.work_stride = align4(kp.off_lmask + kp.n_lmask_words);
-  for (int p = 0; p < kp.P; ++p)
-    if (pl->broad[p].rot_off == -2) pl->broad[p].rot_off = kp.off_rot + 4 * pl->ents[pl->items[kp.J + p].a].rot_slot;
-  if (((kp.work_stride / 4) & 1) == 0) kp.work_stride += 4;  // odd number of float4 per env: groups hit distinct banks
-  const int per_env = 4 * (kp.dyn_stride + kp.stat_stride + kp.act_stride + kp.lidar_stride + kp.work_stride);
-  const int fixed = 16 + 12 * kp.S * kp.pair_words + 16;
-  const int budget = 200 * 1024;
-  int TE = 256 / G;
-  while (TE > 1 && fixed + TE * per_env > budget) TE /= 2;
+  if (TE < 32 || TE > 256 || TE % 32) { set_error("envs_per_cta must be a multiple of 32 in [32, 256]"); return VMASB200_ERR_INVALID; }
   if (fixed + TE * per_env > 226 * 1024) { set_error("world too large for one CTA's shared memory"); return VMASB200_ERR_UNSUPPORTED; }
-  if ((TE * G) % 32) {  // warp votes need full warps: fall back to a warp per env
-    G = 32; kp.G = 32; TE = 8;
-    while (TE > 1 && fixed + TE * per_env > budget) TE /= 2;
-  }
   kp.TE = TE;
 
   // ---- world constants
@@ -269,8 +264,8 @@ int build_plan(const vmasb200_world_desc* d, vmasb200_plan* pl) {
   kp.has_wgrav = !(d->gravity[0] == 0.f && d->gravity[1] == 0.f);  // core.py:2044
 
   vmasb200_layout& L = pl->layout;
-  L.dyn_stride = kp.dyn_stride; L.stat_stride = kp.stat_stride; L.act_stride = kp.act_stride; L.lidar_stride = kp.lidar_stride;
-  L.n_pairs = kp.P; L.pair_words = kp.pair_words; L.lanes_per_env = kp.G;
+  L.dyn_rows = kp.dyn_rows; L.stat_rows = kp.stat_rows; L.act_rows = kp.act_rows; L.lidar_rows = kp.lidar_rows;
+  L.n_pairs = kp.P; L.pair_words = kp.pair_words; L.envs_per_cta = kp.TE;
   L.n_dyn = kp.n_dyn; L.n_stat = n_stat; L.n_agents = kp.A; L.n_act_out = n_act;
   // state read + write, static pose read, action read, clamped action write, lidar write
   L.alg_bytes_per_env = 4ll * (12 * kp.n_dyn + 3 * n_stat + 3 * kp.A + 3 * n_act + kp.n_rays);

@@ -8,6 +8,10 @@
 #include "../../include/vmasb200.h"
 #include "tables.h"
 
+namespace vb {
+constexpr int kHostStreams = 4;  // chunk streams of the host-buffer entry point
+}
+
 struct vmasb200_plan {
   vb::KParams kp{};  // device pointers are filled by upload()
   vmasb200_layout layout{};
@@ -15,10 +19,8 @@ struct vmasb200_plan {
   std::vector<vb::DEnt> ents;
   std::vector<vb::DItem> items;
   std::vector<vb::DBroad> broad;
-  std::vector<int32_t> dyn_list, rot_list, targets;
-  std::vector<float> tcull2;
-  std::vector<vb::DSWord> swords;
-  std::vector<vb::DRay> rays;
+  std::vector<int32_t> dyn_list, trig_list, targets;
+  std::vector<float> tcull2, ray_angles;
   std::vector<vb::DSensor> sensors;
   std::vector<vmasb200_pair> pairs;
   std::vector<int32_t> dyn_slot, stat_slot, act_slot, joint_slot, lidar_slot, agent_entities;
@@ -27,13 +29,16 @@ struct vmasb200_plan {
   bool uploaded = false;
   int device = -1;
   void* d_blob = nullptr;
-  uint32_t* d_bits = nullptr;  // [3][S][pair_words]: exact flags, any, thin
-  // staging of vmasb200_step_host
-  int64_t host_cap = 0;
-  float *d_dyn = nullptr, *d_stat = nullptr, *d_force = nullptr, *d_torque = nullptr, *d_act = nullptr, *d_lidar = nullptr;
-  int64_t u_cap = 0;           // speculative path scratch: tainted env list + their records
+  // [4][S][pair_words] bit arrays (flags, any_exact, any_spec, thin) + 4 counters, and the tainted-env scratch of
+  // the speculative launch.  One step at a time per plan.
+  uint32_t* d_bits = nullptr;
+  int64_t u_cap = 0;
   int* d_ulist = nullptr;
   float* d_ubuf = nullptr;
+  // staging of vmasb200_step_host
+  int64_t host_cap = 0;        // row stride (floats) of the staging buffers
+  float *d_dyn = nullptr, *d_stat = nullptr, *d_force = nullptr, *d_torque = nullptr, *d_act = nullptr, *d_lidar = nullptr;
+  cudaStream_t streams[vb::kHostStreams] = {};
 };
 
 namespace vb {

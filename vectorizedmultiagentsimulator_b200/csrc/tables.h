@@ -1,9 +1,19 @@
-// tables.h - plain-data plan tables shared by the host plan builder (plan.cpp part of vmasb200.cu) and the kernels.
+// tables.h - plain-data plan tables shared by the host plan builder (plan.cpp) and the kernels.
 //
 // The plan is the static half of the reference's per-substep Python work: entity attributes (core.py:537-1085),
-// the pair enumeration + bucketing of core.py:2103-2173, the joint list (joints.py:147-215), the per-entity
-// accumulation order of update_env_forces (core.py:2190-2198) and the Lidar target lists (core.py:1677-1690).
-// Everything is 32-bit words so the tables can be read with ld.global.nc by every lane.
+// the pair enumeration + bucketing of core.py:2103-2173, the joint list (joints.py:147-215), the accumulation order
+// of update_env_forces (core.py:2190-2198) and the Lidar target lists (core.py:1677-1690).
+//
+// Execution model the tables are laid out for: ONE THREAD PER ENVIRONMENT.  Every loop over entities / pairs /
+// joints / sensors is uniform across the warp, so every table read below is a warp-uniform (broadcast) load and
+// all index arithmetic runs once per warp; only the env's own state differs between lanes.  That state lives in
+// shared memory as structure of arrays, "rows" of TE floats (TE = envs per CTA): word `row * TE + tid`.
+//   env rows  [0, dyn_rows)                  staged dyn buffer rows   (6 per dynamic entity: px py vx vy rot w)
+//             [dyn_rows, dyn_rows+stat_rows) staged stat buffer rows  (3 per static entity: px py rot; joint rots)
+//   work rows fin  3 per dynamic entity (Fx Fy T of the running substep, core.py:1975-1992)
+//             trig 4 per entity that needs cos/sin (c s c2 s2)
+//             frc  3 per agent (state.force x y, state.torque; clamped in place, core.py:2017-2040)
+//             lmask one per (sensor, 32-target word)
 #pragma once
 #include <stdint.h>
 
@@ -16,7 +26,7 @@ enum : uint32_t {
   DE_LINF_ON = 1u << 16,   // a linear friction coefficient applies (entity's, else world's > 0; core.py:2075-2087)
   DE_ANGF_ON = 1u << 17,   // same for angular friction (core.py:2088-2101)
   DE_TRIG = 1u << 18,      // cos/sin of the rotation are needed by some pair / joint / ray
-  DE_DYNAMIC = 1u << 19    // has a dyn record (movable or rotatable)
+  DE_DYNAMIC = 1u << 19    // has dyn rows (movable or rotatable)
 };
 
 struct DEnt {               // 32 words
@@ -29,19 +39,24 @@ struct DEnt {               // 32 words
   float lin_fric, ang_fric; // resolved coefficient
   float gx, gy;             // entity gravity
   float max_f, f_range, max_t, t_range;
-  int32_t dyn_off;          // float offset inside the dyn record (px py vx vy rot w) or -1
-  int32_t stat_off;         // float offset inside the stat record (px py rot) or -1
+  int32_t dyn_off;          // first row inside the dyn buffer (px py vx vy rot w) or -1
+  int32_t stat_off;         // first row inside the stat buffer (px py rot) or -1
   int32_t agent;            // agent slot (index into the force / torque pointer tables) or -1
-  int32_t act_off;          // float offset of (fx fy tq) inside the actout record or -1
-  int32_t rot_slot;         // slot of the cos/sin cache or -1
-  int32_t fin_off;          // float offset of (Fx Fy T) in the per-env work area (dynamic entities only)
-  int32_t pad[8];
+  int32_t act_off;          // first row of (fx fy tq) inside the actout buffer or -1
+  int32_t trig_row;         // work row of the cos/sin cache (c s c2 s2) or -1
+  int32_t fin_row;          // work row of (Fx Fy T) (dynamic entities only) or -1
+  int32_t pos_row;          // env row of px (py = +1): dyn_off, or dyn_rows + stat_off; -1 = not staged
+  int32_t rot_row;          // env row of rot: pos_row + 4 (dynamic) / pos_row + 2 (static)
+  int32_t pad[6];
 };
 static_assert(sizeof(DEnt) == 32 * 4, "DEnt must be 32 words");
 
 enum { IT_SS = 0, IT_LS, IT_LL, IT_BS, IT_BL, IT_BB, IT_JOINT };
 
-struct DItem {              // 12 words; joints first (in reference order), then candidate pairs in type order
+// accumulation switches of update_env_forces (core.py:2190-2198)
+enum : int32_t { ACC_A_MOV = 1, ACC_A_ROT = 2, ACC_B_MOV = 4, ACC_B_ROT = 8 };
+
+struct DItem {              // 16 words; joints first (in reference order), then candidate pairs in type order
   int32_t type;
   int32_t a, b;             // entity indices, already in the reference's (line,sphere)/(box,sphere)/(box,line) order
   float thr;                // broad-phase threshold (float)(Rc_a + Rc_b in double), core.py:2796-2800
@@ -49,37 +64,30 @@ struct DItem {              // 12 words; joints first (in reference order), then
   float dist;               // joint distance
   int32_t rotate;           // joint.rotate
   float fixed_rot;
-  int32_t fr_off;           // float offset inside the stat record of the per-env fixed rotation or -1
+  int32_t fr_row;           // env row of the per-env fixed rotation or -1
+  int32_t fin_a, fin_b;     // work rows of the (Fx Fy T) accumulators of a / b, or -1 (static entity)
+  int32_t acc;              // ACC_* bits
+  int32_t pad;
 };
-static_assert(sizeof(DItem) == 12 * 4, "DItem must be 12 words");
+static_assert(sizeof(DItem) == 16 * 4, "DItem must be 16 words");
 
-// Broad-phase row of candidate pair p (same order as the pair items): everything phase A of a substep reads, as two
-// 16-byte loads.  Position offsets are encoded: >= 0 float offset inside the dyn record, < 0: ~offset inside the stat
-// record.  The tests are sqrt-free but EXACT:
+// Broad-phase row of candidate pair p (same order as the pair items): everything the cull of a substep reads, as two
+// 16-byte loads.  The tests are sqrt-free but EXACT:
 //   verdict of World.collides (core.py:2796-2800):  sqrtf(d2) <= thr   <=>  d2 <= t2_bp
 //   (t2_bp = the largest float whose correctly rounded square root is <= thr; d2 = fma(dy,dy,dx*dx) is the very
 //   argument torch.linalg.vector_norm takes the root of)
 // and the cull only drops pairs whose force is provably zero (dist > dist_min, core.py:2835):
-//   rot_off < 0   circle cull: keep iff !(d2 > t2_cull)   (sphere-sphere: exact image of dist > r_a + r_b;
-//                 other types: (Rc_a + Rc_b + LINE_MIN_DIST) with a safety margin)
-//   rot_off >= 0  frame cull (a = line or box, b = sphere): b's centre in a's frame, keep iff |x| <= hx and |y| <= hy
-//                 (half extents + radius + LINE_MIN_DIST with a safety margin); rot_off = float offset of a's
-//                 cos/sin cache inside the env work area.
+//   trig_row < 0   circle cull: keep iff !(d2 > t2_cull)   (sphere-sphere: exact image of dist > r_a + r_b;
+//                  other types: (Rc_a + Rc_b + LINE_MIN_DIST) with a safety margin)
+//   trig_row >= 0  frame cull (a = line or box, b = sphere): b's centre in a's frame, keep iff |x| <= hx and |y| <= hy
+//                  (half extents + radius + LINE_MIN_DIST with a safety margin); trig_row = work row of a's cos/sin.
 struct DBroad {             // 8 words
-  int32_t pa_off, pb_off;
-  int32_t rot_off;
-  int32_t entry;            // list entry of the pair: item index | a << 12 | b << 21  (bit 30 = verdict, set at run time)
+  int32_t pa_row, pb_row;   // env rows of the two positions
+  int32_t trig_row;
+  int32_t pad;
   float t2_bp, t2_cull, hx, hy;
 };
 static_assert(sizeof(DBroad) == 8 * 4, "DBroad must be 8 words");
-constexpr int kEntryItemBits = 12, kEntryEntBits = 9;   // limits: 4096 items, 512 entities
-
-struct DRay {               // one per (sensor, ray): 4 words
-  int32_t sensor;
-  float angle;              // sensor-frame angle (row 0 of Lidar._angles)
-  int32_t out_off;          // float offset inside the lidar record
-  int32_t pad;
-};
 
 struct DSensor {            // 8 words
   int32_t entity;
@@ -87,16 +95,9 @@ struct DSensor {            // 8 words
   float max_range;
   int32_t n_targets;
   int32_t tg_begin;         // index into the target list
-  int32_t out_off;
-  int32_t tw_off;           // first word of this sensor's target survival mask inside the env's lmask area
+  int32_t out_off;          // first row inside the lidar buffer
+  int32_t tw_off;           // first lmask work row of this sensor
   int32_t n_tw;             // words of that mask = ceil(n_targets / 32)
-};
-
-struct DSWord {             // one per (sensor, 32-target word) of the LIDAR cull: 4 words
-  int32_t sensor;
-  int32_t tg_begin;         // index into targets[] / tcull2[] of bit 0
-  int32_t n;                // targets in this word (<= 32)
-  int32_t pad;
 };
 
 constexpr int kMaxAgents = 96;   // by-value kernel parameter tables
@@ -110,22 +111,22 @@ struct AgentIO {            // kernel parameter (by value)
 
 struct KParams {            // kernel parameter (by value)
   // sizes
-  int32_t E, n_dyn, J, P, n_items, S, A, n_rot, n_sensors, n_rays, pair_words;
-  int32_t dyn_stride, stat_stride, act_stride, lidar_stride;
-  int32_t G, TE;            // lanes per env, envs per CTA (threads per CTA = G * TE)
-  // per-env work area (4-byte words): [fin 3*n_dyn][rot 4*n_rot][res 4*n_items][frc 3*A][list n_items][lmask]
-  int32_t work_stride, off_fin, off_rot, off_res, off_frc, off_list, off_lmask, n_lmask_words;
+  int32_t E, n_dyn, J, P, n_items, S, A, n_trig, n_sensors, n_rays, pair_words, max_rays;
+  int32_t dyn_rows, stat_rows, act_rows, lidar_rows;
+  int32_t TE;               // envs (= threads) per CTA
+  // work rows: [fin 3*n_dyn][trig 4*n_trig][frc 3*A][lmask]
+  int32_t work_rows, row_fin, row_trig, row_frc, row_lmask, n_lmask_words;
   // device tables
   const DEnt* ents;
   const DItem* items;
   const DBroad* broad;      // [P]
   const int32_t* dyn_list;  // entity index of every dynamic entity, in entity order
-  const int32_t* rot_list;  // entity index per rot slot
-  const DRay* rays;
+  const int32_t* trig_list; // entity index per trig slot
+  const int32_t* agent_ents;// entity index per agent slot
+  const float* ray_angles;  // [n_rays] sensor-frame angles, sensors concatenated (row 0 of Lidar._angles)
   const DSensor* sensors;
   const int32_t* targets;
   const float* tcull2;      // [n targets] squared LIDAR cull distance per (sensor, target): (max_range + Rc) with margin
-  const DSWord* swords;     // [n_lmask_words]
   // world constants (core.py:1090-1143)
   float sub_dt, Kc, Kj, Kt, margin;
   float xs, ys;

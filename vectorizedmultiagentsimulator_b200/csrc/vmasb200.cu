@@ -1,5 +1,6 @@
 // vmasb200.cu - C ABI of libvmasb200.so (include/vmasb200.h): plan upload, launches, host-buffer entry point.
 // Compiled with -fmad=false: every reference torch op is one rounded fp32 instruction (see geom.cuh).
+#include <algorithm>
 #include <cstdio>
 #include <cstring>
 #include <new>
@@ -27,6 +28,8 @@ static size_t put(std::vector<char>& blob, const std::vector<T>& v) {
   return off;
 }
 
+static size_t bits_words(const KParams& kp) { return (size_t)kp.S * std::max(kp.pair_words, 1); }
+
 int upload_plan(vmasb200_plan* pl) {
   if (pl->uploaded) return VMASB200_OK;
   int ndev = 0;
@@ -35,9 +38,9 @@ int upload_plan(vmasb200_plan* pl) {
   VB_CUDA(cudaGetDevice(&pl->device));
   std::vector<char> blob;
   size_t o_ent = put(blob, pl->ents), o_item = put(blob, pl->items), o_broad = put(blob, pl->broad);
-  size_t o_tc = put(blob, pl->tcull2), o_sw = put(blob, pl->swords);
-  size_t o_dyn = put(blob, pl->dyn_list), o_rot = put(blob, pl->rot_list), o_ray = put(blob, pl->rays);
-  size_t o_sen = put(blob, pl->sensors), o_tg = put(blob, pl->targets);
+  size_t o_dyn = put(blob, pl->dyn_list), o_trig = put(blob, pl->trig_list), o_ag = put(blob, pl->agent_entities);
+  size_t o_ray = put(blob, pl->ray_angles), o_sen = put(blob, pl->sensors), o_tg = put(blob, pl->targets);
+  size_t o_tc = put(blob, pl->tcull2);
   VB_CUDA(cudaMalloc(&pl->d_blob, blob.size()));
   VB_CUDA(cudaMemcpy(pl->d_blob, blob.data(), blob.size(), cudaMemcpyHostToDevice));
   char* b = static_cast<char*>(pl->d_blob);
@@ -45,14 +48,15 @@ int upload_plan(vmasb200_plan* pl) {
   kp.ents = reinterpret_cast<const DEnt*>(b + o_ent);
   kp.items = reinterpret_cast<const DItem*>(b + o_item);
   kp.broad = reinterpret_cast<const DBroad*>(b + o_broad);
-  kp.tcull2 = reinterpret_cast<const float*>(b + o_tc);
-  kp.swords = reinterpret_cast<const DSWord*>(b + o_sw);
   kp.dyn_list = reinterpret_cast<const int32_t*>(b + o_dyn);
-  kp.rot_list = reinterpret_cast<const int32_t*>(b + o_rot);
-  kp.rays = reinterpret_cast<const DRay*>(b + o_ray);
+  kp.trig_list = reinterpret_cast<const int32_t*>(b + o_trig);
+  kp.agent_ents = reinterpret_cast<const int32_t*>(b + o_ag);
+  kp.ray_angles = reinterpret_cast<const float*>(b + o_ray);
   kp.sensors = reinterpret_cast<const DSensor*>(b + o_sen);
   kp.targets = reinterpret_cast<const int32_t*>(b + o_tg);
-  size_t nbits = (4 * (size_t)kp.S * std::max(kp.pair_words, 1) + 4) * sizeof(uint32_t);  // 4 bit arrays + counters
+  kp.tcull2 = reinterpret_cast<const float*>(b + o_tc);
+  // 4 bit arrays (flags, any_exact, any_spec, thin) + 4 counters
+  const size_t nbits = (4 * bits_words(kp) + 4) * sizeof(uint32_t);
   VB_CUDA(cudaMalloc(&pl->d_bits, nbits));
   VB_CUDA(cudaMemset(pl->d_bits, 0, nbits));
   pl->smem_bytes = smem_map(kp).total_bytes;
@@ -64,20 +68,25 @@ int upload_plan(vmasb200_plan* pl) {
 static int check_io(const vmasb200_plan* pl, const vmasb200_step_io* io) {
   const KParams& kp = pl->kp;
   if (!io || io->n_envs < 0) { set_error("step: bad io"); return VMASB200_ERR_INVALID; }
+  if (io->ld < io->n_envs || (io->ld & 3)) { set_error("step: ld must be >= n_envs and a multiple of 4"); return VMASB200_ERR_INVALID; }
   if (!io->dyn_in || !io->dyn_out) { set_error("step: dyn_in / dyn_out are required"); return VMASB200_ERR_INVALID; }
-  if (kp.stat_stride && !io->stat) { set_error("step: stat record missing"); return VMASB200_ERR_INVALID; }
-  if (kp.act_stride && !io->act_out) { set_error("step: act_out missing"); return VMASB200_ERR_INVALID; }
+  if (kp.stat_rows && !io->stat) { set_error("step: stat buffer missing"); return VMASB200_ERR_INVALID; }
+  if (kp.act_rows && !io->act_out) { set_error("step: act_out missing"); return VMASB200_ERR_INVALID; }
   if (kp.A && (!io->force_ptrs || !io->torque_ptrs || !io->force_strides || !io->torque_strides)) {
     set_error("step: force / torque pointer tables missing"); return VMASB200_ERR_INVALID;
   }
   auto mis = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) != 0; };
   if (mis(io->dyn_in) || mis(io->dyn_out) || mis(io->stat) || mis(io->act_out) || mis(io->lidar_out)) {
-    set_error("step: env records must be 16-byte aligned (TMA bulk copies)"); return VMASB200_ERR_INVALID;
+    set_error("step: SoA buffers must be 16-byte aligned (TMA bulk copies)"); return VMASB200_ERR_INVALID;
   }
   return VMASB200_OK;
 }
 
-static int launch_step(vmasb200_plan* pl, const vmasb200_step_io* io) {
+// Envs [env_begin, env_end) of one World.step on stream io->stream.  A step may be issued as several such launches
+// (on different streams); together they must cover total_ctas CTAs: the CTA that finishes last - of ALL launches -
+// verifies the speculation over the whole batch.  env_begin must be a multiple of the CTA tile.
+static int launch_step(vmasb200_plan* pl, const vmasb200_step_io* io, long long env_begin, long long env_end,
+                       unsigned total_ctas) {
   const KParams& kp = pl->kp;
   cudaStream_t st = static_cast<cudaStream_t>(io->stream);
   AgentIO aio;
@@ -87,22 +96,23 @@ static int launch_step(vmasb200_plan* pl, const vmasb200_step_io* io) {
     aio.fstride[a] = (int32_t)io->force_strides[a]; aio.tstride[a] = (int32_t)io->torque_strides[a];
   }
   const int nw = kp.S * kp.pair_words;
-  const size_t bw = (size_t)kp.S * std::max(kp.pair_words, 1);
+  const size_t bw = bits_words(kp);
   uint32_t* flags = pl->d_bits;
   StepArgs sa{};
   sa.dyn_in = io->dyn_in; sa.dyn_out = io->dyn_out; sa.stat = io->stat; sa.act_out = io->act_out;
-  sa.lidar_out = io->lidar_out; sa.n_envs = io->n_envs;
+  sa.lidar_out = io->lidar_out; sa.n_envs = io->n_envs; sa.ld = io->ld;
+  sa.env_begin = env_begin; sa.env_end = env_end; sa.total_ctas = (int)total_ctas;
   sa.flags_out = flags; sa.any_exact = flags + bw; sa.any_spec = flags + 2 * bw; sa.thin = flags + 3 * bw;
   sa.counters = reinterpret_cast<int*>(flags + 4 * bw);
-  const unsigned grid = (unsigned)((io->n_envs + kp.TE - 1) / kp.TE);
-  const unsigned block = (unsigned)(kp.TE * kp.G);
+  const unsigned grid = (unsigned)((env_end - env_begin + kp.TE - 1) / kp.TE);
+  const unsigned block = (unsigned)kp.TE;
   if (io->exact) {
     // exact path: the batch-wide World.collides verdicts are reduced before every substep (core.py:2796-2800)
     if (nw) VB_CUDA(cudaMemsetAsync(flags, 0, nw * sizeof(uint32_t), st));
     for (int s = 0; s < kp.S; ++s) {
       if (kp.P) {
         unsigned fg = (unsigned)((io->n_envs + 255) / 256);
-        flags_kernel<<<fg, 256, 0, st>>>(kp, sa.dyn_in, sa.stat, io->n_envs, s, flags);
+        flags_kernel<<<fg, 256, 0, st>>>(kp, sa.dyn_in, sa.stat, io->n_envs, io->ld, s, flags);
       }
       sa.s_begin = s; sa.s_end = s + 1; sa.flags_in = flags;
       sa.do_lidar = (s == kp.S - 1);
@@ -115,7 +125,7 @@ static int launch_step(vmasb200_plan* pl, const vmasb200_step_io* io) {
       cudaFree(pl->d_ulist); cudaFree(pl->d_ubuf);
       pl->d_ulist = nullptr; pl->d_ubuf = nullptr; pl->u_cap = 0;
       VB_CUDA(cudaMalloc(&pl->d_ulist, (size_t)io->n_envs * sizeof(int)));
-      VB_CUDA(cudaMalloc(&pl->d_ubuf, (size_t)io->n_envs * kp.dyn_stride * sizeof(float)));
+      VB_CUDA(cudaMalloc(&pl->d_ubuf, (size_t)io->n_envs * std::max(kp.dyn_rows, 1) * sizeof(float)));
       pl->u_cap = io->n_envs;
     }
     sa.u_list = pl->d_ulist; sa.u_buf = pl->d_ubuf;
@@ -152,6 +162,7 @@ int vmasb200_plan_destroy(vmasb200_plan* pl) {
   if (pl->uploaded) {
     cudaFree(pl->d_blob); cudaFree(pl->d_bits); cudaFree(pl->d_ulist); cudaFree(pl->d_ubuf);
     cudaFree(pl->d_dyn); cudaFree(pl->d_stat); cudaFree(pl->d_force); cudaFree(pl->d_torque); cudaFree(pl->d_act); cudaFree(pl->d_lidar);
+    for (cudaStream_t s : pl->streams) if (s) cudaStreamDestroy(s);
   }
   delete pl;
   return VMASB200_OK;
@@ -196,68 +207,104 @@ int vmasb200_step(vmasb200_plan* pl, const vmasb200_step_io* io) {
   if (rc) return rc;
   if ((rc = upload_plan(pl))) return rc;
   if (io->n_envs == 0 || pl->kp.n_dyn == 0) return VMASB200_OK;
-  return launch_step(pl, io);
+  const unsigned ctas = (unsigned)((io->n_envs + pl->kp.TE - 1) / pl->kp.TE);
+  return launch_step(pl, io, 0, io->n_envs, ctas);
 }
 
-static int grow_host_staging(vmasb200_plan* pl, int64_t n) {
-  if (n <= pl->host_cap) return VMASB200_OK;
+static int grow_host_staging(vmasb200_plan* pl, int64_t ld) {
+  if (ld <= pl->host_cap) return VMASB200_OK;
   const KParams& kp = pl->kp;
   cudaFree(pl->d_dyn); cudaFree(pl->d_stat); cudaFree(pl->d_force); cudaFree(pl->d_torque); cudaFree(pl->d_act); cudaFree(pl->d_lidar);
   pl->d_dyn = pl->d_stat = pl->d_force = pl->d_torque = pl->d_act = pl->d_lidar = nullptr;
   pl->host_cap = 0;
-  auto bytes = [&](int stride) { return std::max<size_t>((size_t)n * stride * sizeof(float), 16); };
-  VB_CUDA(cudaMalloc(&pl->d_dyn, bytes(kp.dyn_stride)));
-  VB_CUDA(cudaMalloc(&pl->d_stat, bytes(kp.stat_stride)));
+  auto bytes = [&](int rows) { return std::max<size_t>((size_t)ld * rows * sizeof(float), 16); };
+  VB_CUDA(cudaMalloc(&pl->d_dyn, bytes(kp.dyn_rows)));
+  VB_CUDA(cudaMalloc(&pl->d_stat, bytes(kp.stat_rows)));
   VB_CUDA(cudaMalloc(&pl->d_force, bytes(2 * kp.A)));
   VB_CUDA(cudaMalloc(&pl->d_torque, bytes(kp.A)));
-  VB_CUDA(cudaMalloc(&pl->d_act, bytes(kp.act_stride)));
-  VB_CUDA(cudaMalloc(&pl->d_lidar, bytes(kp.lidar_stride)));
-  pl->host_cap = n;
+  VB_CUDA(cudaMalloc(&pl->d_act, bytes(kp.act_rows)));
+  VB_CUDA(cudaMalloc(&pl->d_lidar, bytes(kp.lidar_rows)));
+  pl->host_cap = ld;
   return VMASB200_OK;
 }
 
 int vmasb200_step_host(vmasb200_plan* pl, const float* h_dyn_in, const float* h_stat, const float* h_force,
                        const float* h_torque, float* h_dyn_out, float* h_act_out, float* h_lidar_out,
-                       uint32_t* h_pair_active, int64_t n, int32_t exact) {
-  if (!pl || !h_dyn_in || n < 0) { set_error("step_host: bad argument"); return VMASB200_ERR_INVALID; }
+                       uint32_t* h_pair_active, int64_t n, int64_t ld, int32_t exact) {
+  if (!pl || !h_dyn_in || n < 0 || ld < n || (ld & 3)) { set_error("step_host: bad argument (ld >= n_envs, ld % 4 == 0)"); return VMASB200_ERR_INVALID; }
   int rc = upload_plan(pl);
   if (rc) return rc;
   const KParams& kp = pl->kp;
-  if (kp.stat_stride && !h_stat) { set_error("step_host: stat record missing"); return VMASB200_ERR_INVALID; }
+  if (kp.stat_rows && !h_stat) { set_error("step_host: stat buffer missing"); return VMASB200_ERR_INVALID; }
   if (n == 0) return VMASB200_OK;
-  if ((rc = grow_host_staging(pl, n))) return rc;
-  cudaStream_t st = nullptr;
-  VB_CUDA(cudaMemcpyAsync(pl->d_dyn, h_dyn_in, (size_t)n * kp.dyn_stride * 4, cudaMemcpyHostToDevice, st));
-  if (kp.stat_stride) VB_CUDA(cudaMemcpyAsync(pl->d_stat, h_stat, (size_t)n * kp.stat_stride * 4, cudaMemcpyHostToDevice, st));
-  if (kp.A && h_force) VB_CUDA(cudaMemcpyAsync(pl->d_force, h_force, (size_t)n * kp.A * 8, cudaMemcpyHostToDevice, st));
-  if (kp.A && h_torque) VB_CUDA(cudaMemcpyAsync(pl->d_torque, h_torque, (size_t)n * kp.A * 4, cudaMemcpyHostToDevice, st));
+  if ((rc = grow_host_staging(pl, ld))) return rc;
+  for (cudaStream_t& s : pl->streams)
+    if (!s) VB_CUDA(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
+  const int64_t dld = pl->host_cap;  // row stride of the device staging (>= ld)
+
+  // chunks of envs, one stream each: H2D(k+1) overlaps kernel(k) overlaps D2H(k-1).  Boundaries are multiples of
+  // 256 envs (every CTA tile size divides 256); the exact path needs batch-wide flags between substeps: one chunk.
+  int64_t nchunk = exact ? 1 : std::min<int64_t>(kHostStreams, (n + 8191) / 8192);
+  int64_t csize = ((n + nchunk - 1) / nchunk + 255) & ~int64_t(255);
+  nchunk = (n + csize - 1) / csize;
+  const unsigned total_ctas = (unsigned)((n + kp.TE - 1) / kp.TE);
+
   const float* fptr[kMaxAgents]; const float* tptr[kMaxAgents];
   int64_t fstr[kMaxAgents], tstr[kMaxAgents];
   for (int a = 0; a < kp.A; ++a) {  // h_force [n][A][2], h_torque [n][A]
     fptr[a] = h_force ? pl->d_force + 2 * a : nullptr; fstr[a] = 2 * kp.A;
     tptr[a] = h_torque ? pl->d_torque + a : nullptr; tstr[a] = kp.A;
   }
-  vmasb200_step_io io{};
-  io.dyn_in = pl->d_dyn; io.dyn_out = pl->d_dyn; io.stat = pl->d_stat;
-  io.force_ptrs = fptr; io.force_strides = fstr; io.torque_ptrs = tptr; io.torque_strides = tstr;
-  io.act_out = kp.act_stride ? pl->d_act : nullptr;
-  io.lidar_out = (kp.lidar_stride && h_lidar_out) ? pl->d_lidar : nullptr;
-  io.pair_active_out = nullptr; io.n_envs = n; io.exact = exact; io.stream = st;
-  if (kp.n_dyn && (rc = launch_step(pl, &io))) return rc;
-  if (h_dyn_out) VB_CUDA(cudaMemcpyAsync(h_dyn_out, pl->d_dyn, (size_t)n * kp.dyn_stride * 4, cudaMemcpyDeviceToHost, st));
-  if (h_act_out && kp.act_stride) VB_CUDA(cudaMemcpyAsync(h_act_out, pl->d_act, (size_t)n * kp.act_stride * 4, cudaMemcpyDeviceToHost, st));
-  if (h_lidar_out && kp.lidar_stride) VB_CUDA(cudaMemcpyAsync(h_lidar_out, pl->d_lidar, (size_t)n * kp.lidar_stride * 4, cudaMemcpyDeviceToHost, st));
-  if (h_pair_active && kp.S * kp.pair_words) {
-    VB_CUDA(cudaMemcpyAsync(h_pair_active, pl->d_bits, (size_t)kp.S * kp.pair_words * 4, cudaMemcpyDeviceToHost, st));
+  const bool want_lidar = kp.lidar_rows && h_lidar_out;
+  auto rows2d = [&](void* dst, size_t dpitch, const void* src, size_t spitch, int64_t c0, int64_t ncol, int rows,
+                    cudaMemcpyKind kind, cudaStream_t st) {
+    return cudaMemcpy2DAsync(static_cast<char*>(dst) + c0 * 4, dpitch * 4, static_cast<const char*>(src) + c0 * 4,
+                             spitch * 4, (size_t)ncol * 4, (size_t)rows, kind, st);
+  };
+  auto d2h = [&](int64_t c0, int64_t ncol, cudaStream_t st) -> int {
+    if (h_dyn_out && kp.dyn_rows) VB_CUDA(rows2d(h_dyn_out, ld, pl->d_dyn, dld, c0, ncol, kp.dyn_rows, cudaMemcpyDeviceToHost, st));
+    if (h_act_out && kp.act_rows) VB_CUDA(rows2d(h_act_out, ld, pl->d_act, dld, c0, ncol, kp.act_rows, cudaMemcpyDeviceToHost, st));
+    if (want_lidar) VB_CUDA(rows2d(h_lidar_out, ld, pl->d_lidar, dld, c0, ncol, kp.lidar_rows, cudaMemcpyDeviceToHost, st));
+    return VMASB200_OK;
+  };
+  int repairs_before = 0;
+  const int* d_repairs = reinterpret_cast<const int*>(pl->d_bits + 4 * bits_words(kp)) + 2;
+  if (nchunk > 1) VB_CUDA(cudaMemcpy(&repairs_before, d_repairs, sizeof(int), cudaMemcpyDeviceToHost));
+  for (int64_t k = 0; k < nchunk; ++k) {
+    cudaStream_t st = pl->streams[k % kHostStreams];
+    const int64_t c0 = k * csize, c1 = std::min(n, c0 + csize), ncol = c1 - c0;
+    if (kp.dyn_rows) VB_CUDA(rows2d(pl->d_dyn, dld, h_dyn_in, ld, c0, ncol, kp.dyn_rows, cudaMemcpyHostToDevice, st));
+    if (kp.stat_rows) VB_CUDA(rows2d(pl->d_stat, dld, h_stat, ld, c0, ncol, kp.stat_rows, cudaMemcpyHostToDevice, st));
+    if (kp.A && h_force) VB_CUDA(cudaMemcpyAsync(pl->d_force + c0 * 2 * kp.A, h_force + c0 * 2 * kp.A, (size_t)ncol * kp.A * 8, cudaMemcpyHostToDevice, st));
+    if (kp.A && h_torque) VB_CUDA(cudaMemcpyAsync(pl->d_torque + c0 * kp.A, h_torque + c0 * kp.A, (size_t)ncol * kp.A * 4, cudaMemcpyHostToDevice, st));
+    vmasb200_step_io io{};
+    io.dyn_in = pl->d_dyn; io.dyn_out = pl->d_dyn; io.stat = pl->d_stat;
+    io.force_ptrs = fptr; io.force_strides = fstr; io.torque_ptrs = tptr; io.torque_strides = tstr;
+    io.act_out = kp.act_rows ? pl->d_act : nullptr;
+    io.lidar_out = want_lidar ? pl->d_lidar : nullptr;
+    io.pair_active_out = nullptr; io.n_envs = n; io.ld = dld; io.exact = exact; io.stream = st;
+    if (kp.n_dyn && (rc = launch_step(pl, &io, c0, c1, total_ctas))) return rc;
+    if ((rc = d2h(c0, ncol, st))) return rc;
   }
-  VB_CUDA(cudaStreamSynchronize(st));
+  for (int64_t k = 0; k < std::min<int64_t>(nchunk, kHostStreams); ++k) VB_CUDA(cudaStreamSynchronize(pl->streams[k]));
+  if (nchunk > 1) {
+    // a repair by the step's last CTA may have rewritten envs of a chunk whose results were already copied out
+    int repairs_after = 0;
+    VB_CUDA(cudaMemcpy(&repairs_after, d_repairs, sizeof(int), cudaMemcpyDeviceToHost));
+    if (repairs_after != repairs_before) {
+      if ((rc = d2h(0, n, pl->streams[0]))) return rc;
+      VB_CUDA(cudaStreamSynchronize(pl->streams[0]));
+    }
+  }
+  if (h_pair_active && kp.S * kp.pair_words)
+    VB_CUDA(cudaMemcpy(h_pair_active, pl->d_bits, (size_t)kp.S * kp.pair_words * 4, cudaMemcpyDeviceToHost));
   return VMASB200_OK;
 }
 
-int vmasb200_cast_rays(vmasb200_plan* pl, const float* dyn, const float* stat, int32_t entity, const float* angles,
-                       int64_t angles_stride, int32_t n_rays, float max_range, const int32_t* targets,
-                       int32_t n_targets, float* out, int64_t n, void* stream) {
-  if (!pl || !dyn || !angles || !out || n < 0 || n_rays < 0 || n_targets < 0 || (n_targets && !targets)) {
+int vmasb200_cast_rays(vmasb200_plan* pl, const float* dyn, const float* stat, int64_t ld, int32_t entity,
+                       const float* angles, int64_t angles_stride, int32_t n_rays, float max_range,
+                       const int32_t* targets, int32_t n_targets, float* out, int64_t n, void* stream) {
+  if (!pl || !dyn || !angles || !out || n < 0 || ld < n || n_rays < 0 || n_targets < 0 || (n_targets && !targets)) {
     set_error("cast_rays: bad argument"); return VMASB200_ERR_INVALID;
   }
   int rc = upload_plan(pl);
@@ -265,11 +312,11 @@ int vmasb200_cast_rays(vmasb200_plan* pl, const float* dyn, const float* stat, i
   const KParams& kp = pl->kp;
   if (entity < 0 || entity >= kp.E) { set_error("cast_rays: entity out of range"); return VMASB200_ERR_INVALID; }
   auto has_rec = [&](int e) { return pl->ents[e].dyn_off >= 0 || pl->ents[e].stat_off >= 0; };
-  if (!has_rec(entity)) { set_error("cast_rays: the casting entity has no record in this plan"); return VMASB200_ERR_INVALID; }
+  if (!has_rec(entity)) { set_error("cast_rays: the casting entity has no rows in this plan"); return VMASB200_ERR_INVALID; }
   if (n_targets > 64) { set_error("cast_rays: more than 64 targets"); return VMASB200_ERR_UNSUPPORTED; }
   for (int t = 0; t < n_targets; ++t)
     if (targets[t] < 0 || targets[t] >= kp.E || !has_rec(targets[t])) {
-      set_error("cast_rays: a target has no record in this plan"); return VMASB200_ERR_INVALID;
+      set_error("cast_rays: a target has no rows in this plan"); return VMASB200_ERR_INVALID;
     }
   if (n == 0 || n_rays == 0) return VMASB200_OK;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
@@ -277,8 +324,8 @@ int vmasb200_cast_rays(vmasb200_plan* pl, const float* dyn, const float* stat, i
   rt.n = n_targets;
   for (int t = 0; t < n_targets; ++t) rt.e[t] = targets[t];
   const long long total = (long long)n * n_rays;
-  cast_rays_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(kp, dyn, stat ? stat : dyn, entity, angles, angles_stride,
-                                                                   n_rays, max_range, rt, out, n);
+  cast_rays_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(kp, dyn, stat ? stat : dyn, ld, entity, angles,
+                                                                   angles_stride, n_rays, max_range, rt, out, n);
   VB_CUDA(cudaGetLastError());
   return VMASB200_OK;
 }
@@ -290,8 +337,7 @@ int vmasb200_sync_check(vmasb200_plan* pl, void* stream, int64_t* n_fixups) {
     *n_fixups = 0;
     if (pl && pl->uploaded) {
       int c = 0;
-      const size_t bw = (size_t)pl->kp.S * std::max(pl->kp.pair_words, 1);
-      VB_CUDA(cudaMemcpy(&c, reinterpret_cast<int*>(pl->d_bits + 4 * bw) + 2, sizeof(int), cudaMemcpyDeviceToHost));
+      VB_CUDA(cudaMemcpy(&c, reinterpret_cast<int*>(pl->d_bits + 4 * bits_words(pl->kp)) + 2, sizeof(int), cudaMemcpyDeviceToHost));
       *n_fixups = c;
     }
   }

@@ -62,30 +62,47 @@ class StepPlan:
         except Exception:
             pass
 
-    # ------------------------------------------------------------------ record packing (numpy; tests / bench / host API)
+    # ------------------------------------------------------------------ SoA packing (numpy; tests / bench / host API)
+    @staticmethod
+    def ld_for(n: int) -> int:
+        """Row stride of the SoA buffers for n environments: a multiple of 4 floats (16-byte rows for TMA)."""
+        return max(4, (n + 3) & ~3)
+
     def pack(self, state: np.ndarray, jrot: Optional[np.ndarray] = None):
-        """fixture layout state[E,N,6] (+ jrot[J,N]) -> env records dyn[N,dyn_stride], stat[N,stat_stride]."""
+        """fixture layout state[E,N,6] (+ jrot[J,N]) -> SoA buffers dyn[dyn_rows, ld], stat[stat_rows, ld]."""
         n = state.shape[1]
-        dyn = np.zeros((n, self.dyn_stride), np.float32)
-        stat = np.zeros((n, self.stat_stride), np.float32)
+        ld = self.ld_for(n)
+        dyn = np.zeros((self.dyn_rows, ld), np.float32)
+        stat = np.zeros((self.stat_rows, ld), np.float32)
         for e in range(self.E):
             if self.dyn_slot[e] >= 0:
-                dyn[:, self.dyn_slot[e]: self.dyn_slot[e] + 6] = state[e]
+                dyn[self.dyn_slot[e]: self.dyn_slot[e] + 6, :n] = state[e].T
             elif self.stat_slot[e] >= 0:
                 o = self.stat_slot[e]
-                stat[:, o: o + 2] = state[e][:, 0:2]
-                stat[:, o + 2] = state[e][:, 4]
+                stat[o: o + 2, :n] = state[e][:, 0:2].T
+                stat[o + 2, :n] = state[e][:, 4]
         for j, o in enumerate(self.joint_slot):
             if o >= 0 and jrot is not None and jrot.size:
-                stat[:, o] = jrot[j]
+                stat[o, :n] = jrot[j]
         return dyn, stat
 
     def unpack(self, dyn: np.ndarray, state: np.ndarray) -> np.ndarray:
-        """Writes the dyn records back into a fixture-layout state (static entities untouched)."""
+        """Writes the dyn rows back into a fixture-layout state (static entities untouched)."""
+        n = state.shape[1]
         for e in range(self.E):
             if self.dyn_slot[e] >= 0:
-                state[e] = dyn[:, self.dyn_slot[e]: self.dyn_slot[e] + 6]
+                state[e] = dyn[self.dyn_slot[e]: self.dyn_slot[e] + 6, :n].T
         return state
+
+    def lidar_of(self, lid: np.ndarray, k: int, n: int) -> np.ndarray:
+        """[n, n_rays] measurement of sensor k out of the lidar SoA buffer."""
+        o, r = self.lidar_slot[k], len(self.desc.lidars[k].angles)
+        return lid[o: o + r, :n].T
+
+    def act_of(self, act: np.ndarray, e: int, n: int):
+        """clamped (force [n,2], torque [n]) of entity e out of the actout SoA buffer."""
+        o = self.act_slot[e]
+        return act[o: o + 2, :n].T, act[o + 2, :n]
 
     def masks_matrix(self, words: np.ndarray) -> np.ndarray:
         """pair_active words [S, pair_words] -> bool [S, E, E] (a<b), the shape the golden fixtures store."""
@@ -99,25 +116,30 @@ class StepPlan:
         return m
 
     # ------------------------------------------------------------------ compute: host buffers (H2D + kernel + D2H inside)
-    def step_host(self, dyn, stat, force=None, torque=None, exact=False, want_lidar=True, want_masks=True):
-        """dyn [N,dyn_stride], stat [N,stat_stride], force [N,A,2], torque [N,A] numpy fp32.
-        Returns (dyn_out, act_out, lidar_out, pair_active_words)."""
-        n = dyn.shape[0]
-        assert dyn.dtype == np.float32 and dyn.flags.c_contiguous and dyn.shape == (n, self.dyn_stride)
-        for a, shp in ((stat, (n, self.stat_stride)), (force, (n, self.A, 2)), (torque, (n, self.A))):
+    def step_host(self, dyn, stat, force=None, torque=None, exact=False, want_lidar=True, want_masks=True, out=None):
+        """dyn [dyn_rows, ld], stat [stat_rows, ld], force [N,A,2], torque [N,A] numpy fp32 (N = force/torque rows, else
+        ld).  out = optional (dyn_out, act, lidar) buffers to fill (e.g. pinned).  Returns (dyn_out, act_out, lidar_out,
+        pair_active_words)."""
+        ld = dyn.shape[1]
+        n = force.shape[0] if force is not None else (torque.shape[0] if torque is not None else ld)
+        assert dyn.dtype == np.float32 and dyn.flags.c_contiguous and dyn.shape == (self.dyn_rows, ld)
+        for a, shp in ((stat, (self.stat_rows, ld)), (force, (n, self.A, 2)), (torque, (n, self.A))):
             assert a is None or (a.dtype == np.float32 and a.flags.c_contiguous and a.shape == shp), shp
-        dyn_out = np.empty_like(dyn)
-        act = np.zeros((n, self.act_stride), np.float32) if self.act_stride else None
-        lid = np.zeros((n, self.lidar_stride), np.float32) if (self.lidar_stride and want_lidar) else None
+        if out is not None:
+            dyn_out, act, lid = out
+        else:
+            dyn_out = np.zeros_like(dyn)
+            act = np.zeros((self.act_rows, ld), np.float32) if self.act_rows else None
+            lid = np.zeros((self.lidar_rows, ld), np.float32) if (self.lidar_rows and want_lidar) else None
         pa = np.zeros((self.S, self.pair_words), np.uint32) if (self.pair_words and want_masks) else None
-        rc = _lib.lib().vmasb200_step_host(self._h, _ptr(dyn), _ptr(stat), _ptr(force), _ptr(torque), _ptr(dyn_out),
-                                           _ptr(act), _ptr(lid), _ptr(pa), n, int(exact))
+        rc = _lib.lib().vmasb200_step_host(self._h, _ptr(dyn), _ptr(stat) if self.stat_rows else None, _ptr(force),
+                                           _ptr(torque), _ptr(dyn_out), _ptr(act), _ptr(lid), _ptr(pa), n, ld, int(exact))
         _lib.check(rc, "vmasb200_step_host")
         return dyn_out, act, lid, pa
 
     # ------------------------------------------------------------------ compute: device buffers (asynchronous)
     def make_io(self, dyn_in, dyn_out, stat, forces: List, torques: List, act_out, lidar_out, pair_active_out,
-                n_envs: int, exact: bool, stream: int):
+                n_envs: int, ld: int, exact: bool, stream: int):
         """Builds a reusable vmasb200_step_io; forces/torques are per-agent CUDA tensors ([N,2] / [N,1]) or None."""
         io = CStepIO()
         fp = (C.c_void_p * max(self.A, 1))()
@@ -134,17 +156,17 @@ class StepPlan:
         io.force_ptrs, io.force_strides = C.cast(fp, C.POINTER(C.c_void_p)), C.cast(fs, C.POINTER(C.c_int64))
         io.torque_ptrs, io.torque_strides = C.cast(tp, C.POINTER(C.c_void_p)), C.cast(ts, C.POINTER(C.c_int64))
         io.act_out, io.lidar_out, io.pair_active_out = _ptr(act_out), _ptr(lidar_out), _ptr(pair_active_out)
-        io.n_envs, io.exact, io.stream = n_envs, int(exact), stream
+        io.n_envs, io.ld, io.exact, io.stream = n_envs, ld, int(exact), stream
         io._keep = (fp, tp, fs, ts, dyn_in, dyn_out, stat, forces, torques, act_out, lidar_out, pair_active_out)
         return io
 
     def step_io(self, io):
         _lib.check(_lib.lib().vmasb200_step(self._h, C.byref(io)), "vmasb200_step")
 
-    def cast_rays(self, dyn, stat, entity: int, angles, max_range: float, targets, out, stream: int):
+    def cast_rays(self, dyn, stat, ld: int, entity: int, angles, max_range: float, targets, out, stream: int):
         n, r = angles.shape
         tg = np.ascontiguousarray(targets, np.int32)
-        rc = _lib.lib().vmasb200_cast_rays(self._h, _ptr(dyn), _ptr(stat), entity, _ptr(angles), angles.stride(0), r,
+        rc = _lib.lib().vmasb200_cast_rays(self._h, _ptr(dyn), _ptr(stat), ld, entity, _ptr(angles), angles.stride(0), r,
                                            float(max_range), tg.ctypes.data_as(C.POINTER(C.c_int32)), len(tg),
                                            _ptr(out), n, stream)
         _lib.check(rc, "vmasb200_cast_rays")

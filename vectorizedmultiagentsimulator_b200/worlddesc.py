@@ -41,7 +41,7 @@ E_MAX_T = 1 << 12
 E_T_RANGE = 1 << 13
 E_COLLIDE = 1 << 14
 
-ABI_VERSION = 1
+ABI_VERSION = 2
 
 
 class UnsupportedWorld(RuntimeError):
@@ -120,7 +120,7 @@ class CWorldDesc(C.Structure):
         ("torque_constraint_force", C.c_float),
         ("contact_margin", C.c_float),
         ("gravity", C.c_float * 2),
-        ("lanes_per_env", C.c_int32),
+        ("envs_per_cta", C.c_int32),
     ]
 
 
@@ -130,13 +130,13 @@ class CPair(C.Structure):
 
 class CLayout(C.Structure):
     _fields_ = [
-        ("dyn_stride", C.c_int32),
-        ("stat_stride", C.c_int32),
-        ("act_stride", C.c_int32),
-        ("lidar_stride", C.c_int32),
+        ("dyn_rows", C.c_int32),
+        ("stat_rows", C.c_int32),
+        ("act_rows", C.c_int32),
+        ("lidar_rows", C.c_int32),
         ("n_pairs", C.c_int32),
         ("pair_words", C.c_int32),
-        ("lanes_per_env", C.c_int32),
+        ("envs_per_cta", C.c_int32),
         ("n_dyn", C.c_int32),
         ("n_stat", C.c_int32),
         ("n_agents", C.c_int32),
@@ -158,6 +158,7 @@ class CStepIO(C.Structure):
         ("lidar_out", C.c_void_p),
         ("pair_active_out", C.c_void_p),
         ("n_envs", C.c_int64),
+        ("ld", C.c_int64),
         ("exact", C.c_int32),
         ("stream", C.c_void_p),
     ]
@@ -242,7 +243,7 @@ class WorldDesc:
     torque_constraint_force: float
     contact_margin: float
     gravity: List[float]
-    lanes_per_env: int = 0
+    envs_per_cta: int = 0
 
     # ------------------------------------------------------------------ (de)serialisation
     def to_json(self) -> str:
@@ -251,6 +252,7 @@ class WorldDesc:
     @staticmethod
     def from_json(s: str) -> "WorldDesc":
         d = json.loads(s)
+        d.pop("lanes_per_env", None)  # fixtures written for ABI 1
         d["entities"] = [EntityDesc(**e) for e in d["entities"]]
         d["joints"] = [JointDesc(**j) for j in d["joints"]]
         d["lidars"] = [LidarDesc(**l) for l in d["lidars"]]
@@ -312,7 +314,7 @@ class WorldDesc:
         d.collision_force, d.joint_force = self.collision_force, self.joint_force
         d.torque_constraint_force, d.contact_margin = self.torque_constraint_force, self.contact_margin
         d.gravity[0], d.gravity[1] = self.gravity
-        d.lanes_per_env = self.lanes_per_env
+        d.envs_per_cta = self.envs_per_cta
         return d, keep
 
     # ------------------------------------------------------------------ extraction from a live reference World
