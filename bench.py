@@ -237,7 +237,7 @@ def run_b200(args, rank, local_rank, world):
     barrier()
     ms = e0.elapsed_time(e1)
     clocks = sampler.stop()
-    plan.sync_check(stream)
+    repairs = plan.sync_check(stream)
     if world > 1:
         t = torch.tensor([ms], device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -269,7 +269,7 @@ def run_b200(args, rank, local_rank, world):
             "config": {"workload": f"{args.scenario} num_envs={n} per GPU, substeps={plan.S}, {len(wl.desc.lidars)} lidars",
                        "l2": f"{R} env batches visited round-robin, working set {R * per_batch / 2**20:.0f} MiB > L2 126 MiB",
                        "envs_per_cta": plan.envs_per_cta, "layout": "SoA rows [field][env], one thread per env",
-                       "exact": int(args.exact),
+                       "exact": int(args.exact), "speculation_repairs": repairs,
                        "l2_resident_ms_per_step": ms_hot / K},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": None, "peak_source": peak_src, "alg_bytes_per_env": plan.alg_bytes_per_env,

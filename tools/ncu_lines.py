@@ -22,8 +22,8 @@ def line_table(so, kernel):
     for f in os.listdir(tmp):
         if not f.endswith(".cubin"):
             continue
-        out = subprocess.run(["nvdisasm", "-g", "-c", os.path.join(tmp, f)], capture_output=True, text=True).stdout
-        sect, cur, base = None, None, 0
+        out = subprocess.run(["nvdisasm", "-gi", "-c", os.path.join(tmp, f)], capture_output=True, text=True).stdout
+        sect, cur, chain, fresh = None, None, [], True
         for ln in out.splitlines():
             m = re.match(r"\s*\.section\s+\.text\.(\S+?),", ln)
             if m:
@@ -31,13 +31,16 @@ def line_table(so, kernel):
                 continue
             if sect is None or kernel not in sect:
                 continue
-            m = re.match(r'\s*//## File "(.*)", line (\d+)', ln)
+            m = re.match(r'\s*//## File "(.*?)", line (\d+)', ln)
             if m:
-                cur = (os.path.basename(m.group(1)), int(m.group(2)))
+                if fresh:
+                    chain, fresh = [], False
+                chain.append((os.path.basename(m.group(1)), int(m.group(2))))  # innermost first, outermost last
                 continue
             m = re.match(r"\s*/\*([0-9a-f]{4,})\*/\s+(.*?);", ln)
             if m:
-                table[(sect, int(m.group(1), 16))] = (cur, m.group(2).strip())
+                fresh = True
+                table[(sect, int(m.group(1), 16))] = (tuple(chain), m.group(2).strip())
     return table
 
 
@@ -56,6 +59,7 @@ def main():
     # the report lists the entry function first, then its non-inlined callees; offsets restart per function
     by_line = collections.defaultdict(lambda: [0, 0, 0])
     by_op = collections.defaultdict(lambda: [0, 0])
+    by_frame = {l: collections.defaultdict(lambda: [0, 0, 0]) for l in (1, 2, 3)}
     total = [0, 0, 0]
     base, prev, si = None, None, 0
     entry = [s for s in sects if "step_kernel" in s or kernel in s]
@@ -77,14 +81,22 @@ def main():
                 break
         smp, ins, tins = int(r[ci["# Samples"]] or 0), int(r[ci["Instructions Executed"]] or 0), int(r[ci["Thread Instructions Executed"]] or 0)
         total[0] += smp; total[1] += ins; total[2] += tins
-        loc = key[0] if key and key[0] else ("?", 0)
+        chain = key[0] if key and key[0] else (("?", 0),)
+        loc = chain[0]
         by_line[loc][0] += smp; by_line[loc][1] += ins; by_line[loc][2] += tins
+        for lvl in (1, 2, 3):  # frames counted from the kernel body inwards
+            fr = chain[-lvl] if len(chain) >= lvl else chain[0]
+            by_frame[lvl][fr][0] += smp; by_frame[lvl][fr][1] += ins; by_frame[lvl][fr][2] += tins
         op = r[ci["Source"]].strip().split()[0].split(".")[0]
         by_op[op][0] += smp; by_op[op][1] += ins
     print(f"total: samples {total[0]}  warp-inst {total[1]}  thread-inst {total[2]}")
     print("--- top source lines by warp instructions executed")
     for loc, v in sorted(by_line.items(), key=lambda kv: -kv[1][1])[:45]:
         print(f"{loc[0]}:{loc[1]:<5d} inst {v[1]:>10d} ({100*v[1]/max(total[1],1):5.1f}%)  samples {v[0]:>7d} ({100*v[0]/max(total[0],1):5.1f}%)  thr/inst {v[2]/max(v[1],1):5.1f}")
+    for lvl, name in ((1, "kernel body line"), (2, "first inlined frame"), (3, "second inlined frame")):
+        print(f"--- by {name} (inclusive of everything inlined below it)")
+        for loc, v in sorted(by_frame[lvl].items(), key=lambda kv: -kv[1][1])[:22]:
+            print(f"{loc[0]}:{loc[1]:<5d} inst {v[1]:>10d} ({100*v[1]/max(total[1],1):5.1f}%)  samples {v[0]:>7d} ({100*v[0]/max(total[0],1):5.1f}%)  thr/inst {v[2]/max(v[1],1):5.1f}")
     print("--- top source lines by stall samples")
     for loc, v in sorted(by_line.items(), key=lambda kv: -kv[1][0])[:25]:
         print(f"{loc[0]}:{loc[1]:<5d} samples {v[0]:>7d} ({100*v[0]/max(total[0],1):5.1f}%)  inst {v[1]:>10d}")

@@ -38,16 +38,20 @@ struct StepArgs {
 
 // dynamic shared memory carve-up (4-byte words); every row starts 16B aligned because TE % 4 == 0
 struct SmemMap {
-  int bar, env, work, lid, queue, flags, total_bytes;
+  int bar, env, work, lid, queue, rayq, wtask, wres, flags, total_bytes;
 };
+constexpr int kWarpTasks = 32;  // narrow-phase tasks a warp redistributes per round
 __host__ __device__ inline SmemMap smem_map(const KParams& kp) {
   SmemMap m;
   int o = 0;
-  m.bar = o; o += 4;  // 16 bytes: mbarrier (8) + LIDAR queue counter (4)
+  m.bar = o; o += 4;  // 16 bytes: mbarrier (8) + the two LIDAR queue counters (4 + 4)
   m.env = o; o += kp.TE * (kp.dyn_rows + kp.stat_rows);
   m.work = o; o += kp.TE * kp.work_rows;
   m.lid = o; o += kp.TE * kp.lidar_rows;
+  m.wres = o; o += (kp.TE / 32) * kWarpTasks * 4;   // float4 per task (16B aligned: everything above is a multiple of 4)
+  m.wtask = o; o += (kp.TE / 32) * kWarpTasks;
   m.queue = o; o += kp.TE * kp.n_sensors;
+  m.rayq = o; o += kp.TE * kp.lidar_rows;
   m.flags = o; o += kp.S * kp.pair_words;
   m.total_bytes = o * 4;
   return m;
@@ -55,7 +59,9 @@ __host__ __device__ inline SmemMap smem_map(const KParams& kp) {
 
 struct Tile {
   float *envS, *workS, *lidS;
-  int *queue, *qcount;
+  int *queue, *rayq, *qcount;  // qcount[0]: sensor queue length, qcount[1]: ray queue length
+  int* wtask;                  // [TE/32][kWarpTasks]
+  float4* wres;                // [TE/32][kWarpTasks]
   int TE;
 };
 VB_DI Env env_view(const Tile& t, int col) {
@@ -84,8 +90,8 @@ VB_DI void load_forces(const KParams& kp, const AgentIO& aio, const Env& E, long
 // Substeps [s_begin, s_end) of one env (a thread-private column of the tile).  flags: batch-wide verdicts to obey
 // (smem or global), or NULL = speculative (every pair considered; verdict / thin bits OR-ed into sa.any_exact /
 // any_spec / thin).  All 32 lanes of a warp call this together (warp reductions).  Returns the env's taint.
-VB_DI bool run_substeps(const KParams& kp, const StepArgs& sa, const Env& E, bool ok, int s_begin, int s_end,
-                        const uint32_t* flags) {
+VB_DI bool run_substeps(const KParams& kp, const StepArgs& sa, const Tile& t, const Env& E, bool ok, int s_begin,
+                        int s_end, const uint32_t* flags) {
   // prologue: cos/sin cache of every entity that needs it, first force accumulators
   for (int r = 0; r < kp.n_trig; ++r) {
     const DEnt* en = kp.ents + __ldg(kp.trig_list + r);
@@ -98,6 +104,8 @@ VB_DI bool run_substeps(const KParams& kp, const StepArgs& sa, const Env& E, boo
 
   bool tainted = false;
   const int lane = threadIdx.x & 31;
+  int* wtask = t.wtask + (threadIdx.x >> 5) * kWarpTasks;
+  float4* wres = t.wres + (threadIdx.x >> 5) * kWarpTasks;
   for (int s = s_begin; s < s_end; ++s) {
     // ---- joints (core.py:2175, always evaluated)
     for (int j = 0; j < kp.J; ++j) {
@@ -141,17 +149,58 @@ VB_DI bool run_substeps(const KParams& kp, const StepArgs& sa, const Env& E, boo
           if (sp) or_global(sa.any_spec + w, sp);
         }
       }
-      while (sv) {
-        const int k = __ffs(sv) - 1;
-        sv &= sv - 1u;
-        const DItem* it = kp.items + kp.J + base + k;
-        V2 fa; float ta, tb;
-        eval_item(kp, it, E, fa, ta, tb);
-        if (!flags && ok && !((bpw >> k) & 1u) && (fa.x != 0.f || fa.y != 0.f)) {
-          or_global(sa.thin + w, 1u << k);
-          thin_now = true;
+      if (!ok) sv = 0u;
+      // ---- narrow phase of the survivors.  Contacts are sparse and hit different pairs in different envs, so the
+      // warp pools its (env, pair) tasks and every lane evaluates one task per round - possibly of another lane's env
+      // (the tile is shared memory) - then each lane adds up its OWN env's results in pair order.
+      const uint32_t cnt = __popc(sv);
+      uint32_t incl = cnt;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += v;
+      }
+      const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
+      const uint32_t first = incl - cnt;  // index of this lane's first task
+      for (uint32_t r0 = 0; r0 < total; r0 += kWarpTasks) {
+        {
+          uint32_t m = sv, idx = first;
+          while (m) {
+            const int k = __ffs(m) - 1;
+            m &= m - 1u;
+            if (idx - r0 < (uint32_t)kWarpTasks) wtask[idx - r0] = (lane << 8) | k;
+            ++idx;
+          }
         }
-        accumulate(it, E, fa, ta, tb);
+        __syncwarp();
+        const uint32_t nt = min((uint32_t)kWarpTasks, total - r0);
+        for (uint32_t q = lane; q < nt; q += 32) {
+          const int task = wtask[q];
+          const int src = task >> 8;
+          Env E2;
+          E2.env = E.env + (src - lane); E2.work = E.work + (src - lane); E2.TE = E.TE;
+          V2 fa; float ta, tb;
+          eval_item(kp, kp.items + kp.J + base + (task & 31), E2, fa, ta, tb);
+          wres[q] = make_float4(fa.x, fa.y, ta, tb);
+        }
+        __syncwarp();
+        {
+          uint32_t m = sv, idx = first;
+          while (m) {
+            const int k = __ffs(m) - 1;
+            m &= m - 1u;
+            if (idx - r0 < (uint32_t)kWarpTasks) {
+              const float4 r = wres[idx - r0];
+              if (!flags && !((bpw >> k) & 1u) && (r.x != 0.f || r.y != 0.f)) {
+                or_global(sa.thin + w, 1u << k);
+                thin_now = true;
+              }
+              accumulate(kp.items + kp.J + base + k, E, mk(r.x, r.y), r.z, r.w);
+            }
+            ++idx;
+          }
+        }
+        __syncwarp();
       }
     }
     tainted = tainted || thin_now;  // the taint applies from the NEXT substep on
@@ -165,48 +214,89 @@ VB_DI bool run_substeps(const KParams& kp, const StepArgs& sa, const Env& E, boo
   return tainted;
 }
 
-// LIDAR epilogue for the whole tile (every thread of the CTA calls it; contains CTA barriers).
-// n_cols = columns of the tile that hold real environments.
+// LIDAR epilogue for the whole tile (every thread of the CTA calls it, helper warps included; contains CTA barriers).
+// n_cols = columns of the tile that hold real environments.  Three passes, each on full warps:
+//   1  thread per env: per sensor the mask of targets a ray could reach at all; sensors that see something go to
+//      the sensor queue (and get cos/sin of their rotation cached); every ray starts at max_range;
+//   2  thread per (queued sensor, ray): ray-level cull with an APPROXIMATE direction (angle-sum formula) and a slack
+//      that covers the approximation: a target farther than Rc from the ray's line, or behind the origin, cannot be
+//      hit (core.py:1467-1489 sphere, :1344-1371 box, :1598-1625 line); rays that may hit go to the ray queue;
+//   3  thread per queued ray: the reference's exact arithmetic (sincosf of the fp32 angle sum, sensors.py:117).
 VB_DI void lidar_epilogue(const KParams& kp, const Tile& t, int n_cols) {
-  const int tid = threadIdx.x, TE = t.TE;
-  if (tid == 0) *t.qcount = 0;
+  const int tid = threadIdx.x, TE = t.TE, nthr = blockDim.x;
+  if (tid < 2) t.qcount[tid] = 0;
+  for (int k = 0; k < kp.n_sensors; ++k) {  // every ray starts at max_range
+    const DSensor* sn = kp.sensors + k;
+    const float mr = sn->max_range;
+    for (int i = tid; i < sn->n_rays * TE; i += nthr) t.lidS[sn->out_off * TE + i] = mr;
+  }
   __syncthreads();
-  {
+  if (tid < TE) {
     const Env E = env_view(t, tid);
     for (int k = 0; k < kp.n_sensors; ++k) {
       const DSensor* sn = kp.sensors + k;
-      const V2 o = pos_at(E, kp.ents[sn->entity].pos_row);
+      const DEnt* se = kp.ents + sn->entity;
+      const V2 o = pos_at(E, se->pos_row);
       uint32_t any = 0u;
-      for (int w = 0; w < sn->n_tw; ++w) {  // which targets can a ray of this sensor reach at all
+      for (int w = 0; w < sn->n_tw; ++w) {
         const int tb = sn->tg_begin + 32 * w, nt = min(32, sn->n_targets - 32 * w);
         uint32_t m = 0u;
         for (int q = 0; q < nt; ++q) {
           const V2 p = pos_at(E, kp.ents[__ldg(kp.targets + tb + q)].pos_row);
           const float dx = o.x - p.x, dy = o.y - p.y;
-          if (!(fmaf(dy, dy, dx * dx) > __ldg(kp.tcull2 + tb + q))) m |= 1u << q;
+          if (!(fmaf(dy, dy, dx * dx) > __ldg(&kp.tcull[tb + q].x))) m |= 1u << q;
         }
         WR(E, sn->tw_off + w) = __uint_as_float(m);
         any |= m;
       }
-      const float mr = sn->max_range;
-      for (int r = 0; r < sn->n_rays; ++r) t.lidS[(sn->out_off + r) * TE + tid] = mr;
-      if (any && tid < n_cols) t.queue[atomicAdd(t.qcount, 1)] = tid | (k << 16);
+      if (any && tid < n_cols) {
+        float s, c;
+        sincosf(ER(E, se->rot_row), &s, &c);
+        WR(E, kp.row_strig + 2 * k) = c; WR(E, kp.row_strig + 2 * k + 1) = s;
+        t.queue[atomicAdd(t.qcount, 1)] = tid | (k << 16);
+      }
     }
   }
   __syncthreads();
-  const int total = *t.qcount * kp.max_rays;
-  for (int task = tid; task < total; task += blockDim.x) {
+  const int total = t.qcount[0] * kp.max_rays;
+  for (int task = tid; task < total; task += nthr) {
     const int qi = task / kp.max_rays, r = task - qi * kp.max_rays;
-    const int item = t.queue[qi];
-    const DSensor* sn = kp.sensors + (item >> 16);
-    if (r < sn->n_rays) {
-      const int col = item & 0xffff;
-      const Env E = env_view(t, col);
-      const DEnt* se = kp.ents + sn->entity;
-      const V2 o = pos_at(E, se->pos_row);
-      const float ang = __ldg(kp.ray_angles + sn->out_off + r) + ER(E, se->rot_row);  // sensors.py:117
-      t.lidS[(sn->out_off + r) * TE + col] = cast_one_ray(kp, sn, E, o, ang);
+    const int item = t.queue[qi], k = item >> 16, col = item & 0xffff;
+    const DSensor* sn = kp.sensors + k;
+    if (r >= sn->n_rays) continue;
+    const Env E = env_view(t, col);
+    const DEnt* se = kp.ents + sn->entity;
+    const V2 o = pos_at(E, se->pos_row);
+    const float c0 = WR(E, kp.row_strig + 2 * k), s0 = WR(E, kp.row_strig + 2 * k + 1);
+    const float2 cs = __ldg(kp.ray_cs + sn->out_off + r);
+    const float dc = c0 * cs.x - s0 * cs.y, ds = s0 * cs.x + c0 * cs.y;  // ~ cos/sin(angle_r + rot)
+    const float aslack = fabsf(ER(E, se->rot_row)) + 8.f;                // radians the angle sum may have rounded over
+    bool cand = false;
+    for (int w = 0; w < sn->n_tw; ++w) {
+      uint32_t m = __float_as_uint(WR(E, sn->tw_off + w));
+      const int tb = sn->tg_begin + 32 * w;
+      while (m) {
+        const int q = __ffs(m) - 1;
+        m &= m - 1u;
+        const float4 tc = __ldg(kp.tcull + tb + q);
+        const V2 p = pos_at(E, kp.ents[__ldg(kp.targets + tb + q)].pos_row);
+        const float rx = p.x - o.x, ry = p.y - o.y;
+        const float slack = tc.w * aslack;
+        const float lat = fabsf(rx * ds - ry * dc), along = rx * dc + ry * ds;
+        cand = cand || (!(lat > tc.y + slack) && !(along < -(tc.z + slack)));
+      }
     }
+    if (cand) t.rayq[atomicAdd(t.qcount + 1, 1)] = col | (k << 8) | (r << 16);
+  }
+  __syncthreads();
+  const int nq = t.qcount[1];
+  for (int qi = tid; qi < nq; qi += nthr) {
+    const int item = t.rayq[qi], col = item & 0xff, k = (item >> 8) & 0xff, r = item >> 16;
+    const DSensor* sn = kp.sensors + k;
+    const Env E = env_view(t, col);
+    const DEnt* se = kp.ents + sn->entity;
+    const float ang = __ldg(kp.ray_angles + sn->out_off + r) + ER(E, se->rot_row);  // sensors.py:117
+    t.lidS[(sn->out_off + r) * TE + col] = cast_one_ray(kp, sn, E, pos_at(E, se->pos_row), ang);
   }
   __syncthreads();
 }
@@ -253,7 +343,8 @@ __device__ __noinline__ void repair_tainted(const KParams& kp, const AgentIO& ai
         load_forces(kp, aio, E, env);
       }
       const bool last = s == kp.S;
-      run_substeps(kp, sa, E, ok, s, last ? s : s + 1, flagS);  // s == S: prologue only (cos/sin cache, clamps)
+      // s == S: prologue only (cos/sin cache, clamps).  Helper warps (tid >= TE) have no column.
+      if (tid < TE) run_substeps(kp, sa, t, E, ok, s, last ? s : s + 1, flagS);
       if (!last) {
         if (ok) for (int r = 0; r < kp.dyn_rows; ++r) sa.u_buf[(size_t)idx * kp.dyn_rows + r] = ER(E, r);
       } else {
@@ -278,7 +369,9 @@ __global__ void __launch_bounds__(256) step_kernel(const __grid_constant__ KPara
   const int TE = kp.TE;
   Tile t;
   t.envS = smem + m.env; t.workS = smem + m.work; t.lidS = smem + m.lid;
-  t.queue = reinterpret_cast<int*>(smem + m.queue); t.qcount = reinterpret_cast<int*>(smem + m.bar) + 2;
+  t.queue = reinterpret_cast<int*>(smem + m.queue); t.rayq = reinterpret_cast<int*>(smem + m.rayq);
+  t.qcount = reinterpret_cast<int*>(smem + m.bar) + 2;
+  t.wtask = reinterpret_cast<int*>(smem + m.wtask); t.wres = reinterpret_cast<float4*>(smem + m.wres);
   t.TE = TE;
   uint32_t* flagS = reinterpret_cast<uint32_t*>(smem + m.flags);
   const int nw = kp.S * kp.pair_words;
@@ -309,11 +402,14 @@ __global__ void __launch_bounds__(256) step_kernel(const __grid_constant__ KPara
       bulk_g2s(t.envS + r * TE, src, row_bytes, bar);
     }
   }
-  const Env E = env_view(t, tid);
-  if (ok) load_forces(kp, aio, E, env0 + tid);
-  mbar_wait(bar, 0);
-
-  const bool tainted = run_substeps(kp, sa, E, ok, sa.s_begin, sa.s_end, sa.flags_in);
+  // threads [0, TE) own one env each; helper warps (tid >= TE, LIDAR worlds only) join for the LIDAR epilogue
+  const Env E = env_view(t, tid < TE ? tid : 0);
+  bool tainted = false;
+  if (tid < TE) {
+    if (ok) load_forces(kp, aio, E, env0 + tid);
+    mbar_wait(bar, 0);
+    tainted = run_substeps(kp, sa, t, E, ok, sa.s_begin, sa.s_end, sa.flags_in);
+  }
   const bool lidar = sa.do_lidar && sa.lidar_out && kp.n_rays;
   if (lidar) lidar_epilogue(kp, t, n_valid);
 

@@ -98,7 +98,7 @@ int build_plan(const vmasb200_world_desc* d, vmasb200_plan* pl) {
 
   // ---- sensors (sensors.py:46-69, core.py:1677-1690)
   pl->sensors.clear(); pl->ray_angles.clear(); pl->targets.clear(); pl->lidar_slot.assign(d->n_lidars, 0);
-  pl->tcull2.clear();
+  pl->tcull.clear(); pl->ray_cs.clear();
   int ray_off = 0, n_lmask = 0, max_rays = 0;
   for (int k = 0; k < d->n_lidars; ++k) {
     const vmasb200_lidar& ld = d->lidars[k];
@@ -111,18 +111,27 @@ int build_plan(const vmasb200_world_desc* d, vmasb200_plan* pl) {
     for (int t = 0; t < ld.n_targets; ++t) {
       if (ld.targets[t] < 0 || ld.targets[t] >= E) { set_error("world desc: lidar target out of range"); return VMASB200_ERR_INVALID; }
       pl->targets.push_back(ld.targets[t]);
-      // a ray of length max_range cannot reach a shape whose centre is farther than max_range + circumscribed radius
-      pl->tcull2.push_back(sq_up(with_margin((double)ld.max_range + d->entities[ld.targets[t]].circumscribed_radius)));
+      // a ray of length max_range cannot reach a shape whose centre is farther than max_range + circumscribed radius,
+      // nor one whose centre is farther than Rc from the ray's line, nor one that lies behind the origin
+      const vmasb200_entity& te = d->entities[ld.targets[t]];
+      const double reach = with_margin((double)ld.max_range + te.circumscribed_radius);
+      const double lat = with_margin(te.circumscribed_radius);
+      pl->tcull.push_back(make_float4(sq_up(reach), (float)lat, te.shape == VMASB200_SPHERE ? 1e-5f : (float)lat,
+                                      (float)(reach * 4.8e-7)));
     }
     sn.tw_off = n_lmask;  // relative to row_lmask
     sn.n_tw = (ld.n_targets + 31) / 32;
     n_lmask += sn.n_tw;
-    for (int r = 0; r < ld.n_rays; ++r) pl->ray_angles.push_back(ld.angles[r]);
+    for (int r = 0; r < ld.n_rays; ++r) {
+      pl->ray_angles.push_back(ld.angles[r]);
+      pl->ray_cs.push_back(make_float2((float)std::cos((double)ld.angles[r]), (float)std::sin((double)ld.angles[r])));
+    }
     pl->lidar_slot[k] = ray_off;
     ray_off += ld.n_rays;
     max_rays = std::max(max_rays, ld.n_rays);
     pl->sensors.push_back(sn);
   }
+  if (d->n_lidars > 255 || max_rays > 32767) { set_error("more than 255 sensors / 32767 rays per sensor are not supported"); return VMASB200_ERR_UNSUPPORTED; }
   kp.n_sensors = d->n_lidars; kp.n_rays = ray_off; kp.max_rays = max_rays;
   kp.lidar_rows = ray_off;
   kp.n_lmask_words = n_lmask;
@@ -202,7 +211,8 @@ int build_plan(const vmasb200_world_desc* d, vmasb200_plan* pl) {
   kp.row_trig = kp.row_fin + 3 * kp.n_dyn;
   kp.row_frc = kp.row_trig + 4 * kp.n_trig;
   kp.row_lmask = kp.row_frc + 3 * kp.A;
-  kp.work_rows = kp.row_lmask + kp.n_lmask_words;
+  kp.row_strig = kp.row_lmask + kp.n_lmask_words;
+  kp.work_rows = kp.row_strig + 2 * kp.n_sensors;
   for (int i = 0; i < kp.n_dyn; ++i) pl->ents[pl->dyn_list[i]].fin_row = kp.row_fin + 3 * i;
   for (int i = 0; i < kp.n_trig; ++i) pl->ents[pl->trig_list[i]].trig_row = kp.row_trig + 4 * i;
   for (int e = 0; e < E; ++e) {
@@ -245,8 +255,10 @@ int build_plan(const vmasb200_world_desc* d, vmasb200_plan* pl) {
   }
 
   // ---- kernel shape: one thread per env, TE envs per CTA; keep >= 2 CTAs per SM resident when the world allows it
-  const int per_env = 4 * (kp.dyn_rows + kp.stat_rows + kp.lidar_rows + kp.work_rows) + 4 * kp.n_sensors;
-  const int fixed = 64;
+  // per env: staged rows, work rows, lidar rows + ray queue (one int per ray), sensor queue; per warp: 32 narrow-phase
+  // tasks (int + float4)
+  const int per_env = 4 * (kp.dyn_rows + kp.stat_rows + kp.work_rows + 2 * kp.lidar_rows + kp.n_sensors) + 20;
+  const int fixed = 64 + 4 * kp.S * kp.pair_words;
   int TE = d->envs_per_cta;
   if (TE == 0) {
     TE = 64;
@@ -255,6 +267,7 @@ int build_plan(const vmasb200_world_desc* d, vmasb200_plan* pl) {
   if (TE < 32 || TE > 256 || TE % 32) { set_error("envs_per_cta must be a multiple of 32 in [32, 256]"); return VMASB200_ERR_INVALID; }
   if (fixed + TE * per_env > 226 * 1024) { set_error("world too large for one CTA's shared memory"); return VMASB200_ERR_UNSUPPORTED; }
   kp.TE = TE;
+  kp.NT = kp.n_rays ? std::min(256, 2 * TE) : TE;  // helper warps for the LIDAR epilogue (register file: 4 CTAs / SM)
 
   // ---- world constants
   kp.sub_dt = (float)((double)d->dt / (double)d->substeps);  // core.py:1124 (Python doubles)

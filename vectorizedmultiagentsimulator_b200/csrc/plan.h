@@ -20,7 +20,9 @@ struct vmasb200_plan {
   std::vector<vb::DItem> items;
   std::vector<vb::DBroad> broad;
   std::vector<int32_t> dyn_list, trig_list, targets;
-  std::vector<float> tcull2, ray_angles;
+  std::vector<float> ray_angles;
+  std::vector<float4> tcull;
+  std::vector<float2> ray_cs;
   std::vector<vb::DSensor> sensors;
   std::vector<vmasb200_pair> pairs;
   std::vector<int32_t> dyn_slot, stat_slot, act_slot, joint_slot, lidar_slot, agent_entities;

@@ -14,6 +14,7 @@
 //             trig 4 per entity that needs cos/sin (c s c2 s2)
 //             frc  3 per agent (state.force x y, state.torque; clamped in place, core.py:2017-2040)
 //             lmask one per (sensor, 32-target word)
+//             strig 2 per sensor (cos/sin of the sensing entity's rotation, for the ray cull)
 #pragma once
 #include <stdint.h>
 
@@ -113,9 +114,10 @@ struct KParams {            // kernel parameter (by value)
   // sizes
   int32_t E, n_dyn, J, P, n_items, S, A, n_trig, n_sensors, n_rays, pair_words, max_rays;
   int32_t dyn_rows, stat_rows, act_rows, lidar_rows;
-  int32_t TE;               // envs (= threads) per CTA
-  // work rows: [fin 3*n_dyn][trig 4*n_trig][frc 3*A][lmask]
-  int32_t work_rows, row_fin, row_trig, row_frc, row_lmask, n_lmask_words;
+  int32_t TE;               // envs per CTA (= threads that run the physics)
+  int32_t NT;               // threads per CTA: TE, or a multiple of it when helper warps share the LIDAR epilogue
+  // work rows: [fin 3*n_dyn][trig 4*n_trig][frc 3*A][lmask][strig 2*n_sensors]
+  int32_t work_rows, row_fin, row_trig, row_frc, row_lmask, n_lmask_words, row_strig;
   // device tables
   const DEnt* ents;
   const DItem* items;
@@ -126,7 +128,11 @@ struct KParams {            // kernel parameter (by value)
   const float* ray_angles;  // [n_rays] sensor-frame angles, sensors concatenated (row 0 of Lidar._angles)
   const DSensor* sensors;
   const int32_t* targets;
-  const float* tcull2;      // [n targets] squared LIDAR cull distance per (sensor, target): (max_range + Rc) with margin
+  // [n targets] LIDAR culls per (sensor, target): x = squared reach (max_range + Rc, with margin) of the sensor-level
+  // cull; y = lateral reach of the ray-level cull (Rc with margin); z = how far behind the origin the centre may be;
+  // w = slack per radian of ray angle (the cull uses an approximate ray direction)
+  const float4* tcull;
+  const float2* ray_cs;     // [n_rays] (cos, sin) of the sensor-frame ray angles (ray cull only)
   // world constants (core.py:1090-1143)
   float sub_dt, Kc, Kj, Kt, margin;
   float xs, ys;

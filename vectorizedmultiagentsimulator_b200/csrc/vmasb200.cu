@@ -40,7 +40,7 @@ int upload_plan(vmasb200_plan* pl) {
   size_t o_ent = put(blob, pl->ents), o_item = put(blob, pl->items), o_broad = put(blob, pl->broad);
   size_t o_dyn = put(blob, pl->dyn_list), o_trig = put(blob, pl->trig_list), o_ag = put(blob, pl->agent_entities);
   size_t o_ray = put(blob, pl->ray_angles), o_sen = put(blob, pl->sensors), o_tg = put(blob, pl->targets);
-  size_t o_tc = put(blob, pl->tcull2);
+  size_t o_tc = put(blob, pl->tcull), o_cs = put(blob, pl->ray_cs);
   VB_CUDA(cudaMalloc(&pl->d_blob, blob.size()));
   VB_CUDA(cudaMemcpy(pl->d_blob, blob.data(), blob.size(), cudaMemcpyHostToDevice));
   char* b = static_cast<char*>(pl->d_blob);
@@ -54,7 +54,8 @@ int upload_plan(vmasb200_plan* pl) {
   kp.ray_angles = reinterpret_cast<const float*>(b + o_ray);
   kp.sensors = reinterpret_cast<const DSensor*>(b + o_sen);
   kp.targets = reinterpret_cast<const int32_t*>(b + o_tg);
-  kp.tcull2 = reinterpret_cast<const float*>(b + o_tc);
+  kp.tcull = reinterpret_cast<const float4*>(b + o_tc);
+  kp.ray_cs = reinterpret_cast<const float2*>(b + o_cs);
   // 4 bit arrays (flags, any_exact, any_spec, thin) + 4 counters
   const size_t nbits = (4 * bits_words(kp) + 4) * sizeof(uint32_t);
   VB_CUDA(cudaMalloc(&pl->d_bits, nbits));
@@ -105,7 +106,7 @@ static int launch_step(vmasb200_plan* pl, const vmasb200_step_io* io, long long 
   sa.flags_out = flags; sa.any_exact = flags + bw; sa.any_spec = flags + 2 * bw; sa.thin = flags + 3 * bw;
   sa.counters = reinterpret_cast<int*>(flags + 4 * bw);
   const unsigned grid = (unsigned)((env_end - env_begin + kp.TE - 1) / kp.TE);
-  const unsigned block = (unsigned)kp.TE;
+  const unsigned block = (unsigned)kp.NT;
   if (io->exact) {
     // exact path: the batch-wide World.collides verdicts are reduced before every substep (core.py:2796-2800)
     if (nw) VB_CUDA(cudaMemsetAsync(flags, 0, nw * sizeof(uint32_t), st));
