@@ -1,0 +1,170 @@
+"""GPU: the drop-in (vectorizedmultiagentsimulator_b200.dropin.enable) inside the reference's own Environment.step.
+
+Two environments are built from the UNMODIFIED reference (oracle/_ref, see oracle/make_ref.sh) on the same CUDA device
+with the same seed; one keeps the reference's torch World.step / cast_rays, the other is patched.  Both are driven with
+the same random actions; observations, rewards, dones and the full entity state must agree (fp32 rtol 1e-5 / atol 1e-6
+after one step; the stated drift bound of tests/fixtures.drift_bounds over the rollout), including across a full
+reset and a partial reset_at."""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REF = os.path.join(ROOT, "oracle", "_ref")
+
+CASES = [
+    ("simple_spread", dict(n_agents=3), 1),
+    ("navigation", dict(n_agents=4), 1),
+    ("transport", dict(n_agents=4), 1),
+    ("transport", dict(n_agents=4), 5),
+    ("joint_passage", dict(), 1),
+    ("football", dict(ai_red_agents=False), 1),
+    ("flocking", dict(), 1),
+    ("balance", dict(), 1),
+    ("give_way", dict(), 1),
+]
+
+
+def _vmas():
+    if not os.path.isdir(os.path.join(REF, "vmas")):
+        pytest.skip("oracle/_ref (the reference install) did not travel to this box")
+    for p in (REF, os.path.join(ROOT, "oracle", "gym_stub")):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    import vmas
+
+    return vmas
+
+
+def _make(vmas, scenario, kw, n, substeps):
+    env = vmas.make_env(scenario, num_envs=n, device="cuda", seed=0, continuous_actions=True, **kw)
+    if substeps > 1:
+        env.world._substeps = substeps
+        env.world._sub_dt = env.world._dt / substeps
+    return env
+
+
+def _state(env):
+    import torch
+
+    return torch.stack([torch.cat([e.state.pos, e.state.vel, e.state.rot, e.state.ang_vel], -1) for e in env.world.entities])
+
+
+def _flat(x):
+    import torch
+
+    if isinstance(x, dict):
+        return torch.cat([_flat(v) for _, v in sorted(x.items())], -1)
+    if isinstance(x, (list, tuple)):
+        return torch.cat([_flat(v) for v in x], -1)
+    return x.reshape(x.shape[0], -1).float()
+
+
+@pytest.mark.parametrize("scenario,kw,substeps", CASES)
+def test_environment_step_matches_reference(scenario, kw, substeps):
+    import torch
+
+    from vectorizedmultiagentsimulator_b200 import dropin
+
+    vmas = _vmas()
+    n, steps = 96, 30
+    ref = _make(vmas, scenario, kw, n, substeps)
+    env = _make(vmas, scenario, kw, n, substeps)
+    b = dropin.enable(env)
+    jointed = bool(getattr(env.world, "_joints", {}))
+    pos_tol, vel_tol = (1e-2, 2e-1) if jointed else (1e-4, 1e-3)
+    # Stiff jointed worlds (joint_force 900, 10 substeps, inertia ~5e-4) are chaotic: one input ulp grows to O(0.1)
+    # within ~15 steps.  Their bound is therefore calibrated on the reference itself: a twin reference env whose
+    # positions are moved by ONE fp32 ulp after every (re)synchronisation shows how many envs leave the tolerance by
+    # sensitivity alone; the drop-in may not lose more than twice that many (+2).
+    twin = _make(vmas, scenario, kw, n, substeps) if jointed else None
+
+    def nudge():
+        if twin is not None:
+            for e in twin.world.entities:
+                if e.movable:
+                    e.state.pos = torch.nextafter(e.state.pos, torch.full_like(e.state.pos, float("inf")))
+
+    nudge()
+    torch.manual_seed(7)
+    for t in range(steps):
+        if t == 12:
+            o1, o2 = ref.reset(seed=3), env.reset(seed=3)
+            assert torch.allclose(_flat(o1), _flat(o2), rtol=1e-5, atol=1e-6)
+            if twin is not None:
+                twin.reset(seed=3)
+                nudge()
+        if t == 20:  # partial reset: in-place writes through the bound views (the spawn draws from the global RNG)
+            torch.manual_seed(11)
+            ref.reset_at(5)
+            torch.manual_seed(11)
+            env.reset_at(5)
+            if twin is not None:
+                torch.manual_seed(11)
+                twin.reset_at(5)
+            torch.manual_seed(12)
+        acts = [torch.rand(n, a.action_size, device="cuda") * 2 * a.u_range - a.u_range for a in ref.agents]
+        o1, r1, d1, _ = ref.step([a.clone() for a in acts])
+        o2, r2, d2, _ = env.step([a.clone() for a in acts])
+        s1, s2 = _state(ref), _state(env)
+        if twin is not None:
+            twin.step([a.clone() for a in acts])
+            if t not in (0, 12):
+                s3 = _state(twin)
+                lost = lambda a, b: int(((a[..., 0:2] - b[..., 0:2]).abs().amax(dim=(0, 2)) > pos_tol).sum())
+                assert lost(s1, s2) <= 2 * lost(s1, s3) + 2, f"{scenario}: {lost(s1, s2)} envs diverged at step {t}, ulp twin {lost(s1, s3)}"
+                assert torch.equal(d1, d2)
+                continue
+        if t == 0:
+            assert torch.allclose(s1, s2, rtol=1e-5, atol=1e-6), f"{scenario}: state after one step {float((s1 - s2).abs().max()):.3e}"
+            assert torch.allclose(_flat(o1), _flat(o2), rtol=1e-5, atol=1e-5), f"{scenario}: obs after one step"
+        assert float((s1[..., 0:2] - s2[..., 0:2]).abs().max()) <= pos_tol, f"{scenario}: pos drift at step {t}"
+        assert float((s1[..., 2:4] - s2[..., 2:4]).abs().max()) <= vel_tol, f"{scenario}: vel drift at step {t}"
+        assert torch.equal(d1, d2), f"{scenario}: done flags differ at step {t}"
+        assert torch.allclose(_flat(r1), _flat(r2), rtol=1e-3, atol=10 * vel_tol), f"{scenario}: reward at step {t}"
+    assert b.n_steps == steps
+    dropin.disable(env)
+
+
+def test_lidar_measure_uses_epilogue_and_falls_back():
+    import torch
+
+    from vectorizedmultiagentsimulator_b200 import dropin
+
+    vmas = _vmas()
+    n = 64
+    ref = _make(vmas, "navigation", dict(n_agents=4), n, 1)
+    env = _make(vmas, "navigation", dict(n_agents=4), n, 1)
+    b = dropin.enable(env)
+    acts = [torch.zeros(n, 2, device="cuda") for _ in ref.agents]
+    ref.step(acts)
+    env.step(acts)
+    for a1, a2 in zip(ref.agents, env.agents):
+        m1, m2 = a1.sensors[0].measure(), a2.sensors[0].measure()
+        assert torch.allclose(m1, m2, rtol=1e-5, atol=1e-6)
+    assert b._state_untouched()
+    # moving an agent invalidates the epilogue hand-off: measure must see the new position (standalone cast_rays)
+    p = env.agents[0].state.pos.clone()
+    p[:, 0] += 0.05
+    env.agents[0].set_pos(p, batch_index=None)
+    ref.agents[0].set_pos(p.clone(), batch_index=None)
+    for a1, a2 in zip(ref.agents, env.agents):
+        assert torch.allclose(a1.sensors[0].measure(), a2.sensors[0].measure(), rtol=1e-5, atol=1e-6)
+    # in-place write through the bound view
+    env.agents[1].state.pos[:, 1] += 0.03
+    ref.agents[1].state.pos[:, 1] += 0.03
+    for a1, a2 in zip(ref.agents, env.agents):
+        assert torch.allclose(a1.sensors[0].measure(), a2.sensors[0].measure(), rtol=1e-5, atol=1e-6)
+
+
+def test_cpu_world_is_rejected():
+    from vectorizedmultiagentsimulator_b200 import _lib, dropin
+
+    vmas = _vmas()
+    env = vmas.make_env("simple_spread", num_envs=4, device="cpu", seed=0, continuous_actions=True)
+    with pytest.raises(_lib.VmasB200Error):
+        dropin.enable(env)

@@ -90,17 +90,18 @@ VB_DI void load_forces(const KParams& kp, const AgentIO& aio, const Env& E, long
 // Substeps [s_begin, s_end) of one env (a thread-private column of the tile).  flags: batch-wide verdicts to obey
 // (smem or global), or NULL = speculative (every pair considered; verdict / thin bits OR-ed into sa.any_exact /
 // any_spec / thin).  All 32 lanes of a warp call this together (warp reductions).  Returns the env's taint.
+template <bool CT>
 VB_DI bool run_substeps(const KParams& kp, const StepArgs& sa, const Tile& t, const Env& E, bool ok, int s_begin,
                         int s_end, const uint32_t* flags) {
   // prologue: cos/sin cache of every entity that needs it, first force accumulators
   for (int r = 0; r < kp.n_trig; ++r) {
-    const DEnt* en = kp.ents + __ldg(kp.trig_list + r);
+    const DEnt* en = &T_ent<CT>(kp, T_trig<CT>(kp, r));
     store_trig(en, E, ER(E, en->rot_row));
   }
   // the clamp of core.py:2017-2040 is re-applied to its own result every substep: replay it for the substeps
   // that earlier launches of a split step already did
   for (int rep = 0; rep <= s_begin; ++rep)
-    for (int d = 0; d < kp.n_dyn; ++d) begin_forces(kp, kp.ents + __ldg(kp.dyn_list + d), E);
+    for (int d = 0; d < kp.n_dyn; ++d) begin_forces(kp, &T_ent<CT>(kp, T_dyn<CT>(kp, d)), E);
 
   bool tainted = false;
   const int lane = threadIdx.x & 31;
@@ -111,7 +112,7 @@ VB_DI bool run_substeps(const KParams& kp, const StepArgs& sa, const Tile& t, co
     for (int j = 0; j < kp.J; ++j) {
       const DItem* it = kp.items + j;
       V2 fa; float ta, tb;
-      eval_item(kp, it, E, fa, ta, tb);
+      eval_item<CT>(kp, it, E, fa, ta, tb);
       accumulate(it, E, fa, ta, tb);
     }
     // ---- candidate pairs, 32 at a time: broad phase for all, narrow phase for the survivors
@@ -121,19 +122,18 @@ VB_DI bool run_substeps(const KParams& kp, const StepArgs& sa, const Tile& t, co
       uint32_t bpw = 0u, sv = 0u;
 #pragma unroll 4
       for (int k = 0; k < n; ++k) {
-        const DBroad* bq = kp.broad + base + k;
-        const int4 bi = __ldg(reinterpret_cast<const int4*>(bq));
-        const float4 bf = __ldg(reinterpret_cast<const float4*>(bq) + 1);
-        const float dx = ER(E, bi.x) - ER(E, bi.y), dy = ER(E, bi.x + 1) - ER(E, bi.y + 1);
+        const DBroad& bq = T_broad<CT>(kp, base + k);
+        const int ra = bq.pa_row, rb = bq.pb_row, rt = bq.trig_row;
+        const float dx = ER(E, ra) - ER(E, rb), dy = ER(E, ra + 1) - ER(E, rb + 1);
         const float d2 = fmaf(dy, dy, dx * dx);
-        const bool bp = d2 <= bf.x;  // == (norm(pa - pb) <= Rc_a + Rc_b), core.py:2796-2800
+        const bool bp = d2 <= bq.t2_bp;  // == (norm(pa - pb) <= Rc_a + Rc_b), core.py:2796-2800
         bool surv;
-        if (bi.z < 0) {
-          surv = !(d2 > bf.y);
-        } else {  // sphere centre in the line / box frame
-          const float c = WR(E, bi.z), sn = WR(E, bi.z + 1);
-          const float lx = dx * c + dy * sn, ly = dx * sn - dy * c;
-          surv = !(fabsf(lx) > bf.z) && !(fabsf(ly) > bf.w);
+        if (rt < 0) {
+          surv = !(d2 > bq.t2_cull);
+        } else {  // sphere centre in the line / box frame (a conservative cull: fused arithmetic is fine here)
+          const float c = WR(E, rt), sn = WR(E, rt + 1);
+          const float lx = fmaf(dx, c, dy * sn), ly = fmaf(dx, sn, -(dy * c));
+          surv = !(fabsf(lx) > bq.hx) && !(fabsf(ly) > bq.hy);
         }
         bpw |= (bp ? 1u : 0u) << k;
         sv |= (surv ? 1u : 0u) << k;
@@ -180,7 +180,7 @@ VB_DI bool run_substeps(const KParams& kp, const StepArgs& sa, const Tile& t, co
           Env E2;
           E2.env = E.env + (src - lane); E2.work = E.work + (src - lane); E2.TE = E.TE;
           V2 fa; float ta, tb;
-          eval_item(kp, kp.items + kp.J + base + (task & 31), E2, fa, ta, tb);
+          eval_item<CT>(kp, kp.items + kp.J + base + (task & 31), E2, fa, ta, tb);
           wres[q] = make_float4(fa.x, fa.y, ta, tb);
         }
         __syncwarp();
@@ -206,7 +206,7 @@ VB_DI bool run_substeps(const KParams& kp, const StepArgs& sa, const Tile& t, co
     tainted = tainted || thin_now;  // the taint applies from the NEXT substep on
     // ---- integrate, then open the next substep's accumulators
     for (int d = 0; d < kp.n_dyn; ++d) {
-      const DEnt* en = kp.ents + __ldg(kp.dyn_list + d);
+      const DEnt* en = &T_ent<CT>(kp, T_dyn<CT>(kp, d));
       integrate(kp, en, E, s);
       if (s + 1 < s_end) begin_forces(kp, en, E);
     }
@@ -222,11 +222,12 @@ VB_DI bool run_substeps(const KParams& kp, const StepArgs& sa, const Tile& t, co
 //      that covers the approximation: a target farther than Rc from the ray's line, or behind the origin, cannot be
 //      hit (core.py:1467-1489 sphere, :1344-1371 box, :1598-1625 line); rays that may hit go to the ray queue;
 //   3  thread per queued ray: the reference's exact arithmetic (sincosf of the fp32 angle sum, sensors.py:117).
+template <bool CT>
 VB_DI void lidar_epilogue(const KParams& kp, const Tile& t, int n_cols) {
   const int tid = threadIdx.x, TE = t.TE, nthr = blockDim.x;
   if (tid < 2) t.qcount[tid] = 0;
   for (int k = 0; k < kp.n_sensors; ++k) {  // every ray starts at max_range
-    const DSensor* sn = kp.sensors + k;
+    const DSensor* sn = &T_sensor<CT>(kp, k);
     const float mr = sn->max_range;
     for (int i = tid; i < sn->n_rays * TE; i += nthr) t.lidS[sn->out_off * TE + i] = mr;
   }
@@ -234,15 +235,15 @@ VB_DI void lidar_epilogue(const KParams& kp, const Tile& t, int n_cols) {
   if (tid < TE) {
     const Env E = env_view(t, tid);
     for (int k = 0; k < kp.n_sensors; ++k) {
-      const DSensor* sn = kp.sensors + k;
-      const DEnt* se = kp.ents + sn->entity;
+      const DSensor* sn = &T_sensor<CT>(kp, k);
+      const DEnt* se = &T_ent<CT>(kp, sn->entity);
       const V2 o = pos_at(E, se->pos_row);
       uint32_t any = 0u;
       for (int w = 0; w < sn->n_tw; ++w) {
         const int tb = sn->tg_begin + 32 * w, nt = min(32, sn->n_targets - 32 * w);
         uint32_t m = 0u;
         for (int q = 0; q < nt; ++q) {
-          const V2 p = pos_at(E, kp.ents[__ldg(kp.targets + tb + q)].pos_row);
+          const V2 p = pos_at(E, T_ent<CT>(kp, __ldg(kp.targets + tb + q)).pos_row);
           const float dx = o.x - p.x, dy = o.y - p.y;
           if (!(fmaf(dy, dy, dx * dx) > __ldg(&kp.tcull[tb + q].x))) m |= 1u << q;
         }
@@ -262,10 +263,10 @@ VB_DI void lidar_epilogue(const KParams& kp, const Tile& t, int n_cols) {
   for (int task = tid; task < total; task += nthr) {
     const int qi = task / kp.max_rays, r = task - qi * kp.max_rays;
     const int item = t.queue[qi], k = item >> 16, col = item & 0xffff;
-    const DSensor* sn = kp.sensors + k;
+    const DSensor* sn = &T_sensor<CT>(kp, k);
     if (r >= sn->n_rays) continue;
     const Env E = env_view(t, col);
-    const DEnt* se = kp.ents + sn->entity;
+    const DEnt* se = &T_ent<CT>(kp, sn->entity);
     const V2 o = pos_at(E, se->pos_row);
     const float c0 = WR(E, kp.row_strig + 2 * k), s0 = WR(E, kp.row_strig + 2 * k + 1);
     const float2 cs = __ldg(kp.ray_cs + sn->out_off + r);
@@ -279,7 +280,7 @@ VB_DI void lidar_epilogue(const KParams& kp, const Tile& t, int n_cols) {
         const int q = __ffs(m) - 1;
         m &= m - 1u;
         const float4 tc = __ldg(kp.tcull + tb + q);
-        const V2 p = pos_at(E, kp.ents[__ldg(kp.targets + tb + q)].pos_row);
+        const V2 p = pos_at(E, T_ent<CT>(kp, __ldg(kp.targets + tb + q)).pos_row);
         const float rx = p.x - o.x, ry = p.y - o.y;
         const float slack = tc.w * aslack;
         const float lat = fabsf(rx * ds - ry * dc), along = rx * dc + ry * ds;
@@ -292,11 +293,11 @@ VB_DI void lidar_epilogue(const KParams& kp, const Tile& t, int n_cols) {
   const int nq = t.qcount[1];
   for (int qi = tid; qi < nq; qi += nthr) {
     const int item = t.rayq[qi], col = item & 0xff, k = (item >> 8) & 0xff, r = item >> 16;
-    const DSensor* sn = kp.sensors + k;
+    const DSensor* sn = &T_sensor<CT>(kp, k);
     const Env E = env_view(t, col);
-    const DEnt* se = kp.ents + sn->entity;
+    const DEnt* se = &T_ent<CT>(kp, sn->entity);
     const float ang = __ldg(kp.ray_angles + sn->out_off + r) + ER(E, se->rot_row);  // sensors.py:117
-    t.lidS[(sn->out_off + r) * TE + col] = cast_one_ray(kp, sn, E, pos_at(E, se->pos_row), ang);
+    t.lidS[(sn->out_off + r) * TE + col] = cast_one_ray<CT>(kp, sn, E, pos_at(E, se->pos_row), ang);
   }
   __syncthreads();
 }
@@ -304,6 +305,7 @@ VB_DI void lidar_epilogue(const KParams& kp, const Tile& t, int n_cols) {
 // Re-simulation of the tainted envs by the last CTA (rare path; see the header comment).  flagS (smem, [S][pair_words])
 // starts as any_exact and ends as the reference's verdicts.  u_buf holds the evolving state of tainted env `idx` as
 // dyn_rows consecutive floats; each thread works on one tainted env at a time in its own tile column.
+template <bool CT>
 __device__ __noinline__ void repair_tainted(const KParams& kp, const AgentIO& aio, const StepArgs& sa, const Tile& t,
                                             uint32_t* flagS, int nu) {
   const int tid = threadIdx.x, nthr = blockDim.x, TE = t.TE;
@@ -321,7 +323,7 @@ __device__ __noinline__ void repair_tainted(const KParams& kp, const AgentIO& ai
           return row < kp.dyn_rows ? dyn[row + k] : sa.stat[(size_t)(row - kp.dyn_rows + k) * sa.ld + env];
         };
         for (int p = 0; p < kp.P; ++p) {
-          const DBroad* bq = kp.broad + p;
+          const DBroad* bq = &T_broad<CT>(kp, p);
           const float dx = px(bq->pa_row, 0) - px(bq->pb_row, 0), dy = px(bq->pa_row, 1) - px(bq->pb_row, 1);
           if (fmaf(dy, dy, dx * dx) <= bq->t2_bp) {
             uint32_t* w = flagS + s * kp.pair_words + (p >> 5);
@@ -344,11 +346,11 @@ __device__ __noinline__ void repair_tainted(const KParams& kp, const AgentIO& ai
       }
       const bool last = s == kp.S;
       // s == S: prologue only (cos/sin cache, clamps).  Helper warps (tid >= TE) have no column.
-      if (tid < TE) run_substeps(kp, sa, t, E, ok, s, last ? s : s + 1, flagS);
+      if (tid < TE) run_substeps<CT>(kp, sa, t, E, ok, s, last ? s : s + 1, flagS);
       if (!last) {
         if (ok) for (int r = 0; r < kp.dyn_rows; ++r) sa.u_buf[(size_t)idx * kp.dyn_rows + r] = ER(E, r);
       } else {
-        if (sa.lidar_out && kp.n_rays) lidar_epilogue(kp, t, min(TE, nu - base));
+        if (sa.lidar_out && kp.n_rays) lidar_epilogue<CT>(kp, t, min(TE, nu - base));
         if (ok) {
           for (int r = 0; r < kp.dyn_rows; ++r) sa.dyn_out[(size_t)r * sa.ld + env] = ER(E, r);
           if (sa.lidar_out)
@@ -360,6 +362,7 @@ __device__ __noinline__ void repair_tainted(const KParams& kp, const AgentIO& ai
   }
 }
 
+template <bool CT>
 __global__ void __launch_bounds__(256) step_kernel(const __grid_constant__ KParams kp, const __grid_constant__ AgentIO aio,
                                                    const __grid_constant__ StepArgs sa) {
   extern __shared__ __align__(16) float smem[];
@@ -408,10 +411,10 @@ __global__ void __launch_bounds__(256) step_kernel(const __grid_constant__ KPara
   if (tid < TE) {
     if (ok) load_forces(kp, aio, E, env0 + tid);
     mbar_wait(bar, 0);
-    tainted = run_substeps(kp, sa, t, E, ok, sa.s_begin, sa.s_end, sa.flags_in);
+    tainted = run_substeps<CT>(kp, sa, t, E, ok, sa.s_begin, sa.s_end, sa.flags_in);
   }
   const bool lidar = sa.do_lidar && sa.lidar_out && kp.n_rays;
-  if (lidar) lidar_epilogue(kp, t, n_valid);
+  if (lidar) lidar_epilogue<CT>(kp, t, n_valid);
 
   if (spec && tainted && ok) {  // keep the INPUT state of a tainted env (dyn_in is intact until our own store)
     const int idx = atomicAdd(sa.counters + 1, 1);
@@ -425,7 +428,7 @@ __global__ void __launch_bounds__(256) step_kernel(const __grid_constant__ KPara
     for (int r = tid; r < kp.dyn_rows; r += 32) bulk_s2g(sa.dyn_out + (size_t)r * sa.ld + env0, t.envS + r * TE, row_bytes);
     if (sa.act_out)  // clamped action write-back (core.py:2019-2026, 2031-2038): the frc rows of the clamped agents
       for (int a = tid; a < kp.A; a += 32) {
-        const int ao = kp.ents[__ldg(kp.agent_ents + a)].act_off;
+        const int ao = T_ent<CT>(kp, T_agent<CT>(kp, a)).act_off;
         if (ao >= 0)
           for (int k = 0; k < 3; ++k)
             bulk_s2g(sa.act_out + (size_t)(ao + k) * sa.ld + env0, t.workS + (kp.row_frc + 3 * a + k) * TE, row_bytes);
@@ -448,7 +451,7 @@ __global__ void __launch_bounds__(256) step_kernel(const __grid_constant__ KPara
   bad = __syncthreads_or(bad);
   const int nu = *reinterpret_cast<volatile int*>(sa.counters + 1);
   if (bad) {
-    repair_tainted(kp, aio, sa, t, flagS, nu);
+    repair_tainted<CT>(kp, aio, sa, t, flagS, nu);
     for (int w = tid; w < nw; w += blockDim.x) sa.flags_out[w] = flagS[w];
   } else {
     for (int w = tid; w < nw; w += blockDim.x) sa.flags_out[w] = __ldcg(sa.any_exact + w) | __ldcg(sa.any_spec + w);

@@ -2,6 +2,7 @@
 #pragma once
 #include <cuda_runtime.h>
 
+#include <memory>
 #include <string>
 #include <vector>
 
@@ -9,6 +10,7 @@
 #include "tables.h"
 
 namespace vb {
+struct CTab;
 constexpr int kHostStreams = 4;  // chunk streams of the host-buffer entry point
 }
 
@@ -27,6 +29,8 @@ struct vmasb200_plan {
   std::vector<vmasb200_pair> pairs;
   std::vector<int32_t> dyn_slot, stat_slot, act_slot, joint_slot, lidar_slot, agent_entities;
   int smem_bytes = 0;
+  uint64_t serial = 0;                      // identity for the constant-bank ownership check
+  std::shared_ptr<vb::CTab> h_ctab;         // host image of the constant-bank tables (built on first use)
   // device side (lazy: nothing CUDA happens before the first compute call)
   bool uploaded = false;
   int device = -1;

@@ -60,6 +60,27 @@ VB_DI void bulk_s2g(void* dst_gmem, const void* src_smem, uint32_t bytes) {
 VB_DI void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 VB_DI void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 
+// Plan tables every substep walks, in the constant bank: the walks are warp-uniform, so these become uniform-datapath
+// constant loads (LDCU) with uniform address arithmetic instead of per-thread global loads.  One copy per device; the
+// host re-uploads it (stream-ordered) when a launch belongs to another plan (vmasb200.cu bind_const).  Worlds that do
+// not fit take the same kernel with the tables in global memory.
+constexpr int kCPairs = 1024, kCEnts = 160, kCSensors = 64;
+struct CTab {
+  DBroad broad[kCPairs];
+  DEnt ents[kCEnts];
+  int32_t dyn_list[kCEnts], trig_list[kCEnts], agent_ents[kMaxAgents];
+  DSensor sensors[kCSensors];
+};
+__constant__ CTab c_tab;
+
+// table accessors: CT = the walk tables are in the constant bank (c_tab), else in global memory behind kp
+template <bool CT> VB_DI const DEnt& T_ent(const KParams& kp, int e) { if (CT) return c_tab.ents[e]; else return kp.ents[e]; }
+template <bool CT> VB_DI const DBroad& T_broad(const KParams& kp, int p) { if (CT) return c_tab.broad[p]; else return kp.broad[p]; }
+template <bool CT> VB_DI const DSensor& T_sensor(const KParams& kp, int k) { if (CT) return c_tab.sensors[k]; else return kp.sensors[k]; }
+template <bool CT> VB_DI int T_dyn(const KParams& kp, int d) { if (CT) return c_tab.dyn_list[d]; else return kp.dyn_list[d]; }
+template <bool CT> VB_DI int T_trig(const KParams& kp, int r) { if (CT) return c_tab.trig_list[r]; else return kp.trig_list[r]; }
+template <bool CT> VB_DI int T_agent(const KParams& kp, int a) { if (CT) return c_tab.agent_ents[a]; else return kp.agent_ents[a]; }
+
 // ---------------------------------------------------------------------------------------- per-env view of the tile
 struct Env {
   float* env;   // &envS[column]: row r of this env's dyn / stat state at env[r * TE]
@@ -129,10 +150,11 @@ VB_DI void begin_forces(const KParams& kp, const DEnt* __restrict__ en, const En
 
 // One work item (joint constraint or candidate pair): force on a (the force on b is its exact negation) and the
 // two torques.  `type` is warp-uniform, so the switch does not diverge.
+template <bool CT>
 VB_DI void eval_item(const KParams& kp, const DItem* __restrict__ it, const Env& E, V2& fa, float& ta, float& tb) {
   const int type = it->type;
-  const DEnt* __restrict__ ea = kp.ents + it->a;
-  const DEnt* __restrict__ eb = kp.ents + it->b;
+  const DEnt* __restrict__ ea = &T_ent<CT>(kp, it->a);
+  const DEnt* __restrict__ eb = &T_ent<CT>(kp, it->b);
   const V2 pa = pos_at(E, ea->pos_row), pb = pos_at(E, eb->pos_row);
   const float Kc = kp.Kc, k = kp.margin;
   ta = 0.f; tb = 0.f;
@@ -258,6 +280,7 @@ VB_DI void integrate(const KParams& kp, const DEnt* __restrict__ en, const Env& 
 
 // One LIDAR ray (sensors.py:115-118 -> core.py:1661-1785) of env view E: min over the sensor's targets within reach
 // (the sensor's survival mask words are in the env's lmask rows; an unreachable target would have given max_range).
+template <bool CT>
 VB_DI float cast_one_ray(const KParams& kp, const DSensor* __restrict__ sn, const Env& E, V2 o, float ang) {
   const float max_range = sn->max_range;
   float best = max_range;
@@ -269,7 +292,7 @@ VB_DI float cast_one_ray(const KParams& kp, const DSensor* __restrict__ sn, cons
     while (m) {
       const int t = __ffs(m) - 1;
       m &= m - 1;
-      const DEnt* __restrict__ en = kp.ents + __ldg(kp.targets + tb + t);
+      const DEnt* __restrict__ en = &T_ent<CT>(kp, __ldg(kp.targets + tb + t));
       V2 p = pos_at(E, en->pos_row);
       float d;
       if (en->shape == VMASB200_SPHERE) {

@@ -3,6 +3,8 @@
 #include <algorithm>
 #include <cstdio>
 #include <cstring>
+#include <memory>
+#include <mutex>
 #include <new>
 
 #include "kernels.cuh"
@@ -61,7 +63,8 @@ int upload_plan(vmasb200_plan* pl) {
   VB_CUDA(cudaMalloc(&pl->d_bits, nbits));
   VB_CUDA(cudaMemset(pl->d_bits, 0, nbits));
   pl->smem_bytes = smem_map(kp).total_bytes;
-  VB_CUDA(cudaFuncSetAttribute(step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
+  VB_CUDA(cudaFuncSetAttribute(step_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
+  VB_CUDA(cudaFuncSetAttribute(step_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
   pl->uploaded = true;
   return VMASB200_OK;
 }
@@ -80,6 +83,44 @@ static int check_io(const vmasb200_plan* pl, const vmasb200_step_io* io) {
   if (mis(io->dyn_in) || mis(io->dyn_out) || mis(io->stat) || mis(io->act_out) || mis(io->lidar_out)) {
     set_error("step: SoA buffers must be 16-byte aligned (TMA bulk copies)"); return VMASB200_ERR_INVALID;
   }
+  return VMASB200_OK;
+}
+
+// The constant-bank copy of the walk tables (kernels.cuh CTab): one per device, owned by the plan that launched last.
+struct ConstOwner {
+  const vmasb200_plan* plan = nullptr;
+  uint64_t serial = 0;
+  cudaEvent_t last_use = nullptr;  // recorded after every launch that reads the tables
+};
+static ConstOwner g_const[64];
+static std::mutex g_const_mu;
+static uint64_t g_plan_serial = 0;
+
+static int bind_const(vmasb200_plan* pl, cudaStream_t st, bool* ct) {
+  const KParams& kp = pl->kp;
+  *ct = kp.P <= kCPairs && kp.E <= kCEnts && kp.n_sensors <= kCSensors && pl->device >= 0 && pl->device < 64;
+  if (!*ct) return VMASB200_OK;
+  std::lock_guard<std::mutex> lock(g_const_mu);
+  ConstOwner& o = g_const[pl->device];
+  if (!o.last_use) VB_CUDA(cudaEventCreateWithFlags(&o.last_use, cudaEventDisableTiming));
+  if (pl->serial == 0) pl->serial = ++g_plan_serial;
+  if (o.plan == pl && o.serial == pl->serial) return VMASB200_OK;
+  // another plan's launches may still be reading the tables: order the upload after them
+  VB_CUDA(cudaStreamWaitEvent(st, o.last_use, 0));
+  if (!pl->h_ctab) {
+    pl->h_ctab.reset(new CTab());
+    CTab& t = *pl->h_ctab;
+    std::memset(&t, 0, sizeof(t));
+    std::copy(pl->broad.begin(), pl->broad.end(), t.broad);
+    std::copy(pl->ents.begin(), pl->ents.end(), t.ents);
+    std::copy(pl->dyn_list.begin(), pl->dyn_list.end(), t.dyn_list);
+    std::copy(pl->trig_list.begin(), pl->trig_list.end(), t.trig_list);
+    std::copy(pl->agent_entities.begin(), pl->agent_entities.end(), t.agent_ents);
+    std::copy(pl->sensors.begin(), pl->sensors.end(), t.sensors);
+  }
+  VB_CUDA(cudaMemcpyToSymbolAsync(c_tab, pl->h_ctab.get(), sizeof(CTab), 0, cudaMemcpyHostToDevice, st));
+  VB_CUDA(cudaEventRecord(o.last_use, st));
+  o.plan = pl; o.serial = pl->serial;
   return VMASB200_OK;
 }
 
@@ -107,6 +148,9 @@ static int launch_step(vmasb200_plan* pl, const vmasb200_step_io* io, long long 
   sa.counters = reinterpret_cast<int*>(flags + 4 * bw);
   const unsigned grid = (unsigned)((env_end - env_begin + kp.TE - 1) / kp.TE);
   const unsigned block = (unsigned)kp.NT;
+  bool ct = false;
+  int rc_ct = bind_const(pl, st, &ct);
+  if (rc_ct) return rc_ct;
   if (io->exact) {
     // exact path: the batch-wide World.collides verdicts are reduced before every substep (core.py:2796-2800)
     if (nw) VB_CUDA(cudaMemsetAsync(flags, 0, nw * sizeof(uint32_t), st));
@@ -117,7 +161,8 @@ static int launch_step(vmasb200_plan* pl, const vmasb200_step_io* io, long long 
       }
       sa.s_begin = s; sa.s_end = s + 1; sa.flags_in = flags;
       sa.do_lidar = (s == kp.S - 1);
-      step_kernel<<<grid, block, pl->smem_bytes, st>>>(kp, aio, sa);
+      if (ct) step_kernel<true><<<grid, block, pl->smem_bytes, st>>>(kp, aio, sa);
+      else step_kernel<false><<<grid, block, pl->smem_bytes, st>>>(kp, aio, sa);
       sa.dyn_in = io->dyn_out;
     }
   } else {
@@ -131,8 +176,10 @@ static int launch_step(vmasb200_plan* pl, const vmasb200_step_io* io, long long 
     }
     sa.u_list = pl->d_ulist; sa.u_buf = pl->d_ubuf;
     sa.s_begin = 0; sa.s_end = kp.S; sa.flags_in = nullptr; sa.do_lidar = 1;
-    step_kernel<<<grid, block, pl->smem_bytes, st>>>(kp, aio, sa);
+    if (ct) step_kernel<true><<<grid, block, pl->smem_bytes, st>>>(kp, aio, sa);
+    else step_kernel<false><<<grid, block, pl->smem_bytes, st>>>(kp, aio, sa);
   }
+  if (ct) VB_CUDA(cudaEventRecord(g_const[pl->device].last_use, st));
   if (io->pair_active_out && nw) VB_CUDA(cudaMemcpyAsync(io->pair_active_out, flags, nw * sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
   VB_CUDA(cudaGetLastError());
   return VMASB200_OK;
@@ -160,6 +207,10 @@ int vmasb200_plan_create(const vmasb200_world_desc* desc, vmasb200_plan** out) {
 
 int vmasb200_plan_destroy(vmasb200_plan* pl) {
   if (!pl) return VMASB200_OK;
+  {
+    std::lock_guard<std::mutex> lock(g_const_mu);
+    for (ConstOwner& o : g_const) if (o.plan == pl) o.plan = nullptr;
+  }
   if (pl->uploaded) {
     cudaFree(pl->d_blob); cudaFree(pl->d_bits); cudaFree(pl->d_ulist); cudaFree(pl->d_ubuf);
     cudaFree(pl->d_dyn); cudaFree(pl->d_stat); cudaFree(pl->d_force); cudaFree(pl->d_torque); cudaFree(pl->d_act); cudaFree(pl->d_lidar);

@@ -1,0 +1,333 @@
+"""Drop-in for the two bound methods that make up the reference's physics hot path:
+
+* ``vmas.simulator.core.World.step``       (core.py:1971)  -> one fused CUDA launch (``vmasb200_step``)
+* ``vmas.simulator.core.World.cast_rays``  (core.py:1661)  -> ``vmasb200_cast_rays``; ``Lidar.measure``
+  (sensors.py:100) additionally returns the measurement the step's LIDAR epilogue already produced when nothing
+  touched the state in between.
+
+``enable(world_or_env)`` patches ONE world instance (and its Lidar sensors); ``make_env``, ``Environment.step``, the
+scenario hooks and the returned obs / reward / done / info tensors stay untouched.  Nothing from ``vmas`` is imported:
+the world is duck-typed, so the same code serves any fork that keeps the reference's attribute names.
+
+State ownership.  The kernel works on structure-of-arrays buffers ``[row][ld]`` (include/vmasb200.h).  After a step
+every ``entity.state.pos / vel / rot / ang_vel`` of a dynamic entity is bound to a strided VIEW of a freshly allocated
+output buffer (the reference also rebinds fresh tensors every step, core.py:2866-2907, so stale references a scenario
+kept stay valid), and agents whose action is clamped get ``state.force / torque`` bound to views of the clamped
+write-back (core.py:2019-2038).  Before a step each field is compared with the view it should be (data_ptr + strides);
+only fields a scenario or ``reset`` rebound are copied in.  In-place writes through the views land in the buffer directly.
+
+What is NOT done here, on purpose: no CPU fallback (a world that is not on a CUDA device is an error), and no autograd
+(if grad mode is on and a state / force tensor requires grad, the saved original ``World.step`` runs: the reference's
+torch path remains the gradient path).  ``world.forces_dict / torques_dict`` are not materialised (no scenario reads
+them).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import types
+from typing import Dict, List, Optional
+
+import numpy as np
+
+from . import _lib
+from .plan import StepPlan
+from .worlddesc import CStepIO, UnsupportedWorld, WorldDesc  # noqa: F401
+
+_FIELDS = ("pos", "vel", "rot", "ang_vel")
+
+
+def _same_view(t, v) -> bool:
+    return t is v or (t.data_ptr() == v.data_ptr() and t.shape == v.shape and t.stride() == v.stride()
+                      and t.dtype == v.dtype)
+
+
+class WorldBinding:
+    """Plan + device buffers of one enabled World."""
+
+    def __init__(self, world, exact: bool = False):
+        import torch
+
+        self.torch = torch
+        self.world = world
+        self.exact = exact
+        dev = torch.device(world.device)
+        if dev.type != "cuda":
+            raise _lib.VmasB200Error(
+                f"vmas-b200: world.device is {dev}; the CUDA step has no CPU fallback (create the env with device='cuda')")
+        self.device = dev
+        self.n = int(world.batch_dim)
+        self.ld = StepPlan.ld_for(self.n)
+        self.orig_step = world.step
+        self.orig_cast_rays = world.cast_rays
+        self.dirty = True
+        self.desc_json = None
+        self.plan: Optional[StepPlan] = None
+        self.lidar_valid = False
+        self.n_steps = 0
+        self.n_copies = 0
+
+    # ------------------------------------------------------------------ plan (re)build
+    def refresh(self):
+        """Re-extract the static description (entity table, collision filters, joints, sensors); rebuild the plan and
+        the buffers only when it changed (collision filters may depend on state set at reset: joint_passage.py:615-622)."""
+        torch = self.torch
+        desc = WorldDesc.from_world(self.world)
+        js = desc.to_json()
+        self.dirty = False
+        if js == self.desc_json:
+            return
+        self.desc_json = js
+        self.desc = desc
+        self.plan = pl = StepPlan(desc)
+        n, ld, dev = self.n, self.ld, self.device
+        self.ents = list(self.world.entities)
+        self.agents = [self.ents[i] for i in pl.agents]
+        self.dyn = torch.zeros(pl.dyn_rows, ld, device=dev)
+        self.stat = torch.zeros(max(pl.stat_rows, 1), ld, device=dev)
+        self.act = None
+        self.lid = None
+        self.dyn_ents = [(e, int(pl.dyn_slot[i])) for i, e in enumerate(self.ents) if pl.dyn_slot[i] >= 0]
+        self.stat_ents = [(e, int(pl.stat_slot[i])) for i, e in enumerate(self.ents) if pl.stat_slot[i] >= 0]
+        self.act_agents = [(e, int(pl.act_slot[i])) for i, e in enumerate(self.ents) if pl.act_slot[i] >= 0]
+        self.joint_rows = []
+        if len(pl.joint_slot) and (pl.joint_slot >= 0).any():
+            order = _joints_in_order(self.world, self.ents)
+            self.joint_rows = [(order[j], int(o)) for j, o in enumerate(pl.joint_slot) if o >= 0]
+        self.sensors = {}
+        for k, ld_ in enumerate(desc.lidars):
+            sensor = self.ents[ld_.entity].sensors[ld_.agent_sensor_index]
+            self.sensors[id(sensor)] = k
+        self._bind_static()
+        self._dyn_views = self._views_of(self.dyn)
+        self.lidar_valid = False
+        # reusable C structures
+        A = pl.A
+        self._io = io = CStepIO()
+        self._fp = (C.c_void_p * max(A, 1))()
+        self._tp = (C.c_void_p * max(A, 1))()
+        self._fs = (C.c_int64 * max(A, 1))()
+        self._ts = (C.c_int64 * max(A, 1))()
+        io.force_ptrs, io.force_strides = C.cast(self._fp, C.POINTER(C.c_void_p)), C.cast(self._fs, C.POINTER(C.c_int64))
+        io.torque_ptrs, io.torque_strides = C.cast(self._tp, C.POINTER(C.c_void_p)), C.cast(self._ts, C.POINTER(C.c_int64))
+        io.n_envs, io.ld, io.exact = n, ld, int(self.exact)
+
+    def _views_of(self, dyn):
+        n = self.n
+        out = []
+        for e, o in self.dyn_ents:
+            out.append((e, (dyn[o:o + 2, :n].t(), dyn[o + 2:o + 4, :n].t(), dyn[o + 4:o + 5, :n].t(),
+                            dyn[o + 5:o + 6, :n].t())))
+        return out
+
+    def _bind_static(self):
+        n = self.n
+        self._stat_views = [(e, (self.stat[o:o + 2, :n].t(), self.stat[o + 2:o + 3, :n].t())) for e, o in self.stat_ents]
+
+    # ------------------------------------------------------------------ state hand-over
+    def sync_in(self):
+        """Copies into the buffers every state field that is not (any more) the view the last step bound."""
+        for e, views in self._dyn_views:
+            st = e.state
+            for name, v in zip(_FIELDS, views):
+                t = getattr(st, name)
+                if not _same_view(t, v):
+                    v.copy_(t)
+                    setattr(st, "_" + name, v)
+                    self.n_copies += 1
+                    self.lidar_valid = False
+        for e, (vp, vr) in self._stat_views:
+            st = e.state
+            if not _same_view(st.pos, vp):
+                vp.copy_(st.pos)
+                st._pos = vp
+                self.n_copies += 1
+                self.lidar_valid = False
+            if not _same_view(st.rot, vr):
+                vr.copy_(st.rot)
+                st._rot = vr
+                self.n_copies += 1
+                self.lidar_valid = False
+        for joint, row in self.joint_rows:
+            fr = joint.fixed_rotation
+            self.stat[row, :self.n].copy_(fr.reshape(-1).expand(self.n) if hasattr(fr, "reshape") else
+                                          self.torch.full((self.n,), float(fr), device=self.device))
+
+    def _needs_grad(self) -> bool:
+        if not self.torch.is_grad_enabled():
+            return False
+        for e in self.ents:
+            for name in _FIELDS:
+                t = getattr(e.state, name)
+                if t is not None and t.requires_grad:
+                    return True
+        for a in self.agents:
+            for t in (a.state.force, a.state.torque):
+                if t is not None and t.requires_grad:
+                    return True
+        return False
+
+    # ------------------------------------------------------------------ World.step
+    def step(self):
+        world, torch = self.world, self.torch
+        if self.dirty or len(world.entities) != len(getattr(self, "ents", ())):
+            self.refresh()
+        if self._needs_grad():
+            self.lidar_valid = False
+            return self.orig_step()  # the reference's torch path is the gradient path
+        pl, n, ld = self.plan, self.n, self.ld
+        world.entity_index_map = {e: i for i, e in enumerate(world.entities)}  # core.py:1972
+        self.sync_in()
+        io = self._io
+        keep = []
+        for a, ag in enumerate(self.agents):
+            f, t = ag.state.force, ag.state.torque
+            if f is not None:
+                if f.dtype != torch.float32 or f.stride(1) != 1:
+                    f = f.to(torch.float32).contiguous()
+                keep.append(f)
+                self._fp[a], self._fs[a] = f.data_ptr(), f.stride(0)
+            else:
+                self._fp[a], self._fs[a] = None, 0
+            if t is not None:
+                if t.dtype != torch.float32:
+                    t = t.to(torch.float32)
+                keep.append(t)
+                self._tp[a], self._ts[a] = t.data_ptr(), t.stride(0)
+            else:
+                self._tp[a], self._ts[a] = None, 0
+        # fresh output buffers every step: the reference rebinds new tensors too (core.py:2866-2907)
+        dyn_out = torch.empty_like(self.dyn)
+        act = torch.empty(pl.act_rows, ld, device=self.device) if pl.act_rows else None
+        lid = torch.empty(pl.lidar_rows, ld, device=self.device) if pl.lidar_rows else None
+        io.dyn_in, io.dyn_out = self.dyn.data_ptr(), dyn_out.data_ptr()
+        io.stat = self.stat.data_ptr() if pl.stat_rows else None
+        io.act_out = act.data_ptr() if act is not None else None
+        io.lidar_out = lid.data_ptr() if lid is not None else None
+        io.pair_active_out = None
+        io.stream = torch.cuda.current_stream(self.device).cuda_stream
+        pl.step_io(io)
+        # bind the results
+        self.dyn = dyn_out
+        self._dyn_views = self._views_of(dyn_out)
+        for e, views in self._dyn_views:
+            st = e.state
+            st._pos, st._vel, st._rot, st._ang_vel = views
+        if act is not None:
+            self.act = act
+            for ag, o in self.act_agents:
+                ag.state._force = act[o:o + 2, :n].t()
+                ag.state._torque = act[o + 2:o + 3, :n].t()
+        if lid is not None:
+            self.lid = lid
+            self.lidar_valid = True
+            self._versions = (dyn_out._version, self.stat._version)
+        if world._dim_c > 0:  # core.py:2909-2912
+            for ag in world._agents:
+                if not ag.silent:
+                    ag.state.c = ag.action.c
+        self.n_steps += 1
+
+    # ------------------------------------------------------------------ World.cast_rays / Lidar.measure
+    def _state_untouched(self) -> bool:
+        if not self.lidar_valid or self._versions != (self.dyn._version, self.stat._version):
+            return False
+        for e, views in self._dyn_views:
+            st = e.state
+            if st._pos is not views[0] or st._rot is not views[2]:
+                return False
+        for e, (vp, vr) in self._stat_views:
+            if e.state._pos is not vp or e.state._rot is not vr:
+                return False
+        return True
+
+    def measure(self, sensor, orig_measure, vectorized: bool = True):
+        k = self.sensors.get(id(sensor))
+        if vectorized and k is not None and not self.dirty and self._state_untouched():
+            o, r = int(self.plan.lidar_slot[k]), len(self.desc.lidars[k].angles)
+            m = self.lid[o:o + r, :self.n].t()
+            sensor._last_measurement = m
+            return m
+        return orig_measure(vectorized)
+
+    def cast_rays(self, entity, angles, max_range: float, entity_filter=lambda _: False):
+        torch = self.torch
+        if self.dirty or self.plan is None:
+            self.refresh()
+        if self.torch.is_grad_enabled() and angles.requires_grad:
+            return self.orig_cast_rays(entity, angles, max_range, entity_filter)
+        ents = self.ents
+        index = {id(e): i for i, e in enumerate(ents)}
+        targets = []
+        for e in ents:
+            if e is entity or not entity_filter(e):
+                continue
+            assert e.collides(entity) and entity.collides(e), "Rays are only casted among collidables"  # core.py:1680
+            targets.append(index[id(e)])
+        pl = self.plan
+        me = index[id(entity)]
+        if any(pl.dyn_slot[i] < 0 and pl.stat_slot[i] < 0 for i in targets + [me]) or len(targets) > 64:
+            return self.orig_cast_rays(entity, angles, max_range, entity_filter)  # entity the step never reads
+        self.sync_in()
+        ang = angles if (angles.dtype == torch.float32 and angles.stride(1) == 1) else angles.to(torch.float32).contiguous()
+        out = torch.empty(ang.shape[0], ang.shape[1], device=self.device)
+        pl.cast_rays(self.dyn, self.stat, self.ld, me, ang, float(max_range), np.asarray(targets, np.int32), out,
+                     torch.cuda.current_stream(self.device).cuda_stream)
+        return out
+
+
+def _joints_in_order(world, ents):
+    """JointConstraints in the order _apply_vectorized_enviornment_force meets them (core.py:2111-2121)."""
+    out = []
+    wj = getattr(world, "_joints", {})
+    for a in range(len(ents)):
+        for b in range(a + 1, len(ents)):
+            j = wj.get(frozenset({ents[a].name, ents[b].name}), None)
+            if j is not None:
+                out.append(j)
+    return out
+
+
+def enable(world_or_env, exact: bool = False) -> WorldBinding:
+    """Routes ``world.step`` / ``world.cast_rays`` / its Lidars' ``measure`` of ONE world through libvmasb200.
+    ``exact=True`` takes the per-substep exact path instead of the verified speculative single launch."""
+    world = getattr(world_or_env, "world", world_or_env)
+    if getattr(world, "_vmasb200", None) is not None:
+        return world._vmasb200
+    _lib.lib()  # fail loudly when the extension is missing
+    b = WorldBinding(world, exact=exact)
+    b.refresh()
+    world._vmasb200 = b
+    world.step = types.MethodType(lambda self: b.step(), world)
+    world.cast_rays = types.MethodType(
+        lambda self, entity, angles, max_range, entity_filter=lambda _: False: b.cast_rays(entity, angles, max_range, entity_filter),
+        world)
+    orig_reset = world.reset
+
+    def reset(self, env_index=None):
+        b.dirty = True  # collision filters / joint rotations may depend on what reset sets
+        return orig_reset(env_index)
+
+    world.reset = types.MethodType(reset, world)
+    b._orig_reset = orig_reset
+    b._orig_measures = []
+    for ag in world.agents:
+        for sensor in getattr(ag, "sensors", None) or []:
+            if hasattr(sensor, "measure") and hasattr(sensor, "_angles"):
+                om = sensor.measure
+                b._orig_measures.append((sensor, om))
+                sensor.measure = (lambda s, o: (lambda vectorized=True: b.measure(s, o, vectorized)))(sensor, om)
+    return b
+
+
+def disable(world_or_env) -> None:
+    world = getattr(world_or_env, "world", world_or_env)
+    b = getattr(world, "_vmasb200", None)
+    if b is None:
+        return
+    for name in ("step", "cast_rays", "reset"):
+        if name in world.__dict__:
+            del world.__dict__[name]
+    for sensor, _ in b._orig_measures:
+        if "measure" in sensor.__dict__:
+            del sensor.__dict__["measure"]
+    world._vmasb200 = None
