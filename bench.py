@@ -28,7 +28,10 @@ def parse():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=10)
-    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference", "reference-cuda", "dropin"],
+                    help="b200: the CUDA step through the C ABI (the driver's arm); reference: the reference's CPU path; "
+                         "reference-cuda / dropin: the reference Environment on this GPU with its own torch World.step, "
+                         "or with vectorizedmultiagentsimulator_b200.dropin enabled (reported comparison, needs oracle/_ref)")
     ap.add_argument("--scenario", default="navigation")
     ap.add_argument("--num-envs", type=int, default=32768, help="environments PER GPU (weak scaling)")
     ap.add_argument("--envs-per-cta", type=int, default=0, help="CTA tile override (0 = plan default)")
@@ -328,10 +331,75 @@ def run_e2e(plan, wl, n, K, world, dev):
             "api": "vmasb200_step_host (C ABI, pinned host SoA buffers, chunked over 4 streams)"}
 
 
+def run_env_cuda(args, rank):
+    """The reference's Environment on cuda:0, stepped with pre-generated random actions; World.step is timed on its own
+    (CUDA events around the bound method) and Environment.step as a whole.  --impl dropin patches the world first."""
+    if rank != 0:
+        return
+    import torch
+
+    ref_dir = os.path.join(ROOT, "oracle", "_ref")
+    if not os.path.isdir(os.path.join(ref_dir, "vmas")):
+        print(json.dumps({"impl": args.impl, "unavailable": "oracle/_ref (reference install) not present"}))
+        return
+    sys.path.insert(0, ref_dir)
+    sys.path.insert(0, os.path.join(ROOT, "oracle", "gym_stub"))
+    import vmas
+
+    from vectorizedmultiagentsimulator_b200.workload import Workload
+
+    wl = Workload(args.scenario, 1, seed=0)
+    n, K, W = args.num_envs, args.steps, max(args.warmup, 3)
+    env = vmas.make_env(wl.meta["scenario"], num_envs=n, device="cuda", seed=0, continuous_actions=True, **wl.meta["kwargs"])
+    world = env.world
+    if world._substeps != wl.desc.substeps:
+        world._substeps, world._sub_dt = wl.desc.substeps, world._dt / wl.desc.substeps
+    if args.impl == "dropin":
+        from vectorizedmultiagentsimulator_b200 import dropin
+
+        dropin.enable(env)
+    torch.manual_seed(1234)
+    acts = [[torch.rand(n, a.action_size, device="cuda") * 2 * a.u_range - a.u_range for a in env.agents] for _ in range(8)]
+    inner = world.step
+    ev = []
+
+    def timed_step():
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        inner()
+        e1.record()
+        ev.append((e0, e1))
+
+    world.step = timed_step
+    for i in range(W):
+        env.step([a.clone() for a in acts[i % 8]])
+    torch.cuda.synchronize()
+    ev.clear()
+    t0 = time.perf_counter()
+    for i in range(K):
+        env.step([a.clone() for a in acts[i % 8]])
+    torch.cuda.synchronize()
+    el = time.perf_counter() - t0
+    ws_gpu = sum(a.elapsed_time(b) for a, b in ev) / K
+    # host-side cost of World.step alone (launch-bound torch code is limited by it, not by the GPU)
+    t1 = time.perf_counter()
+    for i in range(K):
+        inner()
+    torch.cuda.synchronize()
+    ws_wall = (time.perf_counter() - t1) / K * 1e3
+    line = {"impl": args.impl, "metric": METRIC, "unit": "env-steps/s", "n_gpus": 1, "steps": K, "warmup": W,
+            "config": {"workload": f"{args.scenario} num_envs={n}, reference Environment on cuda:0 (torch {torch.__version__})"},
+            "world_step_ms_gpu_events": ws_gpu, "world_step_ms_wall": ws_wall, "env_step_ms_wall": el / K * 1e3,
+            "world_step_env_steps_per_s": n / (ws_wall * 1e-3), "value": n * K / el, "data": "synthetic"}
+    print(json.dumps(line), flush=True)
+
+
 def main():
     args = parse()
     rank, local_rank, world = dist_env()
-    if args.impl == "reference":
+    if args.impl in ("reference-cuda", "dropin"):
+        run_env_cuda(args, rank)
+    elif args.impl == "reference":
         run_reference(args, rank, world)
     else:
         run_b200(args, rank, local_rank, world)
