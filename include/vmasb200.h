@@ -139,7 +139,7 @@ typedef struct vmasb200_world_desc {
   float x_semidim, y_semidim;
   float collision_force, joint_force, torque_constraint_force, contact_margin;
   float gravity[2];
-  /* Kernel shape override: environments (= threads) per CTA, a multiple of 32 up to 256; 0 = let the plan choose. */
+  /* Kernel shape override: environments (= threads) per CTA, 32, 64 or 128; 0 = let the plan choose. */
   int32_t envs_per_cta;
 } vmasb200_world_desc;
 

@@ -62,11 +62,11 @@ struct Tile {
   int *queue, *rayq, *qcount;  // qcount[0]: sensor queue length, qcount[1]: ray queue length
   int* wtask;                  // [TE/32][kWarpTasks]
   float4* wres;                // [TE/32][kWarpTasks]
-  int TE;
 };
-VB_DI Env env_view(const Tile& t, int col) {
-  Env E;
-  E.env = t.envS + col; E.work = t.workS + col; E.TE = t.TE;
+template <int TE>
+VB_DI EnvT<TE> env_view(const Tile& t, int col) {
+  EnvT<TE> E;
+  E.env = t.envS + col; E.work = t.workS + col;
   return E;
 }
 
@@ -75,7 +75,8 @@ VB_DI void or_global(uint32_t* word, uint32_t v) {
 }
 
 // agent.state.force / torque of env `env` into the env's frc rows
-VB_DI void load_forces(const KParams& kp, const AgentIO& aio, const Env& E, long long env) {
+template <class EV>
+VB_DI void load_forces(const KParams& kp, const AgentIO& aio, const EV& E, long long env) {
   for (int a = 0; a < kp.A; ++a) {
     float fx = 0.f, fy = 0.f, tq = 0.f;
     const float* fp = aio.force[a];
@@ -90,8 +91,8 @@ VB_DI void load_forces(const KParams& kp, const AgentIO& aio, const Env& E, long
 // Substeps [s_begin, s_end) of one env (a thread-private column of the tile).  flags: batch-wide verdicts to obey
 // (smem or global), or NULL = speculative (every pair considered; verdict / thin bits OR-ed into sa.any_exact /
 // any_spec / thin).  All 32 lanes of a warp call this together (warp reductions).  Returns the env's taint.
-template <bool CT>
-VB_DI bool run_substeps(const KParams& kp, const StepArgs& sa, const Tile& t, const Env& E, bool ok, int s_begin,
+template <bool CT, class EV>
+VB_DI bool run_substeps(const KParams& kp, const StepArgs& sa, const Tile& t, const EV& E, bool ok, int s_begin,
                         int s_end, const uint32_t* flags) {
   // prologue: cos/sin cache of every entity that needs it, first force accumulators
   for (int r = 0; r < kp.n_trig; ++r) {
@@ -120,24 +121,27 @@ VB_DI bool run_substeps(const KParams& kp, const StepArgs& sa, const Tile& t, co
     for (int base = 0; base < kp.P; base += 32) {
       const int n = min(32, kp.P - base);
       uint32_t bpw = 0u, sv = 0u;
-#pragma unroll 4
-      for (int k = 0; k < n; ++k) {
-        const DBroad& bq = T_broad<CT>(kp, base + k);
-        const int ra = bq.pa_row, rb = bq.pb_row, rt = bq.trig_row;
-        const float dx = ER(E, ra) - ER(E, rb), dy = ER(E, ra + 1) - ER(E, rb + 1);
-        const float d2 = fmaf(dy, dy, dx * dx);
-        const bool bp = d2 <= bq.t2_bp;  // == (norm(pa - pb) <= Rc_a + Rc_b), core.py:2796-2800
-        bool surv;
-        if (rt < 0) {
-          surv = !(d2 > bq.t2_cull);
-        } else {  // sphere centre in the line / box frame (a conservative cull: fused arithmetic is fine here)
-          const float c = WR(E, rt), sn = WR(E, rt + 1);
-          const float lx = fmaf(dx, c, dy * sn), ly = fmaf(dx, sn, -(dy * c));
-          surv = !(fabsf(lx) > bq.hx) && !(fabsf(ly) > bq.hy);
+      // fully unrolled: table offsets and bit positions are immediates.  The table is padded to a multiple of 32 rows
+      // with rows that never pass (plan.cpp); the mask below only matters for NaN state.
+#pragma unroll
+      for (int k = 0; k < 32; ++k) {
+        {
+          const DBroad& bq = T_broad<CT>(kp, base + k);
+          const int ra = bq.pa_row, rb = bq.pb_row, rt = bq.trig_row;
+          const float dx = ER(E, ra) - ER(E, rb), dy = ER(E, ra + 1) - ER(E, rb + 1);
+          const float d2 = fmaf(dy, dy, dx * dx);
+          if (d2 <= bq.t2_bp) bpw |= 1u << k;  // == (norm(pa - pb) <= Rc_a + Rc_b), core.py:2796-2800
+          if (rt < 0) {
+            if (!(d2 > bq.t2_cull)) sv |= 1u << k;
+          } else {  // sphere centre in the line / box frame (a conservative cull: fused arithmetic is fine here)
+            const float c = WR(E, rt), sn = WR(E, rt + 1);
+            const float lx = fmaf(dx, c, dy * sn), ly = fmaf(dx, sn, -(dy * c));
+            if (!(fabsf(lx) > bq.hx) && !(fabsf(ly) > bq.hy)) sv |= 1u << k;
+          }
         }
-        bpw |= (bp ? 1u : 0u) << k;
-        sv |= (surv ? 1u : 0u) << k;
       }
+      const uint32_t valid = n == 32 ? 0xffffffffu : (1u << n) - 1u;
+      bpw &= valid; sv &= valid;
       const int w = s * kp.pair_words + (base >> 5);
       if (flags) {
         sv &= flags[w];
@@ -177,8 +181,8 @@ VB_DI bool run_substeps(const KParams& kp, const StepArgs& sa, const Tile& t, co
         for (uint32_t q = lane; q < nt; q += 32) {
           const int task = wtask[q];
           const int src = task >> 8;
-          Env E2;
-          E2.env = E.env + (src - lane); E2.work = E.work + (src - lane); E2.TE = E.TE;
+          EV E2;
+          E2.env = E.env + (src - lane); E2.work = E.work + (src - lane);
           V2 fa; float ta, tb;
           eval_item<CT>(kp, kp.items + kp.J + base + (task & 31), E2, fa, ta, tb);
           wres[q] = make_float4(fa.x, fa.y, ta, tb);
@@ -222,9 +226,9 @@ VB_DI bool run_substeps(const KParams& kp, const StepArgs& sa, const Tile& t, co
 //      that covers the approximation: a target farther than Rc from the ray's line, or behind the origin, cannot be
 //      hit (core.py:1467-1489 sphere, :1344-1371 box, :1598-1625 line); rays that may hit go to the ray queue;
 //   3  thread per queued ray: the reference's exact arithmetic (sincosf of the fp32 angle sum, sensors.py:117).
-template <bool CT>
+template <bool CT, int TE>
 VB_DI void lidar_epilogue(const KParams& kp, const Tile& t, int n_cols) {
-  const int tid = threadIdx.x, TE = t.TE, nthr = blockDim.x;
+  const int tid = threadIdx.x, nthr = blockDim.x;
   if (tid < 2) t.qcount[tid] = 0;
   for (int k = 0; k < kp.n_sensors; ++k) {  // every ray starts at max_range
     const DSensor* sn = &T_sensor<CT>(kp, k);
@@ -233,7 +237,7 @@ VB_DI void lidar_epilogue(const KParams& kp, const Tile& t, int n_cols) {
   }
   __syncthreads();
   if (tid < TE) {
-    const Env E = env_view(t, tid);
+    const EnvT<TE> E = env_view<TE>(t, tid);
     for (int k = 0; k < kp.n_sensors; ++k) {
       const DSensor* sn = &T_sensor<CT>(kp, k);
       const DEnt* se = &T_ent<CT>(kp, sn->entity);
@@ -265,7 +269,7 @@ VB_DI void lidar_epilogue(const KParams& kp, const Tile& t, int n_cols) {
     const int item = t.queue[qi], k = item >> 16, col = item & 0xffff;
     const DSensor* sn = &T_sensor<CT>(kp, k);
     if (r >= sn->n_rays) continue;
-    const Env E = env_view(t, col);
+    const EnvT<TE> E = env_view<TE>(t, col);
     const DEnt* se = &T_ent<CT>(kp, sn->entity);
     const V2 o = pos_at(E, se->pos_row);
     const float c0 = WR(E, kp.row_strig + 2 * k), s0 = WR(E, kp.row_strig + 2 * k + 1);
@@ -294,7 +298,7 @@ VB_DI void lidar_epilogue(const KParams& kp, const Tile& t, int n_cols) {
   for (int qi = tid; qi < nq; qi += nthr) {
     const int item = t.rayq[qi], col = item & 0xff, k = (item >> 8) & 0xff, r = item >> 16;
     const DSensor* sn = &T_sensor<CT>(kp, k);
-    const Env E = env_view(t, col);
+    const EnvT<TE> E = env_view<TE>(t, col);
     const DEnt* se = &T_ent<CT>(kp, sn->entity);
     const float ang = __ldg(kp.ray_angles + sn->out_off + r) + ER(E, se->rot_row);  // sensors.py:117
     t.lidS[(sn->out_off + r) * TE + col] = cast_one_ray<CT>(kp, sn, E, pos_at(E, se->pos_row), ang);
@@ -305,12 +309,12 @@ VB_DI void lidar_epilogue(const KParams& kp, const Tile& t, int n_cols) {
 // Re-simulation of the tainted envs by the last CTA (rare path; see the header comment).  flagS (smem, [S][pair_words])
 // starts as any_exact and ends as the reference's verdicts.  u_buf holds the evolving state of tainted env `idx` as
 // dyn_rows consecutive floats; each thread works on one tainted env at a time in its own tile column.
-template <bool CT>
+template <bool CT, int TE>
 __device__ __noinline__ void repair_tainted(const KParams& kp, const AgentIO& aio, const StepArgs& sa, const Tile& t,
                                             uint32_t* flagS, int nu) {
-  const int tid = threadIdx.x, nthr = blockDim.x, TE = t.TE;
+  const int tid = threadIdx.x, nthr = blockDim.x;
   const int nw = kp.S * kp.pair_words;
-  const Env E = env_view(t, tid);
+  const EnvT<TE> E = env_view<TE>(t, tid);
   for (int w = tid; w < nw; w += nthr) flagS[w] = __ldcg(sa.any_exact + w);
   __syncthreads();
   for (int s = 0; s <= kp.S; ++s) {  // s == S: LIDAR + write-back pass
@@ -350,7 +354,7 @@ __device__ __noinline__ void repair_tainted(const KParams& kp, const AgentIO& ai
       if (!last) {
         if (ok) for (int r = 0; r < kp.dyn_rows; ++r) sa.u_buf[(size_t)idx * kp.dyn_rows + r] = ER(E, r);
       } else {
-        if (sa.lidar_out && kp.n_rays) lidar_epilogue<CT>(kp, t, min(TE, nu - base));
+        if (sa.lidar_out && kp.n_rays) lidar_epilogue<CT, TE>(kp, t, min(TE, nu - base));
         if (ok) {
           for (int r = 0; r < kp.dyn_rows; ++r) sa.dyn_out[(size_t)r * sa.ld + env] = ER(E, r);
           if (sa.lidar_out)
@@ -362,20 +366,18 @@ __device__ __noinline__ void repair_tainted(const KParams& kp, const AgentIO& ai
   }
 }
 
-template <bool CT>
+template <bool CT, int TE>
 __global__ void __launch_bounds__(256) step_kernel(const __grid_constant__ KParams kp, const __grid_constant__ AgentIO aio,
                                                    const __grid_constant__ StepArgs sa) {
   extern __shared__ __align__(16) float smem[];
   __shared__ int s_last;
   const SmemMap m = smem_map(kp);
   uint64_t* bar = reinterpret_cast<uint64_t*>(smem + m.bar);
-  const int TE = kp.TE;
   Tile t;
   t.envS = smem + m.env; t.workS = smem + m.work; t.lidS = smem + m.lid;
   t.queue = reinterpret_cast<int*>(smem + m.queue); t.rayq = reinterpret_cast<int*>(smem + m.rayq);
   t.qcount = reinterpret_cast<int*>(smem + m.bar) + 2;
   t.wtask = reinterpret_cast<int*>(smem + m.wtask); t.wres = reinterpret_cast<float4*>(smem + m.wres);
-  t.TE = TE;
   uint32_t* flagS = reinterpret_cast<uint32_t*>(smem + m.flags);
   const int nw = kp.S * kp.pair_words;
 
@@ -406,7 +408,7 @@ __global__ void __launch_bounds__(256) step_kernel(const __grid_constant__ KPara
     }
   }
   // threads [0, TE) own one env each; helper warps (tid >= TE, LIDAR worlds only) join for the LIDAR epilogue
-  const Env E = env_view(t, tid < TE ? tid : 0);
+  const EnvT<TE> E = env_view<TE>(t, tid < TE ? tid : 0);
   bool tainted = false;
   if (tid < TE) {
     if (ok) load_forces(kp, aio, E, env0 + tid);
@@ -414,7 +416,7 @@ __global__ void __launch_bounds__(256) step_kernel(const __grid_constant__ KPara
     tainted = run_substeps<CT>(kp, sa, t, E, ok, sa.s_begin, sa.s_end, sa.flags_in);
   }
   const bool lidar = sa.do_lidar && sa.lidar_out && kp.n_rays;
-  if (lidar) lidar_epilogue<CT>(kp, t, n_valid);
+  if (lidar) lidar_epilogue<CT, TE>(kp, t, n_valid);
 
   if (spec && tainted && ok) {  // keep the INPUT state of a tainted env (dyn_in is intact until our own store)
     const int idx = atomicAdd(sa.counters + 1, 1);
@@ -451,7 +453,7 @@ __global__ void __launch_bounds__(256) step_kernel(const __grid_constant__ KPara
   bad = __syncthreads_or(bad);
   const int nu = *reinterpret_cast<volatile int*>(sa.counters + 1);
   if (bad) {
-    repair_tainted<CT>(kp, aio, sa, t, flagS, nu);
+    repair_tainted<CT, TE>(kp, aio, sa, t, flagS, nu);
     for (int w = tid; w < nw; w += blockDim.x) sa.flags_out[w] = flagS[w];
   } else {
     for (int w = tid; w < nw; w += blockDim.x) sa.flags_out[w] = __ldcg(sa.any_exact + w) | __ldcg(sa.any_spec + w);

@@ -253,6 +253,11 @@ int build_plan(const vmasb200_world_desc* d, vmasb200_plan* pl) {
     }
     pl->broad.push_back(b);
   }
+  while (pl->broad.size() % 32) {  // padding rows of the unrolled broad phase: d2 <= -1 never holds
+    DBroad b{};
+    b.trig_row = -1; b.t2_bp = -1.f; b.t2_cull = -1.f;
+    pl->broad.push_back(b);
+  }
 
   // ---- kernel shape: one thread per env, TE envs per CTA; keep >= 2 CTAs per SM resident when the world allows it
   // per env: staged rows, work rows, lidar rows + ray queue (one int per ray), sensor queue; per warp: 32 narrow-phase
@@ -264,7 +269,7 @@ int build_plan(const vmasb200_world_desc* d, vmasb200_plan* pl) {
     TE = 64;
     while (TE > 32 && fixed + TE * per_env > 100 * 1024) TE -= 32;
   }
-  if (TE < 32 || TE > 256 || TE % 32) { set_error("envs_per_cta must be a multiple of 32 in [32, 256]"); return VMASB200_ERR_INVALID; }
+  if (TE != 32 && TE != 64 && TE != 128) { set_error("envs_per_cta must be 32, 64 or 128"); return VMASB200_ERR_INVALID; }
   if (fixed + TE * per_env > 226 * 1024) { set_error("world too large for one CTA's shared memory"); return VMASB200_ERR_UNSUPPORTED; }
   kp.TE = TE;
   kp.NT = kp.n_rays ? std::min(256, 2 * TE) : TE;  // helper warps for the LIDAR epilogue (register file: 4 CTAs / SM)

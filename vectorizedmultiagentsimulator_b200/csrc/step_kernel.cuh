@@ -82,16 +82,19 @@ template <bool CT> VB_DI int T_trig(const KParams& kp, int r) { if (CT) return c
 template <bool CT> VB_DI int T_agent(const KParams& kp, int a) { if (CT) return c_tab.agent_ents[a]; else return kp.agent_ents[a]; }
 
 // ---------------------------------------------------------------------------------------- per-env view of the tile
-struct Env {
+// TE (envs per CTA = floats per smem row) is a compile-time constant: row addressing is one shift, row + 1 an immediate
+template <int TE_>
+struct EnvT {
+  static constexpr int TE = TE_;
   float* env;   // &envS[column]: row r of this env's dyn / stat state at env[r * TE]
   float* work;  // &workS[column]
-  int TE;
 };
-VB_DI float& ER(const Env& E, int row) { return E.env[row * E.TE]; }
-VB_DI float& WR(const Env& E, int row) { return E.work[row * E.TE]; }
-VB_DI V2 pos_at(const Env& E, int row) { return mk(ER(E, row), ER(E, row + 1)); }
+template <class EV> VB_DI float& ER(const EV& E, int row) { return E.env[row * EV::TE]; }
+template <class EV> VB_DI float& WR(const EV& E, int row) { return E.work[row * EV::TE]; }
+template <class EV> VB_DI V2 pos_at(const EV& E, int row) { return mk(ER(E, row), ER(E, row + 1)); }
 
-VB_DI Rot trig_of(const Env& E, const DEnt* __restrict__ en) {
+template <class EV>
+VB_DI Rot trig_of(const EV& E, const DEnt* __restrict__ en) {
   const int r = en->trig_row;
   Rot o;
   o.c = WR(E, r); o.s = WR(E, r + 1); o.c2 = WR(E, r + 2); o.s2 = WR(E, r + 3);
@@ -99,7 +102,8 @@ VB_DI Rot trig_of(const Env& E, const DEnt* __restrict__ en) {
 }
 
 // cos/sin cache of one entity (physics.py:299-301, 412; utils.py:183-184)
-VB_DI void store_trig(const DEnt* __restrict__ en, const Env& E, float rot) {
+template <class EV>
+VB_DI void store_trig(const DEnt* __restrict__ en, const EV& E, float rot) {
   const int r = en->trig_row;
   float s, c;
   sincosf(rot, &s, &c);
@@ -113,7 +117,8 @@ VB_DI void store_trig(const DEnt* __restrict__ en, const Env& E, float rot) {
 
 // Start of a substep for one dynamic entity: F = T = 0, then action force/torque (core.py:2017-2040, with the
 // clamped value written back to the env's frc rows), friction (core.py:2053-2101), gravity (core.py:2042-2051).
-VB_DI void begin_forces(const KParams& kp, const DEnt* __restrict__ en, const Env& E) {
+template <class EV>
+VB_DI void begin_forces(const KParams& kp, const DEnt* __restrict__ en, const EV& E) {
   const uint32_t fl = en->flags;
   V2 F = mk(0.f, 0.f);
   float T = 0.f;
@@ -150,8 +155,8 @@ VB_DI void begin_forces(const KParams& kp, const DEnt* __restrict__ en, const En
 
 // One work item (joint constraint or candidate pair): force on a (the force on b is its exact negation) and the
 // two torques.  `type` is warp-uniform, so the switch does not diverge.
-template <bool CT>
-VB_DI void eval_item(const KParams& kp, const DItem* __restrict__ it, const Env& E, V2& fa, float& ta, float& tb) {
+template <bool CT, class EV>
+VB_DI void eval_item(const KParams& kp, const DItem* __restrict__ it, const EV& E, V2& fa, float& ta, float& tb) {
   const int type = it->type;
   const DEnt* __restrict__ ea = &T_ent<CT>(kp, it->a);
   const DEnt* __restrict__ eb = &T_ent<CT>(kp, it->b);
@@ -232,7 +237,8 @@ VB_DI void eval_item(const KParams& kp, const DItem* __restrict__ it, const Env&
 }
 
 // update_env_forces (core.py:2190-2198): F_a += f_a if a.movable, T_a += t_a if a.rotatable, then b with -f_a.
-VB_DI void accumulate(const DItem* __restrict__ it, const Env& E, V2 fa, float ta, float tb) {
+template <class EV>
+VB_DI void accumulate(const DItem* __restrict__ it, const EV& E, V2 fa, float ta, float tb) {
   const int acc = it->acc;
   if (acc & (ACC_A_MOV | ACC_A_ROT)) {
     const int r = it->fin_a;
@@ -247,7 +253,8 @@ VB_DI void accumulate(const DItem* __restrict__ it, const Env& E, V2 fa, float t
 }
 
 // _integrate_state of one dynamic entity (core.py:2861-2907) from its accumulated (Fx Fy T).
-VB_DI void integrate(const KParams& kp, const DEnt* __restrict__ en, const Env& E, int substep) {
+template <class EV>
+VB_DI void integrate(const KParams& kp, const DEnt* __restrict__ en, const EV& E, int substep) {
   const uint32_t fl = en->flags;
   const int fin = en->fin_row, d = en->dyn_off;
   const float sub_dt = kp.sub_dt;
@@ -255,7 +262,8 @@ VB_DI void integrate(const KParams& kp, const DEnt* __restrict__ en, const Env& 
     V2 F = mk(WR(E, fin), WR(E, fin + 1));
     V2 vel = mk(ER(E, d + 2), ER(E, d + 3));
     if (substep == 0) vel = vel * en->one_minus_drag;
-    V2 acc = F / en->mass;
+    const float mass = en->mass;
+    V2 acc = mass == 1.f ? F : F / mass;  // x / 1 == x exactly
     vel = vel + acc * sub_dt;
     if (fl & VMASB200_E_MAX_SPEED) vel = clamp_norm2(vel, en->max_speed);
     if (fl & VMASB200_E_V_RANGE) {
@@ -280,8 +288,8 @@ VB_DI void integrate(const KParams& kp, const DEnt* __restrict__ en, const Env& 
 
 // One LIDAR ray (sensors.py:115-118 -> core.py:1661-1785) of env view E: min over the sensor's targets within reach
 // (the sensor's survival mask words are in the env's lmask rows; an unreachable target would have given max_range).
-template <bool CT>
-VB_DI float cast_one_ray(const KParams& kp, const DSensor* __restrict__ sn, const Env& E, V2 o, float ang) {
+template <bool CT, class EV>
+VB_DI float cast_one_ray(const KParams& kp, const DSensor* __restrict__ sn, const EV& E, V2 o, float ang) {
   const float max_range = sn->max_range;
   float best = max_range;
   float ds, dc;

@@ -30,6 +30,13 @@ static size_t put(std::vector<char>& blob, const std::vector<T>& v) {
   return off;
 }
 
+// the step kernel instantiations: tables in the constant bank or in global memory x CTA tile (envs per CTA)
+using StepFn = void (*)(const KParams, const AgentIO, const StepArgs);
+static StepFn step_fn(bool ct, int te) {
+  if (ct) return te == 32 ? step_kernel<true, 32> : te == 64 ? step_kernel<true, 64> : step_kernel<true, 128>;
+  return te == 32 ? step_kernel<false, 32> : te == 64 ? step_kernel<false, 64> : step_kernel<false, 128>;
+}
+
 static size_t bits_words(const KParams& kp) { return (size_t)kp.S * std::max(kp.pair_words, 1); }
 
 int upload_plan(vmasb200_plan* pl) {
@@ -63,8 +70,9 @@ int upload_plan(vmasb200_plan* pl) {
   VB_CUDA(cudaMalloc(&pl->d_bits, nbits));
   VB_CUDA(cudaMemset(pl->d_bits, 0, nbits));
   pl->smem_bytes = smem_map(kp).total_bytes;
-  VB_CUDA(cudaFuncSetAttribute(step_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
-  VB_CUDA(cudaFuncSetAttribute(step_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
+  for (int ct = 0; ct < 2; ++ct)
+    for (int te : {32, 64, 128})
+      VB_CUDA(cudaFuncSetAttribute(step_fn(ct != 0, te), cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
   pl->uploaded = true;
   return VMASB200_OK;
 }
@@ -98,7 +106,7 @@ static uint64_t g_plan_serial = 0;
 
 static int bind_const(vmasb200_plan* pl, cudaStream_t st, bool* ct) {
   const KParams& kp = pl->kp;
-  *ct = kp.P <= kCPairs && kp.E <= kCEnts && kp.n_sensors <= kCSensors && pl->device >= 0 && pl->device < 64;
+  *ct = (int)pl->broad.size() <= kCPairs && kp.E <= kCEnts && kp.n_sensors <= kCSensors && pl->device >= 0 && pl->device < 64;
   if (!*ct) return VMASB200_OK;
   std::lock_guard<std::mutex> lock(g_const_mu);
   ConstOwner& o = g_const[pl->device];
@@ -161,8 +169,7 @@ static int launch_step(vmasb200_plan* pl, const vmasb200_step_io* io, long long 
       }
       sa.s_begin = s; sa.s_end = s + 1; sa.flags_in = flags;
       sa.do_lidar = (s == kp.S - 1);
-      if (ct) step_kernel<true><<<grid, block, pl->smem_bytes, st>>>(kp, aio, sa);
-      else step_kernel<false><<<grid, block, pl->smem_bytes, st>>>(kp, aio, sa);
+      step_fn(ct, kp.TE)<<<grid, block, pl->smem_bytes, st>>>(kp, aio, sa);
       sa.dyn_in = io->dyn_out;
     }
   } else {
@@ -176,8 +183,7 @@ static int launch_step(vmasb200_plan* pl, const vmasb200_step_io* io, long long 
     }
     sa.u_list = pl->d_ulist; sa.u_buf = pl->d_ubuf;
     sa.s_begin = 0; sa.s_end = kp.S; sa.flags_in = nullptr; sa.do_lidar = 1;
-    if (ct) step_kernel<true><<<grid, block, pl->smem_bytes, st>>>(kp, aio, sa);
-    else step_kernel<false><<<grid, block, pl->smem_bytes, st>>>(kp, aio, sa);
+    step_fn(ct, kp.TE)<<<grid, block, pl->smem_bytes, st>>>(kp, aio, sa);
   }
   if (ct) VB_CUDA(cudaEventRecord(g_const[pl->device].last_use, st));
   if (io->pair_active_out && nw) VB_CUDA(cudaMemcpyAsync(io->pair_active_out, flags, nw * sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
