@@ -126,18 +126,16 @@ VB_DI bool run_substeps(const KParams& kp, const StepArgs& sa, const Tile& t, co
 #pragma unroll
       for (int k = 0; k < 32; ++k) {
         {
+          // branch-free, so that the 32 bodies interleave: a circle row carries hx = hy = +inf (and any valid trig
+          // row), a frame row t2_cull = +inf; NaN passes every test and is left to the narrow phase
           const DBroad& bq = T_broad<CT>(kp, base + k);
           const int ra = bq.pa_row, rb = bq.pb_row, rt = bq.trig_row;
           const float dx = ER(E, ra) - ER(E, rb), dy = ER(E, ra + 1) - ER(E, rb + 1);
           const float d2 = fmaf(dy, dy, dx * dx);
-          if (d2 <= bq.t2_bp) bpw |= 1u << k;  // == (norm(pa - pb) <= Rc_a + Rc_b), core.py:2796-2800
-          if (rt < 0) {
-            if (!(d2 > bq.t2_cull)) sv |= 1u << k;
-          } else {  // sphere centre in the line / box frame (a conservative cull: fused arithmetic is fine here)
-            const float c = WR(E, rt), sn = WR(E, rt + 1);
-            const float lx = fmaf(dx, c, dy * sn), ly = fmaf(dx, sn, -(dy * c));
-            if (!(fabsf(lx) > bq.hx) && !(fabsf(ly) > bq.hy)) sv |= 1u << k;
-          }
+          const float c = WR(E, rt), sn = WR(E, rt + 1);
+          const float lx = fmaf(dx, c, dy * sn), ly = fmaf(dx, sn, -(dy * c));  // b's centre in a's frame
+          bpw |= (d2 <= bq.t2_bp ? 1u : 0u) << k;  // == (norm(pa - pb) <= Rc_a + Rc_b), core.py:2796-2800
+          sv |= ((!(d2 > bq.t2_cull) && !(fabsf(lx) > bq.hx) && !(fabsf(ly) > bq.hy)) ? 1u : 0u) << k;
         }
       }
       const uint32_t valid = n == 32 ? 0xffffffffu : (1u << n) - 1u;

@@ -237,7 +237,7 @@ int build_plan(const vmasb200_world_desc* d, vmasb200_plan* pl) {
     const vmasb200_entity &sa = d->entities[it.a], &sb = d->entities[it.b];
     DBroad b{};
     b.pa_row = pl->ents[it.a].pos_row; b.pb_row = pl->ents[it.b].pos_row;
-    b.trig_row = -1;
+    b.trig_row = 0; b.hx = b.hy = INFINITY;  // circle cull only (any valid work row; the frame test always passes)
     b.t2_bp = sq_le(it.thr);
     if (it.type == IT_SS) {
       const float dmin = sa.radius + sb.radius;  // fp32 sum = the kernel's dist_min (core.py:2312)
@@ -249,13 +249,14 @@ int build_plan(const vmasb200_world_desc* d, vmasb200_plan* pl) {
         b.hx = (float)((double)sa.length / 2 + reach);
         b.hy = (float)((it.type == IT_BS ? (double)sa.width / 2 : 0.0) + reach);
         b.trig_row = pl->ents[it.a].trig_row;
+        b.t2_cull = INFINITY;
       }
     }
     pl->broad.push_back(b);
   }
   while (pl->broad.size() % 32) {  // padding rows of the unrolled broad phase: d2 <= -1 never holds
     DBroad b{};
-    b.trig_row = -1; b.t2_bp = -1.f; b.t2_cull = -1.f;
+    b.trig_row = 0; b.t2_bp = -1.f; b.t2_cull = -1.f; b.hx = b.hy = INFINITY;
     pl->broad.push_back(b);
   }
 

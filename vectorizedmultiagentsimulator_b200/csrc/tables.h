@@ -78,10 +78,12 @@ static_assert(sizeof(DItem) == 16 * 4, "DItem must be 16 words");
 //   (t2_bp = the largest float whose correctly rounded square root is <= thr; d2 = fma(dy,dy,dx*dx) is the very
 //   argument torch.linalg.vector_norm takes the root of)
 // and the cull only drops pairs whose force is provably zero (dist > dist_min, core.py:2835):
-//   trig_row < 0   circle cull: keep iff !(d2 > t2_cull)   (sphere-sphere: exact image of dist > r_a + r_b;
-//                  other types: (Rc_a + Rc_b + LINE_MIN_DIST) with a safety margin)
-//   trig_row >= 0  frame cull (a = line or box, b = sphere): b's centre in a's frame, keep iff |x| <= hx and |y| <= hy
-//                  (half extents + radius + LINE_MIN_DIST with a safety margin); trig_row = work row of a's cos/sin.
+//   circle cull: keep iff !(d2 > t2_cull)   (sphere-sphere: exact image of dist > r_a + r_b; other types:
+//                (Rc_a + Rc_b + LINE_MIN_DIST) with a safety margin); such rows carry hx = hy = +inf
+//   frame cull (a = line or box, b = sphere): b's centre in a's frame, keep iff |x| <= hx and |y| <= hy (half
+//                extents + radius + LINE_MIN_DIST with a safety margin); trig_row = work row of a's cos/sin;
+//                such rows carry t2_cull = +inf.
+// Every row is evaluated with BOTH tests (branch-free); NaN passes both.
 struct DBroad {             // 8 words
   int32_t pa_row, pb_row;   // env rows of the two positions
   int32_t trig_row;
