@@ -38,9 +38,9 @@ struct StepArgs {
 
 // dynamic shared memory carve-up (4-byte words); every row starts 16B aligned because TE % 4 == 0
 struct SmemMap {
-  int bar, env, work, lid, queue, rayq, wtask, wres, flags, total_bytes;
+  int bar, env, work, lid, queue, rayq, flags, total_bytes;
 };
-constexpr int kWarpTasks = 32;  // narrow-phase tasks a warp redistributes per round
+constexpr int kThreads = 128;   // threads per CTA; a team of Q = kThreads / TE members works on every env of the tile
 __host__ __device__ inline SmemMap smem_map(const KParams& kp) {
   SmemMap m;
   int o = 0;
@@ -48,8 +48,6 @@ __host__ __device__ inline SmemMap smem_map(const KParams& kp) {
   m.env = o; o += kp.TE * (kp.dyn_rows + kp.stat_rows);
   m.work = o; o += kp.TE * kp.work_rows;
   m.lid = o; o += kp.TE * kp.lidar_rows;
-  m.wres = o; o += (kp.TE / 32) * kWarpTasks * 4;   // float4 per task (16B aligned: everything above is a multiple of 4)
-  m.wtask = o; o += (kp.TE / 32) * kWarpTasks;
   m.queue = o; o += kp.TE * kp.n_sensors;
   m.rayq = o; o += kp.TE * kp.lidar_rows;
   m.flags = o; o += kp.S * kp.pair_words;
@@ -60,8 +58,6 @@ __host__ __device__ inline SmemMap smem_map(const KParams& kp) {
 struct Tile {
   float *envS, *workS, *lidS;
   int *queue, *rayq, *qcount;  // qcount[0]: sensor queue length, qcount[1]: ray queue length
-  int* wtask;                  // [TE/32][kWarpTasks]
-  float4* wres;                // [TE/32][kWarpTasks]
 };
 template <int TE>
 VB_DI EnvT<TE> env_view(const Tile& t, int col) {
@@ -74,10 +70,10 @@ VB_DI void or_global(uint32_t* word, uint32_t v) {
   if (v & ~__ldcg(word)) atomicOr(word, v);
 }
 
-// agent.state.force / torque of env `env` into the env's frc rows
+// agent.state.force / torque of env `env` into the env's frc rows (agents q, q + Q, ...)
 template <class EV>
-VB_DI void load_forces(const KParams& kp, const AgentIO& aio, const EV& E, long long env) {
-  for (int a = 0; a < kp.A; ++a) {
+VB_DI void load_forces(const KParams& kp, const AgentIO& aio, const EV& E, long long env, int q, int Q) {
+  for (int a = q; a < kp.A; a += Q) {
     float fx = 0.f, fy = 0.f, tq = 0.f;
     const float* fp = aio.force[a];
     const float* tp = aio.torque[a];
@@ -88,137 +84,141 @@ VB_DI void load_forces(const KParams& kp, const AgentIO& aio, const EV& E, long 
   }
 }
 
-// Substeps [s_begin, s_end) of one env (a thread-private column of the tile).  flags: batch-wide verdicts to obey
-// (smem or global), or NULL = speculative (every pair considered; verdict / thin bits OR-ed into sa.any_exact /
-// any_spec / thin).  All 32 lanes of a warp call this together (warp reductions).  Returns the env's taint.
-template <bool CT, class EV>
-VB_DI bool run_substeps(const KParams& kp, const StepArgs& sa, const Tile& t, const EV& E, bool ok, int s_begin,
-                        int s_end, const uint32_t* flags) {
+// Substeps [s_begin, s_end) of the tile.  EVERY thread of the CTA calls this (CTA barriers inside): thread t is
+// member q = t / TE of the team of column t % TE.  flags: batch-wide verdicts to obey (smem or global), or NULL =
+// speculative (every pair considered; verdict / thin bits OR-ed into sa.any_exact / any_spec / thin).
+// Work split of a substep (tables.h): joints, 8-pair slices of the broad phase, narrow-phase survivors (in the env's
+// pair order, survivor i to member i mod Q), then per dynamic entity the ordered sum of its forces + integration.
+// Returns the column's taint.
+template <bool CT, int TE>
+VB_DI bool run_substeps(const KParams& kp, const StepArgs& sa, const Tile& t, bool ok, int s_begin, int s_end,
+                        const uint32_t* flags) {
+  constexpr int Q = kThreads / TE;
+  constexpr int R = kSlots / Q;     // survivors a member evaluates per round
+  const int col = threadIdx.x % TE, q = threadIdx.x / TE;
+  const int lane = threadIdx.x & 31;
+  const EnvT<TE> E = env_view<TE>(t, col);
+  __syncthreads();  // the caller's tile loads
   // prologue: cos/sin cache of every entity that needs it, first force accumulators
-  for (int r = 0; r < kp.n_trig; ++r) {
+  for (int r = q; r < kp.n_trig; r += Q) {
     const DEnt* en = &T_ent<CT>(kp, T_trig<CT>(kp, r));
     store_trig(en, E, ER(E, en->rot_row));
   }
   // the clamp of core.py:2017-2040 is re-applied to its own result every substep: replay it for the substeps
   // that earlier launches of a split step already did
-  for (int rep = 0; rep <= s_begin; ++rep)
-    for (int d = 0; d < kp.n_dyn; ++d) begin_forces(kp, &T_ent<CT>(kp, T_dyn<CT>(kp, d)), E);
+  for (int d = q; d < kp.n_dyn; d += Q)
+    for (int rep = 0; rep <= s_begin; ++rep) begin_forces(kp, &T_ent<CT>(kp, T_dyn<CT>(kp, d)), E);
+  if (q == 0) WR(E, kp.row_taint) = 0.f;
+  __syncthreads();
 
-  bool tainted = false;
-  const int lane = threadIdx.x & 31;
-  int* wtask = t.wtask + (threadIdx.x >> 5) * kWarpTasks;
-  float4* wres = t.wres + (threadIdx.x >> 5) * kWarpTasks;
+  const int n_oct = kp.n_blk * 4;
   for (int s = s_begin; s < s_end; ++s) {
-    // ---- joints (core.py:2175, always evaluated)
-    for (int j = 0; j < kp.J; ++j) {
-      const DItem* it = kp.items + j;
+    // ---- joints (core.py:2175, always evaluated), from the last member down (the broad phase starts at member 0)
+    for (int j = Q - 1 - q; j < kp.J; j += Q) {
       V2 fa; float ta, tb;
-      eval_item<CT>(kp, it, E, fa, ta, tb);
-      accumulate(it, E, fa, ta, tb);
+      eval_item<CT>(kp, kp.items + j, E, fa, ta, tb);
+      const int r = kp.row_jres + 4 * j;
+      WR(E, r) = fa.x; WR(E, r + 1) = fa.y; WR(E, r + 2) = ta; WR(E, r + 3) = tb;
     }
-    // ---- candidate pairs, 32 at a time: broad phase for all, narrow phase for the survivors
-    bool thin_now = false;
-    for (int base = 0; base < kp.P; base += 32) {
-      const int n = min(32, kp.P - base);
+    // ---- broad phase, 8 candidate pairs at a time
+    const bool tainted = WR(E, kp.row_taint) != 0.f;
+    for (int u = q; u < n_oct; u += Q) {
       uint32_t bpw = 0u, sv = 0u;
-      // fully unrolled: table offsets and bit positions are immediates.  The table is padded to a multiple of 32 rows
-      // with rows that never pass (plan.cpp); the mask below only matters for NaN state.
+      // The table is padded to a multiple of 32 rows with rows that never pass (plan.cpp).
 #pragma unroll
-      for (int k = 0; k < 32; ++k) {
-        {
-          // branch-free, so that the 32 bodies interleave: a circle row carries hx = hy = +inf (and any valid trig
-          // row), a frame row t2_cull = +inf; NaN passes every test and is left to the narrow phase
-          const DBroad& bq = T_broad<CT>(kp, base + k);
-          const int ra = bq.pa_row, rb = bq.pb_row, rt = bq.trig_row;
-          const float dx = ER(E, ra) - ER(E, rb), dy = ER(E, ra + 1) - ER(E, rb + 1);
-          const float d2 = fmaf(dy, dy, dx * dx);
-          const float c = WR(E, rt), sn = WR(E, rt + 1);
-          const float lx = fmaf(dx, c, dy * sn), ly = fmaf(dx, sn, -(dy * c));  // b's centre in a's frame
-          bpw |= (d2 <= bq.t2_bp ? 1u : 0u) << k;  // == (norm(pa - pb) <= Rc_a + Rc_b), core.py:2796-2800
-          sv |= ((!(d2 > bq.t2_cull) && !(fabsf(lx) > bq.hx) && !(fabsf(ly) > bq.hy)) ? 1u : 0u) << k;
-        }
+      for (int k = 0; k < 8; ++k) {
+        // branch-free, so that the bodies interleave: a circle row carries hx = hy = +inf (and any valid trig
+        // row), a frame row t2_cull = +inf; NaN passes every test and is left to the narrow phase
+        const DBroad& bq = T_broad<CT>(kp, u * 8 + k);
+        const int ra = bq.pa_row, rb = bq.pb_row, rt = bq.trig_row;
+        const float dx = ER(E, ra) - ER(E, rb), dy = ER(E, ra + 1) - ER(E, rb + 1);
+        const float d2 = fmaf(dy, dy, dx * dx);
+        const float c = WR(E, rt), sn = WR(E, rt + 1);
+        const float lx = fmaf(dx, c, dy * sn), ly = fmaf(dx, sn, -(dy * c));  // b's centre in a's frame
+        bpw |= (d2 <= bq.t2_bp ? 1u : 0u) << k;  // == (norm(pa - pb) <= Rc_a + Rc_b), core.py:2796-2800
+        sv |= ((!(d2 > bq.t2_cull) && !(fabsf(lx) > bq.hx) && !(fabsf(ly) > bq.hy)) ? 1u : 0u) << k;
       }
-      const uint32_t valid = n == 32 ? 0xffffffffu : (1u << n) - 1u;
+      const int n = kp.P - u * 8;  // the mask only matters for NaN state in the padding rows
+      const uint32_t valid = n >= 8 ? 0xffu : (n > 0 ? (1u << n) - 1u : 0u);
       bpw &= valid; sv &= valid;
-      const int w = s * kp.pair_words + (base >> 5);
+      const int w = s * kp.pair_words + (u >> 2), sh = 8 * (u & 3);
       if (flags) {
-        sv &= flags[w];
+        sv &= flags[w] >> sh;
       } else {
         const uint32_t e = __reduce_or_sync(0xffffffffu, (ok && !tainted) ? bpw : 0u);
         const uint32_t sp = __reduce_or_sync(0xffffffffu, (ok && tainted) ? bpw : 0u);
         if (lane == 0) {
-          if (e) or_global(sa.any_exact + w, e);
-          if (sp) or_global(sa.any_spec + w, sp);
+          if (e) or_global(sa.any_exact + w, e << sh);
+          if (sp) or_global(sa.any_spec + w, sp << sh);
         }
       }
       if (!ok) sv = 0u;
-      // ---- narrow phase of the survivors.  Contacts are sparse and hit different pairs in different envs, so the
-      // warp pools its (env, pair) tasks and every lane evaluates one task per round - possibly of another lane's env
-      // (the tile is shared memory) - then each lane adds up its OWN env's results in pair order.
-      const uint32_t cnt = __popc(sv);
-      uint32_t incl = cnt;
-#pragma unroll
-      for (int o = 1; o < 32; o <<= 1) {
-        const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
-        if (lane >= o) incl += v;
-      }
-      const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
-      const uint32_t first = incl - cnt;  // index of this lane's first task
-      for (uint32_t r0 = 0; r0 < total; r0 += kWarpTasks) {
-        {
-          uint32_t m = sv, idx = first;
-          while (m) {
-            const int k = __ffs(m) - 1;
-            m &= m - 1u;
-            if (idx - r0 < (uint32_t)kWarpTasks) wtask[idx - r0] = (lane << 8) | k;
-            ++idx;
-          }
-        }
-        __syncwarp();
-        const uint32_t nt = min((uint32_t)kWarpTasks, total - r0);
-        for (uint32_t q = lane; q < nt; q += 32) {
-          const int task = wtask[q];
-          const int src = task >> 8;
-          EV E2;
-          E2.env = E.env + (src - lane); E2.work = E.work + (src - lane);
-          V2 fa; float ta, tb;
-          eval_item<CT>(kp, kp.items + kp.J + base + (task & 31), E2, fa, ta, tb);
-          wres[q] = make_float4(fa.x, fa.y, ta, tb);
-        }
-        __syncwarp();
-        {
-          uint32_t m = sv, idx = first;
-          while (m) {
-            const int k = __ffs(m) - 1;
-            m &= m - 1u;
-            if (idx - r0 < (uint32_t)kWarpTasks) {
-              const float4 r = wres[idx - r0];
-              if (!flags && !((bpw >> k) & 1u) && (r.x != 0.f || r.y != 0.f)) {
-                or_global(sa.thin + w, 1u << k);
-                thin_now = true;
-              }
-              accumulate(kp.items + kp.J + base + k, E, mk(r.x, r.y), r.z, r.w);
-            }
-            ++idx;
-          }
-        }
-        __syncwarp();
-      }
+      reinterpret_cast<uint8_t*>(&WR(E, kp.row_sv + (u >> 2)))[u & 3] = (uint8_t)sv;
+      reinterpret_cast<uint8_t*>(&WR(E, kp.row_bp + (u >> 2)))[u & 3] = (uint8_t)bpw;
     }
-    tainted = tainted || thin_now;  // the taint applies from the NEXT substep on
-    // ---- integrate, then open the next substep's accumulators
-    for (int d = 0; d < kp.n_dyn; ++d) {
+    __syncthreads();
+    // ---- narrow phase of the survivors in rounds of kSlots per env, then the ordered sums
+    for (int lo = 0;; lo += kSlots) {
+      int cnt = 0;
+      int task[R];
+#pragma unroll
+      for (int r = 0; r < R; ++r) task[r] = -1;
+      for (int b = 0; b < kp.n_blk; ++b) {
+        uint32_t m = __float_as_uint(WR(E, kp.row_sv + b));
+        while (m) {
+          const int k = __ffs(m) - 1;
+          m &= m - 1u;
+#pragma unroll
+          for (int r = 0; r < R; ++r)
+            if (cnt == lo + q + r * Q) task[r] = b * 32 + k;
+          ++cnt;
+        }
+      }
+#pragma unroll
+      for (int r = 0; r < R; ++r) {
+        const int p = task[r];
+        if (p >= 0) {
+          V2 fa; float ta, tb;
+          eval_item<CT>(kp, kp.items + kp.J + p, E, fa, ta, tb);
+          const int pr = kp.row_pres + 5 * (q + r * Q);
+          WR(E, pr) = fa.x; WR(E, pr + 1) = fa.y; WR(E, pr + 2) = ta; WR(E, pr + 3) = tb;
+          WR(E, pr + 4) = __int_as_float(p);
+          if (!flags && (fa.x != 0.f || fa.y != 0.f) &&
+              !((__float_as_uint(WR(E, kp.row_bp + (p >> 5))) >> (p & 31)) & 1u)) {
+            or_global(sa.thin + s * kp.pair_words + (p >> 5), 1u << (p & 31));
+            WR(E, kp.row_taint) = 1.f;  // read by the NEXT substep's broad phase
+          }
+        }
+      }
+      const int more = __syncthreads_or(cnt > lo + kSlots);
+      if (lo == 0)
+        for (int j = 0; j < kp.J; ++j) {
+          const int r = kp.row_jres + 4 * j;
+          accumulate<Q>(kp.items + j, E, mk(WR(E, r), WR(E, r + 1)), WR(E, r + 2), WR(E, r + 3), q);
+        }
+      const int n = min(cnt - lo, kSlots);
+      for (int i = 0; i < n; ++i) {
+        const int pr = kp.row_pres + 5 * i;
+        accumulate<Q>(kp.items + kp.J + __float_as_int(WR(E, pr + 4)), E, mk(WR(E, pr), WR(E, pr + 1)), WR(E, pr + 2),
+                      WR(E, pr + 3), q);
+      }
+      if (!more) break;
+      __syncthreads();  // the result slots are reused
+    }
+    // ---- integrate the entities this member sums, then open their next accumulators
+    for (int d = q; d < kp.n_dyn; d += Q) {
       const DEnt* en = &T_ent<CT>(kp, T_dyn<CT>(kp, d));
       integrate(kp, en, E, s);
       if (s + 1 < s_end) begin_forces(kp, en, E);
     }
+    __syncthreads();
   }
-  return tainted;
+  return WR(E, kp.row_taint) != 0.f;
 }
 
 // LIDAR epilogue for the whole tile (every thread of the CTA calls it, helper warps included; contains CTA barriers).
 // n_cols = columns of the tile that hold real environments.  Three passes, each on full warps:
-//   1  thread per env: per sensor the mask of targets a ray could reach at all; sensors that see something go to
+//   1  thread per (env, sensor mod Q): per sensor the mask of targets a ray could reach at all; sensors that see something go to
 //      the sensor queue (and get cos/sin of their rotation cached); every ray starts at max_range;
 //   2  thread per (queued sensor, ray): ray-level cull with an APPROXIMATE direction (angle-sum formula) and a slack
 //      that covers the approximation: a target farther than Rc from the ray's line, or behind the origin, cannot be
@@ -234,9 +234,11 @@ VB_DI void lidar_epilogue(const KParams& kp, const Tile& t, int n_cols) {
     for (int i = tid; i < sn->n_rays * TE; i += nthr) t.lidS[sn->out_off * TE + i] = mr;
   }
   __syncthreads();
-  if (tid < TE) {
-    const EnvT<TE> E = env_view<TE>(t, tid);
-    for (int k = 0; k < kp.n_sensors; ++k) {
+  {
+    constexpr int Q = kThreads / TE;
+    const int col = tid % TE;
+    const EnvT<TE> E = env_view<TE>(t, col);
+    for (int k = tid / TE; k < kp.n_sensors; k += Q) {
       const DSensor* sn = &T_sensor<CT>(kp, k);
       const DEnt* se = &T_ent<CT>(kp, sn->entity);
       const V2 o = pos_at(E, se->pos_row);
@@ -252,11 +254,11 @@ VB_DI void lidar_epilogue(const KParams& kp, const Tile& t, int n_cols) {
         WR(E, sn->tw_off + w) = __uint_as_float(m);
         any |= m;
       }
-      if (any && tid < n_cols) {
+      if (any && col < n_cols) {
         float s, c;
         sincosf(ER(E, se->rot_row), &s, &c);
         WR(E, kp.row_strig + 2 * k) = c; WR(E, kp.row_strig + 2 * k + 1) = s;
-        t.queue[atomicAdd(t.qcount, 1)] = tid | (k << 16);
+        t.queue[atomicAdd(t.qcount, 1)] = col | (k << 16);
       }
     }
   }
@@ -310,9 +312,11 @@ VB_DI void lidar_epilogue(const KParams& kp, const Tile& t, int n_cols) {
 template <bool CT, int TE>
 __device__ __noinline__ void repair_tainted(const KParams& kp, const AgentIO& aio, const StepArgs& sa, const Tile& t,
                                             uint32_t* flagS, int nu) {
+  constexpr int Q = kThreads / TE;
   const int tid = threadIdx.x, nthr = blockDim.x;
+  const int col = tid % TE, q = tid / TE;
   const int nw = kp.S * kp.pair_words;
-  const EnvT<TE> E = env_view<TE>(t, tid);
+  const EnvT<TE> E = env_view<TE>(t, col);
   for (int w = tid; w < nw; w += nthr) flagS[w] = __ldcg(sa.any_exact + w);
   __syncthreads();
   for (int s = 0; s <= kp.S; ++s) {  // s == S: LIDAR + write-back pass
@@ -338,25 +342,25 @@ __device__ __noinline__ void repair_tainted(const KParams& kp, const AgentIO& ai
     }
     // pass 2: one substep with the now exact flags (or the epilogue), a tile of TE tainted envs at a time
     for (int base = 0; base < nu; base += TE) {
-      const int idx = base + tid;
-      const bool ok = tid < TE && idx < nu;
+      const int idx = base + col;
+      const bool ok = idx < nu;
       const long long env = ok ? sa.u_list[idx] : 0;
       if (ok) {
-        for (int r = 0; r < kp.dyn_rows; ++r) ER(E, r) = sa.u_buf[(size_t)idx * kp.dyn_rows + r];
-        for (int r = 0; r < kp.stat_rows; ++r) ER(E, kp.dyn_rows + r) = sa.stat[(size_t)r * sa.ld + env];
-        load_forces(kp, aio, E, env);
+        for (int r = q; r < kp.dyn_rows; r += Q) ER(E, r) = sa.u_buf[(size_t)idx * kp.dyn_rows + r];
+        for (int r = q; r < kp.stat_rows; r += Q) ER(E, kp.dyn_rows + r) = sa.stat[(size_t)r * sa.ld + env];
+        load_forces(kp, aio, E, env, q, Q);
       }
       const bool last = s == kp.S;
-      // s == S: prologue only (cos/sin cache, clamps).  Helper warps (tid >= TE) have no column.
-      if (tid < TE) run_substeps<CT>(kp, sa, t, E, ok, s, last ? s : s + 1, flagS);
+      // s == S: prologue only (cos/sin cache, clamps)
+      run_substeps<CT, TE>(kp, sa, t, ok, s, last ? s : s + 1, flagS);
       if (!last) {
-        if (ok) for (int r = 0; r < kp.dyn_rows; ++r) sa.u_buf[(size_t)idx * kp.dyn_rows + r] = ER(E, r);
+        if (ok) for (int r = q; r < kp.dyn_rows; r += Q) sa.u_buf[(size_t)idx * kp.dyn_rows + r] = ER(E, r);
       } else {
         if (sa.lidar_out && kp.n_rays) lidar_epilogue<CT, TE>(kp, t, min(TE, nu - base));
         if (ok) {
-          for (int r = 0; r < kp.dyn_rows; ++r) sa.dyn_out[(size_t)r * sa.ld + env] = ER(E, r);
+          for (int r = q; r < kp.dyn_rows; r += Q) sa.dyn_out[(size_t)r * sa.ld + env] = ER(E, r);
           if (sa.lidar_out)
-            for (int r = 0; r < kp.lidar_rows; ++r) sa.lidar_out[(size_t)r * sa.ld + env] = t.lidS[r * TE + tid];
+            for (int r = q; r < kp.lidar_rows; r += Q) sa.lidar_out[(size_t)r * sa.ld + env] = t.lidS[r * TE + col];
         }
       }
       __syncthreads();
@@ -364,27 +368,30 @@ __device__ __noinline__ void repair_tainted(const KParams& kp, const AgentIO& ai
   }
 }
 
+// Fused step of one tile of TE environments.  Registers: kThreads * 7 CTAs of TE = 32 must fit the register file for
+// one wave at 32768 envs, hence the tighter bound for the 4-member teams.
 template <bool CT, int TE>
-__global__ void __launch_bounds__(256) step_kernel(const __grid_constant__ KParams kp, const __grid_constant__ AgentIO aio,
-                                                   const __grid_constant__ StepArgs sa) {
+__global__ void __launch_bounds__(kThreads, TE == 32 ? 7 : 4)
+step_kernel(const __grid_constant__ KParams kp, const __grid_constant__ AgentIO aio, const __grid_constant__ StepArgs sa) {
   extern __shared__ __align__(16) float smem[];
   __shared__ int s_last;
+  constexpr int Q = kThreads / TE;
   const SmemMap m = smem_map(kp);
   uint64_t* bar = reinterpret_cast<uint64_t*>(smem + m.bar);
   Tile t;
   t.envS = smem + m.env; t.workS = smem + m.work; t.lidS = smem + m.lid;
   t.queue = reinterpret_cast<int*>(smem + m.queue); t.rayq = reinterpret_cast<int*>(smem + m.rayq);
   t.qcount = reinterpret_cast<int*>(smem + m.bar) + 2;
-  t.wtask = reinterpret_cast<int*>(smem + m.wtask); t.wres = reinterpret_cast<float4*>(smem + m.wres);
   uint32_t* flagS = reinterpret_cast<uint32_t*>(smem + m.flags);
   const int nw = kp.S * kp.pair_words;
 
   const int tid = threadIdx.x;
+  const int col = tid % TE, q = tid / TE;
   const long long env0 = sa.env_begin + (long long)blockIdx.x * TE;
   const int n_valid = (int)min((long long)TE, sa.env_end - env0);  // real environments of the tile
   // columns moved by TMA (multiple of 4): the batch's last tile also carries the padding columns up to ld
   const int n_cols = (int)min((long long)TE, (sa.env_end == sa.n_envs ? sa.ld : sa.env_end) - env0);
-  const bool ok = tid < n_valid;
+  const bool ok = col < n_valid;
   const bool spec = sa.flags_in == nullptr;
   const uint32_t row_bytes = (uint32_t)n_cols * 4u;
   const int n_in = kp.dyn_rows + kp.stat_rows;
@@ -405,21 +412,17 @@ __global__ void __launch_bounds__(256) step_kernel(const __grid_constant__ KPara
       bulk_g2s(t.envS + r * TE, src, row_bytes, bar);
     }
   }
-  // threads [0, TE) own one env each; helper warps (tid >= TE, LIDAR worlds only) join for the LIDAR epilogue
-  const EnvT<TE> E = env_view<TE>(t, tid < TE ? tid : 0);
-  bool tainted = false;
-  if (tid < TE) {
-    if (ok) load_forces(kp, aio, E, env0 + tid);
-    mbar_wait(bar, 0);
-    tainted = run_substeps<CT>(kp, sa, t, E, ok, sa.s_begin, sa.s_end, sa.flags_in);
-  }
+  const EnvT<TE> E = env_view<TE>(t, col);
+  if (ok) load_forces(kp, aio, E, env0 + col, q, Q);
+  mbar_wait(bar, 0);
+  const bool tainted = run_substeps<CT, TE>(kp, sa, t, ok, sa.s_begin, sa.s_end, sa.flags_in);
   const bool lidar = sa.do_lidar && sa.lidar_out && kp.n_rays;
   if (lidar) lidar_epilogue<CT, TE>(kp, t, n_valid);
 
-  if (spec && tainted && ok) {  // keep the INPUT state of a tainted env (dyn_in is intact until our own store)
+  if (spec && tainted && ok && q == 0) {  // keep the INPUT state of a tainted env (dyn_in is intact until our own store)
     const int idx = atomicAdd(sa.counters + 1, 1);
-    sa.u_list[idx] = (int)(env0 + tid);
-    for (int r = 0; r < kp.dyn_rows; ++r) sa.u_buf[(size_t)idx * kp.dyn_rows + r] = sa.dyn_in[(size_t)r * sa.ld + env0 + tid];
+    sa.u_list[idx] = (int)(env0 + col);
+    for (int r = 0; r < kp.dyn_rows; ++r) sa.u_buf[(size_t)idx * kp.dyn_rows + r] = sa.dyn_in[(size_t)r * sa.ld + env0 + col];
   }
   // ---- write back: one TMA bulk store per output row
   fence_proxy_async();

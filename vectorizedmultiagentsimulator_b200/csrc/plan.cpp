@@ -212,7 +212,13 @@ int build_plan(const vmasb200_world_desc* d, vmasb200_plan* pl) {
   kp.row_frc = kp.row_trig + 4 * kp.n_trig;
   kp.row_lmask = kp.row_frc + 3 * kp.A;
   kp.row_strig = kp.row_lmask + kp.n_lmask_words;
-  kp.work_rows = kp.row_strig + 2 * kp.n_sensors;
+  kp.n_blk = (kp.P + 31) / 32;
+  kp.row_jres = kp.row_strig + 2 * kp.n_sensors;
+  kp.row_sv = kp.row_jres + 4 * kp.J;
+  kp.row_bp = kp.row_sv + kp.n_blk;
+  kp.row_pres = kp.row_bp + kp.n_blk;
+  kp.row_taint = kp.row_pres + 5 * kSlots;
+  kp.work_rows = kp.row_taint + 1;
   for (int i = 0; i < kp.n_dyn; ++i) pl->ents[pl->dyn_list[i]].fin_row = kp.row_fin + 3 * i;
   for (int i = 0; i < kp.n_trig; ++i) pl->ents[pl->trig_list[i]].trig_row = kp.row_trig + 4 * i;
   for (int e = 0; e < E; ++e) {
@@ -225,6 +231,7 @@ int build_plan(const vmasb200_world_desc* d, vmasb200_plan* pl) {
     DItem& it = pl->items[i];
     const DEnt &a = pl->ents[it.a], &b = pl->ents[it.b];
     it.fin_a = a.fin_row; it.fin_b = b.fin_row;
+    it.own = (uint32_t)(a.fin_row >= 0 ? (a.fin_row - kp.row_fin) / 3 : 0) | (uint32_t)(b.fin_row >= 0 ? (b.fin_row - kp.row_fin) / 3 : 0) << 16;
     it.acc = ((a.flags & VMASB200_E_MOVABLE) ? ACC_A_MOV : 0) | ((a.flags & VMASB200_E_ROTATABLE) ? ACC_A_ROT : 0) |
              ((b.flags & VMASB200_E_MOVABLE) ? ACC_B_MOV : 0) | ((b.flags & VMASB200_E_ROTATABLE) ? ACC_B_ROT : 0);
     if (i < kp.J && pl->joint_slot[i] >= 0) it.fr_row = kp.dyn_rows + pl->joint_slot[i];
@@ -266,14 +273,11 @@ int build_plan(const vmasb200_world_desc* d, vmasb200_plan* pl) {
   const int per_env = 4 * (kp.dyn_rows + kp.stat_rows + kp.work_rows + 2 * kp.lidar_rows + kp.n_sensors) + 20;
   const int fixed = 64 + 4 * kp.S * kp.pair_words;
   int TE = d->envs_per_cta;
-  if (TE == 0) {
-    TE = 64;
-    while (TE > 32 && fixed + TE * per_env > 100 * 1024) TE -= 32;
-  }
+  if (TE == 0) TE = 32;  // 4 team members per env: the shortest critical path and the most warps per byte of smem
   if (TE != 32 && TE != 64 && TE != 128) { set_error("envs_per_cta must be 32, 64 or 128"); return VMASB200_ERR_INVALID; }
   if (fixed + TE * per_env > 226 * 1024) { set_error("world too large for one CTA's shared memory"); return VMASB200_ERR_UNSUPPORTED; }
   kp.TE = TE;
-  kp.NT = kp.n_rays ? std::min(256, 2 * TE) : TE;  // helper warps for the LIDAR epilogue (register file: 4 CTAs / SM)
+  kp.NT = 128;  // Q = 128 / TE team members per env
 
   // ---- world constants
   kp.sub_dt = (float)((double)d->dt / (double)d->substeps);  // core.py:1124 (Python doubles)

@@ -237,15 +237,18 @@ VB_DI void eval_item(const KParams& kp, const DItem* __restrict__ it, const EV& 
 }
 
 // update_env_forces (core.py:2190-2198): F_a += f_a if a.movable, T_a += t_a if a.rotatable, then b with -f_a.
-template <class EV>
-VB_DI void accumulate(const DItem* __restrict__ it, const EV& E, V2 fa, float ta, float tb) {
+template <int Q, class EV>
+VB_DI void accumulate(const DItem* __restrict__ it, const EV& E, V2 fa, float ta, float tb, int q) {
+  // member q of the env's team sums the entities it owns (dyn index = q mod Q): every accumulator still receives
+  // its addends in the reference's order
   const int acc = it->acc;
-  if (acc & (ACC_A_MOV | ACC_A_ROT)) {
+  const uint32_t own = it->own;
+  if ((acc & (ACC_A_MOV | ACC_A_ROT)) && (int)(own & (Q - 1)) == q) {
     const int r = it->fin_a;
     if (acc & ACC_A_MOV) { WR(E, r) = WR(E, r) + fa.x; WR(E, r + 1) = WR(E, r + 1) + fa.y; }
     if (acc & ACC_A_ROT) WR(E, r + 2) = WR(E, r + 2) + ta;
   }
-  if (acc & (ACC_B_MOV | ACC_B_ROT)) {
+  if ((acc & (ACC_B_MOV | ACC_B_ROT)) && (int)((own >> 16) & (Q - 1)) == q) {
     const int r = it->fin_b;
     if (acc & ACC_B_MOV) { WR(E, r) = WR(E, r) + (-fa.x); WR(E, r + 1) = WR(E, r + 1) + (-fa.y); }
     if (acc & ACC_B_ROT) WR(E, r + 2) = WR(E, r + 2) + tb;

@@ -15,6 +15,10 @@
 //             frc  3 per agent (state.force x y, state.torque; clamped in place, core.py:2017-2040)
 //             lmask one per (sensor, 32-target word)
 //             strig 2 per sensor (cos/sin of the sensing entity's rotation, for the ray cull)
+//             jres 4 per joint, pres 5 per result slot (fx fy ta tb of an evaluated pair, pair index), sv / bp one per 32-pair
+//             block (survivor / verdict bits of the running substep), taint 1
+// A TEAM of Q = NT / TE warps-groups shares the TE columns: thread t works on column t % TE as member q = t / TE and
+// takes the entities / joints / pair blocks / sensors with index = q (mod Q); order-sensitive sums stay with member 0.
 #pragma once
 #include <stdint.h>
 
@@ -68,7 +72,7 @@ struct DItem {              // 16 words; joints first (in reference order), then
   int32_t fr_row;           // env row of the per-env fixed rotation or -1
   int32_t fin_a, fin_b;     // work rows of the (Fx Fy T) accumulators of a / b, or -1 (static entity)
   int32_t acc;              // ACC_* bits
-  int32_t pad;
+  uint32_t own;             // dynamic-entity index (position in dyn_list) of a | of b << 16: who of the team sums it
 };
 static_assert(sizeof(DItem) == 16 * 4, "DItem must be 16 words");
 
@@ -103,6 +107,7 @@ struct DSensor {            // 8 words
   int32_t n_tw;             // words of that mask = ceil(n_targets / 32)
 };
 
+constexpr int kSlots = 8;        // narrow-phase results a team holds per env and round (more survivors = more rounds)
 constexpr int kMaxAgents = 96;   // by-value kernel parameter tables
 
 struct AgentIO {            // kernel parameter (by value)
@@ -120,6 +125,8 @@ struct KParams {            // kernel parameter (by value)
   int32_t NT;               // threads per CTA: TE, or a multiple of it when helper warps share the LIDAR epilogue
   // work rows: [fin 3*n_dyn][trig 4*n_trig][frc 3*A][lmask][strig 2*n_sensors]
   int32_t work_rows, row_fin, row_trig, row_frc, row_lmask, n_lmask_words, row_strig;
+  // team rows: [jres 4*J][sv n_blk][bp n_blk][pres 5*kSlots][taint 1]; n_blk = ceil(P / 32)
+  int32_t row_jres, row_sv, row_bp, row_pres, row_taint, n_blk;
   // device tables
   const DEnt* ents;
   const DItem* items;
