@@ -1,0 +1,4 @@
+for sc in simple_spread navigation; do
+  ncu --set full --import-source on --clock-control none -k regex:step_kernel -s 5 -c 1 -f -o gpurun_out/r1q_$sc python bench.py --scenario $sc --steps 4 --warmup 3 --no-cpu-baseline --no-e2e > /dev/null 2>&1
+done
+ls -la gpurun_out/*.ncu-rep

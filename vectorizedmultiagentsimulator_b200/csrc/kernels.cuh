@@ -111,7 +111,7 @@ VB_DI bool run_substeps(const KParams& kp, const StepArgs& sa, const Tile& t, bo
   if (q == 0) WR(E, kp.row_taint) = 0.f;
   __syncthreads();
 
-  const int n_oct = kp.n_blk * 4;
+  const int n_oct = kp.n_blk * 4, n_real = (kp.P + 7) >> 3;  // octets of the sv / bp words; octets that hold pairs
   for (int s = s_begin; s < s_end; ++s) {
     // ---- joints (core.py:2175, always evaluated), from the last member down (the broad phase starts at member 0)
     for (int j = Q - 1 - q; j < kp.J; j += Q) {
@@ -125,6 +125,7 @@ VB_DI bool run_substeps(const KParams& kp, const StepArgs& sa, const Tile& t, bo
     for (int u = q; u < n_oct; u += Q) {
       uint32_t bpw = 0u, sv = 0u;
       // The table is padded to a multiple of 32 rows with rows that never pass (plan.cpp).
+      if (u < n_real)
 #pragma unroll
       for (int k = 0; k < 8; ++k) {
         // branch-free, so that the bodies interleave: a circle row carries hx = hy = +inf (and any valid trig
@@ -450,12 +451,19 @@ step_kernel(const __grid_constant__ KParams kp, const __grid_constant__ AgentIO 
   if (!s_last) return;
   __threadfence();
   int bad = 0;
-  for (int w = tid; w < nw; w += blockDim.x) bad |= (__ldcg(sa.thin + w) & ~__ldcg(sa.any_exact + w)) != 0u;
+  uint32_t keep = 0u;  // the published word of this thread when one pass covers them all
+  for (int w = tid; w < nw; w += blockDim.x) {
+    const uint32_t th = __ldcg(sa.thin + w), ex = __ldcg(sa.any_exact + w), sp = __ldcg(sa.any_spec + w);
+    bad |= (th & ~ex) != 0u;
+    keep = ex | sp;
+  }
   bad = __syncthreads_or(bad);
-  const int nu = *reinterpret_cast<volatile int*>(sa.counters + 1);
   if (bad) {
+    const int nu = *reinterpret_cast<volatile int*>(sa.counters + 1);
     repair_tainted<CT, TE>(kp, aio, sa, t, flagS, nu);
     for (int w = tid; w < nw; w += blockDim.x) sa.flags_out[w] = flagS[w];
+  } else if (nw <= (int)blockDim.x) {
+    if (tid < nw) sa.flags_out[tid] = keep;
   } else {
     for (int w = tid; w < nw; w += blockDim.x) sa.flags_out[w] = __ldcg(sa.any_exact + w) | __ldcg(sa.any_spec + w);
   }

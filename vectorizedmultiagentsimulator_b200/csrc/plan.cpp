@@ -273,8 +273,9 @@ int build_plan(const vmasb200_world_desc* d, vmasb200_plan* pl) {
   const int per_env = 4 * (kp.dyn_rows + kp.stat_rows + kp.work_rows + 2 * kp.lidar_rows + kp.n_sensors) + 20;
   const int fixed = 64 + 4 * kp.S * kp.pair_words;
   int TE = d->envs_per_cta;
-  if (TE == 0) TE = 32;  // 4 team members per env: the shortest critical path and the most warps per byte of smem
-  if (TE != 32 && TE != 64 && TE != 128) { set_error("envs_per_cta must be 32, 64 or 128"); return VMASB200_ERR_INVALID; }
+  if (TE != 0 && TE != 32 && TE != 64 && TE != 128) { set_error("envs_per_cta must be 0, 32, 64 or 128"); return VMASB200_ERR_INVALID; }
+  pl->te_fixed = TE;
+  if (TE == 0) TE = 32;  // the launch picks 32 or 64 by batch size (vmasb200.cu tile_for)
   if (fixed + TE * per_env > 226 * 1024) { set_error("world too large for one CTA's shared memory"); return VMASB200_ERR_UNSUPPORTED; }
   kp.TE = TE;
   kp.NT = 128;  // Q = 128 / TE team members per env

@@ -22,6 +22,13 @@
 
 namespace vb {
 
+// eval_item has three call sites (joints, pair survivors, repair); out of line keeps the hot path's code compact
+#ifdef VB_EVAL_INLINE
+#define VB_EVAL VB_DI
+#else
+#define VB_EVAL __device__ __noinline__
+#endif
+
 // ---------------------------------------------------------------------------------------- TMA / mbarrier PTX
 VB_DI uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 VB_DI void mbar_init(uint64_t* bar, int count) {
@@ -156,7 +163,7 @@ VB_DI void begin_forces(const KParams& kp, const DEnt* __restrict__ en, const EV
 // One work item (joint constraint or candidate pair): force on a (the force on b is its exact negation) and the
 // two torques.  `type` is warp-uniform, so the switch does not diverge.
 template <bool CT, class EV>
-VB_DI void eval_item(const KParams& kp, const DItem* __restrict__ it, const EV& E, V2& fa, float& ta, float& tb) {
+VB_EVAL void eval_item(const KParams& kp, const DItem* __restrict__ it, const EV& E, V2& fa, float& ta, float& tb) {
   const int type = it->type;
   const DEnt* __restrict__ ea = &T_ent<CT>(kp, it->a);
   const DEnt* __restrict__ eb = &T_ent<CT>(kp, it->b);

@@ -69,7 +69,6 @@ int upload_plan(vmasb200_plan* pl) {
   const size_t nbits = (4 * bits_words(kp) + 4) * sizeof(uint32_t);
   VB_CUDA(cudaMalloc(&pl->d_bits, nbits));
   VB_CUDA(cudaMemset(pl->d_bits, 0, nbits));
-  pl->smem_bytes = smem_map(kp).total_bytes;
   for (int ct = 0; ct < 2; ++ct)
     for (int te : {32, 64, 128})
       VB_CUDA(cudaFuncSetAttribute(step_fn(ct != 0, te), cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
@@ -132,12 +131,27 @@ static int bind_const(vmasb200_plan* pl, cudaStream_t st, bool* ct) {
   return VMASB200_OK;
 }
 
+// CTA tile of a step over n environments (measured on B200, profiles/README.md): 4-member teams on 32 envs while that
+// fills the GPU in about one wave - the shortest critical path; beyond, throughput counts: whole-env threads (128 envs
+// per CTA, no work shared, fewest barriers) when two such CTAs fit an SM and there is no LIDAR epilogue to share,
+// else 2-member teams on 64 envs.
+static int tile_for(const vmasb200_plan* pl, long long n) {
+  if (pl->te_fixed) return pl->te_fixed;
+  auto smem = [&](int te) { KParams k = pl->kp; k.TE = te; return smem_map(k).total_bytes; };
+  if (n <= 48 * 1024) return 32;
+  if (!pl->kp.n_rays && smem(128) <= 113 * 1024) return 128;
+  return smem(64) <= 226 * 1024 ? 64 : 32;
+}
+
 // Envs [env_begin, env_end) of one World.step on stream io->stream.  A step may be issued as several such launches
-// (on different streams); together they must cover total_ctas CTAs: the CTA that finishes last - of ALL launches -
+// (on different streams); together they must cover the whole batch: the CTA that finishes last - of ALL launches -
 // verifies the speculation over the whole batch.  env_begin must be a multiple of the CTA tile.
-static int launch_step(vmasb200_plan* pl, const vmasb200_step_io* io, long long env_begin, long long env_end,
-                       unsigned total_ctas) {
-  const KParams& kp = pl->kp;
+static int launch_step(vmasb200_plan* pl, const vmasb200_step_io* io, long long env_begin, long long env_end) {
+  KParams kp = pl->kp;
+  kp.TE = tile_for(pl, io->n_envs);
+  // every launch boundary of a chunked step is a multiple of the tile
+  const long long total_ctas = (io->n_envs + kp.TE - 1) / kp.TE;
+  const int smem_bytes = smem_map(kp).total_bytes;
   cudaStream_t st = static_cast<cudaStream_t>(io->stream);
   AgentIO aio;
   std::memset(&aio, 0, sizeof(aio));
@@ -169,7 +183,7 @@ static int launch_step(vmasb200_plan* pl, const vmasb200_step_io* io, long long 
       }
       sa.s_begin = s; sa.s_end = s + 1; sa.flags_in = flags;
       sa.do_lidar = (s == kp.S - 1);
-      step_fn(ct, kp.TE)<<<grid, block, pl->smem_bytes, st>>>(kp, aio, sa);
+      step_fn(ct, kp.TE)<<<grid, block, smem_bytes, st>>>(kp, aio, sa);
       sa.dyn_in = io->dyn_out;
     }
   } else {
@@ -183,7 +197,7 @@ static int launch_step(vmasb200_plan* pl, const vmasb200_step_io* io, long long 
     }
     sa.u_list = pl->d_ulist; sa.u_buf = pl->d_ubuf;
     sa.s_begin = 0; sa.s_end = kp.S; sa.flags_in = nullptr; sa.do_lidar = 1;
-    step_fn(ct, kp.TE)<<<grid, block, pl->smem_bytes, st>>>(kp, aio, sa);
+    step_fn(ct, kp.TE)<<<grid, block, smem_bytes, st>>>(kp, aio, sa);
   }
   if (ct) VB_CUDA(cudaEventRecord(g_const[pl->device].last_use, st));
   if (io->pair_active_out && nw) VB_CUDA(cudaMemcpyAsync(io->pair_active_out, flags, nw * sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
@@ -265,8 +279,7 @@ int vmasb200_step(vmasb200_plan* pl, const vmasb200_step_io* io) {
   if (rc) return rc;
   if ((rc = upload_plan(pl))) return rc;
   if (io->n_envs == 0 || pl->kp.n_dyn == 0) return VMASB200_OK;
-  const unsigned ctas = (unsigned)((io->n_envs + pl->kp.TE - 1) / pl->kp.TE);
-  return launch_step(pl, io, 0, io->n_envs, ctas);
+  return launch_step(pl, io, 0, io->n_envs);
 }
 
 static int grow_host_staging(vmasb200_plan* pl, int64_t ld) {
@@ -305,8 +318,6 @@ int vmasb200_step_host(vmasb200_plan* pl, const float* h_dyn_in, const float* h_
   int64_t nchunk = exact ? 1 : std::min<int64_t>(kHostStreams, (n + 8191) / 8192);
   int64_t csize = ((n + nchunk - 1) / nchunk + 255) & ~int64_t(255);
   nchunk = (n + csize - 1) / csize;
-  const unsigned total_ctas = (unsigned)((n + kp.TE - 1) / kp.TE);
-
   const float* fptr[kMaxAgents]; const float* tptr[kMaxAgents];
   int64_t fstr[kMaxAgents], tstr[kMaxAgents];
   for (int a = 0; a < kp.A; ++a) {  // h_force [n][A][2], h_torque [n][A]
@@ -341,7 +352,7 @@ int vmasb200_step_host(vmasb200_plan* pl, const float* h_dyn_in, const float* h_
     io.act_out = kp.act_rows ? pl->d_act : nullptr;
     io.lidar_out = want_lidar ? pl->d_lidar : nullptr;
     io.pair_active_out = nullptr; io.n_envs = n; io.ld = dld; io.exact = exact; io.stream = st;
-    if (kp.n_dyn && (rc = launch_step(pl, &io, c0, c1, total_ctas))) return rc;
+    if (kp.n_dyn && (rc = launch_step(pl, &io, c0, c1))) return rc;
     if ((rc = d2h(c0, ncol, st))) return rc;
   }
   for (int64_t k = 0; k < std::min<int64_t>(nchunk, kHostStreams); ++k) VB_CUDA(cudaStreamSynchronize(pl->streams[k]));
