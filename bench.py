@@ -90,6 +90,16 @@ def peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def ncu_traffic(scenario, n):
+    """dram__bytes_read.sum + dram__bytes_write.sum of one step_kernel launch, from the committed ncu --set full capture
+    of this workload (profiles/r1_traffic.json, written by tools/profile_round.sh); None when it was not captured."""
+    try:
+        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r1_traffic.json")) as f:
+            return json.load(f).get(f"{scenario}@{n}", {}).get("dram_bytes")
+    except (OSError, ValueError):
+        return None
+
+
 def cpu_port_rate(wl, seconds=8.0, n_sample=None, threads=0):
     """The C oracle (oracle/vmas_oracle.c: scalar port of the reference step, OpenMP over envs) timed on the host."""
     from oracle.oracle import Oracle
@@ -271,11 +281,11 @@ def run_b200(args, rank, local_rank, world):
             "data": "synthetic",
             "config": {"workload": f"{args.scenario} num_envs={n} per GPU, substeps={plan.S}, {len(wl.desc.lidars)} lidars",
                        "l2": f"{R} env batches visited round-robin, working set {R * per_batch / 2**20:.0f} MiB > L2 126 MiB",
-                       "envs_per_cta": plan.envs_per_cta, "layout": "SoA rows [field][env], one thread per env",
+                       "envs_per_cta": plan.tile_for(n), "layout": "SoA rows [field][env]; 128 threads per CTA, 128 / envs_per_cta of them share an env",
                        "exact": int(args.exact), "speculation_repairs": repairs,
                        "l2_resident_ms_per_step": ms_hot / K},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "peak_source": peak_src, "alg_bytes_per_env": plan.alg_bytes_per_env,
+                         "traffic": ncu_traffic(args.scenario, n), "peak_source": peak_src, "alg_bytes_per_env": plan.alg_bytes_per_env,
                          "kernel": "vb::step_kernel"},
             "gpu_launches": K * (2 * plan.S if args.exact else 1),
             "clocks": clocks,

@@ -139,7 +139,8 @@ typedef struct vmasb200_world_desc {
   float x_semidim, y_semidim;
   float collision_force, joint_force, torque_constraint_force, contact_margin;
   float gravity[2];
-  /* Kernel shape override: environments (= threads) per CTA, 32, 64 or 128; 0 = let the plan choose. */
+  /* Kernel shape override: environments per CTA, 32, 64 or 128 (a CTA has 128 threads: 4, 2 or 1 of them share an
+   * environment's work); 0 = chosen per step from the batch size (vmasb200_plan_tile). */
   int32_t envs_per_cta;
 } vmasb200_world_desc;
 
@@ -154,7 +155,7 @@ typedef struct vmasb200_layout {
   int32_t dyn_rows, stat_rows, act_rows, lidar_rows; /* rows of the four SoA buffers                     */
   int32_t n_pairs;        /* candidate pairs, in flag-bit order (ss, ls, ll, bs, bl, bb; a<b inside)     */
   int32_t pair_words;     /* ceil(n_pairs/32): words per substep in pair_active_out                      */
-  int32_t envs_per_cta;   /* kernel shape actually chosen                                                 */
+  int32_t envs_per_cta;   /* the description's override, or 32 (smallest tile) when 0; see vmasb200_plan_tile */
   int32_t n_dyn, n_stat, n_agents, n_act_out;
   int64_t alg_bytes_per_env; /* algorithmic HBM bytes per env-step (SURVEY 8d formula)                    */
 } vmasb200_layout;
@@ -179,6 +180,9 @@ int vmasb200_plan_pairs(const vmasb200_plan* plan, vmasb200_pair* pairs);
 int vmasb200_plan_joint_slots(const vmasb200_plan* plan, int32_t* joint_slot);
 /* first row inside the lidar buffer of sensor i. h: [n_lidars] */
 int vmasb200_plan_lidar_slots(const vmasb200_plan* plan, int32_t* lidar_slot);
+/* environments per CTA a step over n_envs environments runs with (32, 64 or 128): the description's envs_per_cta,
+ * or, when that is 0, chosen from the batch size.  128 / tile threads share each environment's work. */
+int vmasb200_plan_tile(const vmasb200_plan* plan, int64_t n_envs);
 
 typedef struct vmasb200_step_io {
   const float* dyn_in;             /* d: [dyn_rows][ld]                                                 */

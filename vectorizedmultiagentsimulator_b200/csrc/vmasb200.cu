@@ -273,6 +273,8 @@ int vmasb200_plan_lidar_slots(const vmasb200_plan* pl, int32_t* lidar_slot) {
   return VMASB200_OK;
 }
 
+int vmasb200_plan_tile(const vmasb200_plan* pl, int64_t n_envs) { return pl ? tile_for(pl, n_envs) : 0; }
+
 int vmasb200_step(vmasb200_plan* pl, const vmasb200_step_io* io) {
   if (!pl) { set_error("step: NULL plan"); return VMASB200_ERR_INVALID; }
   int rc = check_io(pl, io);

@@ -172,6 +172,10 @@ class StepPlan:
         _lib.check(rc, "vmasb200_cast_rays")
         return out
 
+    def tile_for(self, n_envs: int) -> int:
+        """Environments per CTA a step over n_envs environments runs with (vmasb200_plan_tile)."""
+        return int(_lib.lib().vmasb200_plan_tile(self._h, int(n_envs)))
+
     def sync_check(self, stream: int = 0) -> int:
         nf = C.c_int64(0)
         _lib.check(_lib.lib().vmasb200_sync_check(self._h, stream, C.byref(nf)), "vmasb200_sync_check")
