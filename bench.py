@@ -90,14 +90,15 @@ def peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def ncu_traffic(scenario, n):
-    """dram__bytes_read.sum + dram__bytes_write.sum of one step_kernel launch, from the committed ncu --set full capture
-    of this workload (profiles/r1_traffic.json, written by tools/profile_round.sh); None when it was not captured."""
+def ncu_capture(scenario, n):
+    """What the committed `ncu --set full` capture of this workload says about one step_kernel launch
+    (profiles/r1_traffic.json, written by tools/profile_collect.py): dram_bytes = dram__bytes_read.sum +
+    dram__bytes_write.sum, warp_inst = smsp__inst_executed.sum.  {} when the workload was not captured."""
     try:
-        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r1_traffic.json")) as f:
-            return json.load(f).get(f"{scenario}@{n}", {}).get("dram_bytes")
+        with open(os.path.join(ROOT, "profiles", "r1_traffic.json")) as f:
+            return json.load(f).get(f"{scenario}@{n}", {})
     except (OSError, ValueError):
-        return None
+        return {}
 
 
 def cpu_port_rate(wl, seconds=8.0, n_sample=None, threads=0):
@@ -273,6 +274,7 @@ def run_b200(args, rank, local_rank, world):
         e2e = run_e2e(plan, wl, n, K, world, dev)
     if rank == 0:
         peak, peak_src = peaks()
+        cap = ncu_capture(args.scenario, n)
         alg = plan.alg_bytes_per_env * n
         achieved = alg / (ms / K * 1e-3) / 1e9
         line = {
@@ -285,11 +287,18 @@ def run_b200(args, rank, local_rank, world):
                        "exact": int(args.exact), "speculation_repairs": repairs,
                        "l2_resident_ms_per_step": ms_hot / K},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": ncu_traffic(args.scenario, n), "peak_source": peak_src, "alg_bytes_per_env": plan.alg_bytes_per_env,
+                         "traffic": cap.get("dram_bytes"), "peak_source": peak_src, "alg_bytes_per_env": plan.alg_bytes_per_env,
                          "kernel": "vb::step_kernel"},
             "gpu_launches": K * (2 * plan.S if args.exact else 1),
             "clocks": clocks,
         }
+        if cap.get("warp_inst"):
+            # the bound that actually binds: warp instructions of one launch (ncu) over the live launch
+            # time, against 4 issue slots x 148 SMs at the SM clock sampled during the timed region
+            mhz = (clocks or {}).get("sm_mhz") or 1965.0
+            ips = cap["warp_inst"] / (ms / K * 1e-3)
+            line["roofline"]["issue"] = {"warp_inst_per_launch": cap["warp_inst"], "achieved_ginst_s": ips / 1e9,
+                                         "peak_ginst_s": 4 * 148 * mhz * 1e-3, "frac": ips / (4 * 148 * mhz * 1e6)}
         if e2e is not None:
             line["e2e"] = e2e
         if world == 1 and not args.no_cpu_baseline:

@@ -123,3 +123,35 @@ def test_repair_path_is_exercised():
         f, tq = _forces(fx, t)
         pl.step_host(dyn, stat, f, tq, exact=False)
     assert pl.sync_check() > 0
+
+
+@pytest.mark.parametrize("name", ALL)
+def test_tiles_agree_bitwise(name):
+    """The CTA tile (32 / 64 / 128 envs, i.e. 4 / 2 / 1 threads sharing an env) only changes who computes what: every
+    accumulator receives its addends in the reference's order, so all three must give the same bits - also through the
+    repair path (speculative) and with the tile chosen from the batch size (0)."""
+    import copy
+
+    fx = Fixture(name)
+    reps = 12
+    plans = []
+    for te in (0, 32, 64, 128):
+        d = copy.copy(fx.desc)
+        d.envs_per_cta = te
+        plans.append(StepPlan(d))
+    assert plans[0].tile_for(1000) == 32 and plans[2].tile_for(1 << 20) == 64 and plans[0].tile_for(1 << 20) in (64, 128)
+    for state_in, t, k in fx.one_step_cases()[:3]:
+        st = np.ascontiguousarray(np.tile(state_in, (1, reps, 1)))
+        jr = fx.jrot_at(t)
+        jr = np.tile(jr, (1, reps)) if jr.size else jr
+        f, tq = _forces(fx, t)
+        f, tq = np.ascontiguousarray(np.tile(f, (reps, 1, 1))), np.ascontiguousarray(np.tile(tq, (reps, 1)))
+        for exact in (False, True):
+            outs = []
+            for pl in plans:
+                dyn, stat = pl.pack(st, jr)
+                outs.append(pl.step_host(dyn, stat, f, tq, exact=exact))
+            for o in outs[1:]:
+                for x, y, what in zip(outs[0], o, ("dyn", "act", "lidar", "masks")):
+                    if x is not None:
+                        assert np.array_equal(x.view(np.uint32), y.view(np.uint32)), f"{name} t={t} exact={exact}: {what} differs"

@@ -91,6 +91,7 @@ def main():
         rd, wr = to_bytes(*m["dram__bytes_read.sum"]), to_bytes(*m["dram__bytes_write.sum"])
         scen, n = (wl[:-3], 1048576) if wl.endswith("_1m") else (wl, 32768)
         traffic[f"{scen}@{n}"] = {"dram_bytes": rd + wr, "dram_read": rd, "dram_write": wr, "grid": grid,
+                                  "warp_inst": float(m["smsp__inst_executed.sum"][0].replace(",", "")),
                                   "duration": " ".join(m["gpu__time_duration.sum"]),
                                   "source": f"profiles/{tag}_step_kernel_{wl}.txt"}
     if traffic:
