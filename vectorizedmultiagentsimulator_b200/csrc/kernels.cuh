@@ -4,11 +4,15 @@
 // the pair is evaluated: World.collides ends in (||p_a - p_b|| <= Rc_a + Rc_b).any() over envs (core.py:2796-2800).
 // The fused kernel considers every pair in every env.  That differs from the reference only for an env whose own
 // verdict is false while its force is non-zero ("thin" event: contact through the LINE_MIN_DIST shell at a box
-// corner / line end) AND no env of the batch has a true verdict.  Each env therefore tracks a taint bit (set after
-// its first thin event); untainted envs OR their verdicts into any_exact, tainted ones into any_spec.  The last CTA
-// to finish checks thin & ~any_exact == 0, which proves (by induction over substeps) that every env equals the
-// reference; otherwise it re-simulates only the tainted envs from their saved input state, substep by substep,
-// with flags = any_exact | OR over the re-simulated envs' verdicts - which is exactly the reference's flag.
+// corner / line end) AND no env of the batch has a true verdict.  Each env therefore tracks a taint (set after its
+// first thin event); untainted envs OR their verdicts into any_exact, tainted ones into any_spec and, per env, into a
+// record (u_verd) next to the record of their thin events (u_thin).  The last CTA to finish checks
+// thin & ~any_exact == 0, which proves (by induction over substeps) that every env equals the reference.  Otherwise
+// it walks the substeps once (validate_speculation): an env whose thin events so far were all on pairs that exact
+// sources activate is exact itself, so its verdicts join the exact flags of the next substep; the envs left over -
+// typically the one or two whose thin force the reference would really have skipped - are re-simulated from their
+// saved input state, substep by substep, with flags = exact flags | the re-simulated envs' verdicts, which is exactly
+// the reference's flag.
 #pragma once
 #include "step_kernel.cuh"
 
@@ -31,8 +35,12 @@ struct StepArgs {
   uint32_t* any_spec;        // [S][pair_words]
   uint32_t* thin;            // [S][pair_words]
   int* counters;             // [0] finished CTAs, [1] tainted envs, [2] repairs done since plan creation
-  int* u_list;               // [n_envs] env index of every tainted env
+  int* u_list;               // [n_envs] env index of every tainted env (bit 31: to be re-simulated)
   float* u_buf;              // [n_envs][dyn_rows] their input state (then their evolving state)
+  int* u_rep;                // [n_envs] indices into u_list of the envs to re-simulate
+  uint32_t* u_verd;          // [rec_cap][S][pair_words] verdicts of tainted env i from its taint on
+  uint32_t* u_thin;          // [rec_cap][S][pair_words] its thin events
+  int rec_cap;               // tainted envs beyond this have no record and are re-simulated when anything is
   int do_lidar;
 };
 
@@ -86,13 +94,15 @@ VB_DI void load_forces(const KParams& kp, const AgentIO& aio, const EV& E, long 
 
 // Substeps [s_begin, s_end) of the tile.  EVERY thread of the CTA calls this (CTA barriers inside): thread t is
 // member q = t / TE of the team of column t % TE.  flags: batch-wide verdicts to obey (smem or global), or NULL =
-// speculative (every pair considered; verdict / thin bits OR-ed into sa.any_exact / any_spec / thin).
+// speculative (every pair considered; verdict / thin bits OR-ed into sa.any_exact / any_spec / thin).  collect (= flags,
+// shared memory): the tile's own verdicts are OR-ed into the flags before they are obeyed (a tile that holds every env
+// whose verdicts are still missing from the flags).
 // Work split of a substep (tables.h): joints, 8-pair slices of the broad phase, narrow-phase survivors (in the env's
 // pair order, survivor i to member i mod Q), then per dynamic entity the ordered sum of its forces + integration.
-// Returns the column's taint.
+// env: index of the column's environment.  Returns the column's taint: 0, or 1 + its index in sa.u_list.
 template <bool CT, int TE>
-VB_DI bool run_substeps(const KParams& kp, const StepArgs& sa, const Tile& t, bool ok, int s_begin, int s_end,
-                        const uint32_t* flags) {
+VB_DI int run_substeps(const KParams& kp, const StepArgs& sa, const Tile& t, bool ok, long long env, int s_begin,
+                       int s_end, const uint32_t* flags, uint32_t* collect = nullptr) {
   constexpr int Q = kThreads / TE;
   constexpr int R = kSlots / Q;     // survivors a member evaluates per round
   const int col = threadIdx.x % TE, q = threadIdx.x / TE;
@@ -108,7 +118,10 @@ VB_DI bool run_substeps(const KParams& kp, const StepArgs& sa, const Tile& t, bo
   // that earlier launches of a split step already did
   for (int d = q; d < kp.n_dyn; d += Q)
     for (int rep = 0; rep <= s_begin; ++rep) begin_forces(kp, &T_ent<CT>(kp, T_dyn<CT>(kp, d)), E);
-  if (q == 0) WR(E, kp.row_taint) = 0.f;
+  if (q == 0) {
+    WR(E, kp.row_taint) = 0.f;
+    for (int b = 0; b <= kp.n_blk; ++b) WR(E, kp.row_th + b) = 0.f;
+  }
   __syncthreads();
 
   const int n_oct = kp.n_blk * 4, n_real = (kp.P + 7) >> 3;  // octets of the sv / bp words; octets that hold pairs
@@ -121,7 +134,8 @@ VB_DI bool run_substeps(const KParams& kp, const StepArgs& sa, const Tile& t, bo
       WR(E, r) = fa.x; WR(E, r + 1) = fa.y; WR(E, r + 2) = ta; WR(E, r + 3) = tb;
     }
     // ---- broad phase, 8 candidate pairs at a time
-    const bool tainted = WR(E, kp.row_taint) != 0.f;
+    const int tix = __float_as_int(WR(E, kp.row_taint));
+    const bool tainted = tix != 0;
     for (int u = q; u < n_oct; u += Q) {
       uint32_t bpw = 0u, sv = 0u;
       // The table is padded to a multiple of 32 rows with rows that never pass (plan.cpp).
@@ -143,8 +157,11 @@ VB_DI bool run_substeps(const KParams& kp, const StepArgs& sa, const Tile& t, bo
       const uint32_t valid = n >= 8 ? 0xffu : (n > 0 ? (1u << n) - 1u : 0u);
       bpw &= valid; sv &= valid;
       const int w = s * kp.pair_words + (u >> 2), sh = 8 * (u & 3);
-      if (flags) {
-        sv &= flags[w] >> sh;
+      if (flags) {  // obeyed when the survivors are taken up below
+        if (collect) {
+          const uint32_t e = __reduce_or_sync(0xffffffffu, ok ? bpw : 0u) << sh;
+          if (lane == 0 && (e & ~collect[w])) atomicOr(collect + w, e);
+        }
       } else {
         const uint32_t e = __reduce_or_sync(0xffffffffu, (ok && !tainted) ? bpw : 0u);
         const uint32_t sp = __reduce_or_sync(0xffffffffu, (ok && tainted) ? bpw : 0u);
@@ -152,6 +169,8 @@ VB_DI bool run_substeps(const KParams& kp, const StepArgs& sa, const Tile& t, bo
           if (e) or_global(sa.any_exact + w, e << sh);
           if (sp) or_global(sa.any_spec + w, sp << sh);
         }
+        if (ok && tainted && tix <= sa.rec_cap)
+          reinterpret_cast<uint8_t*>(sa.u_verd + ((size_t)(tix - 1) * kp.S + s) * kp.pair_words + (u >> 2))[u & 3] = (uint8_t)bpw;
       }
       if (!ok) sv = 0u;
       reinterpret_cast<uint8_t*>(&WR(E, kp.row_sv + (u >> 2)))[u & 3] = (uint8_t)sv;
@@ -166,6 +185,7 @@ VB_DI bool run_substeps(const KParams& kp, const StepArgs& sa, const Tile& t, bo
       for (int r = 0; r < R; ++r) task[r] = -1;
       for (int b = 0; b < kp.n_blk; ++b) {
         uint32_t m = __float_as_uint(WR(E, kp.row_sv + b));
+        if (flags) m &= flags[s * kp.pair_words + b];
         while (m) {
           const int k = __ffs(m) - 1;
           m &= m - 1u;
@@ -187,7 +207,8 @@ VB_DI bool run_substeps(const KParams& kp, const StepArgs& sa, const Tile& t, bo
           if (!flags && (fa.x != 0.f || fa.y != 0.f) &&
               !((__float_as_uint(WR(E, kp.row_bp + (p >> 5))) >> (p & 31)) & 1u)) {
             or_global(sa.thin + s * kp.pair_words + (p >> 5), 1u << (p & 31));
-            WR(E, kp.row_taint) = 1.f;  // read by the NEXT substep's broad phase
+            atomicOr(reinterpret_cast<uint32_t*>(&WR(E, kp.row_th + 1 + (p >> 5))), 1u << (p & 31));
+            WR(E, kp.row_th) = 1.f;  // member 0 files the substep's thin events below
           }
         }
       }
@@ -212,9 +233,29 @@ VB_DI bool run_substeps(const KParams& kp, const StepArgs& sa, const Tile& t, bo
       integrate(kp, en, E, s);
       if (s + 1 < s_end) begin_forces(kp, en, E);
     }
+    // ---- thin events of this substep: the env is tainted from the NEXT substep on and keeps a record
+    if (!flags && q == 0 && WR(E, kp.row_th) != 0.f) {
+      int tx = __float_as_int(WR(E, kp.row_taint));
+      const size_t rw = (size_t)kp.S * kp.pair_words;
+      if (tx == 0) {
+        tx = atomicAdd(sa.counters + 1, 1) + 1;
+        sa.u_list[tx - 1] = (int)env;
+        WR(E, kp.row_taint) = __int_as_float(tx);
+        if (tx <= sa.rec_cap)
+          for (size_t i = 0; i < rw; ++i) { sa.u_verd[(tx - 1) * rw + i] = 0u; sa.u_thin[(tx - 1) * rw + i] = 0u; }
+      }
+      for (int b = 0; b < kp.n_blk; ++b) {
+        const uint32_t w = __float_as_uint(WR(E, kp.row_th + 1 + b));
+        if (w) {
+          if (tx <= sa.rec_cap) sa.u_thin[(tx - 1) * rw + (size_t)s * kp.pair_words + b] = w;
+          WR(E, kp.row_th + 1 + b) = 0.f;
+        }
+      }
+      WR(E, kp.row_th) = 0.f;
+    }
     __syncthreads();
   }
-  return WR(E, kp.row_taint) != 0.f;
+  return __float_as_int(WR(E, kp.row_taint));
 }
 
 // LIDAR epilogue for the whole tile (every thread of the CTA calls it, helper warps included; contains CTA barriers).
@@ -307,23 +348,80 @@ VB_DI void lidar_epilogue(const KParams& kp, const Tile& t, int n_cols) {
   __syncthreads();
 }
 
-// Re-simulation of the tainted envs by the last CTA (rare path; see the header comment).  flagS (smem, [S][pair_words])
-// starts as any_exact and ends as the reference's verdicts.  u_buf holds the evolving state of tainted env `idx` as
-// dyn_rows consecutive floats; each thread works on one tainted env at a time in its own tile column.
+// One pass over the substeps by the last CTA (rare path; see the header comment): which tainted envs are exact anyway.
+// flagS (smem, [S][pair_words]) ends as any_exact | the verdicts of those envs; the others are listed in sa.u_rep.
+// Returns how many those are.
+__device__ __noinline__ int validate_speculation(const KParams& kp, const StepArgs& sa, uint32_t* flagS, int nu) {
+  __shared__ int s_nd;
+  const int tid = threadIdx.x, nthr = blockDim.x;
+  const int pw = kp.pair_words, nw = kp.S * pw;
+  for (int w = tid; w < nw; w += nthr) flagS[w] = __ldcg(sa.any_exact + w);
+  if (tid == 0) s_nd = 0;
+  const int nrec = min(nu, sa.rec_cap);
+  for (int i = nrec + tid; i < nu; i += nthr) sa.u_list[i] |= 0x80000000;  // no record: cannot be cleared
+  __syncthreads();
+  for (int s = 0; s < kp.S; ++s) {
+    // verdicts of the envs that are exact up to here are reference verdicts
+    for (int i = tid; i < nrec; i += nthr)
+      if (sa.u_list[i] >= 0)
+        for (int w = 0; w < pw; ++w) {
+          const uint32_t v = __ldcg(sa.u_verd + ((size_t)i * kp.S + s) * pw + w);
+          if (v & ~flagS[s * pw + w]) atomicOr(flagS + s * pw + w, v);
+        }
+    __syncthreads();
+    // a thin event on a pair nobody exact activates: the env leaves the reference's trajectory after this substep
+    for (int i = tid; i < nrec; i += nthr)
+      if (sa.u_list[i] >= 0) {
+        bool off = false;
+        for (int w = 0; w < pw; ++w) off = off || (__ldcg(sa.u_thin + ((size_t)i * kp.S + s) * pw + w) & ~flagS[s * pw + w]);
+        if (off) sa.u_list[i] |= 0x80000000;
+      }
+    __syncthreads();
+  }
+  for (int i = tid; i < nu; i += nthr)
+    if (sa.u_list[i] < 0) {
+      sa.u_list[i] &= 0x7fffffff;
+      sa.u_rep[atomicAdd(&s_nd, 1)] = i;
+    }
+  __syncthreads();
+  return s_nd;
+}
+
+// Re-simulation of the nd envs listed in sa.u_rep by the last CTA.  flagS comes from validate_speculation and ends as
+// the reference's verdicts.  u_buf holds the evolving state of tainted env `idx` as dyn_rows consecutive floats; each
+// team works on one of them at a time in its own tile column.
 template <bool CT, int TE>
 __device__ __noinline__ void repair_tainted(const KParams& kp, const AgentIO& aio, const StepArgs& sa, const Tile& t,
-                                            uint32_t* flagS, int nu) {
+                                            uint32_t* flagS, int nd) {
   constexpr int Q = kThreads / TE;
   const int tid = threadIdx.x, nthr = blockDim.x;
   const int col = tid % TE, q = tid / TE;
-  const int nw = kp.S * kp.pair_words;
   const EnvT<TE> E = env_view<TE>(t, col);
-  for (int w = tid; w < nw; w += nthr) flagS[w] = __ldcg(sa.any_exact + w);
-  __syncthreads();
+  if (nd <= TE) {
+    // the usual case, one tile: it stays in shared memory for all substeps and adds its own verdicts to the flags
+    const bool ok = col < nd;
+    const int idx = ok ? sa.u_rep[col] : 0;
+    const long long env = ok ? sa.u_list[idx] : 0;
+    if (ok) {
+      for (int r = q; r < kp.dyn_rows; r += Q) ER(E, r) = sa.u_buf[(size_t)idx * kp.dyn_rows + r];
+      for (int r = q; r < kp.stat_rows; r += Q) ER(E, kp.dyn_rows + r) = sa.stat[(size_t)r * sa.ld + env];
+      load_forces(kp, aio, E, env, q, Q);
+    }
+    run_substeps<CT, TE>(kp, sa, t, ok, env, 0, kp.S, flagS, flagS);
+    if (sa.lidar_out && kp.n_rays) lidar_epilogue<CT, TE>(kp, t, nd);
+    if (ok) {
+      for (int r = q; r < kp.dyn_rows; r += Q) sa.dyn_out[(size_t)r * sa.ld + env] = ER(E, r);
+      if (sa.lidar_out)
+        for (int r = q; r < kp.lidar_rows; r += Q) sa.lidar_out[(size_t)r * sa.ld + env] = t.lidS[r * TE + col];
+    }
+    __syncthreads();
+    return;
+  }
   for (int s = 0; s <= kp.S; ++s) {  // s == S: LIDAR + write-back pass
     if (s < kp.S) {
       // pass 1: verdicts of the tainted envs at their true state
-      for (int idx = tid; idx < nu; idx += nthr) {
+      for (int i = tid; i < nd; i += nthr) {
+        const int idx = sa.u_rep[i];
         const float* dyn = sa.u_buf + (size_t)idx * kp.dyn_rows;
         const long long env = sa.u_list[idx];
         auto px = [&](int row, int k) {
@@ -342,9 +440,9 @@ __device__ __noinline__ void repair_tainted(const KParams& kp, const AgentIO& ai
       __syncthreads();
     }
     // pass 2: one substep with the now exact flags (or the epilogue), a tile of TE tainted envs at a time
-    for (int base = 0; base < nu; base += TE) {
-      const int idx = base + col;
-      const bool ok = idx < nu;
+    for (int base = 0; base < nd; base += TE) {
+      const bool ok = base + col < nd;
+      const int idx = ok ? sa.u_rep[base + col] : 0;
       const long long env = ok ? sa.u_list[idx] : 0;
       if (ok) {
         for (int r = q; r < kp.dyn_rows; r += Q) ER(E, r) = sa.u_buf[(size_t)idx * kp.dyn_rows + r];
@@ -353,11 +451,11 @@ __device__ __noinline__ void repair_tainted(const KParams& kp, const AgentIO& ai
       }
       const bool last = s == kp.S;
       // s == S: prologue only (cos/sin cache, clamps)
-      run_substeps<CT, TE>(kp, sa, t, ok, s, last ? s : s + 1, flagS);
+      run_substeps<CT, TE>(kp, sa, t, ok, env, s, last ? s : s + 1, flagS);
       if (!last) {
         if (ok) for (int r = q; r < kp.dyn_rows; r += Q) sa.u_buf[(size_t)idx * kp.dyn_rows + r] = ER(E, r);
       } else {
-        if (sa.lidar_out && kp.n_rays) lidar_epilogue<CT, TE>(kp, t, min(TE, nu - base));
+        if (sa.lidar_out && kp.n_rays) lidar_epilogue<CT, TE>(kp, t, min(TE, nd - base));
         if (ok) {
           for (int r = q; r < kp.dyn_rows; r += Q) sa.dyn_out[(size_t)r * sa.ld + env] = ER(E, r);
           if (sa.lidar_out)
@@ -416,13 +514,12 @@ step_kernel(const __grid_constant__ KParams kp, const __grid_constant__ AgentIO 
   const EnvT<TE> E = env_view<TE>(t, col);
   if (ok) load_forces(kp, aio, E, env0 + col, q, Q);
   mbar_wait(bar, 0);
-  const bool tainted = run_substeps<CT, TE>(kp, sa, t, ok, sa.s_begin, sa.s_end, sa.flags_in);
+  const int taint = run_substeps<CT, TE>(kp, sa, t, ok, env0 + col, sa.s_begin, sa.s_end, sa.flags_in);
   const bool lidar = sa.do_lidar && sa.lidar_out && kp.n_rays;
   if (lidar) lidar_epilogue<CT, TE>(kp, t, n_valid);
 
-  if (spec && tainted && ok && q == 0) {  // keep the INPUT state of a tainted env (dyn_in is intact until our own store)
-    const int idx = atomicAdd(sa.counters + 1, 1);
-    sa.u_list[idx] = (int)(env0 + col);
+  if (spec && taint && ok && q == 0) {  // keep the INPUT state of a tainted env (dyn_in is intact until our own store)
+    const int idx = taint - 1;
     for (int r = 0; r < kp.dyn_rows; ++r) sa.u_buf[(size_t)idx * kp.dyn_rows + r] = sa.dyn_in[(size_t)r * sa.ld + env0 + col];
   }
   // ---- write back: one TMA bulk store per output row
@@ -458,9 +555,11 @@ step_kernel(const __grid_constant__ KParams kp, const __grid_constant__ AgentIO 
     keep = ex | sp;
   }
   bad = __syncthreads_or(bad);
+  int nd = 0;
   if (bad) {
     const int nu = *reinterpret_cast<volatile int*>(sa.counters + 1);
-    repair_tainted<CT, TE>(kp, aio, sa, t, flagS, nu);
+    nd = validate_speculation(kp, sa, flagS, nu);
+    if (nd) repair_tainted<CT, TE>(kp, aio, sa, t, flagS, nd);
     for (int w = tid; w < nw; w += blockDim.x) sa.flags_out[w] = flagS[w];
   } else if (nw <= (int)blockDim.x) {
     if (tid < nw) sa.flags_out[tid] = keep;
@@ -470,7 +569,7 @@ step_kernel(const __grid_constant__ KParams kp, const __grid_constant__ AgentIO 
   for (int w = tid; w < nw; w += blockDim.x) { sa.any_exact[w] = 0u; sa.any_spec[w] = 0u; sa.thin[w] = 0u; }
   if (tid == 0) {
     sa.counters[0] = 0; sa.counters[1] = 0;
-    if (bad) sa.counters[2] += 1;
+    if (nd) sa.counters[2] += 1;
   }
 }
 

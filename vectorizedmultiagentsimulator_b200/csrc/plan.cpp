@@ -218,7 +218,8 @@ int build_plan(const vmasb200_world_desc* d, vmasb200_plan* pl) {
   kp.row_bp = kp.row_sv + kp.n_blk;
   kp.row_pres = kp.row_bp + kp.n_blk;
   kp.row_taint = kp.row_pres + 5 * kSlots;
-  kp.work_rows = kp.row_taint + 1;
+  kp.row_th = kp.row_taint + 1;
+  kp.work_rows = kp.row_th + 1 + kp.n_blk;
   for (int i = 0; i < kp.n_dyn; ++i) pl->ents[pl->dyn_list[i]].fin_row = kp.row_fin + 3 * i;
   for (int i = 0; i < kp.n_trig; ++i) pl->ents[pl->trig_list[i]].trig_row = kp.row_trig + 4 * i;
   for (int e = 0; e < E; ++e) {

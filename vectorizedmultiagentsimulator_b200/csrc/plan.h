@@ -11,7 +11,8 @@
 
 namespace vb {
 struct CTab;
-constexpr int kHostStreams = 4;  // chunk streams of the host-buffer entry point
+constexpr int kHostStreams = 4;      // chunk streams of the host-buffer entry point
+constexpr int64_t kRecCap = 65536;  // tainted envs that get a verdict / thin-event record
 }
 
 struct vmasb200_plan {
@@ -41,6 +42,7 @@ struct vmasb200_plan {
   int64_t u_cap = 0;
   int* d_ulist = nullptr;
   float* d_ubuf = nullptr;
+  uint32_t* d_urec = nullptr;  // per tainted env: verdict record + thin-event record ([S][pair_words] each)
   // staging of vmasb200_step_host
   int64_t host_cap = 0;        // row stride (floats) of the staging buffers
   float *d_dyn = nullptr, *d_stat = nullptr, *d_force = nullptr, *d_torque = nullptr, *d_act = nullptr, *d_lidar = nullptr;

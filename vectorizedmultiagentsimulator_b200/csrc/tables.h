@@ -16,7 +16,8 @@
 //             lmask one per (sensor, 32-target word)
 //             strig 2 per sensor (cos/sin of the sensing entity's rotation, for the ray cull)
 //             jres 4 per joint, pres 5 per result slot (fx fy ta tb of an evaluated pair, pair index), sv / bp one per 32-pair
-//             block (survivor / verdict bits of the running substep), taint 1
+//             block (survivor / verdict bits of the running substep), taint 1 (record index + 1 of a tainted env),
+//             th 1 + one per 32-pair block (thin events of the running substep)
 // A TEAM of Q = NT / TE warps-groups shares the TE columns: thread t works on column t % TE as member q = t / TE and
 // takes the entities / joints / pair blocks / sensors with index = q (mod Q); order-sensitive sums stay with member 0.
 #pragma once
@@ -125,8 +126,9 @@ struct KParams {            // kernel parameter (by value)
   int32_t NT;               // threads per CTA: TE, or a multiple of it when helper warps share the LIDAR epilogue
   // work rows: [fin 3*n_dyn][trig 4*n_trig][frc 3*A][lmask][strig 2*n_sensors]
   int32_t work_rows, row_fin, row_trig, row_frc, row_lmask, n_lmask_words, row_strig;
-  // team rows: [jres 4*J][sv n_blk][bp n_blk][pres 5*kSlots][taint 1]; n_blk = ceil(P / 32)
+  // team rows: [jres 4*J][sv n_blk][bp n_blk][pres 5*kSlots][taint 1][th 1 + n_blk]; n_blk = ceil(P / 32)
   int32_t row_jres, row_sv, row_bp, row_pres, row_taint, n_blk;
+  int32_t row_th;           // [1 + n_blk]: marker + thin-event bits of the running substep (speculative launch)
   // device tables
   const DEnt* ents;
   const DItem* items;

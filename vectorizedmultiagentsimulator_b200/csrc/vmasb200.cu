@@ -133,13 +133,13 @@ static int bind_const(vmasb200_plan* pl, cudaStream_t st, bool* ct) {
 
 // CTA tile of a step over n environments (measured on B200, profiles/README.md): 4-member teams on 32 envs while that
 // fills the GPU in about one wave - the shortest critical path; beyond, throughput counts: whole-env threads (128 envs
-// per CTA, no work shared, fewest barriers) when two such CTAs fit an SM and there is no LIDAR epilogue to share,
-// else 2-member teams on 64 envs.
+// per CTA, no work shared, fewest barriers) for small worlds - at most 32 candidate pairs, no LIDAR epilogue, two such
+// CTAs fit an SM (transport, simple_spread: +40 %) - else 2-member teams on 64 envs (football: +35 % over 128).
 static int tile_for(const vmasb200_plan* pl, long long n) {
   if (pl->te_fixed) return pl->te_fixed;
   auto smem = [&](int te) { KParams k = pl->kp; k.TE = te; return smem_map(k).total_bytes; };
   if (n <= 48 * 1024) return 32;
-  if (!pl->kp.n_rays && smem(128) <= 113 * 1024) return 128;
+  if (!pl->kp.n_rays && pl->kp.n_blk <= 1 && smem(128) <= 113 * 1024) return 128;
   return smem(64) <= 226 * 1024 ? 64 : 32;
 }
 
@@ -189,13 +189,17 @@ static int launch_step(vmasb200_plan* pl, const vmasb200_step_io* io, long long 
   } else {
     // fused speculative launch; the last CTA verifies it and repairs the (rare) tainted envs in place
     if (io->n_envs > pl->u_cap) {
-      cudaFree(pl->d_ulist); cudaFree(pl->d_ubuf);
-      pl->d_ulist = nullptr; pl->d_ubuf = nullptr; pl->u_cap = 0;
-      VB_CUDA(cudaMalloc(&pl->d_ulist, (size_t)io->n_envs * sizeof(int)));
+      cudaFree(pl->d_ulist); cudaFree(pl->d_ubuf); cudaFree(pl->d_urec);
+      pl->d_ulist = nullptr; pl->d_ubuf = nullptr; pl->d_urec = nullptr; pl->u_cap = 0;
+      const size_t rec = (size_t)std::min<int64_t>(io->n_envs, kRecCap) * bw;  // words of one record array
+      VB_CUDA(cudaMalloc(&pl->d_ulist, 2 * (size_t)io->n_envs * sizeof(int)));
       VB_CUDA(cudaMalloc(&pl->d_ubuf, (size_t)io->n_envs * std::max(kp.dyn_rows, 1) * sizeof(float)));
+      VB_CUDA(cudaMalloc(&pl->d_urec, 2 * rec * sizeof(uint32_t)));
       pl->u_cap = io->n_envs;
     }
-    sa.u_list = pl->d_ulist; sa.u_buf = pl->d_ubuf;
+    sa.u_list = pl->d_ulist; sa.u_rep = pl->d_ulist + pl->u_cap; sa.u_buf = pl->d_ubuf;
+    sa.rec_cap = (int)std::min<int64_t>(pl->u_cap, kRecCap);
+    sa.u_verd = pl->d_urec; sa.u_thin = pl->d_urec + (size_t)sa.rec_cap * bw;
     sa.s_begin = 0; sa.s_end = kp.S; sa.flags_in = nullptr; sa.do_lidar = 1;
     step_fn(ct, kp.TE)<<<grid, block, smem_bytes, st>>>(kp, aio, sa);
   }
@@ -232,7 +236,7 @@ int vmasb200_plan_destroy(vmasb200_plan* pl) {
     for (ConstOwner& o : g_const) if (o.plan == pl) o.plan = nullptr;
   }
   if (pl->uploaded) {
-    cudaFree(pl->d_blob); cudaFree(pl->d_bits); cudaFree(pl->d_ulist); cudaFree(pl->d_ubuf);
+    cudaFree(pl->d_blob); cudaFree(pl->d_bits); cudaFree(pl->d_ulist); cudaFree(pl->d_ubuf); cudaFree(pl->d_urec);
     cudaFree(pl->d_dyn); cudaFree(pl->d_stat); cudaFree(pl->d_force); cudaFree(pl->d_torque); cudaFree(pl->d_act); cudaFree(pl->d_lidar);
     for (cudaStream_t s : pl->streams) if (s) cudaStreamDestroy(s);
   }
