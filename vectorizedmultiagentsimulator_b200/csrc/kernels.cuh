@@ -41,6 +41,7 @@ struct StepArgs {
   uint32_t* u_verd;          // [rec_cap][S][pair_words] verdicts of tainted env i from its taint on
   uint32_t* u_thin;          // [rec_cap][S][pair_words] its thin events
   int rec_cap;               // tainted envs beyond this have no record and are re-simulated when anything is
+  int* repairs_host;         // mapped host copy of counters[2] (read by the host-buffer entry point without a copy)
   int do_lidar;
 };
 
@@ -569,7 +570,11 @@ step_kernel(const __grid_constant__ KParams kp, const __grid_constant__ AgentIO 
   for (int w = tid; w < nw; w += blockDim.x) { sa.any_exact[w] = 0u; sa.any_spec[w] = 0u; sa.thin[w] = 0u; }
   if (tid == 0) {
     sa.counters[0] = 0; sa.counters[1] = 0;
-    if (nd) sa.counters[2] += 1;
+    if (nd) {
+      sa.counters[2] += 1;
+      *sa.repairs_host = sa.counters[2];
+      __threadfence_system();
+    }
   }
 }
 

@@ -42,6 +42,7 @@ struct vmasb200_plan {
   int64_t u_cap = 0;
   int* d_ulist = nullptr;
   float* d_ubuf = nullptr;
+  int* h_repairs = nullptr;    // mapped pinned host word: repairs done since plan creation (written by the kernel)
   uint32_t* d_urec = nullptr;  // per tainted env: verdict record + thin-event record ([S][pair_words] each)
   // staging of vmasb200_step_host
   int64_t host_cap = 0;        // row stride (floats) of the staging buffers

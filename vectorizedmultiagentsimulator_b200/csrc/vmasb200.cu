@@ -2,6 +2,7 @@
 // Compiled with -fmad=false: every reference torch op is one rounded fp32 instruction (see geom.cuh).
 #include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <memory>
 #include <mutex>
@@ -69,6 +70,8 @@ int upload_plan(vmasb200_plan* pl) {
   const size_t nbits = (4 * bits_words(kp) + 4) * sizeof(uint32_t);
   VB_CUDA(cudaMalloc(&pl->d_bits, nbits));
   VB_CUDA(cudaMemset(pl->d_bits, 0, nbits));
+  VB_CUDA(cudaHostAlloc(&pl->h_repairs, sizeof(int), cudaHostAllocMapped));
+  *pl->h_repairs = 0;
   for (int ct = 0; ct < 2; ++ct)
     for (int te : {32, 64, 128})
       VB_CUDA(cudaFuncSetAttribute(step_fn(ct != 0, te), cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
@@ -200,6 +203,7 @@ static int launch_step(vmasb200_plan* pl, const vmasb200_step_io* io, long long 
     sa.u_list = pl->d_ulist; sa.u_rep = pl->d_ulist + pl->u_cap; sa.u_buf = pl->d_ubuf;
     sa.rec_cap = (int)std::min<int64_t>(pl->u_cap, kRecCap);
     sa.u_verd = pl->d_urec; sa.u_thin = pl->d_urec + (size_t)sa.rec_cap * bw;
+    VB_CUDA(cudaHostGetDevicePointer(&sa.repairs_host, pl->h_repairs, 0));
     sa.s_begin = 0; sa.s_end = kp.S; sa.flags_in = nullptr; sa.do_lidar = 1;
     step_fn(ct, kp.TE)<<<grid, block, smem_bytes, st>>>(kp, aio, sa);
   }
@@ -236,7 +240,7 @@ int vmasb200_plan_destroy(vmasb200_plan* pl) {
     for (ConstOwner& o : g_const) if (o.plan == pl) o.plan = nullptr;
   }
   if (pl->uploaded) {
-    cudaFree(pl->d_blob); cudaFree(pl->d_bits); cudaFree(pl->d_ulist); cudaFree(pl->d_ubuf); cudaFree(pl->d_urec);
+    cudaFree(pl->d_blob); cudaFree(pl->d_bits); cudaFreeHost(pl->h_repairs); cudaFree(pl->d_ulist); cudaFree(pl->d_ubuf); cudaFree(pl->d_urec);
     cudaFree(pl->d_dyn); cudaFree(pl->d_stat); cudaFree(pl->d_force); cudaFree(pl->d_torque); cudaFree(pl->d_act); cudaFree(pl->d_lidar);
     for (cudaStream_t s : pl->streams) if (s) cudaStreamDestroy(s);
   }
@@ -321,7 +325,9 @@ int vmasb200_step_host(vmasb200_plan* pl, const float* h_dyn_in, const float* h_
 
   // chunks of envs, one stream each: H2D(k+1) overlaps kernel(k) overlaps D2H(k-1).  Boundaries are multiples of
   // 256 envs (every CTA tile size divides 256); the exact path needs batch-wide flags between substeps: one chunk.
-  int64_t nchunk = exact ? 1 : std::min<int64_t>(kHostStreams, (n + 8191) / 8192);
+  // chunk size: 16384 envs measured best at 32 K - 256 K envs (profiles/README.md); VMASB200_HOST_CHUNK_ENVS overrides
+  static const int64_t chunk_envs = [] { const char* e = std::getenv("VMASB200_HOST_CHUNK_ENVS"); return e ? std::max<int64_t>(256, std::atoll(e)) : int64_t(16384); }();
+  int64_t nchunk = exact ? 1 : std::min<int64_t>(kHostStreams, (n + chunk_envs - 1) / chunk_envs);
   int64_t csize = ((n + nchunk - 1) / nchunk + 255) & ~int64_t(255);
   nchunk = (n + csize - 1) / csize;
   const float* fptr[kMaxAgents]; const float* tptr[kMaxAgents];
@@ -342,9 +348,8 @@ int vmasb200_step_host(vmasb200_plan* pl, const float* h_dyn_in, const float* h_
     if (want_lidar) VB_CUDA(rows2d(h_lidar_out, ld, pl->d_lidar, dld, c0, ncol, kp.lidar_rows, cudaMemcpyDeviceToHost, st));
     return VMASB200_OK;
   };
-  int repairs_before = 0;
-  const int* d_repairs = reinterpret_cast<const int*>(pl->d_bits + 4 * bits_words(kp)) + 2;
-  if (nchunk > 1) VB_CUDA(cudaMemcpy(&repairs_before, d_repairs, sizeof(int), cudaMemcpyDeviceToHost));
+  // repairs so far (mapped host word the verifying CTA writes): every earlier step of this plan has been waited for
+  const int repairs_before = *static_cast<volatile int*>(pl->h_repairs);
   for (int64_t k = 0; k < nchunk; ++k) {
     cudaStream_t st = pl->streams[k % kHostStreams];
     const int64_t c0 = k * csize, c1 = std::min(n, c0 + csize), ncol = c1 - c0;
@@ -364,9 +369,7 @@ int vmasb200_step_host(vmasb200_plan* pl, const float* h_dyn_in, const float* h_
   for (int64_t k = 0; k < std::min<int64_t>(nchunk, kHostStreams); ++k) VB_CUDA(cudaStreamSynchronize(pl->streams[k]));
   if (nchunk > 1) {
     // a repair by the step's last CTA may have rewritten envs of a chunk whose results were already copied out
-    int repairs_after = 0;
-    VB_CUDA(cudaMemcpy(&repairs_after, d_repairs, sizeof(int), cudaMemcpyDeviceToHost));
-    if (repairs_after != repairs_before) {
+    if (*static_cast<volatile int*>(pl->h_repairs) != repairs_before) {
       if ((rc = d2h(0, n, pl->streams[0]))) return rc;
       VB_CUDA(cudaStreamSynchronize(pl->streams[0]));
     }
