@@ -162,3 +162,30 @@ def test_tiles_agree_bitwise(name):
                 for x, y, what in zip(outs[0], o, ("dyn", "act", "lidar", "masks")):
                     if x is not None:
                         assert np.array_equal(x.view(np.uint32), y.view(np.uint32)), f"{name} t={t} exact={exact}: {what} differs"
+
+
+@pytest.mark.parametrize("name", ALL)
+def test_repeatable_bitwise(name):
+    """The team members of an env hand work to each other through shared memory between CTA barriers; a missing barrier
+    would show as run-to-run differences.  Same input, many runs (and enough envs for several CTAs in flight): same bits."""
+    fx = Fixture(name)
+    pl = StepPlan(fx.desc)
+    reps = 64
+    state_in, t, k = fx.one_step_cases()[-1]
+    st = np.ascontiguousarray(np.tile(state_in, (1, reps, 1)))
+    jr = fx.jrot_at(t)
+    jr = np.tile(jr, (1, reps)) if jr.size else jr
+    dyn, stat = pl.pack(st, jr)
+    f, tq = _forces(fx, t)
+    f, tq = np.ascontiguousarray(np.tile(f, (reps, 1, 1))), np.ascontiguousarray(np.tile(tq, (reps, 1)))
+    first = pl.step_host(dyn, stat, f, tq, exact=False)
+    n = fx.n_envs
+    for x in first[:3]:  # every replica of an env must also agree with the first copy
+        if x is not None:
+            cols = x[:, :n * reps].reshape(x.shape[0], reps, n)
+            assert np.array_equal(cols.view(np.uint32), np.broadcast_to(cols[:, :1], cols.shape).view(np.uint32))
+    for _ in range(6):
+        again = pl.step_host(dyn, stat, f, tq, exact=False)
+        for x, y in zip(first, again):
+            if x is not None:
+                assert np.array_equal(x.view(np.uint32), y.view(np.uint32))
