@@ -101,6 +101,16 @@ def ncu_capture(scenario, n):
         return {}
 
 
+def alg_flops_per_env(plan, desc):
+    """SURVEY 8(d) estimate of the step's algorithmic FP32 work per env-step (op lists of the reference; the kernel's
+    culls execute far fewer): per substep 35 / 55 / 190 / 180 / 730 / 5000 per S-S / L-S / L-L / B-S / B-L / B-B pair,
+    110 per joint, 35 per dynamic entity; plus 45 per LIDAR (ray, target)."""
+    per_type = [35, 55, 190, 180, 730, 5000]
+    pairs = sum(per_type[t] for t, _, _ in plan.pairs)
+    rays = sum(len(l.angles) * len(l.targets) for l in desc.lidars)
+    return plan.S * (pairs + 110 * len(desc.joints) + 35 * plan.layout.n_dyn) + 45 * rays
+
+
 def cpu_port_rate(wl, seconds=8.0, n_sample=None, threads=0):
     """The C oracle (oracle/vmas_oracle.c: scalar port of the reference step, OpenMP over envs) timed on the host."""
     from oracle.oracle import Oracle
@@ -292,6 +302,14 @@ def run_b200(args, rank, local_rank, world):
             "gpu_launches": K * (2 * plan.S if args.exact else 1),
             "clocks": clocks,
         }
+        # the step's roofline is the slower of its HBM bytes at peak bandwidth and its FP32 FLOPs at the
+        # non-tensor FP32 peak (148 SMs x 128 lanes x 2 x max SM clock); both fractions are reported, `binding` names it
+        flops = alg_flops_per_env(plan, wl.desc)
+        fp32_peak = 148 * 128 * 2 * ((clocks or {}).get("sm_max_mhz") or 1965.0) * 1e6
+        fp32_frac = flops * value / world / fp32_peak
+        line["roofline"]["fp32"] = {"alg_flops_per_env": flops, "achieved_tflops": flops * value / world / 1e12,
+                                    "peak_tflops": fp32_peak / 1e12, "frac": fp32_frac}
+        line["roofline"]["binding"] = "fp32" if flops / fp32_peak > plan.alg_bytes_per_env / (peak * 1e9) else "hbm"
         if cap.get("warp_inst"):
             # the bound that actually binds: warp instructions of one launch (ncu) over the live launch
             # time, against 4 issue slots x 148 SMs at the SM clock sampled during the timed region
