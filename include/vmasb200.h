@@ -232,6 +232,28 @@ int vmasb200_cast_rays(vmasb200_plan* plan, const float* dyn, const float* stat,
  * steps of this plan needed the exact fix-up path since creation. */
 int vmasb200_sync_check(vmasb200_plan* plan, void* stream, int64_t* n_fixups);
 
+/* ---- distance queries of reward code: World.get_distance_from_point (core.py:1787-1819),
+ * World.get_distance (core.py:1821-1907) and World.is_overlapping (core.py:1909-1966).  They take an entity's shape
+ * and pointers to its pose tensors as they are (any strides, device memory), so they work for every entity of a World,
+ * staged in a plan's SoA buffers (then pos is a strided view into them) or not; no plan is needed. */
+typedef struct vmasb200_pose {
+  int32_t shape;                /* VMASB200_SPHERE / BOX / LINE                                          */
+  double radius, length, width; /* the shape's Python floats; the library rounds them the way torch does   */
+  const float* pos;             /* d: x of env i at pos[i * pos_stride], y at pos[i * pos_stride + pos_stride_xy] */
+  int64_t pos_stride, pos_stride_xy;
+  const float* rot;             /* d: rot of env i at rot[i * rot_stride]; may be NULL for a sphere         */
+  int64_t rot_stride;
+} vmasb200_pose;
+
+/* out d: [n_envs] float, World.get_distance(a, b).  Asynchronous on `stream`. */
+int vmasb200_get_distance(const vmasb200_pose* a, const vmasb200_pose* b, float* out, int64_t n_envs, void* stream);
+/* out d: [n_envs] uint8 (0 / 1), World.is_overlapping(a, b). */
+int vmasb200_is_overlapping(const vmasb200_pose* a, const vmasb200_pose* b, uint8_t* out, int64_t n_envs, void* stream);
+/* points d: test point of env i at points[i * points_stride] (x) and [.. + points_stride_xy] (y);
+ * out d: [n_envs] float, World.get_distance_from_point(a, points). */
+int vmasb200_get_distance_from_point(const vmasb200_pose* a, const float* points, int64_t points_stride,
+                                     int64_t points_stride_xy, float* out, int64_t n_envs, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

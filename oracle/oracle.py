@@ -34,6 +34,13 @@ def lib():
         _LIB.vmas_oracle_cast_rays.argtypes = [
             C.c_void_p, C.c_int64, fp, C.c_int, fp, C.c_int, C.c_float, C.POINTER(C.c_int32), C.c_int, fp, C.c_int,
         ]
+        dp = C.POINTER(C.c_double)
+        _LIB.vmas_oracle_get_distance.restype = C.c_int
+        _LIB.vmas_oracle_get_distance.argtypes = [C.c_int, dp, fp, C.c_int, dp, fp, C.c_int64, fp]
+        _LIB.vmas_oracle_is_overlapping.restype = C.c_int
+        _LIB.vmas_oracle_is_overlapping.argtypes = [C.c_int, dp, fp, C.c_int, dp, fp, C.c_int64, C.POINTER(C.c_uint8)]
+        _LIB.vmas_oracle_distance_from_point.restype = C.c_int
+        _LIB.vmas_oracle_distance_from_point.argtypes = [C.c_int, dp, fp, fp, C.c_int64, fp]
     return _LIB
 
 
@@ -96,3 +103,38 @@ class Oracle:
         if rc:
             raise RuntimeError(f"vmas_oracle_cast_rays failed: {rc}")
         return out
+
+
+# ---- distance queries: shape = VMASB200_SPHERE/BOX/LINE, dims = (radius, length, width) Python floats,
+# state = the entity's [N, 6] block of the fixture state
+def _dims(d):
+    a = np.ascontiguousarray(d, np.float64)
+    return a, a.ctypes.data_as(C.POINTER(C.c_double))
+
+
+def get_distance(shape_a, dims_a, state_a, shape_b, dims_b, state_b):
+    sa, sb = np.ascontiguousarray(state_a, np.float32), np.ascontiguousarray(state_b, np.float32)
+    (ka, da), (kb, db) = _dims(dims_a), _dims(dims_b)
+    out = np.empty(sa.shape[0], np.float32)
+    rc = lib().vmas_oracle_get_distance(int(shape_a), da, _fp(sa), int(shape_b), db, _fp(sb), sa.shape[0], _fp(out))
+    assert rc == 0
+    return out
+
+
+def is_overlapping(shape_a, dims_a, state_a, shape_b, dims_b, state_b):
+    sa, sb = np.ascontiguousarray(state_a, np.float32), np.ascontiguousarray(state_b, np.float32)
+    (ka, da), (kb, db) = _dims(dims_a), _dims(dims_b)
+    out = np.empty(sa.shape[0], np.uint8)
+    rc = lib().vmas_oracle_is_overlapping(int(shape_a), da, _fp(sa), int(shape_b), db, _fp(sb), sa.shape[0],
+                                          out.ctypes.data_as(C.POINTER(C.c_uint8)))
+    assert rc == 0
+    return out.astype(bool)
+
+
+def distance_from_point(shape_a, dims_a, state_a, points):
+    sa, pts = np.ascontiguousarray(state_a, np.float32), np.ascontiguousarray(points, np.float32)
+    ka, da = _dims(dims_a)
+    out = np.empty(sa.shape[0], np.float32)
+    rc = lib().vmas_oracle_distance_from_point(int(shape_a), da, _fp(sa), _fp(pts), sa.shape[0], _fp(out))
+    assert rc == 0
+    return out

@@ -594,3 +594,83 @@ int vmas_oracle_lidar(const vmasb200_world_desc* desc, int64_t n, const float* s
   free(ang);
   return rc;
 }
+
+/* ---- distance queries.  A shape is (kind, radius, length, width) as Python floats (doubles); a pose is
+ * the entity's [N][6] block of the fixture state. */
+typedef struct { int shape; double radius, length, width; const float* st; } qent;
+#define QP(e, i) V((e)->st[(size_t)(i) * 6 + 0], (e)->st[(size_t)(i) * 6 + 1])
+#define QR(e, i) ((e)->st[(size_t)(i) * 6 + 4])
+
+/* core.py:1787-1819 get_distance_from_point */
+static float q_from_point(const qent* e, int64_t i, v2 q) {
+  if (e->shape == VMASB200_SPHERE) return vnorm(vsub(QP(e, i), q)) - (float)e->radius;
+  v2 cp = e->shape == VMASB200_BOX ? closest_point_box(QP(e, i), QR(e, i), (float)e->width, (float)e->length, q)
+                                   : closest_point_line(QP(e, i), QR(e, i), (float)e->length, q, 1);
+  return vnorm(vsub(q, cp)) - LMD;
+}
+
+/* core.py:1936-1964 is_overlapping, box / sphere branch */
+static int q_overlap_box_sphere(const qent* box, const qent* sph, int64_t i) {
+  v2 bp = QP(box, i), sp = QP(sph, i);
+  v2 cp = closest_point_box(bp, QR(box, i), (float)box->width, (float)box->length, sp);
+  float d_sphere_cp = vnorm(vsub(sp, cp));
+  float d_sphere_box = vnorm(vsub(sp, bp));
+  float d_cp_box = vnorm(vsub(bp, cp));
+  float dist_min = (float)(sph->radius + 4.0 / 6e2); /* Python double sum, cast where it meets the tensor */
+  return (d_sphere_box < d_cp_box) || (d_sphere_cp < dist_min);
+}
+
+/* core.py:1821-1907 get_distance */
+static float q_distance(const qent* a, const qent* b, int64_t i) {
+  int sa = a->shape, sb = b->shape;
+  if (sa == VMASB200_SPHERE && sb == VMASB200_SPHERE) return q_from_point(a, i, QP(b, i)) - (float)b->radius;
+  if ((sa == VMASB200_BOX && sb == VMASB200_SPHERE) || (sb == VMASB200_BOX && sa == VMASB200_SPHERE)) {
+    const qent* box = sb == VMASB200_SPHERE ? a : b;
+    const qent* sph = sb == VMASB200_SPHERE ? b : a;
+    float d = q_from_point(box, i, QP(sph, i)) - (float)sph->radius;
+    return q_overlap_box_sphere(box, sph, i) ? -1.f : d;
+  }
+  if ((sa == VMASB200_LINE && sb == VMASB200_SPHERE) || (sb == VMASB200_LINE && sa == VMASB200_SPHERE)) {
+    const qent* line = sb == VMASB200_SPHERE ? a : b;
+    const qent* sph = sb == VMASB200_SPHERE ? b : a;
+    return q_from_point(line, i, QP(sph, i)) - (float)sph->radius;
+  }
+  v2 p1, p2;
+  if (sa == VMASB200_LINE && sb == VMASB200_LINE) {
+    closest_points_line_line(QP(a, i), QR(a, i), (float)a->length, QP(b, i), QR(b, i), (float)b->length, &p1, &p2);
+  } else if (sa == VMASB200_BOX && sb == VMASB200_BOX) {
+    closest_box_box(QP(a, i), QR(a, i), (float)a->width, (float)a->length, QP(b, i), QR(b, i), (float)b->width,
+                    (float)b->length, &p1, &p2);
+  } else {
+    const qent* box = sa == VMASB200_BOX ? a : b;
+    const qent* line = sa == VMASB200_BOX ? b : a;
+    closest_line_box(QP(box, i), QR(box, i), (float)box->width, (float)box->length, QP(line, i), QR(line, i),
+                     (float)line->length, &p1, &p2);
+  }
+  return vnorm(vsub(p1, p2)) - LMD;
+}
+
+int vmas_oracle_get_distance(int shape_a, const double* dims_a, const float* state_a, int shape_b, const double* dims_b,
+                             const float* state_b, int64_t n, float* out) {
+  qent a = {shape_a, dims_a[0], dims_a[1], dims_a[2], state_a}, b = {shape_b, dims_b[0], dims_b[1], dims_b[2], state_b};
+  for (int64_t i = 0; i < n; ++i) out[i] = q_distance(&a, &b, i);
+  return 0;
+}
+
+int vmas_oracle_is_overlapping(int shape_a, const double* dims_a, const float* state_a, int shape_b,
+                               const double* dims_b, const float* state_b, int64_t n, uint8_t* out) {
+  qent a = {shape_a, dims_a[0], dims_a[1], dims_a[2], state_a}, b = {shape_b, dims_b[0], dims_b[1], dims_b[2], state_b};
+  int bs = (shape_a == VMASB200_BOX && shape_b == VMASB200_SPHERE) || (shape_b == VMASB200_BOX && shape_a == VMASB200_SPHERE);
+  for (int64_t i = 0; i < n; ++i) {
+    if (bs) out[i] = (uint8_t)q_overlap_box_sphere(shape_b == VMASB200_SPHERE ? &a : &b, shape_b == VMASB200_SPHERE ? &b : &a, i);
+    else out[i] = q_distance(&a, &b, i) < 0.f; /* core.py:1934 */
+  }
+  return 0;
+}
+
+int vmas_oracle_distance_from_point(int shape_a, const double* dims_a, const float* state_a, const float* points,
+                                    int64_t n, float* out) {
+  qent a = {shape_a, dims_a[0], dims_a[1], dims_a[2], state_a};
+  for (int64_t i = 0; i < n; ++i) out[i] = q_from_point(&a, i, V(points[2 * i], points[2 * i + 1]));
+  return 0;
+}

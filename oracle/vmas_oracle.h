@@ -40,6 +40,16 @@ int vmas_oracle_cast_rays(const vmasb200_world_desc* desc, int64_t n, const floa
                           const float* angles, int n_rays, float max_range, const int32_t* targets, int n_targets,
                           float* out, int n_threads);
 
+/* World.get_distance (core.py:1821-1907), World.is_overlapping (core.py:1909-1966) and
+ * World.get_distance_from_point (core.py:1787-1819).  dims = {radius, length, width} as the shape's Python floats;
+ * state_x = the entity's [N][6] block of the fixture state; points [N][2]; out [N]. */
+int vmas_oracle_get_distance(int shape_a, const double* dims_a, const float* state_a, int shape_b, const double* dims_b,
+                             const float* state_b, int64_t n, float* out);
+int vmas_oracle_is_overlapping(int shape_a, const double* dims_a, const float* state_a, int shape_b,
+                               const double* dims_b, const float* state_b, int64_t n, uint8_t* out);
+int vmas_oracle_distance_from_point(int shape_a, const double* dims_a, const float* state_a, const float* points,
+                                    int64_t n, float* out);
+
 #ifdef __cplusplus
 }
 #endif

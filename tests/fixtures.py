@@ -67,6 +67,26 @@ class Fixture:
                 state[e] = v
 
 
+class QueryFixture:
+    """tests/golden/queries/<name>.npz (tests/golden/make_golden_queries.py): reference outputs of World.get_distance /
+    is_overlapping / get_distance_from_point on recorded states of fixture `name`."""
+
+    def __init__(self, name):
+        self.fx = Fixture(name)
+        z = np.load(os.path.join(GOLDEN, "queries", name + ".npz"))
+        self.snaps = [int(k) for k in z["snaps"]]
+        self.states = [self.fx.state0 if k < 0 else self.fx.state_after[k] for k in self.snaps]
+        self.pairs = [(int(a), int(b)) for a, b in z["pairs"]]
+        self.dist = z["dist"]
+        shp = tuple(int(v) for v in z["overlap_shape"])
+        self.overlap = np.unpackbits(z["overlap"])[: int(np.prod(shp))].reshape(shp).astype(bool)
+        self.pt_entities = [int(e) for e in z["pt_entities"]]
+        self.points = z["points"]
+        self.pt_dist = z["pt_dist"]
+        self.dims = z["dims"]          # [E, 3] radius, length, width as Python floats
+        self.shapes = [int(s) for s in z["shapes"]]
+
+
 def close(a, b, rtol=RTOL, atol=ATOL):
     return np.allclose(a, b, rtol=rtol, atol=atol, equal_nan=True)
 

@@ -168,3 +168,45 @@ def test_cpu_world_is_rejected():
     env = vmas.make_env("simple_spread", num_envs=4, device="cpu", seed=0, continuous_actions=True)
     with pytest.raises(_lib.VmasB200Error):
         dropin.enable(env)
+
+
+@pytest.mark.parametrize("scenario,kw", [("navigation", dict(n_agents=4)), ("transport", dict(n_agents=4)),
+                                         ("joint_passage", dict()), ("football", dict(ai_red_agents=False)),
+                                         ("pollock", dict(lidar=True))])
+def test_distance_queries_match_reference(scenario, kw):
+    """world.get_distance / is_overlapping / get_distance_from_point of a patched world (what the scenario's reward
+    code calls) against the reference's torch implementation on the very same state tensors, for every entity pair."""
+    import itertools
+
+    import torch
+
+    from vectorizedmultiagentsimulator_b200 import dropin
+
+    vmas = _vmas()
+    n = 96
+    env = _make(vmas, scenario, kw, n, 1)
+    b = dropin.enable(env)
+    torch.manual_seed(3)
+    for _ in range(5):
+        env.step([env.get_random_action(a) for a in env.agents])
+    world = env.world
+    ents = list(world.entities)
+    flips = 0
+    for a, c in itertools.permutations(ents, 2):
+        d_ref = b.orig_get_distance(a, c)
+        d = world.get_distance(a, c)
+        assert d.shape == d_ref.shape and torch.allclose(d, d_ref, rtol=1e-5, atol=1e-6), (a.name, c.name)
+        o_ref, o = b.orig_is_overlapping(a, c), world.is_overlapping(a, c)
+        assert o.dtype == torch.bool and o.shape == o_ref.shape
+        diff = o != o_ref
+        flips += int(diff.sum())
+        assert not (diff & (d_ref.abs() > 1e-6)).any(), (a.name, c.name)  # only a distance within rounding of 0 may flip
+    assert flips <= 2
+    pts = torch.rand(n, 2, device="cuda") * 2 - 1
+    for e in ents:
+        assert torch.allclose(world.get_distance_from_point(e, pts), b.orig_get_distance_from_point(e, pts), rtol=1e-5, atol=1e-6)
+    # env_index and autograd keep the reference's own path
+    a0, a1 = env.agents[0], env.agents[1]  # spheres (the reference's env_index handling breaks for box / sphere)
+    assert torch.equal(world.get_distance(a0, a1, env_index=3), b.orig_get_distance(a0, a1, 3))
+    dropin.disable(env)
+    assert "get_distance" not in world.__dict__

@@ -48,6 +48,7 @@ def main():
     rep, so = sys.argv[1], sys.argv[2]
     kernel = sys.argv[3] if len(sys.argv) > 3 else "step_kernel"
     idx = sys.argv[4] if len(sys.argv) > 4 else "1"
+    top = int(os.environ.get("NCU_LINES_TOP", "22"))  # rows per frame table
     out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--kernel-id", f":::{idx}"],
                          capture_output=True, text=True).stdout
     rows = list(csv.reader(out.splitlines()))
@@ -95,7 +96,7 @@ def main():
         print(f"{loc[0]}:{loc[1]:<5d} inst {v[1]:>10d} ({100*v[1]/max(total[1],1):5.1f}%)  samples {v[0]:>7d} ({100*v[0]/max(total[0],1):5.1f}%)  thr/inst {v[2]/max(v[1],1):5.1f}")
     for lvl, name in ((1, "kernel body line"), (2, "first inlined frame"), (3, "second inlined frame")):
         print(f"--- by {name} (inclusive of everything inlined below it)")
-        for loc, v in sorted(by_frame[lvl].items(), key=lambda kv: -kv[1][1])[:22]:
+        for loc, v in sorted(by_frame[lvl].items(), key=lambda kv: -kv[1][1])[:top]:
             print(f"{loc[0]}:{loc[1]:<5d} inst {v[1]:>10d} ({100*v[1]/max(total[1],1):5.1f}%)  samples {v[0]:>7d} ({100*v[0]/max(total[0],1):5.1f}%)  thr/inst {v[2]/max(v[1],1):5.1f}")
     print("--- top source lines by stall samples")
     for loc, v in sorted(by_line.items(), key=lambda kv: -kv[1][0])[:25]:

@@ -1,0 +1,117 @@
+// queries.cuh - the distance queries reward code calls between steps: World.get_distance_from_point
+// (core.py:1787-1819), World.get_distance (core.py:1821-1907), World.is_overlapping (core.py:1909-1966).
+//
+// One thread per environment; the two shapes are uniform over the launch, so the shape switch does not diverge.
+// Poses are read through the tensors' own strides: an entity staged in a plan's SoA rows is read coalesced
+// (pos_stride 1), any other torch tensor works too.  Bytes per env: 4 * (3 + 3 + 1) at most: HBM / launch bound.
+#pragma once
+#include "geom.cuh"
+
+#include "../../include/vmasb200.h"
+
+namespace vb {
+
+struct QPose {  // vmasb200_pose by value, dimensions rounded the way torch rounds a Python scalar operand
+  int shape;
+  float radius, length, width;
+  float overlap_min;  // (float)(radius + LINE_MIN_DIST), the sum taken in double (core.py:1960)
+  const float* pos; long long ps, pxy;
+  const float* rot; long long rs;
+};
+
+VB_DI V2 q_pos(const QPose& p, long long i) { return mk(p.pos[i * p.ps], p.pos[i * p.ps + p.pxy]); }
+VB_DI Rot q_rot(const QPose& p, long long i) {
+  Rot r;
+  r.c = 1.f; r.s = 0.f; r.c2 = 0.f; r.s2 = 1.f;
+  if (p.shape == VMASB200_SPHERE) return r;
+  const float rot = p.rot[i * p.rs];
+  sincosf(rot, &r.s, &r.c);
+  if (p.shape == VMASB200_BOX) sincosf(rot + (float)(3.14159265358979323846 / 2), &r.s2, &r.c2);  // physics.py:299-301
+  return r;
+}
+
+// core.py:1787-1819
+VB_DI float dist_from_point(const QPose& e, V2 pos, const Rot& r, V2 q) {
+  if (e.shape == VMASB200_SPHERE) return norm(pos - q) - e.radius;
+  const V2 cp = e.shape == VMASB200_BOX ? closest_point_box(pos, r, e.width, e.length, q)
+                                        : closest_point_line(pos, r.c, r.s, e.length, q);
+  return norm(q - cp) - kLMD;
+}
+
+// core.py:1944-1966: box / sphere overlap
+VB_DI bool overlap_box_sphere(const QPose& box, V2 bp, const Rot& br, const QPose& sph, V2 sp) {
+  const V2 cp = closest_point_box(bp, br, box.width, box.length, sp);
+  const float d_sphere_cp = norm(sp - cp);
+  const float d_sphere_box = norm(sp - bp);
+  const float d_cp_box = norm(bp - cp);
+  return (d_sphere_box < d_cp_box) || (d_sphere_cp < sph.overlap_min);
+}
+
+// core.py:1821-1907
+VB_DI float pair_distance(const QPose& a, const QPose& b, long long i) {
+  const V2 pa = q_pos(a, i), pb = q_pos(b, i);
+  const Rot ra = q_rot(a, i), rb = q_rot(b, i);
+  const int sa = a.shape, sb = b.shape;
+  if (sa == VMASB200_SPHERE && sb == VMASB200_SPHERE) return dist_from_point(a, pa, ra, pb) - b.radius;
+  if ((sa == VMASB200_BOX && sb == VMASB200_SPHERE) || (sb == VMASB200_BOX && sa == VMASB200_SPHERE)) {
+    const bool a_box = sb == VMASB200_SPHERE;
+    const QPose& box = a_box ? a : b;
+    const QPose& sph = a_box ? b : a;
+    const V2 bp = a_box ? pa : pb, sp = a_box ? pb : pa;
+    const Rot& br = a_box ? ra : rb;
+    const float d = dist_from_point(box, bp, br, sp) - sph.radius;
+    return overlap_box_sphere(box, bp, br, sph, sp) ? -1.f : d;
+  }
+  if ((sa == VMASB200_LINE && sb == VMASB200_SPHERE) || (sb == VMASB200_LINE && sa == VMASB200_SPHERE)) {
+    const bool a_line = sb == VMASB200_SPHERE;
+    const QPose& line = a_line ? a : b;
+    const QPose& sph = a_line ? b : a;
+    return dist_from_point(line, a_line ? pa : pb, a_line ? ra : rb, a_line ? pb : pa) - sph.radius;
+  }
+  V2 p1, p2;
+  if (sa == VMASB200_LINE && sb == VMASB200_LINE) {
+    closest_points_line_line(pa, ra.c, ra.s, a.length, pb, rb.c, rb.s, b.length, p1, p2);
+  } else if (sa == VMASB200_BOX && sb == VMASB200_BOX) {
+    closest_box_box(pa, ra, a.width, a.length, pb, rb, b.width, b.length, p1, p2);
+  } else {  // box / line
+    const bool a_box = sa == VMASB200_BOX;
+    const QPose& box = a_box ? a : b;
+    const QPose& line = a_box ? b : a;
+    const Rot& lr = a_box ? rb : ra;
+    closest_line_box(a_box ? pa : pb, a_box ? ra : rb, box.width, box.length, a_box ? pb : pa, lr.c, lr.s, line.length, p1, p2);
+  }
+  return norm(p1 - p2) - kLMD;
+}
+
+enum { QM_DISTANCE = 0, QM_OVERLAP = 1 };
+
+template <int MODE>
+__global__ void __launch_bounds__(256) pair_query_kernel(const __grid_constant__ QPose a, const __grid_constant__ QPose b,
+                                                         float* __restrict__ out_f, uint8_t* __restrict__ out_b, long long n) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  if (MODE == QM_DISTANCE) {
+    out_f[i] = pair_distance(a, b, i);
+  } else {
+    const bool bs = (a.shape == VMASB200_BOX && b.shape == VMASB200_SPHERE) || (b.shape == VMASB200_BOX && a.shape == VMASB200_SPHERE);
+    bool r;
+    if (bs) {  // core.py:1936-1964
+      const bool a_box = b.shape == VMASB200_SPHERE;
+      const QPose& box = a_box ? a : b;
+      const QPose& sph = a_box ? b : a;
+      r = overlap_box_sphere(box, q_pos(box, i), q_rot(box, i), sph, q_pos(sph, i));
+    } else {
+      r = pair_distance(a, b, i) < 0.f;  // core.py:1934
+    }
+    out_b[i] = r ? 1 : 0;
+  }
+}
+
+__global__ void __launch_bounds__(256) point_query_kernel(const __grid_constant__ QPose a, const float* __restrict__ pts,
+                                                          long long ps, long long pxy, float* __restrict__ out, long long n) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  out[i] = dist_from_point(a, q_pos(a, i), q_rot(a, i), mk(pts[i * ps], pts[i * ps + pxy]));
+}
+
+}  // namespace vb

@@ -9,6 +9,7 @@
 #include <new>
 
 #include "kernels.cuh"
+#include "queries.cuh"
 #include "plan.h"
 
 namespace vb {
@@ -404,6 +405,54 @@ int vmasb200_cast_rays(vmasb200_plan* pl, const float* dyn, const float* stat, i
   const long long total = (long long)n * n_rays;
   cast_rays_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(kp, dyn, stat ? stat : dyn, ld, entity, angles,
                                                                    angles_stride, n_rays, max_range, rt, out, n);
+  VB_CUDA(cudaGetLastError());
+  return VMASB200_OK;
+}
+
+static int to_qpose(const vmasb200_pose* p, QPose* q, const char* who) {
+  if (!p || !p->pos || (p->shape != VMASB200_SPHERE && p->shape != VMASB200_BOX && p->shape != VMASB200_LINE) ||
+      (p->shape != VMASB200_SPHERE && !p->rot)) {
+    set_error(std::string(who) + ": bad pose (shape, pos, rot of a box / line)");
+    return VMASB200_ERR_INVALID;
+  }
+  q->shape = p->shape;
+  q->radius = (float)p->radius; q->length = (float)p->length; q->width = (float)p->width;
+  q->overlap_min = (float)(p->radius + 4.0 / 6e2);
+  q->pos = p->pos; q->ps = p->pos_stride; q->pxy = p->pos_stride_xy;
+  q->rot = p->rot; q->rs = p->rot_stride;
+  return VMASB200_OK;
+}
+
+int vmasb200_get_distance(const vmasb200_pose* a, const vmasb200_pose* b, float* out, int64_t n, void* stream) {
+  QPose qa, qb;
+  int rc;
+  if ((rc = to_qpose(a, &qa, "get_distance")) || (rc = to_qpose(b, &qb, "get_distance"))) return rc;
+  if (!out || n < 0) { set_error("get_distance: bad argument"); return VMASB200_ERR_INVALID; }
+  if (n == 0) return VMASB200_OK;
+  pair_query_kernel<QM_DISTANCE><<<(unsigned)((n + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(qa, qb, out, nullptr, n);
+  VB_CUDA(cudaGetLastError());
+  return VMASB200_OK;
+}
+
+int vmasb200_is_overlapping(const vmasb200_pose* a, const vmasb200_pose* b, uint8_t* out, int64_t n, void* stream) {
+  QPose qa, qb;
+  int rc;
+  if ((rc = to_qpose(a, &qa, "is_overlapping")) || (rc = to_qpose(b, &qb, "is_overlapping"))) return rc;
+  if (!out || n < 0) { set_error("is_overlapping: bad argument"); return VMASB200_ERR_INVALID; }
+  if (n == 0) return VMASB200_OK;
+  pair_query_kernel<QM_OVERLAP><<<(unsigned)((n + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(qa, qb, nullptr, out, n);
+  VB_CUDA(cudaGetLastError());
+  return VMASB200_OK;
+}
+
+int vmasb200_get_distance_from_point(const vmasb200_pose* a, const float* points, int64_t points_stride,
+                                     int64_t points_stride_xy, float* out, int64_t n, void* stream) {
+  QPose qa;
+  int rc;
+  if ((rc = to_qpose(a, &qa, "get_distance_from_point"))) return rc;
+  if (!points || !out || n < 0) { set_error("get_distance_from_point: bad argument"); return VMASB200_ERR_INVALID; }
+  if (n == 0) return VMASB200_OK;
+  point_query_kernel<<<(unsigned)((n + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(qa, points, points_stride, points_stride_xy, out, n);
   VB_CUDA(cudaGetLastError());
   return VMASB200_OK;
 }

@@ -4,6 +4,8 @@
 * ``vmas.simulator.core.World.cast_rays``  (core.py:1661)  -> ``vmasb200_cast_rays``; ``Lidar.measure``
   (sensors.py:100) additionally returns the measurement the step's LIDAR epilogue already produced when nothing
   touched the state in between.
+* ``World.get_distance / is_overlapping / get_distance_from_point`` (core.py:1787-1966, the queries reward code makes
+  between steps) -> one launch each (``vmasb200_get_distance`` ...), reading the entities' state tensors in place.
 
 ``enable(world_or_env)`` patches ONE world instance (and its Lidar sensors); ``make_env``, ``Environment.step``, the
 scenario hooks and the returned obs / reward / done / info tensors stay untouched.  Nothing from ``vmas`` is imported:
@@ -29,7 +31,7 @@ from typing import Dict, List, Optional
 
 import numpy as np
 
-from . import _lib
+from . import _lib, queries
 from .plan import StepPlan
 from .worlddesc import CStepIO, UnsupportedWorld, WorldDesc  # noqa: F401
 
@@ -275,6 +277,50 @@ class WorldBinding:
         return out
 
 
+    # ------------------------------------------------------------------ distance queries of reward code
+    def _poses(self, *entities):
+        """CPose per entity from its live state tensors, or None when the reference's torch path must answer
+        (autograd in play, or a shape the library does not know: the reference raises for those itself)."""
+        torch = self.torch
+        out, keep = [], []
+        for e in entities:
+            sh = queries.shape_of(e)
+            pos, rot = e.state.pos, e.state.rot
+            if sh is None or pos is None or not pos.is_cuda:
+                return None
+            if torch.is_grad_enabled() and (pos.requires_grad or (rot is not None and rot.requires_grad)):
+                return None
+            p, k = queries.make_pose(*sh, pos, rot, torch)
+            out.append(p)
+            keep.append(k)
+        return out, keep
+
+    def get_distance(self, entity_a, entity_b, env_index=None):
+        ps = self._poses(entity_a, entity_b) if env_index is None else None  # env_index: the reference's own quirks
+        if ps is None:
+            return self.orig_get_distance(entity_a, entity_b, env_index)
+        (pa, pb), keep = ps
+        return queries.get_distance(pa, pb, self.n, entity_a.state.pos, self.torch)
+
+    def is_overlapping(self, entity_a, entity_b, env_index=None):
+        ps = self._poses(entity_a, entity_b) if env_index is None else None
+        if ps is None:
+            return self.orig_is_overlapping(entity_a, entity_b, env_index)
+        (pa, pb), keep = ps
+        return queries.is_overlapping(pa, pb, self.n, entity_a.state.pos, self.torch)
+
+    def get_distance_from_point(self, entity, test_point_pos, env_index=None):
+        torch = self.torch
+        ok = (env_index is None and torch.is_tensor(test_point_pos) and test_point_pos.is_cuda
+              and tuple(test_point_pos.shape) == (self.n, 2)
+              and not (torch.is_grad_enabled() and test_point_pos.requires_grad))
+        ps = self._poses(entity) if ok else None
+        if ps is None:
+            return self.orig_get_distance_from_point(entity, test_point_pos, env_index)
+        (pa,), keep = ps
+        return queries.get_distance_from_point(pa, test_point_pos, self.n, torch)
+
+
 def _joints_in_order(world, ents):
     """JointConstraints in the order _apply_vectorized_enviornment_force meets them (core.py:2111-2121)."""
     out = []
@@ -301,6 +347,12 @@ def enable(world_or_env, exact: bool = False) -> WorldBinding:
     world.cast_rays = types.MethodType(
         lambda self, entity, angles, max_range, entity_filter=lambda _: False: b.cast_rays(entity, angles, max_range, entity_filter),
         world)
+    b.orig_get_distance, b.orig_is_overlapping = world.get_distance, world.is_overlapping
+    b.orig_get_distance_from_point = world.get_distance_from_point
+    world.get_distance = types.MethodType(lambda self, a, c, env_index=None: b.get_distance(a, c, env_index), world)
+    world.is_overlapping = types.MethodType(lambda self, a, c, env_index=None: b.is_overlapping(a, c, env_index), world)
+    world.get_distance_from_point = types.MethodType(
+        lambda self, entity, test_point_pos, env_index=None: b.get_distance_from_point(entity, test_point_pos, env_index), world)
     orig_reset = world.reset
 
     def reset(self, env_index=None):
@@ -324,7 +376,7 @@ def disable(world_or_env) -> None:
     b = getattr(world, "_vmasb200", None)
     if b is None:
         return
-    for name in ("step", "cast_rays", "reset"):
+    for name in ("step", "cast_rays", "reset", "get_distance", "is_overlapping", "get_distance_from_point"):
         if name in world.__dict__:
             del world.__dict__[name]
     for sensor, _ in b._orig_measures:
