@@ -28,7 +28,7 @@ def parse():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=10)
-    ap.add_argument("--impl", default="b200", choices=["b200", "reference", "reference-cuda", "dropin"],
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference", "reference-cuda", "dropin", "queries"],
                     help="b200: the CUDA step through the C ABI (the driver's arm); reference: the reference's CPU path; "
                          "reference-cuda / dropin: the reference Environment on this GPU with its own torch World.step, "
                          "or with vectorizedmultiagentsimulator_b200.dropin enabled (reported comparison, needs oracle/_ref)")
@@ -431,11 +431,82 @@ def run_env_cuda(args, rank):
     print(json.dumps(line), flush=True)
 
 
+def run_queries(args, rank):
+    """World.get_distance on device-resident poses, one launch per call, per shape combination; the
+    reference's torch implementation on the same tensors beside it when oracle/_ref travelled.  One JSON line."""
+    if rank != 0:
+        return
+    import torch
+
+    from vectorizedmultiagentsimulator_b200 import queries
+    from vectorizedmultiagentsimulator_b200.worlddesc import BOX, LINE, SPHERE
+
+    dev = torch.device("cuda", 0)
+    n, K, W = args.num_envs, args.steps, max(args.warmup, 3)
+    R = max(2, -(-2 * L2_BYTES // (n * 4 * 7)))  # pose sets visited round-robin: inputs come from HBM
+    g = torch.Generator().manual_seed(1)
+    sets = [[((torch.rand(n, 2, generator=g) * 2 - 1).to(dev), (torch.rand(n, 1, generator=g) * 6.28).to(dev)) for _ in range(2)]
+            for _ in range(R)]
+    dims = {SPHERE: (0.1, 0.0, 0.0), BOX: (0.0, 0.4, 0.2), LINE: (0.0, 0.5, 0.0)}
+    names = {SPHERE: "sphere", BOX: "box", LINE: "line"}
+    ref_world = None
+    ref_dir = os.path.join(ROOT, "oracle", "_ref")
+    if os.path.isdir(os.path.join(ref_dir, "vmas")):
+        sys.path[:0] = [ref_dir, os.path.join(ROOT, "oracle", "gym_stub")]
+        from vmas.simulator import core as rcore
+
+        ref_world = rcore.World(batch_dim=n, device=dev)
+        mk = {SPHERE: lambda: rcore.Sphere(0.1), BOX: lambda: rcore.Box(length=0.4, width=0.2), LINE: lambda: rcore.Line(length=0.5)}
+    peak, peak_src = peaks()
+    res = {}
+    for sa, sb in ((SPHERE, SPHERE), (BOX, SPHERE), (LINE, SPHERE), (LINE, LINE), (BOX, LINE), (BOX, BOX)):
+        poses = [(queries.make_pose(sa, *dims[sa], s[0][0], s[0][1], torch), queries.make_pose(sb, *dims[sb], s[1][0], s[1][1], torch))
+                 for s in sets]
+        for i in range(W * R):
+            queries.get_distance(poses[i % R][0][0], poses[i % R][1][0], n, sets[0][0][0], torch)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(K):
+            queries.get_distance(poses[i % R][0][0], poses[i % R][1][0], n, sets[0][0][0], torch)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / K
+        alg = 4 * n * (2 + (sa != SPHERE) + 2 + (sb != SPHERE) + 1)
+        r = {"ms": ms, "queries_per_s": n / (ms * 1e-3), "hbm_frac": alg / (ms * 1e-3) / 1e9 / peak}
+        if ref_world is not None:
+            ea = rcore.Landmark(f"a{sa}{sb}", shape=mk[sa]())
+            eb = rcore.Landmark(f"b{sa}{sb}", shape=mk[sb]())
+            for e, s in ((ea, sets[0][0]), (eb, sets[0][1])):
+                ref_world.add_landmark(e)  # batch_dim + device (core.py:1178)
+                e.state.pos, e.state.rot = s[0], s[1]
+            for _ in range(3):
+                ref_world.get_distance(ea, eb)
+            torch.cuda.synchronize()
+            e0.record()
+            for _ in range(max(3, K // 10)):
+                ref_world.get_distance(ea, eb)
+            e1.record()
+            torch.cuda.synchronize()
+            r["reference_torch_cuda_ms"] = e0.elapsed_time(e1) / max(3, K // 10)
+        res[f"{names[sa]}-{names[sb]}"] = r
+    ss = res["sphere-sphere"]
+    print(json.dumps({"impl": "queries", "metric": "distance_queries_per_sec", "value": ss["queries_per_s"], "unit": "queries/s",
+                      "n_gpus": 1, "steps": K, "warmup": W, "ms_per_step": ss["ms"], "higher_is_better": True, "dtype": "f32",
+                      "data": "synthetic", "config": {"workload": f"World.get_distance, num_envs={n}, one launch per call",
+                                                     "l2": f"{R} pose sets visited round-robin"},
+                      "roofline": {"bound": "hbm", "achieved": ss["hbm_frac"] * peak, "peak": peak, "unit": "GB/s",
+                                   "frac": ss["hbm_frac"], "traffic": None, "peak_source": peak_src, "kernel": "vb::pair_query_kernel"},
+                      "per_shape_pair": res, "gpu_launches": K}), flush=True)
+
+
 def main():
     args = parse()
     rank, local_rank, world = dist_env()
     if args.impl in ("reference-cuda", "dropin"):
         run_env_cuda(args, rank)
+    elif args.impl == "queries":
+        run_queries(args, rank)
     elif args.impl == "reference":
         run_reference(args, rank, world)
     else:

@@ -254,6 +254,18 @@ int vmasb200_is_overlapping(const vmasb200_pose* a, const vmasb200_pose* b, uint
 int vmasb200_get_distance_from_point(const vmasb200_pose* a, const float* points, int64_t points_stride,
                                      int64_t points_stride_xy, float* out, int64_t n_envs, void* stream);
 
+/* ---- action pre-processing of Environment._set_action for continuous actions without communication / noise
+ * (environment.py:615-668): u = clamp(action, -u_range, +u_range) (when clamp != 0) * u_multiplier, one
+ * launch per agent instead of ~10 and no host synchronisation.
+ *  action d: [n_envs][action_size] fp32, element (i, k) at action[i * stride_env + k * stride_k]
+ *  u_range, u_multiplier h: [action_size] (agent.action.u_range_tensor / u_multiplier_tensor as fp32), action_size <= 8
+ *  u_out d: [n_envs][action_size] contiguous (the new agent.action.u)
+ *  flags d: one int32 the launch ORs into: bit 0 = a NaN action (environment.py:622), bit 1 = |action| > u_range after
+ *  the optional clamp (environment.py:647-649).  The caller reads it when it wants the reference's assertions. */
+int vmasb200_set_action(const float* action, int64_t stride_env, int64_t stride_k, int32_t action_size,
+                        const float* u_range, const float* u_multiplier, int32_t clamp, float* u_out, int32_t* flags,
+                        int64_t n_envs, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -210,3 +210,99 @@ def test_distance_queries_match_reference(scenario, kw):
     assert torch.equal(world.get_distance(a0, a1, env_index=3), b.orig_get_distance(a0, a1, 3))
     dropin.disable(env)
     assert "get_distance" not in world.__dict__
+
+
+
+@pytest.mark.parametrize("scenario,kw", [("navigation", dict(n_agents=4)), ("transport", dict(n_agents=4)),
+                                         ("joint_passage", dict()), ("football", dict(ai_red_agents=False))])
+def test_static_io_equals_fresh_buffers_bitwise(scenario, kw):
+    """enable(env, static_io=True) steps in place on persistent buffers; against a drop-in env that binds fresh output
+    buffers every step, everything Environment.step returns and the whole world state must be bit-identical at every
+    step, across a full reset and a partial reset_at; the state tensors keep their addresses."""
+    import torch
+
+    from vectorizedmultiagentsimulator_b200 import dropin
+
+    vmas = _vmas()
+    n, steps = 96, 30
+    e1, e2 = _make(vmas, scenario, kw, n, 1), _make(vmas, scenario, kw, n, 1)
+    dropin.enable(e1)
+    b2 = dropin.enable(e2, static_io=True)
+
+    def leaves(x):
+        if isinstance(x, dict):
+            return [t for k in sorted(x) for t in leaves(x[k])]
+        if isinstance(x, (list, tuple)):
+            return [t for v in x for t in leaves(v)]
+        return [x]
+
+    torch.manual_seed(7)
+    ptrs = None
+    for t in range(steps):
+        if t == 10:
+            o1, o2 = e1.reset(seed=3), e2.reset(seed=3)
+            assert all(torch.equal(a, c) for a, c in zip(leaves(o1), leaves(o2)))
+            ptrs = None
+        if t == 20:
+            # the reference keeps ONE host RNG state for all Environments (class attribute vmas_random_state,
+            # environment.py:58): both resets must start from the same one (joint_passage draws a randperm from it)
+            rs = type(e1).vmas_random_state
+            saved = list(rs)
+            torch.manual_seed(11)
+            e1.reset_at(5)
+            rs[:] = saved
+            torch.manual_seed(11)
+            e2.reset_at(5)
+            torch.manual_seed(12)
+        acts = [torch.rand(n, a.action_size, device="cuda") * 2 * a.u_range - a.u_range for a in e1.agents]
+        r1 = e1.step([a.clone() for a in acts])
+        r2 = e2.step([a.clone() for a in acts])
+        for i, (a, c) in enumerate(zip(leaves(r1), leaves(r2))):
+            assert torch.equal(a.nan_to_num(), c.nan_to_num()), f"{scenario}: output {i} differs at step {t}"
+        assert torch.equal(_state(e1), _state(e2)), f"{scenario}: state differs at step {t}"
+        now = [a.state.pos.data_ptr() for a in e2.agents]
+        assert ptrs is None or now == ptrs, "state views moved"
+        ptrs = now
+    assert b2.n_steps == steps
+
+
+def test_set_action_matches_reference_and_keeps_its_assertions():
+    """Environment._set_action of a patched env (one launch per agent, vmasb200_set_action) against the reference's:
+    agent.action.u bit-identical for in-range and clamped actions; a NaN action and - with clamp_action off - an action
+    out of range still raise AssertionError inside Environment.step, before the world moves."""
+    import torch
+
+    from vectorizedmultiagentsimulator_b200 import dropin
+
+    vmas = _vmas()
+    n = 200
+    for scenario, kw in (("navigation", dict(n_agents=4)), ("transport", dict(n_agents=4)), ("football", dict(ai_red_agents=False))):
+        ref = _make(vmas, scenario, kw, n, 1)
+        env = _make(vmas, scenario, kw, n, 1)
+        b = dropin.enable(env)
+        assert "_set_action" in env.__dict__
+        torch.manual_seed(5)
+        for scale in (1.0, 1.7):
+            for a1, a2 in zip(ref.agents, env.agents):
+                act = (torch.rand(n, a1.action_size, device="cuda") * 2 - 1) * a1.u_range * scale
+                if not ref.clamp_action and scale > 1:
+                    continue
+                ref._set_action(act.clone(), a1)
+                env._set_action(act.clone(), a2)
+                assert torch.equal(a1.action.u, a2.action.u), (scenario, scale)
+                # a strided view of a wider tensor is read in place
+                wide = torch.zeros(n, a1.action_size + 3, device="cuda")
+                wide[:, 1:1 + a1.action_size] = act
+                env._set_action(wide[:, 1:1 + a1.action_size], a2)
+                assert torch.equal(a1.action.u, a2.action.u)
+        b.check_actions()
+        before = _state(env).clone()
+        acts = [torch.zeros(n, a.action_size, device="cuda") for a in env.agents]
+        acts[1][7, 0] = float("nan")
+        with pytest.raises(AssertionError):
+            env.step(acts)
+        assert torch.equal(_state(env), before), "the world moved although an action was NaN"
+        acts[1][7, 0] = 0.0
+        env.step(acts)  # and it recovers
+        dropin.disable(env)
+        assert "_set_action" not in env.__dict__

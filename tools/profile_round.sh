@@ -21,6 +21,7 @@ for sc in transport football joint_passage simple_spread; do bench $sc --scenari
 for sc in navigation transport football; do bench ${sc}_1m --scenario $sc --num-envs 1048576 --steps 50 --no-cpu-baseline --no-e2e; done
 for n in 4096 16384 65536 262144; do bench football_$n --scenario football --num-envs $n --steps 100 --no-cpu-baseline --no-e2e; done
 # 3. reference arms: the reference's torch CPU step, its torch CUDA step, and the drop-in inside its Environment
+bench queries --impl queries --num-envs 1048576 --steps 100
 bench reference_navigation --impl reference --steps 3 --warmup 1
 for sc in navigation transport; do
   bench reference-cuda_$sc --impl reference-cuda --scenario $sc --steps 50

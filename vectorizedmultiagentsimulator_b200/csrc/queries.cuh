@@ -114,4 +114,25 @@ __global__ void __launch_bounds__(256) point_query_kernel(const __grid_constant_
   out[i] = dist_from_point(a, q_pos(a, i), q_rot(a, i), mk(pts[i * ps], pts[i * ps + pxy]));
 }
 
+// Environment._set_action, continuous physical actions (environment.py:615-668): one thread per (env, component).
+struct ActParams { float range[8], mult[8]; };
+__global__ void __launch_bounds__(256) set_action_kernel(const float* __restrict__ action, long long se, long long sk, int k_n,
+                                                         const __grid_constant__ ActParams ap, int clamp,
+                                                         float* __restrict__ u_out, int* __restrict__ flags, long long n) {
+  const long long gid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  int bad = 0;
+  if (gid < n * k_n) {
+    const long long i = gid / k_n;
+    const int k = (int)(gid - i * k_n);
+    float x = action[i * se + k * sk];
+    const float r = ap.range[k];
+    if (x != x) bad |= 1;                                                   // assert not action.isnan().any()
+    if (clamp && x == x) x = fminf(fmaxf(x, -r), r);                         // torch.clamp keeps NaN
+    if (fabsf(x) > r) bad |= 2;                                             // assert not any(|u| > u_range)
+    u_out[gid] = x * ap.mult[k];                                            // agent.action.u *= u_multiplier_tensor
+  }
+  bad = __reduce_or_sync(0xffffffffu, bad);
+  if (bad && (threadIdx.x & 31) == 0) atomicOr(flags, bad);
+}
+
 }  // namespace vb

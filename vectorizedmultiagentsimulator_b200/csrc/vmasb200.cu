@@ -457,6 +457,22 @@ int vmasb200_get_distance_from_point(const vmasb200_pose* a, const float* points
   return VMASB200_OK;
 }
 
+int vmasb200_set_action(const float* action, int64_t stride_env, int64_t stride_k, int32_t action_size,
+                        const float* u_range, const float* u_multiplier, int32_t clamp, float* u_out, int32_t* flags,
+                        int64_t n, void* stream) {
+  if (!action || !u_range || !u_multiplier || !u_out || !flags || n < 0 || action_size < 1 || action_size > 8) {
+    set_error("set_action: bad argument (1 <= action_size <= 8)"); return VMASB200_ERR_INVALID;
+  }
+  if (n == 0) return VMASB200_OK;
+  ActParams ap{};
+  for (int k = 0; k < action_size; ++k) { ap.range[k] = u_range[k]; ap.mult[k] = u_multiplier[k]; }
+  const long long total = (long long)n * action_size;
+  set_action_kernel<<<(unsigned)((total + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      action, stride_env, stride_k, action_size, ap, clamp, u_out, flags, n);
+  VB_CUDA(cudaGetLastError());
+  return VMASB200_OK;
+}
+
 int vmasb200_sync_check(vmasb200_plan* pl, void* stream, int64_t* n_fixups) {
   VB_CUDA(cudaStreamSynchronize(static_cast<cudaStream_t>(stream)));
   VB_CUDA(cudaGetLastError());

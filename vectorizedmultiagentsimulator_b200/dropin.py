@@ -62,6 +62,10 @@ class WorldBinding:
         self.orig_step = world.step
         self.orig_cast_rays = world.cast_rays
         self.dirty = True
+        self._act_consts: Dict[int, tuple] = {}
+        self._act_flags = None
+        self._act_pending = False
+        self.static_io = False  # persistent buffers stepped in place (enable(..., static_io=True))
         self.desc_json = None
         self.plan: Optional[StepPlan] = None
         self.lidar_valid = False
@@ -88,6 +92,7 @@ class WorldBinding:
         self.stat = torch.zeros(max(pl.stat_rows, 1), ld, device=dev)
         self.act = None
         self.lid = None
+        self._act_views = []
         self.dyn_ents = [(e, int(pl.dyn_slot[i])) for i, e in enumerate(self.ents) if pl.dyn_slot[i] >= 0]
         self.stat_ents = [(e, int(pl.stat_slot[i])) for i, e in enumerate(self.ents) if pl.stat_slot[i] >= 0]
         self.act_agents = [(e, int(pl.act_slot[i])) for i, e in enumerate(self.ents) if pl.act_slot[i] >= 0]
@@ -171,6 +176,7 @@ class WorldBinding:
     # ------------------------------------------------------------------ World.step
     def step(self):
         world, torch = self.world, self.torch
+        self.check_actions()
         if self.dirty or len(world.entities) != len(getattr(self, "ents", ())):
             self.refresh()
         if self._needs_grad():
@@ -197,10 +203,17 @@ class WorldBinding:
                 self._tp[a], self._ts[a] = t.data_ptr(), t.stride(0)
             else:
                 self._tp[a], self._ts[a] = None, 0
-        # fresh output buffers every step: the reference rebinds new tensors too (core.py:2866-2907)
-        dyn_out = torch.empty_like(self.dyn)
-        act = torch.empty(pl.act_rows, ld, device=self.device) if pl.act_rows else None
-        lid = torch.empty(pl.lidar_rows, ld, device=self.device) if pl.lidar_rows else None
+        if self.static_io:
+            # persistent buffers, stepped in place (the kernel stages a tile completely before it stores it): state views
+            # keep their addresses and nothing is allocated
+            dyn_out = self.dyn
+            act = self.act if self.act is not None else (torch.empty(pl.act_rows, ld, device=self.device) if pl.act_rows else None)
+            lid = self.lid if self.lid is not None else (torch.empty(pl.lidar_rows, ld, device=self.device) if pl.lidar_rows else None)
+        else:
+            # fresh output buffers every step: the reference rebinds new tensors too (core.py:2866-2907)
+            dyn_out = torch.empty_like(self.dyn)
+            act = torch.empty(pl.act_rows, ld, device=self.device) if pl.act_rows else None
+            lid = torch.empty(pl.lidar_rows, ld, device=self.device) if pl.lidar_rows else None
         io.dyn_in, io.dyn_out = self.dyn.data_ptr(), dyn_out.data_ptr()
         io.stat = self.stat.data_ptr() if pl.stat_rows else None
         io.act_out = act.data_ptr() if act is not None else None
@@ -209,16 +222,19 @@ class WorldBinding:
         io.stream = torch.cuda.current_stream(self.device).cuda_stream
         pl.step_io(io)
         # bind the results
-        self.dyn = dyn_out
-        self._dyn_views = self._views_of(dyn_out)
-        for e, views in self._dyn_views:
+        if dyn_out is not self.dyn:
+            self.dyn = dyn_out
+            self._dyn_views = self._views_of(dyn_out)
+        for e, views in self._dyn_views:  # (sync_in left every field bound to its view: nothing to do when in place)
             st = e.state
-            st._pos, st._vel, st._rot, st._ang_vel = views
+            if st._pos is not views[0]:
+                st._pos, st._vel, st._rot, st._ang_vel = views
         if act is not None:
-            self.act = act
-            for ag, o in self.act_agents:
-                ag.state._force = act[o:o + 2, :n].t()
-                ag.state._torque = act[o + 2:o + 3, :n].t()
+            if act is not self.act:
+                self.act = act
+                self._act_views = [(ag, act[o:o + 2, :n].t(), act[o + 2:o + 3, :n].t()) for ag, o in self.act_agents]
+            for ag, vf, vt in self._act_views:
+                ag.state._force, ag.state._torque = vf, vt
         if lid is not None:
             self.lid = lid
             self.lidar_valid = True
@@ -277,6 +293,51 @@ class WorldBinding:
         return out
 
 
+    # ------------------------------------------------------------------ Environment._set_action
+    def set_action(self, env, action, agent):
+        """Continuous physical actions without communication / noise: one launch (vmasb200_set_action) instead of the
+        reference's ~10 ops and 3 host synchronisations per agent (environment.py:615-668).  The reference's assertions
+        (NaN action, action out of range) are kept: the launches OR into one flag word that ``step`` reads - a single
+        synchronisation per Environment.step - before it touches the world.  Everything else takes the original."""
+        torch = self.torch
+        act = getattr(agent, "action", None)
+        noise = getattr(act, "u_noise", 0)
+        noisy = any(v > 0 for v in noise) if isinstance(noise, (list, tuple)) else noise > 0
+        ok = (getattr(env, "continuous_actions", False) and torch.is_tensor(action) and action.is_cuda
+              and action.dtype == torch.float32 and action.dim() == 2 and action.shape[0] == self.n
+              and (self.world.dim_c == 0 or agent.silent) and act is not None and not noisy
+              and 1 <= agent.action_size <= 8 and action.shape[1] == agent.action_size
+              and not (getattr(env, "grad_enabled", False) and action.requires_grad))
+        if not ok:
+            return self.orig_set_action(action, agent)
+        key = (id(agent), repr(act.u_range), repr(act.u_multiplier))
+        c = self._act_consts.get(id(agent))
+        if c is None or c[0] != key:
+            k = agent.action_size
+            rng = (C.c_float * k)(*[float(v) for v in act.u_range_tensor.tolist()])
+            mul = (C.c_float * k)(*[float(v) for v in act.u_multiplier_tensor.tolist()])
+            c = self._act_consts[id(agent)] = (key, rng, mul)
+        if self._act_flags is None:
+            self._act_flags = torch.zeros(1, dtype=torch.int32, device=self.device)
+        u = torch.empty(self.n, agent.action_size, device=self.device)
+        _lib.check(_lib.lib().vmasb200_set_action(
+            action.data_ptr(), action.stride(0), action.stride(1), agent.action_size, c[1], c[2],
+            int(bool(getattr(env, "clamp_action", False))), u.data_ptr(), self._act_flags.data_ptr(), self.n,
+            torch.cuda.current_stream(self.device).cuda_stream), "vmasb200_set_action")
+        act.u = u
+        self._act_pending = True
+
+    def check_actions(self):
+        """The reference's assertions on the actions set since the last check (environment.py:622, 647-649)."""
+        if not self._act_pending:
+            return
+        self._act_pending = False
+        bad = int(self._act_flags.item())
+        if bad:
+            self._act_flags.zero_()
+            assert not bad & 1, "an action holds NaN"
+            assert not bad & 2, "Physical actions of an agent are out of its range"
+
     # ------------------------------------------------------------------ distance queries of reward code (SURVEY 8 f3)
     def _poses(self, *entities):
         """CPose per entity from its live state tensors, or None when the reference's torch path must answer
@@ -333,9 +394,13 @@ def _joints_in_order(world, ents):
     return out
 
 
-def enable(world_or_env, exact: bool = False) -> WorldBinding:
-    """Routes ``world.step`` / ``world.cast_rays`` / its Lidars' ``measure`` of ONE world through libvmasb200.
-    ``exact=True`` takes the per-substep exact path instead of the verified speculative single launch."""
+def enable(world_or_env, exact: bool = False, static_io: bool = False) -> WorldBinding:
+    """Routes ``world.step`` / ``world.cast_rays`` / its Lidars' ``measure`` / the distance queries of ONE world through
+    libvmasb200.  ``exact=True`` takes the per-substep exact path instead of the verified speculative single launch.
+    ``static_io=True`` (opt-in): the step works IN PLACE on persistent buffers instead of binding fresh output tensors
+    every step - no allocations and no new views per step, state tensors keep their addresses (what CUDA-graph capture
+    of user code around the step needs) - at the price that a state tensor a caller kept from an earlier step changes
+    with the world instead of staying a snapshot, unlike the reference (core.py:2866-2907 rebinds fresh tensors)."""
     world = getattr(world_or_env, "world", world_or_env)
     if getattr(world, "_vmasb200", None) is not None:
         return world._vmasb200
@@ -368,6 +433,12 @@ def enable(world_or_env, exact: bool = False) -> WorldBinding:
                 om = sensor.measure
                 b._orig_measures.append((sensor, om))
                 sensor.measure = (lambda s, o: (lambda vectorized=True: b.measure(s, o, vectorized)))(sensor, om)
+    b.static_io = bool(static_io)
+    b._env = None
+    if world is not world_or_env and hasattr(world_or_env, "_set_action"):  # an Environment: its action pre-processing too
+        env = world_or_env
+        b._env, b.orig_set_action = env, env._set_action
+        env._set_action = types.MethodType(lambda self, action, agent: b.set_action(self, action, agent), env)
     return b
 
 
@@ -382,4 +453,6 @@ def disable(world_or_env) -> None:
     for sensor, _ in b._orig_measures:
         if "measure" in sensor.__dict__:
             del sensor.__dict__["measure"]
+    if getattr(b, "_env", None) is not None:
+        b._env.__dict__.pop("_set_action", None)
     world._vmasb200 = None
