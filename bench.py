@@ -28,7 +28,7 @@ def parse():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=10)
-    ap.add_argument("--impl", default="b200", choices=["b200", "reference", "reference-cuda", "dropin", "queries"],
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference", "reference-cuda", "dropin", "dropin-hooks", "queries"],
                     help="b200: the CUDA step through the C ABI (the driver's arm); reference: the reference's CPU path; "
                          "reference-cuda / dropin: the reference Environment on this GPU with its own torch World.step, "
                          "or with vectorizedmultiagentsimulator_b200.dropin enabled (reported comparison, needs oracle/_ref)")
@@ -38,6 +38,7 @@ def parse():
     ap.add_argument("--exact", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--static-io", type=int, default=0, help="dropin arms: step in place on persistent buffers")
     return ap.parse_args()
 
 
@@ -391,10 +392,12 @@ def run_env_cuda(args, rank):
     world = env.world
     if world._substeps != wl.desc.substeps:
         world._substeps, world._sub_dt = wl.desc.substeps, world._dt / wl.desc.substeps
-    if args.impl == "dropin":
+    hooks = None
+    if args.impl in ("dropin", "dropin-hooks"):
         from vectorizedmultiagentsimulator_b200 import dropin
 
-        dropin.enable(env)
+        # dropin-hooks: also the fused reward / observation / done launches of SURVEY 8 f1 (navigation, transport)
+        hooks = dropin.enable(env, hooks=args.impl == "dropin-hooks", static_io=bool(args.static_io)).hooks
     torch.manual_seed(1234)
     acts = [[torch.rand(n, a.action_size, device="cuda") * 2 * a.u_range - a.u_range for a in env.agents] for _ in range(8)]
     inner = world.step
@@ -428,6 +431,8 @@ def run_env_cuda(args, rank):
             "config": {"workload": f"{args.scenario} num_envs={n}, reference Environment on cuda:0 (torch {torch.__version__})"},
             "world_step_ms_gpu_events": ws_gpu, "world_step_ms_wall": ws_wall, "env_step_ms_wall": el / K * 1e3,
             "world_step_env_steps_per_s": n / (ws_wall * 1e-3), "value": n * K / el, "data": "synthetic"}
+    if hooks is not None:
+        line["fused_hook_calls"], line["fallback_hook_calls"] = hooks.n_fused, hooks.n_fallback
     print(json.dumps(line), flush=True)
 
 
@@ -503,7 +508,7 @@ def run_queries(args, rank):
 def main():
     args = parse()
     rank, local_rank, world = dist_env()
-    if args.impl in ("reference-cuda", "dropin"):
+    if args.impl in ("reference-cuda", "dropin", "dropin-hooks"):
         run_env_cuda(args, rank)
     elif args.impl == "queries":
         run_queries(args, rank)

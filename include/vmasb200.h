@@ -266,6 +266,92 @@ int vmasb200_set_action(const float* action, int64_t stride_env, int64_t stride_
                         const float* u_range, const float* u_multiplier, int32_t clamp, float* u_out, int32_t* flags,
                         int64_t n_envs, void* stream);
 
+/* ---- scenario hooks: what Environment._get_from_scenario (environment.py:253-308) asks of a scenario
+ * after every World.step - observation / reward / done / info - as one or two launches per step instead of tens to
+ * hundreds of small torch ops with host synchronisations (World.collides, boolean-mask indexing).  All tensors are read
+ * and written in place through (pointer, strides); nothing is allocated and nothing synchronises. */
+typedef struct vmasb200_vec {     /* a [n_envs][k] device tensor: element (i, k) at p[i * stride_env + k * stride_k] */
+  const void* p;
+  int64_t stride_env, stride_k;
+} vmasb200_vec;
+
+enum {
+  VMASB200_OBS_COPY = 0, /* a            (fp32)                                              */
+  VMASB200_OBS_SUB = 1,  /* a - b        (fp32; e.g. agent.state.pos - goal.state.pos)         */
+  VMASB200_OBS_CSUB = 2, /* c - a        (fp32; e.g. sensor._max_range - sensor.measure())     */
+  VMASB200_OBS_BOOL = 3  /* a != 0 ? 1 : 0 (a is a torch.bool / uint8 tensor; cat promotes it) */
+};
+/* One block of columns of one observation tensor: out[i][col0 + k] = op(a[i][k], b[i][k]), k < width
+ * (what one operand of the scenario's torch.cat([...], dim=-1) contributes). */
+typedef struct vmasb200_obs_seg {
+  vmasb200_vec a, b;
+  int32_t op;
+  float c;
+  int32_t width;
+  int32_t out;    /* index into outs[] */
+  int32_t col0;
+  int32_t reserved;
+} vmasb200_obs_seg;
+#define VMASB200_OBS_MAX_SEGS 128
+#define VMASB200_OBS_MAX_OUTS 32
+#define VMASB200_OBS_MAX_WIDTH 352
+/* The observations of ALL agents in one launch (SoA -> [n_envs][width] transposition through shared memory).
+ * segs h: [n_segs]; outs h: [n_outs] device pointers, outs[o] d: [n_envs][out_widths[o]] contiguous fp32.
+ * Every column of every out must be covered by exactly one segment (checked). */
+int vmasb200_gather_obs(const vmasb200_obs_seg* segs, int32_t n_segs, float* const* outs, const int32_t* out_widths,
+                        int32_t n_outs, int64_t n_envs, void* stream);
+
+/* navigation.py:199-232 (reward, agent_reward), :262-273 (done), :275-280 (info): everything `Scenario.reward` computes
+ * when called for the first agent, for all agents, plus the per-agent return values and the done flags. */
+#define VMASB200_NAV_MAX_AGENTS 16
+typedef struct vmasb200_nav_agent {
+  vmasb200_vec pos, goal_pos;   /* agent.state.pos, agent.goal.state.pos: [n_envs][2]                              */
+  double radius, goal_radius;   /* agent.shape.radius (collisions, done), agent.goal.shape.radius (on_goal)         */
+  const float* pos_shaping;     /* d in : [n_envs] agent.pos_shaping of the previous step                          */
+  float* pos_shaping_out;       /* d out: [n_envs] the new agent.pos_shaping (may alias pos_shaping)               */
+  float* distance_to_goal;      /* d out: [n_envs]                                                                 */
+  uint8_t* on_goal;             /* d out: [n_envs] 0 / 1 (torch.bool storage)                                      */
+  float* pos_rew;               /* d out: [n_envs] agent.pos_rew                                                   */
+  float* agent_collision_rew;   /* d out: [n_envs] (the reference zeroes it and adds the penalties, :209, 222-228)  */
+  float* reward;                /* d out: [n_envs] what Scenario.reward(agent) returns (:230-231)                   */
+} vmasb200_nav_agent;
+typedef struct vmasb200_navigation {
+  int32_t n_agents;
+  int32_t shared_rew;
+  double pos_shaping_factor, final_reward, agent_collision_penalty, min_collision_distance;
+  vmasb200_nav_agent agent[VMASB200_NAV_MAX_AGENTS];
+  /* collidable[i][j], j < i: the static part of World.collides(agent_i, agent_j) (core.py:2788-2795); the batch-wide
+   * distance test (core.py:2796-2800) is evaluated by the call itself on `pair_flags`. */
+  uint8_t collidable[VMASB200_NAV_MAX_AGENTS][VMASB200_NAV_MAX_AGENTS];
+  float* pos_rew;               /* d out: [n_envs] Scenario.pos_rew (sum over agents in order, :205-208)            */
+  float* final_rew;             /* d out: [n_envs] Scenario.final_rew                                               */
+  uint8_t* all_goal_reached;    /* d out: [n_envs]                                                                  */
+  uint8_t* done;                /* d out: [n_envs] Scenario.done() or NULL                                           */
+  uint32_t* pair_flags;         /* d scratch: 4 words, zeroed and filled by the call                                 */
+} vmasb200_navigation;
+int vmasb200_navigation_reward(const vmasb200_navigation* nv, int64_t n_envs, void* stream);
+
+/* transport.py:130-164 (reward), :186-193 (done): package.dist_to_goal, package.on_goal (World.is_overlapping with its
+ * goal), package.color, the shared reward and the new package.global_shaping, for every package in one launch. */
+#define VMASB200_TRANSPORT_MAX_PACKAGES 8
+typedef struct vmasb200_transport_package {
+  vmasb200_pose package, goal;
+  const float* global_shaping;  /* d in : [n_envs]                                                                 */
+  float* global_shaping_out;    /* d out: [n_envs] (may alias global_shaping)                                      */
+  float* dist_to_goal;          /* d out: [n_envs]                                                                 */
+  uint8_t* on_goal;             /* d out: [n_envs]                                                                 */
+  float* color;                 /* d out: [n_envs][3] contiguous, or NULL                                          */
+} vmasb200_transport_package;
+typedef struct vmasb200_transport {
+  int32_t n_packages;
+  double shaping_factor;
+  float color_off_goal[3], color_on_goal[3]; /* Color.RED.value, Color.GREEN.value */
+  vmasb200_transport_package package[VMASB200_TRANSPORT_MAX_PACKAGES];
+  float* rew;                   /* d out: [n_envs] Scenario.rew                                                    */
+  uint8_t* done;                /* d out: [n_envs] Scenario.done() or NULL                                          */
+} vmasb200_transport;
+int vmasb200_transport_reward(const vmasb200_transport* tr, int64_t n_envs, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,187 @@
+#!/usr/bin/env python
+"""Golden vectors of the scenario hooks from the UNMODIFIED reference: what navigation.py:199-280 and
+transport.py:130-193 return and leave behind (`reward`, `observation`, `done`, the attributes they set), together with
+the inputs they read (entity state, goal positions, shaping terms of the previous step, LIDAR measurements).
+
+TEST INFRASTRUCTURE.  Run in the build container (torch CPU):
+
+    python tests/golden/make_golden_hooks.py
+
+The reference Environment is stepped with random actions; in a few envs agents are placed on / next to their goals
+and next to each other (and packages on their goal) before a step, so that on_goal, the final reward, the collision
+penalties and the thin case `distance <= min_collision_distance while no env's centres are within r_a + r_b` occur.
+Output: tests/golden/hooks/<scenario>.npz.
+"""
+import os
+import sys
+
+import numpy as np
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path[:0] = [os.path.join(ROOT, "oracle", "_ref"), os.path.join(ROOT, "oracle", "gym_stub"), ROOT, HERE]
+
+import vmas  # noqa: E402
+
+N, STEPS, KEEP = 96, 40, (0, 1, 5, 6, 7, 12, 13, 20, 21, 30, 39)
+
+
+def t2n(t):
+    return t.detach().clone().numpy()
+
+
+def navigation(name="navigation", kw=None, tag=None):
+    kw = dict(n_agents=4) if kw is None else kw
+    torch.manual_seed(1234)
+    torch.set_num_threads(1)
+    env = vmas.make_env("navigation", num_envs=N, device="cpu", seed=0, continuous_actions=True, **kw)
+    sc, world = env.scenario, env.world
+    agents = world.agents
+    A = len(agents)
+    env.reset(seed=0)
+    g = torch.Generator().manual_seed(5)
+    flags_log = []
+    orig_collides = world.collides
+    in_reward = {"on": False}
+
+    def collides(a, b):
+        r = orig_collides(a, b)
+        if in_reward["on"]:
+            flags_log[-1][agents.index(a), agents.index(b)] = bool(r)
+        return r
+
+    world.collides = collides
+    rec = {k: [] for k in ("pos", "vel", "goal", "shaping_in", "lidar", "obs", "reward", "done", "pos_rew", "final_rew",
+                           "coll_rew", "dist", "on_goal", "pos_rew_agent", "shaping_out", "all_goal", "flags")}
+    orig_reward = sc.reward
+
+    def reward(agent):
+        if agent is agents[0]:
+            rec["_pre"] = dict(pos=np.stack([t2n(a.state.pos) for a in agents]), vel=np.stack([t2n(a.state.vel) for a in agents]),
+                               goal=np.stack([t2n(a.goal.state.pos) for a in agents]),
+                               shaping_in=np.stack([t2n(a.pos_shaping) for a in agents]))
+            flags_log.append(np.zeros((A, A), bool))
+            in_reward["on"] = True
+        r = orig_reward(agent)
+        in_reward["on"] = False
+        return r
+
+    sc.reward = reward
+    for t in range(STEPS):
+        acts = [(torch.rand(N, a.action_size, generator=g) * 2 - 1) * a.u_range for a in agents]
+        if t in (5, 12, 20):  # stage the rare events in a few envs BEFORE the step (the step then moves them a little)
+            with torch.no_grad():
+                for k in range(0, 8):
+                    for a in agents[: 1 + k % A]:
+                        a.state.pos[k] = a.goal.state.pos[k] + 0.01 * (torch.rand(2, generator=g) - 0.5)
+                        a.state.vel[k] = 0.0
+                for k in range(8, 12):  # all agents on their goals
+                    for a in agents:
+                        a.state.pos[k] = a.goal.state.pos[k]
+                        a.state.vel[k] = 0.0
+                for k in range(12, 24):  # agent pairs at contact distance: 2 r + [-0.01, 0.012]
+                    i, j = k % A, (k + 1 + k // A) % A
+                    if i != j:
+                        d = 2 * agents[i].shape.radius + float(torch.rand(1, generator=g)) * 0.022 - 0.01
+                        ang = float(torch.rand(1, generator=g)) * 6.28
+                        agents[j].state.pos[k] = agents[i].state.pos[k] + d * torch.tensor([np.cos(ang), np.sin(ang)], dtype=torch.float32)
+                        agents[i].state.vel[k] = 0.0
+                        agents[j].state.vel[k] = 0.0
+            acts = [a * 0 for a in acts]
+        obs, rews, dones, infos = env.step(acts)
+        if t in KEEP:
+            pre = rec.pop("_pre")
+            for k in ("pos", "vel", "goal", "shaping_in"):
+                rec[k].append(pre[k])
+            rec["lidar"].append(np.stack([t2n(a.sensors[0]._last_measurement) for a in agents]) if sc.collisions else np.zeros((A, N, 0), np.float32))
+            rec["obs"].append(np.stack([t2n(o) for o in obs]))
+            rec["reward"].append(np.stack([t2n(r) for r in rews]))
+            rec["done"].append(t2n(dones))
+            rec["pos_rew"].append(t2n(sc.pos_rew))
+            rec["final_rew"].append(t2n(sc.final_rew))
+            rec["coll_rew"].append(np.stack([t2n(a.agent_collision_rew) for a in agents]))
+            rec["dist"].append(np.stack([t2n(a.distance_to_goal) for a in agents]))
+            rec["on_goal"].append(np.stack([t2n(a.on_goal) for a in agents]))
+            rec["pos_rew_agent"].append(np.stack([t2n(a.pos_rew) for a in agents]))
+            rec["shaping_out"].append(np.stack([t2n(a.pos_shaping) for a in agents]))
+            rec["all_goal"].append(t2n(sc.all_goal_reached))
+            rec["flags"].append(flags_log[-1].copy())
+        else:
+            rec.pop("_pre", None)
+    out = {k: np.stack(v) for k, v in rec.items()}
+    out["radius"] = np.array([a.shape.radius for a in agents], np.float64)
+    out["goal_radius"] = np.array([a.goal.shape.radius for a in agents], np.float64)
+    out["params"] = np.array([sc.pos_shaping_factor, sc.final_reward, sc.agent_collision_penalty, sc.min_collision_distance,
+                              float(sc.shared_rew), float(agents[0].sensors[0]._max_range) if sc.collisions else 0.0,
+                              float(sc.observe_all_goals)], np.float64)
+    os.makedirs(os.path.join(HERE, "hooks"), exist_ok=True)
+    np.savez_compressed(os.path.join(HERE, "hooks", f"{tag or name}.npz"), **out)
+    print(tag or name, {k: v.shape for k, v in out.items()}, "events: on_goal", int(out["on_goal"].sum()), "all_goal",
+          int(out["all_goal"].sum()), "collision penalties", int((out["coll_rew"] != 0).sum()), "flags", int(out["flags"].sum()),
+          "done", int(out["done"].sum()))
+
+
+def transport():
+    torch.manual_seed(1234)
+    torch.set_num_threads(1)
+    env = vmas.make_env("transport", num_envs=N, device="cpu", seed=0, continuous_actions=True, n_agents=4)
+    sc, world = env.scenario, env.world
+    agents, pk = world.agents, sc.packages
+    env.reset(seed=0)
+    g = torch.Generator().manual_seed(5)
+    rec = {k: [] for k in ("agent_pos", "agent_vel", "pkg_state", "goal_pos", "shaping_in", "obs", "rew", "done", "on_goal",
+                           "dist", "shaping_out", "color")}
+    orig_reward = sc.reward
+
+    def reward(agent):
+        if agent is agents[0]:
+            rec["_pre"] = dict(
+                agent_pos=np.stack([t2n(a.state.pos) for a in agents]), agent_vel=np.stack([t2n(a.state.vel) for a in agents]),
+                pkg_state=np.stack([t2n(torch.cat([p.state.pos, p.state.vel, p.state.rot, p.state.ang_vel], -1)) for p in pk]),
+                goal_pos=np.stack([t2n(p.goal.state.pos) for p in pk]), shaping_in=np.stack([t2n(p.global_shaping) for p in pk]))
+        return orig_reward(agent)
+
+    sc.reward = reward
+    for t in range(STEPS):
+        acts = [(torch.rand(N, a.action_size, generator=g) * 2 - 1) * a.u_range for a in agents]
+        if t in (5, 12, 20):
+            with torch.no_grad():
+                for p in pk:
+                    L, W, r = p.shape.length, p.shape.width, p.goal.shape.radius
+                    for k in range(0, 24):  # package centre from inside the goal to just outside the overlap distance
+                        d = (k / 23.0) * (max(L, W) / 2 + r + 0.02)
+                        ang = float(torch.rand(1, generator=g)) * 6.28
+                        p.state.pos[k] = p.goal.state.pos[k] + d * torch.tensor([np.cos(ang), np.sin(ang)], dtype=torch.float32)
+                        p.state.vel[k] = 0.0
+                for a in agents:  # keep the agents away so that the step leaves the staged package alone
+                    for k in range(0, 24):
+                        a.state.pos[k] = torch.tensor([5.0, 5.0]) + torch.rand(2, generator=g)
+        obs, rews, dones, infos = env.step(acts)
+        if t in KEEP:
+            pre = rec.pop("_pre")
+            for k in ("agent_pos", "agent_vel", "pkg_state", "goal_pos", "shaping_in"):
+                rec[k].append(pre[k])
+            rec["obs"].append(np.stack([t2n(o) for o in obs]))
+            rec["rew"].append(t2n(rews[0]))
+            rec["done"].append(t2n(dones))
+            rec["on_goal"].append(np.stack([t2n(p.on_goal) for p in pk]))
+            rec["dist"].append(np.stack([t2n(p.dist_to_goal) for p in pk]))
+            rec["shaping_out"].append(np.stack([t2n(p.global_shaping) for p in pk]))
+            rec["color"].append(np.stack([t2n(p.color) for p in pk]))
+        else:
+            rec.pop("_pre", None)
+    out = {k: np.stack(v) for k, v in rec.items()}
+    out["pkg_dims"] = np.array([[0.0, p.shape.length, p.shape.width] for p in pk], np.float64)
+    out["goal_radius"] = np.array([p.goal.shape.radius for p in pk], np.float64)
+    out["params"] = np.array([sc.shaping_factor], np.float64)
+    os.makedirs(os.path.join(HERE, "hooks"), exist_ok=True)
+    np.savez_compressed(os.path.join(HERE, "hooks", "transport.npz"), **out)
+    print("transport", {k: v.shape for k, v in out.items()}, "on_goal", int(out["on_goal"].sum()), "done", int(out["done"].sum()))
+
+
+if __name__ == "__main__":
+    navigation()
+    navigation(kw=dict(n_agents=3, shared_rew=False, observe_all_goals=True), tag="navigation_noshare")
+    navigation(kw=dict(n_agents=2, collisions=False), tag="navigation_nocoll")
+    transport()

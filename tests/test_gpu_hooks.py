@@ -1,0 +1,297 @@
+"""GPU: the fused scenario hooks (include/vmasb200.h vmasb200_gather_obs / vmasb200_navigation_reward /
+vmasb200_transport_reward).
+
+1. Through the C ABI on the golden inputs (tests/golden/hooks/*.npz, outputs of the unmodified reference): every output
+   bit-identical to the reference's (fp32 ops are single correctly rounded instructions in the reference's order; the
+   library is built with -fmad=false).
+2. Inside the reference's own Environment on the GPU (dropin.enable(env, hooks=True)): after every step the fused hooks
+   and the reference's torch hooks are evaluated on the SAME world state and scenario attributes; observations,
+   rewards, dones, infos and every attribute the hooks leave behind must agree (flags equal, floats within one ulp of
+   the norm: torch's CUDA vector_norm differs from torch CPU's by that), across a full reset and a partial reset_at, and
+   the fused path must really have run (counters)."""
+import ctypes as C
+import os
+import sys
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+REF = os.path.join(ROOT, "oracle", "_ref")
+
+
+def load(name):
+    return dict(np.load(os.path.join(HERE, "golden", "hooks", name + ".npz")))
+
+
+def soa(torch, x, pad=5):
+    """[N, k] numpy -> a strided CUDA view [N, k] of an SoA buffer [k][ld] (what the drop-in binds as entity state)."""
+    n, k = x.shape
+    buf = torch.zeros(k, n + pad, device="cuda")
+    buf[:, :n] = torch.from_numpy(np.ascontiguousarray(x.T)).cuda()
+    return buf[:, :n].t()
+
+
+@pytest.mark.parametrize("name", ["navigation", "navigation_noshare", "navigation_nocoll"])
+def test_navigation_c_abi_matches_reference_golden(name):
+    import torch
+
+    from vectorizedmultiagentsimulator_b200 import _lib, hooks as H
+
+    g = load(name)
+    T, A, n = g["pos"].shape[:3]
+    factor, final, pen, mcd, shared, max_range, all_goals = [float(v) for v in g["params"]]
+    L = _lib.lib()
+    stream = torch.cuda.current_stream().cuda_stream
+    for t in range(T):
+        pos = [soa(torch, g["pos"][t, a]) for a in range(A)]
+        vel = [soa(torch, g["vel"][t, a]) for a in range(A)]
+        goal = [torch.from_numpy(g["goal"][t, a]).cuda() for a in range(A)]
+        lidar = [soa(torch, g["lidar"][t, a]) for a in range(A)] if g["lidar"].shape[-1] else None
+        shaping = torch.from_numpy(g["shaping_in"][t]).cuda()
+        fout = torch.full((5 * A + 2, n), float("nan"), device="cuda")
+        bout = torch.full((A + 2, n), 7, dtype=torch.uint8, device="cuda")
+        flags = torch.full((4,), -1, dtype=torch.int32, device="cuda")
+        cn = H.CNavigation()
+        cn.n_agents, cn.shared_rew = A, int(shared)
+        cn.pos_shaping_factor, cn.final_reward, cn.agent_collision_penalty, cn.min_collision_distance = factor, final, pen, mcd
+        for a in range(A):
+            ag = cn.agent[a]
+            H._vec(ag.pos, pos[a]); H._vec(ag.goal_pos, goal[a])
+            ag.radius, ag.goal_radius = float(g["radius"][a]), float(g["goal_radius"][a])
+            ag.pos_shaping = shaping[a].data_ptr()
+            for j, fld in enumerate(("pos_shaping_out", "distance_to_goal", "pos_rew", "agent_collision_rew", "reward")):
+                setattr(ag, fld, fout[5 * a + j].data_ptr())
+            ag.on_goal = bout[a].data_ptr()
+            for b in range(a):
+                cn.collidable[a][b] = int(g["lidar"].shape[-1] > 0)
+        cn.pos_rew, cn.final_rew = fout[5 * A].data_ptr(), fout[5 * A + 1].data_ptr()
+        cn.all_goal_reached, cn.done, cn.pair_flags = bout[A].data_ptr(), bout[A + 1].data_ptr(), flags.data_ptr()
+        _lib.check(L.vmasb200_navigation_reward(C.byref(cn), n, stream), "vmasb200_navigation_reward")
+        fo, bo = fout.cpu().numpy(), bout.cpu().numpy().astype(bool)
+        for j, k in enumerate(("shaping_out", "dist", "pos_rew_agent", "coll_rew", "reward")):
+            assert np.array_equal(fo[j:5 * A:5], g[k][t]), f"{name} step {t}: {k}"
+        assert np.array_equal(fo[5 * A], g["pos_rew"][t]) and np.array_equal(fo[5 * A + 1], g["final_rew"][t])
+        assert np.array_equal(bo[:A], g["on_goal"][t]) and np.array_equal(bo[A], g["all_goal"][t])
+        assert np.array_equal(bo[A + 1], g["done"][t])
+        fl = flags.cpu().numpy().view(np.uint32)
+        for a in range(A):
+            for b in range(a):
+                q = a * (a - 1) // 2 + b
+                assert bool((fl[q >> 5] >> (q & 31)) & 1) == bool(g["flags"][t, a, b]), f"{name} step {t}: World.collides({a},{b})"
+        # observations of all agents in one launch
+        spec = []
+        for a in range(A):
+            parts = [(H.OBS_COPY, pos[a], None, 0.0), (H.OBS_COPY, vel[a], None, 0.0)]
+            for b in (range(A) if all_goals else [a]):
+                parts.append((H.OBS_SUB, pos[a], goal[b], 0.0))
+            if lidar is not None:
+                parts.append((H.OBS_CSUB, lidar[a], None, max_range))
+            spec.append(parts)
+        outs = H.ObsGather(torch, n, torch.device("cuda", 0)).run(spec)
+        for a in range(A):
+            assert np.array_equal(outs[a].cpu().numpy(), g["obs"][t, a]), f"{name} step {t}: obs of agent {a}"
+
+
+def test_transport_c_abi_matches_reference_golden():
+    import torch
+
+    from vectorizedmultiagentsimulator_b200 import _lib, hooks as H
+    from vectorizedmultiagentsimulator_b200.queries import make_pose
+    from vectorizedmultiagentsimulator_b200.worlddesc import BOX, SPHERE
+
+    g = load("transport")
+    T, P, n = g["pkg_state"].shape[:3]
+    A = g["agent_pos"].shape[1]
+    L = _lib.lib()
+    stream = torch.cuda.current_stream().cuda_stream
+    for t in range(T):
+        ct = H.CTransport()
+        ct.n_packages, ct.shaping_factor = P, float(g["params"][0])
+        for k, (r, gr) in enumerate(zip((0.75, 0.25, 0.25), (0.25, 0.75, 0.25))):
+            ct.color_off_goal[k], ct.color_on_goal[k] = r, gr
+        fout = torch.full((2 * P + 1, n), float("nan"), device="cuda")
+        bout = torch.full((P + 1, n), 7, dtype=torch.uint8, device="cuda")
+        colors = torch.full((P, n, 3), float("nan"), device="cuda")
+        shaping = torch.from_numpy(g["shaping_in"][t]).cuda()
+        keep, ppos, pvel, gpos = [], [], [], []
+        for k in range(P):
+            st = g["pkg_state"][t, k]
+            ppos.append(soa(torch, st[:, 0:2])); pvel.append(soa(torch, st[:, 2:4]))
+            rot = soa(torch, st[:, 4:5])
+            gpos.append(torch.from_numpy(g["goal_pos"][t, k]).cuda())
+            pk = ct.package[k]
+            pa, k1 = make_pose(BOX, 0.0, float(g["pkg_dims"][k, 1]), float(g["pkg_dims"][k, 2]), ppos[k], rot, torch)
+            pg, k2 = make_pose(SPHERE, float(g["goal_radius"][k]), 0.0, 0.0, gpos[k], None, torch)
+            keep += k1 + k2
+            pk.package, pk.goal = pa, pg
+            pk.global_shaping, pk.global_shaping_out, pk.dist_to_goal = shaping[k].data_ptr(), fout[2 * k].data_ptr(), fout[2 * k + 1].data_ptr()
+            pk.on_goal, pk.color = bout[k].data_ptr(), colors[k].data_ptr()
+        ct.rew, ct.done = fout[2 * P].data_ptr(), bout[P].data_ptr()
+        _lib.check(L.vmasb200_transport_reward(C.byref(ct), n, stream), "vmasb200_transport_reward")
+        fo, bo = fout.cpu().numpy(), bout.cpu().numpy().astype(bool)
+        assert np.array_equal(fo[0:2 * P:2], g["shaping_out"][t]) and np.array_equal(fo[1:2 * P:2], g["dist"][t]), f"step {t}"
+        assert np.array_equal(fo[2 * P], g["rew"][t]), f"step {t}: rew"
+        assert np.array_equal(bo[:P], g["on_goal"][t]) and np.array_equal(bo[P], g["done"][t]), f"step {t}: on_goal / done"
+        assert np.array_equal(colors.cpu().numpy(), g["color"][t]), f"step {t}: color"
+        apos = [soa(torch, g["agent_pos"][t, a]) for a in range(A)]
+        avel = [soa(torch, g["agent_vel"][t, a]) for a in range(A)]
+        og = bout.view(torch.bool)
+        spec = []
+        for a in range(A):
+            parts = [(H.OBS_COPY, apos[a], None, 0.0), (H.OBS_COPY, avel[a], None, 0.0)]
+            for k in range(P):
+                parts += [(H.OBS_SUB, ppos[k], gpos[k], 0.0), (H.OBS_SUB, ppos[k], apos[a], 0.0), (H.OBS_COPY, pvel[k], None, 0.0),
+                          (H.OBS_BOOL, og[k], None, 0.0)]
+            spec.append(parts)
+        outs = H.ObsGather(torch, n, torch.device("cuda", 0)).run(spec)
+        for a in range(A):
+            assert np.array_equal(outs[a].cpu().numpy(), g["obs"][t, a]), f"step {t}: obs of agent {a}"
+
+
+def test_gather_obs_rejects_bad_tables():
+    import torch
+
+    from vectorizedmultiagentsimulator_b200 import _lib, hooks as H
+
+    n = 40
+    x = torch.rand(n, 2, device="cuda")
+    L = _lib.lib()
+    segs = (H.CObsSeg * 2)()
+    outs, widths = (C.c_void_p * 1)(), (C.c_int32 * 1)()
+    out = torch.empty(n, 4, device="cuda")
+    outs[0], widths[0] = out.data_ptr(), 4
+    for s, col0 in zip(segs, (0, 1)):  # overlapping columns, column 3 uncovered
+        H._vec(s.a, x)
+        s.op, s.width, s.out, s.col0 = H.OBS_COPY, 2, 0, col0
+    assert L.vmasb200_gather_obs(segs, 2, outs, widths, 1, n, None) != 0
+    segs[1].col0 = 2
+    assert L.vmasb200_gather_obs(segs, 2, outs, widths, 1, n, None) == 0
+    torch.cuda.synchronize()
+    assert torch.equal(out, torch.cat([x, x], -1))
+    assert L.vmasb200_gather_obs(segs, 1, outs, widths, 1, n, None) != 0  # columns 2..3 uncovered
+
+
+# ------------------------------------------------------------------------------------------------ inside the reference
+def _vmas():
+    if not os.path.isdir(os.path.join(REF, "vmas")):
+        pytest.skip("oracle/_ref (the reference install) did not travel to this box")
+    for p in (REF, os.path.join(ROOT, "oracle", "gym_stub")):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    import vmas
+
+    return vmas
+
+
+def _leaves(x):
+    if isinstance(x, dict):
+        return [t for k in sorted(x) for t in _leaves(x[k])]
+    if isinstance(x, (list, tuple)):
+        return [t for v in x for t in _leaves(v)]
+    return [x]
+
+
+NAV_ATTRS = ("pos_shaping", "agent_collision_rew", "pos_rew", "on_goal", "distance_to_goal")
+PKG_ATTRS = ("global_shaping", "on_goal", "dist_to_goal", "color")
+
+
+def _snapshot(env, scenario):
+    sc = env.scenario
+    if scenario == "navigation":
+        snap = {(i, k): getattr(a, k).clone() for i, a in enumerate(env.world.agents) for k in NAV_ATTRS if hasattr(a, k)}
+        snap.update({k: getattr(sc, k).clone() for k in ("pos_rew", "final_rew", "all_goal_reached") if hasattr(sc, k)})
+    else:
+        snap = {(i, k): getattr(p, k).clone() for i, p in enumerate(sc.packages) for k in PKG_ATTRS
+                if hasattr(getattr(p, k, None), "clone")}
+        if hasattr(sc, "rew"):
+            snap["rew"] = sc.rew.clone()
+    return snap
+
+
+def _restore(env, scenario, snap):
+    sc = env.scenario
+    objs = env.world.agents if scenario == "navigation" else sc.packages
+    for key, v in snap.items():
+        if isinstance(key, tuple):
+            setattr(objs[key[0]], key[1], v.clone())
+        elif key in ("pos_rew", "final_rew"):
+            getattr(sc, key).copy_(v)  # the reference writes these in place
+        else:
+            setattr(sc, key, v.clone())
+
+
+@pytest.mark.parametrize("scenario,kw", [("navigation", dict(n_agents=4)), ("navigation", dict(n_agents=3, shared_rew=False, observe_all_goals=True)),
+                                         ("navigation", dict(n_agents=2, collisions=False)), ("transport", dict(n_agents=4)),
+                                         ("transport", dict(n_agents=3, n_packages=2))])
+def test_fused_hooks_equal_reference_hooks_on_the_same_state(scenario, kw):
+    import torch
+
+    from vectorizedmultiagentsimulator_b200 import dropin
+
+    vmas = _vmas()
+    n, steps = 200, 36
+    env = vmas.make_env(scenario, num_envs=n, device="cuda", seed=0, continuous_actions=True, **kw)
+    b = dropin.enable(env, hooks=True)
+    h = b.hooks
+    assert h is not None
+    sc = env.scenario
+    # torch's CUDA vector_norm of a 2-vector is not the fma form torch CPU (and the library, bit for bit: the golden
+    # tests above) computes: one ulp of the norm, times the shaping factor (transport: 100), is the float tolerance
+    # here; flags (done, on_goal) must be equal
+    atol = 1e-6 * max(1.0, float(getattr(sc, "shaping_factor", 1.0)))
+
+    def same(x, y):
+        return torch.equal(x, y) if x.dtype == torch.bool else torch.allclose(x, y, rtol=1e-5, atol=atol)
+
+    torch.manual_seed(3)
+    for t in range(steps):
+        if t == 12:
+            env.reset(seed=5)
+        if t == 24:
+            env.reset_at(7)
+        acts = [torch.rand(n, a.action_size, device="cuda") * 2 * a.u_range - a.u_range for a in env.agents]
+        if t % 6 == 5:  # stage goals reached / contacts in a few envs so that the thresholds matter
+            with torch.no_grad():
+                if scenario == "navigation":
+                    for k in range(0, 12):
+                        for a in env.world.agents[: 1 + k % len(env.world.agents)]:
+                            a.state.pos[k] = a.goal.state.pos[k] + 0.004 * (k % 3)
+                    a0, a1 = env.world.agents[0], env.world.agents[1]
+                    for k in range(12, 30):
+                        a1.state.pos[k] = a0.state.pos[k] + torch.tensor([0.19 + 0.001 * (k - 12), 0.0], device="cuda")
+                else:
+                    for p in sc.packages:
+                        for k in range(0, 30):
+                            p.state.pos[k] = p.goal.state.pos[k] + torch.tensor([0.01 * k, 0.0], device="cuda")
+            acts = [a * 0 for a in acts]
+        # Environment.step up to the hooks (environment.py:386-402)
+        for i, agent in enumerate(env.agents):
+            env._set_action(acts[i], agent)
+        for agent in env.world.agents:
+            sc.env_process_action(agent)
+        sc.pre_step(); env.world.step(); sc.post_step()
+        env.steps += 1
+        snap = _snapshot(env, scenario)
+        fused = env._get_from_scenario(get_observations=True, get_rewards=True, get_infos=True, get_dones=True)
+        left_f = _snapshot(env, scenario)
+        _restore(env, scenario, snap)
+        h.remove()
+        ref = env._get_from_scenario(get_observations=True, get_rewards=True, get_infos=True, get_dones=True)
+        left_r = _snapshot(env, scenario)
+        h.attach()
+        lf, lr = _leaves(fused), _leaves(ref)
+        assert len(lf) == len(lr)
+        for i, (x, y) in enumerate(zip(lf, lr)):
+            assert x.shape == y.shape and x.dtype == y.dtype, f"{scenario} step {t}: output {i} {x.shape} {x.dtype} vs {y.shape} {y.dtype}"
+            assert same(x, y), f"{scenario} step {t}: output {i} differs by {float((x.float() - y.float()).abs().max()):.3e}"
+        assert left_f.keys() == left_r.keys() and len(left_f) >= 4
+        for k in left_f:
+            assert left_f[k].dtype == left_r[k].dtype and same(left_f[k], left_r[k]), f"{scenario} step {t}: attribute {k}"
+    assert h.n_fused["reward"] == steps and h.n_fallback["reward"] == 0
+    assert h.n_fused["observation"] >= steps and h.n_fused["done"] == steps
+    dropin.disable(env)
+    assert "reward" not in sc.__dict__ and "observation" not in sc.__dict__

@@ -3,10 +3,11 @@ ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)
 sys.path[:0] = [os.path.join(ROOT, "oracle", "_ref"), os.path.join(ROOT, "oracle", "gym_stub"), ROOT]
 import torch, vmas
 from vectorizedmultiagentsimulator_b200 import dropin
+HOOKS = len(sys.argv) > 1 and sys.argv[1] == "hooks"
 for scenario, kw in (("navigation", dict(n_agents=4)), ("transport", dict(n_agents=4)), ("football", dict(ai_red_agents=False))):
     n = 32768
     env = vmas.make_env(scenario, num_envs=n, device="cuda", seed=0, continuous_actions=True, **kw)
-    dropin.enable(env)
+    dropin.enable(env, hooks=HOOKS)
     T = {}
     def wrap(obj, name, key):
         f = getattr(obj, name)
@@ -26,4 +27,4 @@ for scenario, kw in (("navigation", dict(n_agents=4)), ("transport", dict(n_agen
     torch.cuda.synchronize(); t0 = time.perf_counter()
     for i in range(K): env.step([a.clone() for a in acts[i % 4]])
     torch.cuda.synchronize(); tot = (time.perf_counter() - t0) / K * 1e3
-    print(scenario, "total %.3f ms" % tot, {k: round(v / K * 1e3, 3) for k, v in T.items()})
+    print("hooks" if HOOKS else "plain", scenario, "total %.3f ms" % tot, {k: round(v / K * 1e3, 3) for k, v in T.items()})

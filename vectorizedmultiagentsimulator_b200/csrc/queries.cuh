@@ -83,6 +83,18 @@ VB_DI float pair_distance(const QPose& a, const QPose& b, long long i) {
   return norm(p1 - p2) - kLMD;
 }
 
+// core.py:1909-1966
+VB_DI bool pair_overlap(const QPose& a, const QPose& b, long long i) {
+  const bool bs = (a.shape == VMASB200_BOX && b.shape == VMASB200_SPHERE) || (b.shape == VMASB200_BOX && a.shape == VMASB200_SPHERE);
+  if (bs) {  // core.py:1936-1964
+    const bool a_box = b.shape == VMASB200_SPHERE;
+    const QPose& box = a_box ? a : b;
+    const QPose& sph = a_box ? b : a;
+    return overlap_box_sphere(box, q_pos(box, i), q_rot(box, i), sph, q_pos(sph, i));
+  }
+  return pair_distance(a, b, i) < 0.f;  // core.py:1934
+}
+
 enum { QM_DISTANCE = 0, QM_OVERLAP = 1 };
 
 template <int MODE>
@@ -93,16 +105,7 @@ __global__ void __launch_bounds__(256) pair_query_kernel(const __grid_constant__
   if (MODE == QM_DISTANCE) {
     out_f[i] = pair_distance(a, b, i);
   } else {
-    const bool bs = (a.shape == VMASB200_BOX && b.shape == VMASB200_SPHERE) || (b.shape == VMASB200_BOX && a.shape == VMASB200_SPHERE);
-    bool r;
-    if (bs) {  // core.py:1936-1964
-      const bool a_box = b.shape == VMASB200_SPHERE;
-      const QPose& box = a_box ? a : b;
-      const QPose& sph = a_box ? b : a;
-      r = overlap_box_sphere(box, q_pos(box, i), q_rot(box, i), sph, q_pos(sph, i));
-    } else {
-      r = pair_distance(a, b, i) < 0.f;  // core.py:1934
-    }
+    const bool r = pair_overlap(a, b, i);
     out_b[i] = r ? 1 : 0;
   }
 }

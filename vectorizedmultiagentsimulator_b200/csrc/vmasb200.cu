@@ -10,6 +10,7 @@
 
 #include "kernels.cuh"
 #include "queries.cuh"
+#include "hooks.cuh"
 #include "plan.h"
 
 namespace vb {
@@ -469,6 +470,119 @@ int vmasb200_set_action(const float* action, int64_t stride_env, int64_t stride_
   const long long total = (long long)n * action_size;
   set_action_kernel<<<(unsigned)((total + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
       action, stride_env, stride_k, action_size, ap, clamp, u_out, flags, n);
+  VB_CUDA(cudaGetLastError());
+  return VMASB200_OK;
+}
+
+// ---------------------------------------------------------------------------------------------- scenario hooks (8 f1)
+static DVec to_dvec(const vmasb200_vec& v) { DVec d; d.p = v.p; d.se = v.stride_env; d.sk = v.stride_k; return d; }
+
+int vmasb200_gather_obs(const vmasb200_obs_seg* segs, int32_t n_segs, float* const* outs, const int32_t* out_widths,
+                        int32_t n_outs, int64_t n, void* stream) {
+  if (!segs || !outs || !out_widths || n < 0 || n_segs < 1 || n_segs > VMASB200_OBS_MAX_SEGS || n_outs < 1 ||
+      n_outs > VMASB200_OBS_MAX_OUTS) {
+    set_error("gather_obs: bad argument (1 <= n_segs <= 128, 1 <= n_outs <= 32)"); return VMASB200_ERR_INVALID;
+  }
+  // by value in the kernel's parameter space (grid constant): pointers change every step, nothing is uploaded
+  static thread_local ObsTable tb;
+  tb.n_segs = n_segs; tb.n_outs = n_outs;
+  int max_w = 0;
+  std::vector<std::vector<uint8_t>> cover((size_t)n_outs);
+  for (int o = 0; o < n_outs; ++o) {
+    if (!outs[o] || out_widths[o] < 1 || out_widths[o] > VMASB200_OBS_MAX_WIDTH) {
+      set_error("gather_obs: out pointer NULL or width outside 1..352"); return VMASB200_ERR_INVALID;
+    }
+    tb.outs[o] = outs[o]; tb.width[o] = out_widths[o];
+    max_w = std::max(max_w, (int)out_widths[o]);
+    cover[o].assign((size_t)out_widths[o], 0);
+  }
+  for (int s = 0; s < n_segs; ++s) {
+    const vmasb200_obs_seg& g = segs[s];
+    if (g.out < 0 || g.out >= n_outs || g.width < 1 || g.col0 < 0 || g.col0 + g.width > out_widths[g.out] || !g.a.p ||
+        g.op < VMASB200_OBS_COPY || g.op > VMASB200_OBS_BOOL || (g.op == VMASB200_OBS_SUB && !g.b.p)) {
+      set_error("gather_obs: bad segment (out, columns, operands or op)"); return VMASB200_ERR_INVALID;
+    }
+    for (int k = 0; k < g.width; ++k)
+      if (cover[g.out][(size_t)(g.col0 + k)]++) { set_error("gather_obs: a column is written by two segments"); return VMASB200_ERR_INVALID; }
+    ObsSeg& d = tb.seg[s];
+    d.a = to_dvec(g.a); d.b = to_dvec(g.b); d.op = g.op; d.c = g.c; d.width = g.width; d.out = g.out; d.col0 = g.col0;
+  }
+  for (int o = 0; o < n_outs; ++o)
+    for (uint8_t c : cover[o])
+      if (!c) { set_error("gather_obs: a column of an observation is not covered by any segment"); return VMASB200_ERR_INVALID; }
+  if (n == 0) return VMASB200_OK;
+  const dim3 grid((unsigned)((n + kObsTile - 1) / kObsTile), (unsigned)n_outs);
+  gather_obs_kernel<<<grid, 256, (size_t)max_w * (kObsTile + 1) * sizeof(float), static_cast<cudaStream_t>(stream)>>>(tb, n);
+  VB_CUDA(cudaGetLastError());
+  return VMASB200_OK;
+}
+
+int vmasb200_navigation_reward(const vmasb200_navigation* nv, int64_t n, void* stream) {
+  if (!nv || n < 0 || nv->n_agents < 1 || nv->n_agents > VMASB200_NAV_MAX_AGENTS || !nv->pos_rew || !nv->final_rew ||
+      !nv->all_goal_reached || !nv->pair_flags) {
+    set_error("navigation_reward: bad argument (1 <= n_agents <= 16, output pointers)"); return VMASB200_ERR_INVALID;
+  }
+  static thread_local NavParams np;
+  np.n_agents = nv->n_agents; np.shared_rew = nv->shared_rew;
+  np.factor = (float)nv->pos_shaping_factor; np.final_reward = (float)nv->final_reward;
+  np.penalty = (float)nv->agent_collision_penalty; np.min_coll_dist = (float)nv->min_collision_distance;
+  bool any_pair = false;
+  for (int a = 0; a < nv->n_agents; ++a) {
+    const vmasb200_nav_agent& g = nv->agent[a];
+    if (!g.pos.p || !g.goal_pos.p || !g.pos_shaping || !g.pos_shaping_out || !g.distance_to_goal || !g.on_goal ||
+        !g.pos_rew || !g.agent_collision_rew || !g.reward) {
+      set_error("navigation_reward: an agent has a NULL tensor"); return VMASB200_ERR_INVALID;
+    }
+    NavAgent& d = np.ag[a];
+    d.pos = to_dvec(g.pos); d.goal = to_dvec(g.goal_pos);
+    d.radius = (float)g.radius; d.goal_radius = (float)g.goal_radius;
+    d.shaping_in = g.pos_shaping; d.shaping_out = g.pos_shaping_out; d.dist = g.distance_to_goal; d.on_goal = g.on_goal;
+    d.pos_rew = g.pos_rew; d.coll_rew = g.agent_collision_rew; d.reward = g.reward;
+    for (int b = 0; b < a; ++b) {
+      np.coll[a][b] = nv->collidable[a][b] ? 1 : 0;
+      any_pair = any_pair || np.coll[a][b];
+      np.rc_sum[a][b] = (float)(g.radius + nv->agent[b].radius);  // circumscribed radius of a sphere = its radius
+    }
+  }
+  np.pos_rew = nv->pos_rew; np.final_rew = nv->final_rew; np.all_goal = nv->all_goal_reached; np.done = nv->done;
+  np.flags = nv->pair_flags;
+  if (n == 0) return VMASB200_OK;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const unsigned grid = (unsigned)((n + 255) / 256);
+  VB_CUDA(cudaMemsetAsync(nv->pair_flags, 0, 4 * sizeof(uint32_t), st));
+  const int A = nv->n_agents;
+  if (any_pair) {
+    if (A <= 4) nav_flags_kernel<4><<<grid, 256, 0, st>>>(np, n);
+    else if (A <= 8) nav_flags_kernel<8><<<grid, 256, 0, st>>>(np, n);
+    else nav_flags_kernel<16><<<grid, 256, 0, st>>>(np, n);
+  }
+  if (A <= 4) nav_reward_kernel<4><<<grid, 256, 0, st>>>(np, n);
+  else if (A <= 8) nav_reward_kernel<8><<<grid, 256, 0, st>>>(np, n);
+  else nav_reward_kernel<16><<<grid, 256, 0, st>>>(np, n);
+  VB_CUDA(cudaGetLastError());
+  return VMASB200_OK;
+}
+
+int vmasb200_transport_reward(const vmasb200_transport* tr, int64_t n, void* stream) {
+  if (!tr || n < 0 || tr->n_packages < 1 || tr->n_packages > VMASB200_TRANSPORT_MAX_PACKAGES || !tr->rew) {
+    set_error("transport_reward: bad argument (1 <= n_packages <= 8, rew)"); return VMASB200_ERR_INVALID;
+  }
+  static thread_local TrParams tp;
+  tp.n_packages = tr->n_packages; tp.factor = (float)tr->shaping_factor;
+  for (int k = 0; k < 3; ++k) { tp.off[k] = tr->color_off_goal[k]; tp.on[k] = tr->color_on_goal[k]; }
+  for (int k = 0; k < tr->n_packages; ++k) {
+    const vmasb200_transport_package& g = tr->package[k];
+    int rc;
+    if ((rc = to_qpose(&g.package, &tp.pk[k].pkg, "transport_reward")) || (rc = to_qpose(&g.goal, &tp.pk[k].goal, "transport_reward"))) return rc;
+    if (!g.global_shaping || !g.global_shaping_out || !g.dist_to_goal || !g.on_goal) {
+      set_error("transport_reward: a package has a NULL tensor"); return VMASB200_ERR_INVALID;
+    }
+    tp.pk[k].shaping_in = g.global_shaping; tp.pk[k].shaping_out = g.global_shaping_out; tp.pk[k].dist = g.dist_to_goal;
+    tp.pk[k].on_goal = g.on_goal; tp.pk[k].color = g.color;
+  }
+  tp.rew = tr->rew; tp.done = tr->done;
+  if (n == 0) return VMASB200_OK;
+  transport_reward_kernel<<<(unsigned)((n + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(tp, n);
   VB_CUDA(cudaGetLastError());
   return VMASB200_OK;
 }

@@ -31,7 +31,7 @@ from typing import Dict, List, Optional
 
 import numpy as np
 
-from . import _lib, queries
+from . import _lib, hooks as _hooks, queries
 from .plan import StepPlan
 from .worlddesc import CStepIO, UnsupportedWorld, WorldDesc  # noqa: F401
 
@@ -394,13 +394,15 @@ def _joints_in_order(world, ents):
     return out
 
 
-def enable(world_or_env, exact: bool = False, static_io: bool = False) -> WorldBinding:
+def enable(world_or_env, exact: bool = False, static_io: bool = False, hooks: bool = False) -> WorldBinding:
     """Routes ``world.step`` / ``world.cast_rays`` / its Lidars' ``measure`` / the distance queries of ONE world through
     libvmasb200.  ``exact=True`` takes the per-substep exact path instead of the verified speculative single launch.
     ``static_io=True`` (opt-in): the step works IN PLACE on persistent buffers instead of binding fresh output tensors
     every step - no allocations and no new views per step, state tensors keep their addresses (what CUDA-graph capture
     of user code around the step needs) - at the price that a state tensor a caller kept from an earlier step changes
-    with the world instead of staying a snapshot, unlike the reference (core.py:2866-2907 rebinds fresh tensors)."""
+    with the world instead of staying a snapshot, unlike the reference (core.py:2866-2907 rebinds fresh tensors).
+    ``hooks=True`` (opt-in, needs an Environment): the scenario's reward / observation / done take the fused launches of
+    ``hooks.py`` when the scenario has them (navigation, transport); ``binding.hooks`` is None otherwise."""
     world = getattr(world_or_env, "world", world_or_env)
     if getattr(world, "_vmasb200", None) is not None:
         return world._vmasb200
@@ -439,6 +441,7 @@ def enable(world_or_env, exact: bool = False, static_io: bool = False) -> WorldB
         env = world_or_env
         b._env, b.orig_set_action = env, env._set_action
         env._set_action = types.MethodType(lambda self, action, agent: b.set_action(self, action, agent), env)
+    b.hooks = _hooks.install(world_or_env, b) if (hooks and b._env is not None) else None
     return b
 
 
@@ -455,4 +458,7 @@ def disable(world_or_env) -> None:
             del sensor.__dict__["measure"]
     if getattr(b, "_env", None) is not None:
         b._env.__dict__.pop("_set_action", None)
+    if getattr(b, "hooks", None) is not None:
+        b.hooks.remove()
+        b.hooks = None
     world._vmasb200 = None

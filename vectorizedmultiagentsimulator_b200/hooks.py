@@ -1,0 +1,406 @@
+"""Fused scenario hooks: what ``Environment._get_from_scenario`` (environment.py:253-308) asks of a
+scenario after every ``World.step`` - ``reward`` / ``observation`` / ``done`` / ``info`` - as one or two launches per
+step (include/vmasb200.h: vmasb200_gather_obs, vmasb200_navigation_reward, vmasb200_transport_reward) instead of tens
+to hundreds of small torch ops with host synchronisations (``World.collides``, boolean-mask indexing).
+
+Opt-in and keyed by scenario (``dropin.enable(env, hooks=True)``): the hook API stays the reference's - the same bound
+methods are patched on ONE scenario instance, they return tensors of the same shape / dtype, and every attribute the
+reference's hooks leave behind (``agent.pos_shaping``, ``agent.on_goal``, ``scenario.pos_rew``, ``package.on_goal``,
+``package.color`` ...) is left behind here too, written in place where the reference writes in place and rebound where
+it rebinds.  A configuration a fused hook does not cover (autograd in play, shapes it does not know, non-CUDA tensors)
+takes the saved original method: the reference's torch code is the fallback of the HOOKS, never of the physics.
+
+Scenarios: ``navigation`` (navigation.py:199-280) and ``transport`` (transport.py:130-193)."""
+from __future__ import annotations
+
+import ctypes as C
+from typing import List, Optional
+
+from . import _lib
+from .queries import CPose, make_pose, shape_of
+from .worlddesc import SPHERE
+
+OBS_COPY, OBS_SUB, OBS_CSUB, OBS_BOOL = 0, 1, 2, 3
+NAV_MAX_AGENTS, TRANSPORT_MAX_PACKAGES, OBS_MAX_SEGS, OBS_MAX_OUTS, OBS_MAX_WIDTH = 16, 8, 128, 32, 352
+
+
+class CVec(C.Structure):
+    _fields_ = [("p", C.c_void_p), ("stride_env", C.c_int64), ("stride_k", C.c_int64)]
+
+
+class CObsSeg(C.Structure):
+    _fields_ = [("a", CVec), ("b", CVec), ("op", C.c_int32), ("c", C.c_float), ("width", C.c_int32), ("out", C.c_int32),
+                ("col0", C.c_int32), ("reserved", C.c_int32)]
+
+
+class CNavAgent(C.Structure):
+    _fields_ = [("pos", CVec), ("goal_pos", CVec), ("radius", C.c_double), ("goal_radius", C.c_double),
+                ("pos_shaping", C.c_void_p), ("pos_shaping_out", C.c_void_p), ("distance_to_goal", C.c_void_p),
+                ("on_goal", C.c_void_p), ("pos_rew", C.c_void_p), ("agent_collision_rew", C.c_void_p),
+                ("reward", C.c_void_p)]
+
+
+class CNavigation(C.Structure):
+    _fields_ = [("n_agents", C.c_int32), ("shared_rew", C.c_int32), ("pos_shaping_factor", C.c_double),
+                ("final_reward", C.c_double), ("agent_collision_penalty", C.c_double),
+                ("min_collision_distance", C.c_double), ("agent", CNavAgent * NAV_MAX_AGENTS),
+                ("collidable", (C.c_uint8 * NAV_MAX_AGENTS) * NAV_MAX_AGENTS), ("pos_rew", C.c_void_p),
+                ("final_rew", C.c_void_p), ("all_goal_reached", C.c_void_p), ("done", C.c_void_p),
+                ("pair_flags", C.c_void_p)]
+
+
+class CTransportPackage(C.Structure):
+    _fields_ = [("package", CPose), ("goal", CPose), ("global_shaping", C.c_void_p), ("global_shaping_out", C.c_void_p),
+                ("dist_to_goal", C.c_void_p), ("on_goal", C.c_void_p), ("color", C.c_void_p)]
+
+
+class CTransport(C.Structure):
+    _fields_ = [("n_packages", C.c_int32), ("shaping_factor", C.c_double), ("color_off_goal", C.c_float * 3),
+                ("color_on_goal", C.c_float * 3), ("package", CTransportPackage * TRANSPORT_MAX_PACKAGES),
+                ("rew", C.c_void_p), ("done", C.c_void_p)]
+
+
+def _vec(v: CVec, t):
+    v.p, v.stride_env = t.data_ptr(), t.stride(0)
+    v.stride_k = t.stride(1) if t.dim() > 1 else 0
+
+
+class ObsGather:
+    """torch.cat([...], dim=-1) of every agent in one launch.  ``spec`` = per agent a list of (op, a, b, c) with a / b
+    tensors [N, w] (or [N] -> one column)."""
+
+    def __init__(self, torch, n: int, device):
+        self.torch, self.n, self.device = torch, n, device
+        self.segs = (CObsSeg * OBS_MAX_SEGS)()
+        self.outs = (C.c_void_p * OBS_MAX_OUTS)()
+        self.widths = (C.c_int32 * OBS_MAX_OUTS)()
+
+    @staticmethod
+    def usable(torch, t, boolean=False) -> bool:
+        return (torch.is_tensor(t) and t.is_cuda and t.dim() in (1, 2) and
+                (t.dtype in (torch.bool, torch.uint8) if boolean else t.dtype == torch.float32) and
+                not (torch.is_grad_enabled() and t.requires_grad))
+
+    def run(self, spec) -> Optional[List]:
+        torch, n = self.torch, self.n
+        if len(spec) > OBS_MAX_OUTS:
+            return None
+        s, outs = 0, []
+        for o, parts in enumerate(spec):
+            col = 0
+            for op, a, b, c in parts:
+                if s >= OBS_MAX_SEGS or not self.usable(torch, a, op == OBS_BOOL) or a.shape[0] != n:
+                    return None
+                w = a.shape[1] if a.dim() == 2 else 1
+                g = self.segs[s]
+                _vec(g.a, a)
+                if op == OBS_SUB:
+                    if not self.usable(torch, b) or tuple(b.shape) != tuple(a.shape):
+                        return None
+                    _vec(g.b, b)
+                else:
+                    g.b.p = None
+                g.op, g.c, g.width, g.out, g.col0 = op, float(c), w, o, col
+                col += w
+                s += 1
+            if not 1 <= col <= OBS_MAX_WIDTH:
+                return None
+            out = torch.empty(n, col, device=self.device)
+            outs.append(out)
+            self.outs[o], self.widths[o] = out.data_ptr(), col
+        _lib.check(_lib.lib().vmasb200_gather_obs(self.segs, s, self.outs, self.widths, len(spec), n,
+                                                  torch.cuda.current_stream(self.device).cuda_stream), "vmasb200_gather_obs")
+        return outs
+
+
+def scenario_file(scenario) -> str:
+    """'navigation' for a Scenario defined in .../scenarios/navigation.py.  The reference loads scenario modules from
+    their file path under an EMPTY module name (vmas/scenarios/__init__.py), so the class's code object is asked."""
+    import os
+
+    code = getattr(getattr(type(scenario), "reward", None), "__code__", None)
+    return os.path.splitext(os.path.basename(code.co_filename))[0] if code is not None else ""
+
+
+class ScenarioHooks:
+    """Base: patches reward / observation / done of one scenario instance; ``remove`` restores them."""
+
+    NAMES = ("reward", "observation", "done")
+
+    def __init__(self, env, binding):
+        self.env, self.b = env, binding
+        self.torch, self.scenario, self.world = binding.torch, env.scenario, binding.world
+        self.n, self.device = binding.n, binding.device
+        self.gather = ObsGather(self.torch, self.n, self.device)
+        self.n_fused = {"reward": 0, "observation": 0, "done": 0}
+        self.n_fallback = {"reward": 0, "observation": 0, "done": 0}
+        self._obs = None
+        self._obs_key = None
+        self._done = None
+        self._done_key = None
+        self._rew_ok = False
+        self.orig = {k: getattr(self.scenario, k) for k in self.NAMES}
+        self.attach()
+
+    def attach(self):
+        sc = self.scenario
+        sc.reward = lambda agent: self.reward(agent)
+        sc.observation = lambda agent: self.observation(agent)
+        sc.done = lambda: self.done()
+
+    def remove(self):
+        for k in self.NAMES:
+            self.scenario.__dict__.pop(k, None)
+
+    def state_key(self):
+        """Changes whenever the world's state may have: a step, an in-place write through a state view (version
+        counter of the SoA buffers), a rebound state tensor, a reset (binding.dirty)."""
+        b = self.b
+        if b.dirty or b.plan is None:
+            return None
+        for e, views in b._dyn_views:
+            st = e.state
+            if st._pos is not views[0] or st._vel is not views[1] or st._rot is not views[2] or st._ang_vel is not views[3]:
+                return None
+        return (b.n_steps, id(b.dyn), b.dyn._version) + tuple((id(t), t._version) for t in self.extra_state())
+
+    def extra_state(self):
+        return ()
+
+    def _f32_vec(self, t, k=None) -> bool:
+        torch = self.torch
+        return (torch.is_tensor(t) and t.is_cuda and t.dtype == torch.float32 and t.shape[0] == self.n and
+                (k is None or (t.dim() == 2 and t.shape[1] == k)) and not (torch.is_grad_enabled() and t.requires_grad))
+
+    def _flat(self, t) -> bool:
+        return self._f32_vec(t) and t.dim() == 1 and t.is_contiguous()
+
+    # -- observation / done share the cache discipline
+    def observation(self, agent):
+        agents = self.world.agents
+        key = self.state_key()
+        if agent is agents[0] or self._obs is None or key is None or key != self._obs_key:
+            spec = self.obs_spec() if key is not None else None
+            self._obs = self.gather.run(spec) if spec is not None else None
+            self._obs_key = key
+            if self._obs is not None:
+                self.n_fused["observation"] += 1
+        if self._obs is None:
+            self.n_fallback["observation"] += 1
+            return self.orig["observation"](agent)
+        return self._obs[self._agent_index(agent)]
+
+    def _agent_index(self, agent) -> int:
+        for i, a in enumerate(self.world.agents):
+            if a is agent:
+                return i
+        raise ValueError("agent is not in the world")
+
+    def done(self):
+        key = self.state_key()
+        if self._done is not None and key is not None and key == self._done_key:
+            self.n_fused["done"] += 1
+            return self._done
+        self.n_fallback["done"] += 1
+        return self.orig["done"]()
+
+
+class NavigationHooks(ScenarioHooks):
+    """navigation.py:199-280.  ``reward`` for the first agent launches the whole computation (as the reference's
+    ``is_first`` branch does); the other agents read what it left."""
+
+    @staticmethod
+    def matches(scenario) -> bool:
+        return (scenario_file(scenario) == "navigation" and
+                all(hasattr(scenario, k) for k in ("pos_shaping_factor", "final_reward", "agent_collision_penalty",
+                                                   "min_collision_distance", "shared_rew", "pos_rew", "final_rew")))
+
+    def __init__(self, env, binding):
+        super().__init__(env, binding)
+        self.cn = CNavigation()
+        self.flags = self.torch.zeros(4, dtype=self.torch.int32, device=self.device)
+        self._rewards = {}
+
+    def extra_state(self):
+        return tuple(a.goal.state.pos for a in self.world.agents)
+
+    def _static_collides(self, a, b) -> bool:
+        """World.collides without its batch-wide distance test (core.py:2788-2795)."""
+        w = self.world
+        if (not a.collides(b)) or (not b.collides(a)) or a is b:
+            return False
+        if not a.movable and not a.rotatable and not b.movable and not b.rotatable:
+            return False
+        return {a.shape.__class__, b.shape.__class__} in w._collidable_pairs
+
+    def _reward_usable(self) -> bool:
+        sc, agents = self.scenario, self.world.agents
+        if not 1 <= len(agents) <= NAV_MAX_AGENTS or not self._flat(sc.pos_rew) or not self._flat(sc.final_rew):
+            return False
+        for a in agents:
+            sh, gsh = shape_of(a), shape_of(a.goal)
+            if sh is None or sh[0] != SPHERE or gsh is None or gsh[0] != SPHERE:
+                return False
+            if not (self._f32_vec(a.state.pos, 2) and self._f32_vec(a.goal.state.pos, 2) and
+                    self._flat(getattr(a, "pos_shaping", None)) and self._flat(getattr(a, "agent_collision_rew", None))):
+                return False
+        return True
+
+    def reward(self, agent):
+        sc, agents, torch = self.scenario, self.world.agents, self.torch
+        if agent is not agents[0]:
+            if self._rew_ok:
+                return self._rewards[id(agent)]
+            return self.orig["reward"](agent)
+        self._rew_ok = self._reward_usable()
+        if not self._rew_ok:
+            self.n_fallback["reward"] += 1
+            self._done = None
+            return self.orig["reward"](agent)
+        n, A, cn = self.n, len(agents), self.cn
+        fbuf = torch.empty(4 * A, n, device=self.device)          # per agent: pos_shaping, distance, pos_rew, reward
+        bbuf = torch.empty(A + 2, n, dtype=torch.uint8, device=self.device)  # per agent on_goal; all_goal_reached; done
+        cn.n_agents, cn.shared_rew = A, int(bool(sc.shared_rew))
+        cn.pos_shaping_factor, cn.final_reward = float(sc.pos_shaping_factor), float(sc.final_reward)
+        cn.agent_collision_penalty, cn.min_collision_distance = float(sc.agent_collision_penalty), float(sc.min_collision_distance)
+        fp, bp, row = fbuf.data_ptr(), bbuf.data_ptr(), 4 * n
+        for i, a in enumerate(agents):
+            g = cn.agent[i]
+            _vec(g.pos, a.state.pos)
+            _vec(g.goal_pos, a.goal.state.pos)
+            g.radius, g.goal_radius = float(a.shape.radius), float(a.goal.shape.radius)
+            g.pos_shaping = a.pos_shaping.data_ptr()
+            g.pos_shaping_out = fp + (4 * i) * row
+            g.distance_to_goal = fp + (4 * i + 1) * row
+            g.pos_rew = fp + (4 * i + 2) * row
+            g.reward = fp + (4 * i + 3) * row
+            g.on_goal = bp + i * n
+            g.agent_collision_rew = a.agent_collision_rew.data_ptr()  # written in place (navigation.py:209, 222-228)
+            for j in range(i):
+                cn.collidable[i][j] = int(self._static_collides(a, agents[j]))
+        cn.pos_rew, cn.final_rew = sc.pos_rew.data_ptr(), sc.final_rew.data_ptr()  # in place (navigation.py:203-204)
+        cn.all_goal_reached, cn.done = bp + A * n, bp + (A + 1) * n
+        cn.pair_flags = self.flags.data_ptr()
+        _lib.check(_lib.lib().vmasb200_navigation_reward(C.byref(cn), n, torch.cuda.current_stream(self.device).cuda_stream),
+                   "vmasb200_navigation_reward")
+        bools = bbuf.view(torch.bool)
+        for i, a in enumerate(agents):
+            a.pos_shaping, a.distance_to_goal, a.pos_rew = fbuf[4 * i], fbuf[4 * i + 1], fbuf[4 * i + 2]
+            a.on_goal = bools[i]
+            self._rewards[id(a)] = fbuf[4 * i + 3]
+        sc.all_goal_reached = bools[A]
+        self._done, self._done_key = bools[A + 1], self.state_key()
+        self.n_fused["reward"] += 1
+        return self._rewards[id(agent)]
+
+    def obs_spec(self):
+        sc, agents = self.scenario, self.world.agents
+        spec = []
+        for a in agents:
+            parts = [(OBS_COPY, a.state.pos, None, 0.0), (OBS_COPY, a.state.vel, None, 0.0)]
+            for g in (agents if sc.observe_all_goals else [a]):
+                parts.append((OBS_SUB, a.state.pos, g.goal.state.pos, 0.0))
+            if sc.collisions:
+                s0 = a.sensors[0]
+                parts.append((OBS_CSUB, s0.measure(), None, float(s0._max_range)))
+            spec.append(parts)
+        return spec
+
+
+class TransportHooks(ScenarioHooks):
+    """transport.py:130-193."""
+
+    @staticmethod
+    def matches(scenario) -> bool:
+        return (scenario_file(scenario) == "transport" and
+                all(hasattr(scenario, k) for k in ("packages", "shaping_factor")))
+
+    def __init__(self, env, binding):
+        super().__init__(env, binding)
+        self.ct = CTransport()
+        color = getattr(type(self.scenario).reward, "__globals__", {}).get("Color")  # vmas.simulator.utils.Color
+        red = color.RED.value if color is not None else (0.75, 0.25, 0.25)
+        green = color.GREEN.value if color is not None else (0.25, 0.75, 0.25)
+        for k in range(3):
+            self.ct.color_off_goal[k], self.ct.color_on_goal[k] = float(red[k]), float(green[k])
+
+    def extra_state(self):
+        out = []
+        for p in self.scenario.packages:
+            out += [p.goal.state.pos, p.on_goal]
+        return tuple(out)
+
+    def _reward_usable(self) -> bool:
+        pk = self.scenario.packages
+        if not 1 <= len(pk) <= TRANSPORT_MAX_PACKAGES:
+            return False
+        for p in pk:
+            if shape_of(p) is None or shape_of(p.goal) is None:
+                return False
+            for e in (p, p.goal):
+                if not self._f32_vec(e.state.pos, 2) or (shape_of(e)[0] != SPHERE and not self._f32_vec(e.state.rot)):
+                    return False
+            if not self._flat(getattr(p, "global_shaping", None)):
+                return False
+        return True
+
+    def reward(self, agent):
+        sc, torch = self.scenario, self.torch
+        if agent is not self.world.agents[0]:
+            return sc.rew if self._rew_ok else self.orig["reward"](agent)
+        self._rew_ok = self._reward_usable()
+        if not self._rew_ok:
+            self.n_fallback["reward"] += 1
+            self._done = None
+            return self.orig["reward"](agent)
+        n, ct, pk = self.n, self.ct, sc.packages
+        P = len(pk)
+        fbuf = torch.empty(2 * P + 1, n, device=self.device)   # per package: global_shaping, dist_to_goal; rew
+        bbuf = torch.empty(P + 1, n, dtype=torch.uint8, device=self.device)
+        colors = [torch.empty(n, 3, device=self.device) for _ in pk]
+        ct.n_packages, ct.shaping_factor = P, float(sc.shaping_factor)
+        keep = []
+        fp, bp, row = fbuf.data_ptr(), bbuf.data_ptr(), 4 * n
+        for k, p in enumerate(pk):
+            g = ct.package[k]
+            pa, ka = make_pose(*shape_of(p), p.state.pos, p.state.rot, torch)
+            pg, kg = make_pose(*shape_of(p.goal), p.goal.state.pos, p.goal.state.rot, torch)
+            keep += ka + kg
+            g.package, g.goal = pa, pg
+            g.global_shaping = p.global_shaping.data_ptr()
+            g.global_shaping_out, g.dist_to_goal = fp + (2 * k) * row, fp + (2 * k + 1) * row
+            g.on_goal, g.color = bp + k * n, colors[k].data_ptr()
+        ct.rew, ct.done = fp + (2 * P) * row, bp + P * n
+        _lib.check(_lib.lib().vmasb200_transport_reward(C.byref(ct), n, torch.cuda.current_stream(self.device).cuda_stream),
+                   "vmasb200_transport_reward")
+        bools = bbuf.view(torch.bool)
+        for k, p in enumerate(pk):
+            p.global_shaping, p.dist_to_goal, p.on_goal, p.color = fbuf[2 * k], fbuf[2 * k + 1], bools[k], colors[k]
+        sc.rew = fbuf[2 * P]
+        self._done, self._done_key = bools[P], self.state_key()
+        self.n_fused["reward"] += 1
+        return sc.rew
+
+    def obs_spec(self):
+        spec = []
+        for a in self.world.agents:
+            parts = [(OBS_COPY, a.state.pos, None, 0.0), (OBS_COPY, a.state.vel, None, 0.0)]
+            for p in self.scenario.packages:
+                parts += [(OBS_SUB, p.state.pos, p.goal.state.pos, 0.0), (OBS_SUB, p.state.pos, a.state.pos, 0.0),
+                          (OBS_COPY, p.state.vel, None, 0.0), (OBS_BOOL, p.on_goal, None, 0.0)]
+            spec.append(parts)
+        return spec
+
+
+REGISTRY = (NavigationHooks, TransportHooks)
+
+
+def install(env, binding) -> Optional[ScenarioHooks]:
+    """Fused hooks for ``env.scenario`` when its scenario has them, else None (the scenario keeps its own)."""
+    sc = getattr(env, "scenario", None)
+    if sc is None:
+        return None
+    for cls in REGISTRY:
+        if cls.matches(sc):
+            return cls(env, binding)
+    return None
