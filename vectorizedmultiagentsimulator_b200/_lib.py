@@ -81,3 +81,14 @@ def check(rc: int, what: str):
     if rc != 0:
         msg = lib().vmasb200_last_error()
         raise VmasB200Error(f"{what} failed ({rc}): {msg.decode() if msg else ''}")
+
+
+def raw_stream(torch, device) -> int:
+    """cudaStream_t of torch's CURRENT stream on `device` (the stream every launch of this package goes to).
+    torch._C._cuda_getCurrentRawStream is the cheap accessor (what torch's own Triton launcher uses); the public
+    torch.cuda.current_stream(device).cuda_stream costs ~10 us per call, several times per step."""
+    idx = device.index
+    if idx is None:
+        idx = torch.cuda.current_device()
+    get = getattr(torch._C, "_cuda_getCurrentRawStream", None)
+    return get(idx) if get is not None else torch.cuda.current_stream(device).cuda_stream

@@ -119,11 +119,12 @@ class WorldBinding:
         io.n_envs, io.ld, io.exact = n, ld, int(self.exact)
 
     def _views_of(self, dyn):
-        n = self.n
+        # [n, k] views with strides (1, ld) of rows o .. o + k - 1 (= dyn[o:o + k, :n].t(), one call instead of three)
+        n, ld = self.n, self.ld
         out = []
         for e, o in self.dyn_ents:
-            out.append((e, (dyn[o:o + 2, :n].t(), dyn[o + 2:o + 4, :n].t(), dyn[o + 4:o + 5, :n].t(),
-                            dyn[o + 5:o + 6, :n].t())))
+            out.append((e, (dyn.as_strided((n, 2), (1, ld), o * ld), dyn.as_strided((n, 2), (1, ld), (o + 2) * ld),
+                            dyn.as_strided((n, 1), (1, ld), (o + 4) * ld), dyn.as_strided((n, 1), (1, ld), (o + 5) * ld))))
         return out
 
     def _bind_static(self):
@@ -219,7 +220,7 @@ class WorldBinding:
         io.act_out = act.data_ptr() if act is not None else None
         io.lidar_out = lid.data_ptr() if lid is not None else None
         io.pair_active_out = None
-        io.stream = torch.cuda.current_stream(self.device).cuda_stream
+        io.stream = _lib.raw_stream(torch, self.device)
         pl.step_io(io)
         # bind the results
         if dyn_out is not self.dyn:
@@ -232,7 +233,8 @@ class WorldBinding:
         if act is not None:
             if act is not self.act:
                 self.act = act
-                self._act_views = [(ag, act[o:o + 2, :n].t(), act[o + 2:o + 3, :n].t()) for ag, o in self.act_agents]
+                self._act_views = [(ag, act.as_strided((n, 2), (1, ld), o * ld), act.as_strided((n, 1), (1, ld), (o + 2) * ld))
+                                   for ag, o in self.act_agents]
             for ag, vf, vt in self._act_views:
                 ag.state._force, ag.state._torque = vf, vt
         if lid is not None:
@@ -262,7 +264,7 @@ class WorldBinding:
         k = self.sensors.get(id(sensor))
         if vectorized and k is not None and not self.dirty and self._state_untouched():
             o, r = int(self.plan.lidar_slot[k]), len(self.desc.lidars[k].angles)
-            m = self.lid[o:o + r, :self.n].t()
+            m = self.lid.as_strided((self.n, r), (1, self.ld), o * self.ld)
             sensor._last_measurement = m
             return m
         return orig_measure(vectorized)
@@ -289,7 +291,7 @@ class WorldBinding:
         ang = angles if (angles.dtype == torch.float32 and angles.stride(1) == 1) else angles.to(torch.float32).contiguous()
         out = torch.empty(ang.shape[0], ang.shape[1], device=self.device)
         pl.cast_rays(self.dyn, self.stat, self.ld, me, ang, float(max_range), np.asarray(targets, np.int32), out,
-                     torch.cuda.current_stream(self.device).cuda_stream)
+                     _lib.raw_stream(torch, self.device))
         return out
 
 
@@ -323,7 +325,7 @@ class WorldBinding:
         _lib.check(_lib.lib().vmasb200_set_action(
             action.data_ptr(), action.stride(0), action.stride(1), agent.action_size, c[1], c[2],
             int(bool(getattr(env, "clamp_action", False))), u.data_ptr(), self._act_flags.data_ptr(), self.n,
-            torch.cuda.current_stream(self.device).cuda_stream), "vmasb200_set_action")
+            _lib.raw_stream(torch, self.device)), "vmasb200_set_action")
         act.u = u
         self._act_pending = True
 

@@ -109,7 +109,7 @@ class ObsGather:
             outs.append(out)
             self.outs[o], self.widths[o] = out.data_ptr(), col
         _lib.check(_lib.lib().vmasb200_gather_obs(self.segs, s, self.outs, self.widths, len(spec), n,
-                                                  torch.cuda.current_stream(self.device).cuda_stream), "vmasb200_gather_obs")
+                                                  _lib.raw_stream(torch, self.device)), "vmasb200_gather_obs")
         return outs
 
 
@@ -281,7 +281,7 @@ class NavigationHooks(ScenarioHooks):
         cn.pos_rew, cn.final_rew = sc.pos_rew.data_ptr(), sc.final_rew.data_ptr()  # in place (navigation.py:203-204)
         cn.all_goal_reached, cn.done = bp + A * n, bp + (A + 1) * n
         cn.pair_flags = self.flags.data_ptr()
-        _lib.check(_lib.lib().vmasb200_navigation_reward(C.byref(cn), n, torch.cuda.current_stream(self.device).cuda_stream),
+        _lib.check(_lib.lib().vmasb200_navigation_reward(C.byref(cn), n, _lib.raw_stream(torch, self.device)),
                    "vmasb200_navigation_reward")
         bools = bbuf.view(torch.bool)
         for i, a in enumerate(agents):
@@ -371,7 +371,7 @@ class TransportHooks(ScenarioHooks):
             g.global_shaping_out, g.dist_to_goal = fp + (2 * k) * row, fp + (2 * k + 1) * row
             g.on_goal, g.color = bp + k * n, colors[k].data_ptr()
         ct.rew, ct.done = fp + (2 * P) * row, bp + P * n
-        _lib.check(_lib.lib().vmasb200_transport_reward(C.byref(ct), n, torch.cuda.current_stream(self.device).cuda_stream),
+        _lib.check(_lib.lib().vmasb200_transport_reward(C.byref(ct), n, _lib.raw_stream(torch, self.device)),
                    "vmasb200_transport_reward")
         bools = bbuf.view(torch.bool)
         for k, p in enumerate(pk):

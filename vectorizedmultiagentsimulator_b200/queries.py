@@ -58,7 +58,7 @@ def make_pose(shape, radius, length, width, pos, rot, torch):
 
 
 def _stream(t, torch):
-    return torch.cuda.current_stream(t.device).cuda_stream
+    return _lib.raw_stream(torch, t.device)
 
 
 def get_distance(pose_a, pose_b, n, like, torch):
