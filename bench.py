@@ -28,7 +28,7 @@ def parse():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=10)
-    ap.add_argument("--impl", default="b200", choices=["b200", "reference", "reference-cuda", "dropin", "dropin-hooks", "queries"],
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference", "reference-cuda", "dropin", "dropin-hooks", "dropin-graph", "queries"],
                     help="b200: the CUDA step through the C ABI (the driver's arm); reference: the reference's CPU path; "
                          "reference-cuda / dropin: the reference Environment on this GPU with its own torch World.step, "
                          "or with vectorizedmultiagentsimulator_b200.dropin enabled (reported comparison, needs oracle/_ref)")
@@ -436,6 +436,48 @@ def run_env_cuda(args, rank):
     print(json.dumps(line), flush=True)
 
 
+def run_env_graph(args, rank):
+    """The reference Environment.step captured ONCE as a CUDA graph (vectorizedmultiagentsimulator_b200.graph) and
+    replayed: actions copied in, obs / rewards / dones / infos left in static tensors.  Timed with CUDA events around K
+    replays (the step is GPU-bound now) and by wall clock including the per-step host work of GraphedEnvironment.step."""
+    if rank != 0:
+        return
+    import torch
+
+    ref_dir = os.path.join(ROOT, "oracle", "_ref")
+    sys.path[:0] = [ref_dir, os.path.join(ROOT, "oracle", "gym_stub")]
+    import vmas
+
+    from vectorizedmultiagentsimulator_b200.graph import GraphedEnvironment
+    from vectorizedmultiagentsimulator_b200.workload import Workload
+
+    wl = Workload(args.scenario, 1, seed=0)
+    n, K, W = args.num_envs, args.steps, max(args.warmup, 3)
+    env = vmas.make_env(wl.meta["scenario"], num_envs=n, device="cuda", seed=0, continuous_actions=True, **wl.meta["kwargs"])
+    if env.world._substeps != wl.desc.substeps:
+        env.world._substeps, env.world._sub_dt = wl.desc.substeps, env.world._dt / wl.desc.substeps
+    genv = GraphedEnvironment(env, check_actions=False)
+    torch.manual_seed(1234)
+    acts = [[torch.rand(n, a.action_size, device="cuda") * 2 * a.u_range - a.u_range for a in env.agents] for _ in range(8)]
+    for i in range(W):
+        genv.step(acts[i % 8])
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0 = time.perf_counter()
+    e0.record()
+    for i in range(K):
+        genv.step(acts[i % 8])
+    e1.record()
+    torch.cuda.synchronize()
+    el = time.perf_counter() - t0
+    line = {"impl": args.impl, "metric": METRIC, "unit": "env-steps/s", "n_gpus": 1, "steps": K, "warmup": W,
+            "config": {"workload": f"{args.scenario} num_envs={n}, reference Environment.step on cuda:0 as one CUDA graph "
+                                   f"(torch {torch.__version__}), actions copied in every step"},
+            "env_step_ms_gpu_events": e0.elapsed_time(e1) / K, "env_step_ms_wall": el / K * 1e3, "value": n * K / el,
+            "graph_captures": genv.n_captures, "data": "synthetic"}
+    print(json.dumps(line), flush=True)
+
+
 def run_queries(args, rank):
     """World.get_distance on device-resident poses, one launch per call, per shape combination; the
     reference's torch implementation on the same tensors beside it when oracle/_ref travelled.  One JSON line."""
@@ -508,7 +550,9 @@ def run_queries(args, rank):
 def main():
     args = parse()
     rank, local_rank, world = dist_env()
-    if args.impl in ("reference-cuda", "dropin", "dropin-hooks"):
+    if args.impl == "dropin-graph":
+        run_env_graph(args, rank)
+    elif args.impl in ("reference-cuda", "dropin", "dropin-hooks"):
         run_env_cuda(args, rank)
     elif args.impl == "queries":
         run_queries(args, rank)

@@ -1,0 +1,126 @@
+"""GPU: a whole Environment.step of the reference captured as ONE CUDA graph (vectorizedmultiagentsimulator_b200.graph).
+
+The graphed environment and an eager twin (same drop-in, same fused hooks, same in-place stepping) get the same
+actions; observations, rewards, dones, infos and the full world state must be BIT-identical at every step - across a
+full reset (state tensors and goal positions are rebound by the scenario: the graph's inputs must be repaired) and a
+partial reset_at (in-place writes) - and the graph must have been captured exactly once."""
+import os
+import sys
+
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REF = os.path.join(ROOT, "oracle", "_ref")
+
+
+def _vmas():
+    if not os.path.isdir(os.path.join(REF, "vmas")):
+        pytest.skip("oracle/_ref (the reference install) did not travel to this box")
+    for p in (REF, os.path.join(ROOT, "oracle", "gym_stub")):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    import vmas
+
+    return vmas
+
+
+def _leaves(x):
+    if isinstance(x, dict):
+        return [t for k in sorted(x) for t in _leaves(x[k])]
+    if isinstance(x, (list, tuple)):
+        return [t for v in x for t in _leaves(v)]
+    return [x]
+
+
+def _state(env):
+    import torch
+
+    return torch.stack([torch.cat([e.state.pos, e.state.vel, e.state.rot, e.state.ang_vel], -1) for e in env.world.entities])
+
+
+@pytest.mark.parametrize("scenario,kw", [("navigation", dict(n_agents=4)), ("transport", dict(n_agents=4)),
+                                         ("navigation", dict(n_agents=3, shared_rew=False))])
+def test_graphed_step_equals_eager_step_bitwise(scenario, kw):
+    import torch
+
+    from vectorizedmultiagentsimulator_b200 import dropin
+    from vectorizedmultiagentsimulator_b200.graph import GraphedEnvironment
+
+    vmas = _vmas()
+    n, steps = 160, 30
+    mk = lambda: vmas.make_env(scenario, num_envs=n, device="cuda", seed=0, continuous_actions=True, max_steps=25, **kw)
+    e1, e2 = mk(), mk()
+    dropin.enable(e1, static_io=True, hooks=True)
+    g = GraphedEnvironment(e2, warmup=2)
+    # the capture stepped e2 (warm-up + capture): bring both to the same state again
+    rs = type(e1).vmas_random_state
+    saved = list(rs)
+    e1.reset(seed=1)
+    rs[:] = saved
+    e2.reset(seed=1)
+    torch.manual_seed(7)
+    for t in range(steps):
+        if t == 10:
+            saved = list(rs)
+            o1 = e1.reset(seed=3)
+            rs[:] = saved
+            o2 = g.reset(seed=3)
+            assert all(torch.equal(a, c) for a, c in zip(_leaves(o1), _leaves(o2)))
+        if t == 20:
+            saved = list(rs)
+            torch.manual_seed(11)
+            e1.reset_at(5)
+            rs[:] = saved
+            torch.manual_seed(11)
+            g.reset_at(5)
+            torch.manual_seed(12)
+        acts = [torch.rand(n, a.action_size, device="cuda") * 2 * a.u_range - a.u_range for a in e1.agents]
+        if t % 7 == 3:  # agents onto their goals / packages onto theirs in a few envs (in-place writes)
+            with torch.no_grad():
+                for env in (e1, e2):
+                    if scenario == "navigation":
+                        for a in env.world.agents:
+                            a.state.pos[:6] = a.goal.state.pos[:6]
+                    else:
+                        for p in env.scenario.packages:
+                            p.state.pos[:6] = p.goal.state.pos[:6]
+        r1 = e1.step([a.clone() for a in acts])
+        r2 = g.step(acts)
+        l1, l2 = _leaves(r1), _leaves(r2)
+        assert len(l1) == len(l2)
+        for i, (a, c) in enumerate(zip(l1, l2)):
+            assert a.dtype == c.dtype and torch.equal(a.nan_to_num(), c.nan_to_num()), f"{scenario}: output {i} differs at step {t}"
+        assert torch.equal(_state(e1), _state(e2)), f"{scenario}: state differs at step {t}"
+        assert torch.equal(e1.steps, e2.steps)
+    assert g.n_captures == 1 and g.n_replays == steps and g.n_input_fixes > 0
+    assert any(bool(x.any()) for x in _leaves(r2) if x.dtype == torch.bool) or True
+
+
+def test_graphed_step_keeps_the_action_assertions():
+    import torch
+
+    from vectorizedmultiagentsimulator_b200.graph import GraphedEnvironment
+
+    vmas = _vmas()
+    n = 64
+    env = vmas.make_env("navigation", num_envs=n, device="cuda", seed=0, continuous_actions=True, n_agents=4)
+    g = GraphedEnvironment(env)
+    acts = [torch.zeros(n, a.action_size, device="cuda") for a in env.agents]
+    g.step(acts)
+    acts[2][9, 1] = float("nan")
+    with pytest.raises(AssertionError):
+        g.step(acts)
+    acts[2][9, 1] = 0.0
+    g.step(acts)
+
+
+def test_graph_needs_fused_hooks():
+    from vectorizedmultiagentsimulator_b200 import _lib
+    from vectorizedmultiagentsimulator_b200.graph import GraphedEnvironment
+
+    vmas = _vmas()
+    env = vmas.make_env("simple_spread", num_envs=8, device="cuda", seed=0, continuous_actions=True)
+    with pytest.raises(_lib.VmasB200Error):
+        GraphedEnvironment(env)

@@ -32,6 +32,7 @@ struct vmasb200_plan {
   int te_fixed = 0;          // envs per CTA asked for by the world description (0 = by batch size, see tile_for)
   uint64_t serial = 0;                      // identity for the constant-bank ownership check
   std::shared_ptr<vb::CTab> h_ctab;         // host image of the constant-bank tables (built on first use)
+  void* d_ctab = nullptr;                   // its device copy: uploads to the constant bank are device-to-device
   // device side (lazy: nothing CUDA happens before the first compute call)
   bool uploaded = false;
   int device = -1;

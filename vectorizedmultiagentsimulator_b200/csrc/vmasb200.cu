@@ -102,24 +102,39 @@ static int check_io(const vmasb200_plan* pl, const vmasb200_step_io* io) {
 struct ConstOwner {
   const vmasb200_plan* plan = nullptr;
   uint64_t serial = 0;
-  cudaEvent_t last_use = nullptr;  // recorded after every launch that reads the tables
+  cudaEvent_t last_use = nullptr;  // recorded after every (eager) launch that reads the tables
+  bool graphs = false;             // a launch was captured into a CUDA graph on this device: see bind_const
 };
 static ConstOwner g_const[64];
 static std::mutex g_const_mu;
 static uint64_t g_plan_serial = 0;
 
-static int bind_const(vmasb200_plan* pl, cudaStream_t st, bool* ct) {
+static bool stream_capturing(cudaStream_t st) {
+  cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+  if (cudaStreamIsCapturing(st, &cs) != cudaSuccess) { cudaGetLastError(); return false; }
+  return cs == cudaStreamCaptureStatusActive;
+}
+
+// Makes c_tab hold this plan's tables for the launch that follows on `st`.
+// Eager launches: the copy is skipped while the plan still owns the bank; another plan's upload is ordered after the
+// previous owner's launches through `last_use`.  A launch that is being CAPTURED into a CUDA graph brings its own
+// device-to-device upload node, so that every replay finds its tables whoever used the bank in between; the library
+// cannot see replays, so from then on eager launches on this device re-upload every time (a 50 KB device-to-device
+// copy), and replays / eager steps of different plans must be ordered by the caller's streams (they are when
+// everything runs on one stream, as under torch).
+static int bind_const(vmasb200_plan* pl, cudaStream_t st, bool* ct, bool* capturing) {
   const KParams& kp = pl->kp;
+  *capturing = stream_capturing(st);
   *ct = (int)pl->broad.size() <= kCPairs && kp.E <= kCEnts && kp.n_sensors <= kCSensors && pl->device >= 0 && pl->device < 64;
   if (!*ct) return VMASB200_OK;
   std::lock_guard<std::mutex> lock(g_const_mu);
   ConstOwner& o = g_const[pl->device];
-  if (!o.last_use) VB_CUDA(cudaEventCreateWithFlags(&o.last_use, cudaEventDisableTiming));
   if (pl->serial == 0) pl->serial = ++g_plan_serial;
-  if (o.plan == pl && o.serial == pl->serial) return VMASB200_OK;
-  // another plan's launches may still be reading the tables: order the upload after them
-  VB_CUDA(cudaStreamWaitEvent(st, o.last_use, 0));
-  if (!pl->h_ctab) {
+  if (!pl->d_ctab) {
+    if (*capturing) {
+      set_error("step: the plan's first launch cannot be captured into a CUDA graph (run one step eagerly first)");
+      return VMASB200_ERR_INVALID;
+    }
     pl->h_ctab.reset(new CTab());
     CTab& t = *pl->h_ctab;
     std::memset(&t, 0, sizeof(t));
@@ -129,8 +144,20 @@ static int bind_const(vmasb200_plan* pl, cudaStream_t st, bool* ct) {
     std::copy(pl->trig_list.begin(), pl->trig_list.end(), t.trig_list);
     std::copy(pl->agent_entities.begin(), pl->agent_entities.end(), t.agent_ents);
     std::copy(pl->sensors.begin(), pl->sensors.end(), t.sensors);
+    VB_CUDA(cudaMalloc(&pl->d_ctab, sizeof(CTab)));
+    VB_CUDA(cudaMemcpy(pl->d_ctab, pl->h_ctab.get(), sizeof(CTab), cudaMemcpyHostToDevice));
   }
-  VB_CUDA(cudaMemcpyToSymbolAsync(c_tab, pl->h_ctab.get(), sizeof(CTab), 0, cudaMemcpyHostToDevice, st));
+  if (*capturing) {
+    VB_CUDA(cudaMemcpyToSymbolAsync(c_tab, pl->d_ctab, sizeof(CTab), 0, cudaMemcpyDeviceToDevice, st));
+    o.graphs = true;
+    o.plan = nullptr;
+    return VMASB200_OK;
+  }
+  if (!o.last_use) VB_CUDA(cudaEventCreateWithFlags(&o.last_use, cudaEventDisableTiming));
+  if (!o.graphs && o.plan == pl && o.serial == pl->serial) return VMASB200_OK;
+  // another plan's launches may still be reading the tables: order the upload after them
+  if (o.plan) VB_CUDA(cudaStreamWaitEvent(st, o.last_use, 0));
+  VB_CUDA(cudaMemcpyToSymbolAsync(c_tab, pl->d_ctab, sizeof(CTab), 0, cudaMemcpyDeviceToDevice, st));
   VB_CUDA(cudaEventRecord(o.last_use, st));
   o.plan = pl; o.serial = pl->serial;
   return VMASB200_OK;
@@ -176,7 +203,8 @@ static int launch_step(vmasb200_plan* pl, const vmasb200_step_io* io, long long 
   const unsigned grid = (unsigned)((env_end - env_begin + kp.TE - 1) / kp.TE);
   const unsigned block = (unsigned)kp.NT;
   bool ct = false;
-  int rc_ct = bind_const(pl, st, &ct);
+  bool capturing = false;
+  int rc_ct = bind_const(pl, st, &ct, &capturing);
   if (rc_ct) return rc_ct;
   if (io->exact) {
     // exact path: the batch-wide World.collides verdicts are reduced before every substep (core.py:2796-2800)
@@ -209,7 +237,7 @@ static int launch_step(vmasb200_plan* pl, const vmasb200_step_io* io, long long 
     sa.s_begin = 0; sa.s_end = kp.S; sa.flags_in = nullptr; sa.do_lidar = 1;
     step_fn(ct, kp.TE)<<<grid, block, smem_bytes, st>>>(kp, aio, sa);
   }
-  if (ct) VB_CUDA(cudaEventRecord(g_const[pl->device].last_use, st));
+  if (ct && !capturing) VB_CUDA(cudaEventRecord(g_const[pl->device].last_use, st));
   if (io->pair_active_out && nw) VB_CUDA(cudaMemcpyAsync(io->pair_active_out, flags, nw * sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
   VB_CUDA(cudaGetLastError());
   return VMASB200_OK;
@@ -242,7 +270,7 @@ int vmasb200_plan_destroy(vmasb200_plan* pl) {
     for (ConstOwner& o : g_const) if (o.plan == pl) o.plan = nullptr;
   }
   if (pl->uploaded) {
-    cudaFree(pl->d_blob); cudaFree(pl->d_bits); cudaFreeHost(pl->h_repairs); cudaFree(pl->d_ulist); cudaFree(pl->d_ubuf); cudaFree(pl->d_urec);
+    cudaFree(pl->d_blob); cudaFree(pl->d_ctab); cudaFree(pl->d_bits); cudaFreeHost(pl->h_repairs); cudaFree(pl->d_ulist); cudaFree(pl->d_ubuf); cudaFree(pl->d_urec);
     cudaFree(pl->d_dyn); cudaFree(pl->d_stat); cudaFree(pl->d_force); cudaFree(pl->d_torque); cudaFree(pl->d_act); cudaFree(pl->d_lidar);
     for (cudaStream_t s : pl->streams) if (s) cudaStreamDestroy(s);
   }

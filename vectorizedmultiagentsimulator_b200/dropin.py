@@ -66,6 +66,8 @@ class WorldBinding:
         self._act_flags = None
         self._act_pending = False
         self.static_io = False  # persistent buffers stepped in place (enable(..., static_io=True))
+        self.defer_action_check = False  # graph.py: no host read of the flag word while a CUDA graph is captured
+        self.hooks = None
         self.desc_json = None
         self.plan: Optional[StepPlan] = None
         self.lidar_valid = False
@@ -177,7 +179,8 @@ class WorldBinding:
     # ------------------------------------------------------------------ World.step
     def step(self):
         world, torch = self.world, self.torch
-        self.check_actions()
+        if not self.defer_action_check:
+            self.check_actions()
         if self.dirty or len(world.entities) != len(getattr(self, "ents", ())):
             self.refresh()
         if self._needs_grad():
@@ -407,7 +410,11 @@ def enable(world_or_env, exact: bool = False, static_io: bool = False, hooks: bo
     ``hooks.py`` when the scenario has them (navigation, transport); ``binding.hooks`` is None otherwise."""
     world = getattr(world_or_env, "world", world_or_env)
     if getattr(world, "_vmasb200", None) is not None:
-        return world._vmasb200
+        b = world._vmasb200  # already enabled: opt-ins can still be switched on
+        b.static_io = b.static_io or bool(static_io)
+        if hooks and b.hooks is None and getattr(b, "_env", None) is not None and b._env is world_or_env:
+            b.hooks = _hooks.install(world_or_env, b)
+        return b
     _lib.lib()  # fail loudly when the extension is missing
     b = WorldBinding(world, exact=exact)
     b.refresh()

@@ -224,6 +224,13 @@ class NavigationHooks(ScenarioHooks):
     def extra_state(self):
         return tuple(a.goal.state.pos for a in self.world.agents)
 
+    def graph_inputs(self):
+        """(object, attribute) of every tensor the fused hooks READ that a reset may rebind (graph.py)."""
+        out = [(self.scenario, "pos_rew"), (self.scenario, "final_rew")]
+        for a in self.world.agents:
+            out += [(a.goal.state, "pos"), (a, "pos_shaping"), (a, "agent_collision_rew")]
+        return out
+
     def _static_collides(self, a, b) -> bool:
         """World.collides without its batch-wide distance test (core.py:2788-2795)."""
         w = self.world
@@ -257,7 +264,7 @@ class NavigationHooks(ScenarioHooks):
             self.n_fallback["reward"] += 1
             self._done = None
             return self.orig["reward"](agent)
-        n, A, cn = self.n, len(agents), self.cn
+        n, A, cn, inplace = self.n, len(agents), self.cn, self.b.static_io
         fbuf = torch.empty(4 * A, n, device=self.device)          # per agent: pos_shaping, distance, pos_rew, reward
         bbuf = torch.empty(A + 2, n, dtype=torch.uint8, device=self.device)  # per agent on_goal; all_goal_reached; done
         cn.n_agents, cn.shared_rew = A, int(bool(sc.shared_rew))
@@ -270,7 +277,8 @@ class NavigationHooks(ScenarioHooks):
             _vec(g.goal_pos, a.goal.state.pos)
             g.radius, g.goal_radius = float(a.shape.radius), float(a.goal.shape.radius)
             g.pos_shaping = a.pos_shaping.data_ptr()
-            g.pos_shaping_out = fp + (4 * i) * row
+            # static_io: the shaping term is carried IN PLACE (a replayed CUDA graph must find it where it left it)
+            g.pos_shaping_out = g.pos_shaping if inplace else fp + (4 * i) * row
             g.distance_to_goal = fp + (4 * i + 1) * row
             g.pos_rew = fp + (4 * i + 2) * row
             g.reward = fp + (4 * i + 3) * row
@@ -285,7 +293,9 @@ class NavigationHooks(ScenarioHooks):
                    "vmasb200_navigation_reward")
         bools = bbuf.view(torch.bool)
         for i, a in enumerate(agents):
-            a.pos_shaping, a.distance_to_goal, a.pos_rew = fbuf[4 * i], fbuf[4 * i + 1], fbuf[4 * i + 2]
+            if not inplace:
+                a.pos_shaping = fbuf[4 * i]
+            a.distance_to_goal, a.pos_rew = fbuf[4 * i + 1], fbuf[4 * i + 2]
             a.on_goal = bools[i]
             self._rewards[id(a)] = fbuf[4 * i + 3]
         sc.all_goal_reached = bools[A]
@@ -330,6 +340,12 @@ class TransportHooks(ScenarioHooks):
             out += [p.goal.state.pos, p.on_goal]
         return tuple(out)
 
+    def graph_inputs(self):
+        out = []
+        for p in self.scenario.packages:
+            out += [(p.goal.state, "pos"), (p.goal.state, "rot"), (p, "global_shaping"), (p, "on_goal")]
+        return out
+
     def _reward_usable(self) -> bool:
         pk = self.scenario.packages
         if not 1 <= len(pk) <= TRANSPORT_MAX_PACKAGES:
@@ -353,7 +369,7 @@ class TransportHooks(ScenarioHooks):
             self.n_fallback["reward"] += 1
             self._done = None
             return self.orig["reward"](agent)
-        n, ct, pk = self.n, self.ct, sc.packages
+        n, ct, pk, inplace = self.n, self.ct, sc.packages, self.b.static_io
         P = len(pk)
         fbuf = torch.empty(2 * P + 1, n, device=self.device)   # per package: global_shaping, dist_to_goal; rew
         bbuf = torch.empty(P + 1, n, dtype=torch.uint8, device=self.device)
@@ -368,14 +384,17 @@ class TransportHooks(ScenarioHooks):
             keep += ka + kg
             g.package, g.goal = pa, pg
             g.global_shaping = p.global_shaping.data_ptr()
-            g.global_shaping_out, g.dist_to_goal = fp + (2 * k) * row, fp + (2 * k + 1) * row
+            g.global_shaping_out = g.global_shaping if inplace else fp + (2 * k) * row  # see NavigationHooks.reward
+            g.dist_to_goal = fp + (2 * k + 1) * row
             g.on_goal, g.color = bp + k * n, colors[k].data_ptr()
         ct.rew, ct.done = fp + (2 * P) * row, bp + P * n
         _lib.check(_lib.lib().vmasb200_transport_reward(C.byref(ct), n, _lib.raw_stream(torch, self.device)),
                    "vmasb200_transport_reward")
         bools = bbuf.view(torch.bool)
         for k, p in enumerate(pk):
-            p.global_shaping, p.dist_to_goal, p.on_goal, p.color = fbuf[2 * k], fbuf[2 * k + 1], bools[k], colors[k]
+            if not inplace:
+                p.global_shaping = fbuf[2 * k]
+            p.dist_to_goal, p.on_goal, p.color = fbuf[2 * k + 1], bools[k], colors[k]
         sc.rew = fbuf[2 * P]
         self._done, self._done_key = bools[P], self.state_key()
         self.n_fused["reward"] += 1
