@@ -352,6 +352,20 @@ typedef struct vmasb200_transport {
 } vmasb200_transport;
 int vmasb200_transport_reward(const vmasb200_transport* tr, int64_t n_envs, void* stream);
 
+/* mpe/simple_spread.py:79-110 (reward): for every agent in turn, minus the distance of the closest agent to every
+ * landmark, then minus 1 per other agent overlapping it (World.is_overlapping, spheres), all in the reference's
+ * order of fp32 subtractions. */
+#define VMASB200_SPREAD_MAX 16
+typedef struct vmasb200_simple_spread {
+  int32_t n_agents, n_landmarks;
+  vmasb200_vec agent_pos[VMASB200_SPREAD_MAX];     /* agent.state.pos    [n_envs][2] */
+  vmasb200_vec landmark_pos[VMASB200_SPREAD_MAX];  /* landmark.state.pos [n_envs][2] */
+  double agent_radius[VMASB200_SPREAD_MAX];
+  uint8_t collide[VMASB200_SPREAD_MAX];            /* agent.collide                  */
+  float* rew;                                      /* d out: [n_envs] Scenario.rew   */
+} vmasb200_simple_spread;
+int vmasb200_simple_spread_reward(const vmasb200_simple_spread* sp, int64_t n_envs, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

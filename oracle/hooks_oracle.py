@@ -110,3 +110,19 @@ def transport_reward(pkg_state, pkg_dims, goal_pos, goal_radius, shaping_in, fac
     on_goal = np.stack(on_goal)
     return dict(dist=np.stack(dist), on_goal=on_goal, shaping_out=np.stack(shaping), color=np.stack(color), rew=rew,
                 done=on_goal.all(axis=0))                                                # :186-193
+
+
+def simple_spread_reward(agent_pos, landmark_pos, radius, collide):
+    """mpe/simple_spread.py:79-110.  agent_pos [A, N, 2], landmark_pos [L, N, 2]."""
+    A, n = agent_pos.shape[0], agent_pos.shape[1]
+    closest = [np.stack([_fma_norm(agent_pos[a] - lp) for a in range(A)], -1).min(-1) for lp in landmark_pos]  # :90-101
+    rew = np.zeros(n, F)
+    for s in range(A):                                                                   # :88
+        for c in closest:
+            rew = (rew - c).astype(F)                                                    # :102
+        if collide[s]:
+            for a in range(A):
+                if a != s:                                                               # :104-107, core.py:1934
+                    d = ((_fma_norm(agent_pos[a] - agent_pos[s]) - F(radius[a])).astype(F) - F(radius[s])).astype(F)
+                    rew = np.where(d < 0, (rew - F(1)).astype(F), rew)
+    return rew

@@ -180,7 +180,42 @@ def transport():
     print("transport", {k: v.shape for k, v in out.items()}, "on_goal", int(out["on_goal"].sum()), "done", int(out["done"].sum()))
 
 
+def simple_spread():
+    torch.manual_seed(1234)
+    torch.set_num_threads(1)
+    env = vmas.make_env("simple_spread", num_envs=N, device="cpu", seed=0, continuous_actions=True, n_agents=3)
+    sc, world = env.scenario, env.world
+    agents, lms = world.agents, world.landmarks
+    env.reset(seed=0)
+    g = torch.Generator().manual_seed(5)
+    rec = {k: [] for k in ("agent_pos", "agent_vel", "landmark_pos", "obs", "rew", "done")}
+    for t in range(STEPS):
+        acts = [(torch.rand(N, a.action_size, generator=g) * 2 - 1) * a.u_range for a in agents]
+        if t in (5, 12, 20):  # overlapping agents in a few envs
+            with torch.no_grad():
+                for k in range(0, 24):
+                    i, j = k % 3, (k + 1) % 3
+                    d = 2 * agents[i].shape.radius * (0.8 + 0.4 * float(torch.rand(1, generator=g)))
+                    agents[j].state.pos[k] = agents[i].state.pos[k] + torch.tensor([d, 0.0])
+            acts = [a * 0 for a in acts]
+        obs, rews, dones, infos = env.step(acts)
+        if t in KEEP:
+            rec["agent_pos"].append(np.stack([t2n(a.state.pos) for a in agents]))
+            rec["agent_vel"].append(np.stack([t2n(a.state.vel) for a in agents]))
+            rec["landmark_pos"].append(np.stack([t2n(l.state.pos) for l in lms]))
+            rec["obs"].append(np.stack([t2n(o) for o in obs]))
+            rec["rew"].append(t2n(rews[0]))
+            rec["done"].append(t2n(dones))
+    out = {k: np.stack(v) for k, v in rec.items()}
+    out["radius"] = np.array([a.shape.radius for a in agents], np.float64)
+    out["collide"] = np.array([bool(a.collide) for a in agents])
+    out["params"] = np.array([float(sc.obs_agents)], np.float64)
+    np.savez_compressed(os.path.join(HERE, "hooks", "simple_spread.npz"), **out)
+    print("simple_spread", {k: v.shape for k, v in out.items()}, "rew range", float(out["rew"].min()), float(out["rew"].max()))
+
+
 if __name__ == "__main__":
+    simple_spread()
     navigation()
     navigation(kw=dict(n_agents=3, shared_rew=False, observe_all_goals=True), tag="navigation_noshare")
     navigation(kw=dict(n_agents=2, collisions=False), tag="navigation_nocoll")

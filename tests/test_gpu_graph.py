@@ -41,7 +41,7 @@ def _state(env):
 
 
 @pytest.mark.parametrize("scenario,kw", [("navigation", dict(n_agents=4)), ("transport", dict(n_agents=4)),
-                                         ("navigation", dict(n_agents=3, shared_rew=False))])
+                                         ("navigation", dict(n_agents=3, shared_rew=False)), ("simple_spread", dict(n_agents=3))])
 def test_graphed_step_equals_eager_step_bitwise(scenario, kw):
     import torch
 
@@ -83,6 +83,8 @@ def test_graphed_step_equals_eager_step_bitwise(scenario, kw):
                     if scenario == "navigation":
                         for a in env.world.agents:
                             a.state.pos[:6] = a.goal.state.pos[:6]
+                    elif scenario == "simple_spread":
+                        env.world.agents[1].state.pos[:6] = env.world.agents[0].state.pos[:6] + 0.1
                     else:
                         for p in env.scenario.packages:
                             p.state.pos[:6] = p.goal.state.pos[:6]
@@ -121,6 +123,6 @@ def test_graph_needs_fused_hooks():
     from vectorizedmultiagentsimulator_b200.graph import GraphedEnvironment
 
     vmas = _vmas()
-    env = vmas.make_env("simple_spread", num_envs=8, device="cuda", seed=0, continuous_actions=True)
+    env = vmas.make_env("football", num_envs=8, device="cuda", seed=0, continuous_actions=True, ai_red_agents=False)
     with pytest.raises(_lib.VmasB200Error):
         GraphedEnvironment(env)

@@ -152,6 +152,42 @@ def test_transport_c_abi_matches_reference_golden():
             assert np.array_equal(outs[a].cpu().numpy(), g["obs"][t, a]), f"step {t}: obs of agent {a}"
 
 
+def test_simple_spread_c_abi_matches_reference_golden():
+    import torch
+
+    from vectorizedmultiagentsimulator_b200 import _lib, hooks as H
+
+    g = load("simple_spread")
+    T, A, n = g["agent_pos"].shape[:3]
+    Lm = g["landmark_pos"].shape[1]
+    L = _lib.lib()
+    for t in range(T):
+        apos = [soa(torch, g["agent_pos"][t, a]) for a in range(A)]
+        avel = [soa(torch, g["agent_vel"][t, a]) for a in range(A)]
+        lpos = [torch.from_numpy(g["landmark_pos"][t, l]).cuda() for l in range(Lm)]
+        cs = H.CSimpleSpread()
+        cs.n_agents, cs.n_landmarks = A, Lm
+        for a in range(A):
+            H._vec(cs.agent_pos[a], apos[a])
+            cs.agent_radius[a], cs.collide[a] = float(g["radius"][a]), int(g["collide"][a])
+        for l in range(Lm):
+            H._vec(cs.landmark_pos[l], lpos[l])
+        rew = torch.full((n,), float("nan"), device="cuda")
+        cs.rew = rew.data_ptr()
+        _lib.check(L.vmasb200_simple_spread_reward(C.byref(cs), n, torch.cuda.current_stream().cuda_stream), "vmasb200_simple_spread_reward")
+        assert np.array_equal(rew.cpu().numpy(), g["rew"][t]), f"step {t}: rew"
+        spec = []
+        for a in range(A):
+            parts = [(H.OBS_COPY, apos[a], None, 0.0), (H.OBS_COPY, avel[a], None, 0.0)]
+            parts += [(H.OBS_SUB, lpos[l], apos[a], 0.0) for l in range(Lm)]
+            if g["params"][0]:
+                parts += [(H.OBS_SUB, apos[o], apos[a], 0.0) for o in range(A) if o != a]
+            spec.append(parts)
+        outs = H.ObsGather(torch, n, torch.device("cuda", 0)).run(spec)
+        for a in range(A):
+            assert np.array_equal(outs[a].cpu().numpy(), g["obs"][t, a]), f"step {t}: obs of agent {a}"
+
+
 def test_gather_obs_rejects_bad_tables():
     import torch
 
@@ -204,6 +240,8 @@ def _snapshot(env, scenario):
     if scenario == "navigation":
         snap = {(i, k): getattr(a, k).clone() for i, a in enumerate(env.world.agents) for k in NAV_ATTRS if hasattr(a, k)}
         snap.update({k: getattr(sc, k).clone() for k in ("pos_rew", "final_rew", "all_goal_reached") if hasattr(sc, k)})
+    elif scenario == "simple_spread":
+        snap = {"rew": sc.rew.clone()} if hasattr(sc, "rew") else {}
     else:
         snap = {(i, k): getattr(p, k).clone() for i, p in enumerate(sc.packages) for k in PKG_ATTRS
                 if hasattr(getattr(p, k, None), "clone")}
@@ -214,7 +252,7 @@ def _snapshot(env, scenario):
 
 def _restore(env, scenario, snap):
     sc = env.scenario
-    objs = env.world.agents if scenario == "navigation" else sc.packages
+    objs = env.world.agents if scenario == "navigation" else getattr(sc, "packages", None)
     for key, v in snap.items():
         if isinstance(key, tuple):
             setattr(objs[key[0]], key[1], v.clone())
@@ -226,7 +264,8 @@ def _restore(env, scenario, snap):
 
 @pytest.mark.parametrize("scenario,kw", [("navigation", dict(n_agents=4)), ("navigation", dict(n_agents=3, shared_rew=False, observe_all_goals=True)),
                                          ("navigation", dict(n_agents=2, collisions=False)), ("transport", dict(n_agents=4)),
-                                         ("transport", dict(n_agents=3, n_packages=2))])
+                                         ("transport", dict(n_agents=3, n_packages=2)), ("simple_spread", dict(n_agents=3)),
+                                         ("simple_spread", dict(n_agents=5, obs_agents=False))])
 def test_fused_hooks_equal_reference_hooks_on_the_same_state(scenario, kw):
     import torch
 
@@ -263,6 +302,10 @@ def test_fused_hooks_equal_reference_hooks_on_the_same_state(scenario, kw):
                     a0, a1 = env.world.agents[0], env.world.agents[1]
                     for k in range(12, 30):
                         a1.state.pos[k] = a0.state.pos[k] + torch.tensor([0.19 + 0.001 * (k - 12), 0.0], device="cuda")
+                elif scenario == "simple_spread":
+                    a0, a1 = env.world.agents[0], env.world.agents[1]
+                    for k in range(0, 30):
+                        a1.state.pos[k] = a0.state.pos[k] + torch.tensor([0.2 + 0.01 * k, 0.0], device="cuda")
                 else:
                     for p in sc.packages:
                         for k in range(0, 30):
@@ -288,7 +331,7 @@ def test_fused_hooks_equal_reference_hooks_on_the_same_state(scenario, kw):
         for i, (x, y) in enumerate(zip(lf, lr)):
             assert x.shape == y.shape and x.dtype == y.dtype, f"{scenario} step {t}: output {i} {x.shape} {x.dtype} vs {y.shape} {y.dtype}"
             assert same(x, y), f"{scenario} step {t}: output {i} differs by {float((x.float() - y.float()).abs().max()):.3e}"
-        assert left_f.keys() == left_r.keys() and len(left_f) >= 4
+        assert left_f.keys() == left_r.keys() and len(left_f) >= (1 if scenario == "simple_spread" else 4)
         for k in left_f:
             assert left_f[k].dtype == left_r[k].dtype and same(left_f[k], left_r[k]), f"{scenario} step {t}: attribute {k}"
     assert h.n_fused["reward"] == steps and h.n_fallback["reward"] == 0

@@ -90,3 +90,24 @@ def test_transport_hooks_match_reference():
             assert np.array_equal(r[k], g[k][t]), f"transport step {t}: {k} differs"
         for a in range(g["agent_pos"].shape[1]):
             assert np.array_equal(ho.gather_obs(tr_obs_parts(g, t, a)), g["obs"][t, a]), f"transport step {t} agent {a}: obs"
+
+
+def spread_obs_parts(g, t, a):
+    A = g["agent_pos"].shape[1]
+    parts = [(0, g["agent_pos"][t, a], None, 0.0), (0, g["agent_vel"][t, a], None, 0.0)]
+    parts += [(1, lp, g["agent_pos"][t, a], 0.0) for lp in g["landmark_pos"][t]]
+    if g["params"][0]:
+        parts += [(1, g["agent_pos"][t, o], g["agent_pos"][t, a], 0.0) for o in range(A) if o != a]
+    return parts
+
+
+def test_simple_spread_hooks_match_reference():
+    g = load("simple_spread")
+    hit = 0
+    for t in range(g["rew"].shape[0]):
+        r = ho.simple_spread_reward(g["agent_pos"][t], g["landmark_pos"][t], g["radius"], g["collide"])
+        assert np.array_equal(r, g["rew"][t]), f"simple_spread step {t}: rew differs by {np.abs(r - g['rew'][t]).max():.3e}"
+        hit += int((np.abs(r) > 3).sum())
+        for a in range(g["agent_pos"].shape[1]):
+            assert np.array_equal(ho.gather_obs(spread_obs_parts(g, t, a)), g["obs"][t, a]), f"simple_spread step {t} agent {a}: obs"
+    assert not g["done"].any()

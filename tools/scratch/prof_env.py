@@ -5,7 +5,7 @@ import torch, vmas
 from vectorizedmultiagentsimulator_b200 import dropin
 scenario = sys.argv[1] if len(sys.argv) > 1 else "navigation"
 static_io = len(sys.argv) > 2 and sys.argv[2] == "1"
-kw = dict(n_agents=4)
+kw = dict(n_agents=3 if scenario == "simple_spread" else 4)
 n = 32768
 env = vmas.make_env(scenario, num_envs=n, device="cuda", seed=0, continuous_actions=True, **kw)
 dropin.enable(env, hooks=True, static_io=static_io)

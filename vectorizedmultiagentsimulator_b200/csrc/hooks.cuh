@@ -213,4 +213,34 @@ __global__ void __launch_bounds__(256) transport_reward_kernel(const __grid_cons
   if (tp.done) tp.done[i] = done ? 1 : 0;
 }
 
+// ------------------------------------------------------------------------------------------------ simple_spread
+struct SpreadParams {
+  int n_agents, n_landmarks;
+  DVec apos[VMASB200_SPREAD_MAX], lpos[VMASB200_SPREAD_MAX];
+  float radius[VMASB200_SPREAD_MAX];
+  uint8_t collide[VMASB200_SPREAD_MAX];
+  float* rew;
+};
+__global__ void __launch_bounds__(256) simple_spread_reward_kernel(const __grid_constant__ SpreadParams sp, long long n) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  V2 p[VMASB200_SPREAD_MAX];
+  float closest[VMASB200_SPREAD_MAX];
+  for (int a = 0; a < sp.n_agents; ++a) p[a] = mk(vget(sp.apos[a], i, 0), vget(sp.apos[a], i, 1));
+  for (int l = 0; l < sp.n_landmarks; ++l) {  // torch.min over agents of ||a.pos - landmark.pos|| (simple_spread.py:90-101)
+    const V2 q = mk(vget(sp.lpos[l], i, 0), vget(sp.lpos[l], i, 1));
+    float m = norm(p[0] - q);
+    for (int a = 1; a < sp.n_agents; ++a) m = pmin(m, norm(p[a] - q));
+    closest[l] = m;
+  }
+  float rew = 0.f;
+  for (int s = 0; s < sp.n_agents; ++s) {     // for single_agent in self.world.agents (:88)
+    for (int l = 0; l < sp.n_landmarks; ++l) rew = rew - closest[l];                       // self.rew -= closest (:102)
+    if (sp.collide[s])
+      for (int a = 0; a < sp.n_agents; ++a)
+        if (a != s && (norm(p[a] - p[s]) - sp.radius[a]) - sp.radius[s] < 0.f) rew = rew - 1.f;  // is_overlapping(a, single_agent) (:104-107)
+  }
+  sp.rew[i] = rew;
+}
+
 }  // namespace vb

@@ -615,6 +615,27 @@ int vmasb200_transport_reward(const vmasb200_transport* tr, int64_t n, void* str
   return VMASB200_OK;
 }
 
+int vmasb200_simple_spread_reward(const vmasb200_simple_spread* sp, int64_t n, void* stream) {
+  if (!sp || n < 0 || sp->n_agents < 1 || sp->n_agents > VMASB200_SPREAD_MAX || sp->n_landmarks < 0 ||
+      sp->n_landmarks > VMASB200_SPREAD_MAX || !sp->rew) {
+    set_error("simple_spread_reward: bad argument (1 <= n_agents <= 16, n_landmarks <= 16, rew)"); return VMASB200_ERR_INVALID;
+  }
+  static thread_local SpreadParams p;
+  p.n_agents = sp->n_agents; p.n_landmarks = sp->n_landmarks; p.rew = sp->rew;
+  for (int a = 0; a < sp->n_agents; ++a) {
+    if (!sp->agent_pos[a].p) { set_error("simple_spread_reward: an agent position is NULL"); return VMASB200_ERR_INVALID; }
+    p.apos[a] = to_dvec(sp->agent_pos[a]); p.radius[a] = (float)sp->agent_radius[a]; p.collide[a] = sp->collide[a] ? 1 : 0;
+  }
+  for (int l = 0; l < sp->n_landmarks; ++l) {
+    if (!sp->landmark_pos[l].p) { set_error("simple_spread_reward: a landmark position is NULL"); return VMASB200_ERR_INVALID; }
+    p.lpos[l] = to_dvec(sp->landmark_pos[l]);
+  }
+  if (n == 0) return VMASB200_OK;
+  simple_spread_reward_kernel<<<(unsigned)((n + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(p, n);
+  VB_CUDA(cudaGetLastError());
+  return VMASB200_OK;
+}
+
 int vmasb200_sync_check(vmasb200_plan* pl, void* stream, int64_t* n_fixups) {
   VB_CUDA(cudaStreamSynchronize(static_cast<cudaStream_t>(stream)));
   VB_CUDA(cudaGetLastError());

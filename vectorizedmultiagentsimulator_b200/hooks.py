@@ -10,7 +10,8 @@ reference's hooks leave behind (``agent.pos_shaping``, ``agent.on_goal``, ``scen
 it rebinds.  A configuration a fused hook does not cover (autograd in play, shapes it does not know, non-CUDA tensors)
 takes the saved original method: the reference's torch code is the fallback of the HOOKS, never of the physics.
 
-Scenarios: ``navigation`` (navigation.py:199-280) and ``transport`` (transport.py:130-193)."""
+Scenarios: ``navigation`` (navigation.py:199-280), ``transport`` (transport.py:130-193) and ``simple_spread``
+(mpe/simple_spread.py:79-129)."""
 from __future__ import annotations
 
 import ctypes as C
@@ -21,7 +22,7 @@ from .queries import CPose, make_pose, shape_of
 from .worlddesc import SPHERE
 
 OBS_COPY, OBS_SUB, OBS_CSUB, OBS_BOOL = 0, 1, 2, 3
-NAV_MAX_AGENTS, TRANSPORT_MAX_PACKAGES, OBS_MAX_SEGS, OBS_MAX_OUTS, OBS_MAX_WIDTH = 16, 8, 128, 32, 352
+NAV_MAX_AGENTS, TRANSPORT_MAX_PACKAGES, OBS_MAX_SEGS, OBS_MAX_OUTS, OBS_MAX_WIDTH, SPREAD_MAX = 16, 8, 128, 32, 352, 16
 
 
 class CVec(C.Structure):
@@ -58,6 +59,12 @@ class CTransport(C.Structure):
     _fields_ = [("n_packages", C.c_int32), ("shaping_factor", C.c_double), ("color_off_goal", C.c_float * 3),
                 ("color_on_goal", C.c_float * 3), ("package", CTransportPackage * TRANSPORT_MAX_PACKAGES),
                 ("rew", C.c_void_p), ("done", C.c_void_p)]
+
+
+class CSimpleSpread(C.Structure):
+    _fields_ = [("n_agents", C.c_int32), ("n_landmarks", C.c_int32), ("agent_pos", CVec * SPREAD_MAX),
+                ("landmark_pos", CVec * SPREAD_MAX), ("agent_radius", C.c_double * SPREAD_MAX),
+                ("collide", C.c_uint8 * SPREAD_MAX), ("rew", C.c_void_p)]
 
 
 def _vec(v: CVec, t):
@@ -411,7 +418,74 @@ class TransportHooks(ScenarioHooks):
         return spec
 
 
-REGISTRY = (NavigationHooks, TransportHooks)
+class SimpleSpreadHooks(ScenarioHooks):
+    """mpe/simple_spread.py:79-129.  The scenario keeps BaseScenario.done (scenario.py:326: all False, built from a
+    host list every call - a host-to-device copy no CUDA graph can hold); here the same values come from a device fill."""
+
+    @staticmethod
+    def matches(scenario) -> bool:
+        return scenario_file(scenario) == "simple_spread" and hasattr(scenario, "obs_agents")
+
+    def __init__(self, env, binding):
+        super().__init__(env, binding)
+        self.cs = CSimpleSpread()
+
+    def extra_state(self):
+        return tuple(l.state.pos for l in self.world.landmarks)
+
+    def graph_inputs(self):
+        return [(l.state, "pos") for l in self.world.landmarks]
+
+    def _reward_usable(self) -> bool:
+        agents, lms = self.world.agents, self.world.landmarks
+        if not (1 <= len(agents) <= SPREAD_MAX and len(lms) <= SPREAD_MAX):
+            return False
+        for a in agents:
+            sh = shape_of(a)
+            if sh is None or sh[0] != SPHERE or not self._f32_vec(a.state.pos, 2):
+                return False
+        return all(self._f32_vec(l.state.pos, 2) for l in lms)
+
+    def reward(self, agent):
+        sc, torch, agents = self.scenario, self.torch, self.world.agents
+        if agent is not agents[0]:
+            return sc.rew if self._rew_ok else self.orig["reward"](agent)
+        self._rew_ok = self._reward_usable()
+        if not self._rew_ok:
+            self.n_fallback["reward"] += 1
+            return self.orig["reward"](agent)
+        cs, lms = self.cs, self.world.landmarks
+        cs.n_agents, cs.n_landmarks = len(agents), len(lms)
+        for i, a in enumerate(agents):
+            _vec(cs.agent_pos[i], a.state.pos)
+            cs.agent_radius[i], cs.collide[i] = float(a.shape.radius), int(bool(a.collide))
+        for i, l in enumerate(lms):
+            _vec(cs.landmark_pos[i], l.state.pos)
+        rew = torch.empty(self.n, device=self.device)  # the reference binds a fresh tensor too (simple_spread.py:83)
+        cs.rew = rew.data_ptr()
+        _lib.check(_lib.lib().vmasb200_simple_spread_reward(C.byref(cs), self.n, _lib.raw_stream(torch, self.device)),
+                   "vmasb200_simple_spread_reward")
+        sc.rew = rew
+        self.n_fused["reward"] += 1
+        return rew
+
+    def done(self):
+        self.n_fused["done"] += 1
+        return self.torch.zeros(self.n, dtype=self.torch.bool, device=self.device)
+
+    def obs_spec(self):
+        sc, agents = self.scenario, self.world.agents
+        spec = []
+        for a in agents:
+            parts = [(OBS_COPY, a.state.pos, None, 0.0), (OBS_COPY, a.state.vel, None, 0.0)]
+            parts += [(OBS_SUB, l.state.pos, a.state.pos, 0.0) for l in self.world.landmarks]
+            if sc.obs_agents:
+                parts += [(OBS_SUB, o.state.pos, a.state.pos, 0.0) for o in agents if o is not a]
+            spec.append(parts)
+        return spec
+
+
+REGISTRY = (NavigationHooks, TransportHooks, SimpleSpreadHooks)
 
 
 def install(env, binding) -> Optional[ScenarioHooks]:
