@@ -189,3 +189,43 @@ def test_repeatable_bitwise(name):
         for x, y in zip(first, again):
             if x is not None:
                 assert np.array_equal(x.view(np.uint32), y.view(np.uint32))
+
+
+@pytest.mark.parametrize("scenario", ["navigation", "transport", "joint_passage", "football"])
+def test_step_host_zero_copy_equals_staged_bitwise(scenario, monkeypatch):
+    """vmasb200_step_host with PINNED host buffers takes the zero-copy path (one launch whose TMA bulk copies read and
+    write host memory over PCIe); with VMASB200_HOST_DIRECT=0 - and with pageable buffers - it takes the staged
+    H2D / kernel / D2H pipeline.  Same bits either way, over a rollout that feeds each step's output to the next."""
+    import torch
+
+    from vectorizedmultiagentsimulator_b200.plan import StepPlan
+    from vectorizedmultiagentsimulator_b200.workload import Workload
+
+    n = 2048 + 40
+    wl = Workload(scenario, n, seed=3)
+    plan = StepPlan(wl.desc)
+    dyn0, stat0 = plan.pack(wl.state0, wl.jrot0 if wl.jrot0.size else None)
+    ld = dyn0.shape[1]
+    f, t = wl.random_actions(6)
+    pin = lambda a: torch.from_numpy(np.ascontiguousarray(a)).pin_memory().numpy()
+
+    def rollout(direct, pinned):
+        monkeypatch.setenv("VMASB200_HOST_DIRECT", "1" if direct else "0")
+        mk = pin if pinned else (lambda a: np.ascontiguousarray(a).copy())
+        dyn, stat = mk(dyn0), mk(stat0)
+        res = []
+        for k in range(6):
+            out = (mk(np.zeros((plan.dyn_rows, ld), np.float32)),
+                   mk(np.zeros((plan.act_rows, ld), np.float32)) if plan.act_rows else None,
+                   mk(np.zeros((plan.lidar_rows, ld), np.float32)) if plan.lidar_rows else None)
+            d, a, l, _ = plan.step_host(dyn, stat, mk(f[k]), mk(t[k]), exact=False, want_masks=False, out=out)
+            res.append((d[:, :n].copy(), None if a is None else a[:, :n].copy(), None if l is None else l[:, :n].copy()))
+            dyn = d
+        return res
+
+    zero_copy, staged, pageable = rollout(True, True), rollout(False, True), rollout(True, False)
+    for k, (x, y, z) in enumerate(zip(zero_copy, staged, pageable)):
+        for i in range(3):
+            if x[i] is not None:
+                assert np.array_equal(x[i], y[i], equal_nan=True), f"{scenario}: output {i} of step {k}, zero-copy vs staged"
+                assert np.array_equal(x[i], z[i], equal_nan=True), f"{scenario}: output {i} of step {k}, pinned vs pageable"

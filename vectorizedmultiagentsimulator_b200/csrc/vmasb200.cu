@@ -339,6 +339,17 @@ static int grow_host_staging(vmasb200_plan* pl, int64_t ld) {
   return VMASB200_OK;
 }
 
+// device alias of a pinned (mapped) host buffer; false when `h` is pageable (NULL stays NULL)
+static bool host_dev_ptr(const void* h, void** d) {
+  *d = nullptr;
+  if (!h) return true;
+  cudaPointerAttributes at;
+  if (cudaPointerGetAttributes(&at, h) != cudaSuccess) { cudaGetLastError(); return false; }
+  if (at.type != cudaMemoryTypeHost || !at.devicePointer) return false;
+  *d = at.devicePointer;
+  return true;
+}
+
 int vmasb200_step_host(vmasb200_plan* pl, const float* h_dyn_in, const float* h_stat, const float* h_force,
                        const float* h_torque, float* h_dyn_out, float* h_act_out, float* h_lidar_out,
                        uint32_t* h_pair_active, int64_t n, int64_t ld, int32_t exact) {
@@ -378,6 +389,41 @@ int vmasb200_step_host(vmasb200_plan* pl, const float* h_dyn_in, const float* h_
     if (want_lidar) VB_CUDA(rows2d(h_lidar_out, ld, pl->d_lidar, dld, c0, ncol, kp.lidar_rows, cudaMemcpyDeviceToHost, st));
     return VMASB200_OK;
   };
+  // Zero-copy path: when every buffer is pinned (page-locked, mapped) host memory, ONE launch over the whole batch
+  // reads its tiles from and writes its results to host memory directly - the TMA bulk copies and the force loads go
+  // over PCIe themselves, in both directions at once and overlapped with the arithmetic of the other CTAs - instead of
+  // H2D copies, kernels and D2H copies chained per chunk.  Opt-in (VMASB200_HOST_DIRECT=1): measured on B200 it is
+  // +5 % (navigation) / +17 % (transport) at 32 768 envs, equal at 262 144 and -8 % for football (CTAs that wait
+  // for PCIe hold the SM's shared memory), see profiles/README.md; same bits either way (tests/test_gpu_parity.py).
+  const char* env_direct = std::getenv("VMASB200_HOST_DIRECT");
+  const bool direct_ok = env_direct && std::atoi(env_direct) != 0;
+  if (direct_ok && !exact && h_dyn_out && kp.n_dyn && (!kp.act_rows || h_act_out)) {
+    void *d_in, *d_out, *d_st, *d_f, *d_t, *d_act, *d_lid;
+    if (host_dev_ptr(h_dyn_in, &d_in) && host_dev_ptr(h_dyn_out, &d_out) && host_dev_ptr(h_stat, &d_st) &&
+        host_dev_ptr(h_force, &d_f) && host_dev_ptr(h_torque, &d_t) && host_dev_ptr(h_act_out, &d_act) &&
+        host_dev_ptr(want_lidar ? h_lidar_out : nullptr, &d_lid)) {
+      const float* f2[kMaxAgents]; const float* t2[kMaxAgents];
+      for (int a = 0; a < kp.A; ++a) {
+        f2[a] = d_f ? static_cast<const float*>(d_f) + 2 * a : nullptr;
+        t2[a] = d_t ? static_cast<const float*>(d_t) + a : nullptr;
+      }
+      cudaStream_t st = pl->streams[0];
+      vmasb200_step_io io{};
+      io.dyn_in = static_cast<const float*>(d_in); io.dyn_out = static_cast<float*>(d_out);
+      io.stat = static_cast<const float*>(d_st);
+      io.force_ptrs = f2; io.force_strides = fstr; io.torque_ptrs = t2; io.torque_strides = tstr;
+      io.act_out = kp.act_rows ? static_cast<float*>(d_act) : nullptr;
+      io.lidar_out = static_cast<float*>(d_lid);
+      io.pair_active_out = nullptr; io.n_envs = n; io.ld = ld; io.exact = 0; io.stream = st;
+      if ((rc = check_io(pl, &io)) == VMASB200_OK) {
+        if ((rc = launch_step(pl, &io, 0, n))) return rc;
+        VB_CUDA(cudaStreamSynchronize(st));
+        if (h_pair_active && kp.S * kp.pair_words)
+          VB_CUDA(cudaMemcpy(h_pair_active, pl->d_bits, (size_t)kp.S * kp.pair_words * 4, cudaMemcpyDeviceToHost));
+        return VMASB200_OK;
+      }
+    }
+  }
   // repairs so far (mapped host word the verifying CTA writes): every earlier step of this plan has been waited for
   const int repairs_before = *static_cast<volatile int*>(pl->h_repairs);
   for (int64_t k = 0; k < nchunk; ++k) {
