@@ -184,6 +184,20 @@ int vmasb200_plan_lidar_slots(const vmasb200_plan* plan, int32_t* lidar_slot);
  * or, when that is 0, chosen from the batch size.  128 / tile threads share each environment's work. */
 int vmasb200_plan_tile(const vmasb200_plan* plan, int64_t n_envs);
 
+/* World-compiled step kernels.  For worlds without joints whose candidate pairs are all sphere-sphere (simple_spread,
+ * navigation, most MPE scenarios) the library prints the plan as C++ with the world's constants, entity attributes
+ * and pair list as literals, compiles it with NVRTC for sm_100a (same parity flags as the library build) and launches
+ * that instead of the generic table-walking kernel: an environment's state then stays in registers for all substeps.
+ * Results are bit-identical to the generic kernel.  Cubins are cached in `_jit/` beside the library (or
+ * $VMASB200_JIT_CACHE).  Without libnvrtc / libcuda, for other worlds, with VMASB200_JIT=0 in the environment or after
+ * vmasb200_jit_enable(0) the generic kernel runs.
+ *  vmasb200_jit_enable: process-wide switch, returns the previous setting.
+ *  vmasb200_plan_jit: compiles (no GPU needed) the kernel a step over n_envs would take.  *state: 1 compiled / cached,
+ *  0 the world is not covered or the switch is off, -1 compilation failed (vmasb200_last_error says why).
+ *  *launches: launches of this plan that took a compiled kernel so far.  Either out pointer may be NULL. */
+int vmasb200_jit_enable(int on);
+int vmasb200_plan_jit(vmasb200_plan* plan, int64_t n_envs, int32_t* state, int64_t* launches);
+
 typedef struct vmasb200_step_io {
   const float* dyn_in;             /* d: [dyn_rows][ld]                                                 */
   float* dyn_out;                  /* d: [dyn_rows][ld]; may alias dyn_in                               */
@@ -279,8 +293,13 @@ enum {
   VMASB200_OBS_COPY = 0, /* a            (fp32)                                              */
   VMASB200_OBS_SUB = 1,  /* a - b        (fp32; e.g. agent.state.pos - goal.state.pos)         */
   VMASB200_OBS_CSUB = 2, /* c - a        (fp32; e.g. sensor._max_range - sensor.measure())     */
-  VMASB200_OBS_BOOL = 3  /* a != 0 ? 1 : 0 (a is a torch.bool / uint8 tensor; cat promotes it) */
+  VMASB200_OBS_BOOL = 3, /* a != 0 ? 1 : 0 (a is a torch.bool / uint8 tensor; cat promotes it) */
+  VMASB200_OBS_COS = 4,  /* cosf(a)      (joint_passage.py:41-42 angle_to_vector)                  */
+  VMASB200_OBS_SIN = 5   /* sinf(a)                                                              */
 };
+/* Flags of vmasb200_obs_seg.flags.  NEG0: column 0 of BOTH operands is negated before the op (football.py:1376-1397:
+ * a red agent sees every x mirrored, `tensor[..., X] = -tensor[..., X]` on clones of the operands). */
+#define VMASB200_OBS_NEG0 1
 /* One block of columns of one observation tensor: out[i][col0 + k] = op(a[i][k], b[i][k]), k < width
  * (what one operand of the scenario's torch.cat([...], dim=-1) contributes). */
 typedef struct vmasb200_obs_seg {
@@ -290,7 +309,9 @@ typedef struct vmasb200_obs_seg {
   int32_t width;
   int32_t out;    /* index into outs[] */
   int32_t col0;
-  int32_t reserved;
+  int32_t flags;  /* VMASB200_OBS_NEG0 */
+  vmasb200_vec noise; /* p NULL, or a [n_envs][width] fp32 tensor ADDED to the op's result (joint_passage.py:531-541:
+                       * `obs + noise`, the noise drawn by the caller from torch's generator) */
 } vmasb200_obs_seg;
 #define VMASB200_OBS_MAX_SEGS 128
 #define VMASB200_OBS_MAX_OUTS 32
@@ -365,6 +386,72 @@ typedef struct vmasb200_simple_spread {
   float* rew;                                      /* d out: [n_envs] Scenario.rew   */
 } vmasb200_simple_spread;
 int vmasb200_simple_spread_reward(const vmasb200_simple_spread* sp, int64_t n_envs, void* stream);
+
+/* joint_passage.py:387-490 (reward for the first agent: pos / rot shaping of the joint before and after the passage,
+ * collision and energy terms), :547-563 (done).  `done` couples environments in the reference: the [n] position test
+ * is multiplied with the [n, 1] rotation test, which broadcasts to [n, n] before `all(dim=1)`, so
+ * done[i] = rot_ok[i] AND (pos_ok of EVERY env); the call reduces `all pos_ok` over the batch first (done_flag). */
+#define VMASB200_JP_MAX_BODIES 4
+#define VMASB200_JP_MAX_PASSAGES 24
+#define VMASB200_JP_MAX_WALLS 8
+typedef struct vmasb200_joint_passage {
+  int32_t n_agents;                 /* world.agents: all_passed (:401-404), energy (:476-484)                      */
+  int32_t n_bodies;                 /* agents (+ the mass when asym_package): the bodies of the collision loop :454 */
+  int32_t n_passages, n_walls;
+  int32_t all_passed_rot;           /* :432                                                                         */
+  int32_t dim_p;                    /* world.dim_p (:480)                                                           */
+  vmasb200_pose body[VMASB200_JP_MAX_BODIES];      /* agents first, then the mass                                   */
+  vmasb200_vec action_u[VMASB200_JP_MAX_BODIES];   /* agent.action.u [n_envs][2], agents only                       */
+  double f_range[VMASB200_JP_MAX_BODIES];          /* agent.f_range                                                 */
+  vmasb200_pose passage[VMASB200_JP_MAX_PASSAGES]; /* self.passages in order                                        */
+  uint8_t passage_collide[VMASB200_JP_MAX_PASSAGES];
+  vmasb200_pose wall[VMASB200_JP_MAX_WALLS];
+  vmasb200_pose joint;              /* self.joint.landmark (a line)                                                 */
+  vmasb200_vec goal_pos, goal_rot;  /* self.goal.state.pos [n][2], .rot [n][1]                                      */
+  double passage_width, pos_shaping_factor, rot_shaping_factor, collision_reward, energy_reward_coeff,
+      min_collision_distance, middle_angle;
+  const float* shaping_in[4];       /* d in : [n_envs] joint.pos_shaping_pre, pos_shaping_post, rot_shaping_pre, rot_shaping_post */
+  float* shaping_out[4];            /* d out: the new ones (may alias shaping_in)                                   */
+  float* pos_rew;                   /* d out: [n_envs] Scenario.pos_rew (written in place by the reference)         */
+  float* rot_rew;
+  float* collision_rew;
+  float* energy_expenditure;
+  float* energy_rew;
+  float* rew;                       /* d out: [n_envs] what Scenario.reward returns                                 */
+  uint8_t* all_passed;              /* d out: [n_envs]                                                              */
+  uint8_t* done;                    /* d out: [n_envs] Scenario.done(), or NULL                                      */
+  uint32_t* done_flag;              /* d scratch: one word, zeroed and filled by the call (needed when done != NULL) */
+} vmasb200_joint_passage;
+int vmasb200_joint_passage_reward(const vmasb200_joint_passage* jp, int64_t n_envs, void* stream);
+
+/* football.py:1118-1226 (reward for the first agent: sparse scoring reward, done, dense shaping of ball-to-goal and
+ * closest-agent-to-ball for both teams). */
+#define VMASB200_FB_MAX_TEAM 16
+typedef struct vmasb200_football_team {
+  int32_t n_agents;
+  int32_t dense;                    /* the dense terms of this team are computed (:1143-1151)                       */
+  vmasb200_vec agent_pos[VMASB200_FB_MAX_TEAM];
+  float goal_pos[2];                /* right_goal_pos (blue) / left_goal_pos (red), fp32 as the reference holds them */
+  const float* pos_shaping;         /* d in : [n_envs] ball.pos_shaping_blue / _red                                 */
+  float* pos_shaping_out;
+  const float* pos_shaping_agent;   /* d in : [n_envs] ball.pos_shaping_agent_blue / _red                           */
+  float* pos_shaping_agent_out;
+  float* distance_to_goal;          /* d out: [n_envs] ball.distance_to_goal_blue / _red                            */
+  float* pos_rew;                   /* d out: ball.pos_rew_blue / _red                                              */
+  float* min_agent_dist_to_ball;    /* d out                                                                        */
+  float* pos_rew_agent;             /* d out: ball.pos_rew_agent_blue / _red                                        */
+  float* dense_reward;              /* d out: _dense_reward_blue / _red                                             */
+  float* sparse_reward;             /* d out: _sparse_reward_blue / _red                                            */
+  float* reward;                    /* d out: sparse + dense, what Scenario.reward returns for this team's agents   */
+} vmasb200_football_team;
+typedef struct vmasb200_football {
+  vmasb200_vec ball_pos, ball_vel;
+  double pitch_length, ball_size, goal_size, scoring_reward, pos_shaping_factor_ball_goal,
+      pos_shaping_factor_agent_ball, distance_to_ball_trigger;
+  vmasb200_football_team team[2];   /* blue, red                                                                    */
+  uint8_t* done;                    /* d out: [n_envs] Scenario._done                                               */
+} vmasb200_football;
+int vmasb200_football_reward(const vmasb200_football* fb, int64_t n_envs, void* stream);
 
 #ifdef __cplusplus
 }

@@ -1,0 +1,86 @@
+"""GPU: the world-compiled step kernel (csrc/jit.h, NVRTC) against the generic table-walking kernel, BIT for bit, on
+every golden world the generator covers - state, clamped actions, LIDAR, collision masks - over the recorded rollout,
+and at a batch size that takes the large-batch CTA shape.  The generic kernel is the one pinned to the oracle and the
+reference's golden outputs (tests/test_gpu_parity.py, which with exact=False also runs the compiled kernel against
+them when the world has one)."""
+import numpy as np
+import pytest
+
+from tests.fixtures import Fixture
+from vectorizedmultiagentsimulator_b200 import _lib
+from vectorizedmultiagentsimulator_b200.plan import StepPlan
+
+pytestmark = pytest.mark.gpu
+COVERED = ["simple_spread", "navigation", "discovery", "flocking", "dropout"]
+
+
+def _same(a, b):
+    if a is None or b is None:
+        return a is None and b is None
+    return np.array_equal(np.asarray(a).view(np.uint32), np.asarray(b).view(np.uint32))
+
+
+def _forces(fx, t):
+    return np.ascontiguousarray(fx.forces[t].transpose(1, 0, 2)), np.ascontiguousarray(fx.torques[t].transpose(1, 0))
+
+
+@pytest.mark.parametrize("name", COVERED)
+def test_compiled_equals_generic_bitwise(name):
+    L = _lib.lib()
+    fx = Fixture(name)
+    pl = StepPlan(fx.desc)
+    assert pl.jit(fx.n_envs)[0] == 1, L.vmasb200_last_error()
+    n, st = fx.n_envs, fx.state0.copy()
+    launches = 0
+    for t in range(min(fx.steps, 30)):
+        fx.apply_overrides(t, st)
+        dyn, stat = pl.pack(st, fx.jrot_at(t))
+        f, tq = _forces(fx, t)
+        a = pl.step_host(dyn, stat, f, tq, exact=False)
+        now = pl.jit(n)[1]
+        assert now > launches, "the step did not take the world-compiled kernel"
+        launches = now
+        prev = L.vmasb200_jit_enable(0)
+        try:
+            b = pl.step_host(dyn, stat, f, tq, exact=False)
+        finally:
+            L.vmasb200_jit_enable(prev)
+        assert pl.jit(n)[1] == launches, "the generic step took the compiled kernel"
+        rows = pl.dyn_rows
+        assert _same(a[0][:rows, :n], b[0][:rows, :n]), f"{name} t={t}: state differs"
+        for k, what in ((1, "clamped actions"), (2, "lidar")):
+            if a[k] is not None or b[k] is not None:
+                assert _same(a[k][:, :n], b[k][:, :n]), f"{name} t={t}: {what} differ"
+        assert _same(a[3], b[3]), f"{name} t={t}: collision masks differ"
+        st = pl.unpack(a[0], st)
+
+
+@pytest.mark.parametrize("name", ["navigation", "simple_spread", "flocking"])
+@pytest.mark.parametrize("n", [1000, 70001])
+def test_compiled_equals_generic_large_batch(name, n):
+    """ragged batch sizes (last tile partly empty, ld padding) and, at 70001 envs, the large-batch CTA shape"""
+    L = _lib.lib()
+    fx = Fixture(name)
+    pl = StepPlan(fx.desc)
+    rng = np.random.default_rng(7)
+    reps = -(-n // fx.n_envs)
+    st = np.tile(fx.state0, (1, reps, 1))[:, :n].copy()
+    st[..., 0:2] += rng.uniform(-0.05, 0.05, st[..., 0:2].shape).astype(np.float32)   # contacts come and go
+    f = np.tile(fx.forces[0], (1, reps, 1))[:, :n]
+    tq = np.tile(fx.torques[0], (1, reps))[:, :n]
+    f, tq = np.ascontiguousarray(f.transpose(1, 0, 2)), np.ascontiguousarray(tq.transpose(1, 0))
+    jr = fx.jrot_at(0)
+    dyn, stat = pl.pack(st, np.tile(jr, (1, reps))[:, :n] if jr is not None and jr.size else None)
+    for _ in range(3):
+        a = pl.step_host(dyn, stat, f, tq, exact=False)
+        assert pl.jit(n)[1] > 0
+        prev = L.vmasb200_jit_enable(0)
+        try:
+            b = pl.step_host(dyn, stat, f, tq, exact=False)
+        finally:
+            L.vmasb200_jit_enable(prev)
+        assert _same(a[0][:pl.dyn_rows, :n], b[0][:pl.dyn_rows, :n]), "state differs"
+        if a[2] is not None:
+            assert _same(a[2][:, :n], b[2][:, :n]), "lidar differs"
+        assert _same(a[3], b[3]), "collision masks differ"
+        dyn = a[0]

@@ -1,0 +1,44 @@
+"""CPU: the world-compiled kernels (csrc/jit.h) compile without a GPU - NVRTC is a compiler, the cubin is only loaded at
+the first launch - for exactly the worlds the generator covers, and the generic kernel stays the path of the others."""
+import os
+
+import pytest
+
+from tests.fixtures import Fixture
+from vectorizedmultiagentsimulator_b200 import _lib
+from vectorizedmultiagentsimulator_b200.plan import StepPlan
+
+HAVE_NVRTC = os.path.exists("/usr/local/cuda/lib64/libnvrtc.so.12")
+COVERED = ["simple_spread", "navigation", "discovery", "flocking", "dropout"]   # sphere-sphere pairs only, no joints
+NOT_COVERED = ["transport", "football", "joint_passage", "wheel", "pollock"]      # boxes / lines / joints
+
+
+@pytest.mark.skipif(not HAVE_NVRTC, reason="no libnvrtc in this image")
+@pytest.mark.parametrize("name", COVERED)
+def test_covered_worlds_compile(name, tmp_path, monkeypatch):
+    monkeypatch.setenv("VMASB200_JIT_CACHE", str(tmp_path))
+    fx = Fixture(name)
+    pl = StepPlan(fx.desc)
+    for n in (fx.n_envs, 1 << 20):  # the two CTA shapes (jit.h jit_tile)
+        state, launches = pl.jit(n)
+        assert state == 1, _lib.lib().vmasb200_last_error()
+        assert launches == 0
+    assert any(f.endswith(".cubin") for f in os.listdir(tmp_path)), "the cubin cache was not written"
+    # a second plan of the same world takes the cached cubin (same source, same hash)
+    assert StepPlan(fx.desc).jit(fx.n_envs)[0] == 1
+
+
+@pytest.mark.parametrize("name", NOT_COVERED)
+def test_other_worlds_keep_the_generic_kernel(name):
+    fx = Fixture(name)
+    assert StepPlan(fx.desc).jit(fx.n_envs) == (0, 0)
+
+
+def test_switch():
+    L = _lib.lib()
+    fx = Fixture("simple_spread")
+    prev = L.vmasb200_jit_enable(0)
+    try:
+        assert StepPlan(fx.desc).jit(fx.n_envs) == (0, 0)
+    finally:
+        L.vmasb200_jit_enable(prev)

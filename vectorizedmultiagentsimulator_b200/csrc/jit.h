@@ -1,0 +1,431 @@
+// jit.h - world-compiled step kernels: host side (included by vmasb200.cu after kernels.cuh; host code only).
+//
+// The generic step kernel (kernels.cuh) INTERPRETS the plan tables: per entity and per pair it reads flags, row
+// indices and constants and branches on them, which ncu showed to be ~10x the instructions of the physics itself for
+// small worlds (profiles/README.md: simple_spread 2200 instructions per env for 3 agents and 3 pairs).  For worlds
+// whose candidate pairs are all sphere-sphere and that have no joints (simple_spread, navigation and most MPE
+// scenarios) the plan is instead COMPILED: `generate()` prints the world as C++ - constants, one literal EntC per
+// entity, straight-line calls per pair in the reference's order - around csrc/spec_helpers.cuh / spec_kernel.cuh,
+// NVRTC compiles it for sm_100a with the parity flags of the library build (--fmad=false), and the cubin is loaded
+// with the driver API and launched on the caller's stream.  The state of an environment then lives in registers for
+// all substeps.  The library's own sources are embedded as text (jit_sources.inc, made by the Makefile), libnvrtc and
+// libcuda are dlopen-ed on first use, cubins are cached on disk next to the library (`_jit/`, or $VMASB200_JIT_CACHE).
+// No NVRTC, an ineligible world, VMASB200_JIT=0 or vmasb200_jit_enable(0): the generic kernel runs (same bits).
+#pragma once
+#include <dlfcn.h>
+#include <sys/stat.h>
+#include <unistd.h>
+
+#include <cmath>
+#include <cstdarg>
+#include <fstream>
+#include <map>
+#include <sstream>
+
+#include "jit_sources.inc"
+
+namespace vb {
+
+// ------------------------------------------------------------------------------------------------ dynamic APIs
+struct NvrtcApi {
+  void* h = nullptr;
+  int (*CreateProgram)(void**, const char*, const char*, int, const char* const*, const char* const*) = nullptr;
+  int (*CompileProgram)(void*, int, const char* const*) = nullptr;
+  int (*GetCUBINSize)(void*, size_t*) = nullptr;
+  int (*GetCUBIN)(void*, char*) = nullptr;
+  int (*GetProgramLogSize)(void*, size_t*) = nullptr;
+  int (*GetProgramLog)(void*, char*) = nullptr;
+  int (*DestroyProgram)(void**) = nullptr;
+  int (*Version)(int*, int*) = nullptr;
+  bool ok = false;
+};
+struct DriverApi {
+  void* h = nullptr;
+  int (*ModuleLoadData)(void**, const void*) = nullptr;
+  int (*ModuleUnload)(void*) = nullptr;
+  int (*ModuleGetFunction)(void**, void*, const char*) = nullptr;
+  int (*ModuleGetGlobal)(unsigned long long*, size_t*, void*, const char*) = nullptr;
+  int (*MemcpyHtoD)(unsigned long long, const void*, size_t) = nullptr;
+  int (*FuncSetAttribute)(void*, int, int) = nullptr;
+  int (*LaunchKernel)(void*, unsigned, unsigned, unsigned, unsigned, unsigned, unsigned, unsigned, void*, void**, void**) = nullptr;
+  bool ok = false;
+};
+static std::mutex g_jit_mu;
+static NvrtcApi g_nvrtc;
+static DriverApi g_drv;
+static int g_jit_on = -1;  // -1: read VMASB200_JIT on first use
+
+template <class F> static bool sym(void* h, const char* name, F& f) {
+  f = reinterpret_cast<F>(dlsym(h, name));
+  return f != nullptr;
+}
+static bool load_nvrtc() {
+  if (g_nvrtc.h) return g_nvrtc.ok;
+  // the toolkit's NVRTC first: same release as the nvcc that built the library (same libdevice math)
+  for (const char* name : {"/usr/local/cuda/lib64/libnvrtc.so.12", "libnvrtc.so.12", "libnvrtc.so"}) {
+    g_nvrtc.h = dlopen(name, RTLD_NOW | RTLD_LOCAL);
+    if (g_nvrtc.h) break;
+  }
+  if (!g_nvrtc.h) { g_nvrtc.h = reinterpret_cast<void*>(1); return false; }
+  NvrtcApi& a = g_nvrtc;
+  a.ok = sym(a.h, "nvrtcCreateProgram", a.CreateProgram) && sym(a.h, "nvrtcCompileProgram", a.CompileProgram) &&
+         sym(a.h, "nvrtcGetCUBINSize", a.GetCUBINSize) && sym(a.h, "nvrtcGetCUBIN", a.GetCUBIN) &&
+         sym(a.h, "nvrtcGetProgramLogSize", a.GetProgramLogSize) && sym(a.h, "nvrtcGetProgramLog", a.GetProgramLog) &&
+         sym(a.h, "nvrtcDestroyProgram", a.DestroyProgram) && sym(a.h, "nvrtcVersion", a.Version);
+  return a.ok;
+}
+static bool load_driver() {
+  if (g_drv.h) return g_drv.ok;
+  g_drv.h = dlopen("libcuda.so.1", RTLD_NOW | RTLD_LOCAL);
+  if (!g_drv.h) { g_drv.h = reinterpret_cast<void*>(1); return false; }
+  DriverApi& d = g_drv;
+  d.ok = sym(d.h, "cuModuleLoadData", d.ModuleLoadData) && sym(d.h, "cuModuleUnload", d.ModuleUnload) &&
+         sym(d.h, "cuModuleGetFunction", d.ModuleGetFunction) && sym(d.h, "cuModuleGetGlobal_v2", d.ModuleGetGlobal) &&
+         sym(d.h, "cuMemcpyHtoD_v2", d.MemcpyHtoD) && sym(d.h, "cuFuncSetAttribute", d.FuncSetAttribute) &&
+         sym(d.h, "cuLaunchKernel", d.LaunchKernel);
+  return d.ok;
+}
+static bool jit_on() {
+  if (g_jit_on < 0) {
+    const char* e = getenv("VMASB200_JIT");
+    g_jit_on = (e && e[0] == '0') ? 0 : 1;
+  }
+  return g_jit_on != 0;
+}
+
+// ------------------------------------------------------------------------------------------------ eligibility
+// Worlds the generator covers: no joints, every candidate pair sphere-sphere (no "thin" contact is possible: the force
+// of a sphere-sphere pair is non-zero exactly where the env's own World.collides verdict is true), LIDAR targets
+// spheres, sizes that keep the unrolled code and the register state small.
+static bool jit_eligible(const vmasb200_plan* pl) {
+  const KParams& kp = pl->kp;
+  if (kp.J != 0 || kp.n_dyn < 1 || kp.n_dyn > 16 || kp.P > 96 || kp.S > 64 || kp.A > 16 || kp.n_sensors > 32) return false;
+  int n_stat_used = 0;
+  for (const DEnt& e : pl->ents) n_stat_used += e.stat_off >= 0;
+  if (n_stat_used > 32) return false;
+  for (int p = 0; p < kp.P; ++p)
+    if (pl->items[kp.J + p].type != IT_SS) return false;
+  for (int t : pl->targets)
+    if (pl->ents[t].shape != VMASB200_SPHERE) return false;
+  return true;
+}
+
+// ------------------------------------------------------------------------------------------------ generator
+static std::string fl(float v) {  // exact fp32 literal
+  char b[64];
+  if (std::isinf(v)) return v > 0 ? "CUDART_INF_F" : "(-CUDART_INF_F)";
+  if (std::isnan(v)) return "CUDART_NAN_F";
+  snprintf(b, sizeof b, "%af", (double)v);
+  return b;
+}
+static void outf(std::string& s, const char* fmt, ...) {
+  char b[1024];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(b, sizeof b, fmt, ap);
+  va_end(ap);
+  s += b;
+}
+
+struct JitLayout {           // the compact LIDAR tile of the compiled kernel (rows of TE floats)
+  std::vector<int> lid_ents;  // entities staged for the epilogue: 3 rows each (px py rot)
+  int work_rows = 0;
+};
+
+// The world of `pl` as C++: prelude constants, then (after spec_helpers.cuh) the world_* functions.
+static std::string generate(const vmasb200_plan* pl, int te, int nt, JitLayout* lay) {
+  const KParams& kp = pl->kp;
+  std::string s;
+  s += "#include \"kernels.cuh\"\nnamespace vb { namespace gen {\n";
+  int n_stat = 0;
+  std::vector<int> stat_slot(pl->ents.size(), -1);
+  for (size_t e = 0; e < pl->ents.size(); ++e)
+    if (pl->ents[e].stat_off >= 0) stat_slot[e] = n_stat++;
+  std::vector<int> dyn_slot(pl->ents.size(), -1);
+  for (int d = 0; d < kp.n_dyn; ++d) dyn_slot[pl->dyn_list[d]] = d;
+  const bool lidar = kp.n_rays > 0;
+  outf(s, "constexpr int TE = %d, NT = %d, ND = %d, NST = %d, NA = %d, S = %d, P = %d, PW = %d;\n", te, nt, kp.n_dyn, n_stat,
+       kp.A, kp.S, kp.P, kp.pair_words);
+  outf(s, "constexpr bool LIDAR = %s, HAS_XS = %s, HAS_YS = %s, HAS_WGRAV = %s;\n", lidar ? "true" : "false",
+       kp.has_xs ? "true" : "false", kp.has_ys ? "true" : "false", kp.has_wgrav ? "true" : "false");
+  outf(s, "constexpr float SUB_DT = %s, KC = %s, MARGIN = %s, XS = %s, YS = %s, WGX = %s, WGY = %s;\n", fl(kp.sub_dt).c_str(),
+       fl(kp.Kc).c_str(), fl(kp.margin).c_str(), fl(kp.xs).c_str(), fl(kp.ys).c_str(), fl(kp.wgx).c_str(), fl(kp.wgy).c_str());
+  s += "} }\n#include \"spec_helpers.cuh\"\nnamespace vb { namespace gen {\n";
+  auto entc = [&](const DEnt& e) {
+    std::string r = "EntC{";
+    outf(r, "0x%xu, %s, %s, %s, %s, %s, %s, %s, %s, %s, %s, %s, %s, %s, %s}", e.flags, fl(e.radius).c_str(), fl(e.mass).c_str(),
+         fl(e.moi).c_str(), fl(e.max_speed).c_str(), fl(e.v_range).c_str(), fl(e.one_minus_drag).c_str(), fl(e.lin_fric).c_str(),
+         fl(e.ang_fric).c_str(), fl(e.gx).c_str(), fl(e.gy).c_str(), fl(e.max_f).c_str(), fl(e.f_range).c_str(),
+         fl(e.max_t).c_str(), fl(e.t_range).c_str());
+    return r;
+  };
+  // ---- load
+  s += "VB_DI void world_load(St& st, const AgentIO& aio, const StepArgs& sa, long long env) {\n";
+  for (int d = 0; d < kp.n_dyn; ++d) {
+    const DEnt& e = pl->ents[pl->dyn_list[d]];
+    const char* f[6] = {"px", "py", "vx", "vy", "rot", "w"};
+    for (int k = 0; k < 6; ++k) outf(s, "  st.%s[%d] = sa.dyn_in[(size_t)%d * sa.ld + env];\n", f[k], d, e.dyn_off + k);
+  }
+  for (size_t e = 0; e < pl->ents.size(); ++e)
+    if (stat_slot[e] >= 0) {
+      const char* f[3] = {"sx", "sy", "srot"};
+      for (int k = 0; k < 3; ++k) outf(s, "  st.%s[%d] = sa.stat[(size_t)%d * sa.ld + env];\n", f[k], stat_slot[e], pl->ents[e].stat_off + k);
+    }
+  for (int a = 0; a < kp.A; ++a) {  // kernels.cuh load_forces
+    outf(s, "  { const float* fp = aio.force[%d]; const float* tp = aio.torque[%d]; float fx = 0.f, fy = 0.f, tq = 0.f;\n", a, a);
+    outf(s, "    if (fp) { fx = fp[env * aio.fstride[%d]]; fy = fp[env * aio.fstride[%d] + 1]; }\n", a, a);
+    outf(s, "    if (tp) tq = tp[env * aio.tstride[%d]];\n    st.fx[%d] = fx; st.fy[%d] = fy; st.tq[%d] = tq; }\n", a, a, a, a);
+  }
+  s += "}\n";
+  // ---- begin / integrate
+  s += "VB_DI void world_begin(St& st) {\n";
+  for (int d = 0; d < kp.n_dyn; ++d) {
+    const DEnt& e = pl->ents[pl->dyn_list[d]];
+    outf(s, "  begin_r<%d, %d>(%s, st);\n", d, e.agent, entc(e).c_str());
+  }
+  s += "}\nVB_DI void world_integrate(St& st, int s, bool more) {\n";
+  for (int d = 0; d < kp.n_dyn; ++d) {
+    const DEnt& e = pl->ents[pl->dyn_list[d]];
+    outf(s, "  integrate_r<%d>(%s, st, s);\n  if (more) begin_r<%d, %d>(%s, st);\n", d, entc(e).c_str(), d, e.agent, entc(e).c_str());
+  }
+  s += "}\n";
+  // ---- pairs
+  auto posx = [&](int e) {
+    std::string r;
+    if (dyn_slot[e] >= 0) outf(r, "mk(st.px[%d], st.py[%d])", dyn_slot[e], dyn_slot[e]);
+    else outf(r, "mk(st.sx[%d], st.sy[%d])", stat_slot[e], stat_slot[e]);
+    return r;
+  };
+  s += "VB_DI void world_pairs(St& st) {\n";
+  for (int p = 0; p < kp.P; ++p) {
+    const DItem& it = pl->items[kp.J + p];
+    const DBroad& b = pl->broad[p];
+    outf(s, "  pair_ss_r<%d, %d, %d, %d, %d>(st, %s, %s, %s, %s, %s, %s);\n", it.acc, dyn_slot[it.a], dyn_slot[it.b], p >> 5, p & 31,
+         posx(it.a).c_str(), posx(it.b).c_str(), fl(b.t2_bp).c_str(), fl(b.t2_cull).c_str(), fl(pl->ents[it.a].radius).c_str(),
+         fl(pl->ents[it.b].radius).c_str());
+  }
+  s += "}\n";
+  // ---- store
+  s += "VB_DI void world_store(const St& st, const StepArgs& sa, long long env) {\n";
+  for (int d = 0; d < kp.n_dyn; ++d) {
+    const DEnt& e = pl->ents[pl->dyn_list[d]];
+    const char* f[6] = {"px", "py", "vx", "vy", "rot", "w"};
+    for (int k = 0; k < 6; ++k) outf(s, "  sa.dyn_out[(size_t)%d * sa.ld + env] = st.%s[%d];\n", e.dyn_off + k, f[k], d);
+    if (e.act_off >= 0 && e.agent >= 0) {
+      const char* g[3] = {"fx", "fy", "tq"};
+      for (int k = 0; k < 3; ++k)
+        outf(s, "  if (sa.act_out) sa.act_out[(size_t)%d * sa.ld + env] = st.%s[%d];\n", e.act_off + k, g[k], e.agent);
+    }
+  }
+  s += "}\n";
+  // ---- LIDAR staging: compact tile, 3 rows (px py rot) per entity the epilogue reads
+  lay->lid_ents.clear();
+  std::vector<int> lid_slot(pl->ents.size(), -1);
+  auto need = [&](int e) {
+    if (lid_slot[e] < 0) { lid_slot[e] = (int)lay->lid_ents.size(); lay->lid_ents.push_back(e); }
+  };
+  for (const DSensor& sn : pl->sensors) {
+    need(sn.entity);
+    for (int q = 0; q < sn.n_targets; ++q) need(pl->targets[sn.tg_begin + q]);
+  }
+  lay->work_rows = kp.n_lmask_words + 2 * kp.n_sensors;
+  s += "VB_DI void world_stage_lidar(const St& st, float* col) {\n";
+  for (size_t k = 0; k < lay->lid_ents.size(); ++k) {
+    const int e = lay->lid_ents[k];
+    if (dyn_slot[e] >= 0)
+      outf(s, "  col[%d * TE] = st.px[%d]; col[%d * TE] = st.py[%d]; col[%d * TE] = st.rot[%d];\n", (int)(3 * k), dyn_slot[e],
+           (int)(3 * k + 1), dyn_slot[e], (int)(3 * k + 2), dyn_slot[e]);
+    else
+      outf(s, "  col[%d * TE] = st.sx[%d]; col[%d * TE] = st.sy[%d]; col[%d * TE] = st.srot[%d];\n", (int)(3 * k), stat_slot[e],
+           (int)(3 * k + 1), stat_slot[e], (int)(3 * k + 2), stat_slot[e]);
+  }
+  s += "}\n} }\n#include \"spec_kernel.cuh\"\n";
+  return s;
+}
+
+// ------------------------------------------------------------------------------------------------ compile + cache
+struct JitKernel {
+  void* module = nullptr;
+  void* func = nullptr;
+  int te = 0, nt = 0, smem_bytes = 0;
+  KParams kp{};  // the epilogue's view: compact tile rows, this plan's device tables
+  bool failed = false;
+};
+struct JitPlanState {
+  std::map<int, JitKernel> by_te;
+  std::map<int, std::string> cubin;  // compiled (or read from the cache) but not yet loaded
+};
+static std::map<const vmasb200_plan*, JitPlanState> g_jit_plans;
+
+static uint64_t fnv1a(const std::string& s, uint64_t h = 1469598103934665603ull) {
+  for (unsigned char c : s) { h ^= c; h *= 1099511628211ull; }
+  return h;
+}
+static std::string cache_dir() {
+  if (const char* e = getenv("VMASB200_JIT_CACHE")) return e;
+  Dl_info info;
+  if (dladdr(reinterpret_cast<void*>(&cache_dir), &info) && info.dli_fname) {
+    std::string p = info.dli_fname;
+    const size_t k = p.rfind('/');
+    return (k == std::string::npos ? std::string(".") : p.substr(0, k)) + "/_jit";
+  }
+  return "_jit";
+}
+
+static const char* kShimStdint =
+    "#pragma once\ntypedef signed char int8_t; typedef unsigned char uint8_t; typedef short int16_t; typedef unsigned short uint16_t;\n"
+    "typedef int int32_t; typedef unsigned int uint32_t; typedef long long int64_t; typedef unsigned long long uint64_t;\n"
+    "typedef unsigned long uintptr_t;\n";
+static const char* kShimMathConst =
+    "#pragma once\n#define CUDART_INF_F __int_as_float(0x7f800000)\n#define CUDART_NAN_F __int_as_float(0x7fffffff)\n";
+
+// cubin of the world-compiled kernel of (pl, te): from the disk cache, else NVRTC.  Empty string + message on failure.
+static std::string jit_compile(const vmasb200_plan* pl, int te, int nt, JitLayout* lay, std::string* err) {
+  const std::string src = generate(pl, te, nt, lay);
+  // -default-device: the C prototypes of include/vmasb200.h carry no execution space
+  const char* opts[] = {"--gpu-architecture=sm_100a", "--std=c++17", "--fmad=false", "-lineinfo", "-default-device"};
+  uint64_t h = fnv1a(src);
+  for (int i = 0; i < kJitNumSources; ++i) h = fnv1a(kJitSrcText[i], h);
+  for (const char* o : opts) h = fnv1a(o, h);
+  char name[64];
+  snprintf(name, sizeof name, "/world_%016llx.cubin", (unsigned long long)h);
+  const std::string dir = cache_dir(), path = dir + name;
+  {
+    std::ifstream f(path, std::ios::binary);
+    if (f) {
+      std::stringstream ss;
+      ss << f.rdbuf();
+      if (ss.str().size() > 64) return ss.str();
+    }
+  }
+  if (!load_nvrtc()) { *err = "libnvrtc.so.12 not found"; return ""; }
+  std::vector<const char*> hn, hs;
+  for (int i = 0; i < kJitNumSources; ++i) { hn.push_back(kJitSrcNames[i]); hs.push_back(kJitSrcText[i]); }
+  hn.push_back("stdint.h"); hs.push_back(kShimStdint);
+  hn.push_back("math_constants.h"); hs.push_back(kShimMathConst);
+  hn.push_back("cuda_runtime.h"); hs.push_back("#pragma once\n");
+  void* prog = nullptr;
+  if (g_nvrtc.CreateProgram(&prog, src.c_str(), "vmasb200_world.cu", (int)hn.size(), hs.data(), hn.data()) != 0) {
+    *err = "nvrtcCreateProgram failed";
+    return "";
+  }
+  const int rc = g_nvrtc.CompileProgram(prog, (int)(sizeof opts / sizeof opts[0]), opts);
+  std::string out;
+  if (rc != 0) {
+    size_t n = 0;
+    g_nvrtc.GetProgramLogSize(prog, &n);
+    std::string log(n, '\0');
+    if (n) g_nvrtc.GetProgramLog(prog, &log[0]);
+    *err = "NVRTC: " + log.substr(0, 1200);
+  } else {
+    size_t n = 0;
+    g_nvrtc.GetCUBINSize(prog, &n);
+    out.resize(n);
+    if (n) g_nvrtc.GetCUBIN(prog, &out[0]);
+  }
+  g_nvrtc.DestroyProgram(&prog);
+  if (!out.empty()) {  // best effort: a read-only tree just recompiles next time
+    mkdir(dir.c_str(), 0755);
+    const std::string tmp = path + ".tmp" + std::to_string((long long)getpid());
+    std::ofstream f(tmp, std::ios::binary);
+    if (f) {
+      f.write(out.data(), (std::streamsize)out.size());
+      f.close();
+      if (rename(tmp.c_str(), path.c_str()) != 0) remove(tmp.c_str());
+    }
+  }
+  return out;
+}
+
+// CTA shape of the compiled kernel for a batch of n envs: one warp of envs per CTA while that fills the GPU in about
+// one wave (shortest critical path), else 128; with LIDAR the CTA always has 128 threads (kernels.cuh kThreads).
+static int jit_tile(const vmasb200_plan* pl, long long n) {
+  if (pl->te_fixed) return pl->te_fixed;
+  if (n <= 48 * 1024) return 32;
+  return pl->kp.n_rays ? 64 : 128;
+}
+
+static void jit_kparams(const vmasb200_plan* pl, int te, const JitLayout& lay, KParams* out) {
+  KParams k = pl->kp;
+  k.TE = te; k.NT = kThreads;
+  k.dyn_rows = 3 * (int)lay.lid_ents.size(); k.stat_rows = 0;
+  k.work_rows = lay.work_rows;
+  k.row_lmask = 0; k.row_strig = pl->kp.n_lmask_words;
+  *out = k;
+}
+
+// The compiled kernel of (pl, tile) ready to launch, or nullptr: not eligible / switched off / no NVRTC / no driver API
+// (reason in *why when given).  compile_only: stop after the cubin exists (no CUDA context needed).
+static JitKernel* jit_get(vmasb200_plan* pl, int te, bool compile_only, std::string* why) {
+  std::lock_guard<std::mutex> lock(g_jit_mu);
+  auto say = [&](const std::string& m) { if (why) *why = m; return (JitKernel*)nullptr; };
+  if (!jit_on()) return say("switched off (VMASB200_JIT=0 / vmasb200_jit_enable(0))");
+  if (!jit_eligible(pl)) return say("world not covered by the generator (joints or non-sphere pairs / LIDAR targets)");
+  JitPlanState& ps = g_jit_plans[pl];
+  JitKernel& jk = ps.by_te[te];
+  if (jk.failed) return say("an earlier attempt failed");
+  if (jk.func) return &jk;
+  const bool lidar = pl->kp.n_rays > 0;
+  const int nt = lidar ? kThreads : te;
+  JitLayout lay;
+  std::string err;
+  std::string& cubin = ps.cubin[te];
+  if (cubin.empty()) cubin = jit_compile(pl, te, nt, &lay, &err);
+  else generate(pl, te, nt, &lay);
+  if (cubin.empty()) {
+    jk.failed = true;
+    fprintf(stderr, "libvmasb200: world-compiled kernel unavailable, using the generic kernel (%s)\n", err.c_str());
+    return say(err);
+  }
+  jk.te = te; jk.nt = nt;
+  if (compile_only) return say("compiled");
+  if (!load_driver()) { jk.failed = true; return say("libcuda.so.1 not found"); }
+  jit_kparams(pl, te, lay, &jk.kp);
+  jk.smem_bytes = lidar ? smem_map(jk.kp).total_bytes : 0;
+  auto fail = [&](const char* what, int rc) {
+    jk.failed = true;
+    if (jk.module) { g_drv.ModuleUnload(jk.module); jk.module = nullptr; }
+    fprintf(stderr, "libvmasb200: world-compiled kernel unavailable, using the generic kernel (%s: CUresult %d)\n", what, rc);
+    return say(what);
+  };
+  int rc;
+  if ((rc = g_drv.ModuleLoadData(&jk.module, cubin.data()))) return fail("cuModuleLoadData", rc);
+  void* fn = nullptr;
+  if ((rc = g_drv.ModuleGetFunction(&fn, jk.module, "vmasb200_step_world"))) return fail("cuModuleGetFunction", rc);
+  if (lidar) {
+    // this module's own constant bank: the epilogue's tables with the compact tile's rows; uploaded once, never shared
+    std::unique_ptr<CTab> t(new CTab());
+    std::memset(t.get(), 0, sizeof(CTab));
+    std::copy(pl->ents.begin(), pl->ents.end(), t->ents);
+    std::copy(pl->sensors.begin(), pl->sensors.end(), t->sensors);
+    for (size_t e = 0; e < pl->ents.size(); ++e) { t->ents[e].pos_row = -1; t->ents[e].rot_row = -1; t->ents[e].trig_row = -1; }
+    for (size_t k = 0; k < lay.lid_ents.size(); ++k) {
+      t->ents[lay.lid_ents[k]].pos_row = 3 * (int)k;
+      t->ents[lay.lid_ents[k]].rot_row = 3 * (int)k + 2;
+    }
+    for (size_t k = 0; k < pl->sensors.size(); ++k) t->sensors[k].tw_off = pl->sensors[k].tw_off - pl->kp.row_lmask;
+    unsigned long long dptr = 0;
+    size_t bytes = 0;
+    if ((rc = g_drv.ModuleGetGlobal(&dptr, &bytes, jk.module, "_ZN2vb5c_tabE"))) return fail("cuModuleGetGlobal(c_tab)", rc);
+    if (bytes != sizeof(CTab)) return fail("c_tab size mismatch", (int)bytes);
+    if ((rc = g_drv.MemcpyHtoD(dptr, t.get(), sizeof(CTab)))) return fail("cuMemcpyHtoD(c_tab)", rc);
+    if (jk.smem_bytes > 48 * 1024 &&
+        (rc = g_drv.FuncSetAttribute(fn, 8 /* CU_FUNC_ATTRIBUTE_MAX_DYNAMIC_SHARED_SIZE_BYTES */, jk.smem_bytes)))
+      return fail("cuFuncSetAttribute", rc);
+  }
+  jk.func = fn;
+  cubin.clear();
+  cubin.shrink_to_fit();
+  return &jk;
+}
+
+static void jit_forget(const vmasb200_plan* pl) {
+  std::lock_guard<std::mutex> lock(g_jit_mu);
+  auto it = g_jit_plans.find(pl);
+  if (it == g_jit_plans.end()) return;
+  for (auto& kv : it->second.by_te)
+    if (kv.second.module && g_drv.ok) g_drv.ModuleUnload(kv.second.module);
+  g_jit_plans.erase(it);
+}
+
+}  // namespace vb

@@ -12,6 +12,7 @@
 #include "queries.cuh"
 #include "hooks.cuh"
 #include "plan.h"
+#include "jit.h"
 
 namespace vb {
 const char* last_error();
@@ -200,6 +201,23 @@ static int launch_step(vmasb200_plan* pl, const vmasb200_step_io* io, long long 
   sa.env_begin = env_begin; sa.env_end = env_end; sa.total_ctas = (int)total_ctas;
   sa.flags_out = flags; sa.any_exact = flags + bw; sa.any_spec = flags + 2 * bw; sa.thin = flags + 3 * bw;
   sa.counters = reinterpret_cast<int*>(flags + 4 * bw);
+  if (!io->exact) {
+    // world-compiled kernel (jit.h) when the plan has one: same scratch protocol, same bits, no constant-bank upload
+    const int jte = jit_tile(pl, io->n_envs);
+    if (JitKernel* jk = jit_get(pl, jte, false, nullptr)) {
+      if (env_begin % jte) { set_error("step: chunk boundary is not a multiple of the compiled kernel's tile"); return VMASB200_ERR_INVALID; }
+      sa.total_ctas = (int)((io->n_envs + jte - 1) / jte);
+      sa.s_begin = 0; sa.s_end = kp.S; sa.flags_in = nullptr; sa.do_lidar = 1;
+      KParams jkp = jk->kp;
+      void* args[3] = {&jkp, &aio, &sa};
+      const unsigned jgrid = (unsigned)((env_end - env_begin + jte - 1) / jte);
+      const int rc = g_drv.LaunchKernel(jk->func, jgrid, 1, 1, (unsigned)jk->nt, 1, 1, (unsigned)jk->smem_bytes, st, args, nullptr);
+      if (rc) { set_error("cuLaunchKernel(vmasb200_step_world) failed: CUresult " + std::to_string(rc)); return VMASB200_ERR_CUDA; }
+      pl->jit_launches += 1;
+      if (io->pair_active_out && nw) VB_CUDA(cudaMemcpyAsync(io->pair_active_out, flags, nw * sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
+      return VMASB200_OK;
+    }
+  }
   const unsigned grid = (unsigned)((env_end - env_begin + kp.TE - 1) / kp.TE);
   const unsigned block = (unsigned)kp.NT;
   bool ct = false;
@@ -265,6 +283,7 @@ int vmasb200_plan_create(const vmasb200_world_desc* desc, vmasb200_plan** out) {
 
 int vmasb200_plan_destroy(vmasb200_plan* pl) {
   if (!pl) return VMASB200_OK;
+  jit_forget(pl);
   {
     std::lock_guard<std::mutex> lock(g_const_mu);
     for (ConstOwner& o : g_const) if (o.plan == pl) o.plan = nullptr;
@@ -311,7 +330,40 @@ int vmasb200_plan_lidar_slots(const vmasb200_plan* pl, int32_t* lidar_slot) {
   return VMASB200_OK;
 }
 
-int vmasb200_plan_tile(const vmasb200_plan* pl, int64_t n_envs) { return pl ? tile_for(pl, n_envs) : 0; }
+int vmasb200_plan_tile(const vmasb200_plan* pl, int64_t n_envs) {
+  if (!pl) return 0;
+  {
+    std::lock_guard<std::mutex> lock(g_jit_mu);
+    auto it = g_jit_plans.find(pl);
+    if (jit_on() && it != g_jit_plans.end()) {
+      auto k = it->second.by_te.find(jit_tile(pl, n_envs));
+      if (k != it->second.by_te.end() && k->second.func) return k->first;
+    }
+  }
+  return tile_for(pl, n_envs);
+}
+
+int vmasb200_jit_enable(int on) {
+  std::lock_guard<std::mutex> lock(g_jit_mu);
+  const int prev = jit_on() ? 1 : 0;
+  g_jit_on = on ? 1 : 0;
+  return prev;
+}
+
+int vmasb200_plan_jit(vmasb200_plan* pl, int64_t n_envs, int32_t* state, int64_t* launches) {
+  if (!pl) { set_error("plan_jit: NULL plan"); return VMASB200_ERR_INVALID; }
+  std::string why;
+  int st = 0;
+  if (!jit_on() || !jit_eligible(pl)) st = 0;
+  else {
+    jit_get(pl, jit_tile(pl, n_envs), true, &why);
+    st = why == "compiled" ? 1 : -1;
+    if (st < 0) set_error("plan_jit: " + why);
+  }
+  if (state) *state = st;
+  if (launches) *launches = pl->jit_launches;
+  return VMASB200_OK;
+}
 
 int vmasb200_step(vmasb200_plan* pl, const vmasb200_step_io* io) {
   if (!pl) { set_error("step: NULL plan"); return VMASB200_ERR_INVALID; }
