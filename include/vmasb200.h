@@ -184,14 +184,15 @@ int vmasb200_plan_lidar_slots(const vmasb200_plan* plan, int32_t* lidar_slot);
  * or, when that is 0, chosen from the batch size.  128 / tile threads share each environment's work. */
 int vmasb200_plan_tile(const vmasb200_plan* plan, int64_t n_envs);
 
-/* World-compiled step kernels.  For worlds without joints whose candidate pairs are all sphere-sphere (simple_spread,
- * navigation, most MPE scenarios) the library prints the plan as C++ with the world's constants, entity attributes
+/* World-compiled step kernels.  For small worlds (simple_spread, navigation, transport, most MPE scenarios) the library prints the plan as C++ with the world's constants, entity attributes
  * and pair list as literals, compiles it with NVRTC for sm_100a (same parity flags as the library build) and launches
  * that instead of the generic table-walking kernel: an environment's state then stays in registers for all substeps.
  * Results are bit-identical to the generic kernel.  Cubins are cached in `_jit/` beside the library (or
  * $VMASB200_JIT_CACHE).  Without libnvrtc / libcuda, for other worlds, with VMASB200_JIT=0 in the environment or after
  * vmasb200_jit_enable(0) the generic kernel runs.
- *  vmasb200_jit_enable: process-wide switch, returns the previous setting.
+ *  vmasb200_jit_enable: process-wide switch, returns the previous setting.  0 off; 1 (default) worlds the compiled
+ *  kernel is measured to win on: all pairs sphere-sphere, or at most 32 candidate pairs and 2 joints; 2 (also
+ *  VMASB200_JIT=2) every world the generator covers, whatever its size (tests).
  *  vmasb200_plan_jit: compiles (no GPU needed) the kernel a step over n_envs would take.  *state: 1 compiled / cached,
  *  0 the world is not covered or the switch is off, -1 compilation failed (vmasb200_last_error says why).
  *  *launches: launches of this plan that took a compiled kernel so far.  Either out pointer may be NULL. */

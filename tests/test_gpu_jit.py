@@ -6,12 +6,22 @@ them when the world has one)."""
 import numpy as np
 import pytest
 
-from tests.fixtures import Fixture
+from tests.fixtures import Fixture, names
 from vectorizedmultiagentsimulator_b200 import _lib
 from vectorizedmultiagentsimulator_b200.plan import StepPlan
 
 pytestmark = pytest.mark.gpu
-COVERED = ["simple_spread", "navigation", "discovery", "flocking", "dropout"]
+
+
+@pytest.fixture(autouse=True)
+def _every_covered_world():
+    """mode 2: also the worlds the library would leave to the generic kernel for speed (football, joint_passage)"""
+    L = _lib.lib()
+    prev = L.vmasb200_jit_enable(2)
+    yield
+    L.vmasb200_jit_enable(prev)
+
+COVERED = [n for n in names() if n != "pollock"]  # pollock: 990 pairs, beyond what the generator unrolls
 
 
 def _same(a, b):
@@ -40,11 +50,11 @@ def test_compiled_equals_generic_bitwise(name):
         now = pl.jit(n)[1]
         assert now > launches, "the step did not take the world-compiled kernel"
         launches = now
-        prev = L.vmasb200_jit_enable(0)
+        L.vmasb200_jit_enable(0)
         try:
             b = pl.step_host(dyn, stat, f, tq, exact=False)
         finally:
-            L.vmasb200_jit_enable(prev)
+            L.vmasb200_jit_enable(2)
         assert pl.jit(n)[1] == launches, "the generic step took the compiled kernel"
         rows = pl.dyn_rows
         assert _same(a[0][:rows, :n], b[0][:rows, :n]), f"{name} t={t}: state differs"
@@ -55,7 +65,7 @@ def test_compiled_equals_generic_bitwise(name):
         st = pl.unpack(a[0], st)
 
 
-@pytest.mark.parametrize("name", ["navigation", "simple_spread", "flocking"])
+@pytest.mark.parametrize("name", ["navigation", "simple_spread", "flocking", "transport", "football", "joint_passage", "wheel"])
 @pytest.mark.parametrize("n", [1000, 70001])
 def test_compiled_equals_generic_large_batch(name, n):
     """ragged batch sizes (last tile partly empty, ld padding) and, at 70001 envs, the large-batch CTA shape"""
@@ -74,13 +84,46 @@ def test_compiled_equals_generic_large_batch(name, n):
     for _ in range(3):
         a = pl.step_host(dyn, stat, f, tq, exact=False)
         assert pl.jit(n)[1] > 0
-        prev = L.vmasb200_jit_enable(0)
+        L.vmasb200_jit_enable(0)
         try:
             b = pl.step_host(dyn, stat, f, tq, exact=False)
         finally:
-            L.vmasb200_jit_enable(prev)
+            L.vmasb200_jit_enable(2)
         assert _same(a[0][:pl.dyn_rows, :n], b[0][:pl.dyn_rows, :n]), "state differs"
         if a[2] is not None:
             assert _same(a[2][:, :n], b[2][:, :n]), "lidar differs"
         assert _same(a[3], b[3]), "collision masks differ"
         dyn = a[0]
+
+
+def test_compiled_launch_reaches_the_repair():
+    """joint_passage at a few thousand envs has thin contacts at the ends of the passage's wall segments whose pair no
+    exact env activates: the compiled launch must hand over to kernels.cuh repair_kernel, and the result must still be
+    the generic kernel's, bit for bit."""
+    L = _lib.lib()
+    fx = Fixture("joint_passage")
+    pl = StepPlan(fx.desc)
+    n = 8192
+    reps = -(-n // fx.n_envs)
+    rng = np.random.default_rng(3)
+    st = np.tile(fx.state0, (1, reps, 1))[:, :n].copy()
+    dynamic = [e for e in range(st.shape[0]) if pl.dyn_slot[e] >= 0]
+    st[dynamic, :, 0:2] += rng.uniform(-0.02, 0.02, st[dynamic, :, 0:2].shape).astype(np.float32)
+    jr = fx.jrot_at(0)
+    dyn, stat = pl.pack(st, np.tile(jr, (1, reps))[:, :n] if jr is not None and jr.size else None)
+    A = len(pl.agents)
+    repairs0 = pl.sync_check()
+    for t in range(40):
+        f = rng.uniform(-1, 1, (n, A, 2)).astype(np.float32)
+        tq = np.zeros((n, A), np.float32)
+        a = pl.step_host(dyn, stat, f, tq, exact=False)
+        L.vmasb200_jit_enable(0)
+        try:
+            b = pl.step_host(dyn, stat, f, tq, exact=False)
+        finally:
+            L.vmasb200_jit_enable(2)
+        assert _same(a[0][:pl.dyn_rows, :n], b[0][:pl.dyn_rows, :n]), f"t={t}: state differs"
+        assert _same(a[3], b[3]), f"t={t}: collision masks differ"
+        dyn = a[0]
+    assert pl.jit(n)[1] > 0
+    assert pl.sync_check() > repairs0, "no step needed a repair: the test does not exercise the hand-over"

@@ -9,8 +9,9 @@ from vectorizedmultiagentsimulator_b200 import _lib
 from vectorizedmultiagentsimulator_b200.plan import StepPlan
 
 HAVE_NVRTC = os.path.exists("/usr/local/cuda/lib64/libnvrtc.so.12")
-COVERED = ["simple_spread", "navigation", "discovery", "flocking", "dropout"]   # sphere-sphere pairs only, no joints
-NOT_COVERED = ["transport", "football", "joint_passage", "wheel", "pollock"]      # boxes / lines / joints
+COVERED = ["simple_spread", "navigation", "transport", "flocking", "wheel", "dropout"]  # short or all-sphere pair lists
+NOT_COVERED = ["football", "joint_passage", "pollock"]  # many box / line pairs: the generic kernel's teams win (jit.h)
+FORCED = ["football", "joint_passage"]                  # ... but the generator covers them (mode 2, used by the GPU tests)
 
 
 @pytest.mark.skipif(not HAVE_NVRTC, reason="no libnvrtc in this image")
@@ -40,5 +41,18 @@ def test_switch():
     prev = L.vmasb200_jit_enable(0)
     try:
         assert StepPlan(fx.desc).jit(fx.n_envs) == (0, 0)
+    finally:
+        L.vmasb200_jit_enable(prev)
+
+
+@pytest.mark.skipif(not HAVE_NVRTC, reason="no libnvrtc in this image")
+@pytest.mark.parametrize("name", FORCED)
+def test_mode_2_compiles_every_covered_world(name, tmp_path, monkeypatch):
+    monkeypatch.setenv("VMASB200_JIT_CACHE", str(tmp_path))
+    L = _lib.lib()
+    fx = Fixture(name)
+    prev = L.vmasb200_jit_enable(2)
+    try:
+        assert StepPlan(fx.desc).jit(fx.n_envs)[0] == 1, L.vmasb200_last_error()
     finally:
         L.vmasb200_jit_enable(prev)

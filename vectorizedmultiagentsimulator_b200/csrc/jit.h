@@ -85,29 +85,32 @@ static bool load_driver() {
          sym(d.h, "cuLaunchKernel", d.LaunchKernel);
   return d.ok;
 }
-static bool jit_on() {
+static int jit_mode() {  // 0 off, 1 worlds the compiled kernel is measured to win on, 2 every world the generator covers
   if (g_jit_on < 0) {
     const char* e = getenv("VMASB200_JIT");
-    g_jit_on = (e && e[0] == '0') ? 0 : 1;
+    g_jit_on = (e && e[0] == '0') ? 0 : (e && e[0] == '2') ? 2 : 1;
   }
-  return g_jit_on != 0;
+  return g_jit_on;
 }
+static bool jit_on() { return jit_mode() != 0; }
 
 // ------------------------------------------------------------------------------------------------ eligibility
-// Worlds the generator covers: no joints, every candidate pair sphere-sphere (no "thin" contact is possible: the force
-// of a sphere-sphere pair is non-zero exactly where the env's own World.collides verdict is true), LIDAR targets
-// spheres, sizes that keep the unrolled code and the register state small.
+// Worlds the generator covers: every item type, within sizes that keep the unrolled code and the register state small.
 static bool jit_eligible(const vmasb200_plan* pl) {
   const KParams& kp = pl->kp;
-  if (kp.J != 0 || kp.n_dyn < 1 || kp.n_dyn > 16 || kp.P > 96 || kp.S > 64 || kp.A > 16 || kp.n_sensors > 32) return false;
+  if (kp.n_dyn < 1 || kp.n_dyn > 16 || kp.P > 128 || kp.J > 16 || kp.S > 64 || kp.A > 16 || kp.n_sensors > 32 || kp.n_trig > 48)
+    return false;
   int n_stat_used = 0;
   for (const DEnt& e : pl->ents) n_stat_used += e.stat_off >= 0;
-  if (n_stat_used > 32) return false;
-  for (int p = 0; p < kp.P; ++p)
-    if (pl->items[kp.J + p].type != IT_SS) return false;
-  for (int t : pl->targets)
-    if (pl->ents[t].shape != VMASB200_SPHERE) return false;
-  return true;
+  if (n_stat_used > 48) return false;
+  if (jit_mode() >= 2) return true;
+  // Measured on B200 (profiles/README.md): one thread per env wins while the pair list is short or all sphere-sphere
+  // (simple_spread 3.4x, transport 2.7x, navigation 2.3x at 1 M envs); with many box / line pairs whose contacts hit
+  // different pairs in different lanes the generic kernel's teams win (football 91 pairs: equal at 1 M, 0.8x at 32 K;
+  // joint_passage 54 pairs + 3 joints, 10 substeps: 0.7x), so those keep the generic kernel.
+  bool all_ss = kp.J == 0;
+  for (int p = 0; p < kp.P && all_ss; ++p) all_ss = pl->items[kp.J + p].type == IT_SS;
+  return all_ss || (kp.P <= 32 && kp.J <= 2);
 }
 
 // ------------------------------------------------------------------------------------------------ generator
@@ -119,7 +122,7 @@ static std::string fl(float v) {  // exact fp32 literal
   return b;
 }
 static void outf(std::string& s, const char* fmt, ...) {
-  char b[1024];
+  char b[2048];
   va_list ap;
   va_start(ap, fmt);
   vsnprintf(b, sizeof b, fmt, ap);
@@ -127,9 +130,11 @@ static void outf(std::string& s, const char* fmt, ...) {
   s += b;
 }
 
-struct JitLayout {           // the compact LIDAR tile of the compiled kernel (rows of TE floats)
-  std::vector<int> lid_ents;  // entities staged for the epilogue: 3 rows each (px py rot)
+struct JitLayout {            // the compact LIDAR tile of the compiled kernel (rows of TE floats)
+  std::vector<int> lid_ents;  // entities staged for the epilogue: 3 env rows each (px py rot)
+  std::vector<int> lid_trig;  // of those, the non-sphere targets: 4 work rows each (cos/sin cache)
   int work_rows = 0;
+  bool thin_possible = false;
 };
 
 // The world of `pl` as C++: prelude constants, then (after spec_helpers.cuh) the world_* functions.
@@ -137,26 +142,58 @@ static std::string generate(const vmasb200_plan* pl, int te, int nt, JitLayout* 
   const KParams& kp = pl->kp;
   std::string s;
   s += "#include \"kernels.cuh\"\nnamespace vb { namespace gen {\n";
-  int n_stat = 0;
-  std::vector<int> stat_slot(pl->ents.size(), -1);
-  for (size_t e = 0; e < pl->ents.size(); ++e)
+  int n_stat = 0, n_jf = 0;
+  const size_t E = pl->ents.size();
+  std::vector<int> stat_slot(E, -1), dyn_slot(E, -1), trig_slot(E, -1);
+  for (size_t e = 0; e < E; ++e)
     if (pl->ents[e].stat_off >= 0) stat_slot[e] = n_stat++;
-  std::vector<int> dyn_slot(pl->ents.size(), -1);
   for (int d = 0; d < kp.n_dyn; ++d) dyn_slot[pl->dyn_list[d]] = d;
+  for (int t = 0; t < kp.n_trig; ++t) trig_slot[pl->trig_list[t]] = t;
+  std::vector<int> jf_slot((size_t)kp.J, -1);
+  for (int j = 0; j < kp.J; ++j)
+    if (pl->items[j].fr_row >= 0) jf_slot[j] = n_jf++;
   const bool lidar = kp.n_rays > 0;
-  outf(s, "constexpr int TE = %d, NT = %d, ND = %d, NST = %d, NA = %d, S = %d, P = %d, PW = %d;\n", te, nt, kp.n_dyn, n_stat,
-       kp.A, kp.S, kp.P, kp.pair_words);
-  outf(s, "constexpr bool LIDAR = %s, HAS_XS = %s, HAS_YS = %s, HAS_WGRAV = %s;\n", lidar ? "true" : "false",
-       kp.has_xs ? "true" : "false", kp.has_ys ? "true" : "false", kp.has_wgrav ? "true" : "false");
-  outf(s, "constexpr float SUB_DT = %s, KC = %s, MARGIN = %s, XS = %s, YS = %s, WGX = %s, WGY = %s;\n", fl(kp.sub_dt).c_str(),
-       fl(kp.Kc).c_str(), fl(kp.margin).c_str(), fl(kp.xs).c_str(), fl(kp.ys).c_str(), fl(kp.wgx).c_str(), fl(kp.wgy).c_str());
+  bool thin_possible = false;
+  std::vector<char> thin((size_t)kp.P, 1);
+  for (int p = 0; p < kp.P; ++p) {
+    const DItem& it = pl->items[kp.J + p];
+    // a sphere-sphere force is non-zero only within fp32(r_a + r_b); no thin event when the verdict's threshold covers it
+    if (it.type == IT_SS && pl->ents[it.a].radius + pl->ents[it.b].radius <= it.thr) thin[p] = 0;
+    thin_possible = thin_possible || thin[p];
+  }
+  lay->thin_possible = thin_possible;
+  outf(s, "constexpr int TE = %d, NT = %d, ND = %d, NST = %d, NA = %d, NTR = %d, NJF = %d, S = %d, P = %d, PW = %d, DYN_ROWS = %d;\n",
+       te, nt, kp.n_dyn, n_stat, kp.A, kp.n_trig, n_jf, kp.S, kp.P, kp.pair_words, kp.dyn_rows);
+  outf(s, "constexpr bool LIDAR = %s, HAS_XS = %s, HAS_YS = %s, HAS_WGRAV = %s, THIN_POSSIBLE = %s;\n", lidar ? "true" : "false",
+       kp.has_xs ? "true" : "false", kp.has_ys ? "true" : "false", kp.has_wgrav ? "true" : "false", thin_possible ? "true" : "false");
+  outf(s, "constexpr float SUB_DT = %s, KC = %s, KJ = %s, KT = %s, MARGIN = %s, XS = %s, YS = %s, WGX = %s, WGY = %s;\n",
+       fl(kp.sub_dt).c_str(), fl(kp.Kc).c_str(), fl(kp.Kj).c_str(), fl(kp.Kt).c_str(), fl(kp.margin).c_str(), fl(kp.xs).c_str(),
+       fl(kp.ys).c_str(), fl(kp.wgx).c_str(), fl(kp.wgy).c_str());
   s += "} }\n#include \"spec_helpers.cuh\"\nnamespace vb { namespace gen {\n";
-  auto entc = [&](const DEnt& e) {
-    std::string r = "EntC{";
-    outf(r, "0x%xu, %s, %s, %s, %s, %s, %s, %s, %s, %s, %s, %s, %s, %s, %s}", e.flags, fl(e.radius).c_str(), fl(e.mass).c_str(),
-         fl(e.moi).c_str(), fl(e.max_speed).c_str(), fl(e.v_range).c_str(), fl(e.one_minus_drag).c_str(), fl(e.lin_fric).c_str(),
-         fl(e.ang_fric).c_str(), fl(e.gx).c_str(), fl(e.gy).c_str(), fl(e.max_f).c_str(), fl(e.f_range).c_str(),
-         fl(e.max_t).c_str(), fl(e.t_range).c_str());
+  for (size_t e = 0; e < E; ++e) {  // one literal per entity (constant-folded after inlining)
+    const DEnt& d = pl->ents[e];
+    outf(s, "#define VBE%d EntC{%d, 0x%xu, %s, %s, %s, %s, %s, %s, %s, %s, %s, %s, %s, %s, %s, %s, %s, %s}\n", (int)e, d.shape, d.flags,
+         fl(d.radius).c_str(), fl(d.length).c_str(), fl(d.width).c_str(), fl(d.mass).c_str(), fl(d.moi).c_str(),
+         fl(d.max_speed).c_str(), fl(d.v_range).c_str(), fl(d.one_minus_drag).c_str(), fl(d.lin_fric).c_str(),
+         fl(d.ang_fric).c_str(), fl(d.gx).c_str(), fl(d.gy).c_str(), fl(d.max_f).c_str(), fl(d.f_range).c_str(),
+         fl(d.max_t).c_str(), fl(d.t_range).c_str());
+  }
+  auto posx = [&](int e) {
+    std::string r;
+    if (dyn_slot[e] >= 0) outf(r, "mk(st.px[%d], st.py[%d])", dyn_slot[e], dyn_slot[e]);
+    else outf(r, "mk(st.sx[%d], st.sy[%d])", stat_slot[e], stat_slot[e]);
+    return r;
+  };
+  auto rotx = [&](int e) {
+    std::string r;
+    if (dyn_slot[e] >= 0) outf(r, "st.rot[%d]", dyn_slot[e]);
+    else if (stat_slot[e] >= 0) outf(r, "st.srot[%d]", stat_slot[e]);
+    else r = "0.f";
+    return r;
+  };
+  auto trigx = [&](int e) {
+    std::string r;
+    outf(r, "rot_r<%d>(st)", trig_slot[e]);
     return r;
   };
   // ---- load
@@ -166,43 +203,54 @@ static std::string generate(const vmasb200_plan* pl, int te, int nt, JitLayout* 
     const char* f[6] = {"px", "py", "vx", "vy", "rot", "w"};
     for (int k = 0; k < 6; ++k) outf(s, "  st.%s[%d] = sa.dyn_in[(size_t)%d * sa.ld + env];\n", f[k], d, e.dyn_off + k);
   }
-  for (size_t e = 0; e < pl->ents.size(); ++e)
+  for (size_t e = 0; e < E; ++e)
     if (stat_slot[e] >= 0) {
       const char* f[3] = {"sx", "sy", "srot"};
       for (int k = 0; k < 3; ++k) outf(s, "  st.%s[%d] = sa.stat[(size_t)%d * sa.ld + env];\n", f[k], stat_slot[e], pl->ents[e].stat_off + k);
     }
+  for (int j = 0; j < kp.J; ++j)
+    if (jf_slot[j] >= 0) outf(s, "  st.jfr[%d] = sa.stat[(size_t)%d * sa.ld + env];\n", jf_slot[j], pl->items[j].fr_row - kp.dyn_rows);
   for (int a = 0; a < kp.A; ++a) {  // kernels.cuh load_forces
     outf(s, "  { const float* fp = aio.force[%d]; const float* tp = aio.torque[%d]; float fx = 0.f, fy = 0.f, tq = 0.f;\n", a, a);
     outf(s, "    if (fp) { fx = fp[env * aio.fstride[%d]]; fy = fp[env * aio.fstride[%d] + 1]; }\n", a, a);
     outf(s, "    if (tp) tq = tp[env * aio.tstride[%d]];\n    st.fx[%d] = fx; st.fy[%d] = fy; st.tq[%d] = tq; }\n", a, a, a, a);
   }
   s += "}\n";
-  // ---- begin / integrate
+  // ---- prologue (cos/sin cache, first accumulators) / integrate
   s += "VB_DI void world_begin(St& st) {\n";
+  for (int t = 0; t < kp.n_trig; ++t) {
+    const int e = pl->trig_list[t];
+    outf(s, "  trig_r<%d, %d>(st, %s);\n", t, pl->ents[e].shape == VMASB200_BOX ? VMASB200_BOX : VMASB200_SPHERE, rotx(e).c_str());
+  }
   for (int d = 0; d < kp.n_dyn; ++d) {
-    const DEnt& e = pl->ents[pl->dyn_list[d]];
-    outf(s, "  begin_r<%d, %d>(%s, st);\n", d, e.agent, entc(e).c_str());
+    const int e = pl->dyn_list[d];
+    outf(s, "  begin_r<%d, %d>(VBE%d, st);\n", d, pl->ents[e].agent, e);
   }
   s += "}\nVB_DI void world_integrate(St& st, int s, bool more) {\n";
   for (int d = 0; d < kp.n_dyn; ++d) {
-    const DEnt& e = pl->ents[pl->dyn_list[d]];
-    outf(s, "  integrate_r<%d>(%s, st, s);\n  if (more) begin_r<%d, %d>(%s, st);\n", d, entc(e).c_str(), d, e.agent, entc(e).c_str());
+    const int e = pl->dyn_list[d];
+    const bool box = pl->ents[e].shape == VMASB200_BOX && trig_slot[e] >= 0;
+    outf(s, "  %s<%d, %d>(VBE%d, st, s);\n  if (more) begin_r<%d, %d>(VBE%d, st);\n", box ? "integrate_box_r" : "integrate_r", d,
+         trig_slot[e], e, d, pl->ents[e].agent, e);
   }
   s += "}\n";
-  // ---- pairs
-  auto posx = [&](int e) {
-    std::string r;
-    if (dyn_slot[e] >= 0) outf(r, "mk(st.px[%d], st.py[%d])", dyn_slot[e], dyn_slot[e]);
-    else outf(r, "mk(st.sx[%d], st.sy[%d])", stat_slot[e], stat_slot[e]);
-    return r;
-  };
-  s += "VB_DI void world_pairs(St& st) {\n";
+  // ---- joints, then pairs
+  s += "VB_DI void world_items(St& st) {\n";
+  for (int j = 0; j < kp.J; ++j) {
+    const DItem& it = pl->items[j];
+    outf(s, "  joint_r<%d, %d, %d, %d>(st, JointC{%s, %s, %s, %s, %s, %s, %d}, %s, %s, %s, %s, %s, %s);\n", it.acc, dyn_slot[it.a],
+         dyn_slot[it.b], jf_slot[j], fl(it.dax).c_str(), fl(it.day).c_str(), fl(it.dbx).c_str(), fl(it.dby).c_str(),
+         fl(it.dist).c_str(), fl(it.fixed_rot).c_str(), it.rotate, posx(it.a).c_str(), posx(it.b).c_str(), trigx(it.a).c_str(),
+         trigx(it.b).c_str(), rotx(it.a).c_str(), rotx(it.b).c_str());
+  }
   for (int p = 0; p < kp.P; ++p) {
     const DItem& it = pl->items[kp.J + p];
     const DBroad& b = pl->broad[p];
-    outf(s, "  pair_ss_r<%d, %d, %d, %d, %d>(st, %s, %s, %s, %s, %s, %s);\n", it.acc, dyn_slot[it.a], dyn_slot[it.b], p >> 5, p & 31,
-         posx(it.a).c_str(), posx(it.b).c_str(), fl(b.t2_bp).c_str(), fl(b.t2_cull).c_str(), fl(pl->ents[it.a].radius).c_str(),
-         fl(pl->ents[it.b].radius).c_str());
+    const bool frame = !std::isinf(b.hx) || !std::isinf(b.hy);
+    outf(s, "  pair_r<%d, %d, %d, %d, %d, %d, %s, %s>(st, VBE%d, VBE%d, %s, %s, %s, %s, %s, %s, %s, %s);\n", it.type, it.acc,
+         dyn_slot[it.a], dyn_slot[it.b], p >> 5, p & 31, frame ? "true" : "false", thin[p] ? "true" : "false", it.a, it.b,
+         posx(it.a).c_str(), posx(it.b).c_str(), trigx(it.a).c_str(), trigx(it.b).c_str(), fl(b.t2_bp).c_str(),
+         fl(b.t2_cull).c_str(), fl(b.hx).c_str(), fl(b.hy).c_str());
   }
   s += "}\n";
   // ---- store
@@ -218,9 +266,10 @@ static std::string generate(const vmasb200_plan* pl, int te, int nt, JitLayout* 
     }
   }
   s += "}\n";
-  // ---- LIDAR staging: compact tile, 3 rows (px py rot) per entity the epilogue reads
-  lay->lid_ents.clear();
-  std::vector<int> lid_slot(pl->ents.size(), -1);
+  // ---- LIDAR staging: compact tile, 3 env rows (px py rot) per entity the epilogue reads; work rows =
+  // [target masks][2 per sensor: cos/sin of its rotation][4 per non-sphere target: its cos/sin cache]
+  lay->lid_ents.clear(); lay->lid_trig.clear();
+  std::vector<int> lid_slot(E, -1);
   auto need = [&](int e) {
     if (lid_slot[e] < 0) { lid_slot[e] = (int)lay->lid_ents.size(); lay->lid_ents.push_back(e); }
   };
@@ -228,16 +277,20 @@ static std::string generate(const vmasb200_plan* pl, int te, int nt, JitLayout* 
     need(sn.entity);
     for (int q = 0; q < sn.n_targets; ++q) need(pl->targets[sn.tg_begin + q]);
   }
-  lay->work_rows = kp.n_lmask_words + 2 * kp.n_sensors;
-  s += "VB_DI void world_stage_lidar(const St& st, float* col) {\n";
+  for (int e : lay->lid_ents)
+    if (pl->ents[e].shape != VMASB200_SPHERE && trig_slot[e] >= 0) lay->lid_trig.push_back(e);
+  const int trig0 = kp.n_lmask_words + 2 * kp.n_sensors;
+  lay->work_rows = trig0 + 4 * (int)lay->lid_trig.size();
+  s += "VB_DI void world_stage_lidar(const St& st, float* col, float* wcol) {\n";
   for (size_t k = 0; k < lay->lid_ents.size(); ++k) {
     const int e = lay->lid_ents[k];
-    if (dyn_slot[e] >= 0)
-      outf(s, "  col[%d * TE] = st.px[%d]; col[%d * TE] = st.py[%d]; col[%d * TE] = st.rot[%d];\n", (int)(3 * k), dyn_slot[e],
-           (int)(3 * k + 1), dyn_slot[e], (int)(3 * k + 2), dyn_slot[e]);
-    else
-      outf(s, "  col[%d * TE] = st.sx[%d]; col[%d * TE] = st.sy[%d]; col[%d * TE] = st.srot[%d];\n", (int)(3 * k), stat_slot[e],
-           (int)(3 * k + 1), stat_slot[e], (int)(3 * k + 2), stat_slot[e]);
+    outf(s, "  { const V2 p = %s; col[%d * TE] = p.x; col[%d * TE] = p.y; col[%d * TE] = %s; }\n", posx(e).c_str(), (int)(3 * k),
+         (int)(3 * k + 1), (int)(3 * k + 2), rotx(e).c_str());
+  }
+  for (size_t k = 0; k < lay->lid_trig.size(); ++k) {
+    const int t = trig_slot[lay->lid_trig[k]], r = trig0 + 4 * (int)k;
+    outf(s, "  wcol[%d * TE] = st.tc[%d]; wcol[%d * TE] = st.ts[%d]; wcol[%d * TE] = st.tc2[%d]; wcol[%d * TE] = st.ts2[%d];\n", r, t,
+         r + 1, t, r + 2, t, r + 3, t);
   }
   s += "}\n} }\n#include \"spec_kernel.cuh\"\n";
   return s;
@@ -248,7 +301,9 @@ struct JitKernel {
   void* module = nullptr;
   void* func = nullptr;
   int te = 0, nt = 0, smem_bytes = 0;
-  KParams kp{};  // the epilogue's view: compact tile rows, this plan's device tables
+  KParams kp{};   // the epilogue's view: compact tile rows, this plan's device tables
+  KParams kpg{};  // the generic view (kernels.cuh repair_kernel: 32-env tile, tables in global memory)
+  bool thin_possible = false;
   bool failed = false;
 };
 struct JitPlanState {
@@ -353,6 +408,12 @@ static void jit_kparams(const vmasb200_plan* pl, int te, const JitLayout& lay, K
   k.row_lmask = 0; k.row_strig = pl->kp.n_lmask_words;
   *out = k;
 }
+// the generic kernel's view for the last CTA's repair: its 32-env tile with 4-member teams, tables in global memory
+static void jit_kparams_generic(const vmasb200_plan* pl, KParams* out) {
+  KParams k = pl->kp;
+  k.TE = 32; k.NT = kThreads;
+  *out = k;
+}
 
 // The compiled kernel of (pl, tile) ready to launch, or nullptr: not eligible / switched off / no NVRTC / no driver API
 // (reason in *why when given).  compile_only: stop after the cubin exists (no CUDA context needed).
@@ -366,12 +427,13 @@ static JitKernel* jit_get(vmasb200_plan* pl, int te, bool compile_only, std::str
   if (jk.failed) return say("an earlier attempt failed");
   if (jk.func) return &jk;
   const bool lidar = pl->kp.n_rays > 0;
-  const int nt = lidar ? kThreads : te;
   JitLayout lay;
+  const int nt = lidar ? kThreads : te;
   std::string err;
   std::string& cubin = ps.cubin[te];
   if (cubin.empty()) cubin = jit_compile(pl, te, nt, &lay, &err);
   else generate(pl, te, nt, &lay);
+  jk.thin_possible = lay.thin_possible;
   if (cubin.empty()) {
     jk.failed = true;
     fprintf(stderr, "libvmasb200: world-compiled kernel unavailable, using the generic kernel (%s)\n", err.c_str());
@@ -381,6 +443,7 @@ static JitKernel* jit_get(vmasb200_plan* pl, int te, bool compile_only, std::str
   if (compile_only) return say("compiled");
   if (!load_driver()) { jk.failed = true; return say("libcuda.so.1 not found"); }
   jit_kparams(pl, te, lay, &jk.kp);
+  jit_kparams_generic(pl, &jk.kpg);
   jk.smem_bytes = lidar ? smem_map(jk.kp).total_bytes : 0;
   auto fail = [&](const char* what, int rc) {
     jk.failed = true;
@@ -403,16 +466,18 @@ static JitKernel* jit_get(vmasb200_plan* pl, int te, bool compile_only, std::str
       t->ents[lay.lid_ents[k]].pos_row = 3 * (int)k;
       t->ents[lay.lid_ents[k]].rot_row = 3 * (int)k + 2;
     }
+    for (size_t k = 0; k < lay.lid_trig.size(); ++k)
+      t->ents[lay.lid_trig[k]].trig_row = pl->kp.n_lmask_words + 2 * pl->kp.n_sensors + 4 * (int)k;
     for (size_t k = 0; k < pl->sensors.size(); ++k) t->sensors[k].tw_off = pl->sensors[k].tw_off - pl->kp.row_lmask;
     unsigned long long dptr = 0;
     size_t bytes = 0;
     if ((rc = g_drv.ModuleGetGlobal(&dptr, &bytes, jk.module, "_ZN2vb5c_tabE"))) return fail("cuModuleGetGlobal(c_tab)", rc);
     if (bytes != sizeof(CTab)) return fail("c_tab size mismatch", (int)bytes);
     if ((rc = g_drv.MemcpyHtoD(dptr, t.get(), sizeof(CTab)))) return fail("cuMemcpyHtoD(c_tab)", rc);
-    if (jk.smem_bytes > 48 * 1024 &&
-        (rc = g_drv.FuncSetAttribute(fn, 8 /* CU_FUNC_ATTRIBUTE_MAX_DYNAMIC_SHARED_SIZE_BYTES */, jk.smem_bytes)))
-      return fail("cuFuncSetAttribute", rc);
   }
+  if (jk.smem_bytes > 48 * 1024 &&
+      (rc = g_drv.FuncSetAttribute(fn, 8 /* CU_FUNC_ATTRIBUTE_MAX_DYNAMIC_SHARED_SIZE_BYTES */, jk.smem_bytes)))
+    return fail("cuFuncSetAttribute", rc);
   jk.func = fn;
   cubin.clear();
   cubin.shrink_to_fit();

@@ -34,7 +34,7 @@ struct StepArgs {
   uint32_t* any_exact;       // [S][pair_words]
   uint32_t* any_spec;        // [S][pair_words]
   uint32_t* thin;            // [S][pair_words]
-  int* counters;             // [0] finished CTAs, [1] tainted envs, [2] repairs done since plan creation
+  int* counters;             // [0] finished CTAs, [1] tainted envs, [2] repairs done since plan creation, [3] repair_kernel wanted
   int* u_list;               // [n_envs] env index of every tainted env (bit 31: to be re-simulated)
   float* u_buf;              // [n_envs][dyn_rows] their input state (then their evolving state)
   int* u_rep;                // [n_envs] indices into u_list of the envs to re-simulate
@@ -570,6 +570,42 @@ step_kernel(const __grid_constant__ KParams kp, const __grid_constant__ AgentIO 
   for (int w = tid; w < nw; w += blockDim.x) { sa.any_exact[w] = 0u; sa.any_spec[w] = 0u; sa.thin[w] = 0u; }
   if (tid == 0) {
     sa.counters[0] = 0; sa.counters[1] = 0;
+    if (nd) {
+      sa.counters[2] += 1;
+      *sa.repairs_host = sa.counters[2];
+      __threadfence_system();
+    }
+  }
+}
+
+// Verification tail of a world-compiled launch (spec_kernel.cuh) whose last CTA found a thin event on a pair no exact
+// env activates (counters[3] raised): the same validation, repair, publication and scratch reset as the tail of
+// step_kernel.  One CTA, launched behind every such launch; returns at once when there is nothing to do.  A chunked
+// step launches one per chunk stream: the one that claims the flag does the work.
+template <bool CT, int TE>
+__global__ void __launch_bounds__(kThreads)
+repair_kernel(const __grid_constant__ KParams kp, const __grid_constant__ AgentIO aio, const __grid_constant__ StepArgs sa) {
+  extern __shared__ __align__(16) float smem[];
+  __shared__ int s_claim;
+  const int tid = threadIdx.x;
+  if (tid == 0) s_claim = atomicExch(sa.counters + 3, 0);
+  __syncthreads();
+  if (!s_claim) return;
+  __threadfence();
+  const SmemMap m = smem_map(kp);
+  Tile t;
+  t.envS = smem + m.env; t.workS = smem + m.work; t.lidS = smem + m.lid;
+  t.queue = reinterpret_cast<int*>(smem + m.queue); t.rayq = reinterpret_cast<int*>(smem + m.rayq);
+  t.qcount = reinterpret_cast<int*>(smem + m.bar) + 2;
+  uint32_t* flagS = reinterpret_cast<uint32_t*>(smem + m.flags);
+  const int nw = kp.S * kp.pair_words;
+  const int nu = *reinterpret_cast<volatile int*>(sa.counters + 1);
+  const int nd = validate_speculation(kp, sa, flagS, nu);
+  if (nd) repair_tainted<CT, TE>(kp, aio, sa, t, flagS, nd);
+  for (int w = tid; w < nw; w += blockDim.x) sa.flags_out[w] = flagS[w];
+  for (int w = tid; w < nw; w += blockDim.x) { sa.any_exact[w] = 0u; sa.any_spec[w] = 0u; sa.thin[w] = 0u; }
+  if (tid == 0) {
+    sa.counters[1] = 0;
     if (nd) {
       sa.counters[2] += 1;
       *sa.repairs_host = sa.counters[2];

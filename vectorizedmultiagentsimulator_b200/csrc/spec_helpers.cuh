@@ -1,10 +1,10 @@
-// spec_helpers.cuh - register-resident twins of begin_forces / integrate / the sphere-sphere item of step_kernel.cuh
-// for the WORLD-COMPILED step kernel (jit.cpp).  This file is not part of libvmasb200.so's own translation unit: it is
+// spec_helpers.cuh - register-resident twins of begin_forces / integrate / eval_item / accumulate of step_kernel.cuh
+// for the WORLD-COMPILED step kernel (jit.h).  This file is not part of libvmasb200.so's own translation unit: it is
 // embedded in the library as text and compiled at plan time by NVRTC, between a generated prelude that defines the
-// world as compile-time constants (namespace vb::gen: ND, NST, NA, S, PW, SUB_DT, KC ...) and generated straight-line
-// calls of the functions below with literal entity attributes.  After inlining every `en.flags & ...` test, every
-// index into the state arrays and every table read of the generic kernel is a constant: the state lives in registers
-// and only the reference's arithmetic is left.
+// world as compile-time constants (namespace vb::gen: ND, NST, NA, NTR, NJF, S, PW, SUB_DT, KC ...) and generated
+// straight-line calls of the functions below with literal entity attributes.  After inlining, every `en.flags & ...`
+// test, every index into the state arrays and every table read of the generic kernel is a constant: the state lives
+// in registers and only the reference's arithmetic is left.
 //
 // Every function performs the SAME fp32 operations in the SAME order as its generic twin (cited beside it), so the
 // compiled kernel is bit-identical to the generic one (tests/test_gpu_jit.py), which is the one pinned to the oracle.
@@ -14,19 +14,51 @@ namespace vb {
 namespace gen {
 
 struct EntC {  // the attributes of tables.h DEnt the physics reads, by value (constant-folded)
+  int shape;
   uint32_t flags;
-  float radius, mass, moi, max_speed, v_range, one_minus_drag, lin_fric, ang_fric, gx, gy, max_f, f_range, max_t, t_range;
+  float radius, length, width, mass, moi, max_speed, v_range, one_minus_drag, lin_fric, ang_fric, gx, gy, max_f, f_range,
+      max_t, t_range;
+};
+struct JointC {  // tables.h DItem of a joint
+  float dax, day, dbx, dby, dist, fixed_rot;
+  int rotate;
 };
 
 constexpr int kND = ND > 0 ? ND : 1, kNST = NST > 0 ? NST : 1, kNA = NA > 0 ? NA : 1, kPW = PW > 0 ? PW : 1;
+constexpr int kNTR = NTR > 0 ? NTR : 1, kNJF = NJF > 0 ? NJF : 1;
 
 struct St {
   float px[kND], py[kND], vx[kND], vy[kND], rot[kND], w[kND];  // dynamic entities (dyn buffer rows)
   float sx[kNST], sy[kNST], srot[kNST];                       // static entities (stat buffer rows)
+  float jfr[kNJF];                                            // per-env fixed rotations of joints (stat buffer rows)
   float fx[kNA], fy[kNA], tq[kNA];                            // agent.state.force / torque, clamped in place
   float Fx[kND], Fy[kND], T[kND];                             // accumulators of the running substep
+  float tc[kNTR], ts[kNTR], tc2[kNTR], ts2[kNTR];             // cos/sin cache (step_kernel.cuh store_trig)
   uint32_t verd[kPW];                                         // World.collides verdict bits of the running substep
+  uint32_t thin[kPW];                                         // thin events of the running substep (kernels.cuh)
 };
+
+template <int t>
+VB_DI Rot rot_r(const St& st) {
+  Rot o;
+  constexpr int k = t >= 0 ? t : 0;
+  o.c = st.tc[k]; o.s = st.ts[k]; o.c2 = st.tc2[k]; o.s2 = st.ts2[k];
+  return o;
+}
+// step_kernel.cuh store_trig (physics.py:299-301, 412; utils.py:183-184)
+template <int t, int SHAPE>
+VB_DI void trig_r(St& st, float rot) {
+  if (t < 0) return;
+  constexpr int k = t >= 0 ? t : 0;
+  float s, c;
+  sincosf(rot, &s, &c);
+  st.tc[k] = c; st.ts[k] = s;
+  if (SHAPE == VMASB200_BOX) {
+    float rot2 = rot + (float)(3.14159265358979323846 / 2);
+    sincosf(rot2, &s, &c);
+    st.tc2[k] = c; st.ts2[k] = s;
+  }
+}
 
 // step_kernel.cuh begin_forces (core.py:2017-2101): d = dynamic slot, a = agent slot
 template <int d, int a>
@@ -63,8 +95,8 @@ VB_DI void begin_r(const EntC en, St& st) {
   st.Fx[d] = F.x; st.Fy[d] = F.y; st.T[d] = T;
 }
 
-// step_kernel.cuh integrate (core.py:2861-2907)
-template <int d>
+// step_kernel.cuh integrate (core.py:2861-2907); t = trig slot of the entity or -1
+template <int d, int t>
 VB_DI void integrate_r(const EntC en, St& st, int substep) {
   const uint32_t fl = en.flags;
   if (fl & VMASB200_E_MOVABLE) {
@@ -89,26 +121,131 @@ VB_DI void integrate_r(const EntC en, St& st, int substep) {
     if (substep == 0) w = w * en.one_minus_drag;
     w = w + (st.T[d] / en.moi) * SUB_DT;
     st.w[d] = w;
-    st.rot[d] = st.rot[d] + w * SUB_DT;
+    const float nr = st.rot[d] + w * SUB_DT;
+    st.rot[d] = nr;
+    trig_r<t, VMASB200_SPHERE>(st, nr);  // the box branch below needs the shape at compile time
+  }
+}
+template <int d, int t>
+VB_DI void integrate_box_r(const EntC en, St& st, int substep) {  // a rotatable box also refreshes cos/sin(rot + pi/2)
+  integrate_r<d, -1>(en, st, substep);
+  if (en.flags & VMASB200_E_ROTATABLE) trig_r<t, VMASB200_BOX>(st, st.rot[d >= 0 ? d : 0]);
+}
+
+// step_kernel.cuh accumulate = update_env_forces (core.py:2190-2198)
+template <int ACC, int da, int db>
+VB_DI void accumulate_r(St& st, V2 fa, float ta, float tb) {
+  constexpr int ia = da >= 0 ? da : 0, ib = db >= 0 ? db : 0;
+  if (ACC & ACC_A_MOV) { st.Fx[ia] = st.Fx[ia] + fa.x; st.Fy[ia] = st.Fy[ia] + fa.y; }
+  if (ACC & ACC_A_ROT) st.T[ia] = st.T[ia] + ta;
+  if (ACC & ACC_B_MOV) { st.Fx[ib] = st.Fx[ib] + (-fa.x); st.Fy[ib] = st.Fy[ib] + (-fa.y); }
+  if (ACC & ACC_B_ROT) st.T[ib] = st.T[ib] + tb;
+}
+
+// step_kernel.cuh eval_item for the six pair types (core.py:2293-2785)
+template <int TYPE>
+VB_DI void eval_pair_r(const EntC ea, const EntC eb, V2 pa, V2 pb, const Rot qa, const Rot qb, V2& fa, float& ta, float& tb) {
+  ta = 0.f; tb = 0.f;
+  if (TYPE == IT_SS) {
+    fa = constraint_force(pa, pb, ea.radius + eb.radius, KC, MARGIN, false);
+  } else if (TYPE == IT_LS) {
+    V2 cp = closest_point_line(pa, qa.c, qa.s, ea.length, pb);
+    V2 fs = constraint_force(pb, cp, eb.radius + kLMD, KC, MARGIN, false);
+    fa = -fs;
+    ta = cross(cp - pa, fa);
+  } else if (TYPE == IT_LL) {
+    V2 ca, cb;
+    closest_points_line_line(pa, qa.c, qa.s, ea.length, pb, qb.c, qb.s, eb.length, ca, cb);
+    fa = constraint_force(ca, cb, kLMD, KC, MARGIN, false);
+    ta = cross(ca - pa, fa);
+    tb = cross(cb - pb, -fa);
+  } else if (TYPE == IT_BS) {
+    V2 cp = closest_point_box(pa, qa, ea.width, ea.length, pb);
+    V2 ip = cp;
+    float dd = 0.f;
+    if (!(ea.flags & VMASB200_E_HOLLOW)) ip = inner_point_box(pb, cp, pa, dd);
+    V2 fs = constraint_force(pb, ip, (eb.radius + kLMD) + dd, KC, MARGIN, false);
+    fa = -fs;
+    ta = cross(cp - pa, fa);
+  } else if (TYPE == IT_BL) {
+    V2 cbx, cl;
+    closest_line_box(pa, qa, ea.width, ea.length, pb, qb.c, qb.s, eb.length, cbx, cl);
+    V2 ip = cbx;
+    float dd = 0.f;
+    if (!(ea.flags & VMASB200_E_HOLLOW)) ip = inner_point_box(cl, cbx, pa, dd);
+    fa = constraint_force(ip, cl, kLMD + dd, KC, MARGIN, false);
+    ta = cross(cbx - pa, fa);
+    tb = cross(cl - pb, -fa);
+  } else {
+    V2 ca, cb;
+    closest_box_box(pa, qa, ea.width, ea.length, pb, qb, eb.width, eb.length, ca, cb);
+    V2 ia = ca, ib = cb;
+    float da = 0.f, db = 0.f;
+    if (!(ea.flags & VMASB200_E_HOLLOW)) ia = inner_point_box(cb, ca, pa, da);
+    if (!(eb.flags & VMASB200_E_HOLLOW)) ib = inner_point_box(ca, cb, pb, db);
+    fa = constraint_force(ia, ib, (da + db) + kLMD, KC, MARGIN, false);
+    ta = cross(ca - pa, fa);
+    tb = cross(cb - pb, -fa);
+  }
+}
+// box-sphere narrow phase out of line: one copy of the closest-point code per kernel keeps the unrolled pair list
+// compact (joint_passage: 39 such pairs); only the varying operands travel
+__device__ __noinline__ void eval_bs_r(float width, float length, bool hollow, float rb, V2 pa, V2 pb, const Rot qa, V2& fa,
+                                       float& ta) {
+  V2 cp = closest_point_box(pa, qa, width, length, pb);
+  V2 ip = cp;
+  float dd = 0.f;
+  if (!hollow) ip = inner_point_box(pb, cp, pa, dd);
+  V2 fs = constraint_force(pb, ip, (rb + kLMD) + dd, KC, MARGIN, false);
+  fa = -fs;
+  ta = cross(cp - pa, fa);
+}
+
+// One candidate pair of a substep: the broad-phase row (kernels.cuh run_substeps: verdict of World.collides,
+// core.py:2796-2800, and the cull that only drops pairs whose force is provably zero), the narrow phase, the thin-event
+// test of the speculative launch and update_env_forces.  da / db: dynamic slot of a / b or -1; FRAME: the row carries
+// a frame cull (b's centre in a's frame against hx, hy) instead of the circle cull.
+template <int TYPE, int ACC, int da, int db, int word, int bit, bool FRAME, bool THIN>
+VB_DI void pair_r(St& st, const EntC ea, const EntC eb, V2 pa, V2 pb, const Rot qa, const Rot qb, float t2_bp, float t2_cull,
+                  float hx, float hy) {
+  const float dx = pa.x - pb.x, dy = pa.y - pb.y;
+  const float d2 = fmaf(dy, dy, dx * dx);
+  const bool verdict = d2 <= t2_bp;
+  if (verdict) st.verd[word] |= 1u << bit;
+  bool sv = !(d2 > t2_cull);  // NaN passes, as in the generic broad phase
+  if (FRAME) {
+    const float lx = fmaf(dx, qa.c, dy * qa.s), ly = fmaf(dx, qa.s, -(dy * qa.c));
+    sv = sv && !(fabsf(lx) > hx) && !(fabsf(ly) > hy);
+  }
+  if (sv) {
+    V2 fa;
+    float ta, tb;
+    if (TYPE == IT_BS) { tb = 0.f; eval_bs_r(ea.width, ea.length, (ea.flags & VMASB200_E_HOLLOW) != 0, eb.radius, pa, pb, qa, fa, ta); }
+    else eval_pair_r<TYPE>(ea, eb, pa, pb, qa, qb, fa, ta, tb);
+    // THIN = false: a sphere-sphere pair whose fp32 r_a + r_b does not exceed the verdict's threshold cannot be thin
+    if (THIN && (fa.x != 0.f || fa.y != 0.f) && !verdict) st.thin[word] |= 1u << bit;
+    accumulate_r<ACC, da, db>(st, fa, ta, tb);
   }
 }
 
-// One sphere-sphere candidate pair of a substep: the broad-phase row (kernels.cuh run_substeps: verdict of
-// World.collides, core.py:2796-2800, and the exact cull dist > r_a + r_b), eval_item IT_SS (core.py:2293-2338) and
-// accumulate (core.py:2190-2198).  da / db: dynamic slot of a / b or -1 (static: no accumulator); ACC: tables.h ACC_*.
-template <int ACC, int da, int db, int word, int bit>
-VB_DI void pair_ss_r(St& st, V2 pa, V2 pb, float t2_bp, float t2_cull, float ra, float rb) {
-  const float dx = pa.x - pb.x, dy = pa.y - pb.y;
-  const float d2 = fmaf(dy, dy, dx * dx);
-  if (d2 <= t2_bp) st.verd[word] |= 1u << bit;
-  if (!(d2 > t2_cull)) {  // NaN passes, as in the generic broad phase
-    const V2 fa = constraint_force(pa, pb, ra + rb, KC, MARGIN, false);
-    constexpr int ia = da >= 0 ? da : 0, ib = db >= 0 ? db : 0;
-    if (ACC & ACC_A_MOV) { st.Fx[ia] = st.Fx[ia] + fa.x; st.Fy[ia] = st.Fy[ia] + fa.y; }
-    if (ACC & ACC_A_ROT) st.T[ia] = st.T[ia] + 0.f;
-    if (ACC & ACC_B_MOV) { st.Fx[ib] = st.Fx[ib] + (-fa.x); st.Fy[ib] = st.Fy[ib] + (-fa.y); }
-    if (ACC & ACC_B_ROT) st.T[ib] = st.T[ib] + 0.f;
+// step_kernel.cuh eval_item IT_JOINT (core.py:2200-2291, joints.py:206-215); jf = slot of the per-env fixed rotation
+template <int ACC, int da, int db, int jf>
+VB_DI void joint_r(St& st, const JointC jc, V2 pa, V2 pb, const Rot qa, const Rot qb, float ra, float rb) {
+  V2 ja = pa + rotv(mk(jc.dax, jc.day), qa.c, qa.s);
+  V2 jb = pb + rotv(mk(jc.dbx, jc.dby), qb.c, qb.s);
+  V2 att = constraint_force(ja, jb, jc.dist, KJ, MARGIN, true);
+  V2 rep = constraint_force(ja, jb, jc.dist, KJ, MARGIN, false);
+  V2 fa = att + rep;
+  V2 fb = (-att) + (-rep);
+  float ta = cross(ja - pa, fa);
+  float tb = cross(jb - pb, fb);
+  if (!jc.rotate) {
+    float fr = jf >= 0 ? st.jfr[jf >= 0 ? jf : 0] : jc.fixed_rot;
+    float tq = constraint_torque(ra, rb + fr, KT);
+    ta = ta + (-tq);
+    tb = tb + tq;
   }
+  accumulate_r<ACC, da, db>(st, fa, ta, tb);
 }
 
 }  // namespace gen

@@ -1,19 +1,21 @@
 // spec_kernel.cuh - the WORLD-COMPILED step kernel (NVRTC, jit.h).  Included after kernels.cuh, the generated prelude
 // (vb::gen constants), spec_helpers.cuh and the generated world functions:
 //   world_load(st, aio, sa, env)   coalesced row loads of the env's state and agent forces into registers
-//   world_begin(st)                begin_r of every dynamic entity
-//   world_pairs(st)                pair_ss_r of every candidate pair, in the reference's pair order
+//   world_begin(st)                cos/sin cache + begin_r of every dynamic entity
+//   world_items(st)                joint_r of every joint, then pair_r of every candidate pair, in the reference's order
 //   world_integrate(st, s, more)   integrate_r (+ begin_r of the next substep) of every dynamic entity
 //   world_store(st, sa, env)       dyn_out / act_out rows
-//   world_stage_lidar(st, envS)    px py rot of the sensing entities and their targets into the epilogue's tile
+//   world_stage_lidar(st, env, work) px py rot (and cos/sin of non-sphere targets) of the entities the epilogue reads
 //
 // One thread per environment, state in registers for all substeps, no shared memory and no barrier on the physics
-// path; worlds this kernel is generated for (sphere-sphere pairs only, no joints) cannot produce a "thin" contact, so
-// every env equals the reference without the speculation records of the generic kernel: only the verdict bits are
-// OR-ed into any_exact and published by the CTA that finishes last (same protocol and scratch as kernels.cuh, so
-// chunked steps and vmasb200_step_io.pair_active_out work unchanged).
-// LIDAR: the generic three-pass epilogue (kernels.cuh lidar_epilogue) on a compact tile; the CTA keeps 128 threads so
-// that its passes run on full warps even when only TE = 32 of them carry an environment.
+// path.  The speculation protocol is the generic kernel's (kernels.cuh header): verdicts of untainted envs go to
+// any_exact, an env is tainted after its first thin event and from then on files its verdicts and thin events in its
+// record; the CTA that finishes last verifies thin & ~any_exact == 0 and otherwise raises counters[3] for
+// kernels.cuh repair_kernel (generic validation + repair, compiled into the library), which the host launches right
+// behind every launch of a world that can have thin events.  THIN_POSSIBLE = false (sphere-sphere worlds) compiles all
+// of that away.
+// LIDAR: the generic three-pass epilogue (kernels.cuh lidar_epilogue) on a compact tile; such a CTA keeps 128 threads
+// so that its passes run on full warps even when only TE = 32 of them carry an environment.
 #pragma once
 
 namespace vb {
@@ -33,18 +35,51 @@ vmasb200_step_world(const __grid_constant__ KParams kp, const __grid_constant__ 
   if (phys) {
     world_load(st, aio, sa, env);
     world_begin(st);
+    int taint = 0;  // 0, or 1 + the env's index in sa.u_list (kernels.cuh run_substeps)
     for (int s = 0; s < S; ++s) {
 #pragma unroll
-      for (int w = 0; w < kPW; ++w) st.verd[w] = 0u;
-      world_pairs(st);
+      for (int w = 0; w < kPW; ++w) { st.verd[w] = 0u; st.thin[w] = 0u; }
+      world_items(st);
+      const bool tainted = THIN_POSSIBLE && taint != 0;
 #pragma unroll
       for (int w = 0; w < PW; ++w) {
-        const uint32_t e = __reduce_or_sync(0xffffffffu, ok ? st.verd[w] : 0u);
+        const uint32_t e = __reduce_or_sync(0xffffffffu, (ok && !tainted) ? st.verd[w] : 0u);
         if ((tid & 31) == 0 && e) or_global(sa.any_exact + s * PW + w, e);
+        if (THIN_POSSIBLE) {
+          const uint32_t sp = __reduce_or_sync(0xffffffffu, (ok && tainted) ? st.verd[w] : 0u);
+          const uint32_t th = __reduce_or_sync(0xffffffffu, ok ? st.thin[w] : 0u);
+          if ((tid & 31) == 0) {
+            if (sp) or_global(sa.any_spec + s * PW + w, sp);
+            if (th) or_global(sa.thin + s * PW + w, th);
+          }
+          if (ok && tainted && taint <= sa.rec_cap) sa.u_verd[((size_t)(taint - 1) * S + s) * PW + w] = st.verd[w];
+        }
       }
       world_integrate(st, s, s + 1 < S);
+      if (THIN_POSSIBLE && ok) {  // thin events of this substep: tainted from the NEXT substep on, with a record
+        uint32_t any = 0u;
+#pragma unroll
+        for (int w = 0; w < PW; ++w) any |= st.thin[w];
+        if (any) {
+          const size_t rw = (size_t)S * PW;
+          if (taint == 0) {
+            taint = atomicAdd(sa.counters + 1, 1) + 1;
+            sa.u_list[taint - 1] = (int)env;
+            if (taint <= sa.rec_cap)
+              for (size_t i = 0; i < rw; ++i) { sa.u_verd[(taint - 1) * rw + i] = 0u; sa.u_thin[(taint - 1) * rw + i] = 0u; }
+          }
+          if (taint <= sa.rec_cap)
+#pragma unroll
+            for (int w = 0; w < PW; ++w)
+              if (st.thin[w]) sa.u_thin[(taint - 1) * rw + (size_t)s * PW + w] = st.thin[w];
+        }
+      }
     }
-    if (ok) world_store(st, sa, env);
+    if (ok) {
+      if (THIN_POSSIBLE && taint)  // keep the INPUT state of a tainted env (dyn_in is intact until our own store)
+        for (int r = 0; r < DYN_ROWS; ++r) sa.u_buf[(size_t)(taint - 1) * DYN_ROWS + r] = sa.dyn_in[(size_t)r * sa.ld + env];
+      world_store(st, sa, env);
+    }
   }
   if (LIDAR && sa.do_lidar && sa.lidar_out) {
     const SmemMap m = smem_map(kp);
@@ -52,7 +87,7 @@ vmasb200_step_world(const __grid_constant__ KParams kp, const __grid_constant__ 
     t.envS = smem + m.env; t.workS = smem + m.work; t.lidS = smem + m.lid;
     t.queue = reinterpret_cast<int*>(smem + m.queue); t.rayq = reinterpret_cast<int*>(smem + m.rayq);
     t.qcount = reinterpret_cast<int*>(smem + m.bar) + 2;
-    if (phys) world_stage_lidar(st, t.envS + tid);
+    if (phys) world_stage_lidar(st, t.envS + tid, t.workS + tid);
     __syncthreads();
     lidar_epilogue<true, TE>(kp, t, n_valid);
     // one TMA bulk store per LIDAR row; the batch's last tile also carries the padding columns up to ld
@@ -66,18 +101,40 @@ vmasb200_step_world(const __grid_constant__ KParams kp, const __grid_constant__ 
       bulk_wait_all();
     }
   }
-  // ---- last CTA of the step: publish the verdicts, reset the scratch for the next launch
+  // ---- last CTA of the step: verify (repair if needed), publish the verdicts, reset the scratch for the next launch
   __threadfence();
   __syncthreads();
   if (tid == 0) s_last = (atomicAdd(sa.counters, 1) == sa.total_ctas - 1);
   __syncthreads();
   if (!s_last) return;
   __threadfence();
-  for (int w = tid; w < S * PW; w += blockDim.x) {
-    sa.flags_out[w] = __ldcg(sa.any_exact + w);
-    sa.any_exact[w] = 0u;
+  constexpr int nw = S * PW;
+  if (!THIN_POSSIBLE) {
+    for (int w = tid; w < nw; w += blockDim.x) {
+      sa.flags_out[w] = __ldcg(sa.any_exact + w);
+      sa.any_exact[w] = 0u;
+    }
+    if (tid == 0) sa.counters[0] = 0;
+    return;
   }
-  if (tid == 0) sa.counters[0] = 0;
+  int bad = 0;
+  for (int w = tid; w < nw; w += blockDim.x) bad |= (__ldcg(sa.thin + w) & ~__ldcg(sa.any_exact + w)) != 0u;
+  bad = __syncthreads_or(bad);
+  if (bad) {
+    // hand over to kernels.cuh repair_kernel, which the host launches right behind this kernel: it validates the
+    // speculation, re-simulates the envs that left the reference's trajectory, publishes and resets the scratch
+    if (tid == 0) {
+      sa.counters[0] = 0;
+      __threadfence();
+      atomicExch(sa.counters + 3, 1);
+    }
+    return;
+  }
+  for (int w = tid; w < nw; w += blockDim.x) {
+    sa.flags_out[w] = __ldcg(sa.any_exact + w) | __ldcg(sa.any_spec + w);
+    sa.any_exact[w] = 0u; sa.any_spec[w] = 0u; sa.thin[w] = 0u;
+  }
+  if (tid == 0) { sa.counters[0] = 0; sa.counters[1] = 0; }
 }
 
 }  // namespace vb

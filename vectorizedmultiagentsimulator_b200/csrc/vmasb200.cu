@@ -78,6 +78,7 @@ int upload_plan(vmasb200_plan* pl) {
   for (int ct = 0; ct < 2; ++ct)
     for (int te : {32, 64, 128})
       VB_CUDA(cudaFuncSetAttribute(step_fn(ct != 0, te), cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
+  VB_CUDA(cudaFuncSetAttribute(repair_kernel<false, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
   pl->uploaded = true;
   return VMASB200_OK;
 }
@@ -201,28 +202,14 @@ static int launch_step(vmasb200_plan* pl, const vmasb200_step_io* io, long long 
   sa.env_begin = env_begin; sa.env_end = env_end; sa.total_ctas = (int)total_ctas;
   sa.flags_out = flags; sa.any_exact = flags + bw; sa.any_spec = flags + 2 * bw; sa.thin = flags + 3 * bw;
   sa.counters = reinterpret_cast<int*>(flags + 4 * bw);
-  if (!io->exact) {
-    // world-compiled kernel (jit.h) when the plan has one: same scratch protocol, same bits, no constant-bank upload
-    const int jte = jit_tile(pl, io->n_envs);
-    if (JitKernel* jk = jit_get(pl, jte, false, nullptr)) {
-      if (env_begin % jte) { set_error("step: chunk boundary is not a multiple of the compiled kernel's tile"); return VMASB200_ERR_INVALID; }
-      sa.total_ctas = (int)((io->n_envs + jte - 1) / jte);
-      sa.s_begin = 0; sa.s_end = kp.S; sa.flags_in = nullptr; sa.do_lidar = 1;
-      KParams jkp = jk->kp;
-      void* args[3] = {&jkp, &aio, &sa};
-      const unsigned jgrid = (unsigned)((env_end - env_begin + jte - 1) / jte);
-      const int rc = g_drv.LaunchKernel(jk->func, jgrid, 1, 1, (unsigned)jk->nt, 1, 1, (unsigned)jk->smem_bytes, st, args, nullptr);
-      if (rc) { set_error("cuLaunchKernel(vmasb200_step_world) failed: CUresult " + std::to_string(rc)); return VMASB200_ERR_CUDA; }
-      pl->jit_launches += 1;
-      if (io->pair_active_out && nw) VB_CUDA(cudaMemcpyAsync(io->pair_active_out, flags, nw * sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
-      return VMASB200_OK;
-    }
-  }
+  // world-compiled kernel (jit.h) when the plan has one: same scratch protocol, same bits, no constant-bank upload
+  const int jte = jit_tile(pl, io->n_envs);
+  JitKernel* jk = io->exact ? nullptr : jit_get(pl, jte, false, nullptr);
   const unsigned grid = (unsigned)((env_end - env_begin + kp.TE - 1) / kp.TE);
   const unsigned block = (unsigned)kp.NT;
   bool ct = false;
   bool capturing = false;
-  int rc_ct = bind_const(pl, st, &ct, &capturing);
+  int rc_ct = jk ? VMASB200_OK : bind_const(pl, st, &ct, &capturing);
   if (rc_ct) return rc_ct;
   if (io->exact) {
     // exact path: the batch-wide World.collides verdicts are reduced before every substep (core.py:2796-2800)
@@ -253,7 +240,22 @@ static int launch_step(vmasb200_plan* pl, const vmasb200_step_io* io, long long 
     sa.u_verd = pl->d_urec; sa.u_thin = pl->d_urec + (size_t)sa.rec_cap * bw;
     VB_CUDA(cudaHostGetDevicePointer(&sa.repairs_host, pl->h_repairs, 0));
     sa.s_begin = 0; sa.s_end = kp.S; sa.flags_in = nullptr; sa.do_lidar = 1;
-    step_fn(ct, kp.TE)<<<grid, block, smem_bytes, st>>>(kp, aio, sa);
+    if (jk) {
+      if (env_begin % jte) { set_error("step: chunk boundary is not a multiple of the compiled kernel's tile"); return VMASB200_ERR_INVALID; }
+      sa.total_ctas = (int)((io->n_envs + jte - 1) / jte);
+      KParams jkp = jk->kp;
+      void* args[3] = {&jkp, &aio, &sa};
+      const unsigned jgrid = (unsigned)((env_end - env_begin + jte - 1) / jte);
+      const int rc = g_drv.LaunchKernel(jk->func, jgrid, 1, 1, (unsigned)jk->nt, 1, 1, (unsigned)jk->smem_bytes, st, args, nullptr);
+      if (rc) { set_error("cuLaunchKernel(vmasb200_step_world) failed: CUresult " + std::to_string(rc)); return VMASB200_ERR_CUDA; }
+      pl->jit_launches += 1;
+      if (jk->thin_possible) {  // verification tail of the compiled launch (returns at once unless its last CTA asked)
+        KParams gk = jk->kpg;
+        repair_kernel<false, 32><<<1, kThreads, smem_map(gk).total_bytes, st>>>(gk, aio, sa);
+      }
+    } else {
+      step_fn(ct, kp.TE)<<<grid, block, smem_bytes, st>>>(kp, aio, sa);
+    }
   }
   if (ct && !capturing) VB_CUDA(cudaEventRecord(g_const[pl->device].last_use, st));
   if (io->pair_active_out && nw) VB_CUDA(cudaMemcpyAsync(io->pair_active_out, flags, nw * sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
@@ -345,8 +347,8 @@ int vmasb200_plan_tile(const vmasb200_plan* pl, int64_t n_envs) {
 
 int vmasb200_jit_enable(int on) {
   std::lock_guard<std::mutex> lock(g_jit_mu);
-  const int prev = jit_on() ? 1 : 0;
-  g_jit_on = on ? 1 : 0;
+  const int prev = jit_mode();
+  g_jit_on = on < 0 ? 0 : on > 2 ? 2 : on;
   return prev;
 }
 
