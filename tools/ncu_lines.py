@@ -17,7 +17,12 @@ import tempfile
 
 def line_table(so, kernel):
     tmp = tempfile.mkdtemp()
-    subprocess.run(["cuobjdump", "-xelf", "all", os.path.abspath(so)], cwd=tmp, capture_output=True)
+    if so.endswith(".cubin"):  # a world-compiled kernel from the JIT cache (vectorizedmultiagentsimulator_b200/_jit)
+        import shutil
+
+        shutil.copy(so, tmp)
+    else:
+        subprocess.run(["cuobjdump", "-xelf", "all", os.path.abspath(so)], cwd=tmp, capture_output=True)
     table = {}
     for f in os.listdir(tmp):
         if not f.endswith(".cubin"):

@@ -10,12 +10,18 @@ for wl in "$@"; do
   sc=${wl%@*}; n=32768; name=$sc
   if [[ $wl == *@* ]]; then n=${wl#*@}; name=${sc}_$n; fi
   rep=/tmp/step_kernel_$name
-  ncu --set full --import-source on --clock-control none -k regex:step_kernel -s 6 -c 1 -f -o $rep \
+  export VMASB200_JIT_CACHE=/tmp/jit_$name   # this run's world-compiled cubin alone (ncu_lines needs its line table)
+  rm -rf $VMASB200_JIT_CACHE
+  ncu --set full --import-source on --clock-control none -k 'regex:step_kernel|vmasb200_step_world' -s 6 -c 1 -f -o $rep \
     python bench.py --scenario $sc --num-envs $n --steps 4 --warmup 3 --no-cpu-baseline --no-e2e > $OUT/ncu_$name.log 2>&1
   python tools/ncu_summary.py $rep.ncu-rep > $OUT/step_kernel_$name.txt 2>&1
   kname=$(head -1 $OUT/step_kernel_$name.txt)
-  te=$(echo "$kname" | sed -n 's/.*step_kernel<[0-9], \([0-9]*\)>.*/\1/p')
-  python tools/ncu_lines.py $rep.ncu-rep $SO step_kernelILb1ELi$te > $OUT/${name}_lines.txt 2>&1
+  if echo "$kname" | grep -q vmasb200_step_world; then
+    python tools/ncu_lines.py $rep.ncu-rep $(ls $VMASB200_JIT_CACHE/*.cubin | head -1) vmasb200_step_world > $OUT/${name}_lines.txt 2>&1
+  else
+    te=$(echo "$kname" | sed -n 's/.*step_kernel<[0-9], \([0-9]*\)>.*/\1/p')
+    python tools/ncu_lines.py $rep.ncu-rep $SO step_kernelILb1ELi$te > $OUT/${name}_lines.txt 2>&1
+  fi
   rm -f $rep.ncu-rep
 done
 ls -la $OUT

@@ -292,7 +292,67 @@ static std::string generate(const vmasb200_plan* pl, int te, int nt, JitLayout* 
     outf(s, "  wcol[%d * TE] = st.tc[%d]; wcol[%d * TE] = st.ts[%d]; wcol[%d * TE] = st.tc2[%d]; wcol[%d * TE] = st.ts2[%d];\n", r, t,
          r + 1, t, r + 2, t, r + 3, t);
   }
-  s += "}\n} }\n#include \"spec_kernel.cuh\"\n";
+  s += "}\n";
+  // ---- LIDAR epilogue with the sensors as constants (spec_kernel.cuh lidar_world) when every sensor's target mask is
+  // one word; else the generic epilogue runs on the compact tile
+  bool lc = lidar;
+  for (const DSensor& sn : pl->sensors) lc = lc && sn.n_tw == 1 && sn.n_targets >= 1 && sn.n_rays >= 1;
+  lc = lc && te <= 256 && kp.n_sensors <= 255;
+  outf(s, "constexpr bool LIDAR_COMPILED = %s;\nconstexpr int NSENS = %d;\n", lc ? "true" : "false", std::max(kp.n_sensors, 1));
+  if (lc) {
+    // init: rows of one sensor share its max_range
+    s += "VB_DI void world_lidar_init(float* lidS, int tid) {\n";
+    for (const DSensor& sn : pl->sensors)
+      outf(s, "  { const float4 v = make_float4(%s, %s, %s, %s); float4* p = reinterpret_cast<float4*>(lidS + %d * TE);\n"
+              "    for (int i = tid; i < %d * TE / 4; i += NT) p[i] = v; }\n",
+           fl(sn.max_range).c_str(), fl(sn.max_range).c_str(), fl(sn.max_range).c_str(), fl(sn.max_range).c_str(), sn.out_off, sn.n_rays);
+    s += "}\n";
+    s += "VB_DI void world_lidar_pass1(const St& st, bool ok, int col, float* wcol, int* queue, int* qn) {\n";
+    for (int k = 0; k < kp.n_sensors; ++k) {
+      const DSensor& sn = pl->sensors[k];
+      const int mrow = sn.tw_off - kp.row_lmask;
+      outf(s, "  { const V2 o = %s; uint32_t m = 0u;\n", posx(sn.entity).c_str());
+      for (int q = 0; q < sn.n_targets; ++q) {
+        const int tg = pl->targets[sn.tg_begin + q];
+        outf(s, "    { const V2 p = %s; const float dx = o.x - p.x, dy = o.y - p.y; if (!(fmaf(dy, dy, dx * dx) > %s)) m |= %uu; }\n",
+             posx(tg).c_str(), fl(pl->tcull[sn.tg_begin + q].x).c_str(), 1u << q);
+      }
+      outf(s, "    wcol[%d * TE] = __uint_as_float(m);\n", mrow);
+      outf(s, "    if (m && ok) { float sn_, cs_; sincosf(%s, &sn_, &cs_); wcol[%d * TE] = cs_; wcol[%d * TE] = sn_;\n"
+              "      queue[%d * TE + atomicAdd(qn + %d, 1)] = col; } }\n",
+           rotx(sn.entity).c_str(), kp.n_lmask_words + 2 * k, kp.n_lmask_words + 2 * k + 1, k, k);
+    }
+    s += "}\n";
+    s += "VB_DI void world_lidar_pass2(const KParams& kp, const float* envS, const float* workS, const int* queue, int* qn, int* rayq, int tid) {\n";
+    for (int k = 0; k < kp.n_sensors; ++k) {
+      const DSensor& sn = pl->sensors[k];
+      const int mrow = sn.tw_off - kp.row_lmask, es = lid_slot[sn.entity];
+      outf(s, "  { const int total = qn[%d] * %d;\n    for (int task = tid; task < total; task += NT) {\n", k, sn.n_rays);
+      outf(s, "      const int qi = task / %d, r = task - qi * %d, col = queue[%d * TE + qi];\n", sn.n_rays, sn.n_rays, k);
+      outf(s, "      const float* ec = envS + col; const float* wc = workS + col;\n");
+      outf(s, "      const V2 o = mk(ec[%d * TE], ec[%d * TE]);\n", 3 * es, 3 * es + 1);
+      outf(s, "      const float c0 = wc[%d * TE], s0 = wc[%d * TE];\n", kp.n_lmask_words + 2 * k, kp.n_lmask_words + 2 * k + 1);
+      outf(s, "      const float2 cs = __ldg(kp.ray_cs + %d + r);\n", sn.out_off);
+      outf(s, "      const float dc = c0 * cs.x - s0 * cs.y, ds = s0 * cs.x + c0 * cs.y;\n");
+      outf(s, "      const float aslack = fabsf(ec[%d * TE]) + 8.f;\n", 3 * es + 2);
+      outf(s, "      const uint32_t m = __float_as_uint(wc[%d * TE]);\n      bool cand = false;\n", mrow);
+      for (int q = 0; q < sn.n_targets; ++q) {
+        const int tg = pl->targets[sn.tg_begin + q], ts = lid_slot[tg];
+        const float4 tc = pl->tcull[sn.tg_begin + q];
+        outf(s, "      if (m & %uu) { const float rx = ec[%d * TE] - o.x, ry = ec[%d * TE] - o.y; const float slack = %s * aslack;\n"
+                "        const float lat = fabsf(rx * ds - ry * dc), along = rx * dc + ry * ds;\n"
+                "        cand = cand || (!(lat > %s + slack) && !(along < -(%s + slack))); }\n",
+             1u << q, 3 * ts, 3 * ts + 1, fl(tc.w).c_str(), fl(tc.y).c_str(), fl(tc.z).c_str());
+      }
+      outf(s, "      if (cand) rayq[atomicAdd(qn + NSENS, 1)] = col | (%d << 8) | (r << 16);\n    } }\n", k);
+    }
+    s += "}\n";
+  } else {
+    s += "VB_DI void world_lidar_init(float*, int) {}\n"
+         "VB_DI void world_lidar_pass1(const St&, bool, int, float*, int*, int*) {}\n"
+         "VB_DI void world_lidar_pass2(const KParams&, const float*, const float*, const int*, int*, int*, int) {}\n";
+  }
+  s += "} }\n#include \"spec_kernel.cuh\"\n";
   return s;
 }
 

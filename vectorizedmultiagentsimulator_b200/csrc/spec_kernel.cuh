@@ -6,6 +6,7 @@
 //   world_integrate(st, s, more)   integrate_r (+ begin_r of the next substep) of every dynamic entity
 //   world_store(st, sa, env)       dyn_out / act_out rows
 //   world_stage_lidar(st, env, work) px py rot (and cos/sin of non-sphere targets) of the entities the epilogue reads
+//   world_lidar_init / _pass1 / _pass2  see lidar_world below
 //
 // One thread per environment, state in registers for all substeps, no shared memory and no barrier on the physics
 // path.  The speculation protocol is the generic kernel's (kernels.cuh header): verdicts of untainted envs go to
@@ -19,6 +20,40 @@
 #pragma once
 
 namespace vb {
+
+// The LIDAR epilogue with the world's sensors as constants (the three passes of kernels.cuh lidar_epilogue, same culls,
+// same exact arithmetic for the rays that can hit):
+//   1  thread per env, straight from the registers: per sensor the mask of targets within reach (world_lidar_pass1,
+//      generated: unrolled over sensors and targets, thresholds as literals); sensors that see something are queued
+//      per sensor, so that pass 2 knows its sensor at compile time;
+//   2  per sensor, thread per (queued env, ray): ray-level cull with the approximate direction (world_lidar_pass2,
+//      generated: division by the constant ray count, unrolled targets, literal reaches); rays that may hit are queued;
+//   3  thread per queued ray: the reference's exact arithmetic (step_kernel.cuh cast_one_ray).
+// Every thread of the CTA calls it (CTA barriers inside).
+namespace gen {
+VB_DI void lidar_world(const KParams& kp, const Tile& t, const St& st, bool phys, bool ok) {
+  __shared__ int s_qn[NSENS + 1];  // queued envs per sensor; [NSENS]: queued rays
+  const int tid = threadIdx.x;
+  if (tid <= NSENS) s_qn[tid] = 0;
+  world_lidar_init(t.lidS, tid);  // every ray starts at max_range
+  if (phys) world_stage_lidar(st, t.envS + tid, t.workS + tid);
+  __syncthreads();
+  if (phys) world_lidar_pass1(st, ok, tid, t.workS + tid, t.queue, s_qn);
+  __syncthreads();
+  world_lidar_pass2(kp, t.envS, t.workS, t.queue, s_qn, t.rayq, tid);
+  __syncthreads();
+  const int nq = s_qn[NSENS];
+  for (int qi = tid; qi < nq; qi += NT) {
+    const int item = t.rayq[qi], col = item & 0xff, k = (item >> 8) & 0xff, r = item >> 16;
+    const DSensor* sn = &T_sensor<true>(kp, k);
+    const EnvT<TE> E = env_view<TE>(t, col);
+    const DEnt* se = &T_ent<true>(kp, sn->entity);
+    const float ang = __ldg(kp.ray_angles + sn->out_off + r) + ER(E, se->rot_row);  // sensors.py:117
+    t.lidS[(sn->out_off + r) * TE + col] = cast_one_ray<true>(kp, sn, E, pos_at(E, se->pos_row), ang);
+  }
+  __syncthreads();
+}
+}  // namespace gen
 
 extern "C" __global__ void __launch_bounds__(gen::NT)
 vmasb200_step_world(const __grid_constant__ KParams kp, const __grid_constant__ AgentIO aio, const __grid_constant__ StepArgs sa) {
@@ -87,9 +122,13 @@ vmasb200_step_world(const __grid_constant__ KParams kp, const __grid_constant__ 
     t.envS = smem + m.env; t.workS = smem + m.work; t.lidS = smem + m.lid;
     t.queue = reinterpret_cast<int*>(smem + m.queue); t.rayq = reinterpret_cast<int*>(smem + m.rayq);
     t.qcount = reinterpret_cast<int*>(smem + m.bar) + 2;
-    if (phys) world_stage_lidar(st, t.envS + tid, t.workS + tid);
-    __syncthreads();
-    lidar_epilogue<true, TE>(kp, t, n_valid);
+    if (LIDAR_COMPILED) {
+      lidar_world(kp, t, st, phys, ok);
+    } else {
+      if (phys) world_stage_lidar(st, t.envS + tid, t.workS + tid);
+      __syncthreads();
+      lidar_epilogue<true, TE>(kp, t, n_valid);
+    }
     // one TMA bulk store per LIDAR row; the batch's last tile also carries the padding columns up to ld
     const int n_cols = (int)min((long long)TE, (sa.env_end == sa.n_envs ? sa.ld : sa.env_end) - env0);
     const uint32_t row_bytes = (uint32_t)n_cols * 4u;
@@ -102,9 +141,13 @@ vmasb200_step_world(const __grid_constant__ KParams kp, const __grid_constant__ 
     }
   }
   // ---- last CTA of the step: verify (repair if needed), publish the verdicts, reset the scratch for the next launch
-  __threadfence();
+  // release by one thread: the barrier orders the CTA's writes before thread 0's fence (cumulativity), which orders
+  // them before its atomic - no fence per thread (ncu: stall_membar was the top stall of the small worlds)
   __syncthreads();
-  if (tid == 0) s_last = (atomicAdd(sa.counters, 1) == sa.total_ctas - 1);
+  if (tid == 0) {
+    __threadfence();
+    s_last = (atomicAdd(sa.counters, 1) == sa.total_ctas - 1);
+  }
   __syncthreads();
   if (!s_last) return;
   __threadfence();
