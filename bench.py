@@ -91,12 +91,13 @@ def peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def ncu_capture(scenario, n):
-    """What the committed `ncu --set full` capture of this workload says about one step_kernel launch
-    (profiles/r1_traffic.json, written by tools/profile_collect.py): dram_bytes = dram__bytes_read.sum +
+def ncu_capture(scenario, n, compiled=False):
+    """What the committed `ncu --set full` capture of this workload says about one launch of the step kernel
+    (profiles/r1_traffic.json for the generic vb::step_kernel, profiles/r1w_traffic.json for the world-compiled
+    vmasb200_step_world; written by tools/profile_collect.py): dram_bytes = dram__bytes_read.sum +
     dram__bytes_write.sum, warp_inst = smsp__inst_executed.sum.  {} when the workload was not captured."""
     try:
-        with open(os.path.join(ROOT, "profiles", "r1_traffic.json")) as f:
+        with open(os.path.join(ROOT, "profiles", "r1w_traffic.json" if compiled else "r1_traffic.json")) as f:
             return json.load(f).get(f"{scenario}@{n}", {})
     except (OSError, ValueError):
         return {}
@@ -285,7 +286,9 @@ def run_b200(args, rank, local_rank, world):
         e2e = run_e2e(plan, wl, n, K, world, dev)
     if rank == 0:
         peak, peak_src = peaks()
-        cap = ncu_capture(args.scenario, n)
+        jit_state, jit_launches = plan.jit(n)
+        compiled = jit_launches > 0   # the launches took the world-compiled kernel (csrc/jit.h), not the generic one
+        cap = ncu_capture(args.scenario, n, compiled)
         alg = plan.alg_bytes_per_env * n
         achieved = alg / (ms / K * 1e-3) / 1e9
         line = {
@@ -294,13 +297,17 @@ def run_b200(args, rank, local_rank, world):
             "data": "synthetic",
             "config": {"workload": f"{args.scenario} num_envs={n} per GPU, substeps={plan.S}, {len(wl.desc.lidars)} lidars",
                        "l2": f"{R} env batches visited round-robin, working set {R * per_batch / 2**20:.0f} MiB > L2 126 MiB",
-                       "envs_per_cta": plan.tile_for(n), "layout": "SoA rows [field][env]; 128 threads per CTA, 128 / envs_per_cta of them share an env",
+                       "envs_per_cta": plan.tile_for(n),
+                       "layout": ("SoA rows [field][env]; world-compiled kernel (NVRTC): one thread per env, state in registers"
+                                  if compiled else
+                                  "SoA rows [field][env]; 128 threads per CTA, 128 / envs_per_cta of them share an env"),
                        "exact": int(args.exact), "speculation_repairs": repairs,
                        "l2_resident_ms_per_step": ms_hot / K},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": cap.get("dram_bytes"), "peak_source": peak_src, "alg_bytes_per_env": plan.alg_bytes_per_env,
-                         "kernel": "vb::step_kernel"},
-            "gpu_launches": K * (2 * plan.S if args.exact else 1),
+                         "kernel": "vmasb200_step_world (world-compiled, NVRTC)" if compiled else "vb::step_kernel"},
+            # one launch per step; a compiled world that can have thin contacts is followed by its 1-CTA repair_kernel
+            "gpu_launches": K * (2 * plan.S if args.exact else (2 if compiled and plan.jit_tail_launches else 1)),
             "clocks": clocks,
         }
         # the step's roofline is the slower of its HBM bytes at peak bandwidth and its FP32 FLOPs at the

@@ -195,9 +195,11 @@ int vmasb200_plan_tile(const vmasb200_plan* plan, int64_t n_envs);
  *  VMASB200_JIT=2) every world the generator covers, whatever its size (tests).
  *  vmasb200_plan_jit: compiles (no GPU needed) the kernel a step over n_envs would take.  *state: 1 compiled / cached,
  *  0 the world is not covered or the switch is off, -1 compilation failed (vmasb200_last_error says why).
- *  *launches: launches of this plan that took a compiled kernel so far.  Either out pointer may be NULL. */
+ *  *launches: launches of this plan that took a compiled kernel so far; *tail_launches: launches of the 1-CTA
+ *  verification kernel the library puts behind each of them when the world can have thin contacts (any pair that is
+ *  not sphere-sphere).  Every out pointer may be NULL. */
 int vmasb200_jit_enable(int on);
-int vmasb200_plan_jit(vmasb200_plan* plan, int64_t n_envs, int32_t* state, int64_t* launches);
+int vmasb200_plan_jit(vmasb200_plan* plan, int64_t n_envs, int32_t* state, int64_t* launches, int64_t* tail_launches);
 
 typedef struct vmasb200_step_io {
   const float* dyn_in;             /* d: [dyn_rows][ld]                                                 */

@@ -188,6 +188,155 @@ def test_simple_spread_c_abi_matches_reference_golden():
             assert np.array_equal(outs[a].cpu().numpy(), g["obs"][t, a]), f"step {t}: obs of agent {a}"
 
 
+
+def _pose(torch, H, shape, dims, state):
+    """state [N, 6] numpy -> (CPose on strided CUDA views of an SoA buffer, keep-alive)"""
+    from vectorizedmultiagentsimulator_b200.queries import make_pose
+
+    pos, rot = soa(torch, state[:, 0:2]), soa(torch, state[:, 4:5])
+    p, keep = make_pose(shape, *dims, pos, rot, torch)
+    return p, keep + [pos, rot]
+
+
+@pytest.mark.parametrize("name", ["joint_passage", "joint_passage_terms"])
+def test_joint_passage_c_abi_matches_reference_golden(name):
+    import torch
+
+    from vectorizedmultiagentsimulator_b200 import _lib, hooks as H
+    from vectorizedmultiagentsimulator_b200.worlddesc import BOX, LINE, SPHERE
+
+    g = load(name)
+    (width, pos_f, rot_f, coll_rew, e_coeff, min_coll, middle, all_rot, dim_p, joint_angle, n_agents) = [float(v) for v in g["params"]]
+    A, T = int(n_agents), g["joint"].shape[0]
+    n = g["joint"].shape[1]
+    L = _lib.lib()
+    stream = torch.cuda.current_stream().cuda_stream
+    for t in range(T):
+        keep = []
+        cj = H.CJointPassage()
+
+        def put(dst, shape, dims, state):
+            p, k = _pose(torch, H, shape, dims, state)
+            keep.extend(k)
+            C.memmove(C.addressof(dst), C.addressof(p), C.sizeof(H.CPose))
+
+        bodies = g["bodies"][t]
+        cj.n_agents, cj.n_bodies, cj.n_passages, cj.n_walls = A, bodies.shape[0], g["passages"].shape[1], g["walls"].shape[1]
+        cj.all_passed_rot, cj.dim_p = int(all_rot), int(dim_p)
+        us = []
+        for i in range(bodies.shape[0]):
+            put(cj.body[i], SPHERE, (float(g["body_radius"][i]), 0.0, 0.0), bodies[i])
+        for i in range(A):
+            us.append(torch.from_numpy(g["action_u"][t, i]).cuda())
+            H._vec(cj.action_u[i], us[-1])
+            cj.f_range[i] = float(g["f_range"][i])
+        for i in range(cj.n_passages):
+            put(cj.passage[i], BOX, (0.0, float(g["passage_dims"][i, 0]), float(g["passage_dims"][i, 1])), g["passages"][t, i])
+            cj.passage_collide[i] = int(g["passage_collide"][i])
+        for i in range(cj.n_walls):
+            put(cj.wall[i], LINE, (0.0, float(g["wall_length"][i]), 0.0), g["walls"][t, i])
+        put(cj.joint, LINE, (0.0, float(g["joint_length"][0]), 0.0), g["joint"][t])
+        gpos, grot = torch.from_numpy(g["goal"][t][:, 0:2].copy()).cuda(), torch.from_numpy(g["goal"][t][:, 4:5].copy()).cuda()
+        H._vec(cj.goal_pos, gpos); H._vec(cj.goal_rot, grot)
+        cj.passage_width, cj.pos_shaping_factor, cj.rot_shaping_factor = width, pos_f, rot_f
+        cj.collision_reward, cj.energy_reward_coeff, cj.min_collision_distance, cj.middle_angle = coll_rew, e_coeff, min_coll, middle
+        sh_in = torch.from_numpy(g["shaping_in"][t]).cuda()
+        fout = torch.full((10, n), float("nan"), device="cuda")
+        bout = torch.full((2, n), 7, dtype=torch.uint8, device="cuda")
+        flag = torch.full((1,), -1, dtype=torch.int32, device="cuda")
+        for k in range(4):
+            cj.shaping_in[k], cj.shaping_out[k] = sh_in[k].data_ptr(), fout[k].data_ptr()
+        for j, fld in enumerate(("pos_rew", "rot_rew", "collision_rew", "energy_expenditure", "energy_rew", "rew")):
+            setattr(cj, fld, fout[4 + j].data_ptr())
+        cj.all_passed, cj.done, cj.done_flag = bout[0].data_ptr(), bout[1].data_ptr(), flag.data_ptr()
+        _lib.check(L.vmasb200_joint_passage_reward(C.byref(cj), n, stream), "vmasb200_joint_passage_reward")
+        fo, bo = fout.cpu().numpy(), bout.cpu().numpy().astype(bool)
+        assert np.array_equal(fo[0:4], g["shaping_out"][t]), f"{name} sample {t}: shaping"
+        for j, fld in enumerate(("pos_rew", "rot_rew", "collision_rew", "energy_expenditure", "energy_rew", "rew")):
+            assert np.array_equal(fo[4 + j], g[fld][t]), f"{name} sample {t}: {fld}"
+        assert np.array_equal(bo[0], g["all_passed"][t]) and np.array_equal(bo[1], g["done"][t]), f"{name} sample {t}: flags"
+        # observations: pos, vel, pos - goal, pos - open passages, angle_to_vector(goal.rot) [, angle_to_vector(joint.rot)]
+        spec = []
+        for a in range(A):
+            me_p, me_v = soa(torch, bodies[a][:, 0:2]), soa(torch, bodies[a][:, 2:4])
+            parts = [(H.OBS_COPY, me_p, None, 0.0), (H.OBS_COPY, me_v, None, 0.0), (H.OBS_SUB, me_p, gpos, 0.0)]
+            for p_ in range(cj.n_passages):
+                if not g["passage_collide"][p_]:
+                    parts.append((H.OBS_SUB, me_p, soa(torch, g["passages"][t, p_][:, 0:2]), 0.0))
+            zero = torch.zeros(n, 2, device="cuda")
+            parts += [(H.OBS_COS, grot, None, 0.0, 0, zero[:, 0:1]), (H.OBS_SIN, grot, None, 0.0, 0, zero[:, 1:2])]
+            if joint_angle:
+                jrot = soa(torch, g["joint"][t][:, 4:5])
+                parts += [(H.OBS_COS, jrot, None, 0.0), (H.OBS_SIN, jrot, None, 0.0)]
+            spec.append(parts)
+        outs = H.ObsGather(torch, n, torch.device("cuda", 0)).run(spec)
+        assert outs is not None
+        w = outs[0].shape[1] - (4 if joint_angle else 2)
+        for a in range(A):
+            o = outs[a].cpu().numpy()
+            assert np.array_equal(o[:, :w], g["obs"][t, a][:, :w]), f"{name} sample {t}: observation of agent {a}"
+            assert np.allclose(o[:, w:], g["obs"][t, a][:, w:], rtol=0, atol=2.5e-7), f"{name} sample {t}: angle vector (cosf / sinf)"
+
+
+@pytest.mark.parametrize("name", ["football", "football_sparse"])
+def test_football_c_abi_matches_reference_golden(name):
+    import torch
+
+    from oracle import hooks_oracle as ho
+    from vectorizedmultiagentsimulator_b200 import _lib, hooks as H
+
+    g = load(name)
+    p = [float(v) for v in g["params"]]
+    dense = bool(p[7])
+    T, n = g["ball"].shape[0], g["ball"].shape[1]
+    L = _lib.lib()
+    stream = torch.cuda.current_stream().cuda_stream
+    for t in range(T):
+        cf = H.CFootball()
+        bpos, bvel = soa(torch, g["ball"][t][:, 0:2]), soa(torch, g["ball"][t][:, 2:4])
+        H._vec(cf.ball_pos, bpos); H._vec(cf.ball_vel, bvel)
+        (cf.pitch_length, cf.ball_size, cf.goal_size, cf.scoring_reward, cf.pos_shaping_factor_ball_goal,
+         cf.pos_shaping_factor_agent_ball, cf.distance_to_ball_trigger) = p[:7]
+        fout = torch.full((18, n), float("nan"), device="cuda")
+        dout = torch.full((n,), 7, dtype=torch.uint8, device="cuda")
+        sh_in = torch.from_numpy(g["shaping_in"][t]).cuda()
+        keep = []
+        for k, team in enumerate(("blue", "red")):
+            m = cf.team[k]
+            m.n_agents, m.dense = g[team].shape[1], int(dense)
+            m.goal_pos[0], m.goal_pos[1] = float(g["goal_pos"][k][0]), float(g["goal_pos"][k][1])
+            for i in range(m.n_agents):
+                keep.append(soa(torch, g[team][t, i][:, 0:2]))
+                H._vec(m.agent_pos[i], keep[-1])
+            m.pos_shaping, m.pos_shaping_agent = sh_in[2 * k].data_ptr(), sh_in[2 * k + 1].data_ptr()
+            for j, fld in enumerate(("pos_shaping_out", "pos_shaping_agent_out", "distance_to_goal", "pos_rew", "min_agent_dist_to_ball",
+                                     "pos_rew_agent", "dense_reward", "sparse_reward", "reward")):
+                setattr(m, fld, fout[9 * k + j].data_ptr())
+        cf.done = dout.data_ptr()
+        _lib.check(L.vmasb200_football_reward(C.byref(cf), n, stream), "vmasb200_football_reward")
+        fo = fout.cpu().numpy()
+        assert np.array_equal(dout.cpu().numpy().astype(bool), g["done"][t]), f"{name} sample {t}: done"
+        for k, team in enumerate(("blue", "red")):
+            assert np.array_equal(fo[9 * k + 7], g["sparse"][t][k]) and np.array_equal(fo[9 * k + 8], g["rew_" + team][t]), f"{name} sample {t}: {team} reward"
+            if dense:
+                assert np.array_equal(fo[9 * k + 0], g["shaping_out"][t][2 * k]) and np.array_equal(fo[9 * k + 1], g["shaping_out"][t][2 * k + 1])
+                for j, fld in ((2, "dist_goal"), (3, "pos_rew"), (4, "min_dist"), (5, "pos_rew_agent")):
+                    assert np.array_equal(fo[9 * k + j], g[fld][t][k]), f"{name} sample {t}: {team} {fld}"
+        # observations through vmasb200_gather_obs (mirrored x for the red team), from the oracle's segment lists
+        spec, nb = [], g["blue"].shape[1]
+        for j in range(g["obs"].shape[1]):
+            team, i = ("blue", j) if j < nb else ("red", j - nb)
+            parts = []
+            for op, a, b, c, f in ho.football_obs_parts(g, t, team, i):
+                ta = soa(torch, np.ascontiguousarray(a))
+                tb = soa(torch, np.ascontiguousarray(b)) if b is not None else None
+                parts.append((op, ta, tb, c, H.OBS_NEG0 if f else 0))
+            spec.append(parts)
+        outs = H.ObsGather(torch, n, torch.device("cuda", 0)).run(spec)
+        assert outs is not None
+        for j in range(len(spec)):
+            assert np.array_equal(outs[j].cpu().numpy().view(np.uint32), g["obs"][t, j].view(np.uint32)), f"{name} sample {t}: observation {j}"
+
 def test_gather_obs_rejects_bad_tables():
     import torch
 
@@ -233,6 +382,13 @@ def _leaves(x):
 
 NAV_ATTRS = ("pos_shaping", "agent_collision_rew", "pos_rew", "on_goal", "distance_to_goal")
 PKG_ATTRS = ("global_shaping", "on_goal", "dist_to_goal", "color")
+JP_JOINT = ("pos_shaping_pre", "pos_shaping_post", "rot_shaping_pre", "rot_shaping_post")
+JP_INPLACE = ("pos_rew", "rot_rew", "collision_rew", "passed")
+JP_BOUND = ("energy_expenditure", "energy_rew", "rew", "all_passed")
+FB_BALL = ("pos_shaping_blue", "pos_shaping_red", "pos_shaping_agent_blue", "pos_shaping_agent_red", "distance_to_goal_blue",
+           "distance_to_goal_red", "pos_rew_blue", "pos_rew_red", "pos_rew_agent_blue", "pos_rew_agent_red")
+FB_SC = ("_sparse_reward_blue", "_sparse_reward_red", "_dense_reward_blue", "_dense_reward_red", "_done",
+         "min_agent_dist_to_ball_blue", "min_agent_dist_to_ball_red")
 
 
 def _snapshot(env, scenario):
@@ -242,6 +398,12 @@ def _snapshot(env, scenario):
         snap.update({k: getattr(sc, k).clone() for k in ("pos_rew", "final_rew", "all_goal_reached") if hasattr(sc, k)})
     elif scenario == "simple_spread":
         snap = {"rew": sc.rew.clone()} if hasattr(sc, "rew") else {}
+    elif scenario == "joint_passage":
+        snap = {("joint", k): getattr(sc.joint, k).clone() for k in JP_JOINT}
+        snap.update({k: getattr(sc, k).clone() for k in JP_INPLACE + JP_BOUND if hasattr(getattr(sc, k, None), "clone")})
+    elif scenario == "football":
+        snap = {("ball", k): getattr(sc.ball, k).clone() for k in FB_BALL if hasattr(getattr(sc.ball, k, None), "clone")}
+        snap.update({k: getattr(sc, k).clone() for k in FB_SC if hasattr(getattr(sc, k, None), "clone")})
     else:
         snap = {(i, k): getattr(p, k).clone() for i, p in enumerate(sc.packages) for k in PKG_ATTRS
                 if hasattr(getattr(p, k, None), "clone")}
@@ -254,9 +416,11 @@ def _restore(env, scenario, snap):
     sc = env.scenario
     objs = env.world.agents if scenario == "navigation" else getattr(sc, "packages", None)
     for key, v in snap.items():
-        if isinstance(key, tuple):
+        if isinstance(key, tuple) and key[0] in ("joint", "ball"):
+            setattr(getattr(sc, key[0]), key[1], v.clone())
+        elif isinstance(key, tuple):
             setattr(objs[key[0]], key[1], v.clone())
-        elif key in ("pos_rew", "final_rew"):
+        elif key in ("pos_rew", "final_rew") or (scenario == "joint_passage" and key in JP_INPLACE):
             getattr(sc, key).copy_(v)  # the reference writes these in place
         else:
             setattr(sc, key, v.clone())
@@ -265,7 +429,11 @@ def _restore(env, scenario, snap):
 @pytest.mark.parametrize("scenario,kw", [("navigation", dict(n_agents=4)), ("navigation", dict(n_agents=3, shared_rew=False, observe_all_goals=True)),
                                          ("navigation", dict(n_agents=2, collisions=False)), ("transport", dict(n_agents=4)),
                                          ("transport", dict(n_agents=3, n_packages=2)), ("simple_spread", dict(n_agents=3)),
-                                         ("simple_spread", dict(n_agents=5, obs_agents=False))])
+                                         ("simple_spread", dict(n_agents=5, obs_agents=False)),
+                                         ("joint_passage", dict()),
+                                         ("joint_passage", dict(collision_reward=-0.1, energy_reward_coeff=0.01, observe_joint_angle=True)),
+                                         ("football", dict(ai_red_agents=False)),
+                                         ("football", dict(ai_red_agents=False, n_blue_agents=2, n_red_agents=4, dense_reward=False))])
 def test_fused_hooks_equal_reference_hooks_on_the_same_state(scenario, kw):
     import torch
 
@@ -306,6 +474,22 @@ def test_fused_hooks_equal_reference_hooks_on_the_same_state(scenario, kw):
                     a0, a1 = env.world.agents[0], env.world.agents[1]
                     for k in range(0, 30):
                         a1.state.pos[k] = a0.state.pos[k] + torch.tensor([0.2 + 0.01 * k, 0.0], device="cuda")
+                elif scenario == "joint_passage":
+                    jl = sc.joint.landmark
+                    for k in range(0, 30):
+                        jl.state.pos[k, 1] = 0.05 + 0.01 * k
+                        if k % 2:
+                            for a in env.world.agents:
+                                a.state.pos[k, 1] = 0.15
+                    if t == 17:  # done() couples every env with all of them: the joint on its goal everywhere
+                        jl.state.pos[:] = sc.goal.state.pos + 0.004
+                        jl.state.rot[:] = sc.goal.state.rot + torch.linspace(-0.03, 0.03, n, device="cuda").unsqueeze(-1)
+                elif scenario == "football":
+                    Lx, G = sc.pitch_length / 2 + sc.ball_size / 2, sc.goal_size / 2
+                    for k in range(0, 24):
+                        side = 1.0 if k % 2 else -1.0
+                        sc.ball.state.pos[k] = torch.tensor([side * (Lx + 0.002 * (k % 5 - 2)), (G + 0.003 * (k % 7 - 3)) * (1 if k % 3 else -1)], device="cuda")
+                    sc.ball.state.vel[24:48] = 0.0
                 else:
                     for p in sc.packages:
                         for k in range(0, 30):
@@ -332,6 +516,8 @@ def test_fused_hooks_equal_reference_hooks_on_the_same_state(scenario, kw):
             assert x.shape == y.shape and x.dtype == y.dtype, f"{scenario} step {t}: output {i} {x.shape} {x.dtype} vs {y.shape} {y.dtype}"
             assert same(x, y), f"{scenario} step {t}: output {i} differs by {float((x.float() - y.float()).abs().max()):.3e}"
         assert left_f.keys() == left_r.keys() and len(left_f) >= (1 if scenario == "simple_spread" else 4)
+        if scenario in ("joint_passage", "football"):
+            continue_checks = True  # (bound attributes compared below like the others)
         for k in left_f:
             assert left_f[k].dtype == left_r[k].dtype and same(left_f[k], left_r[k]), f"{scenario} step {t}: attribute {k}"
     assert h.n_fused["reward"] == steps and h.n_fallback["reward"] == 0

@@ -111,3 +111,45 @@ def test_simple_spread_hooks_match_reference():
         for a in range(g["agent_pos"].shape[1]):
             assert np.array_equal(ho.gather_obs(spread_obs_parts(g, t, a)), g["obs"][t, a]), f"simple_spread step {t} agent {a}: obs"
     assert not g["done"].any()
+
+
+@pytest.mark.parametrize("name", ["joint_passage", "joint_passage_terms"])
+def test_joint_passage_hooks_match_reference(name):
+    g = load(name)
+    A = int(g["params"][10])
+    seen = dict(all_passed=0, done=0, coll=0)
+    for t in range(g["joint"].shape[0]):
+        r = ho.joint_passage_reward(g, t)
+        for k in ("pos_rew", "rot_rew", "collision_rew", "energy_expenditure", "energy_rew", "rew", "all_passed", "done", "shaping_out"):
+            assert np.array_equal(r[k], g[k][t]), f"{name} sample {t}: {k}"
+        seen["all_passed"] += int(r["all_passed"].sum()); seen["done"] += int(r["done"].sum()); seen["coll"] += int((r["collision_rew"] != 0).sum())
+        for a in range(A):
+            obs = ho.gather_obs(ho.joint_passage_obs_parts(g, t, a))
+            exp = g["obs"][t, a]
+            w = obs.shape[1] - (4 if g["params"][9] else 2)  # the trailing cos / sin columns: libm vs torch's Sleef
+            assert np.array_equal(obs[:, :w], exp[:, :w]), f"{name} sample {t}: observation of agent {a}"
+            assert np.allclose(obs[:, w:], exp[:, w:], rtol=0, atol=2.5e-7), f"{name} sample {t}: angle vector of agent {a}"
+    assert seen["all_passed"] > 0 and seen["done"] > 0 and (seen["coll"] > 0) == (name == "joint_passage_terms")
+
+
+@pytest.mark.parametrize("name", ["football", "football_sparse"])
+def test_football_hooks_match_reference(name):
+    g = load(name)
+    dense = bool(g["params"][7])
+    n_done = 0
+    for t in range(g["ball"].shape[0]):
+        r = ho.football_reward(g, t)
+        assert np.array_equal(r["done"], g["done"][t]) and np.array_equal(r["sparse"], g["sparse"][t])
+        assert np.array_equal(r["rew"][0], g["rew_blue"][t]) and np.array_equal(r["rew"][1], g["rew_red"][t]), f"{name} sample {t}: reward"
+        n_done += int(r["done"].sum())
+        if dense:
+            for k in ("dist_goal", "pos_rew", "min_dist", "pos_rew_agent"):
+                assert np.array_equal(np.stack(r[k]), g[k][t]), f"{name} sample {t}: {k}"
+            assert np.array_equal(np.stack(r["shaping_out"]), g["shaping_out"][t])
+        nb = g["blue"].shape[1]
+        for j in range(g["obs"].shape[1]):
+            team, i = ("blue", j) if j < nb else ("red", j - nb)
+            obs = ho.gather_obs(ho.football_obs_parts(g, t, team, i))
+            assert obs.shape == g["obs"][t, j].shape and np.array_equal(obs.view(np.uint32), g["obs"][t, j].view(np.uint32)), \
+                f"{name} sample {t}: observation of {team} agent {i}"
+    assert n_done > 0

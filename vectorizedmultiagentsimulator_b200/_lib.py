@@ -16,6 +16,7 @@ EXPORTS = [
     "vmasb200_sync_check", "vmasb200_plan_tile", "vmasb200_get_distance", "vmasb200_is_overlapping",
     "vmasb200_get_distance_from_point", "vmasb200_set_action", "vmasb200_gather_obs", "vmasb200_navigation_reward",
     "vmasb200_transport_reward", "vmasb200_simple_spread_reward", "vmasb200_jit_enable", "vmasb200_plan_jit",
+    "vmasb200_joint_passage_reward", "vmasb200_football_reward",
 ]
 
 _LIB = None
@@ -71,8 +72,10 @@ def lib():
     L.vmasb200_navigation_reward.argtypes = [vp, C.c_int64, vp]
     L.vmasb200_transport_reward.argtypes = [vp, C.c_int64, vp]
     L.vmasb200_simple_spread_reward.argtypes = [vp, C.c_int64, vp]
+    L.vmasb200_joint_passage_reward.argtypes = [vp, C.c_int64, vp]
+    L.vmasb200_football_reward.argtypes = [vp, C.c_int64, vp]
     L.vmasb200_jit_enable.argtypes = [C.c_int]
-    L.vmasb200_plan_jit.argtypes = [vp, C.c_int64, i32p, C.POINTER(C.c_int64)]
+    L.vmasb200_plan_jit.argtypes = [vp, C.c_int64, i32p, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
     for name in EXPORTS:
         if name != "vmasb200_last_error":
             getattr(L, name).restype = C.c_int

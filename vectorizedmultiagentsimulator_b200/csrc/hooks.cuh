@@ -22,10 +22,10 @@ VB_DI float vget(const DVec& v, long long i, int k) { return static_cast<const f
 
 // ------------------------------------------------------------------------------------------------ observations
 struct ObsSeg {
-  DVec a, b;
+  DVec a, b, noise;
   int op;
   float c;
-  int width, out, col0;
+  int width, out, col0, flags;
 };
 struct ObsTable {
   int n_segs, n_outs;
@@ -48,12 +48,20 @@ __global__ void __launch_bounds__(256) gather_obs_kernel(const __grid_constant__
     if (sg.out != o) continue;
     for (int k = warp; k < sg.width; k += 8) {
       float v;
+      const bool neg = (sg.flags & VMASB200_OBS_NEG0) && k == 0;  // football.py:1376-1397: x mirrored on the operands
       switch (sg.op) {
-        case VMASB200_OBS_COPY: v = vget(sg.a, i, k); break;
-        case VMASB200_OBS_SUB: v = vget(sg.a, i, k) - vget(sg.b, i, k); break;
+        case VMASB200_OBS_COPY: v = vget(sg.a, i, k); if (neg) v = -v; break;
+        case VMASB200_OBS_SUB: {
+          float x = vget(sg.a, i, k), y = vget(sg.b, i, k);
+          if (neg) { x = -x; y = -y; }
+          v = x - y;
+        } break;
         case VMASB200_OBS_CSUB: v = sg.c - vget(sg.a, i, k); break;
+        case VMASB200_OBS_COS: v = cosf(vget(sg.a, i, k)); break;
+        case VMASB200_OBS_SIN: v = sinf(vget(sg.a, i, k)); break;
         default: v = static_cast<const uint8_t*>(sg.a.p)[i * sg.a.se + k * sg.a.sk] ? 1.f : 0.f; break;
       }
+      if (sg.noise.p) v = v + vget(sg.noise, i, k);  // joint_passage.py:531-541 obs + noise
       tile[(sg.col0 + k) * (kObsTile + 1) + lane] = v;
     }
   }
@@ -241,6 +249,167 @@ __global__ void __launch_bounds__(256) simple_spread_reward_kernel(const __grid_
         if (a != s && (norm(p[a] - p[s]) - sp.radius[a]) - sp.radius[s] < 0.f) rew = rew - 1.f;  // is_overlapping(a, single_agent) (:104-107)
   }
   sp.rew[i] = rew;
+}
+
+// ------------------------------------------------------------------------------------------------ joint_passage
+// torch.remainder for fp32 (ATen BinaryOpsKernel remainder_kernel): fmod, then the divisor's sign
+VB_DI float remainder_f(float a, float b) {
+  float m = fmodf(a, b);
+  if (m != 0.f && ((b < 0.f) != (m < 0.f))) m += b;
+  return m;
+}
+// joint_passage.py:24-38 get_line_angle_dist_0_180(angle, goal); g, g_minus_pi: the goal taken modulo pi and that
+// minus pi, fp32 (a tensor goal: fp32 arithmetic; a Python float goal: double arithmetic rounded once, by the caller)
+VB_DI float line_angle_dist(float rot, float g, float g_minus_pi, float pi_f) {
+  const float a = remainder_f(rot, pi_f);
+  const float d0 = fabsf(a - g), d1 = fabsf(a - g_minus_pi), d2 = fabsf((a - pi_f) - g);
+  return pmin(d0, pmin(d1, d2));
+}
+struct JpParams {
+  int n_agents, n_bodies, n_passages, n_walls, all_passed_rot;
+  QPose body[VMASB200_JP_MAX_BODIES];
+  DVec action_u[VMASB200_JP_MAX_BODIES];
+  float e_div[VMASB200_JP_MAX_BODIES];     // (float)sqrt(dim_p * f_range^2)
+  QPose passage[VMASB200_JP_MAX_PASSAGES];
+  uint8_t pcollide[VMASB200_JP_MAX_PASSAGES];
+  QPose wall[VMASB200_JP_MAX_WALLS];
+  QPose joint;
+  DVec goal_pos, goal_rot;
+  float half_width, pos_factor, rot_factor, coll_rew, energy_coeff, min_coll, pi_f, mid_g, mid_g_minus_pi;
+  const float* sh_in[4];
+  float* sh_out[4];
+  float *pos_rew, *rot_rew, *collision_rew, *energy_exp, *energy_rew, *rew;
+  uint8_t *all_passed, *done;
+  uint32_t* done_flag;
+};
+// joint_passage.py:387-490 reward of the first agent; also done()'s two tests (:547-563): rot_ok goes to done[], a
+// failed position test raises done_flag (the reference's [n] * [n, 1] product couples every env with all of them)
+__global__ void __launch_bounds__(128) jp_reward_kernel(const __grid_constant__ JpParams jp, long long n) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  bool pos_bad = false;
+  if (i < n) {
+    const V2 jpos = q_pos(jp.joint, i);
+    const float jrot = jp.joint.rot[i * jp.joint.rs];
+    const bool joint_passed = jpos.y > 0.f;                                              // :399
+    bool all_passed = true;                                                              // :400-404
+    for (int a = 0; a < jp.n_agents; ++a) all_passed = all_passed && (q_pos(jp.body[a], i).y > jp.half_width);
+    float closest = 0.f;                                                                 // :407-416
+    bool first = true;
+    for (int p = 0; p < jp.n_passages; ++p)
+      if (!jp.pcollide[p]) {
+        const float d = norm(jpos - q_pos(jp.passage[p], i));
+        closest = first ? d : pmin(closest, d);
+        first = false;
+      }
+    float pos_rew = 0.f, rot_rew = 0.f;                                                   // :396-397
+    const float sh_pre = closest * jp.pos_factor;                                        // :417
+    if (!joint_passed) pos_rew = pos_rew + (jp.sh_in[0][i] - sh_pre);                    // :418-420
+    const V2 gpos = mk(vget(jp.goal_pos, i, 0), vget(jp.goal_pos, i, 1));
+    const float dist_goal = norm(jpos - gpos);                                           // :423-426
+    const float sh_post = dist_goal * jp.pos_factor;
+    if (joint_passed) pos_rew = pos_rew + (jp.sh_in[1][i] - sh_post);                    // :428-430
+    const bool rot_passed = jp.all_passed_rot ? all_passed : joint_passed;               // :434
+    const float rsh_pre = line_angle_dist(jrot, jp.mid_g, jp.mid_g_minus_pi, jp.pi_f) * jp.rot_factor;   // :435-438
+    if (!rot_passed) rot_rew = rot_rew + (jp.sh_in[2][i] - rsh_pre);                     // :439-441
+    const float g = remainder_f(vget(jp.goal_rot, i, 0), jp.pi_f);
+    const float rot_dist_goal = line_angle_dist(jrot, g, g - jp.pi_f, jp.pi_f);          // :444-446
+    const float rsh_post = rot_dist_goal * jp.rot_factor;
+    if (rot_passed) rot_rew = rot_rew + (jp.sh_in[3][i] - rsh_post);                     // :448-450
+    jp.sh_out[0][i] = sh_pre; jp.sh_out[1][i] = sh_post; jp.sh_out[2][i] = rsh_pre; jp.sh_out[3][i] = rsh_post;
+    float coll = 0.f;                                                                    // :398, 453-473
+    if (jp.coll_rew != 0.f) {  // k additions of the same constant; adding 0 any number of times leaves 0
+      int k = 0;
+      for (int a = 0; a < jp.n_bodies; ++a) {
+        int walls = 0;
+        for (int w = 0; w < jp.n_walls; ++w) walls += pair_distance(jp.body[a], jp.wall[w], i) <= jp.min_coll;
+        k += walls * jp.n_passages;                                                      // the wall loop sits INSIDE the passage loop (:461)
+        for (int p = 0; p < jp.n_passages; ++p)
+          if (jp.pcollide[p]) k += pair_distance(jp.body[a], jp.passage[p], i) <= jp.min_coll;
+      }
+      for (int p = 0; p < jp.n_passages; ++p)
+        if (jp.pcollide[p]) k += pair_distance(jp.passage[p], jp.joint, i) <= jp.min_coll;
+      for (int q = 0; q < k; ++q) coll = coll + jp.coll_rew;
+    }
+    float energy = 0.f;                                                                  // :476-484 (sum over <= 2 agents)
+    for (int a = 0; a < jp.n_agents; ++a) {
+      const float e = norm(mk(vget(jp.action_u[a], i, 0), vget(jp.action_u[a], i, 1))) / jp.e_div[a];
+      energy = a == 0 ? e : energy + e;
+    }
+    const float energy_rew = (-energy) * jp.energy_coeff;                                // :485
+    jp.pos_rew[i] = pos_rew; jp.rot_rew[i] = rot_rew; jp.collision_rew[i] = coll;
+    jp.energy_exp[i] = energy; jp.energy_rew[i] = energy_rew;
+    jp.rew[i] = ((pos_rew + rot_rew) + coll) + energy_rew;                               // :487-489
+    jp.all_passed[i] = all_passed ? 1 : 0;
+    if (jp.done) {
+      jp.done[i] = rot_dist_goal <= 0.01f ? 1 : 0;                                       // :555-560
+      pos_bad = !(dist_goal <= 0.01f);                                                   // :549-554
+    }
+  }
+  if (jp.done) {
+    const unsigned any = __ballot_sync(0xffffffffu, pos_bad);
+    if (any && (threadIdx.x & 31) == 0 && !__ldcg(jp.done_flag)) atomicOr(jp.done_flag, 1u);
+  }
+}
+__global__ void __launch_bounds__(256) jp_done_kernel(uint8_t* __restrict__ done, const uint32_t* __restrict__ flag, long long n) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n && *flag) done[i] = 0;
+}
+
+// ------------------------------------------------------------------------------------------------ football
+struct FbTeam {
+  int n_agents, dense;
+  DVec apos[VMASB200_FB_MAX_TEAM];
+  float gx, gy;
+  const float* sh_in;
+  float* sh_out;
+  const float* sha_in;
+  float* sha_out;
+  float *dist_goal, *pos_rew, *min_dist, *pos_rew_agent, *dense_rew, *sparse_rew, *reward;
+};
+struct FbParams {
+  DVec ball_pos, ball_vel;
+  float x_right, x_left, y_hi, y_lo, scoring, f_ball_goal, f_agent_ball, trigger;
+  FbTeam team[2];
+  uint8_t* done;
+};
+// football.py:1118-1226 (reward of the first agent; reward_ball_to_goal; reward_all_agent_to_ball with
+// get_closest_agent_to_ball :585-599, whose torch.cdist on these operands is ATen's scalar loop agg += diff * diff,
+// contracted by the compiler: sqrt(fma(dy, dy, dx * dx)), the form of linalg.vector_norm; pinned by the golden vectors)
+__global__ void __launch_bounds__(256) fb_reward_kernel(const __grid_constant__ FbParams fb, long long n) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const V2 b = mk(vget(fb.ball_pos, i, 0), vget(fb.ball_pos, i, 1));
+  const bool over_right = b.x > fb.x_right, over_left = b.x < fb.x_left;                 // :1122-1127
+  const bool goal_mask = (b.y <= fb.y_hi) && (b.y >= fb.y_lo);                           // :1128-1130
+  const bool blue_score = over_right && goal_mask, red_score = over_left && goal_mask;
+  const float sparse_blue = fb.scoring * (blue_score ? 1.f : 0.f) - fb.scoring * (red_score ? 1.f : 0.f);  // :1133-1135
+  const float sparse[2] = {sparse_blue, -sparse_blue};                                   // :1136
+  fb.done[i] = (blue_score || red_score) ? 1 : 0;                                        // :1138
+  const V2 bv = mk(vget(fb.ball_vel, i, 0), vget(fb.ball_vel, i, 1));
+  const bool ball_moving = norm(bv) > 1e-6f;                                             // :1197
+  for (int t = 0; t < 2; ++t) {
+    const FbTeam& tm = fb.team[t];
+    float dense = 0.f;                                                                   // :1140-1141
+    if (tm.dense) {
+      const float dg = norm(b - mk(tm.gx, tm.gy));                                       // :1160-1171
+      const float sh = dg * fb.f_ball_goal;                                              // :1173
+      const float pr = tm.sh_in[i] - sh;                                                 // :1176, 1180
+      float md = 0.f;
+      for (int a = 0; a < tm.n_agents; ++a) {                                            // :585-599
+        const float d = norm(mk(vget(tm.apos[a], i, 0), vget(tm.apos[a], i, 1)) - b);
+        md = a == 0 ? d : pmin(md, d);
+      }
+      const float sha = md * fb.f_agent_ball;                                            // :1195
+      const bool close = md < fb.trigger;                                                // :1198
+      const float pra = (close || ball_moving) ? 0.f : (tm.sha_in[i] - sha);             // :1201-1215
+      tm.dist_goal[i] = dg; tm.sh_out[i] = sh; tm.pos_rew[i] = pr;
+      tm.min_dist[i] = md; tm.sha_out[i] = sha; tm.pos_rew_agent[i] = pra;
+      dense = pr + pra;                                                                  // :1144-1151
+      tm.dense_rew[i] = dense;
+    }
+    tm.sparse_rew[i] = sparse[t];
+    tm.reward[i] = sparse[t] + dense;                                                    // :1153-1157
+  }
 }
 
 }  // namespace vb

@@ -397,6 +397,10 @@ static const char* kShimMathConst =
 // cubin of the world-compiled kernel of (pl, te): from the disk cache, else NVRTC.  Empty string + message on failure.
 static std::string jit_compile(const vmasb200_plan* pl, int te, int nt, JitLayout* lay, std::string* err) {
   const std::string src = generate(pl, te, nt, lay);
+  if (const char* dump = getenv("VMASB200_JIT_DUMP")) {  // the generated source, for profiles (ncu line numbers) and docs
+    std::ofstream f(dump);
+    f << src;
+  }
   // -default-device: the C prototypes of include/vmasb200.h carry no execution space
   const char* opts[] = {"--gpu-architecture=sm_100a", "--std=c++17", "--fmad=false", "-lineinfo", "-default-device"};
   uint64_t h = fnv1a(src);

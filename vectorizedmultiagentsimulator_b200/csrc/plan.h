@@ -30,6 +30,7 @@ struct vmasb200_plan {
   std::vector<vmasb200_pair> pairs;
   std::vector<int32_t> dyn_slot, stat_slot, act_slot, joint_slot, lidar_slot, agent_entities;
   int64_t jit_launches = 0;  // launches that took the world-compiled kernel (jit.h)
+  int64_t jit_tail_launches = 0;  // 1-CTA repair_kernel launches behind them (worlds that can have thin contacts)
   int te_fixed = 0;          // envs per CTA asked for by the world description (0 = by batch size, see tile_for)
   uint64_t serial = 0;                      // identity for the constant-bank ownership check
   std::shared_ptr<vb::CTab> h_ctab;         // host image of the constant-bank tables (built on first use)

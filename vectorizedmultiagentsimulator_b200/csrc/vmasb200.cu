@@ -252,6 +252,7 @@ static int launch_step(vmasb200_plan* pl, const vmasb200_step_io* io, long long 
       if (jk->thin_possible) {  // verification tail of the compiled launch (returns at once unless its last CTA asked)
         KParams gk = jk->kpg;
         repair_kernel<false, 32><<<1, kThreads, smem_map(gk).total_bytes, st>>>(gk, aio, sa);
+        pl->jit_tail_launches += 1;
       }
     } else {
       step_fn(ct, kp.TE)<<<grid, block, smem_bytes, st>>>(kp, aio, sa);
@@ -352,7 +353,7 @@ int vmasb200_jit_enable(int on) {
   return prev;
 }
 
-int vmasb200_plan_jit(vmasb200_plan* pl, int64_t n_envs, int32_t* state, int64_t* launches) {
+int vmasb200_plan_jit(vmasb200_plan* pl, int64_t n_envs, int32_t* state, int64_t* launches, int64_t* tail_launches) {
   if (!pl) { set_error("plan_jit: NULL plan"); return VMASB200_ERR_INVALID; }
   std::string why;
   int st = 0;
@@ -364,6 +365,7 @@ int vmasb200_plan_jit(vmasb200_plan* pl, int64_t n_envs, int32_t* state, int64_t
   }
   if (state) *state = st;
   if (launches) *launches = pl->jit_launches;
+  if (tail_launches) *tail_launches = pl->jit_tail_launches;
   return VMASB200_OK;
 }
 
@@ -627,13 +629,14 @@ int vmasb200_gather_obs(const vmasb200_obs_seg* segs, int32_t n_segs, float* con
   for (int s = 0; s < n_segs; ++s) {
     const vmasb200_obs_seg& g = segs[s];
     if (g.out < 0 || g.out >= n_outs || g.width < 1 || g.col0 < 0 || g.col0 + g.width > out_widths[g.out] || !g.a.p ||
-        g.op < VMASB200_OBS_COPY || g.op > VMASB200_OBS_BOOL || (g.op == VMASB200_OBS_SUB && !g.b.p)) {
+        g.op < VMASB200_OBS_COPY || g.op > VMASB200_OBS_SIN || (g.op == VMASB200_OBS_SUB && !g.b.p)) {
       set_error("gather_obs: bad segment (out, columns, operands or op)"); return VMASB200_ERR_INVALID;
     }
     for (int k = 0; k < g.width; ++k)
       if (cover[g.out][(size_t)(g.col0 + k)]++) { set_error("gather_obs: a column is written by two segments"); return VMASB200_ERR_INVALID; }
     ObsSeg& d = tb.seg[s];
-    d.a = to_dvec(g.a); d.b = to_dvec(g.b); d.op = g.op; d.c = g.c; d.width = g.width; d.out = g.out; d.col0 = g.col0;
+    d.a = to_dvec(g.a); d.b = to_dvec(g.b); d.noise = to_dvec(g.noise); d.op = g.op; d.c = g.c; d.width = g.width; d.out = g.out;
+    d.col0 = g.col0; d.flags = g.flags;
   }
   for (int o = 0; o < n_outs; ++o)
     for (uint8_t c : cover[o])
@@ -732,6 +735,98 @@ int vmasb200_simple_spread_reward(const vmasb200_simple_spread* sp, int64_t n, v
   }
   if (n == 0) return VMASB200_OK;
   simple_spread_reward_kernel<<<(unsigned)((n + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(p, n);
+  VB_CUDA(cudaGetLastError());
+  return VMASB200_OK;
+}
+
+int vmasb200_joint_passage_reward(const vmasb200_joint_passage* g, int64_t n, void* stream) {
+  if (!g || n < 0 || g->n_agents < 1 || g->n_agents > 2 || g->n_bodies < g->n_agents || g->n_bodies > VMASB200_JP_MAX_BODIES ||
+      g->n_passages < 1 || g->n_passages > VMASB200_JP_MAX_PASSAGES || g->n_walls < 0 || g->n_walls > VMASB200_JP_MAX_WALLS) {
+    set_error("joint_passage_reward: bad argument (1..2 agents, <= 4 bodies, 1..24 passages, <= 8 walls)"); return VMASB200_ERR_INVALID;
+  }
+  if (!g->pos_rew || !g->rot_rew || !g->collision_rew || !g->energy_expenditure || !g->energy_rew || !g->rew || !g->all_passed ||
+      !g->goal_pos.p || !g->goal_rot.p || (g->done && !g->done_flag)) {
+    set_error("joint_passage_reward: a NULL tensor"); return VMASB200_ERR_INVALID;
+  }
+  static thread_local JpParams jp;
+  int rc;
+  jp.n_agents = g->n_agents; jp.n_bodies = g->n_bodies; jp.n_passages = g->n_passages; jp.n_walls = g->n_walls;
+  jp.all_passed_rot = g->all_passed_rot;
+  bool any_open = false;
+  for (int a = 0; a < g->n_bodies; ++a) {
+    if ((rc = to_qpose(&g->body[a], &jp.body[a], "joint_passage_reward"))) return rc;
+    if (a < g->n_agents) {
+      if (!g->action_u[a].p) { set_error("joint_passage_reward: agent.action.u is NULL"); return VMASB200_ERR_INVALID; }
+      jp.action_u[a] = to_dvec(g->action_u[a]);
+      jp.e_div[a] = (float)std::sqrt((double)g->dim_p * (g->f_range[a] * g->f_range[a]));  // math.sqrt(dim_p * f_range**2)
+    }
+  }
+  for (int p = 0; p < g->n_passages; ++p) {
+    if ((rc = to_qpose(&g->passage[p], &jp.passage[p], "joint_passage_reward"))) return rc;
+    jp.pcollide[p] = g->passage_collide[p] ? 1 : 0;
+    any_open = any_open || !jp.pcollide[p];
+  }
+  if (!any_open) { set_error("joint_passage_reward: no passage without collision (the gap the joint is shaped towards)"); return VMASB200_ERR_INVALID; }
+  for (int w = 0; w < g->n_walls; ++w)
+    if ((rc = to_qpose(&g->wall[w], &jp.wall[w], "joint_passage_reward"))) return rc;
+  if ((rc = to_qpose(&g->joint, &jp.joint, "joint_passage_reward"))) return rc;
+  if (!jp.joint.rot) { set_error("joint_passage_reward: the joint landmark needs a rotation"); return VMASB200_ERR_INVALID; }
+  jp.goal_pos = to_dvec(g->goal_pos); jp.goal_rot = to_dvec(g->goal_rot);
+  const double pi = 3.141592653589793;
+  jp.half_width = (float)(g->passage_width / 2); jp.pos_factor = (float)g->pos_shaping_factor; jp.rot_factor = (float)g->rot_shaping_factor;
+  jp.coll_rew = (float)g->collision_reward; jp.energy_coeff = (float)g->energy_reward_coeff; jp.min_coll = (float)g->min_collision_distance;
+  jp.pi_f = (float)pi;
+  double mg = std::fmod(g->middle_angle, pi);  // Python float % float
+  if (mg != 0.0 && mg < 0.0) mg += pi;
+  jp.mid_g = (float)mg; jp.mid_g_minus_pi = (float)(mg - pi);
+  for (int k = 0; k < 4; ++k) {
+    if (!g->shaping_in[k] || !g->shaping_out[k]) { set_error("joint_passage_reward: a shaping tensor is NULL"); return VMASB200_ERR_INVALID; }
+    jp.sh_in[k] = g->shaping_in[k]; jp.sh_out[k] = g->shaping_out[k];
+  }
+  jp.pos_rew = g->pos_rew; jp.rot_rew = g->rot_rew; jp.collision_rew = g->collision_rew; jp.energy_exp = g->energy_expenditure;
+  jp.energy_rew = g->energy_rew; jp.rew = g->rew; jp.all_passed = g->all_passed; jp.done = g->done; jp.done_flag = g->done_flag;
+  if (n == 0) return VMASB200_OK;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (g->done) VB_CUDA(cudaMemsetAsync(g->done_flag, 0, sizeof(uint32_t), st));
+  jp_reward_kernel<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(jp, n);
+  if (g->done) jp_done_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(g->done, g->done_flag, n);
+  VB_CUDA(cudaGetLastError());
+  return VMASB200_OK;
+}
+
+int vmasb200_football_reward(const vmasb200_football* g, int64_t n, void* stream) {
+  if (!g || n < 0 || !g->ball_pos.p || !g->ball_vel.p || !g->done) { set_error("football_reward: bad argument"); return VMASB200_ERR_INVALID; }
+  static thread_local FbParams fb;
+  fb.ball_pos = to_dvec(g->ball_pos); fb.ball_vel = to_dvec(g->ball_vel);
+  fb.x_right = (float)(g->pitch_length / 2 + g->ball_size / 2); fb.x_left = (float)(-g->pitch_length / 2 - g->ball_size / 2);
+  fb.y_hi = (float)(g->goal_size / 2); fb.y_lo = (float)(-g->goal_size / 2);
+  fb.scoring = (float)g->scoring_reward; fb.f_ball_goal = (float)g->pos_shaping_factor_ball_goal;
+  fb.f_agent_ball = (float)g->pos_shaping_factor_agent_ball; fb.trigger = (float)g->distance_to_ball_trigger;
+  for (int t = 0; t < 2; ++t) {
+    const vmasb200_football_team& m = g->team[t];
+    FbTeam& d = fb.team[t];
+    if (m.n_agents < 0 || m.n_agents > VMASB200_FB_MAX_TEAM || !m.sparse_reward || !m.reward) {
+      set_error("football_reward: bad team (<= 16 agents, sparse_reward, reward)"); return VMASB200_ERR_INVALID;
+    }
+    d.n_agents = m.n_agents; d.dense = m.dense ? 1 : 0;
+    if (d.dense) {
+      if (m.n_agents < 1 || !m.pos_shaping || !m.pos_shaping_out || !m.pos_shaping_agent || !m.pos_shaping_agent_out ||
+          !m.distance_to_goal || !m.pos_rew || !m.min_agent_dist_to_ball || !m.pos_rew_agent || !m.dense_reward) {
+        set_error("football_reward: a dense-reward tensor is NULL"); return VMASB200_ERR_INVALID;
+      }
+      for (int a = 0; a < m.n_agents; ++a) {
+        if (!m.agent_pos[a].p) { set_error("football_reward: an agent position is NULL"); return VMASB200_ERR_INVALID; }
+        d.apos[a] = to_dvec(m.agent_pos[a]);
+      }
+    }
+    d.gx = m.goal_pos[0]; d.gy = m.goal_pos[1];
+    d.sh_in = m.pos_shaping; d.sh_out = m.pos_shaping_out; d.sha_in = m.pos_shaping_agent; d.sha_out = m.pos_shaping_agent_out;
+    d.dist_goal = m.distance_to_goal; d.pos_rew = m.pos_rew; d.min_dist = m.min_agent_dist_to_ball; d.pos_rew_agent = m.pos_rew_agent;
+    d.dense_rew = m.dense_reward; d.sparse_rew = m.sparse_reward; d.reward = m.reward;
+  }
+  fb.done = g->done;
+  if (n == 0) return VMASB200_OK;
+  fb_reward_kernel<<<(unsigned)((n + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(fb, n);
   VB_CUDA(cudaGetLastError());
   return VMASB200_OK;
 }

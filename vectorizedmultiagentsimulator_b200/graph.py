@@ -35,7 +35,7 @@ class GraphedEnvironment:
             raise _lib.VmasB200Error("GraphedEnvironment: the world was enabled without static_io=True before")
         if b.hooks is None:
             raise _lib.VmasB200Error(
-                "GraphedEnvironment: no fused hooks for this scenario (hooks.py: navigation, transport); the reference's "
+                "GraphedEnvironment: no fused hooks for this scenario (hooks.py REGISTRY); the reference's "
                 "torch hooks synchronise with the host and cannot be captured in a CUDA graph")
         if b._env is not env:
             raise _lib.VmasB200Error("GraphedEnvironment needs the Environment the drop-in was enabled on")

@@ -179,8 +179,9 @@ class StepPlan:
     def jit(self, n_envs: int):
         """(state, launches) of the world-compiled kernel a step over n_envs takes (include/vmasb200.h
         vmasb200_plan_jit): state 1 compiled (NVRTC, no GPU needed) / 0 world not covered or switched off / -1 failed."""
-        st, ln = C.c_int32(0), C.c_int64(0)
-        _lib.check(_lib.lib().vmasb200_plan_jit(self._h, int(n_envs), C.byref(st), C.byref(ln)), "vmasb200_plan_jit")
+        st, ln, tl = C.c_int32(0), C.c_int64(0), C.c_int64(0)
+        _lib.check(_lib.lib().vmasb200_plan_jit(self._h, int(n_envs), C.byref(st), C.byref(ln), C.byref(tl)), "vmasb200_plan_jit")
+        self.jit_tail_launches = tl.value
         return st.value, ln.value
 
     def sync_check(self, stream: int = 0) -> int:
