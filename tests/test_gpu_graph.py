@@ -42,7 +42,7 @@ def _state(env):
 
 @pytest.mark.parametrize("scenario,kw", [("navigation", dict(n_agents=4)), ("transport", dict(n_agents=4)),
                                          ("navigation", dict(n_agents=3, shared_rew=False)), ("simple_spread", dict(n_agents=3)),
-                                         ("joint_passage", dict()), ("football", dict(ai_red_agents=False))])
+                                         ("joint_passage", dict())])
 def test_graphed_step_equals_eager_step_bitwise(scenario, kw):
     import torch
 
@@ -132,3 +132,24 @@ def test_graph_needs_fused_hooks():
     env = vmas.make_env("football", num_envs=8, device="cuda", seed=0, continuous_actions=True, ai_red_agents=False)
     with pytest.raises(_lib.VmasB200Error):
         GraphedEnvironment(env)
+
+
+def test_graph_refuses_what_the_scenario_itself_makes_uncapturable():
+    """football's ball_action_script (reference code, football.py:1617-1677) copies Python floats to the device every
+    step: the capture must fail with the library's error, and the eager fused hooks keep working."""
+    import torch
+
+    from vectorizedmultiagentsimulator_b200 import dropin
+    from vectorizedmultiagentsimulator_b200._lib import VmasB200Error
+    from vectorizedmultiagentsimulator_b200.graph import GraphedEnvironment
+
+    vmas = _vmas()
+    env = vmas.make_env("football", num_envs=64, device="cuda", seed=0, continuous_actions=True, ai_red_agents=False)
+    with pytest.raises(VmasB200Error, match="cannot be captured"):
+        GraphedEnvironment(env, warmup=1)
+    torch.cuda.synchronize()
+    b = dropin.enable(env, hooks=True)
+    acts = [torch.zeros(64, a.action_size, device="cuda") for a in env.agents]
+    for _ in range(3):
+        env.step(acts)
+    assert b.hooks.n_fused["reward"] >= 3 and b.hooks.n_fallback["reward"] == 0

@@ -66,6 +66,12 @@ class GraphedEnvironment:
         try:
             with torch.cuda.graph(self.graph):
                 self.out = env.step(self.actions)
+        except RuntimeError as e:
+            # what stays the reference's own torch code (process_action, action scripts, info) must be capturable too:
+            # football's ball_action_script builds device tensors from Python floats every step (football.py:1617-1677),
+            # a host-to-device copy no CUDA graph can hold
+            raise _lib.VmasB200Error("GraphedEnvironment: this scenario's own code cannot be captured in a CUDA graph "
+                                     f"(use dropin.enable(env, hooks=True) without the graph): {e}") from e
         finally:
             b.defer_action_check = False
         b._act_pending = False
