@@ -93,14 +93,18 @@ def peaks():
 
 def ncu_capture(scenario, n, compiled=False):
     """What the committed `ncu --set full` capture of this workload says about one launch of the step kernel
-    (profiles/r1_traffic.json for the generic vb::step_kernel, profiles/r1w_traffic.json for the world-compiled
-    vmasb200_step_world; written by tools/profile_collect.py): dram_bytes = dram__bytes_read.sum +
-    dram__bytes_write.sum, warp_inst = smsp__inst_executed.sum.  {} when the workload was not captured."""
-    try:
-        with open(os.path.join(ROOT, "profiles", "r1w_traffic.json" if compiled else "r1_traffic.json")) as f:
-            return json.load(f).get(f"{scenario}@{n}", {})
-    except (OSError, ValueError):
-        return {}
+    (profiles/r1w_traffic.json, else the earlier profiles/r1_traffic.json; written by tools/profile_collect.py):
+    dram_bytes = dram__bytes_read.sum + dram__bytes_write.sum, warp_inst = smsp__inst_executed.sum.  Only a capture of
+    the SAME kernel counts (world-compiled vmasb200_step_world or generic vb::step_kernel); {} when there is none."""
+    for name in ("r1w_traffic.json", "r1_traffic.json"):
+        try:
+            with open(os.path.join(ROOT, "profiles", name)) as f:
+                cap = json.load(f).get(f"{scenario}@{n}", {})
+        except (OSError, ValueError):
+            continue
+        if cap and ("vmasb200_step_world" in cap.get("kernel", "step_kernel")) == bool(compiled):
+            return cap
+    return {}
 
 
 def alg_flops_per_env(plan, desc):

@@ -68,32 +68,42 @@ def main():
         except ValueError:
             print("skipping (not a JSON line):", p, line[:120])
             continue
-        arm = name.startswith(("reference", "dropin"))
+        arm = name.startswith(("reference", "dropin", "generic"))
         with open(os.path.join(dst, f"{tag}_{name}.json" if arm else f"{tag}_bench_{name}.json"), "w") as f:
             f.write(line + "\n")
     lp = os.path.join(src, "launches_navigation.csv")
     if os.path.exists(lp):
         launches(lp, os.path.join(dst, f"{tag}_launches_navigation.txt"))
+    # tools/profile_lines.sh reduced every capture on the box: step_kernel_<wl>.txt (raw-page summary, first line = kernel
+    # name) and <wl>_lines.txt (per-source-line cost).  The kernel's DRAM bytes / warp instructions per launch go to
+    # <tag>_traffic.json, which bench.py reads for roofline.traffic / roofline.issue.
     traffic = {}
-    for rep in sorted(glob.glob(os.path.join(src, "step_kernel_*.ncu-rep"))):
-        wl = os.path.basename(rep)[len("step_kernel_"):-len(".ncu-rep")]
-        summ = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "ncu_summary.py"), rep], capture_output=True, text=True).stdout
+    for summ in sorted(glob.glob(os.path.join(src, "step_kernel_*.txt"))):
+        wl = os.path.basename(summ)[len("step_kernel_"):-len(".txt")]
+        text = open(summ).read()
+        kname = text.splitlines()[0].strip("# ") if text else ""
         with open(os.path.join(dst, f"{tag}_step_kernel_{wl}.txt"), "w") as f:
-            f.write(f"# ncu --set full --import-source on --clock-control none -k regex:step_kernel -s 6 -c 1 (bench.py, workload {wl})\n" + summ)
-        m = raw_metrics(rep)
-        grid = int(m["launch__grid_size"][0].replace(",", ""))
-        kname = summ.splitlines()[0] if summ else ""
-        te = re.search(r"step_kernel<\d, (\d+)>", kname)
-        sel = f"step_kernelILb1ELi{te.group(1)}" if te else "step_kernel"
-        lines = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "ncu_lines.py"), rep, SO, sel], capture_output=True, text=True).stdout
-        with open(os.path.join(dst, f"{tag}_{wl}_lines.txt"), "w") as f:
-            f.write(f"# tools/ncu_lines.py on the same capture ({kname.strip('# ')})\n" + lines)
-        rd, wr = to_bytes(*m["dram__bytes_read.sum"]), to_bytes(*m["dram__bytes_write.sum"])
-        scen, n = (wl[:-3], 1048576) if wl.endswith("_1m") else (wl, 32768)
-        traffic[f"{scen}@{n}"] = {"dram_bytes": rd + wr, "dram_read": rd, "dram_write": wr, "grid": grid,
-                                  "warp_inst": float(m["smsp__inst_executed.sum"][0].replace(",", "")),
-                                  "duration": " ".join(m["gpu__time_duration.sum"]),
-                                  "source": f"profiles/{tag}_step_kernel_{wl}.txt"}
+            f.write(f"# ncu --set full --import-source on --clock-control none -k 'regex:step_kernel|vmasb200_step_world' -s 6 -c 1 (bench.py, workload {wl})\n" + text)
+        lp = os.path.join(src, f"{wl}_lines.txt")
+        if os.path.exists(lp):
+            with open(os.path.join(dst, f"{tag}_{wl}_lines.txt"), "w") as f:
+                f.write(f"# tools/ncu_lines.py on the same capture ({kname})\n" + open(lp).read())
+
+        def metric(name):
+            m = re.search(r"^" + re.escape(name) + r" \[(\w*)\]: ([\d.,]+)", text, re.M)
+            return (m.group(2), m.group(1)) if m else None
+
+        rd, wr, inst, dur, grid = (metric(k) for k in ("dram__bytes_read.sum", "dram__bytes_write.sum", "smsp__inst_executed.sum",
+                                                       "gpu__time_duration.sum", "launch__grid_size"))
+        if not (rd and wr and inst):
+            continue
+        m = re.match(r"(.*)_(\d+)$", wl)
+        scen, n = (m.group(1), int(m.group(2))) if m else (wl, 32768)
+        rdb, wrb = to_bytes(*rd), to_bytes(*wr)
+        traffic[f"{scen}@{n}"] = {"dram_bytes": rdb + wrb, "dram_read": rdb, "dram_write": wrb,
+                                  "grid": int(float(grid[0].replace(",", ""))) if grid else None,
+                                  "warp_inst": float(inst[0].replace(",", "")), "duration": " ".join(dur) if dur else None,
+                                  "kernel": kname, "source": f"profiles/{tag}_step_kernel_{wl}.txt"}
     if traffic:
         with open(os.path.join(dst, f"{tag}_traffic.json"), "w") as f:
             json.dump(traffic, f, indent=1, sort_keys=True)
