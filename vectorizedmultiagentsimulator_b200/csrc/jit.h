@@ -294,12 +294,57 @@ static std::string generate(const vmasb200_plan* pl, int te, int nt, JitLayout* 
   }
   s += "}\n";
   // ---- LIDAR epilogue with the sensors as constants (spec_kernel.cuh lidar_world) when every sensor's target mask is
-  // one word; else the generic epilogue runs on the compact tile
+  // one word and the queue entries fit 16 bits; else the generic epilogue runs on the compact tile.
+  //   pair entry  col | p << CB             p: index of (sensor, target) in the plan's target list
+  //   ray entry   col | k << CB | r << (CB + KB)
+  // both queues live in the tile's queue + rayq regions ((NS + R) * TE words): NPT * TE + R * TE 16-bit entries.
+  auto bits = [](int n) { int b = 0; while ((1 << b) < n) ++b; return b; };
+  const int NPT = (int)pl->targets.size(), R = kp.lidar_rows, NS = kp.n_sensors;
+  const int CB = bits(te), KB = bits(std::max(NS, 1)), RB = bits(std::max(kp.max_rays, 1)), PB = bits(std::max(NPT, 1));
   bool lc = lidar;
   for (const DSensor& sn : pl->sensors) lc = lc && sn.n_tw == 1 && sn.n_targets >= 1 && sn.n_rays >= 1;
-  lc = lc && te <= 256 && kp.n_sensors <= 255;
-  outf(s, "constexpr bool LIDAR_COMPILED = %s;\nconstexpr int NSENS = %d;\n", lc ? "true" : "false", std::max(kp.n_sensors, 1));
+  lc = lc && (te & (te - 1)) == 0 && CB + KB + RB <= 16 && CB + PB <= 16 && NPT <= 2 * NS + R;
+  outf(s, "constexpr bool LIDAR_COMPILED = %s;\n", lc ? "true" : "false");
   if (lc) {
+    outf(s, "constexpr int NPT = %d, CB = %d, KB = %d, RAYS_TOTAL = %d;\n", NPT, CB, KB, R);
+    // per (sensor, target) tables; a column whose entries are all equal becomes a literal
+    struct Col { const char* name; const char* type; std::vector<std::string> v; };
+    std::vector<Col> cols = {{"p_es", "int", {}}, {"p_cr", "int", {}}, {"p_ts", "int", {}}, {"p_out", "int", {}}, {"p_nr", "int", {}},
+                             {"p_k", "int", {}}, {"p_lat", "float", {}}, {"p_along", "float", {}}, {"p_slk", "float", {}}};
+    for (int k = 0; k < NS; ++k) {
+      const DSensor& sn = pl->sensors[k];
+      for (int q = 0; q < sn.n_targets; ++q) {
+        const float4 tc = pl->tcull[sn.tg_begin + q];
+        const int vals[6] = {3 * lid_slot[sn.entity], kp.n_lmask_words + 2 * k, 3 * lid_slot[pl->targets[sn.tg_begin + q]], sn.out_off, sn.n_rays, k};
+        for (int c = 0; c < 6; ++c) cols[c].v.push_back(std::to_string(vals[c]));
+        cols[6].v.push_back(fl(tc.y)); cols[7].v.push_back(fl(tc.z)); cols[8].v.push_back(fl(tc.w));
+      }
+    }
+    for (const Col& c : cols) {
+      bool same = true;
+      for (const std::string& v : c.v) same = same && v == c.v[0];
+      if (same) {
+        outf(s, "VB_DI %s %s(int) { return %s; }\n", c.type, c.name, c.v[0].c_str());
+      } else {
+        const bool f = c.type[0] == 'f';
+        outf(s, "__constant__ %s T_%s[%d] = {", f ? "float" : "unsigned short", c.name, NPT);
+        for (size_t i = 0; i < c.v.size(); ++i) outf(s, "%s%s", i ? ", " : "", c.v[i].c_str());
+        outf(s, "};\nVB_DI %s %s(int p) { return T_%s[p]; }\n", c.type, c.name, c.name);
+      }
+    }
+    // ray directions: when every sensor has the same rays the sweep is unrolled over a constant-bank table
+    bool shared_rays = true;
+    const DSensor& s0 = pl->sensors[0];
+    for (const DSensor& sn : pl->sensors) {
+      shared_rays = shared_rays && sn.n_rays == s0.n_rays;
+      for (int r = 0; shared_rays && r < sn.n_rays; ++r)
+        shared_rays = pl->ray_cs[sn.out_off + r].x == pl->ray_cs[s0.out_off + r].x && pl->ray_cs[sn.out_off + r].y == pl->ray_cs[s0.out_off + r].y;
+    }
+    shared_rays = shared_rays && s0.n_rays <= 64;
+    outf(s, "constexpr int SHARED_RAYS = %d;\n__constant__ float2 T_raycs[%d] = {", shared_rays ? s0.n_rays : 0, shared_rays ? s0.n_rays : 1);
+    for (int r = 0; r < (shared_rays ? s0.n_rays : 1); ++r)
+      outf(s, "%s{%s, %s}", r ? ", " : "", fl(pl->ray_cs[s0.out_off + r].x).c_str(), fl(pl->ray_cs[s0.out_off + r].y).c_str());
+    s += "};\n";
     // init: rows of one sensor share its max_range
     s += "VB_DI void world_lidar_init(float* lidS, int tid) {\n";
     for (const DSensor& sn : pl->sensors)
@@ -307,50 +352,35 @@ static std::string generate(const vmasb200_plan* pl, int te, int nt, JitLayout* 
               "    for (int i = tid; i < %d * TE / 4; i += NT) p[i] = v; }\n",
            fl(sn.max_range).c_str(), fl(sn.max_range).c_str(), fl(sn.max_range).c_str(), fl(sn.max_range).c_str(), sn.out_off, sn.n_rays);
     s += "}\n";
-    s += "VB_DI void world_lidar_pass1(const St& st, bool ok, int col, float* wcol, int* queue, int* qn) {\n";
-    for (int k = 0; k < kp.n_sensors; ++k) {
+    // pass 1: reach masks from the registers; every (sensor, target) within reach becomes one entry of the pair queue
+    s += "VB_DI void world_lidar_pass1(const St& st, bool ok, int col, float* wcol, unsigned short* pq, int* qn) {\n  int n = 0;\n";
+    for (int k = 0; k < NS; ++k) {
       const DSensor& sn = pl->sensors[k];
       const int mrow = sn.tw_off - kp.row_lmask;
-      outf(s, "  { const V2 o = %s; uint32_t m = 0u;\n", posx(sn.entity).c_str());
+      outf(s, "  uint32_t m%d = 0u;\n  { const V2 o = %s;\n", k, posx(sn.entity).c_str());
       for (int q = 0; q < sn.n_targets; ++q) {
         const int tg = pl->targets[sn.tg_begin + q];
-        outf(s, "    { const V2 p = %s; const float dx = o.x - p.x, dy = o.y - p.y; if (!(fmaf(dy, dy, dx * dx) > %s)) m |= %uu; }\n",
-             posx(tg).c_str(), fl(pl->tcull[sn.tg_begin + q].x).c_str(), 1u << q);
+        outf(s, "    { const V2 p = %s; const float dx = o.x - p.x, dy = o.y - p.y; if (!(fmaf(dy, dy, dx * dx) > %s)) m%d |= %uu; }\n",
+             posx(tg).c_str(), fl(pl->tcull[sn.tg_begin + q].x).c_str(), k, 1u << q);
       }
-      outf(s, "    wcol[%d * TE] = __uint_as_float(m);\n", mrow);
-      outf(s, "    if (m && ok) { float sn_, cs_; sincosf(%s, &sn_, &cs_); wcol[%d * TE] = cs_; wcol[%d * TE] = sn_;\n"
-              "      queue[%d * TE + atomicAdd(qn + %d, 1)] = col; } }\n",
-           rotx(sn.entity).c_str(), kp.n_lmask_words + 2 * k, kp.n_lmask_words + 2 * k + 1, k, k);
+      outf(s, "    wcol[%d * TE] = __uint_as_float(m%d);\n    if (!ok) m%d = 0u;\n", mrow, k, k);
+      outf(s, "    if (m%d) { float sn_, cs_; sincosf(%s, &sn_, &cs_); wcol[%d * TE] = cs_; wcol[%d * TE] = sn_; n += __popc(m%d); } }\n", k,
+           rotx(sn.entity).c_str(), kp.n_lmask_words + 2 * k, kp.n_lmask_words + 2 * k + 1, k);
     }
-    s += "}\n";
-    s += "VB_DI void world_lidar_pass2(const KParams& kp, const float* envS, const float* workS, const int* queue, int* qn, int* rayq, int tid) {\n";
-    for (int k = 0; k < kp.n_sensors; ++k) {
+    s += "  if (n) {\n    int b = atomicAdd(qn, n);\n";
+    for (int k = 0; k < NS; ++k) {
       const DSensor& sn = pl->sensors[k];
-      const int mrow = sn.tw_off - kp.row_lmask, es = lid_slot[sn.entity];
-      outf(s, "  { const int total = qn[%d] * %d;\n    for (int task = tid; task < total; task += NT) {\n", k, sn.n_rays);
-      outf(s, "      const int qi = task / %d, r = task - qi * %d, col = queue[%d * TE + qi];\n", sn.n_rays, sn.n_rays, k);
-      outf(s, "      const float* ec = envS + col; const float* wc = workS + col;\n");
-      outf(s, "      const V2 o = mk(ec[%d * TE], ec[%d * TE]);\n", 3 * es, 3 * es + 1);
-      outf(s, "      const float c0 = wc[%d * TE], s0 = wc[%d * TE];\n", kp.n_lmask_words + 2 * k, kp.n_lmask_words + 2 * k + 1);
-      outf(s, "      const float2 cs = __ldg(kp.ray_cs + %d + r);\n", sn.out_off);
-      outf(s, "      const float dc = c0 * cs.x - s0 * cs.y, ds = s0 * cs.x + c0 * cs.y;\n");
-      outf(s, "      const float aslack = fabsf(ec[%d * TE]) + 8.f;\n", 3 * es + 2);
-      outf(s, "      const uint32_t m = __float_as_uint(wc[%d * TE]);\n      bool cand = false;\n", mrow);
-      for (int q = 0; q < sn.n_targets; ++q) {
-        const int tg = pl->targets[sn.tg_begin + q], ts = lid_slot[tg];
-        const float4 tc = pl->tcull[sn.tg_begin + q];
-        outf(s, "      if (m & %uu) { const float rx = ec[%d * TE] - o.x, ry = ec[%d * TE] - o.y; const float slack = %s * aslack;\n"
-                "        const float lat = fabsf(rx * ds - ry * dc), along = rx * dc + ry * ds;\n"
-                "        cand = cand || (!(lat > %s + slack) && !(along < -(%s + slack))); }\n",
-             1u << q, 3 * ts, 3 * ts + 1, fl(tc.w).c_str(), fl(tc.y).c_str(), fl(tc.z).c_str());
-      }
-      outf(s, "      if (cand) rayq[atomicAdd(qn + NSENS, 1)] = col | (%d << 8) | (r << 16);\n    } }\n", k);
+      for (int q = 0; q < sn.n_targets; ++q)
+        outf(s, "    if (m%d & %uu) pq[b++] = (unsigned short)(col | (%d << CB));\n", k, 1u << q, sn.tg_begin + q);
     }
-    s += "}\n";
+    s += "  }\n}\n";
   } else {
-    s += "VB_DI void world_lidar_init(float*, int) {}\n"
-         "VB_DI void world_lidar_pass1(const St&, bool, int, float*, int*, int*) {}\n"
-         "VB_DI void world_lidar_pass2(const KParams&, const float*, const float*, const int*, int*, int*, int) {}\n";
+    s += "constexpr int NPT = 1, CB = 0, KB = 0, RAYS_TOTAL = 1, SHARED_RAYS = 0;\n__constant__ float2 T_raycs[1] = {{0.f, 0.f}};\n"
+         "VB_DI int p_es(int) { return 0; }\nVB_DI int p_cr(int) { return 0; }\nVB_DI int p_ts(int) { return 0; }\n"
+         "VB_DI int p_out(int) { return 0; }\nVB_DI int p_nr(int) { return 0; }\nVB_DI int p_k(int) { return 0; }\n"
+         "VB_DI float p_lat(int) { return 0.f; }\nVB_DI float p_along(int) { return 0.f; }\nVB_DI float p_slk(int) { return 0.f; }\n"
+         "VB_DI void world_lidar_init(float*, int) {}\n"
+         "VB_DI void world_lidar_pass1(const St&, bool, int, float*, unsigned short*, int*) {}\n";
   }
   s += "} }\n#include \"spec_kernel.cuh\"\n";
   return s;

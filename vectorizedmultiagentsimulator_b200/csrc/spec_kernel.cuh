@@ -21,30 +21,63 @@
 
 namespace vb {
 
-// The LIDAR epilogue with the world's sensors as constants (the three passes of kernels.cuh lidar_epilogue, same culls,
-// same exact arithmetic for the rays that can hit):
+// The LIDAR epilogue with the world's sensors as constants (the culls of kernels.cuh lidar_epilogue, the same exact
+// arithmetic for the rays that can hit):
 //   1  thread per env, straight from the registers: per sensor the mask of targets within reach (world_lidar_pass1,
-//      generated: unrolled over sensors and targets, thresholds as literals); sensors that see something are queued
-//      per sensor, so that pass 2 knows its sensor at compile time;
-//   2  per sensor, thread per (queued env, ray): ray-level cull with the approximate direction (world_lidar_pass2,
-//      generated: division by the constant ray count, unrolled targets, literal reaches); rays that may hit are queued;
-//   3  thread per queued ray: the reference's exact arithmetic (step_kernel.cuh cast_one_ray).
-// Every thread of the CTA calls it (CTA barriers inside).
+//      generated: unrolled over sensors and targets, thresholds as literals); every (sensor, target) within reach is
+//      one entry of the pair queue (one shared atomic per env);
+//   2  thread per queued pair: the target is turned into the sensor's frame once, then every ray of the sensor is
+//      tested against it with the plan's cos / sin table of the ray angles (6 flops per ray, no memory access when all
+//      sensors share their rays); a ray that may hit is queued once (its output cell is the flag);
+//   3  thread per queued ray: the reference's exact arithmetic (step_kernel.cuh cast_one_ray) over the sensor's mask.
+// A culled ray keeps max_range, which is what the exact arithmetic gives a ray that cannot reach: the culls are
+// conservative (plan.cpp tcull: reach, lateral and behind-the-origin bounds with a slack for the approximate
+// direction), so the result does not depend on them.
+// Every thread of the CTA calls it (CTA barriers inside); s_qn[0..1] must be zero on entry (set at kernel start).
 namespace gen {
-VB_DI void lidar_world(const KParams& kp, const Tile& t, const St& st, bool phys, bool ok) {
-  __shared__ int s_qn[NSENS + 1];  // queued envs per sensor; [NSENS]: queued rays
+constexpr int kRaySentinel = 0x7fc0dead;  // a NaN no range is equal to: "already queued"
+VB_DI void lidar_world(const KParams& kp, const Tile& t, const St& st, bool phys, bool ok, int* s_qn) {
   const int tid = threadIdx.x;
-  if (tid <= NSENS) s_qn[tid] = 0;
+  unsigned short* pq = reinterpret_cast<unsigned short*>(t.queue);  // [NPT * TE]
+  unsigned short* rq = pq + NPT * TE;                                // [RAYS_TOTAL * TE]
   world_lidar_init(t.lidS, tid);  // every ray starts at max_range
-  if (phys) world_stage_lidar(st, t.envS + tid, t.workS + tid);
+  if (phys) {
+    world_stage_lidar(st, t.envS + tid, t.workS + tid);
+    world_lidar_pass1(st, ok, tid, t.workS + tid, pq, s_qn);
+  }
   __syncthreads();
-  if (phys) world_lidar_pass1(st, ok, tid, t.workS + tid, t.queue, s_qn);
+  const int np = s_qn[0];
+  for (int task = tid; task < np; task += NT) {
+    const int e = pq[task], col = e & (TE - 1), p = e >> CB;
+    const float* ec = t.envS + col;
+    const float* wc = t.workS + col;
+    const int es = p_es(p), ts = p_ts(p), cr = p_cr(p);
+    const float ox = ec[es * TE], oy = ec[(es + 1) * TE];
+    const float slack = p_slk(p) * (fabsf(ec[(es + 2) * TE]) + 8.f);
+    const float c0 = wc[cr * TE], s0 = wc[(cr + 1) * TE];
+    const float rx = ec[ts * TE] - ox, ry = ec[(ts + 1) * TE] - oy;
+    const float u = rx * c0 + ry * s0, v = ry * c0 - rx * s0;  // the target in the sensor's frame
+    const float lat_max = p_lat(p) + slack, along_min = -(p_along(p) + slack);
+    const int out = p_out(p);
+    const int tag = col | (p_k(p) << CB);
+    int* cell = reinterpret_cast<int*>(t.lidS) + out * TE + col;
+    auto test = [&](int r, float2 cs) {
+      const float lat = fabsf(u * cs.y - v * cs.x), along = u * cs.x + v * cs.y;
+      if (!(lat > lat_max) && !(along < along_min))
+        if (atomicExch(cell + r * TE, kRaySentinel) != kRaySentinel) rq[atomicAdd(s_qn + 1, 1)] = (unsigned short)(tag | (r << (CB + KB)));
+    };
+    if (SHARED_RAYS) {
+#pragma unroll
+      for (int r = 0; r < SHARED_RAYS; ++r) test(r, T_raycs[r]);
+    } else {
+      const int nr = p_nr(p);
+      for (int r = 0; r < nr; ++r) test(r, __ldg(kp.ray_cs + out + r));
+    }
+  }
   __syncthreads();
-  world_lidar_pass2(kp, t.envS, t.workS, t.queue, s_qn, t.rayq, tid);
-  __syncthreads();
-  const int nq = s_qn[NSENS];
+  const int nq = s_qn[1];
   for (int qi = tid; qi < nq; qi += NT) {
-    const int item = t.rayq[qi], col = item & 0xff, k = (item >> 8) & 0xff, r = item >> 16;
+    const int item = rq[qi], col = item & (TE - 1), k = (item >> CB) & ((1 << KB) - 1), r = item >> (CB + KB);
     const DSensor* sn = &T_sensor<true>(kp, k);
     const EnvT<TE> E = env_view<TE>(t, col);
     const DEnt* se = &T_ent<true>(kp, sn->entity);
@@ -60,7 +93,12 @@ vmasb200_step_world(const __grid_constant__ KParams kp, const __grid_constant__ 
   using namespace gen;
   extern __shared__ __align__(16) float smem[];
   __shared__ int s_last;
+  __shared__ int s_qn[2];  // LIDAR: queued pairs, queued rays
   const int tid = threadIdx.x;
+  if (LIDAR && LIDAR_COMPILED) {  // before the physics, so that the epilogue needs no barrier of its own for it
+    if (tid < 2) s_qn[tid] = 0;
+    __syncthreads();
+  }
   const long long env0 = sa.env_begin + (long long)blockIdx.x * TE;
   const int n_valid = (int)min((long long)TE, sa.env_end - env0);
   const bool phys = tid < TE;
@@ -123,7 +161,7 @@ vmasb200_step_world(const __grid_constant__ KParams kp, const __grid_constant__ 
     t.queue = reinterpret_cast<int*>(smem + m.queue); t.rayq = reinterpret_cast<int*>(smem + m.rayq);
     t.qcount = reinterpret_cast<int*>(smem + m.bar) + 2;
     if (LIDAR_COMPILED) {
-      lidar_world(kp, t, st, phys, ok);
+      lidar_world(kp, t, st, phys, ok, s_qn);
     } else {
       if (phys) world_stage_lidar(st, t.envS + tid, t.workS + tid);
       __syncthreads();
