@@ -96,6 +96,51 @@ def test_compiled_equals_generic_large_batch(name, n):
         dyn = a[0]
 
 
+@pytest.mark.parametrize("name,rays", [("transport", (12, 12)), ("joint_passage", (24, 30)), ("wheel", (7, 5)), ("football", (20, 20)), ("football", (8, 8))])
+def test_compiled_lidar_on_boxes_and_lines(name, rays):
+    """the golden worlds only point their LIDARs at spheres: give the agents of worlds with boxes and lines sensors that
+    see every other entity (equal ray counts: the unrolled constant-bank sweep; different ones: the table-driven sweep)
+    and require the compiled epilogue (pair queue, frame sweep, exact rays with literal dimensions) to equal the
+    generic one bit for bit"""
+    import copy
+    import math
+    from vectorizedmultiagentsimulator_b200.worlddesc import LidarDesc
+    L = _lib.lib()
+    fx = Fixture(name)
+    desc = copy.deepcopy(fx.desc)
+    E = len(desc.entities)
+    desc.lidars = []
+    for i, a in enumerate(desc.agent_indices[:4]):
+        nr = rays[i % len(rays)]
+        desc.lidars.append(LidarDesc(entity=a, angles=[2 * math.pi * r / nr for r in range(nr)], max_range=0.4 + 0.1 * (i % 2),
+                                     targets=[e for e in range(E) if e != a][:32]))
+    pl = StepPlan(desc)
+    n = 5000
+    rng = np.random.default_rng(11)
+    reps = -(-n // fx.n_envs)
+    st = np.tile(fx.state0, (1, reps, 1))[:, :n].copy()
+    st[..., 0:2] += rng.uniform(-0.2, 0.2, st[..., 0:2].shape).astype(np.float32)
+    st[..., 4] += rng.uniform(-3.0, 3.0, st[..., 4].shape).astype(np.float32)
+    f = np.tile(fx.forces[0], (1, reps, 1))[:, :n]
+    tq = np.tile(fx.torques[0], (1, reps))[:, :n]
+    f, tq = np.ascontiguousarray(f.transpose(1, 0, 2)), np.ascontiguousarray(tq.transpose(1, 0))
+    jr = fx.jrot_at(0)
+    dyn, stat = pl.pack(st, np.tile(jr, (1, reps))[:, :n] if jr is not None and jr.size else None)
+    assert pl.jit(n)[0] == 1, L.vmasb200_last_error()
+    for _ in range(2):
+        a = pl.step_host(dyn, stat, f, tq, exact=False)
+        assert pl.jit(n)[1] > 0
+        L.vmasb200_jit_enable(0)
+        try:
+            b = pl.step_host(dyn, stat, f, tq, exact=False)
+        finally:
+            L.vmasb200_jit_enable(2)
+        assert _same(a[0][:pl.dyn_rows, :n], b[0][:pl.dyn_rows, :n]), "state differs"
+        assert a[2] is not None and _same(a[2][:, :n], b[2][:, :n]), "lidar differs"
+        assert (a[2][:, :n] < np.float32(0.39)).any(), "no ray hit anything: the test does not exercise the exact rays"
+        dyn = a[0]
+
+
 def test_compiled_launch_reaches_the_repair():
     """joint_passage at a few thousand envs has thin contacts at the ends of the passage's wall segments whose pair no
     exact env activates: the compiled launch must hand over to kernels.cuh repair_kernel, and the result must still be

@@ -320,18 +320,38 @@ static std::string generate(const vmasb200_plan* pl, int te, int nt, JitLayout* 
         cols[6].v.push_back(fl(tc.y)); cols[7].v.push_back(fl(tc.z)); cols[8].v.push_back(fl(tc.w));
       }
     }
-    for (const Col& c : cols) {
-      bool same = true;
-      for (const std::string& v : c.v) same = same && v == c.v[0];
-      if (same) {
-        outf(s, "VB_DI %s %s(int) { return %s; }\n", c.type, c.name, c.v[0].c_str());
-      } else {
-        const bool f = c.type[0] == 'f';
-        outf(s, "__constant__ %s T_%s[%d] = {", f ? "float" : "unsigned short", c.name, NPT);
-        for (size_t i = 0; i < c.v.size(); ++i) outf(s, "%s%s", i ? ", " : "", c.v[i].c_str());
-        outf(s, "};\nVB_DI %s %s(int p) { return T_%s[p]; }\n", c.type, c.name, c.name);
+    std::vector<Col> scols = {{"k_es", "int", {}}, {"k_mrow", "int", {}}, {"k_tg0", "int", {}}, {"k_out", "int", {}}, {"k_range", "float", {}}};
+    std::vector<Col> tcols = {{"p_shape", "int", {}}, {"p_trig", "int", {}}, {"p_radius", "float", {}}, {"p_length", "float", {}}, {"p_width", "float", {}}};
+    for (int k = 0; k < NS; ++k) {
+      const DSensor& sn = pl->sensors[k];
+      const int vals[4] = {3 * lid_slot[sn.entity], sn.tw_off - kp.row_lmask, sn.tg_begin, sn.out_off};
+      for (int c = 0; c < 4; ++c) scols[c].v.push_back(std::to_string(vals[c]));
+      scols[4].v.push_back(fl(sn.max_range));
+      for (int q = 0; q < sn.n_targets; ++q) {
+        const int tg = pl->targets[sn.tg_begin + q];
+        const DEnt& en = pl->ents[tg];
+        int trow = 0;
+        for (size_t i = 0; i < lay->lid_trig.size(); ++i)
+          if (lay->lid_trig[i] == tg) trow = trig0 + 4 * (int)i;
+        tcols[0].v.push_back(std::to_string(en.shape)); tcols[1].v.push_back(std::to_string(trow));
+        tcols[2].v.push_back(fl(en.radius)); tcols[3].v.push_back(fl(en.length)); tcols[4].v.push_back(fl(en.width));
       }
     }
+    auto emit_cols = [&](const std::vector<Col>& cs) {
+      for (const Col& c : cs) {
+        bool same = true;
+        for (const std::string& v : c.v) same = same && v == c.v[0];
+        if (same) {
+          outf(s, "VB_DI %s %s(int) { return %s; }\n", c.type, c.name, c.v[0].c_str());
+        } else {
+          const bool f = c.type[0] == 'f';
+          outf(s, "__constant__ %s T_%s[%d] = {", f ? "float" : "unsigned short", c.name, (int)c.v.size());
+          for (size_t i = 0; i < c.v.size(); ++i) outf(s, "%s%s", i ? ", " : "", c.v[i].c_str());
+          outf(s, "};\nVB_DI %s %s(int p) { return T_%s[p]; }\n", c.type, c.name, c.name);
+        }
+      }
+    };
+    emit_cols(cols); emit_cols(scols); emit_cols(tcols);
     // ray directions: when every sensor has the same rays the sweep is unrolled over a constant-bank table
     bool shared_rays = true;
     const DSensor& s0 = pl->sensors[0];
@@ -379,6 +399,10 @@ static std::string generate(const vmasb200_plan* pl, int te, int nt, JitLayout* 
          "VB_DI int p_es(int) { return 0; }\nVB_DI int p_cr(int) { return 0; }\nVB_DI int p_ts(int) { return 0; }\n"
          "VB_DI int p_out(int) { return 0; }\nVB_DI int p_nr(int) { return 0; }\nVB_DI int p_k(int) { return 0; }\n"
          "VB_DI float p_lat(int) { return 0.f; }\nVB_DI float p_along(int) { return 0.f; }\nVB_DI float p_slk(int) { return 0.f; }\n"
+         "VB_DI int k_es(int) { return 0; }\nVB_DI int k_mrow(int) { return 0; }\nVB_DI int k_tg0(int) { return 0; }\n"
+         "VB_DI int k_out(int) { return 0; }\nVB_DI float k_range(int) { return 0.f; }\nVB_DI int p_shape(int) { return 0; }\n"
+         "VB_DI int p_trig(int) { return 0; }\nVB_DI float p_radius(int) { return 0.f; }\nVB_DI float p_length(int) { return 0.f; }\n"
+         "VB_DI float p_width(int) { return 0.f; }\n"
          "VB_DI void world_lidar_init(float*, int) {}\n"
          "VB_DI void world_lidar_pass1(const St&, bool, int, float*, unsigned short*, int*) {}\n";
   }

@@ -78,11 +78,32 @@ VB_DI void lidar_world(const KParams& kp, const Tile& t, const St& st, bool phys
   const int nq = s_qn[1];
   for (int qi = tid; qi < nq; qi += NT) {
     const int item = rq[qi], col = item & (TE - 1), k = (item >> CB) & ((1 << KB) - 1), r = item >> (CB + KB);
-    const DSensor* sn = &T_sensor<true>(kp, k);
-    const EnvT<TE> E = env_view<TE>(t, col);
-    const DEnt* se = &T_ent<true>(kp, sn->entity);
-    const float ang = __ldg(kp.ray_angles + sn->out_off + r) + ER(E, se->rot_row);  // sensors.py:117
-    t.lidS[(sn->out_off + r) * TE + col] = cast_one_ray<true>(kp, sn, E, pos_at(E, se->pos_row), ang);
+    const float* ec = t.envS + col;
+    const float* wc = t.workS + col;
+    const int es = k_es(k), out = k_out(k), tg0 = k_tg0(k);
+    const V2 o = mk(ec[es * TE], ec[(es + 1) * TE]);
+    const float ang = __ldg(kp.ray_angles + out + r) + ec[(es + 2) * TE];  // sensors.py:117
+    const float max_range = k_range(k);
+    float best = max_range, ds, dc;
+    sincosf(ang, &ds, &dc);
+    uint32_t m = __float_as_uint(wc[k_mrow(k) * TE]);
+    while (m) {  // step_kernel.cuh cast_one_ray with the targets' dimensions as constants
+      const int p = tg0 + __ffs(m) - 1;
+      m &= m - 1;
+      const int ts = p_ts(p), shape = p_shape(p);
+      const V2 tp = mk(ec[ts * TE], ec[(ts + 1) * TE]);
+      float d;
+      if (shape == VMASB200_SPHERE) {
+        d = ray_sphere(tp, p_radius(p), o, dc, ds, max_range);
+      } else {
+        const int tr = p_trig(p);
+        const float tc = wc[tr * TE], tsn = wc[(tr + 1) * TE];
+        d = shape == VMASB200_BOX ? ray_box(tp, tc, tsn, p_length(p), p_width(p), o, dc, ds, max_range)
+                                  : ray_line(tp, tc, tsn, p_length(p), o, dc, ds, max_range);
+      }
+      best = pmin(best, d);
+    }
+    t.lidS[(out + r) * TE + col] = best;
   }
   __syncthreads();
 }
@@ -175,7 +196,7 @@ vmasb200_step_world(const __grid_constant__ KParams kp, const __grid_constant__ 
     if (tid < 32) {
       for (int r = tid; r < kp.lidar_rows; r += 32) bulk_s2g(sa.lidar_out + (size_t)r * sa.ld + env0, t.lidS + r * TE, row_bytes);
       bulk_commit();
-      bulk_wait_all();
+      bulk_wait_read();  // nothing in this kernel reads or rewrites lidar_out (repairs run in a kernel of their own)
     }
   }
   // ---- last CTA of the step: verify (repair if needed), publish the verdicts, reset the scratch for the next launch

@@ -66,6 +66,8 @@ VB_DI void bulk_s2g(void* dst_gmem, const void* src_smem, uint32_t bytes) {
 }
 VB_DI void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 VB_DI void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+// the sources in shared memory have been read (enough to leave the CTA; the writes complete by the end of the kernel)
+VB_DI void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
 
 // Plan tables every substep walks, in the constant bank: the walks are warp-uniform, so these become uniform-datapath
 // constant loads (LDCU) with uniform address arithmetic instead of per-thread global loads.  One copy per device; the
