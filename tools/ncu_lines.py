@@ -68,6 +68,7 @@ def main():
     by_frame = {l: collections.defaultdict(lambda: [0, 0, 0]) for l in (1, 2, 3)}
     total = [0, 0, 0]
     base, prev, si = None, None, 0
+    dump, dumped = os.environ.get("NCU_LINES_DUMP"), []  # "file.cuh:123": list every SASS instruction of that line
     entry = [s for s in sects if "step_kernel" in s or kernel in s]
     order = entry[:1] + [s for s in sects if s not in entry[:1]]
     for r in rows[hi + 1:]:
@@ -89,6 +90,8 @@ def main():
         total[0] += smp; total[1] += ins; total[2] += tins
         chain = key[0] if key and key[0] else (("?", 0),)
         loc = chain[0]
+        if dump and f"{loc[0]}:{loc[1]}" == dump:
+            dumped.append((off, r[ci["Source"]].strip(), ins, tins, smp))
         by_line[loc][0] += smp; by_line[loc][1] += ins; by_line[loc][2] += tins
         for lvl in (1, 2, 3):  # frames counted from the kernel body inwards
             fr = chain[-lvl] if len(chain) >= lvl else chain[0]
@@ -109,6 +112,10 @@ def main():
     print("--- opcodes by warp instructions")
     for op, v in sorted(by_op.items(), key=lambda kv: -kv[1][1])[:25]:
         print(f"{op:<12s} inst {v[1]:>10d} ({100*v[1]/max(total[1],1):5.1f}%)  samples {v[0]:>7d}")
+    if dump:
+        print(f"--- SASS attributed to {dump} (offset, instruction, warp-inst, thread-inst, samples)")
+        for off, src, ins, tins, smp in dumped:
+            print(f"{off:06x}  {src[:90]:<90s} {ins:>9d} {tins:>11d} {smp:>5d}")
 
 
 if __name__ == "__main__":

@@ -456,7 +456,15 @@ static std::string jit_compile(const vmasb200_plan* pl, int te, int nt, JitLayou
     f << src;
   }
   // -default-device: the C prototypes of include/vmasb200.h carry no execution space
-  const char* opts[] = {"--gpu-architecture=sm_100a", "--std=c++17", "--fmad=false", "-lineinfo", "-default-device"};
+  std::vector<const char*> opts = {"--gpu-architecture=sm_100a", "--std=c++17", "--fmad=false", "-lineinfo", "-default-device"};
+  // VMASB200_JIT_DEFINES="-DVB_X=1 -DVB_Y": extra options for A/B measurements of the kernel sources (part of the cache key)
+  std::vector<std::string> extra;
+  if (const char* d = getenv("VMASB200_JIT_DEFINES")) {
+    std::stringstream ss(d);
+    std::string w;
+    while (ss >> w) extra.push_back(w);
+  }
+  for (const std::string& w : extra) opts.push_back(w.c_str());
   uint64_t h = fnv1a(src);
   for (int i = 0; i < kJitNumSources; ++i) h = fnv1a(kJitSrcText[i], h);
   for (const char* o : opts) h = fnv1a(o, h);
@@ -482,7 +490,7 @@ static std::string jit_compile(const vmasb200_plan* pl, int te, int nt, JitLayou
     *err = "nvrtcCreateProgram failed";
     return "";
   }
-  const int rc = g_nvrtc.CompileProgram(prog, (int)(sizeof opts / sizeof opts[0]), opts);
+  const int rc = g_nvrtc.CompileProgram(prog, (int)opts.size(), opts.data());
   std::string out;
   if (rc != 0) {
     size_t n = 0;

@@ -104,7 +104,7 @@ VB_DI void integrate_r(const EntC en, St& st, int substep) {
     V2 vel = mk(st.vx[d], st.vy[d]);
     if (substep == 0) vel = vel * en.one_minus_drag;
     const float mass = en.mass;
-    V2 acc = mass == 1.f ? F : F / mass;  // x / 1 == x exactly
+    V2 acc = mass == 1.f ? F : mk(div_pos(F.x, mass), div_pos(F.y, mass));  // x / 1 == x exactly
     vel = vel + acc * SUB_DT;
     if (fl & VMASB200_E_MAX_SPEED) vel = clamp_norm2(vel, en.max_speed);
     if (fl & VMASB200_E_V_RANGE) {
@@ -119,7 +119,7 @@ VB_DI void integrate_r(const EntC en, St& st, int substep) {
   if (fl & VMASB200_E_ROTATABLE) {
     float w = st.w[d];
     if (substep == 0) w = w * en.one_minus_drag;
-    w = w + (st.T[d] / en.moi) * SUB_DT;
+    w = w + div_pos(st.T[d], en.moi) * SUB_DT;
     st.w[d] = w;
     const float nr = st.rot[d] + w * SUB_DT;
     st.rot[d] = nr;

@@ -6,7 +6,7 @@
 //   world_integrate(st, s, more)   integrate_r (+ begin_r of the next substep) of every dynamic entity
 //   world_store(st, sa, env)       dyn_out / act_out rows
 //   world_stage_lidar(st, env, work) px py rot (and cos/sin of non-sphere targets) of the entities the epilogue reads
-//   world_lidar_init / _pass1 / _pass2  see lidar_world below
+//   world_lidar_init / _pass1, the p_* / k_* tables of the (sensor, target) pairs and sensors: see lidar_world below
 //
 // One thread per environment, state in registers for all substeps, no shared memory and no barrier on the physics
 // path.  The speculation protocol is the generic kernel's (kernels.cuh header): verdicts of untainted envs go to
@@ -15,8 +15,9 @@
 // kernels.cuh repair_kernel (generic validation + repair, compiled into the library), which the host launches right
 // behind every launch of a world that can have thin events.  THIN_POSSIBLE = false (sphere-sphere worlds) compiles all
 // of that away.
-// LIDAR: the generic three-pass epilogue (kernels.cuh lidar_epilogue) on a compact tile; such a CTA keeps 128 threads
-// so that its passes run on full warps even when only TE = 32 of them carry an environment.
+// LIDAR: lidar_world below (sensors, targets and rays as constants) on a compact tile, or the generic three-pass
+// epilogue (kernels.cuh lidar_epilogue) for the worlds jit.h does not cover; such a CTA keeps 128 threads so that the
+// passes run on full warps even when only TE = 32 of them carry an environment.
 #pragma once
 
 namespace vb {
@@ -61,17 +62,34 @@ VB_DI void lidar_world(const KParams& kp, const Tile& t, const St& st, bool phys
     const int out = p_out(p);
     const int tag = col | (p_k(p) << CB);
     int* cell = reinterpret_cast<int*>(t.lidS) + out * TE + col;
-    auto test = [&](int r, float2 cs) {
+    auto may_hit = [&](float2 cs) {
       const float lat = fabsf(u * cs.y - v * cs.x), along = u * cs.x + v * cs.y;
-      if (!(lat > lat_max) && !(along < along_min))
-        if (atomicExch(cell + r * TE, kRaySentinel) != kRaySentinel) rq[atomicAdd(s_qn + 1, 1)] = (unsigned short)(tag | (r << (CB + KB)));
+      return !(lat > lat_max) && !(along < along_min);
     };
-    if (SHARED_RAYS) {
+    auto push = [&](int r) {  // once per ray: its output cell is the flag
+      if (atomicExch(cell + r * TE, kRaySentinel) != kRaySentinel) rq[atomicAdd(s_qn + 1, 1)] = (unsigned short)(tag | (r << (CB + KB)));
+    };
+#ifdef VB_AB_DIRECT_PUSH
+    if constexpr (SHARED_RAYS > 0) {
 #pragma unroll
-      for (int r = 0; r < SHARED_RAYS; ++r) test(r, T_raycs[r]);
+      for (int r = 0; r < SHARED_RAYS; ++r)
+        if (may_hit(T_raycs[r])) push(r);
+    } else
+#endif
+    if constexpr (SHARED_RAYS > 0 && SHARED_RAYS <= 32) {  // branch-free sweep into a mask, then only the rays that passed
+      uint32_t cm = 0u;
+#pragma unroll
+      for (int r = 0; r < SHARED_RAYS; ++r) cm |= (may_hit(T_raycs[r]) ? 1u : 0u) << r;
+      while (cm) { push(__ffs(cm) - 1); cm &= cm - 1; }
+    } else if constexpr (SHARED_RAYS > 32) {
+      unsigned long long cm = 0ull;
+#pragma unroll
+      for (int r = 0; r < SHARED_RAYS; ++r) cm |= (may_hit(T_raycs[r]) ? 1ull : 0ull) << r;
+      while (cm) { push(__ffsll((long long)cm) - 1); cm &= cm - 1; }
     } else {
       const int nr = p_nr(p);
-      for (int r = 0; r < nr; ++r) test(r, __ldg(kp.ray_cs + out + r));
+      for (int r = 0; r < nr; ++r)
+        if (may_hit(__ldg(kp.ray_cs + out + r))) push(r);
     }
   }
   __syncthreads();

@@ -69,6 +69,17 @@ VB_DI void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "mem
 // the sources in shared memory have been read (enough to leave the CTA; the writes complete by the end of the kernel)
 VB_DI void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
 
+// x / c for a divisor that is normally a positive finite constant (mass, moment of inertia).  +-0 / c is +-0 itself, and
+// a zero numerator sends the IEEE division to its slow path (ncu: ~230 instructions per warp and step in navigation,
+// whose spheres never receive a torque): branch around it.  Same bits as x / c in every case.
+VB_DI float div_pos(float x, float c) {
+#ifndef VB_AB_PLAIN_DIV
+  if (x == 0.f && c > 0.f && c < 3.0e38f) return x;
+  asm volatile("" : "+f"(x));  // keeps the division on this side of the branch (the compiler would otherwise divide, slow path and all, and select)
+#endif
+  return x / c;
+}
+
 // Plan tables every substep walks, in the constant bank: the walks are warp-uniform, so these become uniform-datapath
 // constant loads (LDCU) with uniform address arithmetic instead of per-thread global loads.  One copy per device; the
 // host re-uploads it (stream-ordered) when a launch belongs to another plan (vmasb200.cu bind_const).  Worlds that do
@@ -275,7 +286,7 @@ VB_DI void integrate(const KParams& kp, const DEnt* __restrict__ en, const EV& E
     V2 vel = mk(ER(E, d + 2), ER(E, d + 3));
     if (substep == 0) vel = vel * en->one_minus_drag;
     const float mass = en->mass;
-    V2 acc = mass == 1.f ? F : F / mass;  // x / 1 == x exactly
+    V2 acc = mass == 1.f ? F : mk(div_pos(F.x, mass), div_pos(F.y, mass));  // x / 1 == x exactly
     vel = vel + acc * sub_dt;
     if (fl & VMASB200_E_MAX_SPEED) vel = clamp_norm2(vel, en->max_speed);
     if (fl & VMASB200_E_V_RANGE) {
@@ -290,7 +301,7 @@ VB_DI void integrate(const KParams& kp, const DEnt* __restrict__ en, const EV& E
   if (fl & VMASB200_E_ROTATABLE) {
     float w = ER(E, d + 5);
     if (substep == 0) w = w * en->one_minus_drag;
-    w = w + (WR(E, fin + 2) / en->moi) * sub_dt;
+    w = w + div_pos(WR(E, fin + 2), en->moi) * sub_dt;
     ER(E, d + 5) = w;
     float nr = ER(E, d + 4) + w * sub_dt;
     ER(E, d + 4) = nr;
