@@ -35,9 +35,10 @@ namespace vb {
 // conservative (plan.cpp tcull: reach, lateral and behind-the-origin bounds with a slack for the approximate
 // direction), so the result does not depend on them.
 // Every thread of the CTA calls it (CTA barriers inside); s_qn[0..1] must be zero on entry (set at kernel start).
+// It also counts the CTA as finished (sa.counters[0]) and leaves in *s_last whether it was the step's last one.
 namespace gen {
 constexpr int kRaySentinel = 0x7fc0dead;  // a NaN no range is equal to: "already queued"
-VB_DI void lidar_world(const KParams& kp, const Tile& t, const St& st, bool phys, bool ok, int* s_qn) {
+VB_DI void lidar_world(const KParams& kp, const StepArgs& sa, const Tile& t, const St& st, bool phys, bool ok, int* s_qn, int* s_last) {
   const int tid = threadIdx.x;
   unsigned short* pq = reinterpret_cast<unsigned short*>(t.queue);  // [NPT * TE]
   unsigned short* rq = pq + NPT * TE;                                // [RAYS_TOTAL * TE]
@@ -47,6 +48,14 @@ VB_DI void lidar_world(const KParams& kp, const Tile& t, const St& st, bool phys
     world_lidar_pass1(st, ok, tid, t.workS + tid, pq, s_qn);
   }
   __syncthreads();
+  // the physics of the whole CTA is behind this barrier: count the CTA now (see the kernel's tail), by a thread of the
+  // last warp (a helper warp when NT > TE), so that the fence and the atomic's round trip overlap the passes below
+#ifndef VB_AB_LATE_COUNT
+  if (tid == NT - 1) {
+    __threadfence();
+    *s_last = (atomicAdd(sa.counters, 1) == sa.total_ctas - 1);
+  }
+#endif
   const int np = s_qn[0];
   for (int task = tid; task < np; task += NT) {
     const int e = pq[task], col = e & (TE - 1), p = e >> CB;
@@ -134,6 +143,7 @@ vmasb200_step_world(const __grid_constant__ KParams kp, const __grid_constant__ 
   __shared__ int s_last;
   __shared__ int s_qn[2];  // LIDAR: queued pairs, queued rays
   const int tid = threadIdx.x;
+  bool counted = false;  // the CTA is in sa.counters[0] and s_last is valid
   if (LIDAR && LIDAR_COMPILED) {  // before the physics, so that the epilogue needs no barrier of its own for it
     if (tid < 2) s_qn[tid] = 0;
     __syncthreads();
@@ -199,33 +209,61 @@ vmasb200_step_world(const __grid_constant__ KParams kp, const __grid_constant__ 
     t.envS = smem + m.env; t.workS = smem + m.work; t.lidS = smem + m.lid;
     t.queue = reinterpret_cast<int*>(smem + m.queue); t.rayq = reinterpret_cast<int*>(smem + m.rayq);
     t.qcount = reinterpret_cast<int*>(smem + m.bar) + 2;
+    // LIDAR rows: 16-byte stores straight from the tile (rows are 16-byte aligned: ld % 4 == 0, env0 % TE == 0; a TMA
+    // bulk store per row costs the issuing warp ~14 instructions per row, one lane at a time, and a wait before the CTA
+    // may leave).  The batch's last tile also carries the padding columns up to ld.
+    const int n_cols = (int)min((long long)TE, (sa.env_end == sa.n_envs ? sa.ld : sa.env_end) - env0);
+    auto store_rows = [&]() {
+      constexpr int Q4 = TE / 4;
+      if (((n_cols | (int)(env0 & 3)) & 3) == 0) {
+        for (int i = tid; i < kp.lidar_rows * Q4; i += NT) {
+          const int r = i / Q4, c = (i - r * Q4) * 4;
+          if (c < n_cols) *reinterpret_cast<float4*>(sa.lidar_out + (size_t)r * sa.ld + env0 + c) = *reinterpret_cast<const float4*>(t.lidS + r * TE + c);
+        }
+      } else {
+        for (int i = tid; i < kp.lidar_rows * TE; i += NT) {
+          const int r = i / TE, c = i - r * TE;
+          if (c < n_cols) sa.lidar_out[(size_t)r * sa.ld + env0 + c] = t.lidS[r * TE + c];
+        }
+      }
+    };
     if (LIDAR_COMPILED) {
-      lidar_world(kp, t, st, phys, ok, s_qn);
+      lidar_world(kp, sa, t, st, phys, ok, s_qn, &s_last);
+#ifdef VB_AB_TMA_STORE
+      fence_proxy_async();
+      __syncthreads();
+      if (tid < 32) {
+        for (int r = tid; r < kp.lidar_rows; r += 32) bulk_s2g(sa.lidar_out + (size_t)r * sa.ld + env0, t.lidS + r * TE, (uint32_t)n_cols * 4u);
+        bulk_commit();
+        bulk_wait_read();
+      }
+#else
+      store_rows();
+#endif
+#ifndef VB_AB_LATE_COUNT
+      counted = true;
+#endif
     } else {
       if (phys) world_stage_lidar(st, t.envS + tid, t.workS + tid);
       __syncthreads();
       lidar_epilogue<true, TE>(kp, t, n_valid);
-    }
-    // one TMA bulk store per LIDAR row; the batch's last tile also carries the padding columns up to ld
-    const int n_cols = (int)min((long long)TE, (sa.env_end == sa.n_envs ? sa.ld : sa.env_end) - env0);
-    const uint32_t row_bytes = (uint32_t)n_cols * 4u;
-    fence_proxy_async();
-    __syncthreads();
-    if (tid < 32) {
-      for (int r = tid; r < kp.lidar_rows; r += 32) bulk_s2g(sa.lidar_out + (size_t)r * sa.ld + env0, t.lidS + r * TE, row_bytes);
-      bulk_commit();
-      bulk_wait_read();  // nothing in this kernel reads or rewrites lidar_out (repairs run in a kernel of their own)
+      __syncthreads();
+      store_rows();
     }
   }
   // ---- last CTA of the step: verify (repair if needed), publish the verdicts, reset the scratch for the next launch
-  // release by one thread: the barrier orders the CTA's writes before thread 0's fence (cumulativity), which orders
-  // them before its atomic - no fence per thread (ncu: stall_membar was the top stall of the small worlds)
-  __syncthreads();
-  if (tid == 0) {
-    __threadfence();
-    s_last = (atomicAdd(sa.counters, 1) == sa.total_ctas - 1);
+  // release by one thread: the barrier orders the CTA's writes before that thread's fence (cumulativity), which orders
+  // them before its atomic - no fence per thread (ncu: stall_membar was the top stall of the small worlds).  What the
+  // last CTA reads (verdict words, records) is written by the physics, so lidar_world counts the CTA right behind the
+  // physics and the atomic's latency hides under the LIDAR passes; its closing barrier publishes s_last.
+  if (!counted) {
+    __syncthreads();
+    if (tid == 0) {
+      __threadfence();
+      s_last = (atomicAdd(sa.counters, 1) == sa.total_ctas - 1);
+    }
+    __syncthreads();
   }
-  __syncthreads();
   if (!s_last) return;
   __threadfence();
   constexpr int nw = S * PW;
