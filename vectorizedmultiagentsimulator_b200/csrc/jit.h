@@ -367,10 +367,16 @@ static std::string generate(const vmasb200_plan* pl, int te, int nt, JitLayout* 
     s += "};\n";
     // init: rows of one sensor share its max_range
     s += "VB_DI void world_lidar_init(float* lidS, int tid) {\n";
-    for (const DSensor& sn : pl->sensors)
+    for (size_t k = 0; k < pl->sensors.size();) {  // consecutive sensors of equal range share one fill
+      size_t k2 = k;
+      int rows = 0;
+      while (k2 < pl->sensors.size() && pl->sensors[k2].max_range == pl->sensors[k].max_range) rows += pl->sensors[k2++].n_rays;
+      const std::string v = fl(pl->sensors[k].max_range);
       outf(s, "  { const float4 v = make_float4(%s, %s, %s, %s); float4* p = reinterpret_cast<float4*>(lidS + %d * TE);\n"
-              "    for (int i = tid; i < %d * TE / 4; i += NT) p[i] = v; }\n",
-           fl(sn.max_range).c_str(), fl(sn.max_range).c_str(), fl(sn.max_range).c_str(), fl(sn.max_range).c_str(), sn.out_off, sn.n_rays);
+              "#pragma unroll\n    for (int i = 0; i < (%d * TE / 4 + NT - 1) / NT; ++i) if (i * NT + tid < %d * TE / 4) p[i * NT + tid] = v; }\n",
+           v.c_str(), v.c_str(), v.c_str(), v.c_str(), pl->sensors[k].out_off, rows, rows);
+      k = k2;
+    }
     s += "}\n";
     // pass 1: reach masks from the registers; every (sensor, target) within reach becomes one entry of the pair queue
     s += "VB_DI void world_lidar_pass1(const St& st, bool ok, int col, float* wcol, unsigned short* pq, int* qn) {\n  int n = 0;\n";
@@ -384,8 +390,9 @@ static std::string generate(const vmasb200_plan* pl, int te, int nt, JitLayout* 
              posx(tg).c_str(), fl(pl->tcull[sn.tg_begin + q].x).c_str(), k, 1u << q);
       }
       outf(s, "    wcol[%d * TE] = __uint_as_float(m%d);\n    if (!ok) m%d = 0u;\n", mrow, k, k);
-      outf(s, "    if (m%d) { float sn_, cs_; sincosf(%s, &sn_, &cs_); wcol[%d * TE] = cs_; wcol[%d * TE] = sn_; n += __popc(m%d); } }\n", k,
-           rotx(sn.entity).c_str(), kp.n_lmask_words + 2 * k, kp.n_lmask_words + 2 * k + 1, k);
+      outf(s, "#ifndef VB_AB_SINCOS_P2\n    if (m%d) { float sn_, cs_; sincosf(%s, &sn_, &cs_); wcol[%d * TE] = cs_; wcol[%d * TE] = sn_; }\n#endif\n", k,
+           rotx(sn.entity).c_str(), kp.n_lmask_words + 2 * k, kp.n_lmask_words + 2 * k + 1);
+      outf(s, "    n += __popc(m%d); }\n", k);
     }
     s += "  if (n) {\n    int b = atomicAdd(qn, n);\n";
     for (int k = 0; k < NS; ++k) {
