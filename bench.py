@@ -93,10 +93,10 @@ def peaks():
 
 def ncu_capture(scenario, n, compiled=False):
     """What the committed `ncu --set full` capture of this workload says about one launch of the step kernel
-    (profiles/r1w_traffic.json, else the earlier profiles/r1_traffic.json; written by tools/profile_collect.py):
+    (profiles/r1z_traffic.json, else the earlier r1w / r1 sets; written by tools/profile_collect.py):
     dram_bytes = dram__bytes_read.sum + dram__bytes_write.sum, warp_inst = smsp__inst_executed.sum.  Only a capture of
     the SAME kernel counts (world-compiled vmasb200_step_world or generic vb::step_kernel); {} when there is none."""
-    for name in ("r1w_traffic.json", "r1_traffic.json"):
+    for name in ("r1z_traffic.json", "r1w_traffic.json", "r1_traffic.json"):
         try:
             with open(os.path.join(ROOT, "profiles", name)) as f:
                 cap = json.load(f).get(f"{scenario}@{n}", {})
