@@ -283,6 +283,19 @@ int vmasb200_set_action(const float* action, int64_t stride_env, int64_t stride_
                         const float* u_range, const float* u_multiplier, int32_t clamp, float* u_out, int32_t* flags,
                         int64_t n_envs, void* stream);
 
+/* ---- the same for DISCRETE physical actions without communication / noise (environment.py:660-710):
+ * a flat action (the index into the cartesian product of the agent's action spaces, one column) or a multi-discrete
+ * one (one column per component) becomes u[k] = (a_k / (nvec[k] - 1)) * 2 u_range[k] - u_range[k], with the
+ * reference's re-ordering for odd nvec[k] (action 0 maps to u = 0), times u_multiplier[k].
+ *  action d: [n_envs][1 or action_size] integers of `action_dtype` (VMASB200_I64 / VMASB200_I32), element (i, k) at
+ *            action[i * stride_env + k * stride_k] (strides in elements)
+ *  nvec h: [action_size] agent.discrete_action_nvec (every entry > 1), action_size <= 8
+ *  flags: bit 2 = a component outside [0, nvec[k]) (environment.py:608-612, "Discrete physical actions are out of bounds") */
+enum { VMASB200_I64 = 0, VMASB200_I32 = 1 };
+int vmasb200_set_action_discrete(const void* action, int32_t action_dtype, int64_t stride_env, int64_t stride_k,
+                                 int32_t action_size, int32_t multidiscrete, const int32_t* nvec, const float* u_range,
+                                 const float* u_multiplier, float* u_out, int32_t* flags, int64_t n_envs, void* stream);
+
 /* ---- scenario hooks: what Environment._get_from_scenario (environment.py:253-308) asks of a scenario
  * after every World.step - observation / reward / done / info - as one or two launches per step instead of tens to
  * hundreds of small torch ops with host synchronisations (World.collides, boolean-mask indexing).  All tensors are read

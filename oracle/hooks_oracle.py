@@ -278,3 +278,31 @@ def football_obs_parts(g, t, team, i):
             parts += [(1, me[:, 0:2], st[j][:, 0:2], 0.0, f), (1, me[:, 2:4], st[j][:, 2:4], 0.0, f), (0, st[j][:, 2:4], None, 0.0, f),
                       (0, fo[j], None, 0.0, f)]
     return parts
+
+
+def set_action_discrete(action, nvec, u_range, u_mult, multidiscrete):
+    """Environment._set_action for discrete physical actions (environment.py:660-710): integer `action` [n, 1] (flat index
+    into the cartesian product of the action spaces) or [n, k] (multi-discrete) -> (u [n, k] fp32, out_of_bounds).
+    Floor division / modulo as torch's on integers; fp32 arithmetic in the reference's order."""
+    a = np.asarray(action).astype(np.int64)
+    k = len(nvec)
+    if multidiscrete:
+        comp = [a[:, i].copy() for i in range(k)]
+    else:
+        flat, comp = a[:, 0].copy(), []
+        for i in range(k):
+            n = int(np.prod(nvec[i + 1:], dtype=np.int64))
+            comp.append(flat // n)
+            flat = flat % n
+    u = np.zeros((a.shape[0], k), np.float32)
+    bad = False
+    for i, n in enumerate(nvec):
+        p = comp[i]
+        bad = bad or bool(((p < 0) | (p >= n)).any())
+        if n % 2:
+            stay, dec = p == 0, (p > 0) & (p <= n // 2)
+            p = np.where(stay, n // 2, np.where(dec, p - 1, p))
+        um = np.float32(u_range[i])
+        u[:, i] = (p.astype(np.float32) / np.float32(n - 1)) * (np.float32(2) * um) - um
+        u[:, i] = u[:, i] * np.float32(u_mult[i])
+    return u, bad

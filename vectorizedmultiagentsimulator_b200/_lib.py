@@ -14,7 +14,8 @@ EXPORTS = [
     "vmasb200_plan_layout", "vmasb200_plan_slots", "vmasb200_plan_pairs", "vmasb200_plan_joint_slots",
     "vmasb200_plan_lidar_slots", "vmasb200_step", "vmasb200_step_host", "vmasb200_cast_rays",
     "vmasb200_sync_check", "vmasb200_plan_tile", "vmasb200_get_distance", "vmasb200_is_overlapping",
-    "vmasb200_get_distance_from_point", "vmasb200_set_action", "vmasb200_gather_obs", "vmasb200_navigation_reward",
+    "vmasb200_get_distance_from_point", "vmasb200_set_action", "vmasb200_set_action_discrete", "vmasb200_gather_obs",
+    "vmasb200_navigation_reward",
     "vmasb200_transport_reward", "vmasb200_simple_spread_reward", "vmasb200_jit_enable", "vmasb200_plan_jit",
     "vmasb200_joint_passage_reward", "vmasb200_football_reward",
 ]
@@ -68,6 +69,8 @@ def lib():
     L.vmasb200_is_overlapping.argtypes = [vp, vp, vp, C.c_int64, vp]
     L.vmasb200_get_distance_from_point.argtypes = [vp, vp, C.c_int64, C.c_int64, vp, C.c_int64, vp]
     L.vmasb200_set_action.argtypes = [vp, C.c_int64, C.c_int64, C.c_int32, vp, vp, C.c_int32, vp, vp, C.c_int64, vp]
+    L.vmasb200_set_action_discrete.argtypes = [vp, C.c_int32, C.c_int64, C.c_int64, C.c_int32, C.c_int32, vp, vp, vp, vp, vp,
+                                               C.c_int64, vp]
     L.vmasb200_gather_obs.argtypes = [vp, C.c_int32, vp, vp, C.c_int32, C.c_int64, vp]
     L.vmasb200_navigation_reward.argtypes = [vp, C.c_int64, vp]
     L.vmasb200_transport_reward.argtypes = [vp, C.c_int64, vp]

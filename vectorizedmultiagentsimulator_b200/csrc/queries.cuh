@@ -138,4 +138,47 @@ __global__ void __launch_bounds__(256) set_action_kernel(const float* __restrict
   if (bad && (threadIdx.x & 31) == 0) atomicOr(flags, bad);
 }
 
+// Environment._set_action, discrete physical actions (environment.py:660-707): one thread per (env, component).
+//   flat action (one column): component k = (flat mod prod(nvec[k:])) div prod(nvec[k+1:]) with Python's floor
+//   semantics (component 0 is not reduced: an action beyond the product fails the range check, as in the reference);
+//   multi-discrete: component k is column k.
+//   range check [0, n) on the raw component (environment.py:608-612) -> flag bit 2;
+//   odd n: 0 -> n div 2, 1..n div 2 -> one less (the first action maps to u = 0);
+//   u = (float(a) / (n - 1)) * (2 u_max) - u_max, then u *= u_multiplier (fp32, the reference's op order).
+struct DiscParams { int nvec[8]; long long below[8]; float range[8], mult[8]; };
+VB_DI long long floor_div(long long a, long long b) { long long q = a / b; return (a % b != 0 && ((a < 0) != (b < 0))) ? q - 1 : q; }
+template <class AT>
+__global__ void __launch_bounds__(256) set_action_discrete_kernel(const AT* __restrict__ action, long long se, long long sk, int k_n,
+                                                                  int multi, const __grid_constant__ DiscParams dp,
+                                                                  float* __restrict__ u_out, int* __restrict__ flags, long long n) {
+  const long long gid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  int bad = 0;
+  if (gid < n * k_n) {
+    const long long i = gid / k_n;
+    const int k = (int)(gid - i * k_n);
+    long long a;
+    if (multi) {
+      a = (long long)action[i * se + k * sk];
+    } else {
+      long long flat = (long long)action[i * se];
+      if (k > 0) {  // flat % prod(nvec[k:]) (sign of the divisor), then // prod(nvec[k+1:])
+        const long long m = dp.below[k] * dp.nvec[k];
+        flat -= floor_div(flat, m) * m;
+      }
+      a = floor_div(flat, dp.below[k]);
+    }
+    const int nk = dp.nvec[k];
+    if (a < 0 || a >= nk) bad |= 4;
+    if (nk & 1) {
+      if (a == 0) a = nk / 2;
+      else if (a > 0 && a <= nk / 2) a -= 1;
+    }
+    const float um = dp.range[k];
+    const float u = ((float)a / (float)(nk - 1)) * (2.f * um) - um;
+    u_out[gid] = u * dp.mult[k];
+  }
+  bad = __reduce_or_sync(0xffffffffu, bad);
+  if (bad && (threadIdx.x & 31) == 0) atomicOr(flags, bad);
+}
+
 }  // namespace vb

@@ -604,6 +604,34 @@ int vmasb200_set_action(const float* action, int64_t stride_env, int64_t stride_
   return VMASB200_OK;
 }
 
+int vmasb200_set_action_discrete(const void* action, int32_t action_dtype, int64_t stride_env, int64_t stride_k,
+                                 int32_t action_size, int32_t multidiscrete, const int32_t* nvec, const float* u_range,
+                                 const float* u_multiplier, float* u_out, int32_t* flags, int64_t n, void* stream) {
+  if (!action || !nvec || !u_range || !u_multiplier || !u_out || !flags || n < 0 || action_size < 1 || action_size > 8 ||
+      (action_dtype != VMASB200_I64 && action_dtype != VMASB200_I32)) {
+    set_error("set_action_discrete: bad argument (1 <= action_size <= 8, int64 / int32 actions)"); return VMASB200_ERR_INVALID;
+  }
+  DiscParams dp{};
+  for (int k = 0; k < action_size; ++k) {
+    if (nvec[k] < 2) { set_error("set_action_discrete: nvec entries must be > 1"); return VMASB200_ERR_INVALID; }
+    dp.nvec[k] = nvec[k]; dp.range[k] = u_range[k]; dp.mult[k] = u_multiplier[k];
+  }
+  long long below = 1;
+  for (int k = action_size - 1; k >= 0; --k) { dp.below[k] = below; below *= nvec[k]; }
+  if (n == 0) return VMASB200_OK;
+  const long long total = (long long)n * action_size;
+  const unsigned grid = (unsigned)((total + 255) / 256);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (action_dtype == VMASB200_I64)
+    set_action_discrete_kernel<long long><<<grid, 256, 0, st>>>(static_cast<const long long*>(action), stride_env, stride_k,
+                                                                  action_size, multidiscrete, dp, u_out, flags, n);
+  else
+    set_action_discrete_kernel<int><<<grid, 256, 0, st>>>(static_cast<const int*>(action), stride_env, stride_k, action_size,
+                                                          multidiscrete, dp, u_out, flags, n);
+  VB_CUDA(cudaGetLastError());
+  return VMASB200_OK;
+}
+
 // ---------------------------------------------------------------------------------------------- scenario hooks (8 f1)
 static DVec to_dvec(const vmasb200_vec& v) { DVec d; d.p = v.p; d.se = v.stride_env; d.sk = v.stride_k; return d; }
 

@@ -314,6 +314,8 @@ class WorldBinding:
               and 1 <= agent.action_size <= 8 and action.shape[1] == agent.action_size
               and not (getattr(env, "grad_enabled", False) and action.requires_grad))
         if not ok:
+            if self._set_action_discrete(env, action, agent, act, noisy):
+                return None
             return self.orig_set_action(action, agent)
         key = (id(agent), repr(act.u_range), repr(act.u_multiplier))
         c = self._act_consts.get(id(agent))
@@ -332,6 +334,40 @@ class WorldBinding:
         act.u = u
         self._act_pending = True
 
+    def _set_action_discrete(self, env, action, agent, act, noisy):
+        """Discrete physical actions (flat or multi-discrete, int64 / int32) without communication / noise
+        (environment.py:660-710): one launch (vmasb200_set_action_discrete) instead of ~25 ops and a host
+        synchronisation per action component.  False = not this case, the caller takes the original."""
+        torch = self.torch
+        if getattr(env, "continuous_actions", True) or act is None or noisy or not torch.is_tensor(action):
+            return False
+        multi = bool(getattr(env, "multidiscrete_actions", False))
+        nvec = list(getattr(agent, "discrete_action_nvec", []) or [])
+        k = agent.action_size
+        ok = (action.is_cuda and action.dtype in (torch.int64, torch.int32) and action.dim() == 2 and action.shape[0] == self.n
+              and (self.world.dim_c == 0 or agent.silent) and 1 <= k <= 8 and len(nvec) == k
+              and action.shape[1] == (k if multi else 1) and all(int(v) > 1 for v in nvec))
+        if not ok:
+            return False
+        key = (id(agent), "d", repr(act.u_range), repr(act.u_multiplier), tuple(int(v) for v in nvec))
+        c = self._act_consts.get((id(agent), "d"))
+        if c is None or c[0] != key:
+            rng = (C.c_float * k)(*[float(v) for v in act.u_range_tensor.tolist()])
+            mul = (C.c_float * k)(*[float(v) for v in act.u_multiplier_tensor.tolist()])
+            nv = (C.c_int32 * k)(*[int(v) for v in nvec])
+            c = self._act_consts[(id(agent), "d")] = (key, rng, mul, nv)
+        if self._act_flags is None:
+            self._act_flags = torch.zeros(1, dtype=torch.int32, device=self.device)
+        u = torch.empty(self.n, k, device=self.device)
+        L = _lib.lib()
+        _lib.check(L.vmasb200_set_action_discrete(
+            action.data_ptr(), 0 if action.dtype == torch.int64 else 1, action.stride(0), action.stride(1), k, int(multi),
+            c[3], c[1], c[2], u.data_ptr(), self._act_flags.data_ptr(), self.n, _lib.raw_stream(torch, self.device)),
+            "vmasb200_set_action_discrete")
+        act.u = u
+        self._act_pending = True
+        return True
+
     def check_actions(self):
         """The reference's assertions on the actions set since the last check (environment.py:622, 647-649)."""
         if not self._act_pending:
@@ -342,6 +378,7 @@ class WorldBinding:
             self._act_flags.zero_()
             assert not bad & 1, "an action holds NaN"
             assert not bad & 2, "Physical actions of an agent are out of its range"
+            assert not bad & 4, "Discrete physical actions are out of bounds"
 
     # ------------------------------------------------------------------ distance queries of reward code
     def _poses(self, *entities):
