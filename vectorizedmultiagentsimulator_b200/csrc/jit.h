@@ -134,6 +134,7 @@ struct JitLayout {            // the compact LIDAR tile of the compiled kernel (
   std::vector<int> lid_ents;  // entities staged for the epilogue: 3 env rows each (px py rot)
   std::vector<int> lid_trig;  // of those, the non-sphere targets: 4 work rows each (cos/sin cache)
   int work_rows = 0;
+  int smem_rows = 0;          // > 0: the compiled epilogue's own carve-up (rows of TE words), else kernels.cuh smem_map
   bool thin_possible = false;
 };
 
@@ -303,9 +304,14 @@ static std::string generate(const vmasb200_plan* pl, int te, int nt, JitLayout* 
   const int CB = bits(te), KB = bits(std::max(NS, 1)), RB = bits(std::max(kp.max_rays, 1)), PB = bits(std::max(NPT, 1));
   bool lc = lidar;
   for (const DSensor& sn : pl->sensors) lc = lc && sn.n_tw == 1 && sn.n_targets >= 1 && sn.n_rays >= 1;
-  lc = lc && (te & (te - 1)) == 0 && CB + KB + RB <= 16 && CB + PB <= 16 && NPT <= 2 * NS + R;
+  lc = lc && (te & (te - 1)) == 0 && CB + KB + RB <= 16 && CB + PB <= 16;
   outf(s, "constexpr bool LIDAR_COMPILED = %s;\n", lc ? "true" : "false");
+  lay->smem_rows = 0;
   if (lc) {
+    // shared-memory rows of the compiled epilogue: [env 3 per staged entity][work][lid R][queues: (NPT + R) 16-bit entries per env]
+    const int l_env = 0, l_work = l_env + 3 * (int)lay->lid_ents.size(), l_lid = l_work + lay->work_rows, l_q = l_lid + R;
+    lay->smem_rows = l_q + (NPT + R + 1) / 2;
+    outf(s, "constexpr int L_ENV = %d, L_WORK = %d, L_LID = %d, L_Q = %d;\n", l_env, l_work, l_lid, l_q);
     outf(s, "constexpr int NPT = %d, CB = %d, KB = %d, RAYS_TOTAL = %d;\n", NPT, CB, KB, R);
     // per (sensor, target) tables; a column whose entries are all equal becomes a literal
     struct Col { const char* name; const char* type; std::vector<std::string> v; };
@@ -402,7 +408,7 @@ static std::string generate(const vmasb200_plan* pl, int te, int nt, JitLayout* 
     }
     s += "  }\n}\n";
   } else {
-    s += "constexpr int NPT = 1, CB = 0, KB = 0, RAYS_TOTAL = 1, SHARED_RAYS = 0;\n__constant__ float2 T_raycs[1] = {{0.f, 0.f}};\n"
+    s += "constexpr int L_ENV = 0, L_WORK = 0, L_LID = 0, L_Q = 0;\nconstexpr int NPT = 1, CB = 0, KB = 0, RAYS_TOTAL = 1, SHARED_RAYS = 0;\n__constant__ float2 T_raycs[1] = {{0.f, 0.f}};\n"
          "VB_DI int p_es(int) { return 0; }\nVB_DI int p_cr(int) { return 0; }\nVB_DI int p_ts(int) { return 0; }\n"
          "VB_DI int p_out(int) { return 0; }\nVB_DI int p_nr(int) { return 0; }\nVB_DI int p_k(int) { return 0; }\n"
          "VB_DI float p_lat(int) { return 0.f; }\nVB_DI float p_along(int) { return 0.f; }\nVB_DI float p_slk(int) { return 0.f; }\n"
@@ -533,6 +539,16 @@ static int jit_tile(const vmasb200_plan* pl, long long n) {
   return pl->kp.n_rays ? 64 : 128;
 }
 
+// threads of a LIDAR world's CTA: the TE physics threads plus helper warps for the epilogue's passes
+static int jit_lidar_threads(int te) {
+  if (const char* e = getenv("VMASB200_JIT_NT")) {  // experiments (tools/ab_jit.sh): a multiple of 32, >= te
+    const int v = atoi(e);
+    if (v >= te && v % 32 == 0 && v <= 1024) return v;
+  }
+  // measured (navigation, tools/ab_jit.sh): 32-env tiles 128 threads (64: 14.4 us against 12.7 us at 32 768 envs);
+  // 64-env tiles 96 (141.5 us at 1 M envs; 128: 145.0, 64: 148.1, 256: 250.7)
+  return te == 64 ? 96 : std::max(te, kThreads);
+}
 static void jit_kparams(const vmasb200_plan* pl, int te, const JitLayout& lay, KParams* out) {
   KParams k = pl->kp;
   k.TE = te; k.NT = kThreads;
@@ -561,7 +577,7 @@ static JitKernel* jit_get(vmasb200_plan* pl, int te, bool compile_only, std::str
   if (jk.func) return &jk;
   const bool lidar = pl->kp.n_rays > 0;
   JitLayout lay;
-  const int nt = lidar ? kThreads : te;
+  const int nt = lidar ? jit_lidar_threads(te) : te;
   std::string err;
   std::string& cubin = ps.cubin[te];
   if (cubin.empty()) cubin = jit_compile(pl, te, nt, &lay, &err);
@@ -577,7 +593,7 @@ static JitKernel* jit_get(vmasb200_plan* pl, int te, bool compile_only, std::str
   if (!load_driver()) { jk.failed = true; return say("libcuda.so.1 not found"); }
   jit_kparams(pl, te, lay, &jk.kp);
   jit_kparams_generic(pl, &jk.kpg);
-  jk.smem_bytes = lidar ? smem_map(jk.kp).total_bytes : 0;
+  jk.smem_bytes = !lidar ? 0 : lay.smem_rows ? lay.smem_rows * te * 4 : smem_map(jk.kp).total_bytes;
   auto fail = [&](const char* what, int rc) {
     jk.failed = true;
     if (jk.module) { g_drv.ModuleUnload(jk.module); jk.module = nullptr; }

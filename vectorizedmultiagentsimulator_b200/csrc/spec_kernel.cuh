@@ -210,11 +210,16 @@ vmasb200_step_world(const __grid_constant__ KParams kp, const __grid_constant__ 
     }
   }
   if (LIDAR && sa.do_lidar && sa.lidar_out) {
-    const SmemMap m = smem_map(kp);
     Tile t;
-    t.envS = smem + m.env; t.workS = smem + m.work; t.lidS = smem + m.lid;
-    t.queue = reinterpret_cast<int*>(smem + m.queue); t.rayq = reinterpret_cast<int*>(smem + m.rayq);
-    t.qcount = reinterpret_cast<int*>(smem + m.bar) + 2;
+    if (LIDAR_COMPILED) {  // the generator's own carve-up (jit.h): no mbarrier, 16-bit queues
+      t.envS = smem + L_ENV * TE; t.workS = smem + L_WORK * TE; t.lidS = smem + L_LID * TE;
+      t.queue = reinterpret_cast<int*>(smem + L_Q * TE); t.rayq = nullptr; t.qcount = nullptr;
+    } else {
+      const SmemMap m = smem_map(kp);
+      t.envS = smem + m.env; t.workS = smem + m.work; t.lidS = smem + m.lid;
+      t.queue = reinterpret_cast<int*>(smem + m.queue); t.rayq = reinterpret_cast<int*>(smem + m.rayq);
+      t.qcount = reinterpret_cast<int*>(smem + m.bar) + 2;
+    }
     // LIDAR rows: 16-byte stores straight from the tile (rows are 16-byte aligned: ld % 4 == 0, env0 % TE == 0; a TMA
     // bulk store per row costs the issuing warp ~14 instructions per row, one lane at a time, and a wait before the CTA
     // may leave).  The batch's last tile also carries the padding columns up to ld.
