@@ -160,10 +160,10 @@ vmasb200_step_world(const __grid_constant__ KParams kp, const __grid_constant__ 
   const bool ok = phys && tid < n_valid;
   const long long env = env0 + (ok ? tid : 0);
   St st;
+  int taint = 0;  // 0, or 1 + the env's index in sa.u_list (kernels.cuh run_substeps)
   if (phys) {
     world_load(st, aio, sa, env);
     world_begin(st);
-    int taint = 0;  // 0, or 1 + the env's index in sa.u_list (kernels.cuh run_substeps)
     for (int s = 0; s < S; ++s) {
 #pragma unroll
       for (int w = 0; w < kPW; ++w) { st.verd[w] = 0u; st.thin[w] = 0u; }
@@ -203,6 +203,22 @@ vmasb200_step_world(const __grid_constant__ KParams kp, const __grid_constant__ 
         }
       }
     }
+  }
+  // Everything the step's last CTA reads (verdict words, taint records) is written by now; the state and LIDAR rows
+  // are not part of that hand-shake (a repair runs in a kernel of its own).  So the CTA is counted HERE by one thread
+  // - barrier, fence, atomic; the result stays in a register - and the round trip overlaps the stores below.  (Worlds
+  // with the compiled LIDAR epilogue count behind its first barrier instead, which saves this one.)
+  int count_old = -1;
+#ifndef VB_AB_LATE_COUNT2
+  if (!(LIDAR && LIDAR_COMPILED && sa.do_lidar && sa.lidar_out)) {
+    __syncthreads();
+    if (tid == NT - 1) {
+      __threadfence();
+      count_old = atomicAdd(sa.counters, 1);
+    }
+  }
+#endif
+  if (phys) {
     if (ok) {
       if (THIN_POSSIBLE && taint)  // keep the INPUT state of a tainted env (dyn_in is intact until our own store)
         for (int r = 0; r < DYN_ROWS; ++r) sa.u_buf[(size_t)(taint - 1) * DYN_ROWS + r] = sa.dyn_in[(size_t)r * sa.ld + env];
@@ -273,11 +289,15 @@ vmasb200_step_world(const __grid_constant__ KParams kp, const __grid_constant__ 
   // last CTA reads (verdict words, records) is written by the physics, so lidar_world counts the CTA right behind the
   // physics and the atomic's latency hides under the LIDAR passes; its closing barrier publishes s_last.
   if (!counted) {
+#ifndef VB_AB_LATE_COUNT2
+    if (tid == NT - 1) s_last = (count_old == sa.total_ctas - 1);
+#else
     __syncthreads();
     if (tid == 0) {
       __threadfence();
       s_last = (atomicAdd(sa.counters, 1) == sa.total_ctas - 1);
     }
+#endif
     __syncthreads();
   }
   if (!s_last) return;
