@@ -18,19 +18,26 @@ bench() {  # name, args...
 # 1. the driver's command (navigation, 32768 envs, e2e + CPU baseline) and the other configs at the same size
 bench navigation
 for sc in transport football joint_passage simple_spread; do bench $sc --scenario $sc; done
+# (KERNEL_ONLY=1: only what depends on the step kernel - skips the generic-kernel runs and the reference arms)
+if [ -z "$KERNEL_ONLY" ]; then
 # the same launches through the generic table-walking kernel (world-compiled kernels off)
 for sc in navigation transport simple_spread; do VMASB200_JIT=0 bench generic_$sc --scenario $sc --no-cpu-baseline --no-e2e; done
+fi
 # 2. the large-batch points the roofline fraction is quoted on
 for sc in navigation transport football simple_spread; do bench ${sc}_1m --scenario $sc --num-envs 1048576 --steps 50 --no-cpu-baseline --no-e2e; done
+if [ -z "$KERNEL_ONLY" ]; then
 for sc in navigation transport simple_spread; do VMASB200_JIT=0 bench generic_${sc}_1m --scenario $sc --num-envs 1048576 --steps 50 --no-cpu-baseline --no-e2e; done
+fi
 for n in 4096 16384 65536 262144; do bench football_$n --scenario football --num-envs $n --steps 100 --no-cpu-baseline --no-e2e; done
 # 3. reference arms: the reference's torch CPU step, its torch CUDA step, and the drop-in inside its Environment
+if [ -z "$KERNEL_ONLY" ]; then
 bench reference_navigation --impl reference --steps 3 --warmup 1
 for sc in navigation transport simple_spread joint_passage football; do
   bench reference-cuda_$sc --impl reference-cuda --scenario $sc --steps 30
   bench dropin-hooks_$sc --impl dropin-hooks --scenario $sc --steps 50
 done
 for sc in navigation transport simple_spread joint_passage; do bench dropin-graph_$sc --impl dropin-graph --scenario $sc --steps 50; done
+fi
 # 4. ncu: launch list of the driver's command, then one full capture per workload (only after the plain runs above)
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $OUT/launches_navigation.csv \
   $PY bench.py --steps 20 --warmup 3 --no-cpu-baseline > $OUT/launches_navigation.log 2>&1
