@@ -56,3 +56,22 @@ def test_mode_2_compiles_every_covered_world(name, tmp_path, monkeypatch):
         assert StepPlan(fx.desc).jit(fx.n_envs)[0] == 1, L.vmasb200_last_error()
     finally:
         L.vmasb200_jit_enable(prev)
+
+
+@pytest.mark.skipif(not HAVE_NVRTC, reason="no libnvrtc in this image")
+def test_experiment_switches_are_part_of_the_cache_key(tmp_path, monkeypatch):
+    """VMASB200_JIT_DEFINES (extra NVRTC options) and VMASB200_JIT_NT (threads of a LIDAR world's CTA), the switches
+    of tools/ab_jit.sh, must give cubins of their own: a variant may never be served from another variant's cache"""
+    monkeypatch.setenv("VMASB200_JIT_CACHE", str(tmp_path))
+    fx = Fixture("navigation")
+    seen = set()
+    for defs, nt in (("", ""), ("-DVB_AB_SINCOS_P2", ""), ("", "64")):
+        monkeypatch.setenv("VMASB200_JIT_DEFINES", defs)
+        if nt:
+            monkeypatch.setenv("VMASB200_JIT_NT", nt)
+        else:
+            monkeypatch.delenv("VMASB200_JIT_NT", raising=False)
+        assert StepPlan(fx.desc).jit(fx.n_envs)[0] == 1, _lib.lib().vmasb200_last_error()
+        now = {f for f in os.listdir(tmp_path) if f.endswith(".cubin")}
+        assert len(now - seen) == 1, (defs, nt, now)
+        seen = now
