@@ -368,6 +368,20 @@ typedef struct vmasb200_navigation {
 } vmasb200_navigation;
 int vmasb200_navigation_reward(const vmasb200_navigation* nv, int64_t n_envs, void* stream);
 
+/* Allocation-free variant of vmasb200_navigation_reward.  It has NO counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA-graph capture, tight serving
+ * loops, harnesses that forbid allocation).  Same inputs, outputs, launches and results as vmasb200_navigation_reward,
+ * but `nv->pair_flags` is IGNORED (may be NULL): the scratch of the flag reduction lives in a file-scope
+ * `static __device__ __align__(256)` array of VMASB200_NAV_STATIC_WORDS words (256 bytes, held by every GPU that loads
+ * the library until the process exits).  Limit: n_agents <= VMASB200_NAV_MAX_AGENTS (16 agents = 120 pairs = 4 flag
+ * words); more is rejected with VMASB200_ERR_INVALID and a message.  The call makes no cudaMalloc / cudaFree and calls no
+ * allocating library routine; the array's device address is looked up once per device (cudaGetSymbolAddress, with that
+ * device current) on the first call there.  Every call on a device shares the one array: the words in use are zeroed on
+ * `stream` at the start of each call, and two calls that overlap on the GPU (different streams, no ordering) RACE on it -
+ * order them, or use vmasb200_navigation_reward with a scratch of their own. */
+#define VMASB200_NAV_STATIC_WORDS 64
+int vmasb200_navigation_reward_static(const vmasb200_navigation* nv, int64_t n_envs, void* stream);
+
 /* transport.py:130-164 (reward), :186-193 (done): package.dist_to_goal, package.on_goal (World.is_overlapping with its
  * goal), package.color, the shared reward and the new package.global_shaping, for every package in one launch. */
 #define VMASB200_TRANSPORT_MAX_PACKAGES 8

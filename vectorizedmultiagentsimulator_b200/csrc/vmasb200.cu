@@ -722,6 +722,46 @@ int vmasb200_navigation_reward(const vmasb200_navigation* nv, int64_t n, void* s
   return VMASB200_OK;
 }
 
+// ---- allocation-free variant of vmasb200_navigation_reward (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: CUDA-graph capture, tight serving loops, harnesses that
+// forbid allocation).  The scratch of the flag reduction (nav_flags_kernel -> nav_reward_kernel: one bit per agent pair,
+// 120 pairs = 4 words at the maximum of 16 agents) lives in a file-scope device array that every GPU loading the library
+// holds until exit.  g_nav_static_flags is a HOST-side stand-in for that array in host code, not a device address: the
+// device address is asked for once per device, with that device current, by cudaGetSymbolAddress.
+static __device__ __align__(256) uint32_t g_nav_static_flags[VMASB200_NAV_STATIC_WORDS];
+static uint32_t* g_nav_static_ptr[64];  // per device, filled on the first call there
+static std::mutex g_nav_static_mu;
+
+int vmasb200_navigation_reward_static(const vmasb200_navigation* nv, int64_t n, void* stream) {
+  if (!nv) { set_error("navigation_reward_static: NULL argument"); return VMASB200_ERR_INVALID; }
+  if (nv->n_agents < 1 || nv->n_agents > VMASB200_NAV_MAX_AGENTS) {
+    set_error("navigation_reward_static: n_agents = " + std::to_string(nv->n_agents) + " is outside 1.." +
+              std::to_string(VMASB200_NAV_MAX_AGENTS) + ": the static scratch holds the pair flags of at most " +
+              std::to_string(VMASB200_NAV_MAX_AGENTS) + " agents (120 pairs, 4 of its " +
+              std::to_string(VMASB200_NAV_STATIC_WORDS) + " words)");
+    return VMASB200_ERR_INVALID;
+  }
+  static_assert((VMASB200_NAV_MAX_AGENTS * (VMASB200_NAV_MAX_AGENTS - 1) / 2 + 31) / 32 <= VMASB200_NAV_STATIC_WORDS, "scratch too small");
+  int dev = -1;
+  VB_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) { set_error("navigation_reward_static: device index outside 0..63"); return VMASB200_ERR_UNSUPPORTED; }
+  uint32_t* scratch = nullptr;
+  {
+    std::lock_guard<std::mutex> lock(g_nav_static_mu);
+    if (!g_nav_static_ptr[dev]) {
+      void* p = nullptr;
+      VB_CUDA(cudaGetSymbolAddress(&p, g_nav_static_flags));
+      g_nav_static_ptr[dev] = static_cast<uint32_t*>(p);
+    }
+    scratch = g_nav_static_ptr[dev];
+  }
+  // same launches as vmasb200_navigation_reward, which zeroes the words it uses (cudaMemsetAsync on the stream) before
+  // nav_flags_kernel ORs into them: the array keeps the previous call's bits otherwise
+  vmasb200_navigation with_scratch = *nv;
+  with_scratch.pair_flags = scratch;
+  return vmasb200_navigation_reward(&with_scratch, n, stream);
+}
+
 int vmasb200_transport_reward(const vmasb200_transport* tr, int64_t n, void* stream) {
   if (!tr || n < 0 || tr->n_packages < 1 || tr->n_packages > VMASB200_TRANSPORT_MAX_PACKAGES || !tr->rew) {
     set_error("transport_reward: bad argument (1 <= n_packages <= 8, rew)"); return VMASB200_ERR_INVALID;
