@@ -44,7 +44,7 @@
 extern "C" {
 #endif
 
-#define VMASB200_ABI_VERSION 2
+#define VMASB200_ABI_VERSION 3
 
 typedef enum vmasb200_status {
   VMASB200_OK = 0,
@@ -87,7 +87,8 @@ typedef struct vmasb200_entity {
   float moment_of_inertia;    /* Shape.moment_of_inertia(mass), core.py:122,159,186 (double -> fp32)  */
   float max_speed;
   float v_range;
-  float drag;
+  double drag;                /* entity.drag as the Python float it is: the reference forms 1 - drag in double before
+                                 the product with an fp32 tensor (core.py:2866-2869)                      */
   float linear_friction;
   float angular_friction;
   float gravity[2];
@@ -131,9 +132,9 @@ typedef struct vmasb200_world_desc {
   int32_t n_lidars;
   const vmasb200_lidar* lidars;     /* h: [n_lidars]                                                 */
   /* World constants, core.py:1090-1143 */
-  float dt;
-  int32_t substeps;
-  float drag;
+  double dt;               /* Python floats: sub_dt = dt / substeps (core.py:1124) and 1 - drag (core.py:2866) are  */
+  int32_t substeps;        /* formed in double and only then meet an fp32 tensor                                    */
+  double drag;
   float linear_friction, angular_friction;
   int32_t has_x_semidim, has_y_semidim;
   float x_semidim, y_semidim;
@@ -180,6 +181,9 @@ int vmasb200_plan_pairs(const vmasb200_plan* plan, vmasb200_pair* pairs);
 int vmasb200_plan_joint_slots(const vmasb200_plan* plan, int32_t* joint_slot);
 /* first row inside the lidar buffer of sensor i. h: [n_lidars] */
 int vmasb200_plan_lidar_slots(const vmasb200_plan* plan, int32_t* lidar_slot);
+/* entity index of every cos/sin cache slot (the row order of vmasb200_step_io.trig_in); returns their number.
+ * h: trig_entities [n_entities] or NULL. */
+int vmasb200_plan_trig_entities(const vmasb200_plan* plan, int32_t* trig_entities);
 /* environments per CTA a step over n_envs environments runs with (32, 64 or 128): the description's envs_per_cta,
  * or, when that is 0, chosen from the batch size.  128 / tile threads share each environment's work. */
 int vmasb200_plan_tile(const vmasb200_plan* plan, int64_t n_envs);
@@ -221,6 +225,27 @@ typedef struct vmasb200_step_io {
    * 1: always take the exact per-substep path (flag reduction before every substep).                    */
   int32_t exact;
   void* stream;                    /* cudaStream_t                                                       */
+  /* ---- probe fields (parity tests, tests/test_gpu_substeps.py); all zero / NULL in normal use; they need exact != 0.
+   * substep_begin / substep_end: run only substeps [begin, end) of the World.step loop (core.py:1974; drag is applied
+   *   when substep 0 is among them, core.py:2868); both 0 = all substeps.  The clamp of core.py:2017-2040 is replayed
+   *   for the substeps before `begin` unless force_ptrs already hold the write-back of substep begin - 1
+   *   (forces_are_substep_inputs != 0).
+   * trig_in  d: [4 * n_trig][ld] cos(rot) sin(rot) cos(rot + pi/2) sin(rot + pi/2) of every entity with a cos/sin
+   *   cache, in plan order (vmasb200_plan_trig_entities): used INSTEAD of computing them at the start of the launch
+   *   (a test hands in the reference's own torch.cos / torch.sin values: MKL's on the CPU), or NULL.
+   * jexp_in  d: [n_joints][ld] exp(|rot_a - (rot_b + fixed_rotation)|) of every joint (core.py:2848-2852: torch.exp, MKL's on
+ *   the CPU; exp(a) - 1 cancels for small a), used instead of expf for the joints with rotate == 0; needs a one-substep
+ *   range; or NULL.
+ * force_out d: [3 * n_dyn][ld] forces_dict / torques_dict (core.py:1975-1992) of every dynamic entity (Fx Fy T, plan
+   *   order of the dynamic entities) as _integrate_state of the LAST substep run read them, or NULL.
+   * joint_out d: [4 * n_joints][ld] per joint (fx fy on entity_a; torque on a; torque on b) of the last substep run -
+   *   what core.py:2282-2291 hands to update_env_forces (the force on b is the negation) -, or NULL. */
+  int32_t substep_begin, substep_end;
+  int32_t forces_are_substep_inputs;
+  const float* trig_in;
+  float* force_out;
+  float* joint_out;
+  const float* jexp_in;
 } vmasb200_step_io;
 
 /* One World.step(): all substeps of {action/friction/gravity forces, joints, six collision pair types,

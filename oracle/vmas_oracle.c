@@ -13,6 +13,7 @@
  * Build: make -C oracle   (gcc -O2 -ffp-contract=off -fopenmp -shared -fPIC)
  */
 #include "vmas_oracle.h"
+#include "sleef_f32.h"
 
 #include <math.h>
 #include <stdlib.h>
@@ -42,11 +43,24 @@ static inline float fsign(float x) { return (float)((0.f < x) - (x < 0.f)); }
 static inline float clampf(float x, float lo, float hi) { float m = x < lo ? lo : x; return m > hi ? hi : m; }
 static const v2 VINF = {INFINITY, INFINITY};
 
-/* utils.py:176-191 rotate_vector */
-static inline v2 vrot(v2 v, float ang) {
-  float c = cosf(ang), s = sinf(ang);
-  return V(v.x * c - v.y * s, v.x * s + v.y * c);
+/* cos / sin of an entity's rotation as the reference's call sites take them: (c, s) = torch.cos / torch.sin of rot
+ * (utils.py:183-184, physics.py:299, 412), (c2, s2) of rot + pi/2 (physics.py:300-301, an fp32 sum).  By default they come
+ * from libm; a substep may instead be handed the values torch computed for the same angles (vmas_oracle_substep `trig`):
+ * torch's CPU cos / sin / exp are Intel MKL VML's (vsCos / vsSin / vsExp, high-accuracy mode; closed source, not
+ * correctly rounded: they differ from libm's correctly rounded results by 1 ulp on ~5 % of arguments), and a 1-ulp
+ * difference in an anchor's cos / sin is what a stiff joint (joint_force 900 on a moment of inertia of 5e-4) amplifies. */
+typedef struct { float c, s, c2, s2; } tg;
+static inline tg tg_of(float rot) {
+  tg t;
+  float rot2 = rot + (float)(M_PI / 2);
+  t.c = cosf(rot); t.s = sinf(rot); t.c2 = cosf(rot2); t.s2 = sinf(rot2);
+  return t;
 }
+static inline tg tg_cs(float c, float s) { tg t = {c, s, 0.f, 0.f}; return t; }
+
+/* utils.py:176-191 rotate_vector */
+static inline v2 vrot_cs(v2 v, float c, float s) { return V(v.x * c - v.y * s, v.x * s + v.y * c); }
+static inline v2 vrot(v2 v, float ang) { return vrot_cs(v, cosf(ang), sinf(ang)); }
 
 /* utils.py:168-173 clamp_with_norm on a 2-vector */
 static inline v2 clamp_norm2(v2 t, float maxn) {
@@ -61,15 +75,19 @@ static inline float clamp_norm1(float t, float maxn) {
   return (n > maxn) ? nt : t;
 }
 
-/* torch.logaddexp(0, x) (ATen: max + log1p(exp(-|a-b|)), inf==inf shortcut irrelevant for a=0) */
-static inline float softplus0(float x) {
+/* torch.logaddexp(0, x) (ATen BinaryOpsKernel logaddexp: max + log1p(exp(-|a-b|)), inf==inf shortcut irrelevant for
+ * a=0).  Its vectorised CPU path takes exp and log1p from Vectorized<float>, i.e. SLEEF's expf_u10 / log1pf_u10
+ * (sleef_f32.h restates them; checked bit for bit against the Sleef_* symbols of torch 2.11.0's libtorch_cpu.so). */
+static inline float softplus0v(float x, int vectorised) {
   float m = 0.f > x ? 0.f : x;
-  return m + log1pf(expf(-fabsf(0.f - x)));
+  /* ATen's cpu_kernel_vec runs whole groups of 2 x Vec::size() elements through the Vectorized (SLEEF) lambda and the
+   * remaining tail of the tensor through the scalar one (std::exp, std::log1p: libm), Loops.h vectorized_loop */
+  return vectorised ? m + sleef_log1pf_u10(sleef_expf_u10(-fabsf(0.f - x))) : m + log1pf(expf(-fabsf(0.f - x)));
 }
 
 /* physics.py:399-428 _get_closest_point_line */
-static inline v2 closest_point_line(v2 lp, float rot, float length, v2 q, int limit) {
-  v2 u = V(cosf(rot), sinf(rot));
+static inline v2 closest_point_line(v2 lp, tg rot, float length, v2 q, int limit) {
+  v2 u = V(rot.c, rot.s);
   v2 delta = vsub(lp, q);
   float dot = vdot(delta, u);
   float sg = fsign(dot);
@@ -80,13 +98,13 @@ static inline v2 closest_point_line(v2 lp, float rot, float length, v2 q, int li
   return vsub(lp, V(sm * u.x, sm * u.y));
 }
 
-typedef struct { v2 p[4]; float rot[4]; float len[4]; } boxlines;
+typedef struct { v2 p[4]; tg rot[4]; float len[4]; } boxlines;
 
 /* physics.py:297-324 _get_all_lines_box */
-static inline void all_lines_box(v2 pos, float rot, float width, float length, boxlines* o) {
-  v2 rv = V(cosf(rot), sinf(rot));
-  float rot2 = rot + (float)(M_PI / 2);
-  v2 rv2 = V(cosf(rot2), sinf(rot2));
+static inline void all_lines_box(v2 pos, tg rot, float width, float length, boxlines* o) {
+  v2 rv = V(rot.c, rot.s);
+  v2 rv2 = V(rot.c2, rot.s2);
+  tg rot2 = tg_cs(rot.c2, rot.s2);
   float hl = length / 2.f, hw = width / 2.f;
   o->p[0] = vadd(pos, vscale(rv, hl));
   o->p[1] = vsub(pos, vscale(rv, hl));
@@ -99,7 +117,7 @@ static inline void all_lines_box(v2 pos, float rot, float width, float length, b
 }
 
 /* physics.py:262-294 _get_closest_point_box */
-static inline v2 closest_point_box(v2 pos, float rot, float width, float length, v2 q) {
+static inline v2 closest_point_box(v2 pos, tg rot, float width, float length, v2 q) {
   boxlines bl;
   all_lines_box(pos, rot, width, length, &bl);
   v2 best = VINF;
@@ -125,9 +143,9 @@ static inline v2 inner_point_box(v2 outside, v2 surface, v2 box_pos, float* d_ou
 }
 
 /* physics.py:131-259 _get_line_extrema + _get_intersection_point_line_line + _get_closest_points_line_line */
-static inline void closest_points_line_line(v2 pa, float ra, float la, v2 pb, float rb, float lb, v2* o1, v2* o2) {
-  v2 xya = V((la / 2.f) * cosf(ra), (la / 2.f) * sinf(ra));
-  v2 xyb = V((lb / 2.f) * cosf(rb), (lb / 2.f) * sinf(rb));
+static inline void closest_points_line_line(v2 pa, tg ra, float la, v2 pb, tg rb, float lb, v2* o1, v2* o2) {
+  v2 xya = V((la / 2.f) * ra.c, (la / 2.f) * ra.s);
+  v2 xyb = V((lb / 2.f) * rb.c, (lb / 2.f) * rb.s);
   v2 a1 = vadd(pa, xya), a2 = vsub(pa, xya);
   v2 b1 = vadd(pb, xyb), b2 = vsub(pb, xyb);
   /* intersection */
@@ -153,7 +171,7 @@ static inline void closest_points_line_line(v2 pa, float ra, float la, v2 pb, fl
 }
 
 /* physics.py:327-381 _get_closest_line_box -> (point on box, point on line) */
-static inline void closest_line_box(v2 bpos, float brot, float bw, float bl_, v2 lpos, float lrot, float llen,
+static inline void closest_line_box(v2 bpos, tg brot, float bw, float bl_, v2 lpos, tg lrot, float llen,
                                     v2* pbox, v2* pline) {
   boxlines bl;
   all_lines_box(bpos, brot, bw, bl_, &bl);
@@ -169,7 +187,7 @@ static inline void closest_line_box(v2 bpos, float brot, float bw, float bl_, v2
 }
 
 /* physics.py:25-128 _get_closest_box_box -> (point on box1, point on box2) */
-static inline void closest_box_box(v2 p1, float r1, float w1, float l1, v2 p2, float r2, float w2, float l2, v2* o1,
+static inline void closest_box_box(v2 p1, tg r1, float w1, float l1, v2 p2, tg r2, float w2, float l2, v2* o1,
                                    v2* o2) {
   boxlines la, lb;
   all_lines_box(p1, r1, w1, l1, &la);
@@ -197,11 +215,11 @@ static inline void closest_box_box(v2 p1, float r1, float w1, float l1, v2 p2, f
 /* ------------------------------------------------------------------------------------------------------------
  * core.py:2804-2838 _get_constraint_forces; returns force on a (force on b is its negation).
  * K = force_multiplier, k = contact_margin. */
-static inline v2 constraint_force(v2 pa, v2 pb, float dist_min, float K, float k, int attractive) {
+static inline v2 constraint_force(v2 pa, v2 pb, float dist_min, float K, float k, int attractive, int vectorised) {
   v2 delta = vsub(pa, pb);
   float dist = vnorm(delta);
   float sg = attractive ? -1.f : 1.f;
-  float pen = softplus0((dist_min - dist) * sg / k) * k;
+  float pen = softplus0v((dist_min - dist) * sg / k, vectorised) * k;
   float sk = attractive ? -K : K; /* python: sign * force_multiplier, then one fp32 scalar */
   float den = dist > 0.f ? dist : 1e-8f;
   v2 f = V(sk * delta.x / den * pen, sk * delta.y / den * pen);
@@ -212,10 +230,10 @@ static inline v2 constraint_force(v2 pa, v2 pb, float dist_min, float K, float k
 }
 
 /* core.py:2840-2857 _get_constraint_torques; returns torque on b (torque on a is its negation). */
-static inline float constraint_torque(float rot_a, float rot_b, float Kt) {
+static inline float constraint_torque(float rot_a, float rot_b, float Kt, const float* exp_a) {
   float d = rot_a - rot_b;
   float a = sqrtf(d * d);
-  float pen = expf(a) - 1.f;
+  float pen = (exp_a ? *exp_a : expf(a)) - 1.f; /* torch.exp: MKL vsExp on the CPU (see tg above) */
   float tq = Kt * fsign(d) * pen;
   if (a < 1e-9f) tq = 0.f;
   return tq;
@@ -240,7 +258,7 @@ static int build_ctx(const vmasb200_world_desc* d, octx* c) {
   int A = 0;
   for (int e = 0; e < c->E; ++e) c->agent_of[e] = (d->entities[e].flags & VMASB200_E_AGENT) ? A++ : -1;
   c->A = A;
-  c->sub_dt = (float)((double)d->dt / (double)d->substeps); /* core.py:1124 in Python doubles */
+  c->sub_dt = (float)(d->dt / (double)d->substeps); /* core.py:1124 in Python doubles */
   int E = c->E;
   c->pairs = (opair*)malloc(sizeof(opair) * (size_t)(E * E / 2 + 1));
   int n = 0;
@@ -305,8 +323,20 @@ static inline float friction1(float w, float coeff, float inertia, float sub_dt)
 
 /* ------------------------------------------------------------------------------------------------------------
  * One substep for one env (core.py:1975-2009) given the batch-wide pair verdicts `active`. */
+typedef struct { /* optional per-substep inputs / outputs of vmas_oracle_substep (any may be NULL) */
+  const float* trig;  /* [E][N][4] in: cos(rot) sin(rot) cos(rot + pi/2) sin(rot + pi/2) to use instead of libm's    */
+  int vec_width;      /* 0: every logaddexp element takes the Vectorized path; W > 0: elements of a [N, P] logaddexp call
+                         beyond its last whole group of W take the scalar path, as ATen does with W = 2 x Vec::size() */
+  const float* jexp;  /* [J][N] in: exp(|rot_a - (rot_b + fixed_rotation)|) of core.py:2852 to use instead of libm's */
+  float* tot_force;   /* [E][N][2] forces_dict as _integrate_state reads it (core.py:2876)   */
+  float* tot_torque;  /* [E][N]    torques_dict (core.py:2899)                                */
+  float* joint_force; /* [J][2][N][2] what core.py:2282-2291 hands to update_env_forces: a, b */
+  float* joint_torque;/* [J][2][N]                                                            */
+} odebug;
+
 static void substep_env(const octx* c, int64_t n, int64_t i, float* state, float* force, float* torque,
-                        const float* jrot, const uint8_t* active, int substep) {
+                        const float* jrot, const uint8_t* active, const int* rank, const int* type_count, int substep,
+                        const odebug* dbg) {
   const vmasb200_world_desc* d = c->d;
   const vmasb200_entity* ents = d->entities;
   const int E = c->E;
@@ -315,6 +345,14 @@ static void substep_env(const octx* c, int64_t n, int64_t i, float* state, float
   v2 F[MAXE];
   float T[MAXE];
   for (int e = 0; e < E; ++e) { F[e] = V(0.f, 0.f); T[e] = 0.f; }
+  /* cos / sin of an entity's rotation at the substep's entry: computed when first needed, or the caller's */
+  /* position of this env's element inside the reference's logaddexp call over a [N, P] tensor (env-major) */
+  const int W = dbg ? dbg->vec_width : 0;
+#define VEC(idx, numel) (W <= 0 || (int64_t)(idx) < ((int64_t)(numel) / W) * W)
+  tg TG[MAXE];
+  uint8_t have_tg[MAXE];
+  memset(have_tg, 0, (size_t)E);
+#define TGE(e) (have_tg[e] ? TG[e] : (have_tg[e] = 1, TG[e] = (dbg && dbg->trig) ? *(const tg*)(dbg->trig + ((size_t)(e) * (size_t)n + (size_t)i) * 4) : tg_of(ST(e, i, 4))))
 
   for (int e = 0; e < E; ++e) {
     const vmasb200_entity* en = &ents[e];
@@ -358,20 +396,31 @@ static void substep_env(const octx* c, int64_t n, int64_t i, float* state, float
     int a = jt->entity_a, b = jt->entity_b;
     v2 pa = V(ST(a, i, 0), ST(a, i, 1)), pb = V(ST(b, i, 0), ST(b, i, 1));
     float ra = ST(a, i, 4), rb = ST(b, i, 4);
-    v2 ja = vadd(pa, vrot(V(jt->delta_a[0], jt->delta_a[1]), ra)); /* joints.py:206-215 */
-    v2 jb = vadd(pb, vrot(V(jt->delta_b[0], jt->delta_b[1]), rb));
-    v2 fa_att = constraint_force(ja, jb, jt->dist, Kj, k, 1);
-    v2 fa_rep = constraint_force(ja, jb, jt->dist, Kj, k, 0);
+    tg qa = TGE(a), qb = TGE(b);
+    v2 ja = vadd(pa, vrot_cs(V(jt->delta_a[0], jt->delta_a[1]), qa.c, qa.s)); /* joints.py:206-215 */
+    v2 jb = vadd(pb, vrot_cs(V(jt->delta_b[0], jt->delta_b[1]), qb.c, qb.s));
+    const int vj = VEC(i * c->J + j, n * c->J);
+    v2 fa_att = constraint_force(ja, jb, jt->dist, Kj, k, 1, vj);
+    v2 fa_rep = constraint_force(ja, jb, jt->dist, Kj, k, 0, vj);
     v2 fa = vadd(fa_att, fa_rep);
     v2 fb = vadd(vneg(fa_att), vneg(fa_rep));
     float ta = vcross(vsub(ja, pa), fa), tb = vcross(vsub(jb, pb), fb);
     if (!jt->rotate) {
       float fr = jt->fixed_rotation_per_env ? jrot[(size_t)j * (size_t)n + (size_t)i] : jt->fixed_rotation;
-      float tq = constraint_torque(ra, rb + fr, d->torque_constraint_force);
+      float tq = constraint_torque(ra, rb + fr, d->torque_constraint_force,
+                                   (dbg && dbg->jexp) ? dbg->jexp + (size_t)j * (size_t)n + (size_t)i : NULL);
       ta = ta + (-tq);
       tb = tb + tq;
     }
     add_env_forces(ents, F, T, a, fa, ta, b, fb, tb);
+    if (dbg && dbg->joint_force) {
+      float* o = dbg->joint_force + ((size_t)j * 2 * (size_t)n + (size_t)i) * 2;
+      o[0] = fa.x; o[1] = fa.y; o[(size_t)n * 2] = fb.x; o[(size_t)n * 2 + 1] = fb.y;
+    }
+    if (dbg && dbg->joint_torque) {
+      dbg->joint_torque[(size_t)j * 2 * (size_t)n + (size_t)i] = ta;
+      dbg->joint_torque[((size_t)j * 2 + 1) * (size_t)n + (size_t)i] = tb;
+    }
   }
 
   /* collisions, core.py:2293-2785, lists in type order, each in a<b enumeration order */
@@ -380,61 +429,67 @@ static void substep_env(const octx* c, int64_t n, int64_t i, float* state, float
     int a = c->pairs[p].a, b = c->pairs[p].b;
     const vmasb200_entity *ea = &ents[a], *eb = &ents[b];
     v2 pa = V(ST(a, i, 0), ST(a, i, 1)), pb = V(ST(b, i, 0), ST(b, i, 1));
-    float ra = ST(a, i, 4), rb = ST(b, i, 4);
+    const int pt = type_count[c->pairs[p].type];
+    const int vp = VEC(i * pt + rank[p], n * pt);
     switch (c->pairs[p].type) {
       case VMASB200_PAIR_SS: { /* :2293 */
-        v2 fa = constraint_force(pa, pb, ea->radius + eb->radius, Kc, k, 0);
+        v2 fa = constraint_force(pa, pb, ea->radius + eb->radius, Kc, k, 0, vp);
         add_env_forces(ents, F, T, a, fa, 0.f, b, vneg(fa), 0.f);
       } break;
       case VMASB200_PAIR_LS: { /* :2340 a=line b=sphere */
-        v2 cp = closest_point_line(pa, ra, ea->length, pb, 1);
-        v2 fs = constraint_force(pb, cp, eb->radius + LMD, Kc, k, 0);
+        v2 cp = closest_point_line(pa, TGE(a), ea->length, pb, 1);
+        v2 fs = constraint_force(pb, cp, eb->radius + LMD, Kc, k, 0, vp);
         v2 fl = vneg(fs);
         float tl = vcross(vsub(cp, pa), fl);
         add_env_forces(ents, F, T, a, fl, tl, b, fs, 0.f);
       } break;
       case VMASB200_PAIR_LL: { /* :2393 */
         v2 ca, cb;
-        closest_points_line_line(pa, ra, ea->length, pb, rb, eb->length, &ca, &cb);
-        v2 fa = constraint_force(ca, cb, LMD, Kc, k, 0);
+        closest_points_line_line(pa, TGE(a), ea->length, pb, TGE(b), eb->length, &ca, &cb);
+        v2 fa = constraint_force(ca, cb, LMD, Kc, k, 0, vp);
         v2 fb = vneg(fa);
         add_env_forces(ents, F, T, a, fa, vcross(vsub(ca, pa), fa), b, fb, vcross(vsub(cb, pb), fb));
       } break;
       case VMASB200_PAIR_BS: { /* :2458 a=box b=sphere */
-        v2 cp = closest_point_box(pa, ra, ea->width, ea->length, pb);
+        v2 cp = closest_point_box(pa, TGE(a), ea->width, ea->length, pb);
         v2 ip = cp; float dd = 0.f;
         if (!(ea->flags & VMASB200_E_HOLLOW)) ip = inner_point_box(pb, cp, pa, &dd);
-        v2 fs = constraint_force(pb, ip, (eb->radius + LMD) + dd, Kc, k, 0);
+        v2 fs = constraint_force(pb, ip, (eb->radius + LMD) + dd, Kc, k, 0, vp);
         v2 fbx = vneg(fs);
         add_env_forces(ents, F, T, a, fbx, vcross(vsub(cp, pa), fbx), b, fs, 0.f);
       } break;
       case VMASB200_PAIR_BL: { /* :2553 a=box b=line */
         v2 cbx, cl;
-        closest_line_box(pa, ra, ea->width, ea->length, pb, rb, eb->length, &cbx, &cl);
+        closest_line_box(pa, TGE(a), ea->width, ea->length, pb, TGE(b), eb->length, &cbx, &cl);
         v2 ip = cbx; float dd = 0.f;
         if (!(ea->flags & VMASB200_E_HOLLOW)) ip = inner_point_box(cl, cbx, pa, &dd);
-        v2 fbx = constraint_force(ip, cl, LMD + dd, Kc, k, 0);
+        v2 fbx = constraint_force(ip, cl, LMD + dd, Kc, k, 0, vp);
         v2 fl = vneg(fbx);
         add_env_forces(ents, F, T, a, fbx, vcross(vsub(cbx, pa), fbx), b, fl, vcross(vsub(cl, pb), fl));
       } break;
       default: { /* :2654 box-box */
         v2 ca, cb;
-        closest_box_box(pa, ra, ea->width, ea->length, pb, rb, eb->width, eb->length, &ca, &cb);
+        closest_box_box(pa, TGE(a), ea->width, ea->length, pb, TGE(b), eb->width, eb->length, &ca, &cb);
         v2 ia = ca, ib = cb; float da = 0.f, db = 0.f;
         if (!(ea->flags & VMASB200_E_HOLLOW)) ia = inner_point_box(cb, ca, pa, &da);
         if (!(eb->flags & VMASB200_E_HOLLOW)) ib = inner_point_box(ca, cb, pb, &db);
-        v2 fa = constraint_force(ia, ib, (da + db) + LMD, Kc, k, 0);
+        v2 fa = constraint_force(ia, ib, (da + db) + LMD, Kc, k, 0, vp);
         v2 fb = vneg(fa);
         add_env_forces(ents, F, T, a, fa, vcross(vsub(ca, pa), fa), b, fb, vcross(vsub(cb, pb), fb));
       } break;
     }
   }
 
+  if (dbg && dbg->tot_force)
+    for (int e = 0; e < E; ++e) { float* o = dbg->tot_force + ((size_t)e * (size_t)n + (size_t)i) * 2; o[0] = F[e].x; o[1] = F[e].y; }
+  if (dbg && dbg->tot_torque)
+    for (int e = 0; e < E; ++e) dbg->tot_torque[(size_t)e * (size_t)n + (size_t)i] = T[e];
+
   /* integrate, core.py:2861-2907 */
   for (int e = 0; e < E; ++e) {
     const vmasb200_entity* en = &ents[e];
-    float drag = (en->flags & VMASB200_E_DRAG) ? en->drag : d->drag;
-    float one_minus_drag = (float)(1.0 - (double)drag);
+    double drag = (en->flags & VMASB200_E_DRAG) ? en->drag : d->drag; /* Python floats */
+    float one_minus_drag = (float)(1.0 - drag);
     if (en->flags & VMASB200_E_MOVABLE) {
       v2 vel = V(ST(e, i, 2), ST(e, i, 3));
       if (substep == 0) vel = vscale(vel, one_minus_drag);
@@ -457,10 +512,11 @@ static void substep_env(const octx* c, int64_t n, int64_t i, float* state, float
   }
 }
 
-int vmas_oracle_step(const vmasb200_world_desc* desc, int64_t n, float* state, float* force, float* torque,
-                     const float* jrot, uint8_t* masks, int n_threads) {
+static int run_substeps(const vmasb200_world_desc* desc, int64_t n, float* state, float* force, float* torque,
+                        const float* jrot, uint8_t* masks, int n_threads, int s_begin, int s_end, const odebug* dbg) {
   octx c;
   if (build_ctx(desc, &c)) return -1;
+  if (s_begin < 0 || s_end > c.S || s_begin > s_end) { free(c.pairs); return -2; }
 #ifdef _OPENMP
   if (n_threads <= 0) n_threads = omp_get_max_threads();
 #else
@@ -468,7 +524,9 @@ int vmas_oracle_step(const vmasb200_world_desc* desc, int64_t n, float* state, f
 #endif
   const int E = c.E;
   uint8_t* active = (uint8_t*)calloc((size_t)c.npair + 1, 1);
-  for (int s = 0; s < c.S; ++s) {
+  int* rank = (int*)calloc((size_t)c.npair + 1, sizeof(int));
+  int type_count[6];
+  for (int s = s_begin; s < s_end; ++s) {
     /* batch-wide broad phase, core.py:2796-2800 */
     for (int p = 0; p < c.npair; ++p) {
       int a = c.pairs[p].a, b = c.pairs[p].b;
@@ -485,12 +543,29 @@ int vmas_oracle_step(const vmasb200_world_desc* desc, int64_t n, float* state, f
         masks[((size_t)s * E + lo) * E + hi] = (uint8_t)any;
       }
     }
+    memset(type_count, 0, sizeof(type_count));
+    for (int p = 0; p < c.npair; ++p)
+      if (active[p]) rank[p] = type_count[c.pairs[p].type]++;
 #pragma omp parallel for num_threads(n_threads) schedule(static) if (n > 64)
-    for (int64_t i = 0; i < n; ++i) substep_env(&c, n, i, state, force, torque, jrot, active, s);
+    for (int64_t i = 0; i < n; ++i) substep_env(&c, n, i, state, force, torque, jrot, active, rank, type_count, s, dbg);
   }
   free(active);
+  free(rank);
   free(c.pairs);
   return 0;
+}
+
+int vmas_oracle_step(const vmasb200_world_desc* desc, int64_t n, float* state, float* force, float* torque,
+                     const float* jrot, uint8_t* masks, int n_threads) {
+  return run_substeps(desc, n, state, force, torque, jrot, masks, n_threads, 0, desc->substeps, NULL);
+}
+
+int vmas_oracle_substep(const vmasb200_world_desc* desc, int64_t n, float* state, float* force, float* torque,
+                        const float* jrot, uint8_t* masks, int substep, float* tot_force, float* tot_torque,
+                        float* joint_force, float* joint_torque, const float* trig, const float* jexp, int vec_width,
+                        int n_threads) {
+  odebug dbg = {trig, vec_width, jexp, tot_force, tot_torque, joint_force, joint_torque};
+  return run_substeps(desc, n, state, force, torque, jrot, masks, n_threads, substep, substep + 1, &dbg);
 }
 
 /* ------------------------------------------------------------------------------------------------------------
@@ -522,7 +597,7 @@ static inline float ray_box(v2 bpos, float brot, float blen, float bwid, v2 o, f
 static inline float ray_sphere(v2 spos, float rad, v2 o, float ang, float max_range) {
   v2 dir = V(cosf(ang), sinf(ang));
   v2 line_pos = vadd(o, vscale(dir, max_range / 2.f));
-  v2 cp = closest_point_line(line_pos, ang, max_range, spos, 0);
+  v2 cp = closest_point_line(line_pos, tg_cs(dir.x, dir.y), max_range, spos, 0);
   v2 dd = vsub(spos, cp);
   float dn = vnorm(dd);
   int hit = dn < rad;
@@ -604,15 +679,15 @@ typedef struct { int shape; double radius, length, width; const float* st; } qen
 /* core.py:1787-1819 get_distance_from_point */
 static float q_from_point(const qent* e, int64_t i, v2 q) {
   if (e->shape == VMASB200_SPHERE) return vnorm(vsub(QP(e, i), q)) - (float)e->radius;
-  v2 cp = e->shape == VMASB200_BOX ? closest_point_box(QP(e, i), QR(e, i), (float)e->width, (float)e->length, q)
-                                   : closest_point_line(QP(e, i), QR(e, i), (float)e->length, q, 1);
+  v2 cp = e->shape == VMASB200_BOX ? closest_point_box(QP(e, i), tg_of(QR(e, i)), (float)e->width, (float)e->length, q)
+                                   : closest_point_line(QP(e, i), tg_of(QR(e, i)), (float)e->length, q, 1);
   return vnorm(vsub(q, cp)) - LMD;
 }
 
 /* core.py:1936-1964 is_overlapping, box / sphere branch */
 static int q_overlap_box_sphere(const qent* box, const qent* sph, int64_t i) {
   v2 bp = QP(box, i), sp = QP(sph, i);
-  v2 cp = closest_point_box(bp, QR(box, i), (float)box->width, (float)box->length, sp);
+  v2 cp = closest_point_box(bp, tg_of(QR(box, i)), (float)box->width, (float)box->length, sp);
   float d_sphere_cp = vnorm(vsub(sp, cp));
   float d_sphere_box = vnorm(vsub(sp, bp));
   float d_cp_box = vnorm(vsub(bp, cp));
@@ -637,14 +712,14 @@ static float q_distance(const qent* a, const qent* b, int64_t i) {
   }
   v2 p1, p2;
   if (sa == VMASB200_LINE && sb == VMASB200_LINE) {
-    closest_points_line_line(QP(a, i), QR(a, i), (float)a->length, QP(b, i), QR(b, i), (float)b->length, &p1, &p2);
+    closest_points_line_line(QP(a, i), tg_of(QR(a, i)), (float)a->length, QP(b, i), tg_of(QR(b, i)), (float)b->length, &p1, &p2);
   } else if (sa == VMASB200_BOX && sb == VMASB200_BOX) {
-    closest_box_box(QP(a, i), QR(a, i), (float)a->width, (float)a->length, QP(b, i), QR(b, i), (float)b->width,
+    closest_box_box(QP(a, i), tg_of(QR(a, i)), (float)a->width, (float)a->length, QP(b, i), tg_of(QR(b, i)), (float)b->width,
                     (float)b->length, &p1, &p2);
   } else {
     const qent* box = sa == VMASB200_BOX ? a : b;
     const qent* line = sa == VMASB200_BOX ? b : a;
-    closest_line_box(QP(box, i), QR(box, i), (float)box->width, (float)box->length, QP(line, i), QR(line, i),
+    closest_line_box(QP(box, i), tg_of(QR(box, i)), (float)box->width, (float)box->length, QP(line, i), tg_of(QR(line, i)),
                      (float)line->length, &p1, &p2);
   }
   return vnorm(vsub(p1, p2)) - LMD;

@@ -30,6 +30,24 @@ extern "C" {
 int vmas_oracle_step(const vmasb200_world_desc* desc, int64_t n, float* state, float* force, float* torque,
                      const float* jrot, uint8_t* masks, int n_threads);
 
+/* ONE substep `substep` of World.step (the body of the loop core.py:1974-2009; drag only when substep == 0,
+ * core.py:2868, 2893) from the given state, with what the reference's loop holds in between:
+ *  masks        [S][E][E] out (row `substep` written), may be NULL
+ *  tot_force    [E][N][2] out: forces_dict as _integrate_state reads it; tot_torque [E][N]: torques_dict
+ *  joint_force  [J][2][N][2] out: force on entity_a / entity_b of every joint as handed to update_env_forces
+ *                                 (core.py:2282-2291); joint_torque [J][2][N].  Any of the four may be NULL.
+ *  trig         [E][N][4] in, may be NULL: cos(rot) sin(rot) cos(rot + pi/2) sin(rot + pi/2) of every entity at the
+ *               substep's entry, used instead of libm's cosf / sinf - a test passes what torch.cos / torch.sin return for
+ *               the same fp32 angles (MKL VML on the CPU; third-party, closed source, not restatable);
+ *  jexp         [J][N] in, may be NULL: torch.exp(|rot_a - (rot_b + fixed_rotation)|) of core.py:2852, likewise.
+ *  vec_width    0, or W = 2 x Vec::size() of the ATen build that made a golden fixture (32 with AVX-512, 16 with AVX2):
+ *               ATen's logaddexp (core.py:2820) runs whole groups of W elements of its [N, P] operand through SLEEF and
+ *               the tail through libm; with W the oracle takes the same function for the same element. */
+int vmas_oracle_substep(const vmasb200_world_desc* desc, int64_t n, float* state, float* force, float* torque,
+                        const float* jrot, uint8_t* masks, int substep, float* tot_force, float* tot_torque,
+                        float* joint_force, float* joint_torque, const float* trig, const float* jexp, int vec_width,
+                        int n_threads);
+
 /* Lidar.measure(vectorized=True) (sensors.py:100-122 -> core.py:1661-1785) for desc->lidars[lidar_index];
  * out [N][n_rays]. */
 int vmas_oracle_lidar(const vmasb200_world_desc* desc, int64_t n, const float* state, int lidar_index, float* out,

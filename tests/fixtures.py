@@ -95,23 +95,42 @@ def max_err(a, b):
     return float(np.nanmax(np.abs(a.astype(np.float64) - b.astype(np.float64)))) if a.size else 0.0
 
 
-def ulp_perturb(x, seed=0):
-    """Every element moved by one fp32 ulp in a random direction."""
+# 2 x Vectorized<float>::size() of the ATen build that generated tests/golden/*.npz (AVX-512 container: 2 x 16): ATen's
+# logaddexp runs whole groups of that many elements through SLEEF and the tail through libm (oracle/vmas_oracle.h)
+ATEN_VEC_WIDTH = 32
+
+
+def reference_math_available():
+    """The oracle's bit-exact mode evaluates torch.cos / torch.sin / torch.exp (MKL VML) on the test machine.  True when
+    this machine's torch returns the values the fixture machine's did (checked on the stored angles of a stiff fixture)."""
+    import torch
+
+    z = np.load(os.path.join(GOLDEN, "substeps", "asym_joint.npz"))
+    rot = torch.from_numpy(np.ascontiguousarray(z["states"][:, :-1, :, :, 4]))
+    return bool(np.array_equal(rot.cos().numpy(), z["trig"][..., 0]) and np.array_equal(rot.sin().numpy(), z["trig"][..., 1]))
+
+
+def trig_sensitivity(orc, state_in, force, torque, jrot, trials=6, seed=0):
+    """Per ELEMENT of the output state: how far one World.step moves when every cos / sin value (and the exp of a
+    rotation-holding joint's torque, core.py:2852) of every substep is off by -1 / 0 / +1 ulp at random (what libm or CUDA do to the reference's MKL values): max over `trials` draws of
+    |jittered - exact|.  Zero for entities no stiff joint reaches; ~1e-3 in ang_vel of a line held by joint_force 900."""
+    base = np.ascontiguousarray(state_in.copy())
+    orc.step_torch_math(base, np.ascontiguousarray(force.copy()), np.ascontiguousarray(torque.copy()), jrot, vec_width=ATEN_VEC_WIDTH)
     rng = np.random.default_rng(seed)
-    d = np.where(rng.random(x.shape) < 0.5, -np.inf, np.inf).astype(np.float32)
-    return np.nextafter(x.astype(np.float32), d).astype(np.float32)
+    sens = np.zeros(base.shape, np.float64)
+    for _ in range(trials):
+        st = np.ascontiguousarray(state_in.copy())
+        orc.step_torch_math(st, np.ascontiguousarray(force.copy()), np.ascontiguousarray(torque.copy()), jrot,
+                            vec_width=ATEN_VEC_WIDTH, trig_jitter=rng)
+        sens = np.maximum(sens, np.abs(st.astype(np.float64) - base.astype(np.float64)))
+    return sens
 
 
 def conditioned_close(got, exp, sens, factor=8.0):
-    """|got-exp| <= atol + rtol|exp|, relaxed per state field by `factor` x the change that a 1-ulp perturbation of
-    the INPUT produces in the output (`sens`, per field).  Stiff jointed worlds (joint_force 900, 10 substeps,
-    moments of inertia ~5e-4) amplify one input ulp to ~3e-3 in ang_vel within a single step, so no implementation
-    - including the reference on another device - can meet 1e-5 there; well-conditioned worlds have sens ~ 0 and
-    keep the plain fp32 bar."""
+    """|got - exp| <= atol + rtol |exp| + factor * sens, ELEMENT by element (`sens` has the state's shape, from
+    trig_sensitivity): only the elements a stiff joint really drives get slack, everything else keeps the plain fp32 bar."""
     err = np.abs(got.astype(np.float64) - exp.astype(np.float64))
-    tol = ATOL + RTOL * np.abs(exp.astype(np.float64))
-    extra = factor * np.asarray(sens, dtype=np.float64)
-    tol = tol + extra.reshape((1,) * (got.ndim - 1) + (-1,))
+    tol = ATOL + RTOL * np.abs(exp.astype(np.float64)) + factor * np.asarray(sens, np.float64)
     return bool((err <= tol).all())
 
 

@@ -1,18 +1,21 @@
 """GPU: the CUDA step (through the C ABI, host-buffer entry point vmasb200_step_host) against the CPU oracle and
 the golden outputs of the reference itself, on the same seeded inputs.
 
-Bar (BASELINE.json north_star): fp32 rtol 1e-5 / atol 1e-6 after one step (relaxed only by the measured
-conditioning of stiff jointed worlds, see tests/fixtures.conditioned_close), collision masks bit-exact,
-stated drift bound over the recorded rollout (tests/fixtures.drift_bounds)."""
+Bar (BASELINE.json north_star): fp32 rtol 1e-5 / atol 1e-6 after one step, collision masks bit-exact, stated drift
+bound over the recorded rollout (tests/fixtures.drift_bounds).  The three stiff jointed worlds (joint_passage,
+asym_joint, waterfall) meet the plain bar per SUBSTEP (tests/test_gpu_substeps.py); over a whole step of 5-10 substeps
+the 1-ulp difference between CUDA's sincosf and the reference's MKL cos / sin is amplified, so there - and only for
+the state elements a stiff joint drives - the bar is widened element by element by tests/fixtures.trig_sensitivity."""
 import numpy as np
 import pytest
 
 from oracle.oracle import Oracle
-from tests.fixtures import Fixture, close, conditioned_close, drift_bounds, max_err, names, ulp_perturb
+from tests.fixtures import Fixture, close, conditioned_close, drift_bounds, max_err, names, trig_sensitivity
 from vectorizedmultiagentsimulator_b200.plan import StepPlan
 
 pytestmark = pytest.mark.gpu
 ALL = names()
+STIFF = {"joint_passage", "asym_joint", "waterfall"}
 
 
 def _forces(fx, t):
@@ -42,14 +45,16 @@ def test_one_step(name, exact):
         f, tq = _forces(fx, t)
         dyn_out, act, lid, pa = pl.step_host(dyn, stat, f, tq, exact=exact)
         got = pl.unpack(dyn_out, state_in.copy())
-        # oracle on the same inputs + its conditioning
+        # oracle (libm math) on the same inputs
         st = np.ascontiguousarray(state_in.copy())
         om = orc.step(st, fx.forces[t].copy(), fx.torques[t].copy(), jr)
-        sp = np.ascontiguousarray(ulp_perturb(state_in))
-        orc.step(sp, fx.forces[t].copy(), fx.torques[t].copy(), jr, want_masks=False)
-        sens = [max_err(sp[..., i], st[..., i]) for i in range(6)]
-        assert conditioned_close(got, st, sens), f"{name} t={t} vs oracle: {max_err(got, st):.3e} sens {sens}"
-        assert conditioned_close(got, fx.state_after[k], sens), f"{name} t={t} vs golden: {max_err(got, fx.state_after[k]):.3e}"
+        if name in STIFF:
+            sens = trig_sensitivity(orc, state_in, fx.forces[t], fx.torques[t], jr)
+            assert conditioned_close(got, st, sens), f"{name} t={t} vs oracle: {max_err(got, st):.3e}"
+            assert conditioned_close(got, fx.state_after[k], sens), f"{name} t={t} vs golden: {max_err(got, fx.state_after[k]):.3e}"
+        else:
+            assert close(got, st), f"{name} t={t} vs oracle: {max_err(got, st):.3e}"
+            assert close(got, fx.state_after[k]), f"{name} t={t} vs golden: {max_err(got, fx.state_after[k]):.3e}"
         masks = pl.masks_matrix(pa) if pa is not None else np.zeros_like(om)
         assert (masks == om).all() and (masks == fx.masks[t]).all(), f"{name} t={t}: collision masks differ"
         if act is not None:
@@ -59,13 +64,24 @@ def test_one_step(name, exact):
             assert close(got_l, fx.lidar[li][k]), f"{name} lidar {li}: {max_err(got_l, fx.lidar[li][k]):.3e}"
 
 
+# Stated counts for the recorded rollouts (measured on B200: no env of any world leaves the drift bound; joint_passage
+# differs from the reference in the collision mask of 1 of its 100 steps - a stiff joint amplifies the 1-ulp cos / sin
+# difference until a wall contact is made a substep earlier or later).
+MAX_DIVERGED = {}                                   # envs beyond the drift bound: 0 everywhere
+MAX_MASK_STEPS = {"joint_passage": 3, "asym_joint": 3, "waterfall": 3}
+
+
 @pytest.mark.parametrize("name", ALL)
 def test_rollout_drift(name):
+    """Free-running replay of the recorded forces.  At every snapshot every env must be within the stated drift bound
+    of the reference; worlds without stiff joints must also keep the reference's collision masks at every substep of
+    every step; the stiff worlds get a STATED number of steps whose mask may differ (envs are still all checked)."""
     fx = Fixture(name)
     pl = StepPlan(fx.desc)
     st = fx.state0.copy()
     pos_tol, vel_tol = drift_bounds(fx.desc)
-    diverged = False
+    lost = np.zeros(fx.n_envs, bool)
+    mask_steps = 0
     for t in range(fx.steps):
         fx.apply_overrides(t, st)
         dyn, stat = pl.pack(st, fx.jrot_at(t))
@@ -73,13 +89,17 @@ def test_rollout_drift(name):
         dyn_out, act, lid, pa = pl.step_host(dyn, stat, f, tq, exact=True, want_lidar=False)
         st = pl.unpack(dyn_out, st)
         if pa is not None:
-            diverged = diverged or bool((pl.masks_matrix(pa) != fx.masks[t]).any())
-        if (t + 1) in fx.snaps and not diverged:
+            mask_steps += int((pl.masks_matrix(pa) != fx.masks[t]).any())
+        if (t + 1) in fx.snaps:
             exp = fx.state_after[fx.snap_index(t + 1)]
-            assert max_err(st[..., 0:2], exp[..., 0:2]) <= pos_tol, f"{name} pos drift at step {t+1}"
-            assert max_err(st[..., 2:4], exp[..., 2:4]) <= vel_tol, f"{name} vel drift at step {t+1}"
+            e_pos = np.abs(st[..., 0:2].astype(np.float64) - exp[..., 0:2]).max(axis=(0, 2))
+            e_vel = np.abs(st[..., 2:4].astype(np.float64) - exp[..., 2:4]).max(axis=(0, 2))
+            lost |= (e_pos > pos_tol) | (e_vel > vel_tol)
+            assert int(lost.sum()) <= MAX_DIVERGED.get(name, 0), \
+                f"{name}: {int(lost.sum())} envs beyond the drift bound at step {t + 1} (pos {e_pos.max():.2e}, vel {e_vel.max():.2e})"
     assert np.isfinite(st).all()
-    assert not diverged or fx.desc.joints, f"{name}: collision masks diverged from the reference's"
+    assert mask_steps <= MAX_MASK_STEPS.get(name, 0), f"{name}: collision masks differ from the reference's in {mask_steps} steps"
+    print(f"{name}: envs beyond the drift bound {int(lost.sum())}/{fx.n_envs}, steps with a differing collision mask {mask_steps}/{fx.steps}")
 
 
 @pytest.mark.parametrize("name", ALL)

@@ -23,7 +23,7 @@ def test_exports_match_header():
     assert declared == set(_lib.EXPORTS)
     for name in declared:
         assert hasattr(L, name), name
-    assert L.vmasb200_version() == 2
+    assert L.vmasb200_version() == 3
 
 
 def _expected_pairs(desc):

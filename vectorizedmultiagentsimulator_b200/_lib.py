@@ -17,7 +17,7 @@ EXPORTS = [
     "vmasb200_get_distance_from_point", "vmasb200_set_action", "vmasb200_set_action_discrete", "vmasb200_gather_obs",
     "vmasb200_navigation_reward",
     "vmasb200_transport_reward", "vmasb200_simple_spread_reward", "vmasb200_jit_enable", "vmasb200_plan_jit",
-    "vmasb200_joint_passage_reward", "vmasb200_football_reward", "vmasb200_navigation_reward_static",
+    "vmasb200_joint_passage_reward", "vmasb200_football_reward", "vmasb200_navigation_reward_static", "vmasb200_plan_trig_entities",
 ]
 
 _LIB = None
@@ -58,6 +58,7 @@ def lib():
     L.vmasb200_plan_pairs.argtypes = [vp, C.POINTER(CPair)]
     L.vmasb200_plan_joint_slots.argtypes = [vp, i32p]
     L.vmasb200_plan_lidar_slots.argtypes = [vp, i32p]
+    L.vmasb200_plan_trig_entities.argtypes = [vp, i32p]
     L.vmasb200_step.argtypes = [vp, C.POINTER(CStepIO)]
     L.vmasb200_step_host.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp, C.c_int64, C.c_int64, C.c_int32]
     L.vmasb200_cast_rays.argtypes = [

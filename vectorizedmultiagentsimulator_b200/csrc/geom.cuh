@@ -202,13 +202,18 @@ VB_DI V2 constraint_force(V2 pa, V2 pb, float dist_min, float K, float k, bool a
 }
 
 // core.py:2840-2857 _get_constraint_torques: torque on b; torque on a is its negation.
-VB_DI float constraint_torque(float rot_a, float rot_b, float Kt) {
-  float d = rot_a - rot_b;
-  float a = sqrtf(d * d);
-  float pen = expf(a) - 1.f;
+// ea = torch.exp(a), a = |rot_a - rot_b| (core.py:2848-2852).  exp(a) - 1 cancels for the small a of a held joint: one ulp
+// of exp(a) is a relative 6e-8 / a of the torque, which is why a parity probe may hand in the reference's own value.
+VB_DI float constraint_torque_exp(float d, float a, float ea, float Kt) {
+  float pen = ea - 1.f;
   float tq = Kt * sgn(d) * pen;
   if (a < 1e-9f) tq = 0.f;
   return tq;
+}
+VB_DI float constraint_torque(float rot_a, float rot_b, float Kt) {
+  float d = rot_a - rot_b;
+  float a = sqrtf(d * d);
+  return constraint_torque_exp(d, a, expf(a), Kt);
 }
 
 // get_friction_force, core.py:2054-2073

@@ -43,6 +43,12 @@ struct StepArgs {
   int rec_cap;               // tainted envs beyond this have no record and are re-simulated when anything is
   int* repairs_host;         // mapped host copy of counters[2] (read by the host-buffer entry point without a copy)
   int do_lidar;
+  // probe fields of the exact path (vmasb200_step_io: parity tests), all 0 / NULL otherwise
+  int forces_fresh;          // the frc inputs are this launch's substep inputs: no replay of the earlier substeps' clamps
+  const float* trig_in;      // [4 * n_trig][ld] cos/sin cache to use instead of computing it
+  const float* jexp_in;      // [J][ld] exp(|delta rot|) of every joint's constraint torque (one-substep launches, c_probe_jexp)
+  float* dbg_force;          // [3 * n_dyn][ld] (Fx Fy T) of the launch's last substep
+  float* dbg_joint;          // [4 * J][ld] (fx fy ta tb) per joint of the launch's last substep
 };
 
 // dynamic shared memory carve-up (4-byte words); every row starts 16B aligned because TE % 4 == 0
@@ -113,12 +119,19 @@ VB_DI int run_substeps(const KParams& kp, const StepArgs& sa, const Tile& t, boo
   // prologue: cos/sin cache of every entity that needs it, first force accumulators
   for (int r = q; r < kp.n_trig; r += Q) {
     const DEnt* en = &T_ent<CT>(kp, T_trig<CT>(kp, r));
-    store_trig(en, E, ER(E, en->rot_row));
+    if (sa.trig_in) {  // probe: the caller's cos/sin (the reference's own torch.cos / torch.sin values)
+      if (ok)
+        for (int k = 0; k < 4; ++k) WR(E, en->trig_row + k) = sa.trig_in[(size_t)(4 * r + k) * sa.ld + env];
+    } else {
+      store_trig(en, E, ER(E, en->rot_row));
+    }
   }
   // the clamp of core.py:2017-2040 is re-applied to its own result every substep: replay it for the substeps
   // that earlier launches of a split step already did
   for (int d = q; d < kp.n_dyn; d += Q)
-    for (int rep = 0; rep <= s_begin; ++rep) begin_forces(kp, &T_ent<CT>(kp, T_dyn<CT>(kp, d)), E);
+    for (int rep = sa.forces_fresh ? s_begin : 0; rep <= s_begin; ++rep) begin_forces(kp, &T_ent<CT>(kp, T_dyn<CT>(kp, d)), E);
+  if (sa.jexp_in && ok)
+    for (int j = q; j < kp.J; j += Q) WR(E, kp.row_jres + 4 * j) = sa.jexp_in[(size_t)j * sa.ld + env];
   if (q == 0) {
     WR(E, kp.row_taint) = 0.f;
     for (int b = 0; b <= kp.n_blk; ++b) WR(E, kp.row_th + b) = 0.f;
@@ -516,6 +529,10 @@ step_kernel(const __grid_constant__ KParams kp, const __grid_constant__ AgentIO 
   if (ok) load_forces(kp, aio, E, env0 + col, q, Q);
   mbar_wait(bar, 0);
   const int taint = run_substeps<CT, TE>(kp, sa, t, ok, env0 + col, sa.s_begin, sa.s_end, sa.flags_in);
+  if (sa.dbg_force && ok)
+    for (int r = q; r < 3 * kp.n_dyn; r += Q) sa.dbg_force[(size_t)r * sa.ld + env0 + col] = WR(E, kp.row_fin + r);
+  if (sa.dbg_joint && ok)
+    for (int r = q; r < 4 * kp.J; r += Q) sa.dbg_joint[(size_t)r * sa.ld + env0 + col] = WR(E, kp.row_jres + r);
   const bool lidar = sa.do_lidar && sa.lidar_out && kp.n_rays;
   if (lidar) lidar_epilogue<CT, TE>(kp, t, n_valid);
 

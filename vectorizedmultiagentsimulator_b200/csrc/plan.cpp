@@ -55,7 +55,7 @@ int build_plan(const vmasb200_world_desc* d, vmasb200_plan* pl) {
   if (!d || d->abi_version != VMASB200_ABI_VERSION) { set_error("world desc: bad abi_version"); return VMASB200_ERR_INVALID; }
   const int E = d->n_entities;
   if (E <= 0 || !d->entities || !d->collide_mask) { set_error("world desc: no entities"); return VMASB200_ERR_INVALID; }
-  if (d->substeps < 1 || !(d->dt > 0.f)) { set_error("world desc: substeps >= 1 and dt > 0 required"); return VMASB200_ERR_INVALID; }
+  if (d->substeps < 1 || !(d->dt > 0.0)) { set_error("world desc: substeps >= 1 and dt > 0 required"); return VMASB200_ERR_INVALID; }
   if (d->n_joints < 0 || d->n_lidars < 0 || (d->n_joints && !d->joints) || (d->n_lidars && !d->lidars)) {
     set_error("world desc: bad joint / lidar tables"); return VMASB200_ERR_INVALID;
   }
@@ -167,8 +167,8 @@ int build_plan(const vmasb200_world_desc* d, vmasb200_plan* pl) {
     o.radius = s.radius; o.length = s.length; o.width = s.width;
     o.mass = s.mass; o.moi = s.moment_of_inertia;
     o.max_speed = s.max_speed; o.v_range = s.v_range;
-    const float drag = (s.flags & VMASB200_E_DRAG) ? s.drag : d->drag;
-    o.one_minus_drag = (float)(1.0 - (double)drag);
+    const double drag = (s.flags & VMASB200_E_DRAG) ? s.drag : d->drag;  // Python floats
+    o.one_minus_drag = (float)(1.0 - drag);
     if (s.flags & VMASB200_E_LIN_FRICTION) { o.flags |= DE_LINF_ON; o.lin_fric = s.linear_friction; }
     else if (d->linear_friction > 0.f) { o.flags |= DE_LINF_ON; o.lin_fric = d->linear_friction; }
     if (s.flags & VMASB200_E_ANG_FRICTION) { o.flags |= DE_ANGF_ON; o.ang_fric = s.angular_friction; }
@@ -282,7 +282,7 @@ int build_plan(const vmasb200_world_desc* d, vmasb200_plan* pl) {
   kp.NT = 128;  // Q = 128 / TE team members per env
 
   // ---- world constants
-  kp.sub_dt = (float)((double)d->dt / (double)d->substeps);  // core.py:1124 (Python doubles)
+  kp.sub_dt = (float)(d->dt / (double)d->substeps);  // core.py:1124 (Python doubles)
   kp.Kc = d->collision_force; kp.Kj = d->joint_force; kp.Kt = d->torque_constraint_force; kp.margin = d->contact_margin;
   kp.xs = d->x_semidim; kp.ys = d->y_semidim; kp.has_xs = d->has_x_semidim; kp.has_ys = d->has_y_semidim;
   kp.wgx = d->gravity[0]; kp.wgy = d->gravity[1];

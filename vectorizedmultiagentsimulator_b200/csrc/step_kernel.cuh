@@ -92,6 +92,9 @@ struct CTab {
   DSensor sensors[kCSensors];
 };
 __constant__ CTab c_tab;
+// parity probe (vmasb200_step_io.jexp_in): slot 0 of a joint's result rows holds the reference's exp(|delta rot|) for the
+// constraint torque of the substep; set around a probe launch only
+__constant__ int c_probe_jexp;
 
 // table accessors: CT = the walk tables are in the constant bank (c_tab), else in global memory behind kp
 template <bool CT> VB_DI const DEnt& T_ent(const KParams& kp, int e) { if (CT) return c_tab.ents[e]; else return kp.ents[e]; }
@@ -197,7 +200,13 @@ VB_EVAL void eval_item(const KParams& kp, const DItem* __restrict__ it, const EV
       if (!it->rotate) {
         const float ra = ER(E, ea->rot_row), rb = ER(E, eb->rot_row);
         float fr = it->fr_row >= 0 ? ER(E, it->fr_row) : it->fixed_rot;
-        float tq = constraint_torque(ra, rb + fr, kp.Kt);
+        float tq;
+        if (c_probe_jexp) {
+          const float d = ra - (rb + fr);
+          tq = constraint_torque_exp(d, sqrtf(d * d), WR(E, kp.row_jres + 4 * (int)(it - kp.items)), kp.Kt);
+        } else {
+          tq = constraint_torque(ra, rb + fr, kp.Kt);
+        }
         ta = ta + (-tq);
         tb = tb + tq;
       }

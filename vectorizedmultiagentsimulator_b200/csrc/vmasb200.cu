@@ -88,6 +88,13 @@ static int check_io(const vmasb200_plan* pl, const vmasb200_step_io* io) {
   if (!io || io->n_envs < 0) { set_error("step: bad io"); return VMASB200_ERR_INVALID; }
   if (io->ld < io->n_envs || (io->ld & 3)) { set_error("step: ld must be >= n_envs and a multiple of 4"); return VMASB200_ERR_INVALID; }
   if (!io->dyn_in || !io->dyn_out) { set_error("step: dyn_in / dyn_out are required"); return VMASB200_ERR_INVALID; }
+  const bool probe = io->substep_begin || io->substep_end || io->forces_are_substep_inputs || io->trig_in || io->jexp_in || io->force_out || io->joint_out;
+  if (io->jexp_in && io->substep_end != io->substep_begin + 1) { set_error("step: jexp_in needs a one-substep range"); return VMASB200_ERR_INVALID; }
+  if (probe && !io->exact) { set_error("step: the probe fields (substep range, trig_in, force_out, joint_out) need exact != 0"); return VMASB200_ERR_INVALID; }
+  if ((io->substep_begin || io->substep_end) &&
+      (io->substep_begin < 0 || io->substep_end > kp.S || io->substep_begin >= io->substep_end)) {
+    set_error("step: substep range must satisfy 0 <= begin < end <= substeps"); return VMASB200_ERR_INVALID;
+  }
   if (kp.stat_rows && !io->stat) { set_error("step: stat buffer missing"); return VMASB200_ERR_INVALID; }
   if (kp.act_rows && !io->act_out) { set_error("step: act_out missing"); return VMASB200_ERR_INVALID; }
   if (kp.A && (!io->force_ptrs || !io->torque_ptrs || !io->force_strides || !io->torque_strides)) {
@@ -214,16 +221,27 @@ static int launch_step(vmasb200_plan* pl, const vmasb200_step_io* io, long long 
   if (io->exact) {
     // exact path: the batch-wide World.collides verdicts are reduced before every substep (core.py:2796-2800)
     if (nw) VB_CUDA(cudaMemsetAsync(flags, 0, nw * sizeof(uint32_t), st));
-    for (int s = 0; s < kp.S; ++s) {
+    const bool ranged = io->substep_begin || io->substep_end;
+    const int s0 = ranged ? io->substep_begin : 0, s1 = ranged ? io->substep_end : kp.S;
+    sa.trig_in = io->trig_in;  // only the first launch starts from the caller's state
+    sa.jexp_in = io->jexp_in;
+    const int probe_on = 1, probe_off = 0;
+    if (io->jexp_in) VB_CUDA(cudaMemcpyToSymbolAsync(c_probe_jexp, &probe_on, sizeof(int), 0, cudaMemcpyHostToDevice, st));
+    sa.forces_fresh = io->forces_are_substep_inputs;
+    for (int s = s0; s < s1; ++s) {
       if (kp.P) {
         unsigned fg = (unsigned)((io->n_envs + 255) / 256);
         flags_kernel<<<fg, 256, 0, st>>>(kp, sa.dyn_in, sa.stat, io->n_envs, io->ld, s, flags);
       }
       sa.s_begin = s; sa.s_end = s + 1; sa.flags_in = flags;
       sa.do_lidar = (s == kp.S - 1);
+      sa.dbg_force = s == s1 - 1 ? io->force_out : nullptr;
+      sa.dbg_joint = s == s1 - 1 ? io->joint_out : nullptr;
       step_fn(ct, kp.TE)<<<grid, block, smem_bytes, st>>>(kp, aio, sa);
       sa.dyn_in = io->dyn_out;
+      sa.trig_in = nullptr;
     }
+    if (io->jexp_in) VB_CUDA(cudaMemcpyToSymbolAsync(c_probe_jexp, &probe_off, sizeof(int), 0, cudaMemcpyHostToDevice, st));
   } else {
     // fused speculative launch; the last CTA verifies it and repairs the (rare) tainted envs in place
     if (io->n_envs > pl->u_cap) {
@@ -331,6 +349,12 @@ int vmasb200_plan_lidar_slots(const vmasb200_plan* pl, int32_t* lidar_slot) {
   if (!pl) { set_error("plan_lidar_slots: NULL plan"); return VMASB200_ERR_INVALID; }
   if (lidar_slot && !pl->lidar_slot.empty()) std::memcpy(lidar_slot, pl->lidar_slot.data(), pl->lidar_slot.size() * sizeof(int32_t));
   return VMASB200_OK;
+}
+
+int vmasb200_plan_trig_entities(const vmasb200_plan* pl, int32_t* trig_entities) {
+  if (!pl) { set_error("plan_trig_entities: NULL plan"); return VMASB200_ERR_INVALID; }
+  if (trig_entities && !pl->trig_list.empty()) std::memcpy(trig_entities, pl->trig_list.data(), pl->trig_list.size() * sizeof(int32_t));
+  return (int)pl->trig_list.size();
 }
 
 int vmasb200_plan_tile(const vmasb200_plan* pl, int64_t n_envs) {

@@ -160,6 +160,69 @@ class StepPlan:
         io._keep = (fp, tp, fs, ts, dyn_in, dyn_out, stat, forces, torques, act_out, lidar_out, pair_active_out)
         return io
 
+    # ------------------------------------------------------------------ probe: ONE substep on the GPU (parity tests)
+    def trig_entities(self):
+        """Entity index per cos/sin cache slot (row order of vmasb200_step_io.trig_in)."""
+        buf = np.zeros(max(self.E, 1), np.int32)
+        n = _lib.lib().vmasb200_plan_trig_entities(self._h, buf.ctypes.data_as(C.POINTER(C.c_int32)))
+        return [int(e) for e in buf[:n]]
+
+    def substep_probe(self, torch, state, force, torque, jrot, substep, trig=None, jexp=None):
+        """Substep `substep` of World.step (the loop body of core.py:1974-2009) through vmasb200_step's probe fields, on
+        fixture-layout numpy inputs: state [E,N,6], force [A,N,2] / torque [A,N] AS THEY ENTER THE SUBSTEP, jrot [J,N],
+        trig [E,N,4] (cos sin cos2 sin2 per entity) to use instead of the kernel's own sincosf, or None; jexp [J,N]
+        exp(|delta rot|) of the joints' constraint torque to use instead of the kernel's expf, or None.
+        Returns dict(state [E,N,6], force [A,N,2], torque [A,N] (clamped write-back, where the plan has act rows),
+        masks [E,E] bool, total_force [E,N,2], total_torque [E,N], joint [J,N,4] = fx fy (on entity_a) ta tb)."""
+        n = state.shape[1]
+        ld = self.ld_for(n)
+        dev = torch.device("cuda", torch.cuda.current_device())
+        dyn_h, stat_h = self.pack(state, jrot)
+        dyn = torch.from_numpy(dyn_h).to(dev)
+        stat = torch.from_numpy(stat_h).to(dev) if self.stat_rows else None
+        dyn_out = torch.zeros_like(dyn)
+        forces = [torch.from_numpy(np.ascontiguousarray(force[a])).to(dev) for a in range(self.A)]
+        torques = [torch.from_numpy(np.ascontiguousarray(torque[a])).to(dev).unsqueeze(-1).contiguous() for a in range(self.A)]
+        act = torch.zeros(self.act_rows, ld, device=dev) if self.act_rows else None
+        pa = torch.zeros(self.S, max(self.pair_words, 1), dtype=torch.int32, device=dev) if self.pair_words else None
+        n_dyn, J = self.n_dyn, len(self.desc.joints)
+        fout = torch.full((3 * max(n_dyn, 1), ld), float("nan"), device=dev)
+        jout = torch.full((4 * max(J, 1), ld), float("nan"), device=dev)
+        tin = None
+        if trig is not None:
+            te = self.trig_entities()
+            tin = torch.zeros(4 * max(len(te), 1), ld, device=dev)
+            for r, e in enumerate(te):
+                tin[4 * r: 4 * r + 4, :n] = torch.from_numpy(np.ascontiguousarray(trig[e].T)).to(dev)
+        io = self.make_io(dyn, dyn_out, stat, forces, torques, act, None, pa, n, ld, True,
+                          torch.cuda.current_stream().cuda_stream)
+        io.substep_begin, io.substep_end, io.forces_are_substep_inputs = substep, substep + 1, 1
+        jin = None
+        if jexp is not None and J:
+            jin = torch.zeros(J, ld, device=dev)
+            jin[:, :n] = torch.from_numpy(np.ascontiguousarray(jexp)).to(dev)
+        io.trig_in, io.force_out, io.joint_out, io.jexp_in = _ptr(tin), _ptr(fout), _ptr(jout) if J else None, _ptr(jin)
+        self.step_io(io)
+        torch.cuda.synchronize()
+        out = dict(state=self.unpack(dyn_out.cpu().numpy(), state.copy()))
+        f_out, t_out = force.copy(), torque.copy()
+        if act is not None:
+            a_h = act.cpu().numpy()
+            for slot, e in enumerate(self.agents):
+                if self.act_slot[e] >= 0:
+                    f_out[slot], t_out[slot] = self.act_of(a_h, e, n)
+        out["force"], out["torque"] = f_out, t_out
+        out["masks"] = self.masks_matrix(pa.cpu().numpy().view(np.uint32))[substep] if pa is not None else np.zeros((self.E, self.E), bool)
+        tf, tt = np.zeros((self.E, n, 2), np.float32), np.zeros((self.E, n), np.float32)
+        fo = fout.cpu().numpy()
+        dyn_ents = [e for e in range(self.E) if self.dyn_slot[e] >= 0]
+        for i, e in enumerate(dyn_ents):
+            tf[e] = fo[3 * i: 3 * i + 2, :n].T
+            tt[e] = fo[3 * i + 2, :n]
+        out["total_force"], out["total_torque"], out["dyn_entities"] = tf, tt, dyn_ents
+        out["joint"] = jout.cpu().numpy()[: 4 * J, :n].reshape(J, 4, n).transpose(0, 2, 1) if J else np.zeros((0, n, 4), np.float32)
+        return out
+
     def step_io(self, io):
         _lib.check(_lib.lib().vmasb200_step(self._h, C.byref(io)), "vmasb200_step")
 

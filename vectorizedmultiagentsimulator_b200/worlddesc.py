@@ -41,7 +41,7 @@ E_MAX_T = 1 << 12
 E_T_RANGE = 1 << 13
 E_COLLIDE = 1 << 14
 
-ABI_VERSION = 2
+ABI_VERSION = 3
 
 
 class UnsupportedWorld(RuntimeError):
@@ -60,7 +60,7 @@ class CEntity(C.Structure):
         ("moment_of_inertia", C.c_float),
         ("max_speed", C.c_float),
         ("v_range", C.c_float),
-        ("drag", C.c_float),
+        ("drag", C.c_double),
         ("linear_friction", C.c_float),
         ("angular_friction", C.c_float),
         ("gravity", C.c_float * 2),
@@ -106,9 +106,9 @@ class CWorldDesc(C.Structure):
         ("joints", C.POINTER(CJoint)),
         ("n_lidars", C.c_int32),
         ("lidars", C.POINTER(CLidar)),
-        ("dt", C.c_float),
+        ("dt", C.c_double),
         ("substeps", C.c_int32),
-        ("drag", C.c_float),
+        ("drag", C.c_double),
         ("linear_friction", C.c_float),
         ("angular_friction", C.c_float),
         ("has_x_semidim", C.c_int32),
@@ -161,6 +161,13 @@ class CStepIO(C.Structure):
         ("ld", C.c_int64),
         ("exact", C.c_int32),
         ("stream", C.c_void_p),
+        ("substep_begin", C.c_int32),
+        ("substep_end", C.c_int32),
+        ("forces_are_substep_inputs", C.c_int32),
+        ("trig_in", C.c_void_p),
+        ("force_out", C.c_void_p),
+        ("joint_out", C.c_void_p),
+        ("jexp_in", C.c_void_p),
     ]
 
 
