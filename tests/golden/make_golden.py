@@ -46,6 +46,9 @@ CONFIGS = {
     "navigation": dict(scenario="navigation", kw=dict(n_agents=4), n_envs=32, steps=100),
     "transport": dict(scenario="transport", kw=dict(n_agents=4), n_envs=32, steps=100),
     "transport_s5": dict(scenario="transport", kw=dict(n_agents=4), n_envs=32, steps=100, substeps=5),
+    # dt / substeps and 1 - drag are formed in Python doubles before they meet fp32 tensors (core.py:1124, 2866): values whose
+    # fp32-first evaluation would be 1 ulp off (dt 0.01 / 5 substeps, drag 0.6)
+    "transport_dt": dict(scenario="transport", kw=dict(n_agents=4), n_envs=16, steps=30, substeps=5, dt=0.01, drag=0.6),
     "joint_passage": dict(scenario="joint_passage", kw=dict(), n_envs=16, steps=100),
     "football": dict(scenario="football", kw=dict(ai_red_agents=False), n_envs=32, steps=100),
     # coverage of the remaining pair types / force terms
@@ -103,6 +106,11 @@ def run(name, cfg):
         cfg["scenario"], num_envs=n, device="cpu", seed=0, continuous_actions=True, **cfg["kw"]
     )
     world = env.world
+    if "dt" in cfg:
+        world._dt = cfg["dt"]
+        world._sub_dt = world._dt / world._substeps
+    if "drag" in cfg:
+        world._drag = cfg["drag"]
     if "substeps" in cfg:  # BASELINE config 3: "transport ... substeps>1" (note i)
         world._substeps = cfg["substeps"]
         world._sub_dt = world._dt / world._substeps

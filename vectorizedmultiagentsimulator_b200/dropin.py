@@ -73,6 +73,8 @@ class WorldBinding:
         self.lidar_valid = False
         self.n_steps = 0
         self.n_copies = 0
+        self.record_masks = False  # True: every step also leaves World.collides' verdicts per (substep, pair) in self.masks
+        self.masks = None
 
     # ------------------------------------------------------------------ plan (re)build
     def refresh(self):
@@ -222,7 +224,12 @@ class WorldBinding:
         io.stat = self.stat.data_ptr() if pl.stat_rows else None
         io.act_out = act.data_ptr() if act is not None else None
         io.lidar_out = lid.data_ptr() if lid is not None else None
-        io.pair_active_out = None
+        if self.record_masks and pl.pair_words:
+            if self.masks is None or self.masks.shape != (pl.S, pl.pair_words):
+                self.masks = torch.zeros(pl.S, pl.pair_words, dtype=torch.int32, device=self.device)
+            io.pair_active_out = self.masks.data_ptr()
+        else:
+            io.pair_active_out = None
         io.stream = _lib.raw_stream(torch, self.device)
         pl.step_io(io)
         # bind the results
