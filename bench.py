@@ -39,6 +39,11 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--static-io", type=int, default=0, help="dropin arms: step in place on persistent buffers")
+    ap.add_argument("--fixture-inputs", action="store_true", help="tiled fixture reset states instead of the reference's own make_env reset")
+    ap.add_argument("--no-torch-cuda", action="store_true", help="skip the torch_cuda_baseline block (reference World.step on this GPU)")
+    ap.add_argument("--no-1m", action="store_true", help="skip the roofline_1m block (the same kernel at 1 048 576 envs)")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="weak: --num-envs per GPU; strong: --num-envs in total, split evenly over the GPUs (SURVEY 8d football sweep)")
     return ap.parse_args()
 
 
@@ -93,10 +98,10 @@ def peaks():
 
 def ncu_capture(scenario, n, compiled=False):
     """What the committed `ncu --set full` capture of this workload says about one launch of the step kernel
-    (profiles/r1z_traffic.json, else the earlier r1w / r1 sets; written by tools/profile_collect.py):
+    (profiles/r2_traffic.json, else the earlier r1z / r1w / r1 sets; written by tools/profile_collect.py):
     dram_bytes = dram__bytes_read.sum + dram__bytes_write.sum, warp_inst = smsp__inst_executed.sum.  Only a capture of
     the SAME kernel counts (world-compiled vmasb200_step_world or generic vb::step_kernel); {} when there is none."""
-    for name in ("r1z_traffic.json", "r1w_traffic.json", "r1_traffic.json"):
+    for name in ("r2_traffic.json", "r1z_traffic.json", "r1w_traffic.json", "r1_traffic.json"):
         try:
             with open(os.path.join(ROOT, "profiles", name)) as f:
                 cap = json.load(f).get(f"{scenario}@{n}", {})
@@ -115,6 +120,93 @@ def alg_flops_per_env(plan, desc):
     pairs = sum(per_type[t] for t, _, _ in plan.pairs)
     rays = sum(len(l.angles) * len(l.targets) for l in desc.lidars)
     return plan.S * (pairs + 110 * len(desc.joints) + 35 * plan.layout.n_dyn) + 45 * rays
+
+
+def ref_available():
+    return os.path.isdir(os.path.join(ROOT, "oracle", "_ref", "vmas"))
+
+
+def import_vmas():
+    for p in (os.path.join(ROOT, "oracle", "_ref"), os.path.join(ROOT, "oracle", "gym_stub")):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    import vmas
+
+    return vmas
+
+
+class RefInputs:
+    """The synthetic inputs SURVEY 8(d) specifies, made by the reference itself (oracle/_ref, INPUT GENERATION only, before
+    any timed region): `make_env(scenario, num_envs=N, seed=seed, continuous_actions=True, **kw)`, its reset state, and
+    for n_sets steps the forces / torques its own pre-step path (`get_random_action` under torch.manual_seed(1234) ->
+    `_set_action` -> `env_process_action`, environment.py:386-390, 535-561) hands to World.step.  Same attributes as
+    vectorizedmultiagentsimulator_b200.workload.Workload, which tiles 32 recorded reset states instead and is the
+    fallback where the reference install did not travel."""
+
+    def __init__(self, fixture, n, seed, n_sets, device="cpu"):
+        import torch
+
+        from vectorizedmultiagentsimulator_b200.dropin import _joints_in_order
+        from vectorizedmultiagentsimulator_b200.workload import Workload
+        from vectorizedmultiagentsimulator_b200.worlddesc import WorldDesc
+
+        vmas = import_vmas()
+        fx = Workload(fixture, 1, seed=0)  # fixture meta: reference scenario name, kwargs, substeps
+        self.scenario, self.meta, self.n_envs = fixture, fx.meta, n
+        env = vmas.make_env(fx.meta["scenario"], num_envs=n, device=device, seed=seed, continuous_actions=True, **fx.meta["kwargs"])
+        world = env.world
+        if world._substeps != fx.desc.substeps:  # "transport, substeps>1": imposed on the built world (SURVEY 8, note i)
+            world._substeps, world._sub_dt = fx.desc.substeps, world._dt / fx.desc.substeps
+        self.env = env
+        self.desc = WorldDesc.from_world(world)
+        ents = list(world.entities)
+        self.state0 = torch.stack([torch.cat([e.state.pos, e.state.vel, e.state.rot, e.state.ang_vel], -1) for e in ents]).cpu().numpy()
+        jr = []
+        for j in (_joints_in_order(world, ents) if getattr(world, "_joints", None) else []):
+            fr = j.fixed_rotation
+            jr.append(fr.reshape(-1).expand(n).cpu().numpy() if hasattr(fr, "reshape") else np.full(n, float(fr), np.float32))
+        self.jrot0 = np.stack(jr).astype(np.float32) if jr else np.zeros((0, n), np.float32)
+        agents = list(world.agents)
+        self.A = len(agents)
+        torch.manual_seed(1234)
+        f = np.zeros((n_sets, n, self.A, 2), np.float32)
+        t = np.zeros((n_sets, n, self.A), np.float32)
+        for k in range(n_sets):
+            acts = [env.get_random_action(a) for a in env.agents]
+            for i, a in enumerate(env.agents):
+                env._set_action(acts[i], a)
+            for a in world.agents:
+                env.scenario.env_process_action(a)
+            for i, a in enumerate(agents):
+                if a.state.force is not None:
+                    f[k, :, i] = a.state.force.cpu().numpy()
+                if a.state.torque is not None:
+                    t[k, :, i] = a.state.torque.cpu().numpy()[:, 0]
+        self._f, self._t = f, t
+        self.source = (f"reference make_env('{fx.meta['scenario']}', num_envs={n}, seed={seed}) reset state; forces of "
+                       f"get_random_action under torch.manual_seed(1234), pre-generated ({n_sets} sets)")
+
+    def random_actions(self, n_sets):
+        assert n_sets <= self._f.shape[0]
+        return self._f[:n_sets], self._t[:n_sets]
+
+
+def make_inputs(args, n, seed, n_sets, need_env=False):
+    """SURVEY 8(d) inputs from the reference when its install travelled (oracle/_ref), else the tiled fixture states."""
+    from vectorizedmultiagentsimulator_b200.workload import Workload
+
+    if ref_available() and not args.fixture_inputs:
+        try:
+            import torch
+
+            dev = "cuda" if (n > 65536 and torch.cuda.is_available() and not need_env) else "cpu"
+            return RefInputs(args.scenario, n, seed, n_sets, device=dev)
+        except Exception as e:  # the copy did not import / build this scenario on this box: say so in the line
+            print(f"bench.py: reference inputs unavailable ({type(e).__name__}: {e}); using the tiled fixture states", file=sys.stderr)
+    wl = Workload(args.scenario, n, seed=seed)
+    wl.source = "32 recorded reset states of the reference (tests/golden) tiled with +-0.02 jitter; forces U(-a, a), a = largest recorded force"
+    wl.env = None
+    return wl
 
 
 def cpu_port_rate(wl, seconds=8.0, n_sample=None, threads=0):
@@ -142,97 +234,194 @@ def cpu_port_rate(wl, seconds=8.0, n_sample=None, threads=0):
 
 
 def run_reference(args, rank, world):
-    """Reference arm: the reference's own CPU implementation of the path, on the host cores (rank 0 only)."""
+    """Reference arm: the reference's own CPU implementation of the path, on the host cores (rank 0 only), on the same
+    inputs as the b200 arm (make_inputs), forces pre-generated outside the timed region."""
     if rank != 0:
         return
-    from vectorizedmultiagentsimulator_b200.workload import Workload
-
-    ref_dir = os.path.join(ROOT, "oracle", "_ref")
     line = {"impl": "reference", "metric": METRIC, "unit": "env-steps/s", "n_gpus": args.gpus, "steps": args.steps,
-            "warmup": args.warmup, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "warmup": args.warmup, "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "f32",
             "data": "synthetic"}
     n = args.num_envs
     value = kind = sample = None
     cores = os.cpu_count() or 1
-    if os.path.isdir(os.path.join(ref_dir, "vmas")):
+    wl = make_inputs(args, n, 0, 8, need_env=True)
+    if getattr(wl, "env", None) is not None:
         try:
-            value, sample = _time_ref_torch(args, ref_dir, n)
+            value, sample = _time_ref_torch(args, wl, n)
             kind = "reference"
-        except Exception as e:  # the copy did not import on this box: fall back to the port, say so
+        except Exception as e:  # the copy did not run on this box: fall back to the port, say so
             sample = f"oracle/_ref failed ({type(e).__name__}: {e}); "
     if value is None:
-        wl = Workload(args.scenario, n, seed=0)
         value, cores, s2 = cpu_port_rate(wl, seconds=max(2.0, 0.05 * args.steps))
         kind, sample = "port", (sample or "") + s2
     line.update({"value": value, "ms_per_step": 1e3 * n / value,
-                 "config": {"workload": f"{args.scenario} num_envs={n} (host CPU, {kind})"},
+                 "config": {"workload": f"{args.scenario} num_envs={n} per GPU, substeps={wl.desc.substeps}, {len(wl.desc.lidars)} lidars",
+                            "arm": f"host CPU, {kind}", "inputs": wl.source},
                  "cpu_baseline": {"value": value, "unit": "env-steps/s", "cores": cores, "kind": kind, "sample": sample},
                  "e2e": {"value": value, "unit": "env-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                  "gpu_launches": 0})
     print(json.dumps(line), flush=True)
 
 
-def _time_ref_torch(args, ref_dir, n):
+def _time_ref_torch(args, wl, n):
     """World.step + Lidar.measure of the UNMODIFIED reference physics (oracle/_ref = reference copy with the one-line
-    import fix of oracle/make_ref.sh) under torch CPU with all host threads."""
+    import fix of oracle/make_ref.sh) under torch CPU with all host threads, from the reset state and with the
+    pre-generated forces of `wl` (RefInputs)."""
     import torch
 
-    sys.path.insert(0, ref_dir)
-    sys.path.insert(0, os.path.join(ROOT, "oracle", "gym_stub"))
-    import vmas  # noqa
-
-    from vectorizedmultiagentsimulator_b200.workload import Workload
-
     torch.set_num_threads(os.cpu_count() or 1)
-    wl = Workload(args.scenario, 1, seed=0)  # fixture meta: reference scenario name, kwargs, substeps, action scale
-    env = vmas.make_env(wl.meta["scenario"], num_envs=n, device="cpu", seed=0, continuous_actions=True, **wl.meta["kwargs"])
-    world = env.world
-    if world._substeps != wl.desc.substeps:  # "transport, substeps>1": imposed on the built world (SURVEY 8, note i)
-        world._substeps, world._sub_dt = wl.desc.substeps, world._dt / wl.desc.substeps
+    world = wl.env.world
     agents = list(world.agents)
-    g = torch.Generator().manual_seed(1234)
-    scale = [float(v) for v in wl.f_scale]
+    f, t = wl.random_actions(8)
+    fs = [[torch.from_numpy(np.ascontiguousarray(f[k][:, a])) for a in range(len(agents))] for k in range(8)]
+    ts = [[torch.from_numpy(np.ascontiguousarray(t[k][:, a:a + 1])) for a in range(len(agents))] for k in range(8)]
 
-    def one():
-        for a, sc in zip(agents, scale):
-            a.state.force = (torch.rand(n, 2, generator=g) * 2 - 1) * sc
+    def one(k):
+        for i, a in enumerate(agents):
+            if a.state.force is not None:
+                a.state.force = fs[k % 8][i]
+            if a.state.torque is not None:
+                a.state.torque = ts[k % 8][i]
         world.step()
         for a in agents:
             for s in a.sensors or []:
                 s.measure()
 
-    for _ in range(args.warmup):
-        one()
+    for k in range(args.warmup):
+        one(k)
     t0 = time.perf_counter()
-    for _ in range(args.steps):
-        one()
+    for k in range(args.steps):
+        one(k)
     el = time.perf_counter() - t0
     return n * args.steps / el, f"{args.steps} steps x {n} envs, reference torch {torch.__version__} CPU World.step + Lidar.measure, {torch.get_num_threads()} threads ({el:.1f} s)"
 
 
-def run_b200(args, rank, local_rank, world):
+def torch_cuda_baseline(args, n, value_per_gpu, ms_kernel):
+    """The reference on THIS GPU (what north_star's ">= 10x the reference's torch-CUDA env-steps/s" refers to):
+    its Environment on cuda:0 at the same N, the pre-generated actions of the protocol, World.step + Lidar.measure alone
+    (host clock with a synchronize on both sides: the torch path is launch-bound, the GPU idles between its kernels) and
+    the whole Environment.step; then the same Environment with the drop-in enabled, and as one CUDA graph."""
     import torch
-    import torch.distributed as dist
 
-    from vectorizedmultiagentsimulator_b200.plan import StepPlan
     from vectorizedmultiagentsimulator_b200.workload import Workload
 
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py: no CUDA device (the CUDA step has no CPU fallback)")
-    torch.cuda.set_device(local_rank)
-    dev = torch.device("cuda", local_rank)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
-    n = args.num_envs
-    wl = Workload(args.scenario, n, seed=rank)
-    wl.desc.envs_per_cta = args.envs_per_cta
-    plan = StepPlan(wl.desc)
-    A, K, W = plan.A, args.steps, args.warmup
+    vmas = import_vmas()
+    fx = Workload(args.scenario, 1, seed=0)
+    K, W = max(5, min(args.steps, 30)), 3
 
-    # R independent env batches visited round-robin so that a step's inputs come from HBM, not from L2
+    def make():
+        env = vmas.make_env(fx.meta["scenario"], num_envs=n, device="cuda", seed=0, continuous_actions=True, **fx.meta["kwargs"])
+        if env.world._substeps != fx.desc.substeps:
+            env.world._substeps, env.world._sub_dt = fx.desc.substeps, env.world._dt / fx.desc.substeps
+        return env
+
+    def timed(fn, k):
+        for i in range(W):
+            fn(i)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for i in range(k):
+            fn(i)
+        torch.cuda.synchronize()
+        return (time.perf_counter() - t0) / k
+
+    def arms(env):
+        world = env.world
+        torch.manual_seed(1234)
+        acts = [[torch.rand(n, a.action_size, device="cuda") * 2 * a.u_range - a.u_range for a in env.agents] for _ in range(8)]
+        agents = list(world.agents)
+
+        def world_step(i):
+            world.step()
+            for a in agents:
+                for s_ in a.sensors or []:
+                    s_.measure()
+
+        t_env = timed(lambda i: env.step([a.clone() for a in acts[i % 8]]), K)
+        t_ws = timed(world_step, K)
+        return t_ws, t_env
+
+    out = {"device": f"cuda:0 ({torch.cuda.get_device_name(0)}), torch {torch.__version__}", "num_envs": n, "steps": K, "warmup": W,
+           "unit": "env-steps/s", "timing": "host clock, torch.cuda.synchronize() on both sides"}
+    ref = make()
+    t_ws, t_env = arms(ref)
+    out["reference"] = {"world_step": n / t_ws, "world_step_ms": 1e3 * t_ws, "environment_step": n / t_env, "environment_step_ms": 1e3 * t_env}
+    del ref
+    from vectorizedmultiagentsimulator_b200 import dropin
+
+    env = make()
+    dropin.enable(env, hooks=True)
+    t_ws, t_env = arms(env)
+    out["dropin"] = {"world_step": n / t_ws, "world_step_ms": 1e3 * t_ws, "environment_step": n / t_env, "environment_step_ms": 1e3 * t_env,
+                     "what": "the same Environment with World.step / cast_rays / scenario hooks routed through libvmasb200 (dropin.enable(env, hooks=True))"}
+    try:
+        from vectorizedmultiagentsimulator_b200.graph import GraphedEnvironment
+
+        genv = GraphedEnvironment(make(), check_actions=False)
+        torch.manual_seed(1234)
+        acts = [[torch.rand(n, a.action_size, device="cuda") * 2 * a.u_range - a.u_range for a in genv.env.agents] for _ in range(8)]
+        t_g = timed(lambda i: genv.step(acts[i % 8]), max(K, 50))
+        out["dropin_graph"] = {"environment_step": n / t_g, "environment_step_ms": 1e3 * t_g,
+                               "what": "the reference's Environment.step captured once as a CUDA graph and replayed (graph.GraphedEnvironment)"}
+    except Exception as e:
+        out["dropin_graph"] = {"unavailable": f"{type(e).__name__}: {e}"[:200]}
+    r = out["reference"]
+    out["speedup"] = {"kernel_vs_reference_world_step": value_per_gpu / r["world_step"],
+                      "dropin_world_step": out["dropin"]["world_step"] / r["world_step"],
+                      "dropin_environment_step": out["dropin"]["environment_step"] / r["environment_step"]}
+    if "environment_step" in out["dropin_graph"]:
+        out["speedup"]["graph_environment_step"] = out["dropin_graph"]["environment_step"] / r["environment_step"]
+    return out
+
+
+def pin_rank(local_rank, world):
+    """One rank per GPU: give each rank its own slice of the host cores (all GPUs of these boxes report the same CPU
+    affinity, so the slices are equal shares), before any pinned host buffer is allocated."""
+    try:
+        cores = sorted(os.sched_getaffinity(0))
+        per = max(1, len(cores) // world)
+        mine = cores[local_rank * per:(local_rank + 1) * per] or cores
+        os.sched_setaffinity(0, mine)
+        import torch
+
+        torch.set_num_threads(max(1, len(mine)))
+    except (AttributeError, OSError):
+        pass
+
+
+def fp32_peak_tflops(clocks):
+    """Non-tensor FP32 peak: the FFMA micro-benchmark committed under profiles/ (tools/fma_peak.cu) when there is one, else
+    148 SMs x 128 lanes x 2 x the max SM clock."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r2_fma_peak.json")) as f:
+            m = json.load(f)
+        return float(m["ffma_tflops"]), f"measured FFMA micro-benchmark (profiles/r2_fma_peak.json: {m['ffma_tflops']:.1f} TFLOP/s at {m.get('sm_mhz', '?')} MHz)"
+    except (OSError, ValueError, KeyError):
+        mhz = (clocks or {}).get("sm_max_mhz") or 1965.0
+        return 148 * 128 * 2 * mhz * 1e6 / 1e12, "148 SMs x 128 lanes x 2 x max SM clock"
+
+
+def time_steps(plan, ios, K, W, barrier, torch):
+    """K launches over the batches of `ios` round-robin, CUDA events on the launching stream, >= 3 warm-up steps per batch."""
+    R = len(ios)
+    for i in range(max(W, 3) * R):
+        plan.step_io(ios[i % R])
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(K):
+        plan.step_io(ios[i % R])
+    e1.record()
+    barrier()
+    return e0.elapsed_time(e1)
+
+
+def device_batches(plan, wl, n, dev, exact, torch, max_sets=64):
+    """R independent env batches (same initial state, different forces) so that a step's inputs come from HBM, not L2."""
+    A = plan.A
     ld = plan.ld_for(n)
     per_batch = 4 * ld * (2 * plan.dyn_rows + plan.stat_rows + plan.act_rows + plan.lidar_rows + 3 * A)
-    R = max(2, min(64, -(-2 * L2_BYTES // max(per_batch, 1))))
+    R = max(2, min(max_sets, -(-2 * L2_BYTES // max(per_batch, 1))))
     dyn0, stat0 = plan.pack(wl.state0, wl.jrot0 if wl.jrot0.size else None)
     f_all, t_all = wl.random_actions(R)
     stream = torch.cuda.current_stream().cuda_stream
@@ -240,32 +429,79 @@ def run_b200(args, rank, local_rank, world):
     for r in range(R):
         dyn = torch.from_numpy(dyn0).to(dev)
         stat = torch.from_numpy(stat0).to(dev) if plan.stat_rows else None
-        fr = torch.from_numpy(f_all[r]).to(dev)  # [N, A, 2]
-        tr = torch.from_numpy(t_all[r]).to(dev)  # [N, A]
+        fr = torch.from_numpy(np.ascontiguousarray(f_all[r])).to(dev)  # [N, A, 2]
+        tr = torch.from_numpy(np.ascontiguousarray(t_all[r])).to(dev)  # [N, A]
         forces = [fr[:, a, :] for a in range(A)]
         torques = [tr[:, a:a + 1] for a in range(A)]
         act = torch.zeros(plan.act_rows, ld, device=dev) if plan.act_rows else None
         lid = torch.zeros(plan.lidar_rows, ld, device=dev) if plan.lidar_rows else None
-        ios.append(plan.make_io(dyn, dyn, stat, forces, torques, act, lid, None, n, ld, bool(args.exact), stream))
+        ios.append(plan.make_io(dyn, dyn, stat, forces, torques, act, lid, None, n, ld, bool(exact), stream))
         keep.append((dyn, stat, fr, tr, act, lid))
+    return ios, keep, R, per_batch
+
+
+def roofline_block(args, plan, desc, n, ms_per_step, clocks, compiled, peak, peak_src):
+    """Both roofs of SURVEY 8(d) for one launch over n envs: HBM (algorithmic bytes at the measured copy bandwidth) and FP32
+    (algorithmic FLOPs at the non-tensor FP32 peak); `bound` names the one that binds, i.e. whose ideal time is longer."""
+    cap = ncu_capture(args.scenario, n, compiled)
+    alg = plan.alg_bytes_per_env * n
+    hbm_achieved = alg / (ms_per_step * 1e-3) / 1e9
+    flops = alg_flops_per_env(plan, desc)
+    fpeak, fsrc = fp32_peak_tflops(clocks)
+    fp32_achieved = flops * n / (ms_per_step * 1e-3) / 1e12
+    binding = "fp32" if flops / (fpeak * 1e12) > plan.alg_bytes_per_env / (peak * 1e9) else "hbm"
+    hbm = {"achieved": hbm_achieved, "peak": peak, "unit": "GB/s", "frac": hbm_achieved / peak, "peak_source": peak_src,
+           "alg_bytes_per_env": plan.alg_bytes_per_env}
+    fp32 = {"achieved": fp32_achieved, "peak": fpeak, "unit": "TFLOP/s", "frac": fp32_achieved / fpeak, "peak_source": fsrc,
+            "alg_flops_per_env": flops, "flops_source": "SURVEY 8(d) per-primitive op counts of the reference (the kernel's culls execute fewer)"}
+    if cap.get("fp32_flops"):
+        # FP32 operations the kernel really executed (ncu: thread-level FADD + FMUL + 2 FFMA of one launch)
+        fp32["executed_flops_per_env"] = cap["fp32_flops"] / cap.get("n_envs", n)
+        fp32["executed_tflops"] = cap["fp32_flops"] / (ms_per_step * 1e-3) / 1e12
+    b = hbm if binding == "hbm" else fp32
+    r = {"bound": binding, "achieved": b["achieved"], "peak": b["peak"], "unit": b["unit"], "frac": b["frac"],
+         "traffic": cap.get("dram_bytes"), "hbm": hbm, "fp32": fp32, "num_envs": n, "ms_per_launch": ms_per_step,
+         "kernel": "vmasb200_step_world (world-compiled, NVRTC)" if compiled else "vb::step_kernel"}
+    if cap.get("warp_inst"):
+        mhz = (clocks or {}).get("sm_mhz") or 1965.0
+        ips = cap["warp_inst"] / (ms_per_step * 1e-3)
+        r["issue"] = {"warp_inst_per_launch": cap["warp_inst"], "achieved_ginst_s": ips / 1e9,
+                      "peak_ginst_s": 4 * 148 * mhz * 1e-3, "frac": ips / (4 * 148 * mhz * 1e6)}
+    return r
+
+
+def run_b200(args, rank, local_rank, world):
+    import torch
+    import torch.distributed as dist
+
+    from vectorizedmultiagentsimulator_b200.plan import StepPlan
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (the CUDA step has no CPU fallback)")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+        pin_rank(local_rank, world)
+    # weak: --num-envs per GPU; strong: --num-envs in total, split evenly (SURVEY 8d: "N split evenly" for the football sweep)
+    n = args.num_envs if args.scaling == "weak" else -(-args.num_envs // world)
+    A_guess_sets = 64
+    wl = make_inputs(args, n, rank, A_guess_sets if n <= 65536 else 4)
+    wl.desc.envs_per_cta = args.envs_per_cta
+    plan = StepPlan(wl.desc)
+    K, W = args.steps, args.warmup
+    ios, keep, R, per_batch = device_batches(plan, wl, n, dev, args.exact, torch)
+    stream = torch.cuda.current_stream().cuda_stream
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    for i in range(max(W, 3) * R):  # every batch gets >= 3 warm-up steps
-        plan.step_io(ios[i % R])
-    barrier()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    # warm-up pass (also triggers the NVRTC build / cubin load), then the timed region with the clock sampler running
+    time_steps(plan, ios, 3, W, barrier, torch)
     sampler = ClockSampler(local_rank)
-    barrier()
-    e0.record()
-    for i in range(K):
-        plan.step_io(ios[i % R])
-    e1.record()
-    barrier()
-    ms = e0.elapsed_time(e1)
+    ms = time_steps(plan, ios, K, W, barrier, torch)
     clocks = sampler.stop()
     repairs = plan.sync_check(stream)
     if world > 1:
@@ -275,15 +511,7 @@ def run_b200(args, rank, local_rank, world):
     value = world * n * K / (ms * 1e-3)
 
     # L2-resident variant (one batch stepped in place, what a rollout does): reported beside, not as `value`
-    for _ in range(3):
-        plan.step_io(ios[0])
-    torch.cuda.synchronize()
-    e0.record()
-    for _ in range(K):
-        plan.step_io(ios[0])
-    e1.record()
-    torch.cuda.synchronize()
-    ms_hot = e0.elapsed_time(e1)
+    ms_hot = time_steps(plan, ios[:1], K, 3, lambda: torch.cuda.synchronize(), torch)
 
     e2e = None
     if not args.no_e2e:
@@ -292,14 +520,12 @@ def run_b200(args, rank, local_rank, world):
         peak, peak_src = peaks()
         jit_state, jit_launches = plan.jit(n)
         compiled = jit_launches > 0   # the launches took the world-compiled kernel (csrc/jit.h), not the generic one
-        cap = ncu_capture(args.scenario, n, compiled)
-        alg = plan.alg_bytes_per_env * n
-        achieved = alg / (ms / K * 1e-3) / 1e9
         line = {
             "metric": METRIC, "value": value, "unit": "env-steps/s", "n_gpus": world, "steps": K, "warmup": max(W, 3),
-            "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "ms_per_step": ms / K, "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
             "config": {"workload": f"{args.scenario} num_envs={n} per GPU, substeps={plan.S}, {len(wl.desc.lidars)} lidars",
+                       "inputs": wl.source,
                        "l2": f"{R} env batches visited round-robin, working set {R * per_batch / 2**20:.0f} MiB > L2 126 MiB",
                        "envs_per_cta": plan.tile_for(n),
                        "layout": ("SoA rows [field][env]; world-compiled kernel (NVRTC): one thread per env, state in registers"
@@ -307,30 +533,50 @@ def run_b200(args, rank, local_rank, world):
                                   "SoA rows [field][env]; 128 threads per CTA, 128 / envs_per_cta of them share an env"),
                        "exact": int(args.exact), "speculation_repairs": repairs,
                        "l2_resident_ms_per_step": ms_hot / K},
-            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": cap.get("dram_bytes"), "peak_source": peak_src, "alg_bytes_per_env": plan.alg_bytes_per_env,
-                         "kernel": "vmasb200_step_world (world-compiled, NVRTC)" if compiled else "vb::step_kernel"},
+            "roofline": roofline_block(args, plan, wl.desc, n, ms / K, clocks, compiled, peak, peak_src),
             # one launch per step; a compiled world that can have thin contacts is followed by its 1-CTA repair_kernel
             "gpu_launches": K * (2 * plan.S if args.exact else (2 if compiled and plan.jit_tail_launches else 1)),
             "clocks": clocks,
         }
-        # the step's roofline is the slower of its HBM bytes at peak bandwidth and its FP32 FLOPs at the
-        # non-tensor FP32 peak (148 SMs x 128 lanes x 2 x max SM clock); both fractions are reported, `binding` names it
-        flops = alg_flops_per_env(plan, wl.desc)
-        fp32_peak = 148 * 128 * 2 * ((clocks or {}).get("sm_max_mhz") or 1965.0) * 1e6
-        fp32_frac = flops * value / world / fp32_peak
-        line["roofline"]["fp32"] = {"alg_flops_per_env": flops, "achieved_tflops": flops * value / world / 1e12,
-                                    "peak_tflops": fp32_peak / 1e12, "frac": fp32_frac}
-        line["roofline"]["binding"] = "fp32" if flops / fp32_peak > plan.alg_bytes_per_env / (peak * 1e9) else "hbm"
-        if cap.get("warp_inst"):
-            # the bound that actually binds: warp instructions of one launch (ncu) over the live launch
-            # time, against 4 issue slots x 148 SMs at the SM clock sampled during the timed region
-            mhz = (clocks or {}).get("sm_mhz") or 1965.0
-            ips = cap["warp_inst"] / (ms / K * 1e-3)
-            line["roofline"]["issue"] = {"warp_inst_per_launch": cap["warp_inst"], "achieved_ginst_s": ips / 1e9,
-                                         "peak_ginst_s": 4 * 148 * mhz * 1e-3, "frac": ips / (4 * 148 * mhz * 1e6)}
+        if n < 262144:
+            line["roofline"]["note"] = (f"one launch over {n} envs moves {plan.alg_bytes_per_env * n / 1e6:.1f} MB in a single wave of "
+                                        f"{-(-n // plan.tile_for(n))} CTAs: {1e3 * plan.alg_bytes_per_env * n / (peak * 1e9):.4f} ms at the HBM peak, below one "
+                                        "kernel launch - latency-bound; the roofline fraction of this path is meaningful from ~256 K envs "
+                                        "(SURVEY 8d), see roofline_1m (same kernel, same run)")
         if e2e is not None:
             line["e2e"] = e2e
+    # ---- the same kernel at 1 048 576 envs, measured in this run: what the north_star's ">= 50 % of the HBM roofline" is about
+    if world == 1 and n < 262144 and not args.no_1m:
+        try:
+            from vectorizedmultiagentsimulator_b200.workload import Workload
+
+            n1 = 1 << 20
+            del ios, keep
+            torch.cuda.empty_cache()
+            wl1 = Workload(args.scenario, n1, seed=0)
+            wl1.desc.envs_per_cta = args.envs_per_cta
+            plan1 = StepPlan(wl1.desc)
+            ios1, keep1, R1, pb1 = device_batches(plan1, wl1, n1, dev, args.exact, torch, max_sets=2)
+            time_steps(plan1, ios1, 3, 3, lambda: torch.cuda.synchronize(), torch)
+            s1 = ClockSampler(local_rank)
+            K1 = max(10, min(K, 50))
+            ms1 = time_steps(plan1, ios1, K1, 3, lambda: torch.cuda.synchronize(), torch)
+            ck1 = s1.stop()
+            _, jl1 = plan1.jit(n1)
+            r1 = roofline_block(args, plan1, wl1.desc, n1, ms1 / K1, ck1, jl1 > 0, peak, peak_src)
+            r1.update({"value": n1 * K1 / (ms1 * 1e-3), "unit_value": "env-steps/s", "steps": K1, "clocks": ck1,
+                       "inputs": "tiled fixture reset states (workload.Workload)", "l2": f"{R1} batches of {pb1 / 2**20:.0f} MiB visited round-robin"})
+            line["roofline_1m"] = r1
+            del ios1, keep1
+            torch.cuda.empty_cache()
+        except Exception as e:
+            line["roofline_1m"] = {"unavailable": f"{type(e).__name__}: {e}"[:300]}
+    if rank == 0:
+        if world == 1 and not args.no_torch_cuda and ref_available():
+            try:
+                line["torch_cuda_baseline"] = torch_cuda_baseline(args, n, value, ms / K)
+            except Exception as e:
+                line["torch_cuda_baseline"] = {"unavailable": f"{type(e).__name__}: {e}"[:300]}
         if world == 1 and not args.no_cpu_baseline:
             v, cores, sample = cpu_port_rate(wl, seconds=10.0)
             line["cpu_baseline"] = {"value": v, "unit": "env-steps/s", "cores": cores, "kind": "port", "sample": sample}
@@ -340,8 +586,10 @@ def run_b200(args, rank, local_rank, world):
 
 
 def run_e2e(plan, wl, n, K, world, dev):
-    """Same metric through the C-ABI HOST-buffer call (vmasb200_step_host): pinned host records in, H2D, kernel,
-    D2H of state / clamped actions / LIDAR, stream sync - every step."""
+    """Same metric through the C-ABI HOST-buffer call (vmasb200_step_host) as a rollout drives it: every step the actions
+    come from pinned host memory (H2D), the kernel runs, and the new state + LIDAR readings (what observations are made
+    of) go back to pinned host memory (D2H), then a stream sync.  The state itself stays on the device between the calls
+    (h_dyn_in = NULL from the second call on: it is what the previous call just returned)."""
     import torch
     import torch.distributed as dist
 
@@ -351,33 +599,47 @@ def run_e2e(plan, wl, n, K, world, dev):
 
     dyn0, stat0 = plan.pack(wl.state0, wl.jrot0 if wl.jrot0.size else None)
     ld = dyn0.shape[1]
-    f, t = wl.random_actions(1)
-    keep = [pinned(dyn0), pinned(stat0), pinned(f[0]), pinned(t[0])]
-    dyn, stat, fr, tq = (k[1] for k in keep)
-    outs = [pinned(np.zeros((plan.dyn_rows, ld), np.float32)), pinned(np.zeros((max(plan.act_rows, 1), ld), np.float32)),
-            pinned(np.zeros((max(plan.lidar_rows, 1), ld), np.float32))]
-    out = (outs[0][1], outs[1][1][:plan.act_rows] if plan.act_rows else None,
-           outs[2][1][:plan.lidar_rows] if plan.lidar_rows else None)
-    for _ in range(3):
-        plan.step_host(dyn, stat, fr, tq, exact=False, want_masks=False, out=out)
+    f, t = wl.random_actions(2)
+    keep = [pinned(dyn0), pinned(stat0), pinned(f[0]), pinned(t[0]), pinned(f[1]), pinned(t[1])]
+    dyn, stat = keep[0][1], keep[1][1]
+    acts = [(keep[2][1], keep[3][1]), (keep[4][1], keep[5][1])]
+    outs = [pinned(np.zeros((plan.dyn_rows, ld), np.float32)), pinned(np.zeros((max(plan.lidar_rows, 1), ld), np.float32))]
+    out = (outs[0][1], None, outs[1][1][:plan.lidar_rows] if plan.lidar_rows else None)
+    plan.step_host(dyn, stat, acts[0][0], acts[0][1], exact=False, want_masks=False, out=out)  # uploads state + static rows
+    # one prepared C-ABI call per action buffer (plan.host_stepper: the ctypes call and nothing else)
+    calls = [plan.host_stepper(n, ld, a[0], a[1], out[0], None, out[2]) for a in acts]
+    for i in range(3):
+        calls[i % 2]()
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
     t0 = time.perf_counter()
-    for _ in range(K):
-        # the step's results land in pinned host memory; the next step starts from them (a rollout through the host API)
-        plan.step_host(dyn, stat, fr, tq, exact=False, want_masks=False, out=out)
-        dyn, out = out[0], (dyn, out[1], out[2])
+    for i in range(K):
+        calls[i % 2]()
     torch.cuda.synchronize()
     el = time.perf_counter() - t0
     if world > 1:
         tt = torch.tensor([el], device=dev)
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         el = float(tt.item())
-    h2d = 4 * n * (plan.dyn_rows + plan.stat_rows + 3 * plan.A)
-    d2h = 4 * n * (plan.dyn_rows + plan.act_rows + plan.lidar_rows)
+    h2d = 4 * n * 3 * plan.A
+    d2h = 4 * n * (plan.dyn_rows + plan.lidar_rows)
+    # this box's PCIe link, measured now: one flat device-to-host copy of the step's output bytes into pinned memory
+    src = torch.empty(d2h // 4, device=dev)
+    dst = torch.empty(d2h // 4).pin_memory()
+    for _ in range(3):
+        dst.copy_(src, non_blocking=True)
+    torch.cuda.synchronize()
+    t1 = time.perf_counter()
+    for _ in range(20):
+        dst.copy_(src, non_blocking=True)
+    torch.cuda.synchronize()
+    copy_ms = (time.perf_counter() - t1) / 20 * 1e3
     return {"value": world * n * K / el, "unit": "env-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-            "api": "vmasb200_step_host (C ABI, pinned host SoA buffers, chunked over 4 streams)"}
+            "ms_per_step": 1e3 * el / K,
+            "pcie_floor_ms": copy_ms, "pcie_d2h_gbs": d2h / copy_ms / 1e6,
+            "api": "vmasb200_step_host (C ABI, pinned host buffers): actions in, new state + LIDAR out every step; the state stays "
+                   "device-resident between calls (h_dyn_in = NULL)"}
 
 
 def run_env_cuda(args, rank):

@@ -249,3 +249,32 @@ def test_step_host_zero_copy_equals_staged_bitwise(scenario, monkeypatch):
             if x[i] is not None:
                 assert np.array_equal(x[i], y[i], equal_nan=True), f"{scenario}: output {i} of step {k}, zero-copy vs staged"
                 assert np.array_equal(x[i], z[i], equal_nan=True), f"{scenario}: output {i} of step {k}, pinned vs pageable"
+
+
+@pytest.mark.parametrize("scenario", ["navigation", "transport", "joint_passage"])
+def test_step_host_resident_state_equals_passing_it_bitwise(scenario):
+    """vmasb200_step_host with h_dyn_in = h_stat = NULL continues from the state its device staging holds from the previous
+    call (a rollout through the host API only moves the actions in): same bits as handing the returned state back in,
+    across chunked batches; and without a previous call of that batch size it is an error, not stale data."""
+    from vectorizedmultiagentsimulator_b200._lib import VmasB200Error
+    from vectorizedmultiagentsimulator_b200.workload import Workload
+
+    n = 40000 + 12  # three chunks of the host pipeline, ragged
+    wl = Workload(scenario, n, seed=5)
+    f, t = wl.random_actions(5)
+    ref_plan, plan = StepPlan(wl.desc), StepPlan(wl.desc)
+    dyn0, stat0 = plan.pack(wl.state0, wl.jrot0 if wl.jrot0.size else None)
+    with pytest.raises(VmasB200Error, match="no state"):
+        plan.step_host(None, None, f[0], t[0], exact=False, want_masks=False, out=(np.zeros_like(dyn0), None, None))
+    dyn = dyn0
+    got = None
+    for k in range(5):
+        a = ref_plan.step_host(dyn, stat0, f[k], t[k], exact=False, want_masks=False)
+        b = plan.step_host(dyn0, stat0, f[k], t[k], exact=False, want_masks=False) if k == 0 else \
+            plan.step_host(None, None, f[k], t[k], exact=False, want_masks=False, out=(np.zeros_like(dyn0), got[1], got[2]))
+        for x, y, what in zip(a[:3], b[:3], ("dyn", "act", "lidar")):
+            if x is not None:
+                assert np.array_equal(x[:, :n].view(np.uint32), y[:, :n].view(np.uint32)), f"{scenario} step {k}: {what}"
+        dyn, got = a[0], b
+    with pytest.raises(VmasB200Error, match="no state"):  # another batch size: the staging does not hold it
+        plan.step_host(None, None, f[0][:512], t[0][:512], exact=False, want_masks=False, out=(np.zeros((plan.dyn_rows, 512), np.float32), None, None))

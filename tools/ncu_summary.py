@@ -16,7 +16,7 @@ KEYS = [
     "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum", "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum",
     "smsp__average_warp_latency_issue_stalled", "smsp__average_warps_issue_stalled",
     "smsp__thread_inst_executed_per_inst_executed.ratio", "lts__t_bytes.sum", "l1tex__t_bytes.sum",
-    "smsp__cycles_active.avg", "sm__cycles_elapsed.max", "local_load", "local_store", "smsp__inst_executed_op_local",
+    "smsp__cycles_active.avg", "sm__cycles_elapsed.max", "smsp__sass_thread_inst_executed_op_f", "local_load", "local_store", "smsp__inst_executed_op_local",
 ]
 
 

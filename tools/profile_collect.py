@@ -100,7 +100,12 @@ def main():
         m = re.match(r"(.*)_(\d+)$", wl)
         scen, n = (m.group(1), int(m.group(2))) if m else (wl, 32768)
         rdb, wrb = to_bytes(*rd), to_bytes(*wr)
-        traffic[f"{scen}@{n}"] = {"dram_bytes": rdb + wrb, "dram_read": rdb, "dram_write": wrb,
+        fl = [metric(f"smsp__sass_thread_inst_executed_op_{k}_pred_on.sum") for k in ("fadd", "fmul", "ffma")]
+        flops = None
+        if all(fl):
+            fa, fm, ff = (float(x[0].replace(",", "")) for x in fl)
+            flops = fa + fm + 2 * ff  # FP32 operations the launch executed (thread level)
+        traffic[f"{scen}@{n}"] = {"fp32_flops": flops, "n_envs": n, "dram_bytes": rdb + wrb, "dram_read": rdb, "dram_write": wrb,
                                   "grid": int(float(grid[0].replace(",", ""))) if grid else None,
                                   "warp_inst": float(inst[0].replace(",", "")), "duration": " ".join(dur) if dur else None,
                                   "kernel": kname, "source": f"profiles/{tag}_step_kernel_{wl}.txt"}

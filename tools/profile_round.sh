@@ -4,7 +4,7 @@
 # text (tools/profile_lines.sh: the .ncu-rep files would exceed gpurun_out's 64 MiB).  Everything lands in
 # gpurun_out/<tag>/; tools/profile_collect.py (run afterwards, no GPU needed) turns it into profiles/.
 #   gpurun --timeout 2400 -- 'bash tools/profile_round.sh r1w'
-TAG=${1:-r1w}
+TAG=${1:-r2}
 OUT=gpurun_out/$TAG
 mkdir -p $OUT
 PY=python

@@ -49,6 +49,8 @@ struct vmasb200_plan {
   uint32_t* d_urec = nullptr;  // per tainted env: verdict record + thin-event record ([S][pair_words] each)
   // staging of vmasb200_step_host
   int64_t host_cap = 0;        // row stride (floats) of the staging buffers
+  int64_t res_n = -1;          // envs of the state / static rows the staging holds from the last step_host call (-1: none)
+  bool res_stat = false;       // ... and whether the static rows were ever uploaded for that batch
   float *d_dyn = nullptr, *d_stat = nullptr, *d_force = nullptr, *d_torque = nullptr, *d_act = nullptr, *d_lidar = nullptr;
   cudaStream_t streams[vb::kHostStreams] = {};
 };

@@ -404,6 +404,7 @@ int vmasb200_step(vmasb200_plan* pl, const vmasb200_step_io* io) {
 
 static int grow_host_staging(vmasb200_plan* pl, int64_t ld) {
   if (ld <= pl->host_cap) return VMASB200_OK;
+  pl->res_n = -1; pl->res_stat = false;
   const KParams& kp = pl->kp;
   cudaFree(pl->d_dyn); cudaFree(pl->d_stat); cudaFree(pl->d_force); cudaFree(pl->d_torque); cudaFree(pl->d_act); cudaFree(pl->d_lidar);
   pl->d_dyn = pl->d_stat = pl->d_force = pl->d_torque = pl->d_act = pl->d_lidar = nullptr;
@@ -433,13 +434,17 @@ static bool host_dev_ptr(const void* h, void** d) {
 int vmasb200_step_host(vmasb200_plan* pl, const float* h_dyn_in, const float* h_stat, const float* h_force,
                        const float* h_torque, float* h_dyn_out, float* h_act_out, float* h_lidar_out,
                        uint32_t* h_pair_active, int64_t n, int64_t ld, int32_t exact) {
-  if (!pl || !h_dyn_in || n < 0 || ld < n || (ld & 3)) { set_error("step_host: bad argument (ld >= n_envs, ld % 4 == 0)"); return VMASB200_ERR_INVALID; }
+  if (!pl || n < 0 || ld < n || (ld & 3)) { set_error("step_host: bad argument (ld >= n_envs, ld % 4 == 0)"); return VMASB200_ERR_INVALID; }
   int rc = upload_plan(pl);
   if (rc) return rc;
   const KParams& kp = pl->kp;
-  if (kp.stat_rows && !h_stat) { set_error("step_host: stat buffer missing"); return VMASB200_ERR_INVALID; }
   if (n == 0) return VMASB200_OK;
   if ((rc = grow_host_staging(pl, ld))) return rc;
+  // h_dyn_in == NULL / h_stat == NULL: the rows this plan's device staging holds from the previous call (a rollout through
+  // the host API only moves the actions in: the state it would send is the state it just received)
+  if (!h_dyn_in && pl->res_n != n) { set_error("step_host: h_dyn_in is NULL but the plan holds no state of this batch size from a previous call"); return VMASB200_ERR_INVALID; }
+  if (kp.stat_rows && !h_stat && !(pl->res_stat && pl->res_n == n)) { set_error("step_host: stat buffer missing (NULL = the one uploaded by the previous call of this batch size)"); return VMASB200_ERR_INVALID; }
+  if (h_dyn_in && pl->res_n != n) pl->res_stat = false;
   for (cudaStream_t& s : pl->streams)
     if (!s) VB_CUDA(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
   const int64_t dld = pl->host_cap;  // row stride of the device staging (>= ld)
@@ -477,7 +482,7 @@ int vmasb200_step_host(vmasb200_plan* pl, const float* h_dyn_in, const float* h_
   // for PCIe hold the SM's shared memory), see profiles/README.md; same bits either way (tests/test_gpu_parity.py).
   const char* env_direct = std::getenv("VMASB200_HOST_DIRECT");
   const bool direct_ok = env_direct && std::atoi(env_direct) != 0;
-  if (direct_ok && !exact && h_dyn_out && kp.n_dyn && (!kp.act_rows || h_act_out)) {
+  if (direct_ok && !exact && h_dyn_in && (h_stat || !kp.stat_rows) && h_dyn_out && kp.n_dyn && (!kp.act_rows || h_act_out)) {
     void *d_in, *d_out, *d_st, *d_f, *d_t, *d_act, *d_lid;
     if (host_dev_ptr(h_dyn_in, &d_in) && host_dev_ptr(h_dyn_out, &d_out) && host_dev_ptr(h_stat, &d_st) &&
         host_dev_ptr(h_force, &d_f) && host_dev_ptr(h_torque, &d_t) && host_dev_ptr(h_act_out, &d_act) &&
@@ -498,6 +503,7 @@ int vmasb200_step_host(vmasb200_plan* pl, const float* h_dyn_in, const float* h_
       if ((rc = check_io(pl, &io)) == VMASB200_OK) {
         if ((rc = launch_step(pl, &io, 0, n))) return rc;
         VB_CUDA(cudaStreamSynchronize(st));
+        pl->res_n = -1;  // the state went host -> host: the staging holds nothing
         if (h_pair_active && kp.S * kp.pair_words)
           VB_CUDA(cudaMemcpy(h_pair_active, pl->d_bits, (size_t)kp.S * kp.pair_words * 4, cudaMemcpyDeviceToHost));
         return VMASB200_OK;
@@ -509,8 +515,8 @@ int vmasb200_step_host(vmasb200_plan* pl, const float* h_dyn_in, const float* h_
   for (int64_t k = 0; k < nchunk; ++k) {
     cudaStream_t st = pl->streams[k % kHostStreams];
     const int64_t c0 = k * csize, c1 = std::min(n, c0 + csize), ncol = c1 - c0;
-    if (kp.dyn_rows) VB_CUDA(rows2d(pl->d_dyn, dld, h_dyn_in, ld, c0, ncol, kp.dyn_rows, cudaMemcpyHostToDevice, st));
-    if (kp.stat_rows) VB_CUDA(rows2d(pl->d_stat, dld, h_stat, ld, c0, ncol, kp.stat_rows, cudaMemcpyHostToDevice, st));
+    if (kp.dyn_rows && h_dyn_in) VB_CUDA(rows2d(pl->d_dyn, dld, h_dyn_in, ld, c0, ncol, kp.dyn_rows, cudaMemcpyHostToDevice, st));
+    if (kp.stat_rows && h_stat) VB_CUDA(rows2d(pl->d_stat, dld, h_stat, ld, c0, ncol, kp.stat_rows, cudaMemcpyHostToDevice, st));
     if (kp.A && h_force) VB_CUDA(cudaMemcpyAsync(pl->d_force + c0 * 2 * kp.A, h_force + c0 * 2 * kp.A, (size_t)ncol * kp.A * 8, cudaMemcpyHostToDevice, st));
     if (kp.A && h_torque) VB_CUDA(cudaMemcpyAsync(pl->d_torque + c0 * kp.A, h_torque + c0 * kp.A, (size_t)ncol * kp.A * 4, cudaMemcpyHostToDevice, st));
     vmasb200_step_io io{};
@@ -532,6 +538,8 @@ int vmasb200_step_host(vmasb200_plan* pl, const float* h_dyn_in, const float* h_
   }
   if (h_pair_active && kp.S * kp.pair_words)
     VB_CUDA(cudaMemcpy(h_pair_active, pl->d_bits, (size_t)kp.S * kp.pair_words * 4, cudaMemcpyDeviceToHost));
+  pl->res_n = n;  // the kernel stepped the staging in place: it now holds the new state
+  if (h_stat) pl->res_stat = true;
   return VMASB200_OK;
 }
 

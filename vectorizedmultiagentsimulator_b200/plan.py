@@ -118,24 +118,41 @@ class StepPlan:
     # ------------------------------------------------------------------ compute: host buffers (H2D + kernel + D2H inside)
     def step_host(self, dyn, stat, force=None, torque=None, exact=False, want_lidar=True, want_masks=True, out=None):
         """dyn [dyn_rows, ld], stat [stat_rows, ld], force [N,A,2], torque [N,A] numpy fp32 (N = force/torque rows, else
-        ld).  out = optional (dyn_out, act, lidar) buffers to fill (e.g. pinned).  Returns (dyn_out, act_out, lidar_out,
-        pair_active_words)."""
-        ld = dyn.shape[1]
+        ld).  out = optional (dyn_out, act, lidar) buffers to fill (e.g. pinned).  dyn / stat None (from the second call of a
+        batch on): start from the state / static rows the plan's device staging holds from the previous call; `out` then
+        gives the row stride.  Returns (dyn_out, act_out, lidar_out, pair_active_words)."""
+        ld = dyn.shape[1] if dyn is not None else out[0].shape[1]
         n = force.shape[0] if force is not None else (torque.shape[0] if torque is not None else ld)
-        assert dyn.dtype == np.float32 and dyn.flags.c_contiguous and dyn.shape == (self.dyn_rows, ld)
+        assert dyn is None or (dyn.dtype == np.float32 and dyn.flags.c_contiguous and dyn.shape == (self.dyn_rows, ld))
         for a, shp in ((stat, (self.stat_rows, ld)), (force, (n, self.A, 2)), (torque, (n, self.A))):
             assert a is None or (a.dtype == np.float32 and a.flags.c_contiguous and a.shape == shp), shp
         if out is not None:
             dyn_out, act, lid = out
         else:
-            dyn_out = np.zeros_like(dyn)
+            dyn_out = np.zeros((self.dyn_rows, ld), np.float32)
             act = np.zeros((self.act_rows, ld), np.float32) if self.act_rows else None
             lid = np.zeros((self.lidar_rows, ld), np.float32) if (self.lidar_rows and want_lidar) else None
         pa = np.zeros((self.S, self.pair_words), np.uint32) if (self.pair_words and want_masks) else None
-        rc = _lib.lib().vmasb200_step_host(self._h, _ptr(dyn), _ptr(stat) if self.stat_rows else None, _ptr(force),
+        rc = _lib.lib().vmasb200_step_host(self._h, _ptr(dyn), _ptr(stat) if (self.stat_rows and stat is not None) else None, _ptr(force),
                                            _ptr(torque), _ptr(dyn_out), _ptr(act), _ptr(lid), _ptr(pa), n, ld, int(exact))
         _lib.check(rc, "vmasb200_step_host")
         return dyn_out, act, lid, pa
+
+    def host_stepper(self, n, ld, force, torque, dyn_out, act_out, lidar_out, dyn_in=None, stat=None):
+        """A closure over ONE prepared vmasb200_step_host call (numpy host buffers, ideally pinned): what a rollout loop
+        calls every step without re-validating its buffers - the C ABI call itself, nothing else.  dyn_in / stat None =
+        continue from the state the plan's device staging holds (include/vmasb200.h)."""
+        fn = _lib.lib().vmasb200_step_host
+        args = (self._h, _ptr(dyn_in), _ptr(stat), _ptr(force), _ptr(torque), _ptr(dyn_out), _ptr(act_out), _ptr(lidar_out),
+                None, int(n), int(ld), 0)
+        keep = (force, torque, dyn_out, act_out, lidar_out, dyn_in, stat)
+
+        def step(_keep=keep):
+            rc = fn(*args)
+            if rc:
+                _lib.check(rc, "vmasb200_step_host")
+
+        return step
 
     # ------------------------------------------------------------------ compute: device buffers (asynchronous)
     def make_io(self, dyn_in, dyn_out, stat, forces: List, torques: List, act_out, lidar_out, pair_active_out,
