@@ -310,6 +310,31 @@ int vmasb200_set_action(const float* action, int64_t stride_env, int64_t stride_
                         const float* u_range, const float* u_multiplier, int32_t clamp, float* u_out, int32_t* flags,
                         int64_t n_envs, void* stream);
 
+/* ---- the same with COMMUNICATION actions and / or action NOISE (environment.py:633-645, 711-754), continuous actions:
+ *  action d: [n_envs][>= action_size + n_comm] fp32; physical columns 0 .. action_size - 1, communication columns
+ *            comm_col0 .. comm_col0 + n_comm - 1 (comm_col0 = action_size when env.clamp_action, else world.dim_p: the
+ *            reference slices `action[:, dim_p:]` there, environment.py:742-743)
+ *  u_randn d: [n_envs][action_size] a torch.randn draw or NULL: u += u_randn * u_noise (environment.py:711-720; the
+ *            caller draws it with the reference's own call, so both consume the generator alike)
+ *  c_randn d: [n_envs][n_comm] or NULL: c += c_randn * c_noise (environment.py:745-754)
+ *  c_out  d: [n_envs][n_comm] the new agent.action.c (never clamped: with clamp_action the reference clamps a copy it then
+ *            does not use, environment.py:640-645 vs 737-743)
+ *  flags: bit 0 NaN, bit 1 |u| > u_range, bit 3 a communication action outside [0, 1] (environment.py:738-740) */
+typedef struct vmasb200_action {
+  const float* action;
+  int64_t stride_env, stride_k;
+  int32_t action_size, comm_col0, n_comm, clamp;
+  const float* u_range;       /* h: [action_size] */
+  const float* u_multiplier;  /* h: [action_size] */
+  const float* u_randn;
+  const float* c_randn;
+  double u_noise, c_noise;    /* agent.u_noise / agent.c_noise (Python floats) */
+  float* u_out;
+  float* c_out;
+  int32_t* flags;
+} vmasb200_action;
+int vmasb200_set_action_ex(const vmasb200_action* a, int64_t n_envs, void* stream);
+
 /* ---- the same for DISCRETE physical actions without communication / noise (environment.py:660-710):
  * a flat action (the index into the cartesian product of the agent's action spaces, one column) or a multi-discrete
  * one (one column per component) becomes u[k] = (a_k / (nvec[k] - 1)) * 2 u_range[k] - u_range[k], with the

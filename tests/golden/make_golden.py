@@ -64,6 +64,7 @@ CONFIGS = {
     "flocking": dict(scenario="flocking", kw=dict(), n_envs=16, steps=40),        # LIDAR with static sphere obstacles
     "discovery": dict(scenario="discovery", kw=dict(), n_envs=16, steps=40),
     "dropout": dict(scenario="dropout", kw=dict(), n_envs=16, steps=40),
+    "simple_reference": dict(scenario="simple_reference", kw=dict(), n_envs=16, steps=40),  # dim_c = 10: communication actions / state
 }
 
 

@@ -89,3 +89,60 @@ def test_dropin_discrete_actions_in_the_reference_environment(scenario, multi):
             env.step(bad)
     finally:
         dropin.disable(env)
+
+
+@pytest.mark.parametrize("clamp", [True, False])
+def test_comm_actions_and_action_noise_in_the_environment(clamp):
+    """Environment._set_action with communication columns and u / c noise (environment.py:633-645, 711-754) through
+    vmasb200_set_action_ex: the patched env draws the noise with the reference's own torch.randn calls, so with the same
+    generator state action.u, action.c and - after World.step - state.c (core.py:2909-2912) equal the reference's BIT for
+    bit; and the reference's assertions (NaN, physical range, comm range) still fire."""
+    import os
+    import sys
+
+    import torch
+
+    ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    ref_dir = os.path.join(ROOT, "oracle", "_ref")
+    if not os.path.isdir(os.path.join(ref_dir, "vmas")):
+        pytest.skip("oracle/_ref (the reference install) did not travel to this box")
+    for p in (ref_dir, os.path.join(ROOT, "oracle", "gym_stub")):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    import vmas
+
+    from vectorizedmultiagentsimulator_b200 import dropin
+
+    n = 300
+    mk = lambda: vmas.make_env("simple_reference", num_envs=n, device="cuda", seed=0, continuous_actions=True, clamp_actions=clamp)
+    ref, env = mk(), mk()
+    for e in (ref, env):
+        for a in e.agents:
+            a.action._u_noise = 0.05
+            a._c_noise = 0.02
+    b = dropin.enable(env, strict=True)  # strict: a call that is not covered would raise, not fall back
+    torch.manual_seed(5)
+    for t in range(6):
+        acts = []
+        for a in ref.agents:
+            phys = torch.rand(n, a.action_size, device="cuda") * 2 * a.u_range - a.u_range
+            comm = torch.rand(n, ref.world.dim_c, device="cuda")
+            if clamp and t == 2:  # out-of-range physical values the clamp must bring back (comm actions are never clamped)
+                phys[:7] *= 3.0
+            acts.append(torch.cat([phys, comm], -1))
+        st = torch.cuda.get_rng_state()
+        torch.manual_seed(100 + t)
+        ref.step([x.clone() for x in acts])
+        torch.cuda.set_rng_state(st)
+        torch.manual_seed(100 + t)
+        env.step([x.clone() for x in acts])
+        for a1, a2 in zip(ref.agents, env.agents):
+            assert torch.equal(a1.action.u, a2.action.u), f"action.u of {a1.name} at step {t}"
+            assert torch.equal(a1.action.c, a2.action.c), f"action.c of {a1.name} at step {t}"
+            assert torch.equal(a1.state.c, a2.state.c), f"state.c of {a1.name} at step {t}"
+    assert b.n_fused_actions == 6 * len(env.agents) and b.n_fallback["set_action"] == 0
+    if True:
+        bad = [torch.cat([torch.zeros(n, a.action_size, device="cuda"), torch.full((n, ref.world.dim_c), 0.5, device="cuda")], -1) for a in env.agents]
+        bad[1][3, 5] = 1.5
+        with pytest.raises(AssertionError, match="Comm actions"):
+            env.step(bad)

@@ -26,6 +26,7 @@ CASES = [
     ("flocking", dict(), 1),
     ("balance", dict(), 1),
     ("give_way", dict(), 1),
+    ("simple_reference", dict(), 1),  # world.dim_c = 10: communication actions (environment.py:721-754) and state (core.py:2909-2912)
 ]
 
 
@@ -108,6 +109,8 @@ def test_environment_step_matches_reference(scenario, kw, substeps):
                 twin.reset_at(5)
             torch.manual_seed(12)
         acts = [torch.rand(n, a.action_size, device="cuda") * 2 * a.u_range - a.u_range for a in ref.agents]
+        if ref.world.dim_c > 0:  # communication columns in [0, 1] behind the physical ones (environment.py:545-557)
+            acts = [torch.cat([x, torch.rand(n, ref.world.dim_c, device="cuda")], -1) if not a.silent else x for x, a in zip(acts, ref.agents)]
         o1, r1, d1, _ = ref.step([a.clone() for a in acts])
         o2, r2, d2, _ = env.step([a.clone() for a in acts])
         s1, s2 = _state(ref), _state(env)
@@ -126,7 +129,13 @@ def test_environment_step_matches_reference(scenario, kw, substeps):
         assert float((s1[..., 2:4] - s2[..., 2:4]).abs().max()) <= vel_tol, f"{scenario}: vel drift at step {t}"
         assert torch.equal(d1, d2), f"{scenario}: done flags differ at step {t}"
         assert torch.allclose(_flat(r1), _flat(r2), rtol=1e-3, atol=10 * vel_tol), f"{scenario}: reward at step {t}"
+        if ref.world.dim_c > 0:  # _update_comm_state (core.py:2909-2912): state.c = action.c of every non-silent agent
+            for a1, a2 in zip(ref.world.agents, env.world.agents):
+                assert a1.state.c is not None and torch.equal(a1.state.c, a2.state.c), f"{scenario}: comm state of {a1.name} at step {t}"
     assert b.n_steps == steps
+    assert b.n_fallback["set_action"] == 0, "an action took the reference's torch _set_action"
+    if ref.world.dim_c > 0:
+        assert b.n_fused_actions >= steps * len(env.agents)
     dropin.disable(env)
 
 
@@ -306,3 +315,68 @@ def test_set_action_matches_reference_and_keeps_its_assertions():
         env.step(acts)  # and it recovers
         dropin.disable(env)
         assert "_set_action" not in env.__dict__
+
+
+@pytest.mark.parametrize("scenario,kw", [("flocking", dict()), ("navigation", dict(n_agents=4)), ("pollock", dict(lidar=True))])
+def test_scalar_cast_ray_matches_reference(scenario, kw):
+    """World.cast_ray (core.py:1627-1659, the scalar twin Lidar.measure(vectorized=False) uses) through the same launch
+    with one ray per env, against the reference's own scalar implementation on the same CUDA state; and
+    Lidar.measure(vectorized=False) of the patched world against the reference's."""
+    import torch
+
+    from vectorizedmultiagentsimulator_b200 import dropin
+
+    vmas = _vmas()
+    n = 200
+    ref, env = _make(vmas, scenario, kw, n, 1), _make(vmas, scenario, kw, n, 1)
+    b = dropin.enable(env, strict=True)
+    torch.manual_seed(3)
+    for _ in range(4):
+        acts = [torch.rand(n, a.action_size, device="cuda") * 2 * a.u_range - a.u_range for a in ref.agents]
+        ref.step([a.clone() for a in acts]); env.step([a.clone() for a in acts])
+    for er, ee in zip(ref.world.entities, env.world.entities):  # identical state on both sides
+        for f in ("pos", "vel", "rot", "ang_vel"):
+            setattr(ee.state, f, getattr(er.state, f).clone())
+    checked = 0
+    for ar, ae in zip(ref.agents, env.agents):
+        for sr, se in zip(ar.sensors or [], ae.sensors or []):
+            for k in range(3):
+                ang = torch.rand(n, device="cuda") * 6.2831853
+                d_ref = ref.world.cast_ray(ar, ang, sr._max_range, entity_filter=sr.entity_filter)
+                d_got = env.world.cast_ray(ae, ang.clone(), se._max_range, entity_filter=se.entity_filter)
+                assert d_got.shape == d_ref.shape == (n,)
+                bad = (d_got - d_ref).abs() > 1e-6 + 1e-5 * d_ref.abs()
+                assert int(bad.sum()) == 0 and float((d_got - d_ref).abs().max()) <= 1e-5, f"{scenario} {ar.name}: {float((d_got - d_ref).abs().max()):.3e}"
+                checked += 1
+            m_ref, m_got = sr.measure(vectorized=False), se.measure(vectorized=False)
+            assert torch.allclose(m_got, m_ref, rtol=1e-5, atol=1e-5), f"{scenario} {ar.name}: Lidar.measure(vectorized=False)"
+    assert checked > 0 and b.n_fallback["cast_rays"] == 0
+    dropin.disable(env)
+    assert "cast_ray" not in env.world.__dict__
+
+
+def test_fallbacks_warn_once_and_strict_raises():
+    """A secondary call the library does not cover takes the reference's torch code with ONE warning and a count;
+    under strict=True it raises.  (World.step itself never falls back.)"""
+    import warnings
+
+    import torch
+
+    from vectorizedmultiagentsimulator_b200 import dropin
+    from vectorizedmultiagentsimulator_b200._lib import VmasB200Error
+
+    vmas = _vmas()
+    n = 32
+    env = _make(vmas, "navigation", dict(n_agents=2), n, 1)
+    b = dropin.enable(env)
+    acts = [torch.zeros(n, a.action_size, device="cuda", dtype=torch.float64) for a in env.agents]  # fp64 actions: not covered
+    with warnings.catch_warnings(record=True) as w:
+        warnings.simplefilter("always")
+        env.step(acts)
+        env.step(acts)
+    msgs = [str(x.message) for x in w if "vmas-b200" in str(x.message)]
+    assert len(msgs) == 1 and "set_action" in msgs[0], msgs
+    assert b.n_fallback["set_action"] == 4 and b.n_steps == 2
+    b.strict = True
+    with pytest.raises(VmasB200Error, match="strict"):
+        env.step(acts)

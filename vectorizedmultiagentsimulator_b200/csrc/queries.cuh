@@ -138,6 +138,49 @@ __global__ void __launch_bounds__(256) set_action_kernel(const float* __restrict
   if (bad && (threadIdx.x & 31) == 0) atomicOr(flags, bad);
 }
 
+// Environment._set_action, continuous actions WITH communication and / or action noise (environment.py:615-668, 711-754):
+// one thread per (env, column) over the physical columns and the communication columns.
+//   physical column k: NaN check, clamp to +-u_range (clamp_action), range assertion, u = x * u_multiplier, then
+//     u += randn * u_noise (the caller's torch.randn tensor: the same draw the reference makes, environment.py:712-720);
+//   communication column c (source column comm_col0 + c: action_size when the reference has clamped and re-concatenated
+//     the action, world.dim_p otherwise - environment.py:633-645, 742-743): NaN check, assertion 0 <= c <= 1 (flag bit 3;
+//     never clamped, see below), c += randn * c_noise.
+struct ActExParams { float range[8], mult[8]; int k_n, comm_col0, n_comm, clamp; float u_noise, c_noise; };
+__global__ void __launch_bounds__(256) set_action_ex_kernel(const float* __restrict__ action, long long se, long long sk,
+                                                            const __grid_constant__ ActExParams ap,
+                                                            const float* __restrict__ u_randn, const float* __restrict__ c_randn,
+                                                            float* __restrict__ u_out, float* __restrict__ c_out,
+                                                            int* __restrict__ flags, long long n) {
+  const long long gid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const int cols = ap.k_n + ap.n_comm;
+  int bad = 0;
+  if (gid < n * cols) {
+    const long long i = gid / cols;
+    const int k = (int)(gid - i * cols);
+    if (k < ap.k_n) {
+      float x = action[i * se + k * sk];
+      const float r = ap.range[k];
+      if (x != x) bad |= 1;
+      if (ap.clamp && x == x) x = fminf(fmaxf(x, -r), r);
+      if (fabsf(x) > r) bad |= 2;
+      float u = x * ap.mult[k];
+      if (u_randn) u = u + u_randn[i * ap.k_n + k] * ap.u_noise;
+      u_out[i * ap.k_n + k] = u;
+    } else {
+      const int c = k - ap.k_n;
+      float x = action[i * se + (ap.comm_col0 + c) * sk];
+      if (x != x) bad |= 1;
+      // (with clamp_action the reference concatenates comm.clamp(0, 1) into `action`, but keeps asserting on and storing
+      //  the UNCLAMPED slice it took before, environment.py:640-645, 737-743: communication actions are never clamped)
+      if (x > 1.f || x < 0.f) bad |= 8;                                       // "Comm actions are out of range [0,1]"
+      if (c_randn) x = x + c_randn[i * ap.n_comm + c] * ap.c_noise;
+      c_out[i * ap.n_comm + c] = x;
+    }
+  }
+  bad = __reduce_or_sync(0xffffffffu, bad);
+  if (bad && (threadIdx.x & 31) == 0) atomicOr(flags, bad);
+}
+
 // Environment._set_action, discrete physical actions (environment.py:660-707): one thread per (env, component).
 //   flat action (one column): component k = (flat mod prod(nvec[k:])) div prod(nvec[k+1:]) with Python's floor
 //   semantics (component 0 is not reduced: an action beyond the product fails the range check, as in the reference);

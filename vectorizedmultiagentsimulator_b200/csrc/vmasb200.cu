@@ -636,6 +636,23 @@ int vmasb200_set_action(const float* action, int64_t stride_env, int64_t stride_
   return VMASB200_OK;
 }
 
+int vmasb200_set_action_ex(const vmasb200_action* a, int64_t n, void* stream) {
+  if (!a || !a->action || !a->u_range || !a->u_multiplier || !a->u_out || !a->flags || n < 0 || a->action_size < 1 ||
+      a->action_size > 8 || a->n_comm < 0 || a->n_comm > 64 || a->comm_col0 < 0 || (a->n_comm && !a->c_out)) {
+    set_error("set_action_ex: bad argument (1 <= action_size <= 8, 0 <= n_comm <= 64, c_out when n_comm > 0)"); return VMASB200_ERR_INVALID;
+  }
+  if (n == 0) return VMASB200_OK;
+  ActExParams ap{};
+  for (int k = 0; k < a->action_size; ++k) { ap.range[k] = a->u_range[k]; ap.mult[k] = a->u_multiplier[k]; }
+  ap.k_n = a->action_size; ap.comm_col0 = a->comm_col0; ap.n_comm = a->n_comm; ap.clamp = a->clamp;
+  ap.u_noise = (float)a->u_noise; ap.c_noise = (float)a->c_noise;
+  const long long total = (long long)n * (a->action_size + a->n_comm);
+  set_action_ex_kernel<<<(unsigned)((total + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      a->action, a->stride_env, a->stride_k, ap, a->u_randn, a->n_comm ? a->c_randn : nullptr, a->u_out, a->c_out, a->flags, n);
+  VB_CUDA(cudaGetLastError());
+  return VMASB200_OK;
+}
+
 int vmasb200_set_action_discrete(const void* action, int32_t action_dtype, int64_t stride_env, int64_t stride_k,
                                  int32_t action_size, int32_t multidiscrete, const int32_t* nvec, const float* u_range,
                                  const float* u_multiplier, float* u_out, int32_t* flags, int64_t n, void* stream) {

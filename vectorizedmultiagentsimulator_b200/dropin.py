@@ -43,6 +43,13 @@ def _same_view(t, v) -> bool:
                       and t.dtype == v.dtype)
 
 
+class CAction(C.Structure):  # vmasb200_action (include/vmasb200.h)
+    _fields_ = [("action", C.c_void_p), ("stride_env", C.c_int64), ("stride_k", C.c_int64), ("action_size", C.c_int32),
+                ("comm_col0", C.c_int32), ("n_comm", C.c_int32), ("clamp", C.c_int32), ("u_range", C.c_void_p),
+                ("u_multiplier", C.c_void_p), ("u_randn", C.c_void_p), ("c_randn", C.c_void_p), ("u_noise", C.c_double),
+                ("c_noise", C.c_double), ("u_out", C.c_void_p), ("c_out", C.c_void_p), ("flags", C.c_void_p)]
+
+
 class WorldBinding:
     """Plan + device buffers of one enabled World."""
 
@@ -73,8 +80,23 @@ class WorldBinding:
         self.lidar_valid = False
         self.n_steps = 0
         self.n_copies = 0
+        self.n_fallback = {"set_action": 0, "cast_rays": 0}  # calls that took the reference's torch code instead (see `strict`)
+        self.n_fused_actions = 0
+        self.strict = False  # True: such a call raises instead
         self.record_masks = False  # True: every step also leaves World.collides' verdicts per (substep, pair) in self.masks
         self.masks = None
+
+    def _fallback(self, kind: str, why: str):
+        """A secondary call (never World.step itself) that this library does not cover takes the reference's own torch
+        code.  Counted in n_fallback; a one-time warning says so; with strict=True it is an error instead."""
+        if self.strict:
+            raise _lib.VmasB200Error(f"vmas-b200 (strict): {kind} is not covered here: {why}")
+        if self.n_fallback.get(kind, 0) == 0:
+            import warnings
+
+            warnings.warn(f"vmas-b200: {kind} takes the reference's torch code: {why} (binding.strict = True makes this an error)",
+                          RuntimeWarning, stacklevel=3)
+        self.n_fallback[kind] = self.n_fallback.get(kind, 0) + 1
 
     # ------------------------------------------------------------------ plan (re)build
     def refresh(self):
@@ -296,7 +318,8 @@ class WorldBinding:
         pl = self.plan
         me = index[id(entity)]
         if any(pl.dyn_slot[i] < 0 and pl.stat_slot[i] < 0 for i in targets + [me]) or len(targets) > 64:
-            return self.orig_cast_rays(entity, angles, max_range, entity_filter)  # entity the step never reads
+            self._fallback("cast_rays", "more than 64 targets, or an entity the step never reads (no rows in the plan's buffers)")
+            return self.orig_cast_rays(entity, angles, max_range, entity_filter)
         self.sync_in()
         ang = angles if (angles.dtype == torch.float32 and angles.stride(1) == 1) else angles.to(torch.float32).contiguous()
         out = torch.empty(ang.shape[0], ang.shape[1], device=self.device)
@@ -315,14 +338,20 @@ class WorldBinding:
         act = getattr(agent, "action", None)
         noise = getattr(act, "u_noise", 0)
         noisy = any(v > 0 for v in noise) if isinstance(noise, (list, tuple)) else noise > 0
-        ok = (getattr(env, "continuous_actions", False) and torch.is_tensor(action) and action.is_cuda
-              and action.dtype == torch.float32 and action.dim() == 2 and action.shape[0] == self.n
-              and (self.world.dim_c == 0 or agent.silent) and act is not None and not noisy
-              and 1 <= agent.action_size <= 8 and action.shape[1] == agent.action_size
-              and not (getattr(env, "grad_enabled", False) and action.requires_grad))
+        comm = self.world.dim_c > 0 and not agent.silent
+        base = (getattr(env, "continuous_actions", False) and torch.is_tensor(action) and action.is_cuda
+                and action.dtype == torch.float32 and action.dim() == 2 and action.shape[0] == self.n
+                and act is not None and 1 <= agent.action_size <= 8
+                and not (getattr(env, "grad_enabled", False) and action.requires_grad))
+        if base and (comm or noisy) and not isinstance(noise, (list, tuple)):
+            if self._set_action_ex(env, action, agent, act, comm):
+                return None
+        ok = base and not comm and not noisy and action.shape[1] == agent.action_size
         if not ok:
             if self._set_action_discrete(env, action, agent, act, noisy):
                 return None
+            self._fallback("set_action", f"agent {getattr(agent, 'name', '?')}: not a CUDA fp32 / int action tensor of the agent's "
+                                         "size, autograd in play, per-component noise, or discrete actions with communication")
             return self.orig_set_action(action, agent)
         key = (id(agent), repr(act.u_range), repr(act.u_multiplier))
         c = self._act_consts.get(id(agent))
@@ -340,6 +369,46 @@ class WorldBinding:
             _lib.raw_stream(torch, self.device)), "vmasb200_set_action")
         act.u = u
         self._act_pending = True
+
+    def _set_action_ex(self, env, action, agent, act, comm):
+        """Continuous actions with communication columns and / or action noise (environment.py:633-645, 711-754): one
+        launch (vmasb200_set_action_ex).  The noise is drawn here with the reference's own torch.randn calls, in its
+        order (u first, then c), so the generator advances exactly as in the reference."""
+        torch = self.torch
+        k, dim_c = agent.action_size, (self.world.dim_c if comm else 0)
+        clamp = bool(getattr(env, "clamp_action", False))
+        col0 = k if clamp else self.world.dim_p
+        n_comm = (dim_c if clamp else action.shape[1] - col0) if comm else 0
+        if action.shape[1] != k + dim_c or n_comm < 0 or n_comm > 64:
+            return False
+        key = (id(agent), repr(act.u_range), repr(act.u_multiplier))
+        c = self._act_consts.get(id(agent))
+        if c is None or c[0] != key:
+            rng = (C.c_float * k)(*[float(v) for v in act.u_range_tensor.tolist()])
+            mul = (C.c_float * k)(*[float(v) for v in act.u_multiplier_tensor.tolist()])
+            c = self._act_consts[id(agent)] = (key, rng, mul)
+        if self._act_flags is None:
+            self._act_flags = torch.zeros(1, dtype=torch.int32, device=self.device)
+        u_noise, c_noise = float(getattr(act, "u_noise", 0) or 0), float(getattr(agent, "c_noise", 0) or 0)
+        u = torch.empty(self.n, k, device=self.device)
+        u_randn = torch.randn(self.n, k, device=self.device, dtype=torch.float32) if u_noise > 0 else None
+        cc = torch.empty(self.n, n_comm, device=self.device) if n_comm else None
+        c_randn = torch.randn(self.n, n_comm, device=self.device, dtype=torch.float32) if (n_comm and c_noise > 0) else None
+        a = CAction()
+        a.action, a.stride_env, a.stride_k = action.data_ptr(), action.stride(0), action.stride(1)
+        a.action_size, a.comm_col0, a.n_comm, a.clamp = k, col0, n_comm, int(clamp)
+        a.u_range, a.u_multiplier = C.cast(c[1], C.c_void_p), C.cast(c[2], C.c_void_p)
+        a.u_randn = u_randn.data_ptr() if u_randn is not None else None
+        a.c_randn = c_randn.data_ptr() if c_randn is not None else None
+        a.u_noise, a.c_noise = u_noise, c_noise
+        a.u_out, a.c_out, a.flags = u.data_ptr(), (cc.data_ptr() if cc is not None else None), self._act_flags.data_ptr()
+        _lib.check(_lib.lib().vmasb200_set_action_ex(C.byref(a), self.n, _lib.raw_stream(torch, self.device)), "vmasb200_set_action_ex")
+        act.u = u
+        if cc is not None:
+            act.c = cc
+        self._act_pending = True
+        self.n_fused_actions += 1
+        return True
 
     def _set_action_discrete(self, env, action, agent, act, noisy):
         """Discrete physical actions (flat or multi-discrete, int64 / int32) without communication / noise
@@ -386,6 +455,7 @@ class WorldBinding:
             assert not bad & 1, "an action holds NaN"
             assert not bad & 2, "Physical actions of an agent are out of its range"
             assert not bad & 4, "Discrete physical actions are out of bounds"
+            assert not bad & 8, "Comm actions are out of range [0,1]"
 
     # ------------------------------------------------------------------ distance queries of reward code
     def _poses(self, *entities):
@@ -443,7 +513,7 @@ def _joints_in_order(world, ents):
     return out
 
 
-def enable(world_or_env, exact: bool = False, static_io: bool = False, hooks: bool = False) -> WorldBinding:
+def enable(world_or_env, exact: bool = False, static_io: bool = False, hooks: bool = False, strict: bool = False) -> WorldBinding:
     """Routes ``world.step`` / ``world.cast_rays`` / its Lidars' ``measure`` / the distance queries of ONE world through
     libvmasb200.  ``exact=True`` takes the per-substep exact path instead of the verified speculative single launch.
     ``static_io=True`` (opt-in): the step works IN PLACE on persistent buffers instead of binding fresh output tensors
@@ -451,22 +521,38 @@ def enable(world_or_env, exact: bool = False, static_io: bool = False, hooks: bo
     of user code around the step needs) - at the price that a state tensor a caller kept from an earlier step changes
     with the world instead of staying a snapshot, unlike the reference (core.py:2866-2907 rebinds fresh tensors).
     ``hooks=True`` (opt-in, needs an Environment): the scenario's reward / observation / done take the fused launches of
-    ``hooks.py`` when the scenario has them (navigation, transport); ``binding.hooks`` is None otherwise."""
+    ``hooks.py`` when the scenario has them (navigation, transport); ``binding.hooks`` is None otherwise.
+    ``strict=True``: a secondary call this library does not cover (an action layout, a cast_rays over entities outside
+    the plan, a hook on shapes it does not know) raises instead of taking the reference's torch code with a one-time
+    warning.  ``World.step`` itself never falls back: an unsupported world is an error at plan build."""
     world = getattr(world_or_env, "world", world_or_env)
     if getattr(world, "_vmasb200", None) is not None:
         b = world._vmasb200  # already enabled: opt-ins can still be switched on
         b.static_io = b.static_io or bool(static_io)
+        b.strict = b.strict or bool(strict)
         if hooks and b.hooks is None and getattr(b, "_env", None) is not None and b._env is world_or_env:
             b.hooks = _hooks.install(world_or_env, b)
         return b
     _lib.lib()  # fail loudly when the extension is missing
     b = WorldBinding(world, exact=exact)
+    b.strict = bool(strict)
     b.refresh()
     world._vmasb200 = b
     world.step = types.MethodType(lambda self: b.step(), world)
     world.cast_rays = types.MethodType(
         lambda self, entity, angles, max_range, entity_filter=lambda _: False: b.cast_rays(entity, angles, max_range, entity_filter),
         world)
+    # the scalar twin World.cast_ray (core.py:1627-1659; Lidar.measure(vectorized=False), sensors.py:104-113): same arithmetic,
+    # one ray per env - the same launch with n_rays = 1
+    b.orig_cast_ray = world.cast_ray
+
+    def cast_ray(self, entity, angles, max_range, entity_filter=lambda _: False):
+        pos = entity.state.pos
+        assert pos.ndim == 2 and angles.ndim == 1  # core.py:1636-1637
+        assert pos.shape[0] == angles.shape[0]
+        return b.cast_rays(entity, angles.unsqueeze(-1), max_range, entity_filter)[:, 0]
+
+    world.cast_ray = types.MethodType(cast_ray, world)
     b.orig_get_distance, b.orig_is_overlapping = world.get_distance, world.is_overlapping
     b.orig_get_distance_from_point = world.get_distance_from_point
     world.get_distance = types.MethodType(lambda self, a, c, env_index=None: b.get_distance(a, c, env_index), world)
@@ -503,7 +589,7 @@ def disable(world_or_env) -> None:
     b = getattr(world, "_vmasb200", None)
     if b is None:
         return
-    for name in ("step", "cast_rays", "reset", "get_distance", "is_overlapping", "get_distance_from_point"):
+    for name in ("step", "cast_rays", "cast_ray", "reset", "get_distance", "is_overlapping", "get_distance_from_point"):
         if name in world.__dict__:
             del world.__dict__[name]
     for sensor, _ in b._orig_measures:

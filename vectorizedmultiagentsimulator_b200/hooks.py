@@ -213,6 +213,13 @@ class ScenarioHooks:
         self.orig = {k: getattr(self.scenario, k) for k in self.NAMES}
         self.attach()
 
+    def _not_covered(self, kind):
+        """The fused hook cannot take this call (tensor layouts / shapes it does not know, autograd): the reference's
+        torch hook answers; counted, a one-time warning, an error under binding.strict (dropin.WorldBinding._fallback)."""
+        self.n_fallback[kind] += 1
+        self.b._fallback("hook " + kind, f"{type(self.scenario).__module__}: operand tensors are not CUDA fp32 of the expected "
+                                          "shapes, or autograd is in play")
+
     def attach(self):
         sc = self.scenario
         sc.reward = lambda agent: self.reward(agent)
@@ -257,7 +264,10 @@ class ScenarioHooks:
             if self._obs is not None:
                 self.n_fused["observation"] += 1
         if self._obs is None:
-            self.n_fallback["observation"] += 1
+            if key is None:
+                self.n_fallback["observation"] += 1  # between a reset and the next step: the reference's code answers, by design
+            else:
+                self._not_covered("observation")
             return self.orig["observation"](agent)
         return self._obs[self._agent_index(agent)]
 
@@ -332,7 +342,7 @@ class NavigationHooks(ScenarioHooks):
             return self.orig["reward"](agent)
         self._rew_ok = self._reward_usable()
         if not self._rew_ok:
-            self.n_fallback["reward"] += 1
+            self._not_covered("reward")
             self._done = None
             return self.orig["reward"](agent)
         n, A, cn, inplace = self.n, len(agents), self.cn, self.b.static_io
@@ -437,7 +447,7 @@ class TransportHooks(ScenarioHooks):
             return sc.rew if self._rew_ok else self.orig["reward"](agent)
         self._rew_ok = self._reward_usable()
         if not self._rew_ok:
-            self.n_fallback["reward"] += 1
+            self._not_covered("reward")
             self._done = None
             return self.orig["reward"](agent)
         n, ct, pk, inplace = self.n, self.ct, sc.packages, self.b.static_io
@@ -516,7 +526,7 @@ class SimpleSpreadHooks(ScenarioHooks):
             return sc.rew if self._rew_ok else self.orig["reward"](agent)
         self._rew_ok = self._reward_usable()
         if not self._rew_ok:
-            self.n_fallback["reward"] += 1
+            self._not_covered("reward")
             return self.orig["reward"](agent)
         cs, lms = self.cs, self.world.landmarks
         cs.n_agents, cs.n_landmarks = len(agents), len(lms)
@@ -608,7 +618,7 @@ class JointPassageHooks(ScenarioHooks):
             return sc.rew if self._rew_ok else self.orig["reward"](agent)
         self._rew_ok = self._reward_usable()
         if not self._rew_ok:
-            self.n_fallback["reward"] += 1
+            self._not_covered("reward")
             self._done = None
             return self.orig["reward"](agent)
         n, cj, inplace = self.n, self.cj, self.b.static_io
@@ -733,7 +743,7 @@ class FootballHooks(ScenarioHooks):
             return self.orig["reward"](agent)
         self._rew_ok = agent is not None and self._reward_usable()
         if not self._rew_ok:
-            self.n_fallback["reward"] += 1
+            self._not_covered("reward")
             self._rewards = None
             self._done = None
             return self.orig["reward"](agent)
