@@ -28,7 +28,7 @@ def parse():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=10)
-    ap.add_argument("--impl", default="b200", choices=["b200", "reference", "reference-cuda", "dropin", "dropin-hooks", "dropin-graph", "queries"],
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference", "reference-cuda", "dropin", "dropin-hooks", "dropin-graph", "queries", "reset"],
                     help="b200: the CUDA step through the C ABI (the driver's arm); reference: the reference's CPU path; "
                          "reference-cuda / dropin: the reference Environment on this GPU with its own torch World.step, "
                          "or with vectorizedmultiagentsimulator_b200.dropin enabled (reported comparison, needs oracle/_ref)")
@@ -751,6 +751,54 @@ def run_env_graph(args, rank):
     print(json.dumps(line), flush=True)
 
 
+def run_reset(args, rank):
+    """Environment.reset() and reset_at(i) followed by one step (which pays for the re-packing of the state
+    tensors a reset rebinds), wall clock with a synchronize on both sides: the reference, the drop-in with the reference's
+    reset path, and the drop-in with fused_reset=True.  One JSON line."""
+    if rank != 0:
+        return
+    import torch
+
+    from vectorizedmultiagentsimulator_b200 import dropin
+    from vectorizedmultiagentsimulator_b200.workload import Workload
+
+    vmas = import_vmas()
+    fx = Workload(args.scenario, 1, seed=0)
+    n, K = args.num_envs, max(3, min(args.steps, 20))
+
+    def arm(mode):
+        env = vmas.make_env(fx.meta["scenario"], num_envs=n, device="cuda", seed=0, continuous_actions=True, **fx.meta["kwargs"])
+        b = None
+        if mode != "reference":
+            b = dropin.enable(env, fused_reset=(mode == "fused"))
+        acts = [torch.zeros(n, a.action_size, device="cuda") for a in env.agents]
+        env.step(acts)
+
+        def timed(fn):
+            fn(); fn()
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            for _ in range(K):
+                fn()
+            torch.cuda.synchronize()
+            return (time.perf_counter() - t0) / K * 1e3
+
+        full = timed(lambda: (env.reset(), env.step(acts)))
+        one = timed(lambda: (env.reset_at(7), env.step(acts)))
+        step = timed(lambda: env.step(acts))
+        out = {"reset_plus_step_ms": full, "reset_at_plus_step_ms": one, "step_ms": step,
+               "reset_ms": full - step, "reset_at_ms": one - step}
+        if b is not None:
+            out["state_fields_repacked"] = b.n_copies
+        return out
+
+    line = {"impl": "reset", "metric": "reset_ms", "unit": "ms", "n_gpus": 1, "steps": K, "higher_is_better": False, "data": "synthetic",
+            "config": {"workload": f"{args.scenario} num_envs={n}: Environment.reset() / reset_at(7), each followed by one step"},
+            "reference": arm("reference"), "dropin": arm("dropin"), "dropin_fused_reset": arm("fused")}
+    line["value"] = line["dropin_fused_reset"]["reset_ms"]
+    print(json.dumps(line), flush=True)
+
+
 def run_queries(args, rank):
     """World.get_distance on device-resident poses, one launch per call, per shape combination; the
     reference's torch implementation on the same tensors beside it when oracle/_ref travelled.  One JSON line."""
@@ -829,6 +877,8 @@ def main():
         run_env_cuda(args, rank)
     elif args.impl == "queries":
         run_queries(args, rank)
+    elif args.impl == "reset":
+        run_reset(args, rank)
     elif args.impl == "reference":
         run_reference(args, rank, world)
     else:

@@ -348,6 +348,20 @@ int vmasb200_set_action_discrete(const void* action, int32_t action_dtype, int64
                                  int32_t action_size, int32_t multidiscrete, const int32_t* nvec, const float* u_range,
                                  const float* u_multiplier, float* u_out, int32_t* flags, int64_t n_envs, void* stream);
 
+/* ---- reset path
+ * vmasb200_reset_rows: World.reset(env_index) (core.py:1178-1180 -> EntityState._reset, core.py:285-295) IN PLACE on a
+ * plan's SoA buffer: rows [row0, row0 + n_rows) of buf d: [rows][ld] are zeroed for env `env_index`, for every env
+ * (env_index < 0, mask NULL) or for the envs whose byte of mask d: [n_envs] is non-zero (env_index < 0).  The state
+ * tensors of the reference stay the views they were: no re-pack at the next step.
+ * vmasb200_spawn_select: one iteration of the rejection loop of ScenarioUtils.find_random_pos_for_entity
+ * (utils.py:285-319): overlaps = (torch.cdist(occupied [B][K][2], pos [B][1][2]) < min_dist).any(K);
+ * pos[overlaps] = proposed[overlaps]; *flag |= overlaps.any() (the loop's exit test, read by the caller: the reference
+ * synchronises on it too).  The proposals are the caller's torch `uniform_` draws, so placement is bit-identical. */
+int vmasb200_reset_rows(float* buf, int32_t row0, int32_t n_rows, int64_t ld, int64_t n_envs, int64_t env_index,
+                        const uint8_t* mask, void* stream);
+int vmasb200_spawn_select(float* pos, const float* proposed, const float* occupied, int32_t n_occupied, float min_dist,
+                          int32_t* flag, int64_t batch, void* stream);
+
 /* ---- scenario hooks: what Environment._get_from_scenario (environment.py:253-308) asks of a scenario
  * after every World.step - observation / reward / done / info - as one or two launches per step instead of tens to
  * hundreds of small torch ops with host synchronisations (World.collides, boolean-mask indexing).  All tensors are read

@@ -17,7 +17,7 @@ EXPORTS = [
     "vmasb200_get_distance_from_point", "vmasb200_set_action", "vmasb200_set_action_discrete", "vmasb200_gather_obs",
     "vmasb200_navigation_reward",
     "vmasb200_transport_reward", "vmasb200_simple_spread_reward", "vmasb200_jit_enable", "vmasb200_plan_jit",
-    "vmasb200_joint_passage_reward", "vmasb200_football_reward", "vmasb200_navigation_reward_static", "vmasb200_plan_trig_entities", "vmasb200_set_action_ex",
+    "vmasb200_joint_passage_reward", "vmasb200_football_reward", "vmasb200_navigation_reward_static", "vmasb200_plan_trig_entities", "vmasb200_set_action_ex", "vmasb200_reset_rows", "vmasb200_spawn_select",
 ]
 
 _LIB = None
@@ -73,6 +73,8 @@ def lib():
     L.vmasb200_set_action_discrete.argtypes = [vp, C.c_int32, C.c_int64, C.c_int64, C.c_int32, C.c_int32, vp, vp, vp, vp, vp,
                                                C.c_int64, vp]
     L.vmasb200_set_action_ex.argtypes = [vp, C.c_int64, vp]
+    L.vmasb200_reset_rows.argtypes = [vp, C.c_int32, C.c_int32, C.c_int64, C.c_int64, C.c_int64, vp, vp]
+    L.vmasb200_spawn_select.argtypes = [vp, vp, vp, C.c_int32, C.c_float, vp, C.c_int64, vp]
     L.vmasb200_gather_obs.argtypes = [vp, C.c_int32, vp, vp, C.c_int32, C.c_int64, vp]
     L.vmasb200_navigation_reward.argtypes = [vp, C.c_int64, vp]
     L.vmasb200_navigation_reward_static.argtypes = [vp, C.c_int64, vp]

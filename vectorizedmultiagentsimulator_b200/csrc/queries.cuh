@@ -181,6 +181,43 @@ __global__ void __launch_bounds__(256) set_action_ex_kernel(const float* __restr
   if (bad && (threadIdx.x & 31) == 0) atomicOr(flags, bad);
 }
 
+// ---- reset path
+// World.reset(env_index) (core.py:1178-1180 -> EntityState._reset, core.py:285-295) on the SoA buffers, IN PLACE: the rows
+// [row0, row0 + n_rows) of one buffer are zeroed for env `env_index`, for every env (env_index < 0), or for the envs whose
+// mask byte is set.  One thread per (row, env), env fastest (coalesced).
+__global__ void __launch_bounds__(256) reset_rows_kernel(float* __restrict__ buf, int n_rows, long long ld, long long n,
+                                                         long long env_index, const uint8_t* __restrict__ mask) {
+  const long long gid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (env_index >= 0) {  // one column
+    if (gid < n_rows) buf[gid * ld + env_index] = 0.f;
+    return;
+  }
+  if (gid >= (long long)n_rows * n) return;
+  const long long r = gid / n, i = gid - r * n;
+  if (!mask || mask[i]) buf[r * ld + i] = 0.f;
+}
+
+// One iteration of the rejection loop of ScenarioUtils.find_random_pos_for_entity (utils.py:301-306):
+//   dist = torch.cdist(occupied [B,K,2], pos [B,1,2]); overlaps = (dist < min_dist).any(K)
+//   pos[overlaps] = proposed[overlaps]; and the loop's own `overlaps.any()` into *flag.
+// cdist's p = 2 kernel accumulates diff * diff per coordinate and takes the root: sqrt(fma(dy, dy, dx * dx)).
+__global__ void __launch_bounds__(256) spawn_select_kernel(float* __restrict__ pos, const float* __restrict__ proposed,
+                                                           const float* __restrict__ occupied, int K, float min_dist,
+                                                           int* __restrict__ flag, long long B) {
+  const long long b = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  int over = 0;
+  if (b < B) {
+    const float px = pos[2 * b], py = pos[2 * b + 1];
+    for (int k = 0; k < K; ++k) {
+      const float dx = occupied[(b * K + k) * 2] - px, dy = occupied[(b * K + k) * 2 + 1] - py;
+      over |= sqrtf(fmaf(dy, dy, dx * dx)) < min_dist;
+    }
+    if (over) { pos[2 * b] = proposed[2 * b]; pos[2 * b + 1] = proposed[2 * b + 1]; }
+  }
+  over = __reduce_or_sync(0xffffffffu, over);
+  if (over && (threadIdx.x & 31) == 0) atomicOr(flag, 1);
+}
+
 // Environment._set_action, discrete physical actions (environment.py:660-707): one thread per (env, component).
 //   flat action (one column): component k = (flat mod prod(nvec[k:])) div prod(nvec[k+1:]) with Python's floor
 //   semantics (component 0 is not reduced: an action beyond the product fails the range check, as in the reference);

@@ -636,6 +636,29 @@ int vmasb200_set_action(const float* action, int64_t stride_env, int64_t stride_
   return VMASB200_OK;
 }
 
+int vmasb200_reset_rows(float* buf, int32_t row0, int32_t n_rows, int64_t ld, int64_t n, int64_t env_index, const uint8_t* mask,
+                        void* stream) {
+  if (!buf || row0 < 0 || n_rows < 0 || n < 0 || ld < n || env_index >= n) { set_error("reset_rows: bad argument"); return VMASB200_ERR_INVALID; }
+  if (n_rows == 0 || n == 0) return VMASB200_OK;
+  const long long total = env_index >= 0 ? n_rows : (long long)n_rows * n;
+  reset_rows_kernel<<<(unsigned)((total + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      buf + (size_t)row0 * ld, n_rows, ld, n, env_index, mask);
+  VB_CUDA(cudaGetLastError());
+  return VMASB200_OK;
+}
+
+int vmasb200_spawn_select(float* pos, const float* proposed, const float* occupied, int32_t n_occupied, float min_dist,
+                          int32_t* flag, int64_t batch, void* stream) {
+  if (!pos || !proposed || !flag || batch < 0 || n_occupied < 0 || (n_occupied && !occupied)) {
+    set_error("spawn_select: bad argument"); return VMASB200_ERR_INVALID;
+  }
+  if (batch == 0) return VMASB200_OK;
+  spawn_select_kernel<<<(unsigned)((batch + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      pos, proposed, occupied, n_occupied, min_dist, flag, batch);
+  VB_CUDA(cudaGetLastError());
+  return VMASB200_OK;
+}
+
 int vmasb200_set_action_ex(const vmasb200_action* a, int64_t n, void* stream) {
   if (!a || !a->action || !a->u_range || !a->u_multiplier || !a->u_out || !a->flags || n < 0 || a->action_size < 1 ||
       a->action_size > 8 || a->n_comm < 0 || a->n_comm > 64 || a->comm_col0 < 0 || (a->n_comm && !a->c_out)) {

@@ -83,6 +83,8 @@ class WorldBinding:
         self.n_fallback = {"set_action": 0, "cast_rays": 0}  # calls that took the reference's torch code instead (see `strict`)
         self.n_fused_actions = 0
         self.strict = False  # True: such a call raises instead
+        self.fused_reset = False
+        self.n_plan_builds = 0
         self.record_masks = False  # True: every step also leaves World.collides' verdicts per (substep, pair) in self.masks
         self.masks = None
 
@@ -110,6 +112,7 @@ class WorldBinding:
             return
         self.desc_json = js
         self.desc = desc
+        self.n_plan_builds += 1
         self.plan = pl = StepPlan(desc)
         n, ld, dev = self.n, self.ld, self.device
         self.ents = list(self.world.entities)
@@ -501,6 +504,142 @@ class WorldBinding:
         return queries.get_distance_from_point(pa, test_point_pos, self.n, torch)
 
 
+# ---------------------------------------------------------------------------------------------- reset path
+_SPAWN_PATCH = {"count": 0, "orig": None, "cls": None}
+
+
+def _fused_find_random_pos(occupied_positions, env_index, world, min_dist_between_entities, x_bounds, y_bounds,
+                           disable_warn: bool = False):
+    """ScenarioUtils.find_random_pos_for_entity (utils.py:274-319) for a world with the fused reset enabled: the same
+    torch `uniform_` draws in the same order (so the generator advances exactly as in the reference and the placement is
+    bit-identical), the cdist / compare / any / masked assignment of an iteration as ONE launch (vmasb200_spawn_select),
+    and the loop's exit test read from a flag word (the reference synchronises on `overlaps.any()` there too)."""
+    b = getattr(world, "_vmasb200", None)
+    if b is None or not getattr(b, "fused_reset", False) or not occupied_positions.is_cuda:
+        return _SPAWN_PATCH["orig"](occupied_positions, env_index, world, min_dist_between_entities, x_bounds, y_bounds, disable_warn)
+    torch = b.torch
+    batch = world.batch_dim if env_index is None else 1
+    occ = occupied_positions if occupied_positions.is_contiguous() else occupied_positions.contiguous()
+    K = int(occ.shape[1])
+    flag = b._spawn_flag
+    if flag is None:
+        flag = b._spawn_flag = torch.zeros(1, dtype=torch.int32, device=b.device)
+    L, stream = _lib.lib(), _lib.raw_stream(torch, b.device)
+    pos, tries = None, 0
+    while True:
+        proposed = torch.cat([torch.empty((batch, 1, 1), device=world.device, dtype=torch.float32).uniform_(*x_bounds),
+                              torch.empty((batch, 1, 1), device=world.device, dtype=torch.float32).uniform_(*y_bounds)], dim=2)
+        if pos is None:
+            pos = proposed
+        if K == 0:
+            break
+        flag.zero_()
+        _lib.check(L.vmasb200_spawn_select(pos.data_ptr(), proposed.data_ptr(), occ.data_ptr(), K, float(min_dist_between_entities),
+                                           flag.data_ptr(), batch, stream), "vmasb200_spawn_select")
+        b.n_spawn_launches += 1
+        if not int(flag.item()):
+            break
+        tries += 1
+        if tries > 50_000 and not disable_warn:
+            import warnings
+
+            warnings.warn("It is taking many iterations to spawn the entity, make sure the bounds or "
+                          "the min_dist_between_entities are not too tight to fit all entities."
+                          "You can disable this warning by setting disable_warn=True")
+    return pos
+
+
+def _install_fused_reset(world, b):
+    """World.reset / Entity.set_pos|vel|rot|ang_vel / ScenarioUtils.find_random_pos_for_entity for ONE world: state is
+    zeroed and written IN PLACE through the bound views of the SoA buffers (the reference rebinds fresh tensors,
+    core.py:285-295, 742-755, which the next step would have to re-pack field by field)."""
+    torch = b.torch
+    b.fused_reset, b._spawn_flag, b.n_spawn_launches, b.n_reset_launches = True, None, 0, 0
+    b.sync_in()  # pack the current state now: from here on every state field is a view of the SoA buffers
+
+    def reset(self, env_index=None):
+        b.dirty = True  # collision filters / joint rotations may depend on what the scenario sets next
+        if not (env_index is None or isinstance(env_index, int)) or b.plan is None:
+            return b._orig_reset(env_index)
+        L, stream, pl = _lib.lib(), _lib.raw_stream(torch, b.device), b.plan
+        idx = -1 if env_index is None else int(env_index)
+        in_dyn = {id(e) for e, views in b._dyn_views if all(_same_view(getattr(e.state, f), v) for f, v in zip(_FIELDS, views))}
+        in_stat = {id(e) for e, (vp, vr) in b._stat_views if _same_view(e.state.pos, vp) and _same_view(e.state.rot, vr)}
+        if len(in_dyn) == len(b._dyn_views) and pl.dyn_rows:
+            _lib.check(L.vmasb200_reset_rows(b.dyn.data_ptr(), 0, pl.dyn_rows, b.ld, b.n, idx, None, stream), "vmasb200_reset_rows")
+            b.n_reset_launches += 1
+        else:
+            in_dyn = set()
+        if len(in_stat) == len(b._stat_views) and b._stat_views:
+            rows = 3 * len(b._stat_views)  # entity rows only: the per-env joint rotations behind them are not state
+            _lib.check(L.vmasb200_reset_rows(b.stat.data_ptr(), 0, rows, b.ld, b.n, idx, None, stream), "vmasb200_reset_rows")
+            b.n_reset_launches += 1
+        else:
+            in_stat = set()
+        b.lidar_valid = False
+        for e in self.entities:
+            # everything else an entity resets (Agent._reset: action, dynamics, AgentState's c / force / torque,
+            # core.py:372-387, 1046-1049; fields outside the buffers) stays the reference's own code: the fields already
+            # zeroed in place are hidden from EntityState._reset (it skips None, core.py:285-288) and put back
+            st = e.state
+            hide = _FIELDS if id(e) in in_dyn else (("pos", "rot") if id(e) in in_stat else ())
+            saved = [(k, getattr(st, "_" + k)) for k in hide]
+            for k, _ in saved:
+                setattr(st, "_" + k, None)
+            try:
+                e._reset(env_index)
+            finally:
+                for k, t in saved:
+                    setattr(st, "_" + k, t)
+
+    def set_prop(self, prop, state, new, batch_index):
+        assert self.batch_dim is not None, f"Tried to set property of {self.name} without adding it to the world"
+        self._check_batch_index(batch_index)
+        new = new.to(self.device)
+        cur = prop.fget(state)
+        if batch_index is None:
+            src = new if (len(new.shape) > 1 and new.shape[0] == self.batch_dim) else new.repeat(self.batch_dim, 1)
+            if (cur is not None and cur.shape == src.shape and cur.dtype == src.dtype
+                    and not (torch.is_grad_enabled() and (src.requires_grad or cur.requires_grad))):
+                cur.copy_(src)  # in place: the field stays the view of the SoA buffer it was
+            else:
+                prop.fset(state, src)
+        else:
+            cur[batch_index] = new
+        self.notify_observers()
+
+    world.reset = types.MethodType(reset, world)
+    b._set_prop_patched = []
+    for e in world.entities:
+        if hasattr(e, "_set_state_property"):
+            e._set_state_property = types.MethodType(set_prop, e)
+            b._set_prop_patched.append(e)
+    try:
+        import importlib
+
+        cls = importlib.import_module(type(world).__module__.rsplit(".", 1)[0] + ".utils").ScenarioUtils
+    except Exception:  # a World that is not the reference's: nothing to patch
+        cls = None
+    if cls is not None:
+        if _SPAWN_PATCH["count"] == 0:
+            _SPAWN_PATCH["orig"], _SPAWN_PATCH["cls"] = cls.find_random_pos_for_entity, cls
+            cls.find_random_pos_for_entity = staticmethod(_fused_find_random_pos)
+        _SPAWN_PATCH["count"] += 1
+        b._spawn_patched = True
+
+
+def _remove_fused_reset(world, b):
+    for e in getattr(b, "_set_prop_patched", []):
+        e.__dict__.pop("_set_state_property", None)
+    if getattr(b, "_spawn_patched", False):
+        b._spawn_patched = False
+        _SPAWN_PATCH["count"] -= 1
+        if _SPAWN_PATCH["count"] == 0 and _SPAWN_PATCH["cls"] is not None:
+            _SPAWN_PATCH["cls"].find_random_pos_for_entity = staticmethod(_SPAWN_PATCH["orig"])
+            _SPAWN_PATCH["orig"] = _SPAWN_PATCH["cls"] = None
+    b.fused_reset = False
+
+
 def _joints_in_order(world, ents):
     """JointConstraints in the order _apply_vectorized_enviornment_force meets them (core.py:2111-2121)."""
     out = []
@@ -513,7 +652,8 @@ def _joints_in_order(world, ents):
     return out
 
 
-def enable(world_or_env, exact: bool = False, static_io: bool = False, hooks: bool = False, strict: bool = False) -> WorldBinding:
+def enable(world_or_env, exact: bool = False, static_io: bool = False, hooks: bool = False, strict: bool = False,
+           fused_reset: bool = False) -> WorldBinding:
     """Routes ``world.step`` / ``world.cast_rays`` / its Lidars' ``measure`` / the distance queries of ONE world through
     libvmasb200.  ``exact=True`` takes the per-substep exact path instead of the verified speculative single launch.
     ``static_io=True`` (opt-in): the step works IN PLACE on persistent buffers instead of binding fresh output tensors
@@ -524,7 +664,12 @@ def enable(world_or_env, exact: bool = False, static_io: bool = False, hooks: bo
     ``hooks.py`` when the scenario has them (navigation, transport); ``binding.hooks`` is None otherwise.
     ``strict=True``: a secondary call this library does not cover (an action layout, a cast_rays over entities outside
     the plan, a hook on shapes it does not know) raises instead of taking the reference's torch code with a one-time
-    warning.  ``World.step`` itself never falls back: an unsupported world is an error at plan build."""
+    warning.  ``World.step`` itself never falls back: an unsupported world is an error at plan build.
+    ``fused_reset=True`` (opt-in): ``World.reset`` zeroes the SoA buffers in place (one launch per buffer,
+    for one env or all), ``Entity.set_pos / set_vel / set_rot / set_ang_vel`` write through the bound views, and
+    ``ScenarioUtils.find_random_pos_for_entity`` runs one launch per rejection round on the reference's own ``uniform_``
+    draws - placement bit-identical to the reference, and no re-packing of rebound state tensors at the next step.  The
+    price: a state tensor the caller passed to ``set_pos(..., batch_index=None)`` is copied, not adopted."""
     world = getattr(world_or_env, "world", world_or_env)
     if getattr(world, "_vmasb200", None) is not None:
         b = world._vmasb200  # already enabled: opt-ins can still be switched on
@@ -567,6 +712,8 @@ def enable(world_or_env, exact: bool = False, static_io: bool = False, hooks: bo
 
     world.reset = types.MethodType(reset, world)
     b._orig_reset = orig_reset
+    if fused_reset:
+        _install_fused_reset(world, b)
     b._orig_measures = []
     for ag in world.agents:
         for sensor in getattr(ag, "sensors", None) or []:
@@ -589,6 +736,8 @@ def disable(world_or_env) -> None:
     b = getattr(world, "_vmasb200", None)
     if b is None:
         return
+    if getattr(b, "fused_reset", False):
+        _remove_fused_reset(world, b)
     for name in ("step", "cast_rays", "cast_ray", "reset", "get_distance", "is_overlapping", "get_distance_from_point"):
         if name in world.__dict__:
             del world.__dict__[name]
