@@ -9,9 +9,10 @@ from vectorizedmultiagentsimulator_b200 import _lib
 from vectorizedmultiagentsimulator_b200.plan import StepPlan
 
 HAVE_NVRTC = os.path.exists("/usr/local/cuda/lib64/libnvrtc.so.12")
-COVERED = ["simple_spread", "navigation", "transport", "flocking", "wheel", "dropout"]  # short or all-sphere pair lists
-NOT_COVERED = ["football", "joint_passage", "pollock"]  # many box / line pairs: the generic kernel's teams win (jit.h)
-FORCED = ["football", "joint_passage"]                  # ... but the generator covers them (mode 2, used by the GPU tests)
+COVERED = ["simple_spread", "navigation", "transport", "flocking", "wheel", "dropout",  # short or all-sphere pair lists
+           "football", "joint_passage"]  # pair-heavy without LIDAR: the BIG variant (static tile, table-driven narrow phase)
+NOT_COVERED = ["pollock"]                # 990 pairs and a LIDAR epilogue: the generic kernel's teams
+FORCED = ["waterfall", "passage"]        # covered by the generator but not chosen by default: mode 2 (used by the GPU tests)
 
 
 @pytest.mark.skipif(not HAVE_NVRTC, reason="no libnvrtc in this image")

@@ -96,7 +96,8 @@ static bool jit_on() { return jit_mode() != 0; }
 
 // ------------------------------------------------------------------------------------------------ eligibility
 // Worlds the generator covers: every item type, within sizes that keep the unrolled code and the register state small.
-static bool jit_eligible(const vmasb200_plan* pl) {
+static bool jit_big_world(const vmasb200_plan* pl);
+static bool jit_eligible(const vmasb200_plan* pl, int te = 0) {  // te: the CTA tile of the launch in question (32 = small batch), 0 = any
   const KParams& kp = pl->kp;
   if (kp.n_dyn < 1 || kp.n_dyn > 16 || kp.P > 128 || kp.J > 16 || kp.S > 64 || kp.A > 16 || kp.n_sensors > 32 || kp.n_trig > 48)
     return false;
@@ -104,13 +105,22 @@ static bool jit_eligible(const vmasb200_plan* pl) {
   for (const DEnt& e : pl->ents) n_stat_used += e.stat_off >= 0;
   if (n_stat_used > 48) return false;
   if (jit_mode() >= 2) return true;
-  // Measured on B200 (profiles/README.md): one thread per env wins while the pair list is short or all sphere-sphere
-  // (simple_spread 3.4x, transport 2.7x, navigation 2.3x at 1 M envs); with many box / line pairs whose contacts hit
-  // different pairs in different lanes the generic kernel's teams win (football 91 pairs: equal at 1 M, 0.8x at 32 K;
-  // joint_passage 54 pairs + 3 joints, 10 substeps: 0.7x), so those keep the generic kernel.
+  // Measured on B200 (profiles/README.md): everything in registers wins while the pair list is short or all
+  // sphere-sphere (simple_spread 3.4x, transport 2.7x, navigation 2.3x at 1 M envs).  Pair-heavy worlds without LIDAR take
+  // the BIG variant (jit_big_world: static tile, straight-line broad phase, table-driven narrow phase): football 1.5x at
+  // 1 M envs, 1.1x at 32 K; joint_passage 1.13x.  Pair-heavy worlds WITH a LIDAR epilogue keep the generic kernel.
   bool all_ss = kp.J == 0;
   for (int p = 0; p < kp.P && all_ss; ++p) all_ss = pl->items[kp.J + p].type == IT_SS;
-  return all_ss || (kp.P <= 32 && kp.J <= 2);
+  if (all_ss || (kp.P <= 32 && kp.J <= 2)) return true;
+  if (!jit_big_world(pl)) return false;
+  // ... where it was measured to win (tools/ab_worlds.sh): small batches (32-env tiles, one wave) need more than one substep
+  // to amortise the register load of the whole world (passage, ball_passage: S = 1, 0.9x); large batches lose with box-box
+  // pairs, whose narrow phase is ~5000 flops on a 168-register kernel (waterfall 0.8x at 262 144 envs, 1.4x at 32 768)
+  bool has_bb = false;
+  for (int p = 0; p < kp.P; ++p) has_bb = has_bb || pl->items[kp.J + p].type == IT_BB;
+  if (te == 32) return kp.S > 1;
+  if (te != 0) return !has_bb;
+  return true;
 }
 
 // ------------------------------------------------------------------------------------------------ generator
@@ -135,8 +145,30 @@ struct JitLayout {            // the compact LIDAR tile of the compiled kernel (
   std::vector<int> lid_trig;  // of those, the non-sphere targets: 4 work rows each (cos/sin cache)
   int work_rows = 0;
   int smem_rows = 0;          // > 0: the compiled epilogue's own carve-up (rows of TE words), else kernels.cuh smem_map
+  int stat_tile_rows = 0;     // > 0: pair-heavy world: static entities (pose + cos/sin) live in a shared-memory tile, one column per thread
+  // ... and, behind them, per dynamic entity px py [c s [c2 s2]] and its (Fx Fy T) accumulators: what the table-driven
+  // narrow phase (spec_helpers.cuh narrow_big -> step_kernel.cuh eval_item / accumulate) reads and adds to.  Tile rows:
+  std::vector<int> tile_pos, tile_trig, tile_rot, tile_fin;  // per entity: row of px / of cos / of rot / of Fx, or -1
   bool thin_possible = false;
 };
+
+// Pair-heavy worlds (football: 91 pairs, joint_passage: 54 pairs + 3 joints over 10 substeps): with everything in registers
+// the straight-line kernel needs 213 - 255 of them and issues at ~10 %.  For those the generator keeps the STATIC entities
+// (pose and cos / sin, which never change inside a step) in a shared-memory tile with one private column per thread
+// (literal row offsets: one LDS per use, no barrier) and calls the sphere-sphere / line-sphere narrow phases out of line,
+// like box-sphere: ~50 registers and most of the code size less.
+// The narrow phase itself is TABLE-DRIVEN there (narrow_big): the unrolled list only does the broad phase (verdict and
+// survivor bits, branch-free); then every lane walks ITS OWN survivors through the generic eval_item / accumulate on the
+// tile, so that lanes whose contacts are on different pairs still run together (straight-line narrow phases ran once per
+// pair that ANY lane of the warp had, which is what made the all-in-registers kernel lose on these worlds).
+static bool jit_big_world(const vmasb200_plan* pl) {
+  const KParams& kp = pl->kp;
+  if (kp.n_rays > 0) return false;
+  if (const char* e = getenv("VMASB200_JIT_BIG")) return atoi(e) != 0;
+  bool all_ss = kp.J == 0;
+  for (int p = 0; p < kp.P && all_ss; ++p) all_ss = pl->items[kp.J + p].type == IT_SS;
+  return !(all_ss || (kp.P <= 32 && kp.J <= 2));
+}
 
 // The world of `pl` as C++: prelude constants, then (after spec_helpers.cuh) the world_* functions.
 static std::string generate(const vmasb200_plan* pl, int te, int nt, JitLayout* lay) {
@@ -154,6 +186,32 @@ static std::string generate(const vmasb200_plan* pl, int te, int nt, JitLayout* 
   for (int j = 0; j < kp.J; ++j)
     if (pl->items[j].fr_row >= 0) jf_slot[j] = n_jf++;
   const bool lidar = kp.n_rays > 0;
+  const bool big = jit_big_world(pl);
+  // static tile rows of entity e (big worlds): px py rot [c s [c2 s2]]
+  std::vector<int> srow(E, -1);
+  int n_srows = 0;
+  if (big)
+    for (size_t e = 0; e < E; ++e)
+      if (stat_slot[e] >= 0) {
+        srow[e] = n_srows;
+        n_srows += 3 + (trig_slot[e] >= 0 ? (pl->ents[e].shape == VMASB200_BOX ? 4 : 2) : 0);
+      }
+  // behind the static rows: dynamic entities' px py [c s [c2 s2]], then every dynamic entity's Fx Fy T
+  std::vector<int> drow(E, -1), frow(E, -1);
+  if (big) {
+    for (int d = 0; d < kp.n_dyn; ++d) {
+      const int e = pl->dyn_list[d];
+      drow[e] = n_srows;
+      n_srows += 2 + (trig_slot[e] >= 0 ? (pl->ents[e].shape == VMASB200_BOX ? 4 : 2) : 0);
+    }
+    for (int d = 0; d < kp.n_dyn; ++d) { frow[pl->dyn_list[d]] = n_srows; n_srows += 3; }
+  }
+  lay->stat_tile_rows = n_srows;
+  lay->tile_pos.assign(E, -1); lay->tile_trig.assign(E, -1); lay->tile_rot.assign(E, -1); lay->tile_fin.assign(E, -1);
+  for (size_t e = 0; e < E && big; ++e) {
+    if (srow[e] >= 0) { lay->tile_pos[e] = srow[e]; lay->tile_rot[e] = srow[e] + 2; if (trig_slot[e] >= 0) lay->tile_trig[e] = srow[e] + 3; }
+    if (drow[e] >= 0) { lay->tile_pos[e] = drow[e]; if (trig_slot[e] >= 0) lay->tile_trig[e] = drow[e] + 2; lay->tile_fin[e] = frow[e]; }
+  }
   bool thin_possible = false;
   std::vector<char> thin((size_t)kp.P, 1);
   for (int p = 0; p < kp.P; ++p) {
@@ -163,10 +221,17 @@ static std::string generate(const vmasb200_plan* pl, int te, int nt, JitLayout* 
     thin_possible = thin_possible || thin[p];
   }
   lay->thin_possible = thin_possible;
-  outf(s, "constexpr int TE = %d, NT = %d, ND = %d, NST = %d, NA = %d, NTR = %d, NJF = %d, S = %d, P = %d, PW = %d, DYN_ROWS = %d;\n",
-       te, nt, kp.n_dyn, n_stat, kp.A, kp.n_trig, n_jf, kp.S, kp.P, kp.pair_words, kp.dyn_rows);
-  outf(s, "constexpr bool LIDAR = %s, HAS_XS = %s, HAS_YS = %s, HAS_WGRAV = %s, THIN_POSSIBLE = %s;\n", lidar ? "true" : "false",
-       kp.has_xs ? "true" : "false", kp.has_ys ? "true" : "false", kp.has_wgrav ? "true" : "false", thin_possible ? "true" : "false");
+  outf(s, "constexpr int TE = %d, NT = %d, ND = %d, NST = %d, NA = %d, NTR = %d, NJF = %d, S = %d, P = %d, PW = %d, DYN_ROWS = %d, NJ = %d;\n",
+       te, nt, kp.n_dyn, big ? 0 : n_stat, kp.A, kp.n_trig, n_jf, kp.S, kp.P, kp.pair_words, kp.dyn_rows, kp.J);
+  outf(s, "constexpr bool LIDAR = %s, HAS_XS = %s, HAS_YS = %s, HAS_WGRAV = %s, THIN_POSSIBLE = %s, BIG = %s;\n", lidar ? "true" : "false",
+       kp.has_xs ? "true" : "false", kp.has_ys ? "true" : "false", kp.has_wgrav ? "true" : "false", thin_possible ? "true" : "false",
+       big ? "true" : "false");
+  {
+    // resident CTAs per SM the register allocator must leave room for (VMASB200_JIT_MINB, experiments only)
+    int minb = 1;  // measured (tools/ab_big2.sh): capping the registers of the BIG variant below its natural 168 trades the occupancy for spills one to one
+    if (const char* e = getenv("VMASB200_JIT_MINB")) minb = std::max(1, atoi(e));
+    outf(s, "constexpr int MINB = %d;\n", minb);
+  }
   outf(s, "constexpr float SUB_DT = %s, KC = %s, KJ = %s, KT = %s, MARGIN = %s, XS = %s, YS = %s, WGX = %s, WGY = %s;\n",
        fl(kp.sub_dt).c_str(), fl(kp.Kc).c_str(), fl(kp.Kj).c_str(), fl(kp.Kt).c_str(), fl(kp.margin).c_str(), fl(kp.xs).c_str(),
        fl(kp.ys).c_str(), fl(kp.wgx).c_str(), fl(kp.wgy).c_str());
@@ -182,19 +247,23 @@ static std::string generate(const vmasb200_plan* pl, int te, int nt, JitLayout* 
   auto posx = [&](int e) {
     std::string r;
     if (dyn_slot[e] >= 0) outf(r, "mk(st.px[%d], st.py[%d])", dyn_slot[e], dyn_slot[e]);
+    else if (big) outf(r, "mk(st.ss[%d * NT], st.ss[%d * NT])", srow[e], srow[e] + 1);
     else outf(r, "mk(st.sx[%d], st.sy[%d])", stat_slot[e], stat_slot[e]);
     return r;
   };
   auto rotx = [&](int e) {
     std::string r;
     if (dyn_slot[e] >= 0) outf(r, "st.rot[%d]", dyn_slot[e]);
+    else if (stat_slot[e] >= 0 && big) outf(r, "st.ss[%d * NT]", srow[e] + 2);
     else if (stat_slot[e] >= 0) outf(r, "st.srot[%d]", stat_slot[e]);
     else r = "0.f";
     return r;
   };
   auto trigx = [&](int e) {
     std::string r;
-    outf(r, "rot_r<%d>(st)", trig_slot[e]);
+    if (big && e >= 0 && stat_slot[e] >= 0 && trig_slot[e] >= 0)
+      outf(r, "rot_s<%d, %d>(st)", srow[e] + 3, pl->ents[e].shape == VMASB200_BOX ? 1 : 0);
+    else outf(r, "rot_r<%d>(st)", trig_slot[e]);
     return r;
   };
   // ---- load
@@ -207,7 +276,10 @@ static std::string generate(const vmasb200_plan* pl, int te, int nt, JitLayout* 
   for (size_t e = 0; e < E; ++e)
     if (stat_slot[e] >= 0) {
       const char* f[3] = {"sx", "sy", "srot"};
-      for (int k = 0; k < 3; ++k) outf(s, "  st.%s[%d] = sa.stat[(size_t)%d * sa.ld + env];\n", f[k], stat_slot[e], pl->ents[e].stat_off + k);
+      for (int k = 0; k < 3; ++k) {
+        if (big) outf(s, "  st.ss[%d * NT] = sa.stat[(size_t)%d * sa.ld + env];\n", srow[e] + k, pl->ents[e].stat_off + k);
+        else outf(s, "  st.%s[%d] = sa.stat[(size_t)%d * sa.ld + env];\n", f[k], stat_slot[e], pl->ents[e].stat_off + k);
+      }
     }
   for (int j = 0; j < kp.J; ++j)
     if (jf_slot[j] >= 0) outf(s, "  st.jfr[%d] = sa.stat[(size_t)%d * sa.ld + env];\n", jf_slot[j], pl->items[j].fr_row - kp.dyn_rows);
@@ -221,7 +293,10 @@ static std::string generate(const vmasb200_plan* pl, int te, int nt, JitLayout* 
   s += "VB_DI void world_begin(St& st) {\n";
   for (int t = 0; t < kp.n_trig; ++t) {
     const int e = pl->trig_list[t];
-    outf(s, "  trig_r<%d, %d>(st, %s);\n", t, pl->ents[e].shape == VMASB200_BOX ? VMASB200_BOX : VMASB200_SPHERE, rotx(e).c_str());
+    if (big && stat_slot[e] >= 0)
+      outf(s, "  trig_s<%d, %d>(st, %s);\n", srow[e] + 3, pl->ents[e].shape == VMASB200_BOX ? 1 : 0, rotx(e).c_str());
+    else
+      outf(s, "  trig_r<%d, %d>(st, %s);\n", t, pl->ents[e].shape == VMASB200_BOX ? VMASB200_BOX : VMASB200_SPHERE, rotx(e).c_str());
   }
   for (int d = 0; d < kp.n_dyn; ++d) {
     const int e = pl->dyn_list[d];
@@ -236,7 +311,7 @@ static std::string generate(const vmasb200_plan* pl, int te, int nt, JitLayout* 
   }
   s += "}\n";
   // ---- joints, then pairs
-  s += "VB_DI void world_items(St& st) {\n";
+  s += "VB_DI void world_items(St& st, const KParams& kp) {\n";
   for (int j = 0; j < kp.J; ++j) {
     const DItem& it = pl->items[j];
     outf(s, "  joint_r<%d, %d, %d, %d>(st, JointC{%s, %s, %s, %s, %s, %s, %d}, %s, %s, %s, %s, %s, %s);\n", it.acc, dyn_slot[it.a],
@@ -248,10 +323,34 @@ static std::string generate(const vmasb200_plan* pl, int te, int nt, JitLayout* 
     const DItem& it = pl->items[kp.J + p];
     const DBroad& b = pl->broad[p];
     const bool frame = !std::isinf(b.hx) || !std::isinf(b.hy);
+    if (big) {
+      outf(s, "  pair_b<%d, %d, %s>(st, %s, %s, %s, %s, %s, %s, %s);\n", p >> 5, p & 31, frame ? "true" : "false", posx(it.a).c_str(),
+           posx(it.b).c_str(), frame ? trigx(it.a).c_str() : "Rot{}", fl(b.t2_bp).c_str(), fl(b.t2_cull).c_str(), fl(b.hx).c_str(),
+           fl(b.hy).c_str());
+      continue;
+    }
     outf(s, "  pair_r<%d, %d, %d, %d, %d, %d, %s, %s>(st, VBE%d, VBE%d, %s, %s, %s, %s, %s, %s, %s, %s);\n", it.type, it.acc,
          dyn_slot[it.a], dyn_slot[it.b], p >> 5, p & 31, frame ? "true" : "false", thin[p] ? "true" : "false", it.a, it.b,
          posx(it.a).c_str(), posx(it.b).c_str(), trigx(it.a).c_str(), trigx(it.b).c_str(), fl(b.t2_bp).c_str(),
          fl(b.t2_cull).c_str(), fl(b.hx).c_str(), fl(b.hy).c_str());
+  }
+  if (big && kp.P > 0) {
+    // what the table-driven narrow phase reads and adds to goes to the tile, the sums come back (spec_helpers.cuh narrow_big)
+    for (int d = 0; d < kp.n_dyn; ++d) {
+      const int e = pl->dyn_list[d];
+      outf(s, "  st.ss[%d * NT] = st.px[%d]; st.ss[%d * NT] = st.py[%d];\n", drow[e], d, drow[e] + 1, d);
+      if (trig_slot[e] >= 0) {
+        const int t = trig_slot[e];
+        outf(s, "  st.ss[%d * NT] = st.tc[%d]; st.ss[%d * NT] = st.ts[%d];\n", drow[e] + 2, t, drow[e] + 3, t);
+        if (pl->ents[e].shape == VMASB200_BOX) outf(s, "  st.ss[%d * NT] = st.tc2[%d]; st.ss[%d * NT] = st.ts2[%d];\n", drow[e] + 4, t, drow[e] + 5, t);
+      }
+      outf(s, "  st.ss[%d * NT] = st.Fx[%d]; st.ss[%d * NT] = st.Fy[%d]; st.ss[%d * NT] = st.T[%d];\n", frow[e], d, frow[e] + 1, d, frow[e] + 2, d);
+    }
+    s += "  narrow_big(kp, st);\n";
+    for (int d = 0; d < kp.n_dyn; ++d) {
+      const int e = pl->dyn_list[d];
+      outf(s, "  st.Fx[%d] = st.ss[%d * NT]; st.Fy[%d] = st.ss[%d * NT]; st.T[%d] = st.ss[%d * NT];\n", d, frow[e], d, frow[e] + 1, d, frow[e] + 2);
+    }
   }
   s += "}\n";
   // ---- store
@@ -432,6 +531,7 @@ struct JitKernel {
   KParams kpg{};  // the generic view (kernels.cuh repair_kernel: 32-env tile, tables in global memory)
   bool thin_possible = false;
   bool failed = false;
+  void* d_tables = nullptr;  // BIG worlds: DEnt[E] + DItem[n_items] with the rows of the compiled kernel's tile (narrow_big)
 };
 struct JitPlanState {
   std::map<int, JitKernel> by_te;
@@ -535,6 +635,10 @@ static std::string jit_compile(const vmasb200_plan* pl, int te, int nt, JitLayou
 // one wave (shortest critical path), else 128; with LIDAR the CTA always has 128 threads (kernels.cuh kThreads).
 static int jit_tile(const vmasb200_plan* pl, long long n) {
   if (pl->te_fixed) return pl->te_fixed;
+  if (const char* e = getenv("VMASB200_JIT_TE")) {  // experiments (tools/ab_big.sh)
+    const int v = atoi(e);
+    if (v == 32 || v == 64 || v == 128) return v;
+  }
   if (n <= 48 * 1024) return 32;
   return pl->kp.n_rays ? 64 : 128;
 }
@@ -570,7 +674,7 @@ static JitKernel* jit_get(vmasb200_plan* pl, int te, bool compile_only, std::str
   std::lock_guard<std::mutex> lock(g_jit_mu);
   auto say = [&](const std::string& m) { if (why) *why = m; return (JitKernel*)nullptr; };
   if (!jit_on()) return say("switched off (VMASB200_JIT=0 / vmasb200_jit_enable(0))");
-  if (!jit_eligible(pl)) return say("world not covered by the generator (joints or non-sphere pairs / LIDAR targets)");
+  if (!jit_eligible(pl, te)) return say("world not covered by the generator, or the generic kernel is the measured choice for it at this batch size");
   JitPlanState& ps = g_jit_plans[pl];
   JitKernel& jk = ps.by_te[te];
   if (jk.failed) return say("an earlier attempt failed");
@@ -593,7 +697,7 @@ static JitKernel* jit_get(vmasb200_plan* pl, int te, bool compile_only, std::str
   if (!load_driver()) { jk.failed = true; return say("libcuda.so.1 not found"); }
   jit_kparams(pl, te, lay, &jk.kp);
   jit_kparams_generic(pl, &jk.kpg);
-  jk.smem_bytes = !lidar ? 0 : lay.smem_rows ? lay.smem_rows * te * 4 : smem_map(jk.kp).total_bytes;
+  jk.smem_bytes = !lidar ? lay.stat_tile_rows * nt * 4 : lay.smem_rows ? lay.smem_rows * te * 4 : smem_map(jk.kp).total_bytes;
   auto fail = [&](const char* what, int rc) {
     jk.failed = true;
     if (jk.module) { g_drv.ModuleUnload(jk.module); jk.module = nullptr; }
@@ -624,6 +728,24 @@ static JitKernel* jit_get(vmasb200_plan* pl, int te, bool compile_only, std::str
     if (bytes != sizeof(CTab)) return fail("c_tab size mismatch", (int)bytes);
     if ((rc = g_drv.MemcpyHtoD(dptr, t.get(), sizeof(CTab)))) return fail("cuMemcpyHtoD(c_tab)", rc);
   }
+  if (!lidar && lay.stat_tile_rows > 0) {
+    // the generic narrow phase runs on the compiled kernel's tile: entity / item tables with ITS rows, in global memory
+    std::vector<DEnt> ents = pl->ents;
+    std::vector<DItem> items = pl->items;
+    for (size_t e = 0; e < ents.size(); ++e) {
+      ents[e].pos_row = lay.tile_pos[e]; ents[e].trig_row = lay.tile_trig[e]; ents[e].rot_row = lay.tile_rot[e];
+      ents[e].fin_row = lay.tile_fin[e];
+    }
+    for (DItem& it : items) { it.fin_a = lay.tile_fin[it.a]; it.fin_b = lay.tile_fin[it.b]; it.own = 0u; }
+    const size_t be = ents.size() * sizeof(DEnt), bi = items.size() * sizeof(DItem);
+    if (cudaMalloc(&jk.d_tables, be + bi) != cudaSuccess) return fail("cudaMalloc(tile tables)", -1);
+    cudaMemcpy(jk.d_tables, ents.data(), be, cudaMemcpyHostToDevice);
+    cudaMemcpy(static_cast<char*>(jk.d_tables) + be, items.data(), bi, cudaMemcpyHostToDevice);
+    jk.kp = pl->kp;
+    jk.kp.TE = te; jk.kp.NT = nt;
+    jk.kp.ents = static_cast<const DEnt*>(jk.d_tables);
+    jk.kp.items = reinterpret_cast<const DItem*>(static_cast<char*>(jk.d_tables) + be);
+  }
   if (jk.smem_bytes > 48 * 1024 &&
       (rc = g_drv.FuncSetAttribute(fn, 8 /* CU_FUNC_ATTRIBUTE_MAX_DYNAMIC_SHARED_SIZE_BYTES */, jk.smem_bytes)))
     return fail("cuFuncSetAttribute", rc);
@@ -637,8 +759,10 @@ static void jit_forget(const vmasb200_plan* pl) {
   std::lock_guard<std::mutex> lock(g_jit_mu);
   auto it = g_jit_plans.find(pl);
   if (it == g_jit_plans.end()) return;
-  for (auto& kv : it->second.by_te)
+  for (auto& kv : it->second.by_te) {
     if (kv.second.module && g_drv.ok) g_drv.ModuleUnload(kv.second.module);
+    if (kv.second.d_tables) cudaFree(kv.second.d_tables);
+  }
   g_jit_plans.erase(it);
 }
 

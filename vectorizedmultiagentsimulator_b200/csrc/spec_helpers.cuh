@@ -36,7 +36,30 @@ struct St {
   float tc[kNTR], ts[kNTR], tc2[kNTR], ts2[kNTR];             // cos/sin cache (step_kernel.cuh store_trig)
   uint32_t verd[kPW];                                         // World.collides verdict bits of the running substep
   uint32_t thin[kPW];                                         // thin events of the running substep (kernels.cuh)
+  uint32_t sv[kPW];                                           // BIG worlds: survivors of the broad phase of the running substep
+  float* ss;                                                  // BIG worlds: this thread's column of the static tile (row r at ss[r * NT])
 };
+
+// BIG worlds (jit.h jit_big_world): cos/sin cache of a STATIC entity in the static tile, rows r .. r + 1 (+ 2, 3 for a box)
+template <int r, int BOX>
+VB_DI Rot rot_s(const St& st) {
+  Rot o;
+  o.c = st.ss[r * NT]; o.s = st.ss[(r + 1) * NT];
+  if (BOX) { o.c2 = st.ss[(r + 2) * NT]; o.s2 = st.ss[(r + 3) * NT]; }
+  else { o.c2 = 0.f; o.s2 = 0.f; }
+  return o;
+}
+template <int r, int BOX>
+VB_DI void trig_s(St& st, float rot) {
+  float s, c;
+  sincosf(rot, &s, &c);
+  st.ss[r * NT] = c; st.ss[(r + 1) * NT] = s;
+  if (BOX) {
+    float rot2 = rot + (float)(3.14159265358979323846 / 2);
+    sincosf(rot2, &s, &c);
+    st.ss[(r + 2) * NT] = c; st.ss[(r + 3) * NT] = s;
+  }
+}
 
 template <int t>
 VB_DI Rot rot_r(const St& st) {
@@ -201,6 +224,15 @@ __device__ __noinline__ void eval_bs_r(float width, float length, bool hollow, f
   ta = cross(cp - pa, fa);
 }
 
+// the same for sphere-sphere and line-sphere in BIG worlds (football: 21 + 70 such pairs unrolled)
+__device__ __noinline__ void eval_ss_r(float rsum, V2 pa, V2 pb, V2& fa) { fa = constraint_force(pa, pb, rsum, KC, MARGIN, false); }
+__device__ __noinline__ void eval_ls_r(float length, float rb, V2 pa, V2 pb, float c, float s, V2& fa, float& ta) {
+  V2 cp = closest_point_line(pa, c, s, length, pb);
+  V2 fs = constraint_force(pb, cp, rb + kLMD, KC, MARGIN, false);
+  fa = -fs;
+  ta = cross(cp - pa, fa);
+}
+
 // One candidate pair of a substep: the broad-phase row (kernels.cuh run_substeps: verdict of World.collides,
 // core.py:2796-2800, and the cull that only drops pairs whose force is provably zero), the narrow phase, the thin-event
 // test of the speculative launch and update_env_forces.  da / db: dynamic slot of a / b or -1; FRAME: the row carries
@@ -221,10 +253,48 @@ VB_DI void pair_r(St& st, const EntC ea, const EntC eb, V2 pa, V2 pb, const Rot 
     V2 fa;
     float ta, tb;
     if (TYPE == IT_BS) { tb = 0.f; eval_bs_r(ea.width, ea.length, (ea.flags & VMASB200_E_HOLLOW) != 0, eb.radius, pa, pb, qa, fa, ta); }
+    else if (BIG && TYPE == IT_SS) { ta = 0.f; tb = 0.f; eval_ss_r(ea.radius + eb.radius, pa, pb, fa); }
+    else if (BIG && TYPE == IT_LS) { tb = 0.f; eval_ls_r(ea.length, eb.radius, pa, pb, qa.c, qa.s, fa, ta); }
     else eval_pair_r<TYPE>(ea, eb, pa, pb, qa, qb, fa, ta, tb);
     // THIN = false: a sphere-sphere pair whose fp32 r_a + r_b does not exceed the verdict's threshold cannot be thin
     if (THIN && (fa.x != 0.f || fa.y != 0.f) && !verdict) st.thin[word] |= 1u << bit;
     accumulate_r<ACC, da, db>(st, fa, ta, tb);
+  }
+}
+
+// BIG worlds: the broad-phase row alone (kernels.cuh run_substeps: the verdict of World.collides and the conservative cull),
+// branch-free; the survivors are evaluated afterwards by narrow_big.
+template <int word, int bit, bool FRAME>
+VB_DI void pair_b(St& st, V2 pa, V2 pb, const Rot qa, float t2_bp, float t2_cull, float hx, float hy) {
+  const float dx = pa.x - pb.x, dy = pa.y - pb.y;
+  const float d2 = fmaf(dy, dy, dx * dx);
+  st.verd[word] |= (d2 <= t2_bp ? 1u : 0u) << bit;
+  bool sv = !(d2 > t2_cull);  // NaN passes, as in the generic broad phase
+  if (FRAME) {
+    const float lx = fmaf(dx, qa.c, dy * qa.s), ly = fmaf(dx, qa.s, -(dy * qa.c));
+    sv = sv && !(fabsf(lx) > hx) && !(fabsf(ly) > hy);
+  }
+  st.sv[word] |= (sv ? 1u : 0u) << bit;
+}
+// ... and their narrow phase: every lane walks its own survivors in pair order through the GENERIC eval_item / accumulate
+// (step_kernel.cuh: same code, hence same bits) on its column of the tile, with the tables of jit.h (tile rows, global
+// memory).  Lanes with contacts on different pairs run together; only the pair TYPE can diverge.
+VB_DI void narrow_big(const KParams& kp, St& st) {
+  EnvT<NT> E;
+  E.env = st.ss; E.work = st.ss;
+#pragma unroll
+  for (int w = 0; w < PW; ++w) {
+    uint32_t m = st.sv[w];
+    while (m) {
+      const int b = __ffs(m) - 1;
+      m &= m - 1;
+      const DItem* it = kp.items + (NJ + w * 32 + b);
+      V2 fa;
+      float ta, tb;
+      eval_item<false>(kp, it, E, fa, ta, tb);
+      if (THIN_POSSIBLE && (fa.x != 0.f || fa.y != 0.f) && !((st.verd[w] >> b) & 1u)) st.thin[w] |= 1u << b;
+      accumulate<1>(it, E, fa, ta, tb, 0);
+    }
   }
 }
 

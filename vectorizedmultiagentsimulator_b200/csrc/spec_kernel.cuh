@@ -142,7 +142,7 @@ VB_DI void lidar_world(const KParams& kp, const StepArgs& sa, const Tile& t, con
 }
 }  // namespace gen
 
-extern "C" __global__ void __launch_bounds__(gen::NT)
+extern "C" __global__ void __launch_bounds__(gen::NT, gen::MINB)
 vmasb200_step_world(const __grid_constant__ KParams kp, const __grid_constant__ AgentIO aio, const __grid_constant__ StepArgs sa) {
   using namespace gen;
   extern __shared__ __align__(16) float smem[];
@@ -160,14 +160,15 @@ vmasb200_step_world(const __grid_constant__ KParams kp, const __grid_constant__ 
   const bool ok = phys && tid < n_valid;
   const long long env = env0 + (ok ? tid : 0);
   St st;
+  st.ss = BIG ? smem + tid : nullptr;  // static tile of a pair-heavy world (non-LIDAR): the whole dynamic smem, NT columns
   int taint = 0;  // 0, or 1 + the env's index in sa.u_list (kernels.cuh run_substeps)
   if (phys) {
     world_load(st, aio, sa, env);
     world_begin(st);
     for (int s = 0; s < S; ++s) {
 #pragma unroll
-      for (int w = 0; w < kPW; ++w) { st.verd[w] = 0u; st.thin[w] = 0u; }
-      world_items(st);
+      for (int w = 0; w < kPW; ++w) { st.verd[w] = 0u; st.thin[w] = 0u; st.sv[w] = 0u; }
+      world_items(st, kp);
       const bool tainted = THIN_POSSIBLE && taint != 0;
 #pragma unroll
       for (int w = 0; w < PW; ++w) {

@@ -381,7 +381,7 @@ int vmasb200_plan_jit(vmasb200_plan* pl, int64_t n_envs, int32_t* state, int64_t
   if (!pl) { set_error("plan_jit: NULL plan"); return VMASB200_ERR_INVALID; }
   std::string why;
   int st = 0;
-  if (!jit_on() || !jit_eligible(pl)) st = 0;
+  if (!jit_on() || !jit_eligible(pl, jit_tile(pl, n_envs))) st = 0;
   else {
     jit_get(pl, jit_tile(pl, n_envs), true, &why);
     st = why == "compiled" ? 1 : -1;
