@@ -170,19 +170,35 @@ vmasb200_step_world(const __grid_constant__ KParams kp, const __grid_constant__ 
       for (int w = 0; w < kPW; ++w) { st.verd[w] = 0u; st.thin[w] = 0u; st.sv[w] = 0u; }
       world_items(st, kp);
       const bool tainted = THIN_POSSIBLE && taint != 0;
+      {
+        // the warp's bits of this substep into the batch-wide words: all reductions first, then lane 0 reads every word
+        // it may have to add to (independent L2 loads in flight together; one after the other they were a chain of L2
+        // round trips per substep, 5.6 % of the samples of the football kernel), then the atomics that add a bit
+        uint32_t e[kPW], sp[kPW], th[kPW];
 #pragma unroll
-      for (int w = 0; w < PW; ++w) {
-        const uint32_t e = __reduce_or_sync(0xffffffffu, (ok && !tainted) ? st.verd[w] : 0u);
-        if ((tid & 31) == 0 && e) or_global(sa.any_exact + s * PW + w, e);
-        if (THIN_POSSIBLE) {
-          const uint32_t sp = __reduce_or_sync(0xffffffffu, (ok && tainted) ? st.verd[w] : 0u);
-          const uint32_t th = __reduce_or_sync(0xffffffffu, ok ? st.thin[w] : 0u);
-          if ((tid & 31) == 0) {
-            if (sp) or_global(sa.any_spec + s * PW + w, sp);
-            if (th) or_global(sa.thin + s * PW + w, th);
-          }
-          if (ok && tainted && taint <= sa.rec_cap) sa.u_verd[((size_t)(taint - 1) * S + s) * PW + w] = st.verd[w];
+        for (int w = 0; w < PW; ++w) {
+          e[w] = __reduce_or_sync(0xffffffffu, (ok && !tainted) ? st.verd[w] : 0u);
+          sp[w] = THIN_POSSIBLE ? __reduce_or_sync(0xffffffffu, (ok && tainted) ? st.verd[w] : 0u) : 0u;
+          th[w] = THIN_POSSIBLE ? __reduce_or_sync(0xffffffffu, ok ? st.thin[w] : 0u) : 0u;
         }
+        if ((tid & 31) == 0) {
+          uint32_t ce[kPW], cs[kPW], ct[kPW];
+#pragma unroll
+          for (int w = 0; w < PW; ++w) {
+            ce[w] = e[w] ? __ldcg(sa.any_exact + s * PW + w) : 0xffffffffu;
+            cs[w] = sp[w] ? __ldcg(sa.any_spec + s * PW + w) : 0xffffffffu;
+            ct[w] = th[w] ? __ldcg(sa.thin + s * PW + w) : 0xffffffffu;
+          }
+#pragma unroll
+          for (int w = 0; w < PW; ++w) {
+            if (e[w] & ~ce[w]) atomicOr(sa.any_exact + s * PW + w, e[w]);
+            if (sp[w] & ~cs[w]) atomicOr(sa.any_spec + s * PW + w, sp[w]);
+            if (th[w] & ~ct[w]) atomicOr(sa.thin + s * PW + w, th[w]);
+          }
+        }
+        if (THIN_POSSIBLE && ok && tainted && taint <= sa.rec_cap)
+#pragma unroll
+          for (int w = 0; w < PW; ++w) sa.u_verd[((size_t)(taint - 1) * S + s) * PW + w] = st.verd[w];
       }
       world_integrate(st, s, s + 1 < S);
       if (THIN_POSSIBLE && ok) {  // thin events of this substep: tainted from the NEXT substep on, with a record
