@@ -13,7 +13,7 @@ for wl in "$@"; do
   export VMASB200_JIT_CACHE=/tmp/jit_$name   # this run's world-compiled cubin alone (ncu_lines needs its line table)
   rm -rf $VMASB200_JIT_CACHE
   ncu --set full --metrics smsp__sass_thread_inst_executed_op_fadd_pred_on.sum,smsp__sass_thread_inst_executed_op_fmul_pred_on.sum,smsp__sass_thread_inst_executed_op_ffma_pred_on.sum --import-source on --clock-control none -k 'regex:step_kernel|vmasb200_step_world' -s 6 -c 1 -f -o $rep \
-    python bench.py --scenario $sc --num-envs $n --steps 4 --warmup 3 --no-cpu-baseline --no-e2e > $OUT/ncu_$name.log 2>&1
+    python bench.py --scenario $sc --num-envs $n --steps 4 --warmup 3 --no-cpu-baseline --no-e2e --no-1m --no-torch-cuda > $OUT/ncu_$name.log 2>&1
   python tools/ncu_summary.py $rep.ncu-rep > $OUT/step_kernel_$name.txt 2>&1
   kname=$(head -1 $OUT/step_kernel_$name.txt)
   if echo "$kname" | grep -q vmasb200_step_world; then

@@ -150,6 +150,7 @@ struct JitLayout {            // the compact LIDAR tile of the compiled kernel (
   // narrow phase (spec_helpers.cuh narrow_big -> step_kernel.cuh eval_item / accumulate) reads and adds to.  Tile rows:
   std::vector<int> tile_pos, tile_trig, tile_rot, tile_fin;  // per entity: row of px / of cos / of rot / of Fx, or -1
   bool thin_possible = false;
+  bool coop = false;          // narrow_coop scratch behind the tile: (nt / 32) * (64 / 2 + 4 * 64) words
 };
 
 // Pair-heavy worlds (football: 91 pairs, joint_passage: 54 pairs + 3 joints over 10 substeps): with everything in registers
@@ -232,6 +233,13 @@ static std::string generate(const vmasb200_plan* pl, int te, int nt, JitLayout* 
     if (const char* e = getenv("VMASB200_JIT_MINB")) minb = std::max(1, atoi(e));
     outf(s, "constexpr int MINB = %d;\n", minb);
   }
+  {
+    // BIG worlds: narrow phase shared out over the warp (spec_helpers.cuh narrow_coop); needs the warp's envs in one tile
+    // (all threads carry an env: no LIDAR) and pair numbers that fit the queue's 11 bits
+    const bool coop = big && kp.P < 2048 && !getenv("VMASB200_JIT_NOCOOP");
+    outf(s, "constexpr bool COOP = %s;\nconstexpr int TILE_ROWS = %d;\n", coop ? "true" : "false", n_srows);
+    lay->coop = coop;
+  }
   outf(s, "constexpr float SUB_DT = %s, KC = %s, KJ = %s, KT = %s, MARGIN = %s, XS = %s, YS = %s, WGX = %s, WGY = %s;\n",
        fl(kp.sub_dt).c_str(), fl(kp.Kc).c_str(), fl(kp.Kj).c_str(), fl(kp.Kt).c_str(), fl(kp.margin).c_str(), fl(kp.xs).c_str(),
        fl(kp.ys).c_str(), fl(kp.wgx).c_str(), fl(kp.wgy).c_str());
@@ -266,6 +274,87 @@ static std::string generate(const vmasb200_plan* pl, int te, int nt, JitLayout* 
     else outf(r, "rot_r<%d>(st)", trig_slot[e]);
     return r;
   };
+  // ---- looped runs of the broad phase (big worlds; spec_helpers.cuh pair_l): pairs p0 + j * k + i, j < n, i < k, where block
+  // j is one static entity (tile rows a fixed stride apart, same shape, same role) against the same k dynamic entities
+  struct Run { int p0, n, k, s0, stride; bool stat_is_a; std::vector<int> cls; int kc; };
+  std::vector<Run> runs;
+  std::vector<int> run_of((size_t)kp.P, -1);
+  if (big && !getenv("VMASB200_JIT_NOLOOP")) {
+    auto stat_of = [&](int p, bool* is_a) {  // the pair's static entity when it has exactly one, else -1
+      const DItem& it = pl->items[kp.J + p];
+      const bool sa_ = stat_slot[it.a] >= 0, sb_ = stat_slot[it.b] >= 0;
+      if (sa_ == sb_) return -1;
+      *is_a = sa_;
+      return sa_ ? (int)it.a : (int)it.b;
+    };
+    auto frame_of = [&](int p) { return !std::isinf(pl->broad[p].hx) || !std::isinf(pl->broad[p].hy); };
+    for (int p = 0; p < kp.P;) {
+      bool is_a = false;
+      const int S0 = stat_of(p, &is_a);
+      if (S0 < 0) { ++p; continue; }
+      int k = 1;
+      for (bool a2; p + k < kp.P && stat_of(p + k, &a2) == S0 && a2 == is_a; ++k) {}
+      auto dyn_of = [&](int q) { const DItem& it = pl->items[kp.J + q]; return is_a ? (int)it.b : (int)it.a; };
+      int n = 1, stride = 0;
+      for (;; ++n) {
+        const int q0 = p + n * k;
+        if (q0 + k > kp.P) break;
+        bool a2 = false;
+        const int Sj = stat_of(q0, &a2);
+        if (Sj < 0 || a2 != is_a || pl->ents[Sj].shape != pl->ents[S0].shape || (trig_slot[Sj] >= 0) != (trig_slot[S0] >= 0)) break;
+        const int st_j = srow[Sj] - srow[S0];
+        if (n == 1) stride = st_j;
+        if (st_j != n * stride || stride <= 0) break;
+        bool same = true;
+        for (int i = 0; i < k && same; ++i) {
+          bool a3 = false;
+          same = stat_of(q0 + i, &a3) == Sj && a3 == is_a && dyn_of(q0 + i) == dyn_of(p + i) && frame_of(q0 + i) == frame_of(p + i) &&
+                 (frame_of(p + i) ? std::isinf(pl->broad[q0 + i].t2_cull) : true);
+        }
+        // the block must END here: the next pair may not belong to the same static entity (else k would differ)
+        bool a4 = false;
+        if (same && q0 + k < kp.P && stat_of(q0 + k, &a4) == Sj && a4 == is_a) same = false;
+        if (!same) break;
+      }
+      bool ok_run = n >= 2 && n * k >= 6 && k <= 32;
+      for (int i = 0; i < k && ok_run; ++i)
+        if (frame_of(p + i) && !std::isinf(pl->broad[p + i].t2_cull)) ok_run = false;
+      if (!ok_run) { p += 1; continue; }
+      Run r{p, n, k, srow[S0], stride, is_a, std::vector<int>((size_t)k, 0), 0};
+      for (int i = 0; i < k; ++i) {  // columns with the same thresholds in every block share their table column
+        int c = -1;
+        for (int i2 = 0; i2 < i && c < 0; ++i2) {
+          bool eq = true;
+          for (int j = 0; j < n && eq; ++j) {
+            const DBroad &x = pl->broad[p + j * k + i], &y = pl->broad[p + j * k + i2];
+            eq = x.t2_bp == y.t2_bp && x.t2_cull == y.t2_cull && x.hx == y.hx && x.hy == y.hy;
+          }
+          if (eq) c = r.cls[(size_t)i2];
+        }
+        r.cls[(size_t)i] = c >= 0 ? c : r.kc++;
+      }
+      for (int q = p; q < p + n * k; ++q) run_of[(size_t)q] = (int)runs.size();
+      runs.push_back(r);
+      p += n * k;
+    }
+    for (size_t ri = 0; ri < runs.size(); ++ri) {  // thresholds [block][class][t2_bp t2_cull hx hy]
+      const Run& r = runs[ri];
+      outf(s, "__constant__ uint32_t RT%d[%d] = {", (int)ri, r.n * r.kc * 4);  // bit patterns (inf has no literal)
+      for (int j = 0; j < r.n; ++j)
+        for (int c = 0; c < r.kc; ++c) {
+          int i = 0;
+          while (r.cls[(size_t)i] != c) ++i;
+          const DBroad& b = pl->broad[r.p0 + j * r.k + i];
+          const float v4[4] = {b.t2_bp, b.t2_cull, b.hx, b.hy};
+          for (float f : v4) {
+            uint32_t u;
+            memcpy(&u, &f, 4);
+            outf(s, "0x%08xu, ", u);
+          }
+        }
+      s += "};\n";
+    }
+  }
   // ---- load
   s += "VB_DI void world_load(St& st, const AgentIO& aio, const StepArgs& sa, long long env) {\n";
   // rows through a running pointer (one 64-bit add per row instead of a 64-bit multiply-add: world_load was 12 % of the
@@ -312,6 +401,22 @@ static std::string generate(const vmasb200_plan* pl, int te, int nt, JitLayout* 
   s += "VB_DI void world_begin(St& st) {\n";
   for (int t = 0; t < kp.n_trig; ++t) {
     const int e = pl->trig_list[t];
+    if (big && stat_slot[e] >= 0 && !getenv("VMASB200_JIT_NOLOOP")) {
+      // static entities of one shape whose tile rows are a fixed stride apart: one loop (10 inlined sincosf are 7 KB of code)
+      int n = 1, stride = 0;
+      for (; t + n < kp.n_trig; ++n) {
+        const int e2 = pl->trig_list[t + n];
+        if (stat_slot[e2] < 0 || pl->ents[e2].shape != pl->ents[e].shape) break;
+        if (n == 1) stride = srow[e2] - srow[e];
+        if (stride <= 0 || srow[e2] - srow[e] != n * stride) break;
+      }
+      if (n >= 3) {
+        outf(s, "#pragma unroll 1\n  for (int j = 0; j < %d; ++j) { float* sj = st.ss + j * (%d * NT); trig_sp<%d>(sj + %d * NT, sj[%d * NT]); }\n",
+             n, stride, pl->ents[e].shape == VMASB200_BOX ? 1 : 0, srow[e] + 3, srow[e] + 2);
+        t += n - 1;
+        continue;
+      }
+    }
     if (big && stat_slot[e] >= 0)
       outf(s, "  trig_s<%d, %d>(st, %s);\n", srow[e] + 3, pl->ents[e].shape == VMASB200_BOX ? 1 : 0, rotx(e).c_str());
     else
@@ -342,6 +447,36 @@ static std::string generate(const vmasb200_plan* pl, int te, int nt, JitLayout* 
     const DItem& it = pl->items[kp.J + p];
     const DBroad& b = pl->broad[p];
     const bool frame = !std::isinf(b.hx) || !std::isinf(b.hy);
+    if (big && run_of[(size_t)p] >= 0) {
+      const Run& r = runs[(size_t)run_of[(size_t)p]];
+      if (p != r.p0) continue;  // the whole run is emitted at its first pair
+      const int W = (r.n * r.k + 31) / 32;
+      outf(s, "  {  // pairs %d .. %d: %d static entities x %d dynamic ones\n    uint32_t av[%d] = {}, as[%d] = {};\n", r.p0,
+           r.p0 + r.n * r.k - 1, r.n, r.k, W, W);
+      outf(s, "#pragma unroll 1\n    for (int j = %d; j >= 0; --j) {\n      const float* sj = st.ss + j * (%d * NT);\n", r.n - 1, r.stride);
+      outf(s, "      const uint32_t* th = RT%d + j * %d;\n      uint32_t v = 0u, sv = 0u;\n", run_of[(size_t)p], r.kc * 4);
+      outf(s, "      const V2 ps = mk(sj[%d * NT], sj[%d * NT]);\n", r.s0, r.s0 + 1);
+      for (int i = 0; i < r.k; ++i) {
+        const DItem& iti = pl->items[kp.J + p + i];
+        const bool fr = !std::isinf(pl->broad[p + i].hx) || !std::isinf(pl->broad[p + i].hy);
+        const int dynE = r.stat_is_a ? (int)iti.b : (int)iti.a;
+        std::string pd;
+        outf(pd, "mk(st.px[%d], st.py[%d])", dyn_slot[dynE], dyn_slot[dynE]);
+        std::string qc = "0.f", qs = "0.f";
+        if (fr) {  // the frame is a's (plan.cpp: a = line / box)
+          if (r.stat_is_a) { qc.clear(); qs.clear(); outf(qc, "sj[%d * NT]", r.s0 + 3); outf(qs, "sj[%d * NT]", r.s0 + 4); }
+          else { qc.clear(); qs.clear(); outf(qc, "st.tc[%d]", trig_slot[iti.a]); outf(qs, "st.ts[%d]", trig_slot[iti.a]); }
+        }
+        const int c4 = r.cls[(size_t)i] * 4;
+        outf(s, "      pair_l<%d, %s>(v, sv, %s, %s, %s, %s, __uint_as_float(th[%d]), __uint_as_float(th[%d]), __uint_as_float(th[%d]), __uint_as_float(th[%d]));\n", i, fr ? "true" : "false",
+             r.stat_is_a ? "ps" : pd.c_str(), r.stat_is_a ? pd.c_str() : "ps", qc.c_str(), qs.c_str(), c4, c4 + 1, c4 + 2, c4 + 3);
+      }
+      outf(s, "      run_push<%d, %d>(av, v); run_push<%d, %d>(as, sv);\n    }\n", W, r.k, W, r.k);
+      for (int tw = r.p0 >> 5; tw <= (r.p0 + r.n * r.k - 1) >> 5; ++tw)
+        outf(s, "    st.verd[%d] |= run_word<%d, %d, %d>(av); st.sv[%d] |= run_word<%d, %d, %d>(as);\n", tw, W, r.p0, tw, tw, W, r.p0, tw);
+      s += "  }\n";
+      continue;
+    }
     if (big) {
       outf(s, "  pair_b<%d, %d, %s>(st, %s, %s, %s, %s, %s, %s, %s);\n", p >> 5, p & 31, frame ? "true" : "false", posx(it.a).c_str(),
            posx(it.b).c_str(), frame ? trigx(it.a).c_str() : "Rot{}", fl(b.t2_bp).c_str(), fl(b.t2_cull).c_str(), fl(b.hx).c_str(),
@@ -725,7 +860,7 @@ static JitKernel* jit_get(vmasb200_plan* pl, int te, bool compile_only, std::str
   if (!load_driver()) { jk.failed = true; return say("libcuda.so.1 not found"); }
   jit_kparams(pl, te, lay, &jk.kp);
   jit_kparams_generic(pl, &jk.kpg);
-  jk.smem_bytes = !lidar ? lay.stat_tile_rows * nt * 4 : lay.smem_rows ? lay.smem_rows * te * 4 : smem_map(jk.kp).total_bytes;
+  jk.smem_bytes = !lidar ? lay.stat_tile_rows * nt * 4 + (lay.coop ? (nt / 32) * (64 / 2 + 4 * 64) * 4 : 0) : lay.smem_rows ? lay.smem_rows * te * 4 : smem_map(jk.kp).total_bytes;
   auto fail = [&](const char* what, int rc) {
     jk.failed = true;
     if (jk.module) { g_drv.ModuleUnload(jk.module); jk.module = nullptr; }

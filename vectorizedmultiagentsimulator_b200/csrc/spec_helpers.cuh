@@ -38,6 +38,7 @@ struct St {
   uint32_t thin[kPW];                                         // thin events of the running substep (kernels.cuh)
   uint32_t sv[kPW];                                           // BIG worlds: survivors of the broad phase of the running substep
   float* ss;                                                  // BIG worlds: this thread's column of the static tile (row r at ss[r * NT])
+  float* coop;                                                // BIG worlds: this WARP's scratch of the cooperative narrow phase (narrow_coop)
 };
 
 // BIG worlds (jit.h jit_big_world): cos/sin cache of a STATIC entity in the static tile, rows r .. r + 1 (+ 2, 3 for a box)
@@ -58,6 +59,20 @@ VB_DI void trig_s(St& st, float rot) {
     float rot2 = rot + (float)(3.14159265358979323846 / 2);
     sincosf(rot2, &s, &c);
     st.ss[(r + 2) * NT] = c; st.ss[(r + 3) * NT] = s;
+  }
+}
+
+// ... the same with the tile address at run time (looped runs of static entities, jit.h): p = the entity's cos row in this
+// thread's column
+template <int BOX>
+VB_DI void trig_sp(float* p, float rot) {
+  float s, c;
+  sincosf(rot, &s, &c);
+  p[0] = c; p[NT] = s;
+  if (BOX) {
+    float rot2 = rot + (float)(3.14159265358979323846 / 2);
+    sincosf(rot2, &s, &c);
+    p[2 * NT] = c; p[3 * NT] = s;
   }
 }
 
@@ -276,10 +291,124 @@ VB_DI void pair_b(St& st, V2 pa, V2 pb, const Rot qa, float t2_bp, float t2_cull
   }
   st.sv[word] |= (sv ? 1u : 0u) << bit;
 }
+// The same row inside a LOOPED run (jit.h: consecutive pairs of one list of dynamic entities against static entities whose
+// tile rows are a fixed stride apart run as a loop over the static entities - the straight-line list of football's 91 pairs
+// is 20 KB of code that every warp streams through once per substep, and 42 % of that kernel's stall samples were
+// instruction fetches): the static partner's rows and the thresholds are run-time values, the pair's bit is bit i of the
+// block's masks.  FRAME rows have no circle cull (plan.cpp: t2_cull = inf), the others no frame cull (hx = hy = inf).
+template <int i, bool FRAME>
+VB_DI void pair_l(uint32_t& v, uint32_t& s, V2 pa, V2 pb, float qc, float qs, float t2_bp, float t2_cull, float hx, float hy) {
+  const float dx = pa.x - pb.x, dy = pa.y - pb.y;
+  const float d2 = fmaf(dy, dy, dx * dx);
+  v |= (d2 <= t2_bp ? 1u : 0u) << i;
+  bool sv;
+  if (FRAME) {
+    const float lx = fmaf(dx, qc, dy * qs), ly = fmaf(dx, qs, -(dy * qc));
+    const bool ox = fabsf(lx) > hx, oy = fabsf(ly) > hy;  // both evaluated (no short circuit: the loop stays branch-free)
+    sv = !(ox | oy);
+  } else {
+    sv = !(d2 > t2_cull);  // NaN passes, as in the generic broad phase
+  }
+  s |= (sv ? 1u : 0u) << i;
+}
+// shift a block's k bits into a run's W-word accumulator (blocks are visited last to first: block 0 ends at bit 0)
+template <int W, int k>
+VB_DI void run_push(uint32_t* a, uint32_t bits) {
+#pragma unroll
+  for (int w = W - 1; w > 0; --w) a[w] = __funnelshift_l(a[w - 1], a[w], k);
+  a[0] = (a[0] << k) | bits;
+}
+// the accumulator's bits [32 * tw - p0, +32) : what lands in word tw of the pair masks when the run starts at pair p0
+template <int W, int p0, int tw>
+VB_DI uint32_t run_word(const uint32_t* a) {
+  uint32_t o = 0u;
+#pragma unroll
+  for (int q = 0; q < W; ++q) {
+    const int rel = p0 + 32 * q - 32 * tw;
+    if (rel >= 0 && rel < 32) o |= a[q] << rel;
+    else if (rel < 0 && rel > -32) o |= a[q] >> (-rel);
+  }
+  return o;
+}
+
 // ... and their narrow phase: every lane walks its own survivors in pair order through the GENERIC eval_item / accumulate
 // (step_kernel.cuh: same code, hence same bits) on its column of the tile, with the tables of jit.h (tile rows, global
 // memory).  Lanes with contacts on different pairs run together; only the pair TYPE can diverge.
+//
+// narrow_coop: the same, shared out over the WARP.  A lane's survivors cost max-over-lanes iterations of the walk above
+// while most lanes have none (joint_passage: 1.7 of 32 lanes active in the narrow phase, 40 % of the kernel's
+// instructions).  So the warp's survivors are numbered (prefix sum of the lanes' counts), written to a queue in shared
+// memory as (lane, pair), evaluated one per lane on the OWNER's column of the tile (the state of every env of the warp is
+// there), and the results (fa, ta, tb) go back through shared memory; every lane then applies ITS OWN results in its pair
+// order - the accumulation order per entity is the reference's (and narrow_big's), so the bits do not change.
+constexpr int kCoopQ = 64;                               // queue entries per pass (more survivors: several passes)
+constexpr int kCoopWords = kCoopQ / 2 + 4 * kCoopQ;      // 4-byte words per warp: u16 queue, then float4 results
+VB_DI void narrow_coop(const KParams& kp, St& st) {
+  const int lane = threadIdx.x & 31;
+  unsigned short* q = reinterpret_cast<unsigned short*>(st.coop);
+  float4* res = reinterpret_cast<float4*>(st.coop + kCoopQ / 2);
+  int cnt = 0;
+#pragma unroll
+  for (int w = 0; w < PW; ++w) cnt += __popc(st.sv[w]);
+  int incl = cnt;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const int up = __shfl_up_sync(0xffffffffu, incl, d);
+    if (lane >= d) incl += up;
+  }
+  const int off = incl - cnt, T = __shfl_sync(0xffffffffu, incl, 31);
+  if (T == 0) return;
+  float* col0 = st.ss - lane;  // column of lane 0 of this warp
+  EnvT<NT> Eo;
+  Eo.env = st.ss; Eo.work = st.ss;
+  for (int base = 0; base < T; base += kCoopQ) {
+    {
+      int g = off - base;
+#pragma unroll
+      for (int w = 0; w < PW; ++w) {
+        uint32_t m = st.sv[w];
+        while (m) {
+          const int b = __ffs(m) - 1;
+          m &= m - 1;
+          if (g >= 0 && g < kCoopQ) q[g] = (unsigned short)(lane | (w * 32 + b) << 5);
+          ++g;
+        }
+      }
+    }
+    __syncwarp();
+    const int n = min(kCoopQ, T - base);
+    for (int e = lane; e < n; e += 32) {
+      const int ent = q[e];
+      EnvT<NT> E;
+      E.env = col0 + (ent & 31); E.work = E.env;
+      V2 fa;
+      float ta, tb;
+      eval_item<false>(kp, kp.items + (NJ + (ent >> 5)), E, fa, ta, tb);
+      res[e] = make_float4(fa.x, fa.y, ta, tb);
+    }
+    __syncwarp();
+    {
+      int g = off - base;
+#pragma unroll
+      for (int w = 0; w < PW; ++w) {
+        uint32_t m = st.sv[w];
+        while (m) {
+          const int b = __ffs(m) - 1;
+          m &= m - 1;
+          if (g >= 0 && g < kCoopQ) {
+            const float4 r = res[g];
+            if (THIN_POSSIBLE && (r.x != 0.f || r.y != 0.f) && !((st.verd[w] >> b) & 1u)) st.thin[w] |= 1u << b;
+            accumulate<1>(kp.items + (NJ + w * 32 + b), Eo, mk(r.x, r.y), r.z, r.w, 0);
+          }
+          ++g;
+        }
+      }
+    }
+    __syncwarp();
+  }
+}
 VB_DI void narrow_big(const KParams& kp, St& st) {
+  if (COOP) { narrow_coop(kp, st); return; }
   EnvT<NT> E;
   E.env = st.ss; E.work = st.ss;
 #pragma unroll

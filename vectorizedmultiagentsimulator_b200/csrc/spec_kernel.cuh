@@ -160,7 +160,8 @@ vmasb200_step_world(const __grid_constant__ KParams kp, const __grid_constant__ 
   const bool ok = phys && tid < n_valid;
   const long long env = env0 + (ok ? tid : 0);
   St st;
-  st.ss = BIG ? smem + tid : nullptr;  // static tile of a pair-heavy world (non-LIDAR): the whole dynamic smem, NT columns
+  st.ss = BIG ? smem + tid : nullptr;  // static tile of a pair-heavy world (non-LIDAR): TILE_ROWS rows of NT columns
+  st.coop = BIG && COOP ? smem + TILE_ROWS * NT + (tid >> 5) * kCoopWords : nullptr;  // ... then every warp's scratch (narrow_coop)
   int taint = 0;  // 0, or 1 + the env's index in sa.u_list (kernels.cuh run_substeps)
   if (phys) {
     world_load(st, aio, sa, env);
