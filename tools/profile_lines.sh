@@ -22,6 +22,7 @@ for wl in "$@"; do
     te=$(echo "$kname" | sed -n 's/.*step_kernel<[0-9], \([0-9]*\)>.*/\1/p')
     python tools/ncu_lines.py $rep.ncu-rep $SO step_kernelILb1ELi$te > $OUT/${name}_lines.txt 2>&1
   fi
+  ncu -i $rep.ncu-rep --page source --csv 2>/dev/null | gzip > $OUT/${name}_source.csv.gz  # per-instruction stall reasons
   rm -f $rep.ncu-rep
 done
 ls -la $OUT

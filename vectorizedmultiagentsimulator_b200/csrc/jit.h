@@ -207,6 +207,13 @@ static std::string generate(const vmasb200_plan* pl, int te, int nt, JitLayout* 
     }
     for (int d = 0; d < kp.n_dyn; ++d) { frow[pl->dyn_list[d]] = n_srows; n_srows += 3; }
   }
+  // ... then (spec_helpers.cuh PARK) vx vy rot w of every dynamic entity and fx fy tq of every agent
+  // worth it when it frees enough registers for another warp per scheduler (football: 49 words, 197 -> 167 registers,
+  // 511 -> 417 us at 1 M envs); joint_passage's 22 words only grow its tile (3 -> 2 CTAs per SM: 3300 -> 3980 us)
+  bool park = big && 4 * kp.n_dyn + 3 * kp.A >= 32;
+  if (const char* e = getenv("VMASB200_JIT_PARK")) park = big && atoi(e) != 0;  // experiments
+  const int acc_row = kp.n_dyn > 0 && big ? frow[pl->dyn_list[0]] : 0, park_row = n_srows;
+  if (park) n_srows += 4 * kp.n_dyn + 3 * kp.A;
   lay->stat_tile_rows = n_srows;
   lay->tile_pos.assign(E, -1); lay->tile_trig.assign(E, -1); lay->tile_rot.assign(E, -1); lay->tile_fin.assign(E, -1);
   for (size_t e = 0; e < E && big; ++e) {
@@ -237,7 +244,8 @@ static std::string generate(const vmasb200_plan* pl, int te, int nt, JitLayout* 
     // BIG worlds: narrow phase shared out over the warp (spec_helpers.cuh narrow_coop); needs the warp's envs in one tile
     // (all threads carry an env: no LIDAR) and pair numbers that fit the queue's 11 bits
     const bool coop = big && kp.P < 2048 && !getenv("VMASB200_JIT_NOCOOP");
-    outf(s, "constexpr bool COOP = %s;\nconstexpr int TILE_ROWS = %d;\n", coop ? "true" : "false", n_srows);
+    outf(s, "constexpr bool COOP = %s, PARK = %s;\nconstexpr int TILE_ROWS = %d, PARK_ROW = %d, ACC_ROW = %d;\n", coop ? "true" : "false",
+         park ? "true" : "false", n_srows, park_row, acc_row);
     lay->coop = coop;
   }
   outf(s, "constexpr float SUB_DT = %s, KC = %s, KJ = %s, KT = %s, MARGIN = %s, XS = %s, YS = %s, WGX = %s, WGY = %s;\n",
@@ -456,9 +464,31 @@ static std::string generate(const vmasb200_plan* pl, int te, int nt, JitLayout* 
       outf(s, "#pragma unroll 1\n    for (int j = %d; j >= 0; --j) {\n      const float* sj = st.ss + j * (%d * NT);\n", r.n - 1, r.stride);
       outf(s, "      const uint32_t* th = RT%d + j * %d;\n      uint32_t v = 0u, sv = 0u;\n", run_of[(size_t)p], r.kc * 4);
       outf(s, "      const V2 ps = mk(sj[%d * NT], sj[%d * NT]);\n", r.s0, r.s0 + 1);
+      const bool packed = !getenv("VMASB200_JIT_NOF2");
       for (int i = 0; i < r.k; ++i) {
         const DItem& iti = pl->items[kp.J + p + i];
         const bool fr = !std::isinf(pl->broad[p + i].hx) || !std::isinf(pl->broad[p + i].hy);
+        if (packed && i + 1 < r.k) {  // rows i and i + 1 on the packed fp32 pipe when they share the frame (pair_l2)
+          const DItem& itn = pl->items[kp.J + p + i + 1];
+          const bool fr1 = !std::isinf(pl->broad[p + i + 1].hx) || !std::isinf(pl->broad[p + i + 1].hy);
+          const bool same_frame = fr == fr1 && (!fr || r.stat_is_a || iti.a == itn.a);
+          if (same_frame) {
+            const int d0 = dyn_slot[r.stat_is_a ? iti.b : iti.a], d1 = dyn_slot[r.stat_is_a ? itn.b : itn.a];
+            std::string qc = "0.f", qs = "0.f";
+            if (fr) {
+              qc.clear(); qs.clear();
+              if (r.stat_is_a) { outf(qc, "sj[%d * NT]", r.s0 + 3); outf(qs, "sj[%d * NT]", r.s0 + 4); }
+              else { outf(qc, "st.tc[%d]", trig_slot[iti.a]); outf(qs, "st.ts[%d]", trig_slot[iti.a]); }
+            }
+            const int c0 = r.cls[(size_t)i] * 4, c1 = r.cls[(size_t)i + 1] * 4;
+            outf(s, "      pair_l2<%d, %s, %s>(v, sv, ps, mk(st.px[%d], st.py[%d]), mk(st.px[%d], st.py[%d]), %s, %s", i, fr ? "true" : "false",
+                 r.stat_is_a ? "true" : "false", d0, d0, d1, d1, qc.c_str(), qs.c_str());
+            for (int c : {c0, c0 + 1, c0 + 2, c0 + 3, c1, c1 + 1, c1 + 2, c1 + 3}) outf(s, ", __uint_as_float(th[%d])", c);
+            s += ");\n";
+            ++i;
+            continue;
+          }
+        }
         const int dynE = r.stat_is_a ? (int)iti.b : (int)iti.a;
         std::string pd;
         outf(pd, "mk(st.px[%d], st.py[%d])", dyn_slot[dynE], dyn_slot[dynE]);
@@ -498,10 +528,10 @@ static std::string generate(const vmasb200_plan* pl, int te, int nt, JitLayout* 
         outf(s, "  st.ss[%d * NT] = st.tc[%d]; st.ss[%d * NT] = st.ts[%d];\n", drow[e] + 2, t, drow[e] + 3, t);
         if (pl->ents[e].shape == VMASB200_BOX) outf(s, "  st.ss[%d * NT] = st.tc2[%d]; st.ss[%d * NT] = st.ts2[%d];\n", drow[e] + 4, t, drow[e] + 5, t);
       }
-      outf(s, "  st.ss[%d * NT] = st.Fx[%d]; st.ss[%d * NT] = st.Fy[%d]; st.ss[%d * NT] = st.T[%d];\n", frow[e], d, frow[e] + 1, d, frow[e] + 2, d);
+      if (!park) outf(s, "  st.ss[%d * NT] = st.Fx[%d]; st.ss[%d * NT] = st.Fy[%d]; st.ss[%d * NT] = st.T[%d];\n", frow[e], d, frow[e] + 1, d, frow[e] + 2, d);
     }
     s += "  narrow_big(kp, st);\n";
-    for (int d = 0; d < kp.n_dyn; ++d) {
+    for (int d = 0; d < kp.n_dyn && !park; ++d) {
       const int e = pl->dyn_list[d];
       outf(s, "  st.Fx[%d] = st.ss[%d * NT]; st.Fy[%d] = st.ss[%d * NT]; st.T[%d] = st.ss[%d * NT];\n", d, frow[e], d, frow[e] + 1, d, frow[e] + 2);
     }

@@ -27,12 +27,30 @@ struct JointC {  // tables.h DItem of a joint
 constexpr int kND = ND > 0 ? ND : 1, kNST = NST > 0 ? NST : 1, kNA = NA > 0 ? NA : 1, kPW = PW > 0 ? PW : 1;
 constexpr int kNTR = NTR > 0 ? NTR : 1, kNJF = NJF > 0 ? NJF : 1;
 
+// PARK (BIG worlds): what the pair phase of a substep does not read - velocities, rotations, the agents' forces - and the
+// (Fx Fy T) accumulators (which the table-driven narrow phase adds to in the tile anyway) live in the thread's column of
+// the shared-memory tile instead of registers: football's kernel needed 197 registers (two warps per scheduler), and the
+// scheduler's register file holds three at 168.  Same syntax as the register arrays (st.vx[d]), literal rows after inlining.
+template <int STRIDE>
+struct TileArr {
+  float* p;  // row of element 0 in this thread's column
+  VB_DI float& operator[](int i) const { return p[i * (STRIDE * NT)]; }
+};
+template <bool B, class X, class Y> struct SelT { using type = X; };
+template <class X, class Y> struct SelT<false, X, Y> { using type = Y; };
+template <int STRIDE> VB_DI void park(TileArr<STRIDE>& a, float* col, int row) { a.p = col + row * NT; }
+template <int N> VB_DI void park(float (&)[N], float*, int) {}
+using DynArr = SelT<PARK, TileArr<1>, float[kND]>::type;
+using AgtArr = SelT<PARK, TileArr<1>, float[kNA]>::type;
+using AccArr = SelT<PARK, TileArr<3>, float[kND]>::type;
+
 struct St {
-  float px[kND], py[kND], vx[kND], vy[kND], rot[kND], w[kND];  // dynamic entities (dyn buffer rows)
+  float px[kND], py[kND];                                     // dynamic entities (dyn buffer rows)
+  DynArr vx, vy, rot, w;
   float sx[kNST], sy[kNST], srot[kNST];                       // static entities (stat buffer rows)
   float jfr[kNJF];                                            // per-env fixed rotations of joints (stat buffer rows)
-  float fx[kNA], fy[kNA], tq[kNA];                            // agent.state.force / torque, clamped in place
-  float Fx[kND], Fy[kND], T[kND];                             // accumulators of the running substep
+  AgtArr fx, fy, tq;                                          // agent.state.force / torque, clamped in place
+  AccArr Fx, Fy, T;                                           // accumulators of the running substep
   float tc[kNTR], ts[kNTR], tc2[kNTR], ts2[kNTR];             // cos/sin cache (step_kernel.cuh store_trig)
   uint32_t verd[kPW];                                         // World.collides verdict bits of the running substep
   uint32_t thin[kPW];                                         // thin events of the running substep (kernels.cuh)
@@ -277,19 +295,40 @@ VB_DI void pair_r(St& st, const EntC ea, const EntC eb, V2 pa, V2 pb, const Rot 
   }
 }
 
+// the bit of a row as ONE predicated OR behind its compare(s) (the compiler's own choice is a select per bit plus adds to
+// merge them: 48 of the 100 instructions of football's loop body)
+template <int i>
+VB_DI void bit_le(uint32_t& v, float d2, float t) {  // v |= (d2 <= t) << i
+  asm("{\n\t.reg .pred p;\n\tsetp.le.f32 p, %1, %2;\n\t@p or.b32 %0, %0, %3;\n\t}" : "+r"(v) : "f"(d2), "f"(t), "n"(1u << i));
+}
+template <int i>
+VB_DI void bit_ngt(uint32_t& s, float d2, float t) {  // s |= !(d2 > t) << i   (NaN passes, as in the generic broad phase)
+  asm("{\n\t.reg .pred p;\n\tsetp.gt.f32 p, %1, %2;\n\t@!p or.b32 %0, %0, %3;\n\t}" : "+r"(s) : "f"(d2), "f"(t), "n"(1u << i));
+}
+template <int i>
+VB_DI void bit_frame(uint32_t& s, float lx, float ly, float hx, float hy) {  // s |= !(|lx| > hx || |ly| > hy) << i
+  asm("{\n\t.reg .pred p;\n\t.reg .f32 a, b;\n\tabs.f32 a, %1;\n\tabs.f32 b, %2;\n\tsetp.gt.f32 p, a, %3;\n\tsetp.gt.or.f32 p, b, %4, p;\n\t"
+      "@!p or.b32 %0, %0, %5;\n\t}"
+      : "+r"(s) : "f"(lx), "f"(ly), "f"(hx), "f"(hy), "n"(1u << i));
+}
 // BIG worlds: the broad-phase row alone (kernels.cuh run_substeps: the verdict of World.collides and the conservative cull),
 // branch-free; the survivors are evaluated afterwards by narrow_big.
 template <int word, int bit, bool FRAME>
 VB_DI void pair_b(St& st, V2 pa, V2 pb, const Rot qa, float t2_bp, float t2_cull, float hx, float hy) {
   const float dx = pa.x - pb.x, dy = pa.y - pb.y;
   const float d2 = fmaf(dy, dy, dx * dx);
-  st.verd[word] |= (d2 <= t2_bp ? 1u : 0u) << bit;
-  bool sv = !(d2 > t2_cull);  // NaN passes, as in the generic broad phase
-  if (FRAME) {
+  bit_le<bit>(st.verd[word], d2, t2_bp);
+  if (FRAME && t2_cull == CUDART_INF_F) {  // plan.cpp: rows with a frame cull have no circle cull
     const float lx = fmaf(dx, qa.c, dy * qa.s), ly = fmaf(dx, qa.s, -(dy * qa.c));
-    sv = sv && !(fabsf(lx) > hx) && !(fabsf(ly) > hy);
+    bit_frame<bit>(st.sv[word], lx, ly, hx, hy);
+  } else {
+    bool sv = !(d2 > t2_cull);  // NaN passes, as in the generic broad phase
+    if (FRAME) {
+      const float lx = fmaf(dx, qa.c, dy * qa.s), ly = fmaf(dx, qa.s, -(dy * qa.c));
+      sv = sv && !(fabsf(lx) > hx) && !(fabsf(ly) > hy);
+    }
+    st.sv[word] |= (sv ? 1u : 0u) << bit;
   }
-  st.sv[word] |= (sv ? 1u : 0u) << bit;
 }
 // The same row inside a LOOPED run (jit.h: consecutive pairs of one list of dynamic entities against static entities whose
 // tile rows are a fixed stride apart run as a loop over the static entities - the straight-line list of football's 91 pairs
@@ -300,16 +339,37 @@ template <int i, bool FRAME>
 VB_DI void pair_l(uint32_t& v, uint32_t& s, V2 pa, V2 pb, float qc, float qs, float t2_bp, float t2_cull, float hx, float hy) {
   const float dx = pa.x - pb.x, dy = pa.y - pb.y;
   const float d2 = fmaf(dy, dy, dx * dx);
-  v |= (d2 <= t2_bp ? 1u : 0u) << i;
-  bool sv;
+  bit_le<i>(v, d2, t2_bp);
   if (FRAME) {
     const float lx = fmaf(dx, qc, dy * qs), ly = fmaf(dx, qs, -(dy * qc));
-    const bool ox = fabsf(lx) > hx, oy = fabsf(ly) > hy;  // both evaluated (no short circuit: the loop stays branch-free)
-    sv = !(ox | oy);
+    bit_frame<i>(s, lx, ly, hx, hy);
   } else {
-    sv = !(d2 > t2_cull);  // NaN passes, as in the generic broad phase
+    bit_ngt<i>(s, d2, t2_cull);
   }
-  s |= (sv ? 1u : 0u) << i;
+}
+// Two rows of a block at once (bits i and i + 1; the same static partner `ps`, dynamic partners b0 / b1) on the packed fp32
+// pipe of sm_100 (FADD2 / FMUL2 / FFMA2: two IEEE fp32 operations per instruction, each rounded like its scalar twin, so
+// the bits are pair_l's).  STAT_A: the static entity is the pair's a (dx = ps - b), else its b (dx = b - ps).
+template <int i, bool FRAME, bool STAT_A>
+VB_DI void pair_l2(uint32_t& v, uint32_t& s, V2 ps, V2 b0, V2 b1, float qc, float qs, float t2_bp0, float t2_cull0, float hx0, float hy0,
+                   float t2_bp1, float t2_cull1, float hx1, float hy1) {
+  const float2 sx = make_float2(ps.x, ps.x), sy = make_float2(ps.y, ps.y);
+  const float2 bx = make_float2(b0.x, b1.x), by = make_float2(b0.y, b1.y);
+  const float2 dx = STAT_A ? __fadd2_rn(sx, make_float2(-bx.x, -bx.y)) : __fadd2_rn(bx, make_float2(-sx.x, -sx.y));
+  const float2 dy = STAT_A ? __fadd2_rn(sy, make_float2(-by.x, -by.y)) : __fadd2_rn(by, make_float2(-sy.x, -sy.y));
+  const float2 d2 = __ffma2_rn(dy, dy, __fmul2_rn(dx, dx));
+  bit_le<i>(v, d2.x, t2_bp0);
+  bit_le<i + 1>(v, d2.y, t2_bp1);
+  if (FRAME) {
+    const float2 c2 = make_float2(qc, qc), s2 = make_float2(qs, qs);
+    const float2 lx = __ffma2_rn(dx, c2, __fmul2_rn(dy, s2));
+    const float2 ly = __ffma2_rn(dx, s2, __fmul2_rn(make_float2(-dy.x, -dy.y), c2));  // (-dy) * c == -(dy * c)
+    bit_frame<i>(s, lx.x, ly.x, hx0, hy0);
+    bit_frame<i + 1>(s, lx.y, ly.y, hx1, hy1);
+  } else {
+    bit_ngt<i>(s, d2.x, t2_cull0);
+    bit_ngt<i + 1>(s, d2.y, t2_cull1);
+  }
 }
 // shift a block's k bits into a run's W-word accumulator (blocks are visited last to first: block 0 ends at bit 0)
 template <int W, int k>

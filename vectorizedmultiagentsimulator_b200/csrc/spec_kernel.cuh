@@ -162,6 +162,9 @@ vmasb200_step_world(const __grid_constant__ KParams kp, const __grid_constant__ 
   St st;
   st.ss = BIG ? smem + tid : nullptr;  // static tile of a pair-heavy world (non-LIDAR): TILE_ROWS rows of NT columns
   st.coop = BIG && COOP ? smem + TILE_ROWS * NT + (tid >> 5) * kCoopWords : nullptr;  // ... then every warp's scratch (narrow_coop)
+  park(st.vx, st.ss, PARK_ROW); park(st.vy, st.ss, PARK_ROW + ND); park(st.rot, st.ss, PARK_ROW + 2 * ND); park(st.w, st.ss, PARK_ROW + 3 * ND);
+  park(st.fx, st.ss, PARK_ROW + 4 * ND); park(st.fy, st.ss, PARK_ROW + 4 * ND + NA); park(st.tq, st.ss, PARK_ROW + 4 * ND + 2 * NA);
+  park(st.Fx, st.ss, ACC_ROW); park(st.Fy, st.ss, ACC_ROW + 1); park(st.T, st.ss, ACC_ROW + 2);
   int taint = 0;  // 0, or 1 + the env's index in sa.u_list (kernels.cuh run_substeps)
   if (phys) {
     world_load(st, aio, sa, env);
