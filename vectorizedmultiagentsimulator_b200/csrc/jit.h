@@ -48,6 +48,7 @@ struct DriverApi {
   int (*MemcpyHtoD)(unsigned long long, const void*, size_t) = nullptr;
   int (*FuncSetAttribute)(void*, int, int) = nullptr;
   int (*LaunchKernel)(void*, unsigned, unsigned, unsigned, unsigned, unsigned, unsigned, unsigned, void*, void**, void**) = nullptr;
+  int (*LaunchKernelEx)(const void*, void*, void**, void**) = nullptr;  // optional (CUDA >= 11.8): programmatic dependent launch
   bool ok = false;
 };
 static std::mutex g_jit_mu;
@@ -83,6 +84,7 @@ static bool load_driver() {
          sym(d.h, "cuModuleGetFunction", d.ModuleGetFunction) && sym(d.h, "cuModuleGetGlobal_v2", d.ModuleGetGlobal) &&
          sym(d.h, "cuMemcpyHtoD_v2", d.MemcpyHtoD) && sym(d.h, "cuFuncSetAttribute", d.FuncSetAttribute) &&
          sym(d.h, "cuLaunchKernel", d.LaunchKernel);
+  sym(d.h, "cuLaunchKernelEx", d.LaunchKernelEx);
   return d.ok;
 }
 static int jit_mode() {  // 0 off, 1 worlds the compiled kernel is measured to win on, 2 every world the generator covers
@@ -236,7 +238,10 @@ static std::string generate(const vmasb200_plan* pl, int te, int nt, JitLayout* 
        big ? "true" : "false");
   {
     // resident CTAs per SM the register allocator must leave room for (VMASB200_JIT_MINB, experiments only)
-    int minb = 1;  // measured (tools/ab_big2.sh): capping the registers of the BIG variant below its natural 168 trades the occupancy for spills one to one
+    // 32-env tiles of a LIDAR world (128 threads) serve batches up to 48 K envs: 32 768 envs are 1024 CTAs, which fit the 148
+    // SMs in ONE wave only at 7 CTAs per SM, i.e. at most 72 registers (navigation compiled to 80: 888 resident CTAs and a
+    // second wave of 136)
+    int minb = (lidar && te == 32 && nt == 128) ? 7 : 1;  // otherwise measured (tools/ab_big2.sh): capping the registers of the BIG variant below its natural 168 trades the occupancy for spills one to one
     if (const char* e = getenv("VMASB200_JIT_MINB")) minb = std::max(1, atoi(e));
     outf(s, "constexpr int MINB = %d;\n", minb);
   }

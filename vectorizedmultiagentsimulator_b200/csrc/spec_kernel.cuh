@@ -149,6 +149,10 @@ vmasb200_step_world(const __grid_constant__ KParams kp, const __grid_constant__ 
   __shared__ int s_last;
   __shared__ int s_qn[2];  // LIDAR: queued pairs, queued rays
   const int tid = threadIdx.x;
+  // programmatic dependent launch (vmasb200.cu): nothing of the previous grid on the stream may be read or written before
+  // this returns (at once when the launch carries no such dependency); the next grid may be set up from here on
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   bool counted = false;  // the CTA is in sa.counters[0] and s_last is valid
   if (LIDAR && LIDAR_COMPILED) {  // before the physics, so that the epilogue needs no barrier of its own for it
     if (tid < 2) s_qn[tid] = 0;

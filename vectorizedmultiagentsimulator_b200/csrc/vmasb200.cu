@@ -7,6 +7,7 @@
 #include <memory>
 #include <mutex>
 #include <new>
+#include <cuda.h>  // types of cuLaunchKernelEx only: the driver entry points are resolved with dlsym (jit.h)
 
 #include "kernels.cuh"
 #include "queries.cuh"
@@ -264,7 +265,26 @@ static int launch_step(vmasb200_plan* pl, const vmasb200_step_io* io, long long 
       KParams jkp = jk->kp;
       void* args[3] = {&jkp, &aio, &sa};
       const unsigned jgrid = (unsigned)((env_end - env_begin + jte - 1) / jte);
-      const int rc = g_drv.LaunchKernel(jk->func, jgrid, 1, 1, (unsigned)jk->nt, 1, 1, (unsigned)jk->smem_bytes, st, args, nullptr);
+      // Programmatic dependent launch: the kernel starts with griddepcontrol.wait + launch_dependents (spec_kernel.cuh), so a
+      // step launched right behind another one on the stream is set up on the SMs while its predecessor drains and only its
+      // first instruction waits for that grid to complete (with its memory visible).  Any other predecessor (a torch kernel,
+      // a copy) simply completes first, as without the attribute.  Not inside a stream capture.
+      static const bool pdl = [] { const char* e = getenv("VMASB200_PDL"); return !(e && e[0] == '0'); }();
+      int rc;
+      if (pdl && !capturing && g_drv.LaunchKernelEx) {
+        CUlaunchAttribute attr{};
+        attr.id = CU_LAUNCH_ATTRIBUTE_PROGRAMMATIC_STREAM_SERIALIZATION;
+        attr.value.programmaticStreamSerializationAllowed = 1;
+        CUlaunchConfig cfg{};
+        cfg.gridDimX = jgrid; cfg.gridDimY = 1; cfg.gridDimZ = 1;
+        cfg.blockDimX = (unsigned)jk->nt; cfg.blockDimY = 1; cfg.blockDimZ = 1;
+        cfg.sharedMemBytes = (unsigned)jk->smem_bytes;
+        cfg.hStream = reinterpret_cast<CUstream>(st);
+        cfg.attrs = &attr; cfg.numAttrs = 1;
+        rc = g_drv.LaunchKernelEx(&cfg, jk->func, args, nullptr);
+      } else {
+        rc = g_drv.LaunchKernel(jk->func, jgrid, 1, 1, (unsigned)jk->nt, 1, 1, (unsigned)jk->smem_bytes, st, args, nullptr);
+      }
       if (rc) { set_error("cuLaunchKernel(vmasb200_step_world) failed: CUresult " + std::to_string(rc)); return VMASB200_ERR_CUDA; }
       pl->jit_launches += 1;
       if (jk->thin_possible) {  // verification tail of the compiled launch (returns at once unless its last CTA asked)
