@@ -241,7 +241,9 @@ static std::string generate(const vmasb200_plan* pl, int te, int nt, JitLayout* 
     // 32-env tiles of a LIDAR world (128 threads) serve batches up to 48 K envs: 32 768 envs are 1024 CTAs, which fit the 148
     // SMs in ONE wave only at 7 CTAs per SM, i.e. at most 72 registers (navigation compiled to 80: 888 resident CTAs and a
     // second wave of 136)
-    int minb = (lidar && te == 32 && nt == 128) ? 7 : 1;  // otherwise measured (tools/ab_big2.sh): capping the registers of the BIG variant below its natural 168 trades the occupancy for spills one to one
+    // 64-env tiles (96 threads, large batches): 10 CTAs per SM = 64 registers (navigation compiles to 80 uncapped; 16 more
+    // bytes of spill; 125.8 -> 117.9 us at 1 M envs with the DIRECT epilogue's smaller tile)
+    int minb = (lidar && te == 32 && nt == 128) ? 7 : (lidar && te == 64 && nt == 96) ? 10 : 1;  // otherwise measured (tools/ab_big2.sh): capping the registers of the BIG variant below its natural 168 trades the occupancy for spills one to one
     if (const char* e = getenv("VMASB200_JIT_MINB")) minb = std::max(1, atoi(e));
     outf(s, "constexpr int MINB = %d;\n", minb);
   }
@@ -606,8 +608,17 @@ static std::string generate(const vmasb200_plan* pl, int te, int nt, JitLayout* 
   lay->smem_rows = 0;
   if (lc) {
     // shared-memory rows of the compiled epilogue: [env 3 per staged entity][work][lid R][queues: (NPT + R) 16-bit entries per env]
-    const int l_env = 0, l_work = l_env + 3 * (int)lay->lid_ents.size(), l_lid = l_work + lay->work_rows, l_q = l_lid + R;
+    // DIRECT: no readings tile.  The rows are filled with max_range in global memory at the START of the kernel (by the
+    // helper warps while the physics runs) and pass 3 stores its few hits over them; what is left of the tile's R rows is
+    // one word per sensor ("this ray is queued" bits).  Needs at most 32 rays per sensor.
+    // Measured (navigation): 128.6 -> 125.8 us at 1 M envs (-> 117.9 us with the occupancy the smaller tile allows), but
+    // 10.8 -> 11.1 us at 32 768 envs: the one-wave 32-env tiles keep the readings tile.
+    bool direct = te >= 64;
+    if (const char* e = getenv("VMASB200_JIT_LIDDIRECT")) direct = atoi(e) != 0;  // experiments
+    for (const DSensor& sn : pl->sensors) direct = direct && sn.n_rays <= 32;
+    const int l_env = 0, l_work = l_env + 3 * (int)lay->lid_ents.size(), l_lid = l_work + lay->work_rows, l_q = l_lid + (direct ? NS : R);
     lay->smem_rows = l_q + (NPT + R + 1) / 2;
+    outf(s, "constexpr bool DIRECT_LID = %s;\n", direct ? "true" : "false");
     outf(s, "constexpr int L_ENV = %d, L_WORK = %d, L_LID = %d, L_Q = %d;\n", l_env, l_work, l_lid, l_q);
     outf(s, "constexpr int NPT = %d, CB = %d, KB = %d, RAYS_TOTAL = %d;\n", NPT, CB, KB, R);
     // per (sensor, target) tables; a column whose entries are all equal becomes a literal
@@ -681,6 +692,21 @@ static std::string generate(const vmasb200_plan* pl, int te, int nt, JitLayout* 
       k = k2;
     }
     s += "}\n";
+    // DIRECT: the same fill in global memory (g = lidar_out + env0), by threads t of nth; vec: 16-byte stores are aligned
+    s += "VB_DI void world_lidar_fill(float* g, size_t ld, int n_cols, int t, int nth, bool vec) {\n";
+    for (size_t k = 0; k < pl->sensors.size();) {
+      size_t k2 = k;
+      int rows = 0;
+      while (k2 < pl->sensors.size() && pl->sensors[k2].max_range == pl->sensors[k].max_range) rows += pl->sensors[k2++].n_rays;
+      const std::string v = fl(pl->sensors[k].max_range);
+      outf(s, "  if (vec) { const float4 v = make_float4(%s, %s, %s, %s);\n"
+              "    for (int i = t; i < %d * (TE / 4); i += nth) { const int r = i / (TE / 4), c = (i %% (TE / 4)) * 4;\n"
+              "      if (c < n_cols) *reinterpret_cast<float4*>(g + (size_t)(%d + r) * ld + c) = v; }\n"
+              "  } else {\n    for (int i = t; i < %d * TE; i += nth) { const int r = i / TE, c = i %% TE; if (c < n_cols) g[(size_t)(%d + r) * ld + c] = %s; } }\n",
+           v.c_str(), v.c_str(), v.c_str(), v.c_str(), rows, pl->sensors[k].out_off, rows, pl->sensors[k].out_off, v.c_str());
+      k = k2;
+    }
+    s += "}\n";
     // pass 1: reach masks from the registers; every (sensor, target) within reach becomes one entry of the pair queue
     s += "VB_DI void world_lidar_pass1(const St& st, bool ok, int col, float* wcol, unsigned short* pq, int* qn) {\n  int n = 0;\n";
     for (int k = 0; k < NS; ++k) {
@@ -705,6 +731,7 @@ static std::string generate(const vmasb200_plan* pl, int te, int nt, JitLayout* 
     }
     s += "  }\n}\n";
   } else {
+    s += "constexpr bool DIRECT_LID = false;\nVB_DI void world_lidar_fill(float*, size_t, int, int, int, bool) {}\n";
     s += "constexpr int L_ENV = 0, L_WORK = 0, L_LID = 0, L_Q = 0;\nconstexpr int NPT = 1, CB = 0, KB = 0, RAYS_TOTAL = 1, SHARED_RAYS = 0;\n__constant__ float2 T_raycs[1] = {{0.f, 0.f}};\n"
          "VB_DI int p_es(int) { return 0; }\nVB_DI int p_cr(int) { return 0; }\nVB_DI int p_ts(int) { return 0; }\n"
          "VB_DI int p_out(int) { return 0; }\nVB_DI int p_nr(int) { return 0; }\nVB_DI int p_k(int) { return 0; }\n"

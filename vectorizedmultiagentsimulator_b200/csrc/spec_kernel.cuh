@@ -38,12 +38,15 @@ namespace vb {
 // It also counts the CTA as finished (sa.counters[0]) and leaves in *s_last whether it was the step's last one.
 namespace gen {
 constexpr int kRaySentinel = 0x7fc0dead;  // a NaN no range is equal to: "already queued"
-VB_DI void lidar_world(const KParams& kp, const StepArgs& sa, const Tile& t, const St& st, bool phys, bool ok, int* s_qn, int* s_last) {
+VB_DI void lidar_world(const KParams& kp, const StepArgs& sa, const Tile& t, const St& st, bool phys, bool ok, int* s_qn, int* s_last,
+                       long long env0) {
   const int tid = threadIdx.x;
   unsigned short* pq = reinterpret_cast<unsigned short*>(t.queue);  // [NPT * TE]
   unsigned short* rq = pq + NPT * TE;                                // [RAYS_TOTAL * TE]
-  world_lidar_init(t.lidS, tid);  // every ray starts at max_range
+  if (!DIRECT_LID) world_lidar_init(t.lidS, tid);  // every ray starts at max_range
   if (phys) {
+    if (DIRECT_LID)  // "queued" bits of the env's sensors (one word each)
+      for (int k = 0; k < (L_Q - L_LID); ++k) t.lidS[k * TE + tid] = 0.f;
     world_stage_lidar(st, t.envS + tid, t.workS + tid);
     world_lidar_pass1(st, ok, tid, t.workS + tid, pq, s_qn);
   }
@@ -81,8 +84,13 @@ VB_DI void lidar_world(const KParams& kp, const StepArgs& sa, const Tile& t, con
       const float lat = fabsf(u * cs.y - v * cs.x), along = u * cs.x + v * cs.y;
       return !(lat > lat_max) && !(along < along_min);
     };
-    auto push = [&](int r) {  // once per ray: its output cell is the flag
-      if (atomicExch(cell + r * TE, kRaySentinel) != kRaySentinel) rq[atomicAdd(s_qn + 1, 1)] = (unsigned short)(tag | (r << (CB + KB)));
+    uint32_t* queued = reinterpret_cast<uint32_t*>(t.lidS) + p_k(p) * TE + col;  // DIRECT_LID
+    auto push = [&](int r) {  // once per ray: its output cell (its bit of the sensor's word) is the flag
+      if (DIRECT_LID) {
+        if (!(atomicOr(queued, 1u << r) >> r & 1u)) rq[atomicAdd(s_qn + 1, 1)] = (unsigned short)(tag | (r << (CB + KB)));
+      } else {
+        if (atomicExch(cell + r * TE, kRaySentinel) != kRaySentinel) rq[atomicAdd(s_qn + 1, 1)] = (unsigned short)(tag | (r << (CB + KB)));
+      }
     };
 #ifdef VB_AB_DIRECT_PUSH
     if constexpr (SHARED_RAYS > 0) {
@@ -136,7 +144,8 @@ VB_DI void lidar_world(const KParams& kp, const StepArgs& sa, const Tile& t, con
       }
       best = pmin(best, d);
     }
-    t.lidS[(out + r) * TE + col] = best;
+    if (DIRECT_LID) sa.lidar_out[(size_t)(out + r) * sa.ld + env0 + col] = best;  // over the fill of the kernel's start
+    else t.lidS[(out + r) * TE + col] = best;
   }
   __syncthreads();
 }
@@ -163,6 +172,15 @@ vmasb200_step_world(const __grid_constant__ KParams kp, const __grid_constant__ 
   const bool phys = tid < TE;
   const bool ok = phys && tid < n_valid;
   const long long env = env0 + (ok ? tid : 0);
+  // LIDAR rows of the tile in global memory; the batch's last tile also carries the padding columns up to ld
+  const int n_cols = (int)min((long long)TE, (sa.env_end == sa.n_envs ? sa.ld : sa.env_end) - env0);
+  if (LIDAR && LIDAR_COMPILED && DIRECT_LID && sa.do_lidar && sa.lidar_out) {
+    // every ray starts at max_range: filled here by the helper warps (all threads when there are none), so that the stores
+    // drain while the physics runs; pass 3 of the epilogue stores the hits over them (two CTA barriers later)
+    const bool vec = ((n_cols | (int)(env0 & 3)) & 3) == 0;
+    if (NT > TE) { if (!phys) world_lidar_fill(sa.lidar_out + env0, (size_t)sa.ld, n_cols, tid - TE, NT - TE, vec); }
+    else world_lidar_fill(sa.lidar_out + env0, (size_t)sa.ld, n_cols, tid, NT, vec);
+  }
   St st;
   st.ss = BIG ? smem + tid : nullptr;  // static tile of a pair-heavy world (non-LIDAR): TILE_ROWS rows of NT columns
   st.coop = BIG && COOP ? smem + TILE_ROWS * NT + (tid >> 5) * kCoopWords : nullptr;  // ... then every warp's scratch (narrow_coop)
@@ -263,8 +281,7 @@ vmasb200_step_world(const __grid_constant__ KParams kp, const __grid_constant__ 
     }
     // LIDAR rows: 16-byte stores straight from the tile (rows are 16-byte aligned: ld % 4 == 0, env0 % TE == 0; a TMA
     // bulk store per row costs the issuing warp ~14 instructions per row, one lane at a time, and a wait before the CTA
-    // may leave).  The batch's last tile also carries the padding columns up to ld.
-    const int n_cols = (int)min((long long)TE, (sa.env_end == sa.n_envs ? sa.ld : sa.env_end) - env0);
+    // may leave).
     auto store_rows = [&]() {
       constexpr int LPR = TE / 4, RSTEP = NT / LPR;  // lanes per row, rows per sweep of the CTA
       const int rows = LIDAR_COMPILED ? RAYS_TOTAL : kp.lidar_rows;
@@ -285,7 +302,8 @@ vmasb200_step_world(const __grid_constant__ KParams kp, const __grid_constant__ 
       }
     };
     if (LIDAR_COMPILED) {
-      lidar_world(kp, sa, t, st, phys, ok, s_qn, &s_last);
+      lidar_world(kp, sa, t, st, phys, ok, s_qn, &s_last, env0);
+      if (!DIRECT_LID) {
 #ifdef VB_AB_TMA_STORE
       fence_proxy_async();
       __syncthreads();
@@ -297,6 +315,7 @@ vmasb200_step_world(const __grid_constant__ KParams kp, const __grid_constant__ 
 #else
       store_rows();
 #endif
+      }
 #ifndef VB_AB_LATE_COUNT
       counted = true;
 #endif
