@@ -532,6 +532,10 @@ def run_b200(args, rank, local_rank, world):
                                   if compiled else
                                   "SoA rows [field][env]; 128 threads per CTA, 128 / envs_per_cta of them share an env"),
                        "exact": int(args.exact), "speculation_repairs": repairs,
+                       "launch": ("consecutive steps are launched back to back on one stream with programmatic dependent launch "
+                                  "(griddepcontrol: a step's CTAs are set up while its predecessor drains, its first instruction waits "
+                                  "for that grid); ms_per_step is the period of that pipeline" if compiled and os.environ.get("VMASB200_PDL", "1") != "0"
+                                  else "consecutive steps serialised on one stream"),
                        "l2_resident_ms_per_step": ms_hot / K},
             "roofline": roofline_block(args, plan, wl.desc, n, ms / K, clocks, compiled, peak, peak_src),
             # one launch per step; a compiled world that can have thin contacts is followed by its 1-CTA repair_kernel
@@ -608,7 +612,7 @@ def run_e2e(plan, wl, n, K, world, dev):
     plan.step_host(dyn, stat, acts[0][0], acts[0][1], exact=False, want_masks=False, out=out)  # uploads state + static rows
     # one prepared C-ABI call per action buffer (plan.host_stepper: the ctypes call and nothing else)
     calls = [plan.host_stepper(n, ld, a[0], a[1], out[0], None, out[2]) for a in acts]
-    for i in range(3):
+    for i in range(20):  # the first calls pay for lazy driver work (pinned-buffer mappings, copy-engine warm-up): 0.28 -> 0.25 ms
         calls[i % 2]()
     if world > 1:
         dist.barrier()

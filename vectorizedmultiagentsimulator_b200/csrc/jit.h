@@ -109,8 +109,8 @@ static bool jit_eligible(const vmasb200_plan* pl, int te = 0) {  // te: the CTA 
   if (jit_mode() >= 2) return true;
   // Measured on B200 (profiles/README.md): everything in registers wins while the pair list is short or all
   // sphere-sphere (simple_spread 3.4x, transport 2.7x, navigation 2.3x at 1 M envs).  Pair-heavy worlds without LIDAR take
-  // the BIG variant (jit_big_world: static tile, straight-line broad phase, table-driven narrow phase): football 1.5x at
-  // 1 M envs, 1.1x at 32 K; joint_passage 1.13x.  Pair-heavy worlds WITH a LIDAR epilogue keep the generic kernel.
+  // the BIG variant (jit_big_world: static tile, looped broad phase, warp-cooperative table-driven narrow phase): football
+  // 2.5x at 1 M envs, 1.6x at 32 K; joint_passage 2x.  Pair-heavy worlds WITH a LIDAR epilogue keep the generic kernel.
   bool all_ss = kp.J == 0;
   for (int p = 0; p < kp.P && all_ss; ++p) all_ss = pl->items[kp.J + p].type == IT_SS;
   if (all_ss || (kp.P <= 32 && kp.J <= 2)) return true;
