@@ -605,6 +605,10 @@ repair_kernel(const __grid_constant__ KParams kp, const __grid_constant__ AgentI
   extern __shared__ __align__(16) float smem[];
   __shared__ int s_claim;
   const int tid = threadIdx.x;
+  // programmatic dependent launch (vmasb200.cu): set up while the step's grid still runs, reads nothing before that grid has
+  // completed; the next step's grid may be set up behind this one in turn (it waits for THIS grid, hence for both)
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   if (tid == 0) s_claim = atomicExch(sa.counters + 3, 0);
   __syncthreads();
   if (!s_claim) return;

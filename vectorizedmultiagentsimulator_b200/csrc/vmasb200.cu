@@ -289,7 +289,18 @@ static int launch_step(vmasb200_plan* pl, const vmasb200_step_io* io, long long 
       pl->jit_launches += 1;
       if (jk->thin_possible) {  // verification tail of the compiled launch (returns at once unless its last CTA asked)
         KParams gk = jk->kpg;
-        repair_kernel<false, 32><<<1, kThreads, smem_map(gk).total_bytes, st>>>(gk, aio, sa);
+        if (pdl && !capturing) {  // same linkage as the step's own launch: 6 us per step of launch gaps otherwise (transport)
+          cudaLaunchAttribute ra{};
+          ra.id = cudaLaunchAttributeProgrammaticStreamSerialization;
+          ra.val.programmaticStreamSerializationAllowed = 1;
+          cudaLaunchConfig_t rcfg{};
+          rcfg.gridDim = dim3(1); rcfg.blockDim = dim3(kThreads);
+          rcfg.dynamicSmemBytes = (size_t)smem_map(gk).total_bytes; rcfg.stream = st;
+          rcfg.attrs = &ra; rcfg.numAttrs = 1;
+          VB_CUDA(cudaLaunchKernelEx(&rcfg, repair_kernel<false, 32>, gk, aio, sa));
+        } else {
+          repair_kernel<false, 32><<<1, kThreads, smem_map(gk).total_bytes, st>>>(gk, aio, sa);
+        }
         pl->jit_tail_launches += 1;
       }
     } else {
