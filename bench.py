@@ -66,14 +66,26 @@ class ClockSampler:
         for line in self.p.stdout:
             self.rows.append([c.strip() for c in line.split(",")])
 
-    def stop(self):
+    def mark(self):
+        """the timed region starts here: only samples from now on count"""
+        self.first = len(self.rows)
+
+    def stop(self, busy=None):
+        """busy: a callable that keeps the GPU under the timed region's own load (the same launches, untimed).  A region of
+        a few milliseconds ends before nvidia-smi (one sample per 100 ms, slower to start with 8 ranks) has seen it, so the
+        same load is kept up until three samples exist (at most 3 s): the clocks reported are clocks UNDER this load."""
         if self.p is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
+        first = getattr(self, "first", 0)
+        t0 = time.time()
+        while busy is not None and len(self.rows) < first + 3 and time.time() - t0 < 3.0:
+            busy()
+        if busy is None:
+            time.sleep(0.15)
         self.p.terminate()
         sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
+        for r in self.rows[first:]:
             try:
                 sm.append(float(r[0])); mx.append(float(r[1]))
             except Exception:
@@ -82,7 +94,9 @@ class ClockSampler:
                 if v.lower().startswith("active"):
                     reasons.add(n)
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+                "reasons": sorted(reasons), "samples": len(sm),
+                "window": "from the start of the timed region; the same launches are kept up (untimed) until 3 samples exist"
+                          if busy is not None else "timed region + 0.15 s"}
 
 
 def dist_env():
@@ -499,10 +513,11 @@ def run_b200(args, rank, local_rank, world):
         torch.cuda.synchronize()
 
     # warm-up pass (also triggers the NVRTC build / cubin load), then the timed region with the clock sampler running
+    sampler = ClockSampler(local_rank)  # started early: nvidia-smi takes ~0.1 s to deliver its first sample
     time_steps(plan, ios, 3, W, barrier, torch)
-    sampler = ClockSampler(local_rank)
+    sampler.mark()
     ms = time_steps(plan, ios, K, W, barrier, torch)
-    clocks = sampler.stop()
+    clocks = sampler.stop(busy=lambda: time_steps(plan, ios, max(K, 200), 0, lambda: torch.cuda.synchronize(), torch))
     repairs = plan.sync_check(stream)
     if world > 1:
         t = torch.tensor([ms], device=dev)
@@ -564,8 +579,9 @@ def run_b200(args, rank, local_rank, world):
             time_steps(plan1, ios1, 3, 3, lambda: torch.cuda.synchronize(), torch)
             s1 = ClockSampler(local_rank)
             K1 = max(10, min(K, 50))
+            s1.mark()
             ms1 = time_steps(plan1, ios1, K1, 3, lambda: torch.cuda.synchronize(), torch)
-            ck1 = s1.stop()
+            ck1 = s1.stop(busy=lambda: time_steps(plan1, ios1, K1, 0, lambda: torch.cuda.synchronize(), torch))
             _, jl1 = plan1.jit(n1)
             r1 = roofline_block(args, plan1, wl1.desc, n1, ms1 / K1, ck1, jl1 > 0, peak, peak_src)
             r1.update({"value": n1 * K1 / (ms1 * 1e-3), "unit_value": "env-steps/s", "steps": K1, "clocks": ck1,

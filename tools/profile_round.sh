@@ -40,6 +40,7 @@ for sc in navigation transport simple_spread joint_passage football; do
 done
 for sc in navigation transport simple_spread joint_passage; do bench dropin-graph_$sc --impl dropin-graph --scenario $sc --steps 50; done
 fi
+if [ -n "$SKIP_NCU" ]; then ls $OUT | wc -l; exit 0; fi
 # 4. ncu: launch list of the driver's command, then one full capture per workload (only after the plain runs above)
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $OUT/launches_navigation.csv \
   $PY bench.py --steps 20 --warmup 3 --no-cpu-baseline > $OUT/launches_navigation.log 2>&1
