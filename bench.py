@@ -468,14 +468,28 @@ def roofline_block(args, plan, desc, n, ms_per_step, clocks, compiled, peak, pea
            "alg_bytes_per_env": plan.alg_bytes_per_env}
     fp32 = {"achieved": fp32_achieved, "peak": fpeak, "unit": "TFLOP/s", "frac": fp32_achieved / fpeak, "peak_source": fsrc,
             "alg_flops_per_env": flops, "flops_source": "SURVEY 8(d) per-primitive op counts of the reference (the kernel's culls execute fewer)"}
-    if cap.get("fp32_flops"):
-        # FP32 operations the kernel really executed (ncu: thread-level FADD + FMUL + 2 FFMA of one launch)
-        fp32["executed_flops_per_env"] = cap["fp32_flops"] / cap.get("n_envs", n)
-        fp32["executed_tflops"] = cap["fp32_flops"] / (ms_per_step * 1e-3) / 1e12
+    fcap = cap
+    if not fcap.get("fp32_flops"):  # no capture at this batch size: the per-env count of the same kernel's capture at another one
+        for other in (32768, 1 << 20):
+            c2 = ncu_capture(args.scenario, other, compiled)
+            if c2.get("fp32_flops"):
+                fcap = c2
+                break
+    if fcap.get("fp32_flops"):
+        # FP32 operations the kernel really executed (ncu: thread-level FADD + FMUL + 2 FFMA of one launch).  The algorithmic
+        # count above is the REFERENCE's (every narrow phase and every ray for every env); the kernel's exact
+        # verdicts and conservative culls skip what is provably zero, so `executed_frac` is the real load of the FP32 pipe
+        per_env = fcap["fp32_flops"] / fcap.get("n_envs", n)
+        fp32["executed_flops_per_env"] = per_env
+        fp32["executed_tflops"] = per_env * n / (ms_per_step * 1e-3) / 1e12
+        fp32["executed_frac"] = fp32["executed_tflops"] / fpeak
+        fp32["executed_source"] = f"ncu capture {args.scenario}@{fcap.get('n_envs', n)} (profiles/r2_traffic.json)"
     b = hbm if binding == "hbm" else fp32
     r = {"bound": binding, "achieved": b["achieved"], "peak": b["peak"], "unit": b["unit"], "frac": b["frac"],
          "traffic": cap.get("dram_bytes"), "hbm": hbm, "fp32": fp32, "num_envs": n, "ms_per_launch": ms_per_step,
          "kernel": "vmasb200_step_world (world-compiled, NVRTC)" if compiled else "vb::step_kernel"}
+    r["bound_rule"] = ("the roof whose ideal time for the ALGORITHMIC work of one launch is longer (SURVEY 8d bytes and the reference's "
+                       "op counts); fp32.executed_frac and issue.frac say how busy the FP32 pipe and the issue slots really are")
     if cap.get("warp_inst"):
         mhz = (clocks or {}).get("sm_mhz") or 1965.0
         ips = cap["warp_inst"] / (ms_per_step * 1e-3)
