@@ -7,7 +7,8 @@
 #include <memory>
 #include <mutex>
 #include <new>
-#include <cuda.h>  // types of cuLaunchKernelEx only: the driver entry points are resolved with dlsym (jit.h)
+#include <cuda.h>
+#include <nvtx3/nvToolsExt.h>  // header-only NVTX 3: a range costs one pointer test unless a tool (nsys, ncu --nvtx) is attached  // types of cuLaunchKernelEx only: the driver entry points are resolved with dlsym (jit.h)
 
 #include "kernels.cuh"
 #include "queries.cuh"
@@ -16,6 +17,15 @@
 #include "jit.h"
 
 namespace vb {
+
+// One NVTX range per C-ABI call that launches work (the reference has no tracing hooks at all): `nsys` / `ncu --nvtx`
+// show the step, its host-buffer pipeline, the queries, the action / reward / reset launches by name.
+struct NvtxRange {
+  explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
+  ~NvtxRange() { nvtxRangePop(); }
+  NvtxRange(const NvtxRange&) = delete;
+  NvtxRange& operator=(const NvtxRange&) = delete;
+};
 const char* last_error();
 
 #define VB_CUDA(call)                                                                          \
@@ -323,6 +333,7 @@ int vmasb200_version(void) { return VMASB200_ABI_VERSION; }
 const char* vmasb200_last_error(void) { return vb::last_error(); }
 
 int vmasb200_plan_create(const vmasb200_world_desc* desc, vmasb200_plan** out) {
+  NvtxRange nvtx_("vmasb200_plan_create");
   if (!out) { set_error("plan_create: out is NULL"); return VMASB200_ERR_INVALID; }
   *out = nullptr;
   vmasb200_plan* pl = new (std::nothrow) vmasb200_plan();
@@ -409,6 +420,7 @@ int vmasb200_jit_enable(int on) {
 }
 
 int vmasb200_plan_jit(vmasb200_plan* pl, int64_t n_envs, int32_t* state, int64_t* launches, int64_t* tail_launches) {
+  NvtxRange nvtx_("vmasb200_plan_jit");
   if (!pl) { set_error("plan_jit: NULL plan"); return VMASB200_ERR_INVALID; }
   std::string why;
   int st = 0;
@@ -425,6 +437,7 @@ int vmasb200_plan_jit(vmasb200_plan* pl, int64_t n_envs, int32_t* state, int64_t
 }
 
 int vmasb200_step(vmasb200_plan* pl, const vmasb200_step_io* io) {
+  NvtxRange nvtx_("vmasb200_step");
   if (!pl) { set_error("step: NULL plan"); return VMASB200_ERR_INVALID; }
   int rc = check_io(pl, io);
   if (rc) return rc;
@@ -465,6 +478,7 @@ static bool host_dev_ptr(const void* h, void** d) {
 int vmasb200_step_host(vmasb200_plan* pl, const float* h_dyn_in, const float* h_stat, const float* h_force,
                        const float* h_torque, float* h_dyn_out, float* h_act_out, float* h_lidar_out,
                        uint32_t* h_pair_active, int64_t n, int64_t ld, int32_t exact) {
+  NvtxRange nvtx_("vmasb200_step_host");
   if (!pl || n < 0 || ld < n || (ld & 3)) { set_error("step_host: bad argument (ld >= n_envs, ld % 4 == 0)"); return VMASB200_ERR_INVALID; }
   int rc = upload_plan(pl);
   if (rc) return rc;
@@ -577,6 +591,7 @@ int vmasb200_step_host(vmasb200_plan* pl, const float* h_dyn_in, const float* h_
 int vmasb200_cast_rays(vmasb200_plan* pl, const float* dyn, const float* stat, int64_t ld, int32_t entity,
                        const float* angles, int64_t angles_stride, int32_t n_rays, float max_range,
                        const int32_t* targets, int32_t n_targets, float* out, int64_t n, void* stream) {
+  NvtxRange nvtx_("vmasb200_cast_rays");
   if (!pl || !dyn || !angles || !out || n < 0 || ld < n || n_rays < 0 || n_targets < 0 || (n_targets && !targets)) {
     set_error("cast_rays: bad argument"); return VMASB200_ERR_INVALID;
   }
@@ -618,6 +633,7 @@ static int to_qpose(const vmasb200_pose* p, QPose* q, const char* who) {
 }
 
 int vmasb200_get_distance(const vmasb200_pose* a, const vmasb200_pose* b, float* out, int64_t n, void* stream) {
+  NvtxRange nvtx_("vmasb200_get_distance");
   QPose qa, qb;
   int rc;
   if ((rc = to_qpose(a, &qa, "get_distance")) || (rc = to_qpose(b, &qb, "get_distance"))) return rc;
@@ -629,6 +645,7 @@ int vmasb200_get_distance(const vmasb200_pose* a, const vmasb200_pose* b, float*
 }
 
 int vmasb200_is_overlapping(const vmasb200_pose* a, const vmasb200_pose* b, uint8_t* out, int64_t n, void* stream) {
+  NvtxRange nvtx_("vmasb200_is_overlapping");
   QPose qa, qb;
   int rc;
   if ((rc = to_qpose(a, &qa, "is_overlapping")) || (rc = to_qpose(b, &qb, "is_overlapping"))) return rc;
@@ -641,6 +658,7 @@ int vmasb200_is_overlapping(const vmasb200_pose* a, const vmasb200_pose* b, uint
 
 int vmasb200_get_distance_from_point(const vmasb200_pose* a, const float* points, int64_t points_stride,
                                      int64_t points_stride_xy, float* out, int64_t n, void* stream) {
+  NvtxRange nvtx_("vmasb200_get_distance_from_point");
   QPose qa;
   int rc;
   if ((rc = to_qpose(a, &qa, "get_distance_from_point"))) return rc;
@@ -654,6 +672,7 @@ int vmasb200_get_distance_from_point(const vmasb200_pose* a, const float* points
 int vmasb200_set_action(const float* action, int64_t stride_env, int64_t stride_k, int32_t action_size,
                         const float* u_range, const float* u_multiplier, int32_t clamp, float* u_out, int32_t* flags,
                         int64_t n, void* stream) {
+  NvtxRange nvtx_("vmasb200_set_action");
   if (!action || !u_range || !u_multiplier || !u_out || !flags || n < 0 || action_size < 1 || action_size > 8) {
     set_error("set_action: bad argument (1 <= action_size <= 8)"); return VMASB200_ERR_INVALID;
   }
@@ -669,6 +688,7 @@ int vmasb200_set_action(const float* action, int64_t stride_env, int64_t stride_
 
 int vmasb200_reset_rows(float* buf, int32_t row0, int32_t n_rows, int64_t ld, int64_t n, int64_t env_index, const uint8_t* mask,
                         void* stream) {
+  NvtxRange nvtx_("vmasb200_reset_rows");
   if (!buf || row0 < 0 || n_rows < 0 || n < 0 || ld < n || env_index >= n) { set_error("reset_rows: bad argument"); return VMASB200_ERR_INVALID; }
   if (n_rows == 0 || n == 0) return VMASB200_OK;
   const long long total = env_index >= 0 ? n_rows : (long long)n_rows * n;
@@ -680,6 +700,7 @@ int vmasb200_reset_rows(float* buf, int32_t row0, int32_t n_rows, int64_t ld, in
 
 int vmasb200_spawn_select(float* pos, const float* proposed, const float* occupied, int32_t n_occupied, float min_dist,
                           int32_t* flag, int64_t batch, void* stream) {
+  NvtxRange nvtx_("vmasb200_spawn_select");
   if (!pos || !proposed || !flag || batch < 0 || n_occupied < 0 || (n_occupied && !occupied)) {
     set_error("spawn_select: bad argument"); return VMASB200_ERR_INVALID;
   }
@@ -691,6 +712,7 @@ int vmasb200_spawn_select(float* pos, const float* proposed, const float* occupi
 }
 
 int vmasb200_set_action_ex(const vmasb200_action* a, int64_t n, void* stream) {
+  NvtxRange nvtx_("vmasb200_set_action_ex");
   if (!a || !a->action || !a->u_range || !a->u_multiplier || !a->u_out || !a->flags || n < 0 || a->action_size < 1 ||
       a->action_size > 8 || a->n_comm < 0 || a->n_comm > 64 || a->comm_col0 < 0 || (a->n_comm && !a->c_out)) {
     set_error("set_action_ex: bad argument (1 <= action_size <= 8, 0 <= n_comm <= 64, c_out when n_comm > 0)"); return VMASB200_ERR_INVALID;
@@ -710,6 +732,7 @@ int vmasb200_set_action_ex(const vmasb200_action* a, int64_t n, void* stream) {
 int vmasb200_set_action_discrete(const void* action, int32_t action_dtype, int64_t stride_env, int64_t stride_k,
                                  int32_t action_size, int32_t multidiscrete, const int32_t* nvec, const float* u_range,
                                  const float* u_multiplier, float* u_out, int32_t* flags, int64_t n, void* stream) {
+  NvtxRange nvtx_("vmasb200_set_action_discrete");
   if (!action || !nvec || !u_range || !u_multiplier || !u_out || !flags || n < 0 || action_size < 1 || action_size > 8 ||
       (action_dtype != VMASB200_I64 && action_dtype != VMASB200_I32)) {
     set_error("set_action_discrete: bad argument (1 <= action_size <= 8, int64 / int32 actions)"); return VMASB200_ERR_INVALID;
@@ -740,6 +763,7 @@ static DVec to_dvec(const vmasb200_vec& v) { DVec d; d.p = v.p; d.se = v.stride_
 
 int vmasb200_gather_obs(const vmasb200_obs_seg* segs, int32_t n_segs, float* const* outs, const int32_t* out_widths,
                         int32_t n_outs, int64_t n, void* stream) {
+  NvtxRange nvtx_("vmasb200_gather_obs");
   if (!segs || !outs || !out_widths || n < 0 || n_segs < 1 || n_segs > VMASB200_OBS_MAX_SEGS || n_outs < 1 ||
       n_outs > VMASB200_OBS_MAX_OUTS) {
     set_error("gather_obs: bad argument (1 <= n_segs <= 128, 1 <= n_outs <= 32)"); return VMASB200_ERR_INVALID;
@@ -780,6 +804,7 @@ int vmasb200_gather_obs(const vmasb200_obs_seg* segs, int32_t n_segs, float* con
 }
 
 int vmasb200_navigation_reward(const vmasb200_navigation* nv, int64_t n, void* stream) {
+  NvtxRange nvtx_("vmasb200_navigation_reward");
   if (!nv || n < 0 || nv->n_agents < 1 || nv->n_agents > VMASB200_NAV_MAX_AGENTS || !nv->pos_rew || !nv->final_rew ||
       !nv->all_goal_reached || !nv->pair_flags) {
     set_error("navigation_reward: bad argument (1 <= n_agents <= 16, output pointers)"); return VMASB200_ERR_INVALID;
@@ -866,6 +891,7 @@ int vmasb200_navigation_reward_static(const vmasb200_navigation* nv, int64_t n, 
 }
 
 int vmasb200_transport_reward(const vmasb200_transport* tr, int64_t n, void* stream) {
+  NvtxRange nvtx_("vmasb200_transport_reward");
   if (!tr || n < 0 || tr->n_packages < 1 || tr->n_packages > VMASB200_TRANSPORT_MAX_PACKAGES || !tr->rew) {
     set_error("transport_reward: bad argument (1 <= n_packages <= 8, rew)"); return VMASB200_ERR_INVALID;
   }
@@ -890,6 +916,7 @@ int vmasb200_transport_reward(const vmasb200_transport* tr, int64_t n, void* str
 }
 
 int vmasb200_simple_spread_reward(const vmasb200_simple_spread* sp, int64_t n, void* stream) {
+  NvtxRange nvtx_("vmasb200_simple_spread_reward");
   if (!sp || n < 0 || sp->n_agents < 1 || sp->n_agents > VMASB200_SPREAD_MAX || sp->n_landmarks < 0 ||
       sp->n_landmarks > VMASB200_SPREAD_MAX || !sp->rew) {
     set_error("simple_spread_reward: bad argument (1 <= n_agents <= 16, n_landmarks <= 16, rew)"); return VMASB200_ERR_INVALID;
@@ -911,6 +938,7 @@ int vmasb200_simple_spread_reward(const vmasb200_simple_spread* sp, int64_t n, v
 }
 
 int vmasb200_joint_passage_reward(const vmasb200_joint_passage* g, int64_t n, void* stream) {
+  NvtxRange nvtx_("vmasb200_joint_passage_reward");
   if (!g || n < 0 || g->n_agents < 1 || g->n_agents > 2 || g->n_bodies < g->n_agents || g->n_bodies > VMASB200_JP_MAX_BODIES ||
       g->n_passages < 1 || g->n_passages > VMASB200_JP_MAX_PASSAGES || g->n_walls < 0 || g->n_walls > VMASB200_JP_MAX_WALLS) {
     set_error("joint_passage_reward: bad argument (1..2 agents, <= 4 bodies, 1..24 passages, <= 8 walls)"); return VMASB200_ERR_INVALID;
@@ -966,6 +994,7 @@ int vmasb200_joint_passage_reward(const vmasb200_joint_passage* g, int64_t n, vo
 }
 
 int vmasb200_football_reward(const vmasb200_football* g, int64_t n, void* stream) {
+  NvtxRange nvtx_("vmasb200_football_reward");
   if (!g || n < 0 || !g->ball_pos.p || !g->ball_vel.p || !g->done) { set_error("football_reward: bad argument"); return VMASB200_ERR_INVALID; }
   static thread_local FbParams fb;
   fb.ball_pos = to_dvec(g->ball_pos); fb.ball_vel = to_dvec(g->ball_vel);
@@ -1003,6 +1032,7 @@ int vmasb200_football_reward(const vmasb200_football* g, int64_t n, void* stream
 }
 
 int vmasb200_sync_check(vmasb200_plan* pl, void* stream, int64_t* n_fixups) {
+  NvtxRange nvtx_("vmasb200_sync_check");
   VB_CUDA(cudaStreamSynchronize(static_cast<cudaStream_t>(stream)));
   VB_CUDA(cudaGetLastError());
   if (n_fixups) {
