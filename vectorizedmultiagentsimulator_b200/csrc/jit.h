@@ -243,14 +243,20 @@ static std::string generate(const vmasb200_plan* pl, int te, int nt, JitLayout* 
     // second wave of 136)
     // 64-env tiles (96 threads, large batches): 10 CTAs per SM = 64 registers (navigation compiles to 80 uncapped; 16 more
     // bytes of spill; 125.8 -> 117.9 us at 1 M envs with the DIRECT epilogue's smaller tile)
-    int minb = (lidar && te == 32 && nt == 128) ? 7 : (lidar && te == 64 && nt == 96) ? 10 : 1;  // otherwise measured (tools/ab_big2.sh): capping the registers of the BIG variant below its natural 168 trades the occupancy for spills one to one
+    // pair-heavy worlds: three warps per scheduler = at most 168 registers (joint_passage compiles to 172 uncapped)
+    int minb = (lidar && te == 32 && nt == 128) ? 7 : (lidar && te == 64 && nt == 96) ? 10 : big ? 384 / nt : 1;  // otherwise measured (tools/ab_big2.sh): capping the registers of the BIG variant below its natural 168 trades the occupancy for spills one to one
     if (const char* e = getenv("VMASB200_JIT_MINB")) minb = std::max(1, atoi(e));
     outf(s, "constexpr int MINB = %d;\n", minb);
   }
   {
     // BIG worlds: narrow phase shared out over the warp (spec_helpers.cuh narrow_coop); needs the warp's envs in one tile
     // (all threads carry an env: no LIDAR) and pair numbers that fit the queue's 11 bits
-    const bool coop = big && kp.P < 2048 && !getenv("VMASB200_JIT_NOCOOP");
+    bool has_bbox = false;
+    for (int p = 0; p < kp.P; ++p) has_bbox = has_bbox || pl->items[kp.J + p].type == IT_BB;
+    const bool coop = big && kp.P < 2048 && !has_bbox && !getenv("VMASB200_JIT_NOCOOP");  // box-box worlds: spec_helpers.cuh narrow_big
+    bool has_bl = false;
+    for (int p = 0; p < kp.P; ++p) has_bl = has_bl || pl->items[kp.J + p].type == IT_BL;
+    outf(s, "constexpr bool COOP_EDGES = %s;\n", coop && has_bl && !getenv("VMASB200_JIT_NOEDGES") ? "true" : "false");
     outf(s, "constexpr bool COOP = %s, PARK = %s;\nconstexpr int TILE_ROWS = %d, PARK_ROW = %d, ACC_ROW = %d;\n", coop ? "true" : "false",
          park ? "true" : "false", n_srows, park_row, acc_row);
     lay->coop = coop;

@@ -403,13 +403,10 @@ VB_DI uint32_t run_word(const uint32_t* a) {
 // order - the accumulation order per entity is the reference's (and narrow_big's), so the bits do not change.
 constexpr int kCoopQ = 64;                               // queue entries per pass (more survivors: several passes)
 constexpr int kCoopWords = kCoopQ / 2 + 4 * kCoopQ;      // 4-byte words per warp: u16 queue, then float4 results
-VB_DI void narrow_coop(const KParams& kp, St& st) {
+VB_DI void narrow_coop(const KParams& kp, St& st, const int cnt) {
   const int lane = threadIdx.x & 31;
   unsigned short* q = reinterpret_cast<unsigned short*>(st.coop);
   float4* res = reinterpret_cast<float4*>(st.coop + kCoopQ / 2);
-  int cnt = 0;
-#pragma unroll
-  for (int w = 0; w < PW; ++w) cnt += __popc(st.sv[w]);
   int incl = cnt;
 #pragma unroll
   for (int d = 1; d < 32; d <<= 1) {
@@ -439,12 +436,66 @@ VB_DI void narrow_coop(const KParams& kp, St& st) {
     const int n = min(kCoopQ, T - base);
     for (int e = lane; e < n; e += 32) {
       const int ent = q[e];
+      const DItem* it = kp.items + (NJ + (ent >> 5));
+      if (COOP_EDGES && it->type == IT_BL) continue;  // below, four lanes per entry
       EnvT<NT> E;
       E.env = col0 + (ent & 31); E.work = E.env;
       V2 fa;
       float ta, tb;
-      eval_item<false>(kp, kp.items + (NJ + (ent >> 5)), E, fa, ta, tb);
+      eval_item<false>(kp, it, E, fa, ta, tb);
       res[e] = make_float4(fa.x, fa.y, ta, tb);
+    }
+    if (COOP_EDGES) {
+      // box-line entries (eval_item IT_BL: closest_line_box = 4 box edges x a segment-segment closest-point search, ~1500
+      // instructions on ONE lane while the warp's other lanes idle: joint_passage's bar against the wall boxes): one lane per
+      // box EDGE, the four candidates folded in edge order exactly like closest_line_box's loop, the rest of the item by all
+      // four lanes alike.  Same functions, same operations per result: the bits do not change.
+      for (int e0 = 0; e0 < n; e0 += 32) {
+        const int e = e0 + lane;
+        const bool isbl = e < n && kp.items[NJ + (q[e < n ? e : 0] >> 5)].type == IT_BL;
+        uint32_t bm = __ballot_sync(0xffffffffu, isbl);
+        while (bm) {  // eight entries per round (warp-uniform loop)
+          const uint32_t sel = __fns(bm, 0, (lane >> 2) + 1);
+          const bool have = sel != 0xffffffffu;
+          const int ee = e0 + (have ? (int)sel : 0);
+          const int ent = q[have ? ee : 0];
+          const DItem* it = kp.items + (NJ + (ent >> 5));
+          EnvT<NT> E;
+          E.env = col0 + (ent & 31); E.work = E.env;
+          const DEnt* ea = &kp.ents[it->a];
+          const DEnt* eb = &kp.ents[it->b];
+          const V2 pa = pos_at(E, ea->pos_row), pb = pos_at(E, eb->pos_row);
+          const Rot qa = trig_of(E, ea), qb = trig_of(E, eb);
+          V2 p_box = vinf(), p_line = vinf();
+          float d = CUDART_INF_F;
+          if (have) {
+            const Edge ed = box_edge(lane & 3, pa, qa, ea->width, ea->length);
+            closest_points_line_line(ed.p, ed.c, ed.s, ed.len, pb, qb.c, qb.s, eb->length, p_box, p_line);
+            d = norm(p_box - p_line);
+          }
+          V2 b1 = vinf(), b2 = vinf();
+          float dist = CUDART_INF_F;
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const int src = (lane & ~3) + j;
+            const float dj = __shfl_sync(0xffffffffu, d, src);
+            const float bx = __shfl_sync(0xffffffffu, p_box.x, src), by = __shfl_sync(0xffffffffu, p_box.y, src);
+            const float lx = __shfl_sync(0xffffffffu, p_line.x, src), ly = __shfl_sync(0xffffffffu, p_line.y, src);
+            if (dj < dist) { b1 = mk(bx, by); b2 = mk(lx, ly); dist = dj; }
+          }
+          if (have) {
+            const V2 cbx = b1, cl = b2;
+            V2 ip = cbx;
+            float dd = 0.f;
+            if (!(ea->flags & VMASB200_E_HOLLOW)) ip = inner_point_box(cl, cbx, pa, dd);
+            const V2 fa = constraint_force(ip, cl, kLMD + dd, kp.Kc, kp.margin, false);
+            const float ta = cross(cbx - pa, fa), tb = cross(cl - pb, -fa);
+            if ((lane & 3) == 0) res[ee] = make_float4(fa.x, fa.y, ta, tb);
+          }
+#pragma unroll
+          for (int k8 = 0; k8 < 8; ++k8) bm &= bm - 1;
+        }
+      }
     }
     __syncwarp();
     {
@@ -468,7 +519,16 @@ VB_DI void narrow_coop(const KParams& kp, St& st) {
   }
 }
 VB_DI void narrow_big(const KParams& kp, St& st) {
-  if (COOP) { narrow_coop(kp, st); return; }
+  if (COOP) {
+    // (Worlds with box-box pairs do not share out - jit.h: when every lane has many survivors (waterfall's piled boxes, ~10
+    // each) 32 consecutive queue entries mix all pair types and every round runs the ~5000-flop box-box code, while lanes
+    // walking their OWN lists in pair order stay on one type together: 337 us own lists, 617 us shared out, 478 us generic.)
+    int cnt = 0;
+#pragma unroll
+    for (int w = 0; w < PW; ++w) cnt += __popc(st.sv[w]);
+    narrow_coop(kp, st, cnt);
+    return;
+  }
   EnvT<NT> E;
   E.env = st.ss; E.work = st.ss;
 #pragma unroll
@@ -492,8 +552,8 @@ template <int ACC, int da, int db, int jf>
 VB_DI void joint_r(St& st, const JointC jc, V2 pa, V2 pb, const Rot qa, const Rot qb, float ra, float rb) {
   V2 ja = pa + rotv(mk(jc.dax, jc.day), qa.c, qa.s);
   V2 jb = pb + rotv(mk(jc.dbx, jc.dby), qb.c, qb.s);
-  V2 att = constraint_force(ja, jb, jc.dist, KJ, MARGIN, true);
-  V2 rep = constraint_force(ja, jb, jc.dist, KJ, MARGIN, false);
+  V2 att, rep;
+  constraint_force_pair(ja, jb, jc.dist, KJ, MARGIN, att, rep);
   V2 fa = att + rep;
   V2 fb = (-att) + (-rep);
   float ta = cross(ja - pa, fa);

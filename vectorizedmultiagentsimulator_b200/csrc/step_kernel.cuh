@@ -191,8 +191,8 @@ VB_EVAL void eval_item(const KParams& kp, const DItem* __restrict__ it, const EV
       Rot qa = trig_of(E, ea), qb = trig_of(E, eb);
       V2 ja = pa + rotv(mk(it->dax, it->day), qa.c, qa.s);
       V2 jb = pb + rotv(mk(it->dbx, it->dby), qb.c, qb.s);
-      V2 att = constraint_force(ja, jb, it->dist, kp.Kj, k, true);
-      V2 rep = constraint_force(ja, jb, it->dist, kp.Kj, k, false);
+      V2 att, rep;
+      constraint_force_pair(ja, jb, it->dist, kp.Kj, k, att, rep);
       fa = att + rep;
       V2 fb = (-att) + (-rep);
       ta = cross(ja - pa, fa);
