@@ -456,6 +456,7 @@ static std::string generate(const vmasb200_plan* pl, int te, int nt, JitLayout* 
   }
   s += "}\n";
   // ---- joints, then pairs
+  std::vector<char> run_done(runs.size(), 0);
   s += "VB_DI void world_items(St& st, const KParams& kp) {\n";
   for (int j = 0; j < kp.J; ++j) {
     const DItem& it = pl->items[j];
@@ -469,54 +470,77 @@ static std::string generate(const vmasb200_plan* pl, int te, int nt, JitLayout* 
     const DBroad& b = pl->broad[p];
     const bool frame = !std::isinf(b.hx) || !std::isinf(b.hy);
     if (big && run_of[(size_t)p] >= 0) {
-      const Run& r = runs[(size_t)run_of[(size_t)p]];
-      if (p != r.p0) continue;  // the whole run is emitted at its first pair
-      const int W = (r.n * r.k + 31) / 32;
-      outf(s, "  {  // pairs %d .. %d: %d static entities x %d dynamic ones\n    uint32_t av[%d] = {}, as[%d] = {};\n", r.p0,
-           r.p0 + r.n * r.k - 1, r.n, r.k, W, W);
+      const int ri0 = run_of[(size_t)p];
+      const Run& r = runs[(size_t)ri0];
+      if (p != r.p0 || run_done[(size_t)ri0]) continue;  // the whole run is emitted at its first pair
+      // runs over the SAME static entities share one loop (joint_passage: the 13 wall boxes against the bar, then against the
+      // two agents): the static rows are loaded once per block, one loop overhead; every run keeps its own bit accumulators
+      std::vector<int> group{ri0};
+      for (size_t rj = (size_t)ri0 + 1; rj < runs.size() && !getenv("VMASB200_JIT_NOFUSE"); ++rj) {
+        const Run& o = runs[rj];
+        if (!run_done[rj] && o.n == r.n && o.s0 == r.s0 && o.stride == r.stride && o.stat_is_a == r.stat_is_a) group.push_back((int)rj);
+      }
+      s += "  {\n";
+      for (int ri : group) {
+        const Run& g = runs[(size_t)ri];
+        const int W = (g.n * g.k + 31) / 32;
+        outf(s, "    uint32_t av%d[%d] = {}, as%d[%d] = {};  // pairs %d .. %d: %d static entities x %d dynamic ones\n", ri, W, ri, W, g.p0,
+             g.p0 + g.n * g.k - 1, g.n, g.k);
+      }
       outf(s, "#pragma unroll 1\n    for (int j = %d; j >= 0; --j) {\n      const float* sj = st.ss + j * (%d * NT);\n", r.n - 1, r.stride);
-      outf(s, "      const uint32_t* th = RT%d + j * %d;\n      uint32_t v = 0u, sv = 0u;\n", run_of[(size_t)p], r.kc * 4);
       outf(s, "      const V2 ps = mk(sj[%d * NT], sj[%d * NT]);\n", r.s0, r.s0 + 1);
       const bool packed = !getenv("VMASB200_JIT_NOF2");
-      for (int i = 0; i < r.k; ++i) {
-        const DItem& iti = pl->items[kp.J + p + i];
-        const bool fr = !std::isinf(pl->broad[p + i].hx) || !std::isinf(pl->broad[p + i].hy);
-        if (packed && i + 1 < r.k) {  // rows i and i + 1 on the packed fp32 pipe when they share the frame (pair_l2)
-          const DItem& itn = pl->items[kp.J + p + i + 1];
-          const bool fr1 = !std::isinf(pl->broad[p + i + 1].hx) || !std::isinf(pl->broad[p + i + 1].hy);
-          const bool same_frame = fr == fr1 && (!fr || r.stat_is_a || iti.a == itn.a);
-          if (same_frame) {
-            const int d0 = dyn_slot[r.stat_is_a ? iti.b : iti.a], d1 = dyn_slot[r.stat_is_a ? itn.b : itn.a];
-            std::string qc = "0.f", qs = "0.f";
-            if (fr) {
-              qc.clear(); qs.clear();
-              if (r.stat_is_a) { outf(qc, "sj[%d * NT]", r.s0 + 3); outf(qs, "sj[%d * NT]", r.s0 + 4); }
-              else { outf(qc, "st.tc[%d]", trig_slot[iti.a]); outf(qs, "st.ts[%d]", trig_slot[iti.a]); }
+      for (int ri : group) {
+        const Run& g = runs[(size_t)ri];
+        run_done[(size_t)ri] = 1;
+        const int W = (g.n * g.k + 31) / 32, q0 = g.p0;
+        outf(s, "      const uint32_t* th%d = RT%d + j * %d;\n      uint32_t v%d = 0u, sv%d = 0u;\n", ri, ri, g.kc * 4, ri, ri);
+        for (int i = 0; i < g.k; ++i) {
+          const DItem& iti = pl->items[kp.J + q0 + i];
+          const bool fr = !std::isinf(pl->broad[q0 + i].hx) || !std::isinf(pl->broad[q0 + i].hy);
+          if (packed && i + 1 < g.k) {  // rows i and i + 1 on the packed fp32 pipe when they share the frame (pair_l2)
+            const DItem& itn = pl->items[kp.J + q0 + i + 1];
+            const bool fr1 = !std::isinf(pl->broad[q0 + i + 1].hx) || !std::isinf(pl->broad[q0 + i + 1].hy);
+            const bool same_frame = fr == fr1 && (!fr || g.stat_is_a || iti.a == itn.a);
+            if (same_frame) {
+              const int d0 = dyn_slot[g.stat_is_a ? iti.b : iti.a], d1 = dyn_slot[g.stat_is_a ? itn.b : itn.a];
+              std::string qc = "0.f", qs = "0.f";
+              if (fr) {
+                qc.clear(); qs.clear();
+                if (g.stat_is_a) { outf(qc, "sj[%d * NT]", g.s0 + 3); outf(qs, "sj[%d * NT]", g.s0 + 4); }
+                else { outf(qc, "st.tc[%d]", trig_slot[iti.a]); outf(qs, "st.ts[%d]", trig_slot[iti.a]); }
+              }
+              const int c0 = g.cls[(size_t)i] * 4, c1 = g.cls[(size_t)i + 1] * 4;
+              outf(s, "      pair_l2<%d, %s, %s>(v%d, sv%d, ps, mk(st.px[%d], st.py[%d]), mk(st.px[%d], st.py[%d]), %s, %s", i, fr ? "true" : "false",
+                   g.stat_is_a ? "true" : "false", ri, ri, d0, d0, d1, d1, qc.c_str(), qs.c_str());
+              for (int c : {c0, c0 + 1, c0 + 2, c0 + 3, c1, c1 + 1, c1 + 2, c1 + 3}) outf(s, ", __uint_as_float(th%d[%d])", ri, c);
+              s += ");\n";
+              ++i;
+              continue;
             }
-            const int c0 = r.cls[(size_t)i] * 4, c1 = r.cls[(size_t)i + 1] * 4;
-            outf(s, "      pair_l2<%d, %s, %s>(v, sv, ps, mk(st.px[%d], st.py[%d]), mk(st.px[%d], st.py[%d]), %s, %s", i, fr ? "true" : "false",
-                 r.stat_is_a ? "true" : "false", d0, d0, d1, d1, qc.c_str(), qs.c_str());
-            for (int c : {c0, c0 + 1, c0 + 2, c0 + 3, c1, c1 + 1, c1 + 2, c1 + 3}) outf(s, ", __uint_as_float(th[%d])", c);
-            s += ");\n";
-            ++i;
-            continue;
           }
+          const int dynE = g.stat_is_a ? (int)iti.b : (int)iti.a;
+          std::string pd;
+          outf(pd, "mk(st.px[%d], st.py[%d])", dyn_slot[dynE], dyn_slot[dynE]);
+          std::string qc = "0.f", qs = "0.f";
+          if (fr) {  // the frame is a's (plan.cpp: a = line / box)
+            if (g.stat_is_a) { qc.clear(); qs.clear(); outf(qc, "sj[%d * NT]", g.s0 + 3); outf(qs, "sj[%d * NT]", g.s0 + 4); }
+            else { qc.clear(); qs.clear(); outf(qc, "st.tc[%d]", trig_slot[iti.a]); outf(qs, "st.ts[%d]", trig_slot[iti.a]); }
+          }
+          const int c4 = g.cls[(size_t)i] * 4;
+          outf(s, "      pair_l<%d, %s>(v%d, sv%d, %s, %s, %s, %s, __uint_as_float(th%d[%d]), __uint_as_float(th%d[%d]), __uint_as_float(th%d[%d]), __uint_as_float(th%d[%d]));\n",
+               i, fr ? "true" : "false", ri, ri, g.stat_is_a ? "ps" : pd.c_str(), g.stat_is_a ? pd.c_str() : "ps", qc.c_str(), qs.c_str(), ri, c4, ri,
+               c4 + 1, ri, c4 + 2, ri, c4 + 3);
         }
-        const int dynE = r.stat_is_a ? (int)iti.b : (int)iti.a;
-        std::string pd;
-        outf(pd, "mk(st.px[%d], st.py[%d])", dyn_slot[dynE], dyn_slot[dynE]);
-        std::string qc = "0.f", qs = "0.f";
-        if (fr) {  // the frame is a's (plan.cpp: a = line / box)
-          if (r.stat_is_a) { qc.clear(); qs.clear(); outf(qc, "sj[%d * NT]", r.s0 + 3); outf(qs, "sj[%d * NT]", r.s0 + 4); }
-          else { qc.clear(); qs.clear(); outf(qc, "st.tc[%d]", trig_slot[iti.a]); outf(qs, "st.ts[%d]", trig_slot[iti.a]); }
-        }
-        const int c4 = r.cls[(size_t)i] * 4;
-        outf(s, "      pair_l<%d, %s>(v, sv, %s, %s, %s, %s, __uint_as_float(th[%d]), __uint_as_float(th[%d]), __uint_as_float(th[%d]), __uint_as_float(th[%d]));\n", i, fr ? "true" : "false",
-             r.stat_is_a ? "ps" : pd.c_str(), r.stat_is_a ? pd.c_str() : "ps", qc.c_str(), qs.c_str(), c4, c4 + 1, c4 + 2, c4 + 3);
+        outf(s, "      run_push<%d, %d>(av%d, v%d); run_push<%d, %d>(as%d, sv%d);\n", W, g.k, ri, ri, W, g.k, ri, ri);
       }
-      outf(s, "      run_push<%d, %d>(av, v); run_push<%d, %d>(as, sv);\n    }\n", W, r.k, W, r.k);
-      for (int tw = r.p0 >> 5; tw <= (r.p0 + r.n * r.k - 1) >> 5; ++tw)
-        outf(s, "    st.verd[%d] |= run_word<%d, %d, %d>(av); st.sv[%d] |= run_word<%d, %d, %d>(as);\n", tw, W, r.p0, tw, tw, W, r.p0, tw);
+      s += "    }\n";
+      for (int ri : group) {
+        const Run& g = runs[(size_t)ri];
+        const int W = (g.n * g.k + 31) / 32;
+        for (int tw = g.p0 >> 5; tw <= (g.p0 + g.n * g.k - 1) >> 5; ++tw)
+          outf(s, "    st.verd[%d] |= run_word<%d, %d, %d>(av%d); st.sv[%d] |= run_word<%d, %d, %d>(as%d);\n", tw, W, g.p0, tw, ri, tw, W, g.p0, tw, ri);
+      }
       s += "  }\n";
       continue;
     }
