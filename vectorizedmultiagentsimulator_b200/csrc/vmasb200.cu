@@ -3,6 +3,7 @@
 #include <algorithm>
 #include <cstdio>
 #include <cstdlib>
+#include <chrono>
 #include <cstring>
 #include <memory>
 #include <mutex>
@@ -20,9 +21,14 @@ namespace vb {
 
 // One NVTX range per C-ABI call that launches work (the reference has no tracing hooks at all): `nsys` / `ncu --nvtx`
 // show the step, its host-buffer pipeline, the queries, the action / reward / reset launches by name.
+static bool nvtx_on() {  // VMASB200_NVTX=0 switches the ranges off
+  static const bool on = [] { const char* e = getenv("VMASB200_NVTX"); return !(e && e[0] == '0'); }();
+  return on;
+}
 struct NvtxRange {
-  explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
-  ~NvtxRange() { nvtxRangePop(); }
+  bool on;
+  explicit NvtxRange(const char* name) : on(nvtx_on()) { if (on) nvtxRangePushA(name); }
+  ~NvtxRange() { if (on) nvtxRangePop(); }
   NvtxRange(const NvtxRange&) = delete;
   NvtxRange& operator=(const NvtxRange&) = delete;
 };
@@ -555,6 +561,11 @@ int vmasb200_step_host(vmasb200_plan* pl, const float* h_dyn_in, const float* h_
       }
     }
   }
+  // VMASB200_HOST_TRACE=1: where the host time of a call goes (enqueue of copies + launches vs waiting), every 100 calls
+  static const bool trace = std::getenv("VMASB200_HOST_TRACE") != nullptr;
+  static double tr_enq = 0, tr_wait = 0;
+  static long tr_n = 0;
+  const auto tr0 = std::chrono::steady_clock::now();
   // repairs so far (mapped host word the verifying CTA writes): every earlier step of this plan has been waited for
   const int repairs_before = *static_cast<volatile int*>(pl->h_repairs);
   for (int64_t k = 0; k < nchunk; ++k) {
@@ -573,7 +584,17 @@ int vmasb200_step_host(vmasb200_plan* pl, const float* h_dyn_in, const float* h_
     if (kp.n_dyn && (rc = launch_step(pl, &io, c0, c1))) return rc;
     if ((rc = d2h(c0, ncol, st))) return rc;
   }
+  const auto tr1 = std::chrono::steady_clock::now();
   for (int64_t k = 0; k < std::min<int64_t>(nchunk, kHostStreams); ++k) VB_CUDA(cudaStreamSynchronize(pl->streams[k]));
+  if (trace) {
+    const auto tr2 = std::chrono::steady_clock::now();
+    tr_enq += std::chrono::duration<double, std::micro>(tr1 - tr0).count();
+    tr_wait += std::chrono::duration<double, std::micro>(tr2 - tr1).count();
+    if (++tr_n % 100 == 0) {
+      fprintf(stderr, "libvmasb200 step_host: %ld calls, %lld chunks: enqueue %.1f us, wait %.1f us per call\n", tr_n, (long long)nchunk, tr_enq / 100, tr_wait / 100);
+      tr_enq = tr_wait = 0;
+    }
+  }
   if (nchunk > 1) {
     // a repair by the step's last CTA may have rewritten envs of a chunk whose results were already copied out
     if (*static_cast<volatile int*>(pl->h_repairs) != repairs_before) {
