@@ -258,7 +258,9 @@ int vmasb200_step(vmasb200_plan* plan, const vmasb200_step_io* io);
  * asynchronous; pageable ones still work).  h_force [n_envs][n_agents][2], h_torque [n_envs][n_agents] (either may
  * be NULL = zeros).  Output pointers may be NULL to skip that copy.  h_dyn_in / h_stat may be NULL from the second call on:
  * the step then starts from the state (static rows) the plan's device staging holds from the previous call of the same
- * batch size - a rollout through this entry point only moves the actions in and the results out.  h_pair_active / exact != 0 need the batch-wide
+ * batch size - a rollout through this entry point only moves the actions in and the results out.  Pinned (page-locked,
+ * mapped) h_force / h_torque of up to 131 072 envs are not copied: the kernel loads them over PCIe itself (they must stay
+ * unchanged until the call returns, which it does only after the step has completed).  h_pair_active / exact != 0 need the batch-wide
  * verdicts and therefore run the batch as ONE chunk.  Device staging is owned by the plan and grows on demand. */
 int vmasb200_step_host(vmasb200_plan* plan, const float* h_dyn_in, const float* h_stat, const float* h_force,
                        const float* h_torque, float* h_dyn_out, float* h_act_out, float* h_lidar_out,

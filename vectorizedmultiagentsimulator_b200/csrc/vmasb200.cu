@@ -566,6 +566,24 @@ int vmasb200_step_host(vmasb200_plan* pl, const float* h_dyn_in, const float* h_
   static double tr_enq = 0, tr_wait = 0;
   static long tr_n = 0;
   const auto tr0 = std::chrono::steady_clock::now();
+  // Actions straight from PINNED host memory (batches up to 131 072 envs; VMASB200_HOST_ACTIONS_DIRECT=0 switches it off):
+  // the kernel's force loads go over PCIe themselves instead of an H2D copy in front of the launch, and with the state
+  // resident the batch is ONE chunk - the per-step chain is launch -> D2H instead of two chunks of H2D -> launch -> D2H.
+  // Measured at 32 768 envs on one box: navigation 0.251 -> 0.229 ms per step, transport 0.170 -> 0.140, simple_spread
+  // 0.168 -> 0.099, football 0.274 -> 0.235.  Pageable buffers keep the copies.
+  static const bool act_direct = [] { const char* e = std::getenv("VMASB200_HOST_ACTIONS_DIRECT"); return !(e && std::atoi(e) == 0); }();
+  bool acts_mapped = false;
+  if (act_direct && !exact && n <= 131072 && (h_force || h_torque)) {
+    void *d_f = nullptr, *d_t = nullptr;
+    if (host_dev_ptr(h_force, &d_f) && host_dev_ptr(h_torque, &d_t)) {
+      acts_mapped = true;
+      if (!h_dyn_in) { nchunk = 1; csize = (n + 255) & ~int64_t(255); }
+      for (int a = 0; a < kp.A; ++a) {
+        fptr[a] = d_f ? static_cast<const float*>(d_f) + 2 * a : nullptr;
+        tptr[a] = d_t ? static_cast<const float*>(d_t) + a : nullptr;
+      }
+    }
+  }
   // repairs so far (mapped host word the verifying CTA writes): every earlier step of this plan has been waited for
   const int repairs_before = *static_cast<volatile int*>(pl->h_repairs);
   for (int64_t k = 0; k < nchunk; ++k) {
@@ -573,8 +591,8 @@ int vmasb200_step_host(vmasb200_plan* pl, const float* h_dyn_in, const float* h_
     const int64_t c0 = k * csize, c1 = std::min(n, c0 + csize), ncol = c1 - c0;
     if (kp.dyn_rows && h_dyn_in) VB_CUDA(rows2d(pl->d_dyn, dld, h_dyn_in, ld, c0, ncol, kp.dyn_rows, cudaMemcpyHostToDevice, st));
     if (kp.stat_rows && h_stat) VB_CUDA(rows2d(pl->d_stat, dld, h_stat, ld, c0, ncol, kp.stat_rows, cudaMemcpyHostToDevice, st));
-    if (kp.A && h_force) VB_CUDA(cudaMemcpyAsync(pl->d_force + c0 * 2 * kp.A, h_force + c0 * 2 * kp.A, (size_t)ncol * kp.A * 8, cudaMemcpyHostToDevice, st));
-    if (kp.A && h_torque) VB_CUDA(cudaMemcpyAsync(pl->d_torque + c0 * kp.A, h_torque + c0 * kp.A, (size_t)ncol * kp.A * 4, cudaMemcpyHostToDevice, st));
+    if (kp.A && h_force && !acts_mapped) VB_CUDA(cudaMemcpyAsync(pl->d_force + c0 * 2 * kp.A, h_force + c0 * 2 * kp.A, (size_t)ncol * kp.A * 8, cudaMemcpyHostToDevice, st));
+    if (kp.A && h_torque && !acts_mapped) VB_CUDA(cudaMemcpyAsync(pl->d_torque + c0 * kp.A, h_torque + c0 * kp.A, (size_t)ncol * kp.A * 4, cudaMemcpyHostToDevice, st));
     vmasb200_step_io io{};
     io.dyn_in = pl->d_dyn; io.dyn_out = pl->d_dyn; io.stat = pl->d_stat;
     io.force_ptrs = fptr; io.force_strides = fstr; io.torque_ptrs = tptr; io.torque_strides = tstr;
