@@ -76,3 +76,33 @@ def test_experiment_switches_are_part_of_the_cache_key(tmp_path, monkeypatch):
         now = {f for f in os.listdir(tmp_path) if f.endswith(".cubin")}
         assert len(now - seen) == 1, (defs, nt, now)
         seen = now
+
+
+@pytest.mark.skipif(not HAVE_NVRTC, reason="no libnvrtc in this image")
+def test_pair_heavy_worlds_get_the_looped_broad_phase(tmp_path, monkeypatch):
+    """The generator's shape for pair-heavy worlds: football's 70 line-sphere pairs are ONE loop over its 10
+    static lines (7 rows per block, packed in pairs), joint_passage's two runs over the 13 wall boxes share one loop, the
+    narrow phase is shared out over the warp, and football parks its cold state in the tile."""
+    import re
+
+    monkeypatch.setenv("VMASB200_JIT_CACHE", str(tmp_path))
+    src = {}
+    for name in ("football", "joint_passage", "waterfall"):
+        dump = tmp_path / f"{name}.cu"
+        monkeypatch.setenv("VMASB200_JIT_DUMP", str(dump))
+        L = _lib.lib()
+        prev = L.vmasb200_jit_enable(2)
+        try:
+            assert StepPlan(Fixture(name).desc).jit(1 << 20)[0] == 1, L.vmasb200_last_error()
+        finally:
+            L.vmasb200_jit_enable(prev)
+        src[name] = dump.read_text()
+    fb, jp, wf = src["football"], src["joint_passage"], src["waterfall"]
+    assert "BIG = true" in fb and "COOP = true, PARK = true" in fb
+    assert len(re.findall(r"for \(int j = 9; j >= 0; --j\)", fb)) == 1          # one loop over the 10 lines
+    assert fb.count("pair_l2<") == 3 and fb.count("pair_l<") == 1               # 7 rows per block: 3 packed pairs + 1
+    assert fb.count("pair_b<") == 21                                            # the sphere-sphere pairs stay unrolled
+    assert "COOP = true, PARK = false" in jp and "COOP_EDGES = true" in jp      # box-line pairs over four lanes
+    loops = re.findall(r"for \(int j = 12; j >= 0; --j\)", jp)
+    assert len(loops) == 1 and jp.count("uint32_t av") == 3                     # two runs over the 13 boxes in one loop, + the 4 lines
+    assert "COOP = false" in wf                                                 # box-box pairs: lanes keep their own lists
