@@ -380,3 +380,30 @@ def test_fallbacks_warn_once_and_strict_raises():
     b.strict = True
     with pytest.raises(VmasB200Error, match="strict"):
         env.step(acts)
+
+
+def test_invalidate_picks_up_attribute_changes():
+    """The reference re-reads entity attributes every step; the binding reads them when the plan is built.  After
+    binding.invalidate() a changed mass / max_speed is what the next step uses (and without it the old plan keeps running)."""
+    import torch
+
+    from vectorizedmultiagentsimulator_b200 import dropin
+
+    vmas = _vmas()
+    n = 64
+    ref = _make(vmas, "transport", dict(n_agents=4), n, 1)
+    env = _make(vmas, "transport", dict(n_agents=4), n, 1)
+    b = dropin.enable(env)
+    torch.manual_seed(11)
+    acts = [[torch.rand(n, 2, device="cuda") * 2 - 1 for _ in env.agents] for _ in range(8)]
+    for t in range(8):
+        if t == 4:  # heavier first agent, slower package - the same change on both worlds
+            for w in (ref.world, env.world):
+                w.agents[0]._mass = 5.0
+                w.agents[1]._max_speed = 0.05
+            builds = b.n_plan_builds
+            b.invalidate()
+        ref.step([a.clone() for a in acts[t]])
+        env.step([a.clone() for a in acts[t]])
+        assert torch.allclose(_state(ref), _state(env), rtol=1e-5, atol=1e-6), f"step {t}"
+    assert b.n_plan_builds == builds + 1

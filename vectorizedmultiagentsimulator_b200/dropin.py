@@ -101,6 +101,13 @@ class WorldBinding:
         self.n_fallback[kind] = self.n_fallback.get(kind, 0) + 1
 
     # ------------------------------------------------------------------ plan (re)build
+    def invalidate(self):
+        """The static description of the world changed outside a reset (a mass, max_speed, a force range, gravity, a collide flag
+        or collision filter, a joint, a LIDAR's targets): re-extract it before the next step.  The reference re-reads these
+        attributes every step; this binding reads them when the plan is built - at enable(), after every World.reset /
+        reset_at, and after invalidate().  Cheap when nothing changed (one description compare)."""
+        self.dirty = True
+
     def refresh(self):
         """Re-extract the static description (entity table, collision filters, joints, sensors); rebuild the plan and
         the buffers only when it changed (collision filters may depend on state set at reset: joint_passage.py:615-622)."""
